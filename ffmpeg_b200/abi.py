@@ -1,0 +1,63 @@
+"""ctypes / numpy mirrors of the POD structs declared in include/vvc_b200.h.
+
+These are shared by the product binding (ffmpeg_b200.lib), by bench.py and by the test oracle
+loaders (oracle/refapi.py, oracle/portapi.py); sizes are asserted against the C side at load time.
+"""
+import ctypes as C
+
+import numpy as np
+
+# enum TxType (reference: libavcodec/vvc/vvcdsp.h:30-35)
+DCT2, DST7, DCT8 = 0, 1, 2
+
+TB_TS, TB_BDPCM, TB_BDPCM_VERT, TB_DEP_QUANT = 1, 2, 4, 8
+TB_SCALING, TB_INTER, TB_JOINT, TB_JOINT_SHIFT, TB_LMCS_SCALE = 16, 32, 64, 128, 256
+
+# VVCB200TransformBlock
+TB_DTYPE = np.dtype([
+    ("x0", "<u2"), ("y0", "<u2"), ("c_idx", "u1"), ("log2_w", "u1"), ("log2_h", "u1"),
+    ("nzw", "u1"), ("nzh", "u1"), ("trh", "u1"), ("trv", "u1"), ("qp", "u1"),
+    ("flags", "<u2"), ("lfnst", "u1"), ("reserved", "u1"), ("lmcs_scale", "<u2"),
+    ("reserved2", "<u2"), ("coeff_off", "<u4"),
+], align=False)
+assert TB_DTYPE.itemsize == 24
+
+
+class ResidualParams(C.Structure):
+    _fields_ = [
+        ("bit_depth", C.c_int32), ("log2_transform_range", C.c_int32),
+        ("joint_c_sign", C.c_int32), ("reserved", C.c_int32),
+        ("scaling_matrix_rec", (C.c_uint8 * 64) * 28),
+        ("scaling_matrix_dc_rec", C.c_uint8 * 14),
+        ("pad", C.c_uint8 * 2),
+    ]
+
+
+class Planes(C.Structure):
+    """VVCB200Planes (device pointers) and oracle VVCRefPlanes (host pointers) share this layout."""
+    _fields_ = [
+        ("plane", C.c_void_p * 3), ("stride", C.c_int32 * 3),
+        ("width", C.c_int32 * 3), ("height", C.c_int32 * 3),
+    ]
+
+
+def residual_params(bit_depth=10, joint_c_sign=1, scaling=None, dc=None):
+    p = ResidualParams()
+    p.bit_depth, p.log2_transform_range, p.joint_c_sign = bit_depth, 15, joint_c_sign
+    m = np.full((28, 64), 16, np.uint8) if scaling is None else np.ascontiguousarray(scaling, np.uint8)
+    d = np.full(14, 16, np.uint8) if dc is None else np.ascontiguousarray(dc, np.uint8)
+    C.memmove(p.scaling_matrix_rec, m.ctypes.data, 28 * 64)
+    C.memmove(p.scaling_matrix_dc_rec, d.ctypes.data, 14)
+    return p
+
+
+def host_planes(arrays):
+    """Planes struct over a list of three 2-D uint16 numpy arrays (row stride taken from the array)."""
+    p = Planes()
+    for c, a in enumerate(arrays):
+        assert a.dtype == np.uint16 and a.ndim == 2 and a.strides[1] == 2
+        p.plane[c] = a.ctypes.data
+        p.stride[c] = a.strides[0]
+        p.width[c] = a.shape[1]
+        p.height[c] = a.shape[0]
+    return p

@@ -1,0 +1,51 @@
+// runtime.cu — error reporting, launch accounting and device queries behind the C ABI.
+#include <atomic>
+#include <stdarg.h>
+#include <string.h>
+#include "common.cuh"
+
+namespace vvcb200 {
+
+static thread_local char g_err[512] = "";
+static std::atomic<uint64_t> g_launches{0};
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line)
+{
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    return e == cudaErrorMemoryAllocation ? VVCB200_ERR_NOMEM : VVCB200_ERR_CUDA;
+}
+
+void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+int sm_count()
+{
+    static int cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return 148;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+            n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+}  // namespace vvcb200
+
+extern "C" {
+
+const char *vvcb200_last_error(void) { return vvcb200::g_err; }
+int vvcb200_abi_version(void) { return VVCB200_ABI_VERSION; }
+uint64_t vvcb200_launch_count(void) { return vvcb200::g_launches.load(std::memory_order_relaxed); }
+
+}

@@ -1,0 +1,88 @@
+"""ctypes binding of libvvcb200.so (the C ABI in include/vvc_b200.h).
+
+There is deliberately no fallback: if the shared library is missing, or CUDA is unusable, calls raise.
+Device memory in tests/bench is plain torch CUDA tensors; only raw pointers cross the ABI.
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(_HERE, "libvvcb200.so")
+_lib = None
+
+
+class VVCB200Error(RuntimeError):
+    pass
+
+
+def load():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO):
+            raise VVCB200Error("%s is missing: run `python -m ffmpeg_b200.build` (no CPU fallback exists)" % SO)
+        _lib = C.CDLL(SO)
+        _lib.vvcb200_last_error.restype = C.c_char_p
+        _lib.vvcb200_launch_count.restype = C.c_uint64
+        if _lib.vvcb200_abi_version() != 1:
+            raise VVCB200Error("ABI version mismatch")
+    return _lib
+
+
+def check(rc):
+    if rc != 0:
+        raise VVCB200Error("vvcb200 error %d: %s" % (rc, load().vvcb200_last_error().decode()))
+
+
+def launch_count():
+    return int(load().vvcb200_launch_count())
+
+
+def _ptr(t):
+    """Raw device/host pointer of a torch tensor, numpy array or int."""
+    if t is None:
+        return None
+    if hasattr(t, "data_ptr"):
+        return C.c_void_p(t.data_ptr())
+    if isinstance(t, np.ndarray):
+        return C.c_void_p(t.ctypes.data)
+    return C.c_void_p(int(t))
+
+
+def _stream(stream):
+    if stream is None:
+        import torch
+        return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(int(stream))
+
+
+def device_planes(tensors):
+    """VVCB200Planes over three 2-D torch CUDA tensors of dtype int16/uint16 (row stride from the tensor)."""
+    p = abi.Planes()
+    for c, t in enumerate(tensors):
+        assert t.is_cuda and t.dim() == 2 and t.element_size() == 2 and t.stride(1) == 1
+        p.plane[c] = t.data_ptr()
+        p.stride[c] = t.stride(0) * 2
+        p.width[c] = t.shape[1]
+        p.height[c] = t.shape[0]
+    return p
+
+
+def residual_batch(dst, levels, tbs, n, params, residual=None, stream=None):
+    """vvcb200_residual_batch: dst/residual are device_planes() structs (or None), levels/tbs device tensors."""
+    check(load().vvcb200_residual_batch(
+        C.byref(dst) if dst is not None else None, C.byref(residual) if residual is not None else None,
+        _ptr(levels), _ptr(tbs), int(n), C.byref(params), _stream(stream)))
+
+
+def dsp_itx_batch(coeffs, block_off, tbs, n, log2_transform_range=15, bit_depth=10, stream=None):
+    check(load().vvcb200_dsp_itx_batch(_ptr(coeffs), _ptr(block_off), _ptr(tbs), int(n),
+                                       int(log2_transform_range), int(bit_depth), _stream(stream)))
+
+
+def dsp_add_residual_batch(dst, res, block_off, tbs, n, bit_depth=10, stream=None):
+    check(load().vvcb200_dsp_add_residual_batch(C.byref(dst), _ptr(res), _ptr(block_off), _ptr(tbs), int(n),
+                                                int(bit_depth), _stream(stream)))

@@ -1,0 +1,197 @@
+"""Synthetic "parsed picture" generator (host side, numpy): the descriptor batches a VVC parser would emit.
+
+There are no VVC bitstreams offline, so BASELINE.json's configs are exercised with seeded
+synthetic pictures: random CU/TB partitions, levels, QPs, transform types, motion, filter parameters.
+The same arrays feed the CUDA engine, the oracle port and the compiled reference, so parity is checked on
+identical inputs.  PRNG: numpy PCG64 with the seed given by the caller (printed by tests/bench).
+"""
+import numpy as np
+
+from . import abi
+
+
+def plane_dims(width, height, chroma_shift=1):
+    return [(width, height), (width >> chroma_shift, height >> chroma_shift), (width >> chroma_shift, height >> chroma_shift)]
+
+
+def alloc_planes_np(width, height, align=64):
+    """Three uint16 planes with rows padded to `align` samples."""
+    out = []
+    for w, h in plane_dims(width, height):
+        stride = (w + align - 1) // align * align
+        out.append(np.zeros((h, stride), np.uint16)[:, :w])
+    return out
+
+
+def _split_region(rng, x, y, w, h, pw, ph, min_size, p_split, out):
+    """Random quad/binary partition of (x, y, w, h) clipped to the pw x ph plane."""
+    if x >= pw or y >= ph:
+        return
+    over_x, over_y = x + w > pw, y + h > ph
+    can_h, can_v = h > min_size, w > min_size
+    if over_x or over_y:
+        if over_x and over_y and can_h and can_v:
+            mode = 0
+        elif over_x and can_v:
+            mode = 2
+        elif over_y and can_h:
+            mode = 1
+        else:
+            return  # cannot fit (plane dims are multiples of min_size, so not reached)
+    else:
+        if not (can_h or can_v) or rng.random() >= p_split(w, h):
+            out.append((x, y, w, h))
+            return
+        r = rng.random()
+        if can_h and can_v:
+            mode = 0 if r < 0.4 else (1 if r < 0.7 else 2)
+        else:
+            mode = 1 if can_h else 2
+    if mode == 0:
+        for dy in (0, h // 2):
+            for dx in (0, w // 2):
+                _split_region(rng, x + dx, y + dy, w // 2, h // 2, pw, ph, min_size, p_split, out)
+    elif mode == 1:
+        _split_region(rng, x, y, w, h // 2, pw, ph, min_size, p_split, out)
+        _split_region(rng, x, y + h // 2, w, h // 2, pw, ph, min_size, p_split, out)
+    else:
+        _split_region(rng, x, y, w // 2, h, pw, ph, min_size, p_split, out)
+        _split_region(rng, x + w // 2, y, w // 2, h, pw, ph, min_size, p_split, out)
+
+
+def random_tiling(rng, pw, ph, cell, min_size, mean_log2=4.0):
+    """List of (x, y, w, h) tiles covering the plane; tile sides are powers of two in [min_size, cell]."""
+    def p_split(w, h):
+        return min(0.95, max(0.05, 0.5 + 0.35 * (np.log2(max(w, h)) - mean_log2)))
+    out = []
+    for y in range(0, ph, cell):
+        for x in range(0, pw, cell):
+            _split_region(rng, x, y, cell, cell, pw, ph, min_size, p_split, out)
+    return np.array(out, np.int32).reshape(-1, 4)
+
+
+_DIAG4 = [(0, 0), (0, 1), (1, 0), (0, 2), (1, 1), (2, 0), (0, 3), (1, 2),
+          (2, 1), (3, 0), (1, 3), (2, 2), (3, 1), (2, 3), (3, 2), (3, 3)]   # (x, y), up-right diagonal 4x4
+
+
+def residual_picture(seed, width, height, coded_fraction=1.0, levels="realistic", tools=("mts", "ts", "bdpcm", "lfnst",
+                     "scaling", "joint", "dep_quant"), mean_log2=4.0, max_qp=63, sort=True):
+    """One picture's residual batch.
+
+    Returns dict(tbs=structured array TB_DTYPE, levels=int16 array, params=abi.ResidualParams,
+                 intra_mode=int8 per TB (raw CU mode for LFNST TBs, reference side only), seed=...).
+    """
+    rng = np.random.default_rng(seed)
+    tools = set(tools)
+    dims = plane_dims(width, height)
+    recs = []
+    # luma tiles, then chroma tiles (one tiling shared by Cb and Cr so joint TBs can cover both)
+    luma = random_tiling(rng, dims[0][0], dims[0][1], 64, 4, mean_log2)
+    chroma = random_tiling(rng, dims[1][0], dims[1][1], 32, 2, mean_log2 - 1)
+    for c_set, tiles in (((0,), luma), ((1, 2), chroma)):
+        keep = rng.random(len(tiles)) < coded_fraction
+        for (x, y, w, h) in tiles[keep]:
+            if c_set == (0,):
+                recs.append((x, y, 0, w, h, 0))
+            else:
+                jm = rng.integers(0, 6) if "joint" in tools and w * h > 4 else 0
+                if jm in (1, 2, 3):      # joint: 1 = Cb carries (mode 2: both coded), 2 = Cb carries + shift, 3 = Cr carries + shift
+                    recs.append((x, y, 1 if jm < 3 else 2, w, h, jm))
+                else:
+                    recs.append((x, y, 1, w, h, 0))
+                    if rng.random() < 0.8:
+                        recs.append((x, y, 2, w, h, 0))
+    n = len(recs)
+    tbs = np.zeros(n, abi.TB_DTYPE)
+    intra_mode = np.zeros(n, np.int8)
+    lv_chunks, off = [], 0
+    for i, (x, y, c, w, h, jm) in enumerate(recs):
+        l2w, l2h = int(np.log2(w)), int(np.log2(h))
+        flags, lf, trh, trv = 0, 0, abi.DCT2, abi.DCT2
+        inter = rng.random() < 0.6
+        if inter:
+            flags |= abi.TB_INTER
+        if "dep_quant" in tools and rng.random() < 0.5:
+            flags |= abi.TB_DEP_QUANT
+        if "scaling" in tools and rng.random() < 0.4:
+            flags |= abi.TB_SCALING
+        if jm:
+            flags |= abi.TB_JOINT | (abi.TB_JOINT_SHIFT if jm >= 2 else 0)
+        r = rng.random()
+        mask = None
+        if "ts" in tools and w <= 32 and h <= 32 and w >= 4 and h >= 4 and r < 0.08:
+            flags |= abi.TB_TS
+            if "bdpcm" in tools and not inter and rng.random() < 0.5:
+                flags |= abi.TB_BDPCM | (abi.TB_BDPCM_VERT if rng.random() < 0.5 else 0)
+            nzw, nzh = int(rng.integers(1, w + 1)), int(rng.integers(1, h + 1))
+        elif "lfnst" in tools and not inter and w >= 4 and h >= 4 and r < 0.2:
+            idx = int(rng.integers(1, 3))
+            mode = int(rng.integers(0, 67))
+            intra_mode[i] = mode
+            lf = -1          # resolved below by lfnst_code()
+            nz = 8 if (w, h) in ((4, 4), (8, 8)) else 16
+            k = int(rng.integers(1, nz + 1))
+            pos = _DIAG4[:k]
+            nzw, nzh = max(p[0] for p in pos) + 1, max(p[1] for p in pos) + 1
+            mask = np.zeros((nzh, nzw), bool)
+            for (px, py) in pos:
+                mask[py, px] = True
+            lf = lfnst_code(idx, mode, w, h, c)
+        else:
+            if c == 0 and "mts" in tools and 4 <= w <= 32 and 4 <= h <= 32 and r < 0.5:
+                if r < 0.35:     # explicit MTS
+                    trh, trv = [(abi.DST7, abi.DST7), (abi.DCT8, abi.DST7), (abi.DST7, abi.DCT8), (abi.DCT8, abi.DCT8)][int(rng.integers(0, 4))]
+                else:            # implicit MTS
+                    trh = abi.DST7 if w <= 16 else abi.DCT2
+                    trv = abi.DST7 if h <= 16 else abi.DCT2
+            nzw = int(rng.integers(1, min(w, 32 if trh == abi.DCT2 else 16) + 1))
+            nzh = int(rng.integers(1, min(h, 32 if trv == abi.DCT2 else 16) + 1))
+        if levels == "realistic":
+            lv = np.clip(np.rint(rng.laplace(0, 12, (nzh, nzw))), -256, 255).astype(np.int16)
+            lv[rng.random((nzh, nzw)) < 0.3] = 0
+        else:
+            lv = rng.integers(-32768, 32768, (nzh, nzw)).astype(np.int16)
+        if mask is not None:
+            lv[~mask] = 0
+        lv[nzh - 1, nzw - 1] = lv[nzh - 1, nzw - 1] or 1       # the scan box corner is significant by construction
+        if mask is not None and not mask[nzh - 1, nzw - 1]:
+            lv[nzh - 1, nzw - 1] = 0
+        qp = int(rng.integers(12, max_qp + 1))
+        t = tbs[i]
+        t["x0"], t["y0"], t["c_idx"], t["log2_w"], t["log2_h"] = x, y, c, l2w, l2h
+        t["nzw"], t["nzh"], t["trh"], t["trv"], t["qp"] = nzw, nzh, trh, trv, qp
+        t["flags"], t["lfnst"], t["coeff_off"] = flags, lf, off
+        lv_chunks.append(lv.reshape(-1))
+        off += lv.size
+    level_buf = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
+    if sort and n:
+        order = np.argsort(-(tbs["log2_w"].astype(np.int32) + tbs["log2_h"]), kind="stable")
+        tbs, intra_mode = tbs[order], intra_mode[order]
+    sl = rng.integers(4, 65, (28, 64)).astype(np.uint8)
+    dc = rng.integers(4, 65, 14).astype(np.uint8)
+    params = abi.residual_params(10, 1 if rng.random() < 0.5 else -1, sl, dc)
+    return dict(tbs=tbs, levels=level_buf, params=params, intra_mode=intra_mode, seed=seed, dims=dims)
+
+
+# ---- host-side derivations the parser performs before emitting a TB descriptor -------------------------
+_LFNST_TR_SET = None
+
+
+def wide_angle_mode(mode, w, h, c_idx=0):
+    """ff_vvc_wide_angle_mode_mapping (reference vvc_intra.c:693-714) for non-ISP blocks, raw mode 0..66."""
+    if w == h or mode < 2 or mode > 66:
+        return mode
+    ratio = abs(int(np.log2(w)) - int(np.log2(h)))
+    if w > h and mode >= 2 and mode < (8 + 2 * ratio if ratio > 1 else 8):
+        return mode + 65
+    if h > w and mode <= 66 and mode > (60 - 2 * ratio if ratio > 1 else 60):
+        return mode - 67
+    return mode
+
+
+def lfnst_code(lfnst_idx, raw_mode, w, h, c_idx):
+    """The `lfnst` byte of VVCB200TransformBlock from the CU's raw intra mode (vvc_intra.c:34-77, vvc_itx_1d.c:711)."""
+    from .tables import LFNST_TR_SET
+    m = wide_angle_mode(raw_mode, w, h, c_idx)
+    tr_set = 1 if m < 0 else int(LFNST_TR_SET[m])
+    return lfnst_idx | (tr_set << 2) | ((1 if m > 34 else 0) << 4)

@@ -1,0 +1,134 @@
+/*
+ * vvc_b200.h — C ABI of libvvcb200.so: the B200 (sm_100a) VVC reconstruction and
+ * in-loop-filter engine that sits behind the reference decoder's VVCDSPContext surface.
+ *
+ * Boundary (reference file:line, relative to the FFmpeg/ffvvc tree):
+ *   - the operator table this library stands in for: VVCDSPContext, libavcodec/vvc/vvcdsp.h:160-168,
+ *     bound by ff_vvc_dsp_init (vvcdsp.c:228-257) with the per-arch hook at vvcdsp.c:254-256;
+ *   - the stage drivers whose bodies become descriptor emitters: run_inter … run_alf,
+ *     libavcodec/vvc/vvc_thread.c:432-566.
+ *
+ * Two levels are exported:
+ *   Level A  "vvcb200_dsp_*": one batched device entry per populated VVCDSPContext member, same
+ *            argument meaning as the table entry, arrays of block descriptors instead of one block.
+ *            Pointers named d_* are DEVICE pointers; `stream` is a cudaStream_t passed as void*.
+ *   Level B  "vvcb200_ctx_* / vvcb200_pic_*": the picture-level engine.  HOST buffers in, HOST planes
+ *            out; H2D/D2H copies, streams and scratch planes are owned by the context.
+ *
+ * Conventions: every function returns 0 on success or a negative VVCB200_ERR_* code; nothing throws
+ * across the ABI; no entry point falls back to a CPU implementation — if no CUDA device is usable the
+ * call fails with VVCB200_ERR_CUDA.  Samples are 16-bit little-endian containers (8/10/12-bit content);
+ * plane strides are in BYTES as in the reference (ptrdiff_t stride, vvcdsp.h:49-157).
+ */
+#ifndef VVC_B200_H
+#define VVC_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VVCB200_ABI_VERSION 1
+
+enum {
+    VVCB200_OK          =  0,
+    VVCB200_ERR_ARG     = -1,   /* bad argument (NULL, size out of range, unsupported bit depth) */
+    VVCB200_ERR_CUDA    = -2,   /* CUDA runtime error; vvcb200_last_error() has the text          */
+    VVCB200_ERR_NOMEM   = -3,
+    VVCB200_ERR_UNSUP   = -4,   /* tool the reference snapshot does not implement either (IBC, palette, ACT, RPR) */
+    VVCB200_ERR_TOO_BIG = -5,   /* exceeds a fixed capacity stated in this header                  */
+};
+
+/* enum TxType, vvcdsp.h:30-35 */
+enum { VVCB200_DCT2 = 0, VVCB200_DST7 = 1, VVCB200_DCT8 = 2 };
+
+const char *vvcb200_last_error(void);
+int         vvcb200_abi_version(void);
+/* Number of kernels this library has launched since load (all contexts, all streams). */
+uint64_t    vvcb200_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Residual path descriptors: dequant → (BDPCM) → (LFNST) → inverse DCT-II/DST-VII/DCT-VIII → add.
+ * One record per coded TransformBlock (vvc_ctu.h:136-158); what itransform() (vvc_intra.c:432-478)
+ * reads from TransformBlock/TransformUnit/CodingUnit is flattened into it by the host.
+ * ---------------------------------------------------------------------------------------------- */
+enum {
+    VVCB200_TB_TS          = 1 << 0,  /* transform_skip_flag (tb->ts): bdShift 10, flat scaling, no inverse transform   */
+    VVCB200_TB_BDPCM       = 1 << 1,  /* cu->bdpcm_flag[c_idx]: prefix sum before dequant (vvcdsp_template.c:76-95)      */
+    VVCB200_TB_BDPCM_VERT  = 1 << 2,  /* intra mode == INTRA_VERT (vvc_intra.c:419-430)                                  */
+    VVCB200_TB_DEP_QUANT   = 1 << 3,  /* sh_dep_quant_used_flag of the slice (vvc_intra.c:316,336)                       */
+    VVCB200_TB_SCALING     = 1 << 4,  /* explicit scaling list applies to this TB (vvc_intra.c:367-369)                  */
+    VVCB200_TB_INTER       = 1 << 5,  /* cu->pred_mode != MODE_INTRA — picks the Table-38 row (vvc_intra.c:342-362)       */
+    VVCB200_TB_JOINT       = 1 << 6,  /* chroma TB carrying a joint CbCr residual: also rebuilt into plane 3 - c_idx      */
+    VVCB200_TB_JOINT_SHIFT = 1 << 7,  /* tu->coded_flag[1] ^ tu->coded_flag[2] (vvc_intra.c:172)                          */
+    VVCB200_TB_LMCS_SCALE  = 1 << 8,  /* LMCS chroma residual scaling applies (vvc_intra.c:451); scale in `lmcs_scale`    */
+};
+
+typedef struct VVCB200TransformBlock {
+    uint16_t x0, y0;        /* top-left corner in samples OF THE PLANE c_idx (reference keeps luma units; host shifts)   */
+    uint8_t  c_idx;         /* 0 Y, 1 Cb, 2 Cr                                                                          */
+    uint8_t  log2_w, log2_h;/* 0..6 (w or h == 1 only with the other >= 16, vvcdsp.c:140-195)                            */
+    uint8_t  nzw, nzh;      /* max_scan_x + 1, max_scan_y + 1 as residual parsing left them (1..32)                      */
+    uint8_t  trh, trv;      /* TxType after derive_transform_type (vvc_intra.c:130-164)                                  */
+    uint8_t  qp;            /* tb->qp after derive_qp (vvc_intra.c:277-310)                                              */
+    uint16_t flags;         /* VVCB200_TB_*                                                                              */
+    uint8_t  lfnst;         /* 0 = no LFNST; else bits1:0 = lfnst_idx (1|2), bits3:2 = lfnst_tr_set_idx, bit4 = transpose
+                               (pred_mode_intra > 34 after wide-angle mapping, vvc_intra.c:76-77)                         */
+    uint8_t  reserved;
+    uint16_t lmcs_scale;    /* chroma_scale_coeff picked for this TB's VPDU (vvc_intra_template.c:390-428); 0 if unused  */
+    uint16_t reserved2;
+    uint32_t coeff_off;     /* index into the int16 level buffer of this TB's nzw*nzh levels, row-major, row stride nzw  */
+} VVCB200TransformBlock;    /* 24 bytes */
+
+/* Per-picture constants of the residual path (fields of VVCSPS/VVCPH/VVCScalingList the path reads). */
+typedef struct VVCB200ResidualParams {
+    int32_t  bit_depth;             /* 8, 10 or 12 (sps->bit_depth)                                     */
+    int32_t  log2_transform_range;  /* 15 (sps->log2_transform_range; extended precision is not built)  */
+    int32_t  joint_c_sign;          /* 1 - 2 * ph_joint_cbcr_sign_flag (vvc_intra.c:171)                */
+    int32_t  reserved;
+    uint8_t  scaling_matrix_rec[28][64];   /* VVCScalingList.scaling_matrix_rec, vvc_ps.h:187-190      */
+    uint8_t  scaling_matrix_dc_rec[14];    /* VVCScalingList.scaling_matrix_dc_rec                      */
+    uint8_t  pad[2];
+} VVCB200ResidualParams;
+
+/* A picture (or any sample array triple) resident in device memory. */
+typedef struct VVCB200Planes {
+    void     *d_plane[3];      /* device pointers, 16-bit samples */
+    int32_t   stride[3];       /* bytes                           */
+    int32_t   width[3];        /* samples                         */
+    int32_t   height[3];       /* samples                         */
+} VVCB200Planes;
+
+/*
+ * Level A, itx sub-table (vvcdsp.h:112-120).
+ *
+ * vvcb200_dsp_itx_batch: for each i, run itx.itx[trh][trv][log2_w][log2_h] in place on the w*h int32
+ * block d_coeffs + block_off[i], with (nzw, nzh, log2_transform_range, bit_depth) as the table entry
+ * takes them (vvcdsp.h:117-118).  Only flags==0 fields x0/y0/qp/... are ignored.
+ */
+int vvcb200_dsp_itx_batch(int32_t *d_coeffs, const uint32_t *d_block_off,
+                          const VVCB200TransformBlock *d_tbs, int n,
+                          int log2_transform_range, int bit_depth, void *stream);
+
+/* itx.add_residual (vvcdsp.h:113): dst = clip_pixel(dst + res) for each block; res is the w*h int32
+ * block at d_res + block_off[i]; dst addressed by the TB's (c_idx, x0, y0). */
+int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const int32_t *d_res, const uint32_t *d_block_off,
+                                   const VVCB200TransformBlock *d_tbs, int n, int bit_depth, void *stream);
+
+/*
+ * Fused residual stage = itransform() for a whole picture (vvc_intra.c:432-478): BDPCM, dequant, LFNST,
+ * 2-D/1-D inverse transform, LMCS chroma scaling factor, add_residual, joint CbCr — one launch.
+ * d_levels: int16 level buffer (see coeff_off).  The TBs of one launch must not overlap in the planes.
+ * If `d_residual` is non-NULL the clipped-to-int16 residual is stored there instead (same geometry as
+ * `dst`, int16 samples) and `dst` is left untouched (used by the wavefront intra path).
+ */
+int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
+                           const int16_t *d_levels, const VVCB200TransformBlock *d_tbs, int n,
+                           const VVCB200ResidualParams *params /* host */, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VVC_B200_H */

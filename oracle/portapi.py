@@ -1,0 +1,45 @@
+"""TEST INFRASTRUCTURE: ctypes loader for oracle/_build/libvvcport.so (the plain-C restatement)."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from ffmpeg_b200 import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(_HERE, "_build", "libvvcport.so")
+_lib = None
+
+
+def build():
+    subprocess.check_call(["make", "-s", "-C", _HERE, "port"])
+    return SO
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO):
+            build()
+        _lib = C.CDLL(SO)
+    return _lib
+
+
+def itx(coeffs, trh, trv, log2w, log2h, nzw, nzh, bd=10, log2_range=15):
+    assert coeffs.dtype == np.int32 and coeffs.flags.c_contiguous
+    lib().port_itx(C.c_void_p(coeffs.ctypes.data), trh, trv, log2w, log2h, nzw, nzh, log2_range, bd)
+    return True
+
+
+def residual_batch(planes, levels, tbs, params, want_residual=False):
+    pl = abi.host_planes(planes)
+    levels = np.ascontiguousarray(levels, np.int16)
+    tbs = np.ascontiguousarray(tbs, abi.TB_DTYPE)
+    res = None
+    if want_residual:
+        total = int(np.sum(1 << (tbs["log2_w"].astype(np.int64) + tbs["log2_h"])))
+        res = np.zeros(total, np.int32)
+    lib().port_residual_batch(C.byref(pl), C.c_void_p(levels.ctypes.data), C.c_void_p(tbs.ctypes.data), len(tbs),
+                              C.byref(params), C.c_void_p(res.ctypes.data) if res is not None else None)
+    return res

@@ -1,0 +1,62 @@
+"""TEST INFRASTRUCTURE: ctypes loader for oracle/_ref/libvvcref.so (the reference's own C code)."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from ffmpeg_b200 import abi
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO = os.path.join(_HERE, "_ref", "libvvcref.so")
+
+
+def available():
+    return os.path.exists(SO)
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        _lib = C.CDLL(SO)
+        _lib.vvcref_table.restype = C.c_void_p
+        _lib.vvcref_table.argtypes = [C.c_char_p, C.POINTER(C.c_size_t)]
+    return _lib
+
+
+def table(name, dtype, shape):
+    """Copy of a constant table exported by the reference's vvc_data.c."""
+    n = C.c_size_t(0)
+    p = lib().vvcref_table(name.encode(), C.byref(n))
+    if not p:
+        raise KeyError(name)
+    a = np.frombuffer((C.c_uint8 * n.value).from_address(p), dtype=dtype).copy()
+    return a.reshape(shape)
+
+
+def itx(coeffs, trh, trv, log2w, log2h, nzw, nzh, bd=10, log2_range=15):
+    """itx.itx[trh][trv][log2w][log2h] in place on an int32 array of w*h; returns False if slot empty."""
+    assert coeffs.dtype == np.int32 and coeffs.flags.c_contiguous
+    r = lib().vvcref_itx(bd, trh, trv, log2w, log2h, C.c_void_p(coeffs.ctypes.data), nzw, nzh, log2_range)
+    return r == 0
+
+
+def residual_batch(planes, levels, tbs, params, intra_mode=None, want_residual=False):
+    """Reference itransform() over a TB batch on host planes (list of 3 uint16 arrays), in place."""
+    pl = abi.host_planes(planes)
+    levels = np.ascontiguousarray(levels, np.int16)
+    tbs = np.ascontiguousarray(tbs, abi.TB_DTYPE)
+    res = None
+    if want_residual:
+        total = int(np.sum(1 << (tbs["log2_w"].astype(np.int64) + tbs["log2_h"])))
+        res = np.zeros(total, np.int32)
+    im = None if intra_mode is None else np.ascontiguousarray(intra_mode, np.int8)
+    r = lib().vvcref_residual_batch(
+        C.byref(pl), C.c_void_p(levels.ctypes.data), C.c_void_p(tbs.ctypes.data), len(tbs), C.byref(params),
+        C.c_void_p(im.ctypes.data) if im is not None else None,
+        C.c_void_p(res.ctypes.data) if res is not None else None)
+    if r != 0:
+        raise RuntimeError("vvcref_residual_batch rejected a descriptor")
+    return res
