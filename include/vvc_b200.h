@@ -31,6 +31,11 @@ extern "C" {
 #endif
 
 #define VVCB200_ABI_VERSION 1
+#if defined(__GNUC__)
+#define VVCB200_API __attribute__((visibility("default")))
+#else
+#define VVCB200_API
+#endif
 
 enum {
     VVCB200_OK          =  0,
@@ -44,10 +49,10 @@ enum {
 /* enum TxType, vvcdsp.h:30-35 */
 enum { VVCB200_DCT2 = 0, VVCB200_DST7 = 1, VVCB200_DCT8 = 2 };
 
-const char *vvcb200_last_error(void);
-int         vvcb200_abi_version(void);
+VVCB200_API const char *vvcb200_last_error(void);
+VVCB200_API int         vvcb200_abi_version(void);
 /* Number of kernels this library has launched since load (all contexts, all streams). */
-uint64_t    vvcb200_launch_count(void);
+VVCB200_API uint64_t    vvcb200_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------------
  * Residual path descriptors: dequant → (BDPCM) → (LFNST) → inverse DCT-II/DST-VII/DCT-VIII → add.
@@ -108,13 +113,13 @@ typedef struct VVCB200Planes {
  * block d_coeffs + block_off[i], with (nzw, nzh, log2_transform_range, bit_depth) as the table entry
  * takes them (vvcdsp.h:117-118).  Only flags==0 fields x0/y0/qp/... are ignored.
  */
-int vvcb200_dsp_itx_batch(int32_t *d_coeffs, const uint32_t *d_block_off,
+VVCB200_API int vvcb200_dsp_itx_batch(int32_t *d_coeffs, const uint32_t *d_block_off,
                           const VVCB200TransformBlock *d_tbs, int n,
                           int log2_transform_range, int bit_depth, void *stream);
 
 /* itx.add_residual (vvcdsp.h:113): dst = clip_pixel(dst + res) for each block; res is the w*h int32
  * block at d_res + block_off[i]; dst addressed by the TB's (c_idx, x0, y0). */
-int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const int32_t *d_res, const uint32_t *d_block_off,
+VVCB200_API int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const int32_t *d_res, const uint32_t *d_block_off,
                                    const VVCB200TransformBlock *d_tbs, int n, int bit_depth, void *stream);
 
 /*
@@ -124,9 +129,45 @@ int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const int32_t *d_re
  * If `d_residual` is non-NULL the clipped-to-int16 residual is stored there instead (same geometry as
  * `dst`, int16 samples) and `dst` is left untouched (used by the wavefront intra path).
  */
-int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
+VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
                            const int16_t *d_levels, const VVCB200TransformBlock *d_tbs, int n,
                            const VVCB200ResidualParams *params /* host */, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);
+ * a context is not thread-safe, different contexts are independent (replicas only).
+ * All work is enqueued on the context's own CUDA stream and is asynchronous with respect to the host:
+ * host buffers handed to vvcb200_pic_* must stay valid and unchanged until vvcb200_ctx_sync() returns
+ * (allocate them with vvcb200_host_alloc() to get true overlap; pageable memory also works, slower).
+ * This replaces the bodies of run_inter … run_alf (vvc_thread.c:432-566): the host parser fills the
+ * descriptor batches for one picture, the context uploads them and runs the stages as picture-level
+ * passes in the dependency order of vvc_thread.c:156-184.
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VVCB200Ctx VVCB200Ctx;
+
+/* chroma_format_idc: 1 (4:2:0) is what the engine builds today; others return VVCB200_ERR_UNSUP. */
+VVCB200_API int  vvcb200_ctx_create(VVCB200Ctx **ctx, int device, int width, int height,
+                                    int chroma_format_idc, int bit_depth);
+VVCB200_API void vvcb200_ctx_destroy(VVCB200Ctx *ctx);
+VVCB200_API int  vvcb200_ctx_sync(VVCB200Ctx *ctx);
+/* cudaStream_t of the context (for callers that enqueue their own work or record events on it). */
+VVCB200_API void *vvcb200_ctx_stream(VVCB200Ctx *ctx);
+/* Device planes of the picture under reconstruction (fc->frame, vvcdec.h:96). */
+VVCB200_API int  vvcb200_ctx_current(VVCB200Ctx *ctx, VVCB200Planes *out);
+
+/* Pinned host memory for descriptor batches and frames. */
+VVCB200_API void *vvcb200_host_alloc(size_t bytes);
+VVCB200_API void  vvcb200_host_free(void *p);
+
+/* Start a picture: forgets the previous picture's batches (the planes keep their content). */
+VVCB200_API int vvcb200_pic_begin(VVCB200Ctx *ctx);
+/* Copy host samples into the current picture (prediction produced elsewhere, or test input). strides in bytes. */
+VVCB200_API int vvcb200_pic_upload(VVCB200Ctx *ctx, const uint16_t *const planes[3], const int32_t strides[3]);
+/* Residual stage of the picture: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
+VVCB200_API int vvcb200_pic_residual(VVCB200Ctx *ctx, const int16_t *levels, size_t n_levels,
+                                     const VVCB200TransformBlock *tbs, int n, const VVCB200ResidualParams *params);
+/* Copy the current picture back to host memory (the AVFrame the decoder outputs). strides in bytes. */
+VVCB200_API int vvcb200_pic_download(VVCB200Ctx *ctx, uint16_t *const planes[3], const int32_t strides[3]);
 
 #ifdef __cplusplus
 }

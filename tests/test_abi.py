@@ -1,0 +1,53 @@
+"""CPU tests of the drop-in boundary: the shared library loads without a GPU and exports every symbol that
+include/vvc_b200.h declares; POD struct sizes match between C and the Python mirrors."""
+import ctypes as C
+import os
+import re
+import subprocess
+import tempfile
+
+from ffmpeg_b200 import abi, lib
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "vvc_b200.h")
+
+
+def declared_symbols():
+    src = open(HEADER).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(vvcb200_\w+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    l = lib.load()
+    syms = declared_symbols()
+    assert len(syms) >= 6
+    for s in syms:
+        assert hasattr(l, s), "libvvcb200.so does not export %s" % s
+
+
+def test_abi_version_and_error_string():
+    l = lib.load()
+    assert l.vvcb200_abi_version() == 1
+    assert isinstance(l.vvcb200_last_error(), bytes)
+
+
+def test_struct_sizes_match_c():
+    code = '#include <stdio.h>\n#include "vvc_b200.h"\nint main(void){printf("%zu %zu %zu\\n", sizeof(VVCB200TransformBlock), sizeof(VVCB200ResidualParams), sizeof(VVCB200Planes));return 0;}\n'
+    with tempfile.TemporaryDirectory() as d:
+        src = os.path.join(d, "s.c")
+        open(src, "w").write(code)
+        exe = os.path.join(d, "s")
+        subprocess.check_call(["gcc", "-I", os.path.join(ROOT, "include"), src, "-o", exe])
+        sizes = [int(v) for v in subprocess.check_output([exe]).split()]
+    assert sizes == [abi.TB_DTYPE.itemsize, C.sizeof(abi.ResidualParams), C.sizeof(abi.Planes)]
+
+
+def test_bad_arguments_are_rejected_without_a_gpu():
+    l = lib.load()
+    p = abi.residual_params(bit_depth=9)
+    rc = l.vvcb200_residual_batch(None, None, None, None, 0, C.byref(p), None)
+    assert rc == -1
+    pl = abi.Planes()
+    rc = l.vvcb200_residual_batch(C.byref(pl), None, None, None, 0, C.byref(p), None)
+    assert rc == -1 and b"bit depth" in l.vvcb200_last_error()
