@@ -61,3 +61,47 @@ def host_planes(arrays):
         p.width[c] = a.shape[1]
         p.height[c] = a.shape[0]
     return p
+
+
+# ---- inter prediction -----------------------------------------------------------------------------------
+PB_WP, PB_HPEL_IF, PB_AFFINE, PB_LUMA_ONLY, PB_CHROMA_ONLY = 1, 2, 4, 8, 16
+PB_BDOF, PB_DMVR, PB_CIIP, PB_LMCS = 32, 64, 128, 256
+PF_L0, PF_L1, PF_BI = 1, 2, 3
+
+PB_DTYPE = np.dtype([
+    ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("pred_flag", "u1"), ("bcw_idx", "u1"),
+    ("ref_idx", "i1", (2,)), ("flags", "<u2"), ("mv", "<i4", (2, 2)), ("reserved", "<u4"),
+], align=False)
+assert PB_DTYPE.itemsize == 32
+
+
+class InterParams(C.Structure):
+    _fields_ = [
+        ("bit_depth", C.c_int32), ("log2_denom", C.c_int32 * 2), ("reserved", C.c_int32),
+        ("weight", ((C.c_int16 * 16) * 3) * 2), ("offset", ((C.c_int16 * 16) * 3) * 2),
+        ("ref_slot", (C.c_uint8 * 16) * 2),
+    ]
+
+
+def inter_params(bit_depth=10, log2_denom=(0, 0), weight=None, offset=None, ref_slot=None):
+    p = InterParams()
+    p.bit_depth = bit_depth
+    p.log2_denom[0], p.log2_denom[1] = log2_denom
+    w = np.zeros((2, 3, 16), np.int16) if weight is None else np.ascontiguousarray(weight, np.int16)
+    if weight is None:
+        w[:, 0, :] = 1 << log2_denom[0]
+        w[:, 1:, :] = 1 << log2_denom[1]
+    o = np.zeros((2, 3, 16), np.int16) if offset is None else np.ascontiguousarray(offset, np.int16)
+    r = np.zeros((2, 16), np.uint8) if ref_slot is None else np.ascontiguousarray(ref_slot, np.uint8)
+    C.memmove(p.weight, w.ctypes.data, w.nbytes)
+    C.memmove(p.offset, o.ctypes.data, o.nbytes)
+    C.memmove(p.ref_slot, r.ctypes.data, r.nbytes)
+    return p
+
+
+def planes_array(list_of_planes):
+    """Contiguous C array of Planes structs (for `refs`)."""
+    arr = (Planes * len(list_of_planes))()
+    for i, p in enumerate(list_of_planes):
+        arr[i] = p
+    return arr

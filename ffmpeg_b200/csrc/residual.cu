@@ -3,8 +3,8 @@
 // libavcodec/vvc/vvc_intra.c:432-478, with the DSP entries it calls: vvcdsp.c:94-138 (2-D/1-D drivers),
 // vvc_itx_1d.c (1-D cores), vvcdsp_template.c:32-95 (add_residual, joint, bdpcm)).
 //
-// Mapping: one warp owns one transform block at a time; a CTA of 4 warps walks a chunk of the
-// (size-sorted) descriptor list.  The block lives in shared memory between the two 1-D passes
+// Mapping: one warp owns one transform block at a time; CTAs of 4 warps walk the (size-sorted)
+// descriptor list with a grid stride so that all CTAs see the same mix of block sizes.  The block lives in shared memory between the two 1-D passes
 // (levels -> dequantized 16-bit -> column pass -> 16-bit clip -> row pass -> epilogue), so HBM sees
 // the int16 levels once and the destination samples once (read-modify-write).  All arithmetic is
 // exact int32 on CUDA cores: accumulators wrap mod 2^32 exactly like the reference's `int`.
@@ -153,9 +153,9 @@ residual_kernel(const ResidualArgs a, const ScalingLists sl)
     load_matrices(smat);
     __syncthreads();
 
-    const int first = blockIdx.x * kChunk;
-    const int last  = min(first + kChunk, a.n);
-    for (int t = first + warp; t < last; t += kWarpsPerCta) {
+    // The list is sorted by block area (largest first).  CTA b takes blocks b, b + grid, b + 2*grid, ... so
+    // every CTA gets the same size profile (no tail of CTAs stuck with the 64x64 blocks).
+    for (int t = blockIdx.x + warp * gridDim.x; t < a.n; t += kWarpsPerCta * gridDim.x) {
         const VVCB200TransformBlock d = a.tbs[t];
         const int w = 1 << d.log2_w, h = 1 << d.log2_h;
         const bool ts = d.flags & VVCB200_TB_TS;
@@ -324,9 +324,7 @@ itx_kernel(const ItxArgs a)
 
     load_matrices(smat);
     __syncthreads();
-    const int first = blockIdx.x * kChunk;
-    const int last  = min(first + kChunk, a.n);
-    for (int t = first + warp; t < last; t += kWarpsPerCta) {
+    for (int t = blockIdx.x + warp * gridDim.x; t < a.n; t += kWarpsPerCta * gridDim.x) {
         const VVCB200TransformBlock d = a.tbs[t];
         const int w = 1 << d.log2_w;
         int32_t *blk = a.coeffs + a.block_off[t];

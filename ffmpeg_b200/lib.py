@@ -86,3 +86,89 @@ def dsp_itx_batch(coeffs, block_off, tbs, n, log2_transform_range=15, bit_depth=
 def dsp_add_residual_batch(dst, res, block_off, tbs, n, bit_depth=10, stream=None):
     check(load().vvcb200_dsp_add_residual_batch(C.byref(dst), _ptr(res), _ptr(block_off), _ptr(tbs), int(n),
                                                 int(bit_depth), _stream(stream)))
+
+
+# ---- Level B: picture engine ---------------------------------------------------------------------------
+class Context:
+    """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use
+    pinned() to allocate page-locked ones (needed for asynchronous copies)."""
+
+    def __init__(self, device, width, height, bit_depth=10, chroma_format_idc=1):
+        self._h = C.c_void_p()
+        check(load().vvcb200_ctx_create(C.byref(self._h), int(device), int(width), int(height),
+                                        int(chroma_format_idc), int(bit_depth)))
+        self.width, self.height, self.bit_depth = width, height, bit_depth
+        self._pinned = []
+
+    def close(self):
+        if self._h:
+            load().vvcb200_ctx_destroy(self._h)
+            self._h = C.c_void_p()
+        for p in self._pinned:
+            load().vvcb200_host_free(C.c_void_p(p))
+        self._pinned = []
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def pinned(self, shape, dtype):
+        """Page-locked numpy array owned by this context."""
+        l = load()
+        l.vvcb200_host_alloc.restype = C.c_void_p
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        p = l.vvcb200_host_alloc(C.c_size_t(max(n, 1)))
+        if not p:
+            raise VVCB200Error(l.vvcb200_last_error().decode())
+        self._pinned.append(p)
+        buf = (C.c_uint8 * max(n, 1)).from_address(p)
+        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+
+    def pinned_planes(self):
+        dims = [(self.width, self.height), (self.width // 2, self.height // 2), (self.width // 2, self.height // 2)]
+        return [self.pinned((h, w), np.uint16) for (w, h) in dims]
+
+    def stream(self):
+        l = load()
+        l.vvcb200_ctx_stream.restype = C.c_void_p
+        return l.vvcb200_ctx_stream(self._h)
+
+    def current(self):
+        p = abi.Planes()
+        check(load().vvcb200_ctx_current(self._h, C.byref(p)))
+        return p
+
+    def sync(self):
+        check(load().vvcb200_ctx_sync(self._h))
+
+    def begin(self):
+        check(load().vvcb200_pic_begin(self._h))
+
+    @staticmethod
+    def _plane_args(planes):
+        ptrs = (C.c_void_p * 3)(*[p.ctypes.data for p in planes])
+        strides = (C.c_int32 * 3)(*[p.strides[0] for p in planes])
+        return ptrs, strides
+
+    def upload(self, planes):
+        ptrs, strides = self._plane_args(planes)
+        check(load().vvcb200_pic_upload(self._h, ptrs, strides))
+
+    def download(self, planes):
+        ptrs, strides = self._plane_args(planes)
+        check(load().vvcb200_pic_download(self._h, ptrs, strides))
+
+    def residual(self, levels, tbs, params):
+        assert levels.dtype == np.int16 and tbs.dtype == abi.TB_DTYPE
+        check(load().vvcb200_pic_residual(self._h, _ptr(levels), C.c_size_t(levels.size), _ptr(tbs), len(tbs),
+                                          C.byref(params)))
+
+
+def inter_batch(dst, refs, blocks, n, params, lmcs_fwd_lut=None, tmp14=None, stream=None):
+    """vvcb200_inter_batch: dst/tmp14 device_planes() structs, refs list of device_planes(), blocks device tensor."""
+    ra = abi.planes_array(refs)
+    check(load().vvcb200_inter_batch(
+        C.byref(dst) if dst is not None else None, ra, len(refs), _ptr(blocks), int(n), C.byref(params),
+        _ptr(lmcs_fwd_lut), C.byref(tmp14) if tmp14 is not None else None, _stream(stream)))

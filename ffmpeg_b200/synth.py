@@ -195,3 +195,59 @@ def lfnst_code(lfnst_idx, raw_mode, w, h, c_idx):
     m = wide_angle_mode(raw_mode, w, h, c_idx)
     tr_set = 1 if m < 0 else int(LFNST_TR_SET[m])
     return lfnst_idx | (tr_set << 2) | ((1 if m > 34 else 0) << 4)
+
+
+# ---- inter prediction ------------------------------------------------------------------------------------
+def smooth_planes(seed, dims, bd=10):
+    """Reference pictures: low-pass filtered noise so that filters/decisions see texture and flat areas."""
+    rng = np.random.default_rng(seed)
+    out = []
+    for (w, h) in dims:
+        a = rng.integers(0, 1 << bd, (h // 8 + 2, w // 8 + 2)).astype(np.float64)
+        a = np.kron(a, np.ones((8, 8)))[:h, :w]
+        a = a + rng.normal(0, 24, (h, w))
+        out.append(np.clip(np.rint(a), 0, (1 << bd) - 1).astype(np.uint16))
+    return out
+
+
+def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel"), mv_range=64 * 16, far_mv=0.02,
+                  inter_fraction=1.0, sizes=(4, 8, 16)):
+    """Prediction sub-block batch (<= 16x16) tiling the picture + per-slice InterParams."""
+    rng = np.random.default_rng(seed)
+    tools = set(tools)
+    tiles = random_tiling(rng, width, height, 16, min(sizes), mean_log2=3.6)
+    if inter_fraction < 1.0:
+        tiles = tiles[rng.random(len(tiles)) < inter_fraction]
+    n = len(tiles)
+    b = np.zeros(n, abi.PB_DTYPE)
+    b["x0"], b["y0"], b["w"], b["h"] = tiles[:, 0], tiles[:, 1], tiles[:, 2], tiles[:, 3]
+    pf = rng.integers(1, 4 if "bi" in tools else 3, n)
+    b["pred_flag"] = pf
+    b["ref_idx"] = rng.integers(0, n_refs, (n, 2))
+    mv = rng.integers(-mv_range, mv_range + 1, (n, 2, 2))
+    far = rng.random(n) < far_mv                      # a few vectors pointing far outside the picture
+    mv[far] = rng.integers(-(1 << 17), 1 << 17, (int(far.sum()), 2, 2))
+    integer = rng.random((n, 2, 2)) < 0.2             # plenty of integer / half-pel components
+    mv[integer] &= ~15
+    half = rng.random((n, 2, 2)) < 0.15
+    mv[half] = (mv[half] & ~15) | 8
+    b["mv"] = mv
+    flags = np.zeros(n, np.uint16)
+    if "wp" in tools:
+        flags |= np.where(rng.random(n) < 0.3, abi.PB_WP, 0).astype(np.uint16)
+    if "hpel" in tools:
+        flags |= np.where(rng.random(n) < 0.3, abi.PB_HPEL_IF, 0).astype(np.uint16)
+    b["flags"] = flags
+    if "bcw" in tools:
+        b["bcw_idx"] = np.where((pf == 3) & (rng.random(n) < 0.3), rng.integers(1, 5, n), 0)
+    ld = (int(rng.integers(0, 8)), int(rng.integers(0, 8)))
+    weight = np.zeros((2, 3, 16), np.int16)
+    offset = rng.integers(-64, 64, (2, 3, 16)).astype(np.int16)
+    weight[:, 0, :] = (1 << ld[0]) + rng.integers(-128, 128, (2, 16))
+    weight[:, 1:, :] = (1 << ld[1]) + rng.integers(-128, 128, (2, 2, 16))
+    ref_slot = np.zeros((2, 16), np.uint8)
+    ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
+    params = abi.inter_params(10, ld, weight, offset, ref_slot)
+    dims = plane_dims(width, height)
+    refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
+    return dict(blocks=b, params=params, refs=refs, dims=dims, seed=seed)

@@ -134,6 +134,59 @@ VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pl
                            const VVCB200ResidualParams *params /* host */, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Inter prediction descriptors (stage INTER, ff_vvc_predict_inter, vvc_inter.c:899-913).
+ * One record per prediction sub-block of at most 16x16 luma samples: the host emitter splits larger
+ * prediction units (translational MC is separable per sample, and 16x16 is the reference's own DMVR/BDOF
+ * sub-block, vvc_mvs.c num_sb_x/y), and emits affine CUs as 4x4 luma + 8x8-luma-footprint chroma records.
+ * ---------------------------------------------------------------------------------------------- */
+enum {
+    VVCB200_PB_WP          = 1 << 0,  /* explicit weighted prediction is on for the slice (vvc_inter.c:128-129,149-150) */
+    VVCB200_PB_HPEL_IF     = 1 << 1,  /* mi.hpel_if_idx: luma filter set 1 (vvc_inter.c:792)                           */
+    VVCB200_PB_AFFINE      = 1 << 2,  /* luma filter set 2 (vvc_inter.c:383-384)                                       */
+    VVCB200_PB_LUMA_ONLY   = 1 << 3,
+    VVCB200_PB_CHROMA_ONLY = 1 << 4,
+    VVCB200_PB_BDOF        = 1 << 5,  /* pu->bdof_flag                                                                 */
+    VVCB200_PB_DMVR        = 1 << 6,  /* pu->dmvr_flag                                                                 */
+    VVCB200_PB_CIIP        = 1 << 7,  /* cu->ciip_flag: BCW is ignored (vvc_inter.c:151), blend happens in RECON       */
+    VVCB200_PB_LMCS        = 1 << 8,  /* forward LMCS on the luma prediction (vvc_inter.c:888-891)                     */
+};
+
+typedef struct VVCB200PredBlock {
+    uint16_t x0, y0;        /* luma position                                                   */
+    uint8_t  w, h;          /* luma size, 4/8/16 each (chroma footprint is w>>1 x h>>1)        */
+    uint8_t  pred_flag;     /* PF_L0 = 1, PF_L1 = 2, PF_BI = 3 (vvc_ctu.h:222-227)             */
+    uint8_t  bcw_idx;       /* MvField.bcw_idx                                                 */
+    int8_t   ref_idx[2];    /* MvField.ref_idx                                                 */
+    uint16_t flags;         /* VVCB200_PB_*                                                    */
+    int32_t  mv[2][2];      /* MvField.mv[list] = {x, y} in 1/16 luma sample, 18-bit           */
+    uint32_t reserved;
+} VVCB200PredBlock;         /* 32 bytes */
+
+/* Per-slice constants of inter prediction: PredWeightTable (vvc_ps.h:135-143) and the RefPicList -> DPB map. */
+typedef struct VVCB200InterParams {
+    int32_t  bit_depth;
+    int32_t  log2_denom[2];         /* luma, chroma                                            */
+    int32_t  reserved;
+    int16_t  weight[2][3][16];      /* [list][c_idx][ref_idx]                                  */
+    int16_t  offset[2][3][16];
+    uint8_t  ref_slot[2][16];       /* index into the `refs` array of (list, ref_idx)          */
+} VVCB200InterParams;
+
+/*
+ * Level A/B shared entry: predict every block into `dst` (fc->frame) from the reference pictures `refs`
+ * (host array of n_refs plane triples with device pointers).  Covers inter.put / put_uni / put_uni_w
+ * (vvcdsp.h:49-59) for luma 8-tap and chroma 4-tap, avg / w_avg (vvcdsp.h:61-66) incl. BCW, and the
+ * replicate-edge fetch of emulated_edge_mc (videodsp_template.c:27-105).
+ * If `d_tmp14` is non-NULL the 14-bit intermediate of list 0 (what inter.put writes, int16) is stored
+ * there instead of pixels (plane geometry of `dst`) — the checkasm-style view of inter.put.
+ * Blocks flagged VVCB200_PB_LMCS get lmcs.filter (vvcdsp.h:124) with the forward LUT on their luma.
+ */
+VVCB200_API int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes *refs, int n_refs,
+                                    const VVCB200PredBlock *d_blocks, int n, const VVCB200InterParams *params /* host */,
+                                    const uint16_t *d_lmcs_fwd_lut /* 1 << bit_depth entries, or NULL */,
+                                    const VVCB200Planes *d_tmp14, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);
  * a context is not thread-safe, different contexts are independent (replicas only).
  * All work is enqueued on the context's own CUDA stream and is asynchronous with respect to the host:

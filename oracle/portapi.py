@@ -43,3 +43,16 @@ def residual_batch(planes, levels, tbs, params, want_residual=False):
     lib().port_residual_batch(C.byref(pl), C.c_void_p(levels.ctypes.data), C.c_void_p(tbs.ctypes.data), len(tbs),
                               C.byref(params), C.c_void_p(res.ctypes.data) if res is not None else None)
     return res
+
+
+def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None):
+    pl = abi.host_planes(dst)
+    ra = abi.planes_array([abi.host_planes(r) for r in refs])
+    blocks = np.ascontiguousarray(blocks, abi.PB_DTYPE)
+    lut = None if lmcs_fwd_lut is None else np.ascontiguousarray(lmcs_fwd_lut, np.uint16)
+    t14 = None
+    if tmp14 is not None:
+        t14 = abi.host_planes([t.view(np.uint16) for t in tmp14])
+    lib().port_inter_batch(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks), C.byref(params),
+                           C.c_void_p(lut.ctypes.data) if lut is not None else None,
+                           C.byref(t14) if t14 is not None else None)

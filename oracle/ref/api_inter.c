@@ -6,3 +6,157 @@
  */
 #include "libavcodec/vvc/vvc_inter.c"
 #include "api_common.h"
+
+#include <stdlib.h>
+
+typedef struct InterEnv {
+    VVCFrameContext      fc;
+    SliceContext         sc;
+    AVFrame              frame;
+    VVCSPS               sps;
+    VVCPPS               pps;
+    H266RawSPS           rsps;
+    H266RawPPS           rpps;
+    H266RawPictureHeader rph;
+    H266RawSliceHeader   rsh;
+    RefPicList           rpl[2];
+    VVCFrame             cur;
+    VVCFrame             refs[16];
+    AVFrame              ref_frames[16];
+    CodingUnit           cu;
+} InterEnv;
+
+/*
+ * INTER stage for a batch of prediction sub-blocks on host planes through the reference's own
+ * predict_inter() (vvc_inter.c:875-892): each descriptor becomes a one-sub-block CodingUnit whose MvField
+ * is planted in fc->tab.mvf, so the reference's MV -> address arithmetic, edge emulation, weight
+ * derivation, DMVR search and BDOF all run unmodified.  Arguments mirror vvcb200_inter_batch().
+ * refined_mv (optional, n x 2 x 2 ints): MvField.mv after DMVR as stored in tab_dmvr_mvf.
+ */
+VVCREF_EXPORT int vvcref_inter_batch(const VVCRefPlanes *dst, const VVCRefPlanes *refs, int n_refs,
+                                     const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *p,
+                                     const uint16_t *lmcs_fwd_lut, int32_t *refined_mv)
+{
+    InterEnv *e         = calloc(1, sizeof(*e));
+    VVCLocalContext *lc = NULL;
+    int ret             = -1;
+    int min_pu_width, min_pu_height;
+
+    if (!e || n_refs > 16 || !(lc = aligned_alloc(64, (sizeof(*lc) + 63) & ~(size_t)63)))
+        return -1;
+    memset(lc, 0, sizeof(*lc));
+    e->fc.frame   = &e->frame;
+    e->fc.ps.sps  = &e->sps;
+    e->fc.ps.pps  = &e->pps;
+    e->fc.ps.ph.r = &e->rph;
+    e->fc.ref     = &e->cur;
+    e->sps.r      = &e->rsps;
+    e->pps.r      = &e->rpps;
+    e->sc.sh.r    = &e->rsh;
+    e->sc.rpl     = e->rpl;
+    lc->fc        = &e->fc;
+    lc->sc        = &e->sc;
+    lc->cu        = &e->cu;
+    for (int c = 0; c < 3; c++) {
+        e->frame.data[c]     = dst->plane[c];
+        e->frame.linesize[c] = dst->stride[c];
+    }
+    e->sps.width  = e->pps.width  = dst->width[0];
+    e->sps.height = e->pps.height = dst->height[0];
+    e->sps.bit_depth        = p->bit_depth;
+    e->sps.pixel_shift      = 1;
+    e->sps.hshift[1] = e->sps.hshift[2] = 1;
+    e->sps.vshift[1] = e->sps.vshift[2] = 1;
+    e->sps.ctb_log2_size_y  = 7;
+    e->sps.ctb_size_y       = 128;
+    e->rsps.sps_chroma_format_idc = 1;
+    e->rsh.sh_slice_type    = VVC_SLICE_TYPE_B;
+    min_pu_width  = e->pps.min_pu_width  = (dst->width[0]  + 3) >> 2;
+    min_pu_height = e->pps.min_pu_height = (dst->height[0] + 3) >> 2;
+    e->fc.tab.mvf        = calloc((size_t)min_pu_width * min_pu_height, sizeof(MvField));
+    e->cur.tab_dmvr_mvf  = calloc((size_t)min_pu_width * min_pu_height, sizeof(MvField));
+    if (!e->fc.tab.mvf || !e->cur.tab_dmvr_mvf)
+        goto end;
+    ff_vvc_dsp_init(&e->fc.vvcdsp, p->bit_depth);
+    ff_videodsp_init(&e->fc.vdsp, p->bit_depth);
+    for (int i = 0; i < n_refs; i++) {
+        for (int c = 0; c < 3; c++) {
+            e->ref_frames[i].data[c]     = refs[i].plane[c];
+            e->ref_frames[i].linesize[c] = refs[i].stride[c];
+        }
+        e->refs[i].frame = &e->ref_frames[i];
+    }
+    for (int l = 0; l < 2; l++)
+        for (int i = 0; i < 15; i++)
+            e->rpl[l].ref[i] = p->ref_slot[l][i] < n_refs ? &e->refs[p->ref_slot[l][i]] : NULL;
+    {
+        PredWeightTable *w = &e->sc.sh.pwt;
+        w->log2_denom[0] = p->log2_denom[0];
+        w->log2_denom[1] = p->log2_denom[1];
+        for (int l = 0; l < 2; l++)
+            for (int c = 0; c < 3; c++)
+                for (int i = 0; i < MAX_WEIGHTS; i++) {
+                    w->weight[l][c][i] = p->weight[l][c][i];
+                    w->offset[l][c][i] = p->offset[l][c][i];
+                }
+    }
+    if (lmcs_fwd_lut)
+        memcpy(e->fc.ps.lmcs.fwd_lut, lmcs_fwd_lut, sizeof(uint16_t) << p->bit_depth);
+
+    for (int i = 0; i < n; i++) {
+        const VVCB200PredBlock *b = &blocks[i];
+        CodingUnit *cu = &e->cu;
+        MvField mvf    = { 0 };
+
+        if (b->flags & (VVCB200_PB_LUMA_ONLY | VVCB200_PB_CHROMA_ONLY | VVCB200_PB_AFFINE | VVCB200_PB_CIIP))
+            goto end;                       /* affine / CIIP records are driven by the CU-level harness */
+        memset(cu, 0, sizeof(*cu));
+        cu->x0 = b->x0; cu->y0 = b->y0; cu->cb_width = b->w; cu->cb_height = b->h;
+        cu->pred_mode = MODE_INTER;
+        cu->pu.mi.num_sb_x = cu->pu.mi.num_sb_y = 1;
+        cu->pu.mi.hpel_if_idx = !!(b->flags & VVCB200_PB_HPEL_IF);
+        cu->pu.mi.pred_flag   = b->pred_flag;
+        cu->pu.bdof_flag      = !!(b->flags & VVCB200_PB_BDOF);
+        cu->pu.dmvr_flag      = !!(b->flags & VVCB200_PB_DMVR);
+        e->rpps.pps_weighted_bipred_flag = !!(b->flags & VVCB200_PB_WP);
+        e->rsh.sh_lmcs_used_flag         = !!(b->flags & VVCB200_PB_LMCS);
+        for (int l = 0; l < 2; l++) {
+            mvf.mv[l].x    = b->mv[l][0];
+            mvf.mv[l].y    = b->mv[l][1];
+            mvf.ref_idx[l] = b->ref_idx[l];
+        }
+        mvf.pred_flag   = b->pred_flag;
+        mvf.bcw_idx     = b->bcw_idx;
+        mvf.hpel_if_idx = cu->pu.mi.hpel_if_idx;
+        for (int y = b->y0 >> 2; y < (b->y0 + b->h) >> 2; y++)
+            for (int x = b->x0 >> 2; x < (b->x0 + b->w) >> 2; x++)
+                e->fc.tab.mvf[y * min_pu_width + x] = mvf;
+        predict_inter(lc);
+        if (refined_mv) {
+            const MvField *r = cu->pu.dmvr_flag ? &e->cur.tab_dmvr_mvf[(b->y0 >> 2) * min_pu_width + (b->x0 >> 2)] : &mvf;
+            for (int l = 0; l < 2; l++) {
+                refined_mv[i * 4 + l * 2 + 0] = r->mv[l].x;
+                refined_mv[i * 4 + l * 2 + 1] = r->mv[l].y;
+            }
+        }
+    }
+    ret = 0;
+end:
+    free(e->fc.tab.mvf);
+    free(e->cur.tab_dmvr_mvf);
+    free(lc);
+    free(e);
+    return ret;
+}
+
+/* inter.put[is_chroma][log2(w)-1][my != 0][mx != 0] (vvcdsp.h:49-51): src points at the block origin inside a
+ * caller-padded buffer; filters are the reference's own tables, set `filter_set`. dst stride is MAX_PB_SIZE. */
+VVCREF_EXPORT void vvcref_put(int bd, int is_chroma, int16_t *dst, const uint8_t *src, ptrdiff_t src_stride,
+                              int w, int h, int mx, int my, int filter_set)
+{
+    VVCDSPContext c;
+    const int8_t *hf = is_chroma ? ff_vvc_inter_chroma_filters[filter_set][mx] : ff_vvc_inter_luma_filters[filter_set][mx];
+    const int8_t *vf = is_chroma ? ff_vvc_inter_chroma_filters[filter_set][my] : ff_vvc_inter_luma_filters[filter_set][my];
+    ff_vvc_dsp_init(&c, bd);
+    c.inter.put[is_chroma][av_log2(w) - 1][!!my][!!mx](dst, src, src_stride, h, hf, vf, w);
+}

@@ -60,3 +60,18 @@ def residual_batch(planes, levels, tbs, params, intra_mode=None, want_residual=F
     if r != 0:
         raise RuntimeError("vvcref_residual_batch rejected a descriptor")
     return res
+
+
+def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, want_refined_mv=False):
+    """Reference predict_inter() over a batch of sub-block descriptors; dst/refs are lists of 3 uint16 arrays."""
+    pl = abi.host_planes(dst)
+    ra = abi.planes_array([abi.host_planes(r) for r in refs])
+    blocks = np.ascontiguousarray(blocks, abi.PB_DTYPE)
+    lut = None if lmcs_fwd_lut is None else np.ascontiguousarray(lmcs_fwd_lut, np.uint16)
+    mv = np.zeros((len(blocks), 2, 2), np.int32) if want_refined_mv else None
+    r = lib().vvcref_inter_batch(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks),
+                                 C.byref(params), C.c_void_p(lut.ctypes.data) if lut is not None else None,
+                                 C.c_void_p(mv.ctypes.data) if mv is not None else None)
+    if r != 0:
+        raise RuntimeError("vvcref_inter_batch rejected a descriptor")
+    return mv

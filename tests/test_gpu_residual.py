@@ -129,3 +129,30 @@ def test_full_size_properties_1080p():
     util.oracle_residual(want, sample)
     got = _run_gpu(sample, base)
     assert util.plane_md5(got) == util.plane_md5(want)
+
+
+def test_level_b_context_host_buffers():
+    """The picture engine with HOST buffers (upload -> residual -> download) equals the oracle."""
+    pic = synth.residual_picture(31, 416, 240)
+    base = util.noise_planes(31, pic["dims"])
+    want = [p.copy() for p in base]
+    util.oracle_residual(want, pic)
+    ctx = lib.Context(0, 416, 240)
+    try:
+        src = ctx.pinned_planes()
+        out = ctx.pinned_planes()
+        for s, b in zip(src, base):
+            s[...] = b
+        levels = ctx.pinned(pic["levels"].shape, np.int16)
+        levels[...] = pic["levels"]
+        tbs = ctx.pinned(pic["tbs"].shape, abi.TB_DTYPE)
+        tbs[...] = pic["tbs"]
+        for _ in range(2):                      # twice: the second picture reuses the device buffers
+            ctx.begin()
+            ctx.upload(src)
+            ctx.residual(levels, tbs, pic["params"])
+            ctx.download(out)
+            ctx.sync()
+            assert util.plane_md5(out) == util.plane_md5(want)
+    finally:
+        ctx.close()

@@ -50,10 +50,21 @@ def golden_residual():
     return out
 
 
+def golden_inter():
+    out = {}
+    for name, seed, w, h, n_refs in (("a", 21, 352, 288, 2), ("b", 22, 416, 240, 4)):
+        pic = synth.inter_picture(seed, w, h, n_refs=n_refs)
+        planes = util.noise_planes(seed, pic["dims"])
+        refapi.inter_batch(planes, pic["refs"], pic["blocks"], pic["params"])
+        out[name + "_plane_md5"] = np.array(util.plane_md5(planes))
+        out[name + "_args"] = np.array([seed, w, h, n_refs], np.int32)
+    return out
+
+
 def main():
     check = "--check" in sys.argv
     os.makedirs(util.GOLDEN, exist_ok=True)
-    for name, fn in (("itx", golden_itx), ("residual", golden_residual)):
+    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter)):
         data = fn()
         path = os.path.join(util.GOLDEN, name + ".npz")
         if check:
