@@ -105,3 +105,19 @@ def planes_array(list_of_planes):
     for i, p in enumerate(list_of_planes):
         arr[i] = p
     return arr
+
+
+# ---- deblocking ----------------------------------------------------------------------------------------------
+class DeblockParams(C.Structure):
+    _fields_ = [
+        ("bit_depth", C.c_int32), ("ctb_log2_size", C.c_int32), ("ladf_enabled", C.c_int32),
+        ("ladf_lowest_interval_qp_offset", C.c_int32), ("num_ladf_intervals", C.c_int32),
+        ("ladf_qp_offset", C.c_int32 * 4), ("ladf_interval_lower_bound", C.c_int32 * 5),
+    ]
+
+
+class DeblockTables(C.Structure):
+    _fields_ = [
+        ("edge", (C.c_void_p * 3) * 2), ("qp", C.c_void_p * 3), ("ctb_offsets", C.c_void_p),
+        ("stride4", C.c_int32), ("reserved", C.c_int32),
+    ]

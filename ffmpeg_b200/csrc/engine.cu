@@ -233,3 +233,43 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
 }
 
 }  // extern "C"
+
+// ---- host-side descriptor producers ----------------------------------------------------------------------
+extern "C" int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const uint8_t *const bs[2][3],
+                                          const uint8_t *const len_p[2], const uint8_t *const len_q[2],
+                                          const uint8_t *tb_w_c, const uint8_t *tb_h_c,
+                                          int stride4, int rows4, int ctb_log2_size)
+{
+    if (!edge_out || !bs || !len_p || !len_q || !tb_w_c || !tb_h_c || stride4 <= 0 || rows4 <= 0) {
+        set_error("vvcb200_pack_deblock_edges: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    const int ctb_units = 1 << (ctb_log2_size - 2);
+    for (int dir = 0; dir < 2; dir++) {
+        const int vertical = dir == 0;
+        for (int uy = 0; uy < rows4; uy++) {
+            for (int ux = 0; ux < stride4; ux++) {
+                const int u = uy * stride4 + ux;
+                const int b0 = bs[dir][0][u] & 3;
+                edge_out[dir][0][u] = (uint8_t)(b0 | ((len_p[dir][u] & 7) << 2) | ((len_q[dir][u] & 7) << 5));
+                // chroma lengths: max_filter_length_chroma(), vvc_filter.c:796-817
+                const int pu = vertical ? (ux ? u - 1 : u) : (uy ? u - stride4 : u);
+                const uint8_t *size = vertical ? tb_w_c : tb_h_c;
+                const int big = size[pu] >= 8 && size[u] >= 8;
+                const int ctu_edge = !vertical && !(uy % ctb_units);
+                for (int c = 1; c < 3; c++) {
+                    const int b = bs[dir][c][u] & 3;
+                    int lp, lq;
+                    if (big) {
+                        lq = 3;
+                        lp = ctu_edge ? 1 : 3;
+                    } else {
+                        lp = lq = b == 2;
+                    }
+                    edge_out[dir][c][u] = (uint8_t)(b | (lp << 2) | (lq << 5));
+                }
+            }
+        }
+    }
+    return 0;
+}

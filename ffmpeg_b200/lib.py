@@ -172,3 +172,37 @@ def inter_batch(dst, refs, blocks, n, params, lmcs_fwd_lut=None, tmp14=None, str
     check(load().vvcb200_inter_batch(
         C.byref(dst) if dst is not None else None, ra, len(refs), _ptr(blocks), int(n), C.byref(params),
         _ptr(lmcs_fwd_lut), C.byref(tmp14) if tmp14 is not None else None, _stream(stream)))
+
+
+def _ptr_grid(tabs, shape):
+    if len(shape) == 1:
+        return (C.c_void_p * shape[0])(*[tabs[i].ctypes.data for i in range(shape[0])])
+    inner = C.c_void_p * shape[1]
+    return (inner * shape[0])(*[inner(*[tabs[i, j].ctypes.data for j in range(shape[1])]) for i in range(shape[0])])
+
+
+def pack_deblock_edges(bs, len_p, len_q, tb_w_c, tb_h_c, ctb_log2, out=None):
+    """vvcb200_pack_deblock_edges (host, no CUDA): reference-format tables -> packed edge bytes [2][3][rows4][stride4]."""
+    rows4, stride4 = bs.shape[-2:]
+    if out is None:
+        out = np.zeros((2, 3, rows4, stride4), np.uint8)
+    check(load().vvcb200_pack_deblock_edges(_ptr_grid(out, (2, 3)), _ptr_grid(bs, (2, 3)), _ptr_grid(len_p, (2,)),
+                                            _ptr_grid(len_q, (2,)), _ptr(tb_w_c), _ptr(tb_h_c), stride4, rows4, ctb_log2))
+    return out
+
+
+def deblock_tables(edge, qp, ctb_offsets, stride4):
+    """DeblockTables struct over device tensors: edge [2][3][r4][s4] uint8, qp [3][r4][s4] int8, ctb_offsets [n][6] int8."""
+    t = abi.DeblockTables()
+    for d in range(2):
+        for c in range(3):
+            t.edge[d][c] = edge[d][c].data_ptr() if hasattr(edge, "data_ptr") else edge[d, c].ctypes.data
+    for c in range(3):
+        t.qp[c] = qp[c].data_ptr() if hasattr(qp, "data_ptr") else qp[c].ctypes.data
+    t.ctb_offsets = ctb_offsets.data_ptr() if hasattr(ctb_offsets, "data_ptr") else ctb_offsets.ctypes.data
+    t.stride4 = stride4
+    return t
+
+
+def deblock_picture(pic, tables, params, stream=None):
+    check(load().vvcb200_deblock_picture(C.byref(pic), C.byref(tables), C.byref(params), _stream(stream)))

@@ -251,3 +251,80 @@ def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     return dict(blocks=b, params=params, refs=refs, dims=dims, seed=seed)
+
+
+# ---- deblocking --------------------------------------------------------------------------------------------
+def deblock_picture(seed, width, height, ctb_log2=7, ladf=None, bs_prob=(0.25, 0.4, 0.35)):
+    """Per-4x4 deblocking tables in the REFERENCE's format (fc->tab.vertical_bs & co, vvcdec.h:158-163), derived
+    from a random TB partition with the reference's own length rules (vvc_filter.c:374-397, 418-427) so that
+    neighbouring edges never overlap, plus QP tables, per-CTB offsets and LADF parameters."""
+    rng = np.random.default_rng(seed)
+    s4, r4 = (width + 3) // 4, (height + 3) // 4
+    bs = np.zeros((2, 3, r4, s4), np.uint8)
+    len_p = np.zeros((2, r4, s4), np.uint8)
+    len_q = np.zeros((2, r4, s4), np.uint8)
+    tb = np.zeros((2, r4, s4), np.int32)            # luma TB width / height per unit
+    sb = np.zeros((r4, s4), bool)                   # unit belongs to a sub-block (affine / sbTMVP) CU
+    qp = np.zeros((3, r4, s4), np.int8)
+    luma = random_tiling(rng, width, height, 64, 4, 4.0)
+    for (x, y, w, h) in luma:
+        ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
+        tb[0, uy:uy + uh, ux:ux + uw] = w
+        tb[1, uy:uy + uh, ux:ux + uw] = h
+        sb[uy:uy + uh, ux:ux + uw] = w > 8 and h > 8 and rng.random() < 0.25
+        qp[0, uy:uy + uh, ux:ux + uw] = rng.integers(10, 56)
+    pick = lambda n: rng.choice(3, n, p=bs_prob).astype(np.uint8)
+    for (x, y, w, h) in luma:
+        ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
+        for d, (pos, size, ext, uext) in enumerate(((x, w, h, uh), (y, h, w, uw))):
+            sl = (slice(uy, uy + uh), ux) if d == 0 else (uy, slice(ux, ux + uw))
+            if pos > 0:                              # transform edge on the left / top side of this TB
+                size_p = tb[d][uy:uy + uh, ux - 1] if d == 0 else tb[d][uy - 1, ux:ux + uw]
+                sb_p = sb[uy:uy + uh, ux - 1] if d == 0 else sb[uy - 1, ux:ux + uw]
+                small = (size_p <= 4) | (size <= 4)
+                lp = np.where(small, 1, np.where(size_p >= 32, 7, 3))
+                lq = np.where(small, 1, 7 if size >= 32 else 3)
+                if sb[uy, ux]:
+                    lq = np.minimum(lq, 5)
+                lp = np.where(sb_p, np.minimum(lp, 5), lp)
+                bs[d, 0][sl] = pick(uext)
+                len_p[d][sl] = lp
+                len_q[d][sl] = lq
+            if sb[uy, ux]:                           # sub-block edges every 8 samples inside the TB
+                for i in range(8, size, 8):
+                    ln = 2 if i in (8, size - 8) else 3
+                    sl2 = (slice(uy, uy + uh), ux + (i >> 2)) if d == 0 else (uy + (i >> 2), slice(ux, ux + uw))
+                    bs[d, 0][sl2] = rng.integers(0, 2, uext)
+                    len_p[d][sl2] = ln
+                    len_q[d][sl2] = ln
+    # chroma: its own TB partition (chroma samples), edges only on the 8-chroma-sample grid
+    tbc = np.zeros((2, r4, s4), np.uint8)
+    chroma = random_tiling(rng, width // 2, height // 2, 32, 4, 3.2)
+    for (x, y, w, h) in chroma:
+        ux, uy, uw, uh = x >> 1, y >> 1, max(w >> 1, 1), max(h >> 1, 1)
+        tbc[0, uy:uy + uh, ux:ux + uw] = w
+        tbc[1, uy:uy + uh, ux:ux + uw] = h
+        q = rng.integers(22, 68, 2)
+        qp[1, uy:uy + uh, ux:ux + uw] = q[0]
+        qp[2, uy:uy + uh, ux:ux + uw] = q[1]
+        if x > 0 and x % 8 == 0:
+            for c in (1, 2):
+                bs[0, c, uy:uy + uh, ux] = pick(uh)
+        if y > 0 and y % 8 == 0:
+            for c in (1, 2):
+                bs[1, c, uy, ux:ux + uw] = pick(uw)
+    n_ctb = ((width + (1 << ctb_log2) - 1) >> ctb_log2) * ((height + (1 << ctb_log2) - 1) >> ctb_log2)
+    ctb_offsets = rng.integers(-12, 13, (n_ctb, 6)).astype(np.int8)
+    p = abi.DeblockParams()
+    p.bit_depth, p.ctb_log2_size = 10, ctb_log2
+    use_ladf = bool(rng.random() < 0.5) if ladf is None else ladf
+    if use_ladf:
+        p.ladf_enabled, p.num_ladf_intervals = 1, 4
+        p.ladf_lowest_interval_qp_offset = int(rng.integers(-6, 7))
+        for i in range(4):
+            p.ladf_qp_offset[i] = int(rng.integers(-6, 7))
+        bounds = [0] + sorted(int(v) for v in rng.integers(100, 900, 3)) + [0]
+        for i in range(5):
+            p.ladf_interval_lower_bound[i] = bounds[i]
+    return dict(bs=bs, len_p=len_p, len_q=len_q, tb_w_c=tbc[0], tb_h_c=tbc[1], qp=qp, ctb_offsets=ctb_offsets,
+                params=p, stride4=s4, rows4=r4, dims=plane_dims(width, height), seed=seed)

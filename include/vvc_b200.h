@@ -187,6 +187,49 @@ VVCB200_API int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Plane
                                     const VVCB200Planes *d_tmp14, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * Deblocking (stages DEBLOCK_V / DEBLOCK_H, ff_vvc_deblock_vertical/horizontal, vvc_filter.c:861-1003,
+ * lf.filter_luma / filter_chroma / ladf_level, vvcdsp.h:126-133).
+ * Boundary strengths and filter lengths are host-type table logic over CU/TU/MV state
+ * (vvc_deblock_bs, vvc_filter.c:308-782); the host derives them exactly as the reference does and hands
+ * the device the per-4x4 tables below.  All tables are indexed by luma 4x4 unit:
+ * t[(y >> 2) * stride4 + (x >> 2)], like fc->tab.vertical_bs & co (vvcdec.h:158-163).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VVCB200DeblockParams {
+    int32_t bit_depth;
+    int32_t ctb_log2_size;                  /* sps->ctb_log2_size_y                                       */
+    int32_t ladf_enabled;                   /* sps_ladf_enabled_flag (vvc_filter.c:835)                   */
+    int32_t ladf_lowest_interval_qp_offset;
+    int32_t num_ladf_intervals;             /* sps->num_ladf_intervals                                    */
+    int32_t ladf_qp_offset[4];              /* sps_ladf_qp_offset[]                                       */
+    int32_t ladf_interval_lower_bound[5];   /* sps->ladf_interval_lower_bound[]                           */
+} VVCB200DeblockParams;
+
+typedef struct VVCB200DeblockTables {
+    const uint8_t *d_edge[2][3];    /* [0: vertical edges, 1: horizontal edges][c_idx]; one byte per unit:
+                                       bs (bits 1:0) | maxFilterLengthP << 2 | maxFilterLengthQ << 5        */
+    const int8_t  *d_qp[3];         /* QpY / Qp'Cb / Qp'Cr of the unit (fc->tab.qp[], vvcdec.h:131)        */
+    const int8_t  *d_ctb_offsets;   /* per CTB (raster): beta_offset[3] then tc_offset[3] (DBParams)        */
+    int32_t        stride4;         /* units per table row (pps->min_tu_width)                             */
+    int32_t        reserved;
+} VVCB200DeblockTables;
+
+/*
+ * Host helper (pure CPU, no CUDA): fold the reference's table set — vertical_bs/horizontal_bs[3],
+ * vertical_p/q, horizontal_p/q (luma lengths) and the chroma TB size tables used by
+ * max_filter_length_chroma (vvc_filter.c:796-817) — into the packed edge bytes above.
+ * `bs[dir][c]`, `len_p[dir]`, `len_q[dir]`, `tb_w_c`, `tb_h_c`: host tables of stride4 x rows4 bytes;
+ * `edge_out[dir][c]`: host output tables of the same size.  Luma coordinates; 4:2:0.
+ */
+VVCB200_API int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const uint8_t *const bs[2][3],
+                                           const uint8_t *const len_p[2], const uint8_t *const len_q[2],
+                                           const uint8_t *tb_w_c, const uint8_t *tb_h_c,
+                                           int stride4, int rows4, int ctb_log2_size);
+
+/* Both deblocking passes over the whole picture, in place: all vertical edges, then all horizontal edges. */
+VVCB200_API int vvcb200_deblock_picture(const VVCB200Planes *pic, const VVCB200DeblockTables *tables /* host struct */,
+                                        const VVCB200DeblockParams *params /* host */, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);
  * a context is not thread-safe, different contexts are independent (replicas only).
  * All work is enqueued on the context's own CUDA stream and is asynchronous with respect to the host:

@@ -56,3 +56,11 @@ def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None):
     lib().port_inter_batch(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks), C.byref(params),
                            C.c_void_p(lut.ctypes.data) if lut is not None else None,
                            C.byref(t14) if t14 is not None else None)
+
+
+def deblock_picture(planes, edge, qp, ctb_offsets, stride4, params):
+    """Port of both deblocking passes; edge = packed bytes [2][3][r4][s4] (host numpy)."""
+    from ffmpeg_b200 import lib as product
+    pl = abi.host_planes(planes)
+    t = product.deblock_tables(edge, qp, ctb_offsets, stride4)
+    lib().port_deblock_picture(C.byref(pl), C.byref(t), C.byref(params))

@@ -6,3 +6,150 @@
  */
 #include "libavcodec/vvc/vvc_filter.c"
 #include "api_common.h"
+
+#include <stdlib.h>
+
+typedef struct FilterEnv {
+    VVCFrameContext      fc;
+    VVCLocalContext     *lc;
+    SliceContext         sc;
+    AVFrame              frame;
+    VVCSPS               sps;
+    VVCPPS               pps;
+    H266RawSPS           rsps;
+    H266RawPPS           rpps;
+    H266RawPictureHeader rph;
+    H266RawSliceHeader   rsh;
+    RefPicList           rpl[2];
+    uint16_t            *col_bd, *row_bd;
+} FilterEnv;
+
+static FilterEnv *filter_env_new(const VVCRefPlanes *pl, int bit_depth, int ctb_log2)
+{
+    FilterEnv *e = calloc(1, sizeof(*e));
+    if (!e)
+        return NULL;
+    e->lc = aligned_alloc(64, (sizeof(*e->lc) + 63) & ~(size_t)63);
+    memset(e->lc, 0, sizeof(*e->lc));
+    e->fc.frame   = &e->frame;
+    e->fc.ps.sps  = &e->sps;
+    e->fc.ps.pps  = &e->pps;
+    e->fc.ps.ph.r = &e->rph;
+    e->sps.r      = &e->rsps;
+    e->pps.r      = &e->rpps;
+    e->sc.sh.r    = &e->rsh;
+    e->sc.rpl     = e->rpl;
+    e->lc->fc     = &e->fc;
+    e->lc->sc     = &e->sc;
+    for (int c = 0; c < 3; c++) {
+        e->frame.data[c]     = pl->plane[c];
+        e->frame.linesize[c] = pl->stride[c];
+    }
+    e->sps.width  = e->pps.width  = pl->width[0];
+    e->sps.height = e->pps.height = pl->height[0];
+    e->sps.bit_depth          = bit_depth;
+    e->sps.qp_bd_offset       = 6 * (bit_depth - 8);
+    e->sps.pixel_shift        = 1;
+    e->sps.hshift[1] = e->sps.hshift[2] = 1;
+    e->sps.vshift[1] = e->sps.vshift[2] = 1;
+    e->sps.ctb_log2_size_y    = ctb_log2;
+    e->sps.ctb_size_y         = 1 << ctb_log2;
+    e->sps.min_cb_log2_size_y = 2;
+    e->rsps.sps_chroma_format_idc = 1;
+    e->pps.ctb_width   = (pl->width[0]  + (1 << ctb_log2) - 1) >> ctb_log2;
+    e->pps.ctb_height  = (pl->height[0] + (1 << ctb_log2) - 1) >> ctb_log2;
+    e->pps.ctb_count   = e->pps.ctb_width * e->pps.ctb_height;
+    e->pps.min_cb_width = e->pps.min_pu_width = e->pps.min_tu_width = (pl->width[0] + 3) >> 2;
+    e->pps.min_cb_height = e->pps.min_pu_height = e->pps.min_tu_height = (pl->height[0] + 3) >> 2;
+    /* one tile, one slice: all CTBs map to tile column/row 0 */
+    e->col_bd = calloc(e->pps.ctb_width + 2, sizeof(uint16_t));
+    e->row_bd = calloc(e->pps.ctb_height + 2, sizeof(uint16_t));
+    e->pps.ctb_to_col_bd = e->col_bd;
+    e->pps.ctb_to_row_bd = e->row_bd;
+    e->fc.tab.slice_idx  = calloc(e->pps.ctb_count, sizeof(int16_t));
+    e->rpps.pps_loop_filter_across_slices_enabled_flag = 1;
+    e->rpps.pps_loop_filter_across_tiles_enabled_flag  = 1;
+    ff_vvc_dsp_init(&e->fc.vvcdsp, bit_depth);
+    ff_videodsp_init(&e->fc.vdsp, bit_depth);
+    return e;
+}
+
+static void filter_env_free(FilterEnv *e)
+{
+    free(e->fc.tab.slice_idx);
+    free(e->col_bd);
+    free(e->row_bd);
+    free(e->lc);
+    free(e);
+}
+
+/*
+ * DEBLOCK_V then DEBLOCK_H over a whole picture through the reference's own ff_vvc_deblock_vertical /
+ * ff_vvc_deblock_horizontal (vvc_filter.c:861-1003), CTU by CTU in raster order.  The boundary-strength and
+ * filter-length tables (fc->tab.vertical_bs & co) are planted by the caller in the reference's own format;
+ * the TB-position tables are filled with a value that never matches, so vvc_deblock_bs() (vvc_filter.c:756)
+ * visits no TB and leaves the planted tables as they are.
+ *   bs[dir][c], len_p[dir], len_q[dir], tb_w_c, tb_h_c, qp[c]: stride4 x rows4 bytes, luma 4x4 units
+ *   ctb_offsets: per CTB beta_offset[3], tc_offset[3]
+ */
+VVCREF_EXPORT int vvcref_deblock_picture(const VVCRefPlanes *pl, const uint8_t *const bs[2][3],
+                                         const uint8_t *const len_p[2], const uint8_t *const len_q[2],
+                                         const uint8_t *tb_w_c, const uint8_t *tb_h_c, const int8_t *const qp[3],
+                                         const int8_t *ctb_offsets, const VVCB200DeblockParams *p)
+{
+    FilterEnv *e = filter_env_new(pl, p->bit_depth, p->ctb_log2_size);
+    const size_t units = (size_t)e->pps.min_tu_width * e->pps.min_tu_height;
+    uint8_t *copy[10];
+    int *never = malloc(units * sizeof(int));
+    DBParams *db = calloc(e->pps.ctb_count, sizeof(*db));
+    int k = 0;
+
+    for (size_t i = 0; i < units; i++)
+        never[i] = -4;
+    for (int i = 0; i < 2; i++)
+        e->fc.tab.tb_pos_x0[i] = e->fc.tab.tb_pos_y0[i] = never;
+#define DUP(src) (copy[k] = malloc(units), memcpy(copy[k], (src), units), copy[k++])
+    for (int c = 0; c < 3; c++) {
+        e->fc.tab.vertical_bs[c]   = DUP(bs[0][c]);
+        e->fc.tab.horizontal_bs[c] = DUP(bs[1][c]);
+        e->fc.tab.qp[c]            = (int8_t *)qp[c];
+    }
+    e->fc.tab.vertical_p   = DUP(len_p[0]);
+    e->fc.tab.vertical_q   = DUP(len_q[0]);
+    e->fc.tab.horizontal_p = DUP(len_p[1]);
+    e->fc.tab.horizontal_q = DUP(len_q[1]);
+    e->fc.tab.tb_width[CHROMA]  = (uint8_t *)tb_w_c;
+    e->fc.tab.tb_height[CHROMA] = (uint8_t *)tb_h_c;
+    e->fc.tab.tb_width[LUMA]    = (uint8_t *)tb_w_c;     /* not read: lengths come from the planted tables */
+    e->fc.tab.tb_height[LUMA]   = (uint8_t *)tb_h_c;
+    for (unsigned i = 0; i < e->pps.ctb_count; i++)
+        for (int c = 0; c < 3; c++) {
+            db[i].beta_offset[c] = ctb_offsets[i * 6 + c];
+            db[i].tc_offset[c]   = ctb_offsets[i * 6 + 3 + c];
+        }
+    e->fc.tab.deblock = db;
+    e->rsps.sps_ladf_enabled_flag = p->ladf_enabled;
+    e->rsps.sps_ladf_lowest_interval_qp_offset = p->ladf_lowest_interval_qp_offset;
+    e->sps.num_ladf_intervals = p->num_ladf_intervals;
+    for (int i = 0; i < 4; i++)
+        e->rsps.sps_ladf_qp_offset[i] = p->ladf_qp_offset[i];
+    for (int i = 0; i < 5; i++)
+        e->sps.ladf_interval_lower_bound[i] = p->ladf_interval_lower_bound[i];
+
+    for (int pass = 0; pass < 2; pass++)
+        for (int ry = 0; ry < e->pps.ctb_height; ry++)
+            for (int rx = 0; rx < e->pps.ctb_width; rx++) {
+                const int x0 = rx << p->ctb_log2_size, y0 = ry << p->ctb_log2_size;
+                ff_vvc_decode_neighbour(e->lc, x0, y0, rx, ry, ry * e->pps.ctb_width + rx);
+                if (!pass)
+                    ff_vvc_deblock_vertical(e->lc, x0, y0);
+                else
+                    ff_vvc_deblock_horizontal(e->lc, x0, y0);
+            }
+    while (k)
+        free(copy[--k]);
+    free(never);
+    free(db);
+    filter_env_free(e);
+    return 0;
+}

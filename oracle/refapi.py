@@ -75,3 +75,22 @@ def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, want_refined_mv=Fa
     if r != 0:
         raise RuntimeError("vvcref_inter_batch rejected a descriptor")
     return mv
+
+
+def _ptr_grid(tabs, shape):
+    """ctypes array-of-pointers (nested) over a numpy array of tables whose last two axes are one table."""
+    if len(shape) == 1:
+        return (C.c_void_p * shape[0])(*[tabs[i].ctypes.data for i in range(shape[0])])
+    inner = C.c_void_p * shape[1]
+    return (inner * shape[0])(*[inner(*[tabs[i, j].ctypes.data for j in range(shape[1])]) for i in range(shape[0])])
+
+
+def deblock_picture(planes, t):
+    """Reference ff_vvc_deblock_vertical/horizontal over the picture; `t` is synth.deblock_picture()."""
+    pl = abi.host_planes(planes)
+    for k in ("bs", "len_p", "len_q", "tb_w_c", "tb_h_c", "qp", "ctb_offsets"):
+        assert t[k].flags.c_contiguous
+    lib().vvcref_deblock_picture(C.byref(pl), _ptr_grid(t["bs"], (2, 3)), _ptr_grid(t["len_p"], (2,)),
+                                 _ptr_grid(t["len_q"], (2,)), C.c_void_p(t["tb_w_c"].ctypes.data),
+                                 C.c_void_p(t["tb_h_c"].ctypes.data), _ptr_grid(t["qp"], (3,)),
+                                 C.c_void_p(t["ctb_offsets"].ctypes.data), C.byref(t["params"]))

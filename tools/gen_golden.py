@@ -61,10 +61,21 @@ def golden_inter():
     return out
 
 
+def golden_deblock():
+    out = {}
+    for name, seed, w, h, ctb in (("a", 31, 352, 288, 7), ("b", 32, 416, 240, 6)):
+        t = synth.deblock_picture(seed, w, h, ctb_log2=ctb)
+        planes = synth.smooth_planes(seed, t["dims"])
+        refapi.deblock_picture(planes, t)
+        out[name + "_plane_md5"] = np.array(util.plane_md5(planes))
+        out[name + "_args"] = np.array([seed, w, h, ctb], np.int32)
+    return out
+
+
 def main():
     check = "--check" in sys.argv
     os.makedirs(util.GOLDEN, exist_ok=True)
-    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter)):
+    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter), ("deblock", golden_deblock)):
         data = fn()
         path = os.path.join(util.GOLDEN, name + ".npz")
         if check:
