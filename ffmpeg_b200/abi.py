@@ -121,3 +121,24 @@ class DeblockTables(C.Structure):
         ("edge", (C.c_void_p * 3) * 2), ("qp", C.c_void_p * 3), ("ctb_offsets", C.c_void_p),
         ("stride4", C.c_int32), ("reserved", C.c_int32),
     ]
+
+
+# ---- SAO / ALF -------------------------------------------------------------------------------------------------
+SAO_DTYPE = np.dtype([
+    ("type_idx", "u1", (3,)), ("band_position", "u1", (3,)), ("eo_class", "u1", (3,)), ("no_filter", "u1"),
+    ("offset_val", "<i2", (3, 5)),
+], align=False)
+assert SAO_DTYPE.itemsize == 40
+
+ALF_CTB_DTYPE = np.dtype([
+    ("ctb_flag", "u1", (3,)), ("filt_set_idx_y", "u1"), ("alt_idx", "u1", (2,)), ("cc_idc", "u1", (2,)),
+    ("edges", "u1"), ("reserved", "u1", (3,)),
+], align=False)
+assert ALF_CTB_DTYPE.itemsize == 12
+
+ALF_PARAMS_DTYPE = np.dtype([
+    ("bit_depth", "<i4"), ("ctb_log2_size", "<i4"),
+    ("luma_coeff", "<i2", (7, 25, 12)), ("luma_clip_idx", "u1", (7, 25, 12)),
+    ("chroma_coeff", "<i2", (8, 6)), ("chroma_clip_idx", "u1", (8, 6)),
+    ("cc_coeff", "<i2", (2, 4, 7)), ("cc_enabled", "<i4", (2,)),
+], align=True)

@@ -1,0 +1,368 @@
+// alf.cu — stage ALF as out-of-place picture passes: luma (4x4 classification + 7x7 diamond), chroma (5x5
+// diamond) + CC-ALF.
+// Reference semantics: ff_vvc_alf_filter and its buffer preparation (libavcodec/vvc/vvc_filter.c:1005-1319),
+// alf.classify / recon_coeff_and_clip / filter[luma|chroma] / filter_cc (vvc_filter_template.c:38-408).
+//
+// The reference pads each CTB with its neighbours' pre-ALF samples, or — at a picture / slice / tile limit —
+// with replicated CTB samples (alf_prepare_buffer).  Here that is a per-CTB coordinate clamp applied while a
+// 32x32 tile (+3 halo) is staged into shared memory from the SAO output plane.  Virtual-boundary handling
+// (row substitution around ctb_size-4, the >>10 rounding next to it, the reduced classification window)
+// follows the template exactly.
+#include "common.cuh"
+
+#define VVC_TABLE_QUAL static __device__ const
+#include "vvc_tables.h"
+
+namespace vvcb200 {
+
+constexpr int kTile   = 32;
+constexpr int kHalo   = 3;
+constexpr int kPad    = kTile + 2 * kHalo;       // 38
+constexpr int kPadStr = kPad + 2;                // 40 samples per staged row
+constexpr int kCells  = kTile / 2 + 2;           // 18 gradient cells per tile side
+
+struct AlfArgs {
+    PlanesView dst, src;
+    const VVCB200AlfCtb *ctbs;
+    const VVCB200AlfParams *params;
+    int ctb_log2, ctb_width, bd;
+};
+
+struct CtbGeom {
+    int x0, y0, w, h;      // CTB rectangle in the component's plane
+    int edges;             // bit0 L, bit1 T, bit2 R, bit3 B incl. picture borders
+};
+
+__device__ __forceinline__ CtbGeom ctb_geom(const AlfArgs &a, int c, int x, int y, int edges)
+{
+    CtbGeom g;
+    const int l2 = a.ctb_log2 - (c ? 1 : 0);
+    g.x0 = (x >> l2) << l2;
+    g.y0 = (y >> l2) << l2;
+    g.w = min(1 << l2, a.src.w[c] - g.x0);
+    g.h = min(1 << l2, a.src.h[c] - g.y0);
+    g.edges = edges | (g.x0 == 0 ? 1 : 0) | (g.y0 == 0 ? 2 : 0) |
+              (g.x0 + g.w >= a.src.w[c] ? 4 : 0) | (g.y0 + g.h >= a.src.h[c] ? 8 : 0);
+    return g;
+}
+
+// alf_prepare_buffer as a coordinate clamp: source sample seen by CTB g at plane position (x, y)
+__device__ __forceinline__ int padded_sample(const uint16_t *plane, int stride, const CtbGeom &g, int x, int y)
+{
+    if (x < g.x0 && (g.edges & 1)) x = g.x0;
+    if (x >= g.x0 + g.w && (g.edges & 4)) x = g.x0 + g.w - 1;
+    if (y < g.y0 && (g.edges & 2)) y = g.y0;
+    if (y >= g.y0 + g.h && (g.edges & 8)) y = g.y0 + g.h - 1;
+    return plane[(size_t)y * stride + x];
+}
+
+// row offsets of the taps one / two / three rows away for a sample at CTB row yy (vvc_filter_template.c:83-101)
+__device__ __forceinline__ void vb_rows(int yy, int vb, int reach, int &o1, int &o2, int &o3, bool &near_vb)
+{
+    o1 = 1; o2 = 2; o3 = 3;
+    if (yy < vb && yy >= vb - reach - 1) {
+        o1 = yy == vb - 1 ? 0 : 1;
+        o2 = yy >= vb - 2 ? o1 : 2;
+        o3 = yy >= vb - 3 ? o2 : 3;
+    } else if (yy >= vb && yy <= vb + reach) {
+        o1 = yy == vb ? 0 : 1;
+        o2 = yy <= vb + 1 ? o1 : 2;
+        o3 = yy <= vb + 2 ? o2 : 3;
+    }
+    near_vb = yy == vb - 1 || yy == vb;
+}
+
+__device__ __forceinline__ int alf_clip2(int curr, int v0, int v1, int c)
+{
+    return clip3(v0 - curr, -c, c) + clip3(v1 - curr, -c, c);
+}
+
+__global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
+{
+    __shared__ uint16_t s_pix[kPad * kPadStr];
+    __shared__ uint16_t s_grad[kCells * kCells][4];
+    __shared__ int16_t  s_coef[64][12];
+    __shared__ int16_t  s_clip[64][12];
+
+    const int tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
+    const int W = a.src.w[0], H = a.src.h[0];
+    const int ctb = (ty0 >> a.ctb_log2) * a.ctb_width + (tx0 >> a.ctb_log2);
+    const VVCB200AlfCtb cp = a.ctbs[ctb];
+    const uint16_t *src = a.src.p[0];
+    const int sstride = a.src.stride[0];
+    uint16_t *dst = a.dst.p[0];
+    const int dstride = a.dst.stride[0];
+    const int t = threadIdx.x;
+
+    if (!cp.ctb_flag[0]) {                               // ALF off for this CTB: pass the SAO samples through
+        for (int i = t; i < kTile * kTile / 2; i += 256) {
+            const int y = ty0 + i / (kTile / 2), x = tx0 + (i % (kTile / 2)) * 2;
+            if (x < W && y < H)
+                *reinterpret_cast<uint32_t *>(dst + (size_t)y * dstride + x) =
+                    *reinterpret_cast<const uint32_t *>(src + (size_t)y * sstride + x);
+        }
+        return;
+    }
+    const CtbGeom g = ctb_geom(a, 0, tx0, ty0, cp.edges);
+    const int vb = (1 << a.ctb_log2) - 4;                // ALF_VB_POS_ABOVE_LUMA, CTB-relative (vvc_filter.c:1304)
+    const int ty_ctb = ty0 - g.y0;                       // tile origin inside the CTB
+    const int tw = min(kTile, g.x0 + g.w - tx0), th = min(kTile, g.y0 + g.h - ty0);
+
+    // ---- stage the tile + halo
+    for (int i = t; i < kPad * kPad; i += 256) {
+        const int r = i / kPad, col = i - r * kPad;
+        const int x = tx0 + col - kHalo, y = ty0 + r - kHalo;
+        // halo positions not clamped by an edge flag are real neighbours inside the picture (picture borders are
+        // always flagged by ctb_geom), so every read is in bounds
+        s_pix[r * kPadStr + col] = (uint16_t)padded_sample(src, sstride, g, x, y);
+    }
+    __syncthreads();
+
+    // ---- gradients per 2x2 cell (alf_classify first loop); cell (gy, gx) has p0 at tile (2gy-2, 2gx-2)
+    for (int i = t; i < kCells * kCells; i += 256) {
+        const int gy = i / kCells, gx = i - gy * kCells;
+        const int r0 = 2 * gy - 2 + kHalo, c0 = 2 * gx - 2 + kHalo;     // staged coordinates of p0
+        const int ygrad = ty_ctb + 2 * gy;                                // the reference's loop variable y
+        int ra = r0 - 1, rb = r0, rc = r0 + 1, rd = r0 + 2;               // s0..s3
+        if (ygrad == vb)
+            rd = rc;
+        else if (ygrad == vb + 2)
+            ra = rb;
+        const uint16_t *s0 = s_pix + ra * kPadStr, *s1 = s_pix + rb * kPadStr;
+        const uint16_t *s2 = s_pix + rc * kPadStr, *s3 = s_pix + rd * kPadStr;
+        const int val0 = s1[c0] << 1, val1 = s2[c0 + 1] << 1;
+        s_grad[i][0] = (uint16_t)(abs(val0 - s0[c0] - s2[c0]) + abs(val1 - s1[c0 + 1] - s3[c0 + 1]));
+        s_grad[i][1] = (uint16_t)(abs(val0 - s1[c0 - 1] - s1[c0 + 1]) + abs(val1 - s2[c0] - s2[c0 + 2]));
+        s_grad[i][2] = (uint16_t)(abs(val0 - s0[c0 - 1] - s2[c0 + 1]) + abs(val1 - s1[c0] - s3[c0 + 2]));
+        s_grad[i][3] = (uint16_t)(abs(val0 - s0[c0 + 1] - s2[c0 - 1]) + abs(val1 - s1[c0 + 2] - s3[c0]));
+    }
+    __syncthreads();
+
+    // ---- class / transpose per 4x4 block, then its 12 coefficients and clips (alf_get_idx, recon_coeff_and_clip)
+    if (t < 64) {
+        const int bx = t & 7, by = t >> 3;
+        const int yb = ty_ctb + by * 4;
+        int start = 0, end = 4, ac = 2;
+        if (yb + 4 == vb) { end = 3; ac = 3; }
+        else if (yb == vb) { start = 1; ac = 3; }
+        int sum[4] = { 0, 0, 0, 0 };
+        for (int i = start; i < end; i++)
+            for (int j = 0; j < 4; j++) {
+                const uint16_t *c = s_grad[(by * 2 + i) * kCells + bx * 2 + j];
+                sum[0] += c[0]; sum[1] += c[1]; sum[2] += c[2]; sum[3] += c[3];
+            }
+        const int dir_hv = sum[0] <= sum[1];
+        const int hv1 = max(sum[0], sum[1]), hv0 = min(sum[0], sum[1]);
+        const int dir_d = sum[2] <= sum[3];
+        const int d1 = max(sum[2], sum[3]), d0 = min(sum[2], sum[3]);
+        const int dir1 = (unsigned long long)d1 * hv0 <= (unsigned long long)hv1 * d0;
+        const int hvd1 = dir1 ? hv1 : d1, hvd0 = dir1 ? hv0 : d0;
+        const int act = min(max(((sum[0] + sum[1]) * ac) >> (a.bd - 1), 0), 15);
+        int cls = act == 0 ? 0 : act == 1 ? 1 : act < 7 ? 2 : act < 15 ? 3 : 4;
+        if (hvd1 * 2 > 9 * hvd0)
+            cls += ((dir1 << 1) + 2) * 5;
+        else if (hvd1 > 2 * hvd0)
+            cls += ((dir1 << 1) + 1) * 5;
+        const int tr = dir_d * 2 + dir_hv;
+
+        const int set = cp.filt_set_idx_y;
+        const int16_t *coeff;
+        const uint8_t *clip_idx = nullptr;
+        if (set < 16) {
+            coeff = VVC_ALF_FIX_FILT_COEFF + VVC_ALF_CLASS_TO_FILT_MAP[set * 25 + cls] * 12;
+        } else {
+            const int k = min(set - 16, 6);
+            coeff = a.params->luma_coeff[k][VVC_ALF_APS_CLASS_TO_FILT_MAP[cls]];
+            clip_idx = a.params->luma_clip_idx[k][cls];
+        }
+#pragma unroll
+        for (int j = 0; j < 12; j++) {
+            // transposition tables of alf_recon_coeff_and_clip (vvc_filter_template.c:386-391)
+            const int i1[12] = { 9, 4, 10, 8, 1, 5, 11, 7, 3, 0, 2, 6 };
+            const int i2[12] = { 0, 3, 2, 1, 8, 7, 6, 5, 4, 9, 10, 11 };
+            const int i3[12] = { 9, 8, 10, 4, 3, 7, 11, 5, 1, 0, 2, 6 };
+            const int idx = tr == 0 ? j : tr == 1 ? i1[j] : tr == 2 ? i2[j] : i3[j];
+            const int ci = clip_idx ? clip_idx[idx] : 0;
+            s_coef[t][j] = coeff[idx];
+            s_clip[t][j] = (int16_t)(1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7)));
+        }
+    }
+    __syncthreads();
+
+    // ---- filter: each thread owns 4 horizontally adjacent samples of one 4x4 block
+    {
+        const int row = t >> 3, xg = t & 7;
+        if (row < th && xg * 4 < tw) {
+            const int blk = (row >> 2) * 8 + xg;
+            int f[12], cl[12];
+#pragma unroll
+            for (int j = 0; j < 12; j++) {
+                f[j] = s_coef[blk][j];
+                cl[j] = s_clip[blk][j];
+            }
+            int o1, o2, o3;
+            bool near_vb;
+            vb_rows(ty_ctb + row, vb, 3, o1, o2, o3, near_vb);
+            const uint16_t *p0 = s_pix + (row + kHalo) * kPadStr + xg * 4 + kHalo;
+            const uint16_t *p1 = p0 + o1 * kPadStr, *p2 = p0 - o1 * kPadStr;
+            const uint16_t *p3 = p0 + o2 * kPadStr, *p4 = p0 - o2 * kPadStr;
+            const uint16_t *p5 = p0 + o3 * kPadStr, *p6 = p0 - o3 * kPadStr;
+            uint16_t out[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const int curr = p0[j];
+                int sum = 0;
+                sum += f[0]  * alf_clip2(curr, p5[j],     p6[j],     cl[0]);
+                sum += f[1]  * alf_clip2(curr, p3[j + 1], p4[j - 1], cl[1]);
+                sum += f[2]  * alf_clip2(curr, p3[j],     p4[j],     cl[2]);
+                sum += f[3]  * alf_clip2(curr, p3[j - 1], p4[j + 1], cl[3]);
+                sum += f[4]  * alf_clip2(curr, p1[j + 2], p2[j - 2], cl[4]);
+                sum += f[5]  * alf_clip2(curr, p1[j + 1], p2[j - 1], cl[5]);
+                sum += f[6]  * alf_clip2(curr, p1[j],     p2[j],     cl[6]);
+                sum += f[7]  * alf_clip2(curr, p1[j - 1], p2[j + 1], cl[7]);
+                sum += f[8]  * alf_clip2(curr, p1[j - 2], p2[j + 2], cl[8]);
+                sum += f[9]  * alf_clip2(curr, p0[j + 3], p0[j - 3], cl[9]);
+                sum += f[10] * alf_clip2(curr, p0[j + 2], p0[j - 2], cl[10]);
+                sum += f[11] * alf_clip2(curr, p0[j + 1], p0[j - 1], cl[11]);
+                sum = near_vb ? (sum + 512) >> 10 : (sum + 64) >> 7;
+                out[j] = (uint16_t)clip_pixel(sum + curr, a.bd);
+            }
+            uint16_t *d = dst + (size_t)(ty0 + row) * dstride + tx0 + xg * 4;
+            *reinterpret_cast<uint2 *>(d) = make_uint2(out[0] | ((uint32_t)out[1] << 16), out[2] | ((uint32_t)out[3] << 16));
+        }
+    }
+}
+
+// chroma ALF (5x5) + CC-ALF; grid.z selects Cb / Cr
+__global__ void __launch_bounds__(256) alf_chroma_kernel(const AlfArgs a)
+{
+    __shared__ uint16_t s_pix[(kTile + 4) * (kTile + 4)];
+    const int T = min(kTile, 1 << (a.ctb_log2 - 1));      // a tile never straddles a chroma CTB
+    const int S = T + 4;
+    const int c = 1 + blockIdx.z;
+    const int tx0 = blockIdx.x * T, ty0 = blockIdx.y * T;
+    const int W = a.src.w[c], H = a.src.h[c];
+    const int l2 = a.ctb_log2 - 1;
+    const int ctb = (ty0 >> l2) * a.ctb_width + (tx0 >> l2);
+    const VVCB200AlfCtb cp = a.ctbs[ctb];
+    const uint16_t *src = a.src.p[c];
+    const int sstride = a.src.stride[c];
+    uint16_t *dst = a.dst.p[c];
+    const int dstride = a.dst.stride[c];
+    const int t = threadIdx.x;
+    const bool do_alf = cp.ctb_flag[c];
+    const int cc = cp.cc_idc[c - 1];
+    const bool do_cc = cc && a.params->cc_enabled[c - 1];
+    const CtbGeom g = ctb_geom(a, c, tx0, ty0, cp.edges);
+    const int ty_ctb = ty0 - g.y0;
+
+    if (do_alf) {
+        for (int i = t; i < S * S; i += 256) {
+            const int r = i / S, col = i - r * S;
+            s_pix[i] = (uint16_t)padded_sample(src, sstride, g, tx0 + col - 2, ty0 + r - 2);
+        }
+        __syncthreads();
+    }
+    int f[6], cl[6];
+    if (do_alf) {
+        const int alt = min((int)cp.alt_idx[c - 1], 7);
+#pragma unroll
+        for (int j = 0; j < 6; j++) {
+            const int ci = a.params->chroma_clip_idx[alt][j];
+            f[j] = a.params->chroma_coeff[alt][j];
+            cl[j] = 1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7));
+        }
+    }
+    int fc[7];
+    CtbGeom gl = g;
+    if (do_cc) {
+#pragma unroll
+        for (int j = 0; j < 7; j++)
+            fc[j] = a.params->cc_coeff[c - 1][min(cc - 1, 3)][j];
+        gl = ctb_geom(a, 0, tx0 * 2, ty0 * 2, cp.edges);
+    }
+    const int vb = (1 << l2) - 2;                        // ALF_VB_POS_ABOVE_CHROMA
+    const int vb_luma = (1 << a.ctb_log2) - 4;
+    for (int i = t; i < T * T; i += 256) {
+        const int row = i / T, col = i - row * T;
+        const int x = tx0 + col, y = ty0 + row;
+        if (x >= W || y >= H)
+            continue;
+        int v = src[(size_t)y * sstride + x];
+        if (do_alf) {
+            int o1, o2, o3;
+            bool near_vb;
+            vb_rows(ty_ctb + row, vb, 1, o1, o2, o3, near_vb);
+            const uint16_t *p0 = s_pix + (row + 2) * S + col + 2;
+            const uint16_t *p1 = p0 + o1 * S, *p2 = p0 - o1 * S, *p3 = p0 + o2 * S, *p4 = p0 - o2 * S;
+            const int curr = p0[0];
+            int sum = 0;
+            sum += f[0] * alf_clip2(curr, p3[0],  p4[0],  cl[0]);
+            sum += f[1] * alf_clip2(curr, p1[1],  p2[-1], cl[1]);
+            sum += f[2] * alf_clip2(curr, p1[0],  p2[0],  cl[2]);
+            sum += f[3] * alf_clip2(curr, p1[-1], p2[1],  cl[3]);
+            sum += f[4] * alf_clip2(curr, p0[2],  p0[-2], cl[4]);
+            sum += f[5] * alf_clip2(curr, p0[1],  p0[-1], cl[5]);
+            sum = near_vb ? (sum + 512) >> 10 : (sum + 64) >> 7;
+            v = clip_pixel(sum + curr, a.bd);
+        }
+        if (do_cc) {
+            // alf_filter_cc (vvc_filter_template.c:223-263), 4:2:0: luma position (2x, 2y)
+            const uint16_t *lp = a.src.p[0];
+            const int ls = a.src.stride[0];
+            const int lx = x * 2, ly = y * 2;
+            const int pos = (ty_ctb + row) * 2;
+            int r0 = ly - 1, r2 = ly + 1, r3 = ly + 2;
+            if (pos == vb_luma - 2 || pos == vb_luma + 1)
+                r3 = r2;
+            else if (pos == vb_luma - 1 || pos == vb_luma)
+                r3 = r2 = r0 = ly;
+            const int cur = padded_sample(lp, ls, gl, lx, ly);
+            int sum = 0;
+            sum += fc[0] * (padded_sample(lp, ls, gl, lx, r0) - cur);
+            sum += fc[1] * (padded_sample(lp, ls, gl, lx - 1, ly) - cur);
+            sum += fc[2] * (padded_sample(lp, ls, gl, lx + 1, ly) - cur);
+            sum += fc[3] * (padded_sample(lp, ls, gl, lx - 1, r2) - cur);
+            sum += fc[4] * (padded_sample(lp, ls, gl, lx, r2) - cur);
+            sum += fc[5] * (padded_sample(lp, ls, gl, lx + 1, r2) - cur);
+            sum += fc[6] * (padded_sample(lp, ls, gl, lx, r3) - cur);
+            sum = clip3((sum + 64) >> 7, -(1 << (a.bd - 1)), (1 << (a.bd - 1)) - 1);
+            v = clip_pixel(v + sum, a.bd);
+        }
+        dst[(size_t)y * dstride + x] = (uint16_t)v;
+    }
+}
+
+}  // namespace vvcb200
+
+using namespace vvcb200;
+
+extern "C" int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes *src, const VVCB200AlfCtb *d_ctbs,
+                                   const VVCB200AlfParams *d_params, int ctb_log2_size, int bit_depth, void *stream)
+{
+    if (!dst || !src || !d_ctbs || !d_params || ctb_log2_size < 5 || ctb_log2_size > 7 ||
+        (bit_depth != 8 && bit_depth != 10 && bit_depth != 12)) {
+        set_error("vvcb200_alf_picture: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    AlfArgs a;
+    a.dst = make_view(dst);
+    a.src = make_view(src);
+    a.ctbs = d_ctbs;
+    a.params = d_params;
+    a.ctb_log2 = ctb_log2_size;
+    a.ctb_width = (src->width[0] + (1 << ctb_log2_size) - 1) >> ctb_log2_size;
+    a.bd = bit_depth;
+    if ((a.dst.stride[0] & 3) || ((uintptr_t)a.dst.p[0] & 7) || (a.src.stride[0] & 1) || ((uintptr_t)a.src.p[0] & 3)) {
+        set_error("vvcb200_alf_picture: luma planes must be 8-byte aligned with strides that are multiples of 8 bytes");
+        return VVCB200_ERR_ARG;
+    }
+    dim3 gl((src->width[0] + kTile - 1) / kTile, (src->height[0] + kTile - 1) / kTile, 1);
+    alf_luma_kernel<<<gl, 256, 0, (cudaStream_t)stream>>>(a);
+    VVC_LAUNCH_CHECK();
+    const int ct = kTile < (1 << (ctb_log2_size - 1)) ? kTile : (1 << (ctb_log2_size - 1));
+    dim3 gc((src->width[1] + ct - 1) / ct, (src->height[1] + ct - 1) / ct, 2);
+    alf_chroma_kernel<<<gc, 256, 0, (cudaStream_t)stream>>>(a);
+    VVC_LAUNCH_CHECK();
+    return 0;
+}

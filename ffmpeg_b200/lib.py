@@ -206,3 +206,18 @@ def deblock_tables(edge, qp, ctb_offsets, stride4):
 
 def deblock_picture(pic, tables, params, stream=None):
     check(load().vvcb200_deblock_picture(C.byref(pic), C.byref(tables), C.byref(params), _stream(stream)))
+
+
+def sao_picture(dst, src, ctbs, ctb_log2, bit_depth=10, stream=None):
+    """vvcb200_sao_picture: dst/src device_planes(); ctbs device tensor of VVCB200SaoCtb records."""
+    check(load().vvcb200_sao_picture(C.byref(dst), C.byref(src), _ptr(ctbs), int(ctb_log2), int(bit_depth), _stream(stream)))
+
+
+def alf_picture(dst, src, ctbs, params, ctb_log2, bit_depth=10, stream=None):
+    """vvcb200_alf_picture: ctbs / params are DEVICE tensors (VVCB200AlfCtb records, one VVCB200AlfParams)."""
+    check(load().vvcb200_alf_picture(C.byref(dst), C.byref(src), _ptr(ctbs), _ptr(params), int(ctb_log2), int(bit_depth),
+                                     _stream(stream)))
+
+
+def lmcs_picture(pic, lut, bit_depth=10, stream=None):
+    check(load().vvcb200_lmcs_picture(C.byref(pic), _ptr(lut), int(bit_depth), _stream(stream)))

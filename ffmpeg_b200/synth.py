@@ -328,3 +328,97 @@ def deblock_picture(seed, width, height, ctb_log2=7, ladf=None, bs_prob=(0.25, 0
             p.ladf_interval_lower_bound[i] = bounds[i]
     return dict(bs=bs, len_p=len_p, len_q=len_q, tb_w_c=tbc[0], tb_h_c=tbc[1], qp=qp, ctb_offsets=ctb_offsets,
                 params=p, stride4=s4, rows4=r4, dims=plane_dims(width, height), seed=seed)
+
+
+# ---- SAO / ALF / LMCS ----------------------------------------------------------------------------------------
+def slice_map(rng, ctb_w, ctb_h, n_slices):
+    """Per-CTB slice index: raster-scan slices (consecutive CTB runs), like VVC raster-scan slice mode."""
+    n = ctb_w * ctb_h
+    if n_slices <= 1:
+        return np.zeros(n, np.int16)
+    cuts = np.sort(rng.choice(np.arange(1, n), min(n_slices - 1, n - 1), replace=False))
+    return np.searchsorted(cuts, np.arange(n), side="right").astype(np.int16)
+
+
+def sao_no_filter_flags(slice_idx, ctb_w, ctb_h, lfase):
+    """Host-side derivation of VVCB200SaoCtb.no_filter (vert/horiz/diag_edge of ff_vvc_sao_filter,
+    reference vvc_filter.c:175-212) for one tile and pps_loop_filter_across_slices_enabled_flag = lfase."""
+    out = np.zeros(ctb_w * ctb_h, np.uint8)
+    if lfase:
+        return out
+    s = slice_idx.reshape(ctb_h, ctb_w)
+    for y in range(ctb_h):
+        for x in range(ctb_w):
+            L, T, R, B = x == 0, y == 0, x == ctb_w - 1, y == ctb_h - 1
+            f = 0
+            if not L and s[y, x] != s[y, x - 1]: f |= 1
+            if not R and s[y, x] != s[y, x + 1]: f |= 2
+            if not T and s[y, x] != s[y - 1, x]: f |= 4
+            if not B and s[y, x] != s[y + 1, x]: f |= 8
+            if not L and not T and s[y, x] != s[y - 1, x - 1]: f |= 16
+            if not T and not R and s[y, x] != s[y - 1, x + 1]: f |= 32
+            if not R and not B and s[y, x] != s[y + 1, x + 1]: f |= 64
+            if not L and not B and s[y, x] != s[y + 1, x - 1]: f |= 128
+            out[y * ctb_w + x] = f
+    return out
+
+
+def alf_edge_flags(slice_idx, ctb_w, ctb_h, lfase):
+    """Host-side derivation of VVCB200AlfCtb.edges beyond the picture borders (reference vvc_filter.c:1273-1280)."""
+    out = np.zeros(ctb_w * ctb_h, np.uint8)
+    if lfase:
+        return out
+    s = slice_idx.reshape(ctb_h, ctb_w)
+    for y in range(ctb_h):
+        for x in range(ctb_w):
+            f = 0
+            if x > 0 and s[y, x] != s[y, x - 1]: f |= 1
+            if y > 0 and s[y, x] != s[y - 1, x]: f |= 2
+            if x < ctb_w - 1 and s[y, x] != s[y, x + 1]: f |= 4
+            if y < ctb_h - 1 and s[y, x] != s[y + 1, x]: f |= 8
+            out[y * ctb_w + x] = f
+    return out
+
+
+def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on=0.85, cc_on=0.5, bd=10):
+    """Per-CTB SAO and ALF parameters + the slice's ALF APS content (random, int8-range coefficients like
+    tests/checkasm/vvc_alf.c:52-66; SAO offsets < 1 << (bd - 5) like tests/checkasm/vvc_sao.c:37)."""
+    rng = np.random.default_rng(seed)
+    ctb_w = (width + (1 << ctb_log2) - 1) >> ctb_log2
+    ctb_h = (height + (1 << ctb_log2) - 1) >> ctb_log2
+    n = ctb_w * ctb_h
+    slices = slice_map(rng, ctb_w, ctb_h, n_slices)
+    sao = np.zeros(n, abi.SAO_DTYPE)
+    sao["type_idx"] = rng.integers(0, 3, (n, 3))
+    sao["band_position"] = rng.integers(0, 32, (n, 3))
+    sao["eo_class"] = rng.integers(0, 4, (n, 3))
+    off = rng.integers(-(1 << (bd - 5)) + 1, 1 << (bd - 5), (n, 3, 5)).astype(np.int16)
+    off[:, :, 0] = 0
+    sao["offset_val"] = off
+    sao["no_filter"] = sao_no_filter_flags(slices, ctb_w, ctb_h, lfase)
+    alf = np.zeros(n, abi.ALF_CTB_DTYPE)
+    alf["ctb_flag"] = rng.random((n, 3)) < alf_on
+    alf["filt_set_idx_y"] = np.where(rng.random(n) < 0.4, rng.integers(0, 16, n), 16 + rng.integers(0, 6, n))
+    alf["alt_idx"] = rng.integers(0, 8, (n, 2))
+    alf["cc_idc"] = np.where(rng.random((n, 2)) < cc_on, rng.integers(1, 5, (n, 2)), 0)
+    alf["edges"] = alf_edge_flags(slices, ctb_w, ctb_h, lfase)
+    p = np.zeros(1, abi.ALF_PARAMS_DTYPE)
+    p["bit_depth"], p["ctb_log2_size"] = bd, ctb_log2
+    p["luma_coeff"] = rng.integers(-128, 128, (7, 25, 12))
+    p["luma_clip_idx"] = rng.integers(0, 4, (7, 25, 12))
+    p["chroma_coeff"] = rng.integers(-128, 128, (8, 6))
+    p["chroma_clip_idx"] = rng.integers(0, 4, (8, 6))
+    p["cc_coeff"] = rng.integers(-64, 64, (2, 4, 7))
+    p["cc_enabled"] = 1
+    return dict(sao=sao, alf=alf, alf_params=p, slice_idx=slices, lfase=lfase, ctb_log2=ctb_log2,
+                dims=plane_dims(width, height), seed=seed)
+
+
+def lmcs_luts(seed, bd=10):
+    """A monotone forward LUT and its (approximate) inverse, both 1 << bd entries of uint16."""
+    rng = np.random.default_rng(seed)
+    n = 1 << bd
+    steps = rng.integers(1, 4, n).astype(np.float64)
+    fwd = np.clip(np.rint(np.cumsum(steps) / steps.sum() * (n - 1)), 0, n - 1).astype(np.uint16)
+    inv = np.clip(np.searchsorted(fwd, np.arange(n)), 0, n - 1).astype(np.uint16)
+    return fwd, inv

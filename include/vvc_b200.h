@@ -230,6 +230,58 @@ VVCB200_API int vvcb200_deblock_picture(const VVCB200Planes *pic, const VVCB200D
                                         const VVCB200DeblockParams *params /* host */, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
+ * SAO and ALF (stages SAO / ALF, ff_vvc_sao_filter vvc_filter.c:154-298, ff_vvc_alf_filter 1254-1319;
+ * sao.band_filter / edge_filter / edge_restore vvcdsp.h:138-145, alf.classify / recon_coeff_and_clip /
+ * filter[2] / filter_cc vvcdsp.h:149-157).  Both are out-of-place picture passes here: the reference keeps
+ * pre-filter border copies per CTU (sao_pixel_buffer_*, alf_pixel_buffer_*, vvcdec.h:165-168) so that each
+ * CTU sees unfiltered neighbours — exactly what reading a separate source plane gives.
+ * ---------------------------------------------------------------------------------------------- */
+enum { VVCB200_SAO_OFF = 0, VVCB200_SAO_BAND = 1, VVCB200_SAO_EDGE = 2 };  /* enum SAOType, vvc_ctu.h:92-96 */
+
+typedef struct VVCB200SaoCtb {      /* SAOParams, vvc_ctu.h:440-451, plus the restore flags of vvc_filter.c:163-212 */
+    uint8_t type_idx[3];            /* VVCB200_SAO_*                                                              */
+    uint8_t band_position[3];
+    uint8_t eo_class[3];            /* 0 horizontal, 1 vertical, 2 135 deg, 3 45 deg (enum SAOEOClass)            */
+    uint8_t no_filter;              /* CTB sides / corners SAO must not read across because of a slice or tile
+                                       boundary: bit0 vert_edge[0] (left), bit1 vert_edge[1] (right),
+                                       bit2 horiz_edge[0] (top), bit3 horiz_edge[1] (bottom), bits4-7 diag_edge[0..3]
+                                       (up-left, up-right, low-right, low-left)                                   */
+    int16_t offset_val[3][5];       /* SaoOffsetVal, [c][0] == 0                                                  */
+} VVCB200SaoCtb;                    /* 40 bytes */
+
+/* SAO over the whole picture: dst = SAO(src); CTBs with type 0 are copied. d_ctbs: one record per CTB, raster. */
+VVCB200_API int vvcb200_sao_picture(const VVCB200Planes *dst, const VVCB200Planes *src, const VVCB200SaoCtb *d_ctbs,
+                                    int ctb_log2_size, int bit_depth, void *stream);
+
+typedef struct VVCB200AlfCtb {      /* ALFParams, vvc_ctu.h:453-460, plus the CTB edge flags of vvc_filter.c:1264-1280 */
+    uint8_t ctb_flag[3];            /* alf_ctb_flag[]                                                             */
+    uint8_t filt_set_idx_y;         /* AlfCtbFiltSetIdxY: < 16 fixed filter set, else 16 + index into luma sets   */
+    uint8_t alt_idx[2];             /* alf_ctb_filter_alt_idx[]                                                   */
+    uint8_t cc_idc[2];              /* alf_ctb_cc_cb_idc, alf_ctb_cc_cr_idc                                       */
+    uint8_t edges;                  /* bit0 LEFT, bit1 TOP, bit2 RIGHT, bit3 BOTTOM: picture / slice / tile limit */
+    uint8_t reserved[3];
+} VVCB200AlfCtb;                    /* 12 bytes */
+
+typedef struct VVCB200AlfParams {   /* per slice: the APS content the slice header selects (VVCALF, vvc_ps.h:163-173) */
+    int32_t  bit_depth;
+    int32_t  ctb_log2_size;
+    int16_t  luma_coeff[7][25][12];     /* [sh_alf_aps_id_luma index][filter][coeff]                              */
+    uint8_t  luma_clip_idx[7][25][12];
+    int16_t  chroma_coeff[8][6];        /* APS sh_alf_aps_id_chroma                                               */
+    uint8_t  chroma_clip_idx[8][6];
+    int16_t  cc_coeff[2][4][7];         /* [Cb, Cr][filter][coeff] of sh_alf_cc_cb/cr_aps_id                      */
+    int32_t  cc_enabled[2];             /* the CC APS exists (vvc_filter.c:1213)                                  */
+} VVCB200AlfParams;
+
+/* ALF (luma 7x7 + classification, chroma 5x5, CC-ALF) over the whole picture: dst = ALF(src); CTBs/components
+ * with ALF off are copied.  `d_params`/`d_ctbs` are DEVICE pointers (the struct is larger than kernel argument space). */
+VVCB200_API int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes *src, const VVCB200AlfCtb *d_ctbs,
+                                    const VVCB200AlfParams *d_params, int ctb_log2_size, int bit_depth, void *stream);
+
+/* lmcs.filter (vvcdsp.h:124) over whole luma plane in place: pix = lut[pix] (ff_vvc_lmcs_filter, vvc_filter.c:1322-1332). */
+VVCB200_API int vvcb200_lmcs_picture(const VVCB200Planes *pic, const uint16_t *d_lut, int bit_depth, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
  * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);
  * a context is not thread-safe, different contexts are independent (replicas only).
  * All work is enqueued on the context's own CUDA stream and is asynchronous with respect to the host:

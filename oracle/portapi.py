@@ -64,3 +64,22 @@ def deblock_picture(planes, edge, qp, ctb_offsets, stride4, params):
     pl = abi.host_planes(planes)
     t = product.deblock_tables(edge, qp, ctb_offsets, stride4)
     lib().port_deblock_picture(C.byref(pl), C.byref(t), C.byref(params))
+
+
+def sao_picture(dst, src, lf, bit_depth=10):
+    d, s = abi.host_planes(dst), abi.host_planes(src)
+    sao = np.ascontiguousarray(lf["sao"])
+    lib().port_sao_picture(C.byref(d), C.byref(s), C.c_void_p(sao.ctypes.data), int(lf["ctb_log2"]), bit_depth)
+
+
+def alf_picture(dst, src, lf):
+    d, s = abi.host_planes(dst), abi.host_planes(src)
+    alf = np.ascontiguousarray(lf["alf"])
+    p = np.ascontiguousarray(lf["alf_params"])
+    lib().port_alf_picture(C.byref(d), C.byref(s), C.c_void_p(alf.ctypes.data), C.c_void_p(p.ctypes.data))
+
+
+def lmcs_picture(planes, lut):
+    pl = abi.host_planes(planes)
+    lut = np.ascontiguousarray(lut, np.uint16)
+    lib().port_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data))

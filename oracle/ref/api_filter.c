@@ -153,3 +153,139 @@ VVCREF_EXPORT int vvcref_deblock_picture(const VVCRefPlanes *pl, const uint8_t *
     filter_env_free(e);
     return 0;
 }
+
+/* ---- SAO / ALF / LMCS through the reference's own stage functions ------------------------------------------ */
+
+/* slice_idx: per CTB (raster) slice number; lfase: pps_loop_filter_across_slices_enabled_flag */
+static void plant_slices(FilterEnv *e, const int16_t *slice_idx, int lfase)
+{
+    if (slice_idx)
+        memcpy(e->fc.tab.slice_idx, slice_idx, e->pps.ctb_count * sizeof(int16_t));
+    e->rpps.pps_loop_filter_across_slices_enabled_flag = lfase;
+    e->rpps.num_tiles_in_pic = 1;
+}
+
+/*
+ * Stage SAO over a whole picture, in place, through ff_vvc_sao_copy_ctb_to_hv + ff_vvc_sao_filter
+ * (vvc_filter.c:143-298): first every CTB saves its pre-SAO borders (what run_deblock_h does, vvc_thread.c:504-525),
+ * then every CTB is filtered (run_sao).  ctbs: VVCB200SaoCtb per CTB (no_filter is NOT read: the reference
+ * derives those flags itself from slice_idx / lfase).
+ */
+VVCREF_EXPORT int vvcref_sao_picture(const VVCRefPlanes *pl, const VVCB200SaoCtb *ctbs, const int16_t *slice_idx,
+                                     int lfase, int ctb_log2, int bit_depth)
+{
+    FilterEnv *e = filter_env_new(pl, bit_depth, ctb_log2);
+    SAOParams *sao = calloc(e->pps.ctb_count, sizeof(*sao));
+    plant_slices(e, slice_idx, lfase);
+    e->rsps.sps_sao_enabled_flag = 1;
+    for (unsigned i = 0; i < e->pps.ctb_count; i++)
+        for (int c = 0; c < 3; c++) {
+            sao[i].type_idx[c]      = ctbs[i].type_idx[c];
+            sao[i].band_position[c] = ctbs[i].band_position[c];
+            sao[i].eo_class[c]      = ctbs[i].eo_class[c];
+            for (int k = 0; k < 5; k++)
+                sao[i].offset_val[c][k] = ctbs[i].offset_val[c][k];
+        }
+    e->fc.tab.sao = sao;
+    for (int c = 0; c < 3; c++) {
+        const int w = pl->width[c], h = pl->height[c];
+        e->fc.tab.sao_pixel_buffer_h[c] = calloc((size_t)w * 2 * e->pps.ctb_height, 2);
+        e->fc.tab.sao_pixel_buffer_v[c] = calloc((size_t)h * 2 * e->pps.ctb_width, 2);
+    }
+    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < e->pps.ctb_width; rx++)
+            ff_vvc_sao_copy_ctb_to_hv(e->lc, rx, ry, ry == e->pps.ctb_height - 1);
+    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < e->pps.ctb_width; rx++) {
+            ff_vvc_decode_neighbour(e->lc, rx << ctb_log2, ry << ctb_log2, rx, ry, ry * e->pps.ctb_width + rx);
+            ff_vvc_sao_filter(e->lc, rx << ctb_log2, ry << ctb_log2);
+        }
+    for (int c = 0; c < 3; c++) {
+        free(e->fc.tab.sao_pixel_buffer_h[c]);
+        free(e->fc.tab.sao_pixel_buffer_v[c]);
+    }
+    free(sao);
+    filter_env_free(e);
+    return 0;
+}
+
+/*
+ * Stage ALF over a whole picture, in place, through ff_vvc_alf_copy_ctu_to_hv + ff_vvc_alf_filter
+ * (vvc_filter.c:1230-1319).  `p` is the slice's resolved APS content (include/vvc_b200.h); it is unfolded into
+ * the VVCALF APS list the reference indexes through the slice header (luma set k -> APS id k, chroma -> id 7 ...).
+ */
+VVCREF_EXPORT int vvcref_alf_picture(const VVCRefPlanes *pl, const VVCB200AlfCtb *ctbs, const VVCB200AlfParams *p,
+                                     const int16_t *slice_idx, int lfase)
+{
+    FilterEnv *e = filter_env_new(pl, p->bit_depth, p->ctb_log2_size);
+    ALFParams *alf = calloc(e->pps.ctb_count, sizeof(*alf));
+    VVCALF *aps = calloc(8, sizeof(*aps));
+    plant_slices(e, slice_idx, lfase);
+    e->rsps.sps_alf_enabled_flag = 1;
+    for (int k = 0; k < 7; k++) {
+        memcpy(aps[k].luma_coeff, p->luma_coeff[k], sizeof(aps[k].luma_coeff));
+        memcpy(aps[k].luma_clip_idx, p->luma_clip_idx[k], sizeof(aps[k].luma_clip_idx));
+        e->rsh.sh_alf_aps_id_luma[k] = k;
+    }
+    /* APS 7 carries the chroma and the cross-component filters */
+    memcpy(aps[7].chroma_coeff, p->chroma_coeff, sizeof(aps[7].chroma_coeff));
+    memcpy(aps[7].chroma_clip_idx, p->chroma_clip_idx, sizeof(aps[7].chroma_clip_idx));
+    for (int i = 0; i < 2; i++)
+        for (int f = 0; f < 4; f++)
+            for (int k = 0; k < 7; k++)
+                aps[7].cc_coeff[i][f][k] = p->cc_coeff[i][f][k];
+    e->rsh.sh_alf_aps_id_chroma = 7;
+    e->rsh.sh_alf_cc_cb_aps_id  = p->cc_enabled[0] ? 7 : 6;
+    e->rsh.sh_alf_cc_cr_aps_id  = p->cc_enabled[1] ? 7 : 6;
+    for (int k = 0; k < 8; k++)
+        e->fc.ps.alf_list[k] = &aps[k];
+    if (!p->cc_enabled[0] || !p->cc_enabled[1])
+        e->fc.ps.alf_list[6] = NULL;         /* "no such APS" (vvc_filter.c:1213); luma set 6 is then unusable */
+    for (unsigned i = 0; i < e->pps.ctb_count; i++) {
+        for (int c = 0; c < 3; c++)
+            alf[i].ctb_flag[c] = ctbs[i].ctb_flag[c];
+        alf[i].ctb_filt_set_idx_y = ctbs[i].filt_set_idx_y;
+        for (int c = 0; c < 2; c++) {
+            alf[i].alf_ctb_filter_alt_idx[c] = ctbs[i].alt_idx[c];
+            alf[i].ctb_cc_idc[c]             = ctbs[i].cc_idc[c];
+        }
+    }
+    e->fc.tab.alf = alf;
+    for (int c = 0; c < 3; c++) {
+        const int w = pl->width[c], h = pl->height[c], b = c ? ALF_BORDER_CHROMA : ALF_BORDER_LUMA;
+        for (int i = 0; i < 2; i++) {
+            e->fc.tab.alf_pixel_buffer_h[c][i] = calloc((size_t)w * b * e->pps.ctb_height, 2);
+            e->fc.tab.alf_pixel_buffer_v[c][i] = calloc((size_t)h * ALF_PADDING_SIZE * e->pps.ctb_width, 1);
+        }
+    }
+    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < e->pps.ctb_width; rx++)
+            ff_vvc_alf_copy_ctu_to_hv(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size);
+    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < e->pps.ctb_width; rx++) {
+            ff_vvc_decode_neighbour(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size, rx, ry, ry * e->pps.ctb_width + rx);
+            ff_vvc_alf_filter(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size);
+        }
+    for (int c = 0; c < 3; c++)
+        for (int i = 0; i < 2; i++) {
+            free(e->fc.tab.alf_pixel_buffer_h[c][i]);
+            free(e->fc.tab.alf_pixel_buffer_v[c][i]);
+        }
+    free(aps);
+    free(alf);
+    filter_env_free(e);
+    return 0;
+}
+
+/* Stage LMCS (inverse luma mapping of the whole picture) through ff_vvc_lmcs_filter (vvc_filter.c:1322-1332). */
+VVCREF_EXPORT int vvcref_lmcs_picture(const VVCRefPlanes *pl, const uint16_t *inv_lut, int ctb_log2, int bit_depth)
+{
+    FilterEnv *e = filter_env_new(pl, bit_depth, ctb_log2);
+    e->rsh.sh_lmcs_used_flag = 1;
+    memcpy(e->fc.ps.lmcs.inv_lut, inv_lut, sizeof(uint16_t) << bit_depth);
+    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < e->pps.ctb_width; rx++)
+            ff_vvc_lmcs_filter(e->lc, rx << ctb_log2, ry << ctb_log2);
+    filter_env_free(e);
+    return 0;
+}

@@ -94,3 +94,27 @@ def deblock_picture(planes, t):
                                  _ptr_grid(t["len_q"], (2,)), C.c_void_p(t["tb_w_c"].ctypes.data),
                                  C.c_void_p(t["tb_h_c"].ctypes.data), _ptr_grid(t["qp"], (3,)),
                                  C.c_void_p(t["ctb_offsets"].ctypes.data), C.byref(t["params"]))
+
+
+def sao_picture(planes, lf, bit_depth=10):
+    """Reference SAO stage in place; `lf` is synth.loopfilter_ctbs()."""
+    pl = abi.host_planes(planes)
+    sao = np.ascontiguousarray(lf["sao"])
+    sl = np.ascontiguousarray(lf["slice_idx"], np.int16)
+    lib().vvcref_sao_picture(C.byref(pl), C.c_void_p(sao.ctypes.data), C.c_void_p(sl.ctypes.data), int(lf["lfase"]),
+                             int(lf["ctb_log2"]), bit_depth)
+
+
+def alf_picture(planes, lf):
+    pl = abi.host_planes(planes)
+    alf = np.ascontiguousarray(lf["alf"])
+    sl = np.ascontiguousarray(lf["slice_idx"], np.int16)
+    p = np.ascontiguousarray(lf["alf_params"])
+    lib().vvcref_alf_picture(C.byref(pl), C.c_void_p(alf.ctypes.data), C.c_void_p(p.ctypes.data),
+                             C.c_void_p(sl.ctypes.data), int(lf["lfase"]))
+
+
+def lmcs_picture(planes, inv_lut, ctb_log2=7, bit_depth=10):
+    pl = abi.host_planes(planes)
+    lut = np.ascontiguousarray(inv_lut, np.uint16)
+    lib().vvcref_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data), ctb_log2, bit_depth)

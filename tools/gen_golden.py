@@ -72,10 +72,24 @@ def golden_deblock():
     return out
 
 
+def golden_loopfilter():
+    """SAO then ALF chained (the ALF input is the SAO output), both through the reference's stage functions."""
+    out = {}
+    for name, seed, w, h, ctb, ns, lfase in (("a", 41, 352, 288, 7, 1, 1), ("b", 42, 416, 240, 5, 5, 0)):
+        lf = synth.loopfilter_ctbs(seed, w, h, ctb_log2=ctb, n_slices=ns, lfase=lfase)
+        planes = synth.smooth_planes(seed, lf["dims"])
+        refapi.sao_picture(planes, lf)
+        out[name + "_sao_md5"] = np.array(util.plane_md5(planes))
+        refapi.alf_picture(planes, lf)
+        out[name + "_alf_md5"] = np.array(util.plane_md5(planes))
+        out[name + "_args"] = np.array([seed, w, h, ctb, ns, lfase], np.int32)
+    return out
+
+
 def main():
     check = "--check" in sys.argv
     os.makedirs(util.GOLDEN, exist_ok=True)
-    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter), ("deblock", golden_deblock)):
+    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter), ("deblock", golden_deblock), ("loopfilter", golden_loopfilter)):
         data = fn()
         path = os.path.join(util.GOLDEN, name + ".npz")
         if check:
