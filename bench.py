@@ -3,17 +3,22 @@
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p]
 
-One "step" = one synthetic picture through every stage the engine implements (see `config.stages`).
-`value`   : pictures/s, device-resident inputs, CUDA-event timed, max over ranks (N independent streams).
-`e2e`     : same picture through the Level-B C ABI with HOST (pinned) buffers, H2D + D2H inside the timed region.
-`roofline`: dominant kernel's algorithmic bytes / its live CUDA-event duration vs MEASURED_PEAKS.json.
-`cpu_baseline` / `--impl reference`: the reference's own C (oracle/_ref) — or the oracle port when that is
-not built — on the box's host cores, all threads, same picture.
+One "step" = one synthetic inter picture through every stage the engine implements (see `config.stages`):
+INTER (luma 8-tap / chroma 4-tap MC, uni/bi/weighted/BCW) -> residual (dequant + inverse DCT2/DST7/DCT8 + add)
+-> DEBLOCK_V -> DEBLOCK_H -> SAO -> ALF (+CC-ALF).
+`value`   : pictures/s with all descriptor batches and reference pictures resident in HBM, CUDA-event timed,
+            max over ranks (N independent streams, one per GPU).
+`e2e`     : the same picture through the Level-B C ABI with HOST (pinned) buffers: every step uploads all
+            descriptor batches and downloads the finished picture inside the timed region.
+`roofline`: the slowest kernel's algorithmic bytes / its live CUDA-event duration vs MEASURED_PEAKS.json.
+`cpu_baseline` / `--impl reference`: the reference's own C (oracle/_ref; the oracle port when that is absent)
+            on the box's host cores, all threads, same picture, same stage chain.
 Prints exactly one JSON line on rank 0.
 """
 import argparse
 import json
 import os
+import pickle
 import subprocess
 import sys
 import threading
@@ -28,6 +33,7 @@ if ROOT not in sys.path:
 METRIC = "4K 10-bit VVC recon+loop-filter frames/s per B200; % HBM roofline; 8-GPU agg"
 WORKLOADS = {"4k": (3840, 2160), "1080p": (1920, 1080)}
 L2_BYTES = 126 * 1024 * 1024
+STAGES = ["inter", "residual", "deblock", "sao", "alf"]
 
 
 def env_int(name, default):
@@ -49,39 +55,51 @@ def measured_peaks():
 # workload
 # ----------------------------------------------------------------------------------------------------------
 def make_picture(seed, width, height):
-    """Synthetic parsed picture (dense residual, config-1 level model).  Cached under /tmp for re-runs."""
+    """Synthetic parsed inter picture (SURVEY.md §8d config 2/3 shape).  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_%dx%d_%d.npz" % (width, height, seed)
+    cache = "/tmp/vvcb200_bench_v2_%dx%d_%d.pkl" % (width, height, seed)
     if os.path.exists(cache):
-        z = np.load(cache)
-        params = abi.ResidualParams.from_buffer_copy(z["params"].tobytes())
-        return dict(tbs=z["tbs"].view(abi.TB_DTYPE).reshape(-1), levels=z["levels"], params=params,
-                    intra_mode=z["intra_mode"], dims=[tuple(d) for d in z["dims"]], seed=seed)
-    pic = synth.residual_picture(seed, width, height, mean_log2=4.3)
+        try:
+            with open(cache, "rb") as f:
+                pic = pickle.load(f)
+            for k, cls in (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams)):
+                pic[k]["params"] = cls.from_buffer_copy(pic[k]["params"])
+            return pic
+        except Exception:
+            pass
+    pic = synth.full_picture(seed, width, height)
     try:
-        np.savez(cache, tbs=pic["tbs"].view(np.uint8), levels=pic["levels"], intra_mode=pic["intra_mode"],
-                 params=np.frombuffer(bytes(pic["params"]), np.uint8), dims=np.array(pic["dims"], np.int32))
+        dump = dict(pic)
+        for k in ("inter", "residual", "deblock"):
+            dump[k] = dict(pic[k], params=bytes(pic[k]["params"]))
+        with open(cache + ".tmp", "wb") as f:
+            pickle.dump(dump, f, protocol=4)
+        os.replace(cache + ".tmp", cache)
     except OSError:
         pass
     return pic
 
 
-def level_variant(levels, k):
-    """Picture k of the rotation: same partition, different levels (sign pattern) — defeats L2 reuse."""
-    if k == 0:
-        return levels
-    rng = np.random.default_rng(1000 + k)
-    sign = rng.integers(0, 2, levels.size).astype(np.int16) * 2 - 1
-    return (levels * sign).astype(np.int16)
-
-
-def residual_algorithmic_bytes(pic):
-    """SURVEY.md §8(d), stage-isolated residual: 2 B/sample int16 levels in + 2 B/sample written, plus the
-    destination sample read of the in-place add (2 B) — per coded sample."""
-    n = int(np.sum(1 << (pic["tbs"]["log2_w"].astype(np.int64) + pic["tbs"]["log2_h"])))
-    joint = pic["tbs"]["flags"] & 64
-    n_joint = int(np.sum((1 << (pic["tbs"]["log2_w"].astype(np.int64) + pic["tbs"]["log2_h"]))[joint != 0]))
-    return 2 * n + 2 * (n + n_joint), n
+def picture_stats(pic):
+    """Samples and algorithmic bytes (SURVEY.md §8d / DESIGN.md §5) of one picture, per stage and in total."""
+    S = sum(w * h for (w, h) in pic["dims"])
+    S_y, S_c = pic["dims"][0][0] * pic["dims"][0][1], pic["dims"][1][0] * pic["dims"][1][1]
+    tbs = pic["residual"]["tbs"]
+    area = (1 << (tbs["log2_w"].astype(np.int64) + tbs["log2_h"]))
+    coded = int(area.sum() + area[(tbs["flags"] & 64) != 0].sum())            # joint TBs rebuild a second plane
+    b = pic["inter"]["blocks"]
+    lists = np.where(b["pred_flag"] == 3, 2, 1).astype(np.int64)
+    ref_samples = int((b["w"].astype(np.int64) * b["h"] * lists).sum() * 3 // 2)   # luma + 2 x quarter-size chroma
+    stage = {
+        "inter": 2 * ref_samples + 2 * S,             # reference samples in, prediction out
+        "residual": 2 * int(area.sum()) + 4 * coded,  # int16 levels in, destination read + write
+        "deblock": 2 * (2 * S + 2 * S),               # two passes, each at most picture in + picture out
+        "sao": 2 * S + 2 * S,
+        "alf": (2 * S + 2 * S) + 2 * S_y,             # picture in + out, luma once more for CC-ALF
+    }
+    a_pic = 2 * int(area.sum()) + 2 * ref_samples + 2 * S   # §8d: levels in + reference reads + final picture out
+    return dict(S=S, coded_samples=coded, ref_samples=ref_samples, stage_bytes=stage, a_pic=a_pic, rho=coded / S,
+                r=ref_samples / S)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -130,53 +148,64 @@ class ClockSampler:
 
 
 # ----------------------------------------------------------------------------------------------------------
-# CPU arm: the reference's own C on host threads
+# CPU arm: the reference's own C on host threads, same stage chain
 # ----------------------------------------------------------------------------------------------------------
-def cpu_run(pic, planes, threads):
-    """One whole picture through the reference's residual path, TBs dealt round-robin to `threads` threads."""
+def cpu_picture(pic, threads):
+    """One whole picture through the reference's stage functions, every stage spread over `threads` host threads
+    (sub-blocks / TBs dealt round-robin; loop filters by CTB rows with a join per pass).  Returns seconds, kind."""
+    from ffmpeg_b200 import lib
     from oracle import portapi, refapi
+    it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+    planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
     use_ref = refapi.available()
-    kind = "reference" if use_ref else "port"
-    parts = []
-    for t in range(threads):
-        sub = dict(pic, tbs=np.ascontiguousarray(pic["tbs"][t::threads]),
-                   intra_mode=np.ascontiguousarray(pic["intra_mode"][t::threads]))
-        parts.append(sub)
 
-    def work(sub):
-        if use_ref:
-            refapi.residual_batch(planes, sub["levels"], sub["tbs"], sub["params"], sub["intra_mode"])
-        else:
-            portapi.residual_batch(planes, sub["levels"], sub["tbs"], sub["params"])
-    ths = [threading.Thread(target=work, args=(p,)) for p in parts]
+    def spread(fn, parts):
+        ths = [threading.Thread(target=fn, args=(p,)) for p in parts]
+        for th in ths:
+            th.start()
+        for th in ths:
+            th.join()
+
+    blocks = [np.ascontiguousarray(it["blocks"][t::threads]) for t in range(threads)]
+    tbs = [(np.ascontiguousarray(rs["tbs"][t::threads]), np.ascontiguousarray(rs["intra_mode"][t::threads]))
+           for t in range(threads)]
+    edge = None if use_ref else lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"],
+                                                       pic["ctb_log2"])
     t0 = time.perf_counter()
-    for th in ths:
-        th.start()
-    for th in ths:
-        th.join()
-    return time.perf_counter() - t0, kind
+    if use_ref:
+        spread(lambda b: refapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
+        spread(lambda tb: refapi.residual_batch(planes, rs["levels"], tb[0], rs["params"], tb[1]), tbs)
+        refapi.deblock_picture(planes, db, threads=threads)
+        refapi.sao_picture(planes, lf, threads=threads)
+        refapi.alf_picture(planes, lf, threads=threads)
+    else:
+        spread(lambda b: portapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
+        spread(lambda tb: portapi.residual_batch(planes, rs["levels"], tb[0], rs["params"]), tbs)
+        portapi.deblock_picture(planes, edge, db["qp"], db["ctb_offsets"], db["stride4"], db["params"])
+        tmp = [np.zeros_like(p) for p in planes]
+        portapi.sao_picture(tmp, planes, lf)
+        portapi.alf_picture(planes, tmp, lf)
+    return time.perf_counter() - t0, ("reference" if use_ref else "port")
 
 
-def cpu_baseline(pic, budget_s=12.0):
-    from tests import util
+def cpu_baseline(pic, budget_s=15.0, max_pics=30):
     threads = os.cpu_count() or 1
-    planes = util.noise_planes(1, pic["dims"])
-    cpu_run(pic, planes, threads)                      # warm-up (page-in, first-touch)
-    n, t = 0, 0.0
-    while t < budget_s and n < 50:
-        dt, kind = cpu_run(pic, planes, threads)
+    cpu_picture(pic, threads)                      # warm-up (page-in, first touch)
+    n, t, kind = 0, 0.0, "port"
+    while t < budget_s and n < max_pics:
+        dt, kind = cpu_picture(pic, threads)
         t += dt
         n += 1
     return {"value": n / t, "unit": "frames/s", "cores": threads, "kind": kind,
-            "sample": "%d whole pictures (%d TBs each) through the residual stage, TBs dealt round-robin to %d host threads"
-                      % (n, len(pic["tbs"]), threads)}
+            "sample": "%d whole pictures through INTER + residual + deblock + SAO + ALF; sub-blocks/TBs dealt "
+                      "round-robin and loop-filter CTB rows split over %d host threads (x86 asm not built: no nasm)" % (n, threads)}
 
 
 # ----------------------------------------------------------------------------------------------------------
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k", choices=sorted(WORKLOADS))
@@ -187,30 +216,32 @@ def main():
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     width, height = WORKLOADS[args.workload]
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    config = {"workload": "%s 4:2:0 10-bit synthetic parsed picture (%dx%d), CTU 128" % (args.workload, width, height),
-              "stages": ["dequant", "bdpcm", "lfnst", "inverse DCT2/DST7/DCT8", "add_residual", "joint CbCr"],
+    config = {"workload": "%s 4:2:0 10-bit synthetic inter picture (%dx%d), CTU 128, 2 reference pictures"
+                          % (args.workload, width, height),
+              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW)",
+                         "residual (dequant, inverse DCT2/DST7/DCT8, TS, joint CbCr, add)",
+                         "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
+              "not_in_step": "intra prediction, DMVR/BDOF/PROF/affine/GPM/CIIP (not built yet, see DESIGN.md)",
               "streams": "one independent picture stream per GPU (replicas, no collective)"}
 
     if args.impl == "reference":
         if rank != 0:
             return 0
         pic = make_picture(args.seed, width, height)
-        from tests import util
         threads = os.cpu_count() or 1
-        planes = util.noise_planes(1, pic["dims"])
         for _ in range(args.warmup):
-            cpu_run(pic, planes, threads)
+            cpu_picture(pic, threads)
         t, kind = 0.0, "port"
         for _ in range(args.steps):
-            dt, kind = cpu_run(pic, planes, threads)
+            dt, kind = cpu_picture(pic, threads)
             t += dt
         v = args.steps / t
-        config["cpu"] = "reference C (--disable-x86asm equivalent: no nasm on this image), %d host threads" % threads
+        config["cpu"] = "reference C built from its own sources (no x86 asm: no nasm on this image), %d host threads" % threads
         out = {"metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config, "impl": "reference",
                "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind,
-                                "sample": "each step = one whole picture's residual stage (%d TBs)" % len(pic["tbs"])},
+                                "sample": "each step = one whole picture through the full stage chain"},
                "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
         print(json.dumps(out))
@@ -218,8 +249,8 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from ffmpeg_b200 import abi, lib
-    from tests import util
+    from ffmpeg_b200 import lib
+    from tests import pipeline, util
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl ours needs a CUDA device: the engine has no CPU fallback")
     torch.cuda.set_device(local)
@@ -232,49 +263,86 @@ def main():
         torch.cuda.synchronize()
 
     pic = make_picture(args.seed + rank, width, height)
-    n_tb = len(pic["tbs"])
-    algo_bytes, n_samples = residual_algorithmic_bytes(pic)
-    frame_bytes = sum(w * h * 2 for (w, h) in pic["dims"])
-    per_pic_dev = pic["levels"].nbytes + pic["tbs"].nbytes + frame_bytes
-    rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_pic_dev)))     # rotation set > 2x L2
-    config["l2"] = "rotating %d distinct pictures (%.0f MB) > 126 MB L2 between timed iterations" % (rot, rot * per_pic_dev / 1e6)
-    config["transform_blocks"] = n_tb
+    st = picture_stats(pic)
+    it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+    frame_bytes = 2 * st["S"]
+    config.update({"transform_blocks": int(len(rs["tbs"])), "pred_blocks": int(len(it["blocks"])),
+                   "coded_fraction": round(st["rho"], 3), "ref_samples_per_sample": round(st["r"], 3)})
 
-    # ---- device-resident arm --------------------------------------------------------------------------
-    base = util.noise_planes(args.seed, pic["dims"])
-    tbs_d = torch.from_numpy(pic["tbs"].view(np.uint8).reshape(-1)).cuda()
-    pics_d = []
+    # ---- device-resident arm: `rot` complete copies of the picture's working set, visited round-robin -----------
+    edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+
+    def dev(a):
+        return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()
+
+    per_set = (len(it["refs"]) + 2) * frame_bytes + rs["levels"].nbytes + rs["tbs"].nbytes + it["blocks"].nbytes + \
+        edge.nbytes + db["qp"].nbytes
+    rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
+    config["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
+        rot, rot * per_set / 1e6)
+    sets = []
     for k in range(rot):
-        planes = util.to_device_planes(base, torch)
-        pics_d.append((lib.device_planes(planes), planes, torch.from_numpy(level_variant(pic["levels"], k)).cuda()))
+        s = {}
+        s["refs"] = [util.to_device_planes(r, torch) for r in it["refs"]]
+        s["cur"] = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
+        s["tmp"] = [torch.zeros_like(t) for t in s["cur"]]
+        s["cur_p"], s["tmp_p"] = lib.device_planes(s["cur"]), lib.device_planes(s["tmp"])
+        s["refs_p"] = [lib.device_planes(r) for r in s["refs"]]
+        s["blocks"], s["levels"], s["tbs"] = dev(it["blocks"]), dev(rs["levels"]), dev(rs["tbs"])
+        s["edge"] = torch.from_numpy(edge).cuda()
+        s["qp"] = torch.from_numpy(db["qp"]).cuda()
+        s["off"] = torch.from_numpy(db["ctb_offsets"]).cuda()
+        s["db"] = lib.deblock_tables(s["edge"], s["qp"], s["off"], db["stride4"])
+        s["sao"], s["alf"], s["alfp"] = dev(lf["sao"]), dev(lf["alf"]), dev(lf["alf_params"])
+        sets.append(s)
+    n_blocks, n_tbs = len(it["blocks"]), len(rs["tbs"])
 
-    def step(i):
-        pl, _, lv = pics_d[i % rot]
-        lib.residual_batch(pl, lv, tbs_d, n_tb, pic["params"])
+    def step(i, ev=None):
+        s = sets[i % rot]
+        marks = []
+        lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], n_blocks, it["params"])
+        marks.append("inter")
+        if ev is not None:
+            ev[1].record()
+        lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], n_tbs, rs["params"])
+        if ev is not None:
+            ev[2].record()
+        lib.deblock_picture(s["cur_p"], s["db"], db["params"])
+        if ev is not None:
+            ev[3].record()
+        lib.sao_picture(s["tmp_p"], s["cur_p"], s["sao"], pic["ctb_log2"])
+        if ev is not None:
+            ev[4].record()
+        lib.alf_picture(s["cur_p"], s["tmp_p"], s["alf"], s["alfp"], pic["ctb_log2"])
+        if ev is not None:
+            ev[5].record()
 
     for i in range(warmup):
         step(i)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    # stage boundaries are marked with events on the launching stream (torch's current stream)
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
+    ev_end = torch.cuda.Event(enable_timing=True)
     l0 = lib.launch_count()
     t_host0 = time.perf_counter()
-    ev0.record()
     for i in range(args.steps):
-        step(warmup + i)
-    ev1.record()
+        evs[i][0].record()
+        step(warmup + i, evs[i])
+    ev_end.record()
     barrier()
     t_host1 = time.perf_counter()
     launches = lib.launch_count() - l0
-    ms = ev0.elapsed_time(ev1)
-    # keep the GPU under the same load a little longer if the timed region was too short for nvidia-smi
+    ms = evs[0][0].elapsed_time(ev_end)
+    stage_ms = {name: float(np.mean([evs[i][k].elapsed_time(evs[i][k + 1]) for i in range(args.steps)]))
+                for k, name in enumerate(STAGES)}
     if sampler is not None and t_host1 - t_host0 < 0.5:
-        t_end = time.perf_counter() + 0.6
-        i = 0
+        # too short for nvidia-smi's sampling period: keep the same load running a little longer (not timed)
+        t_end, i = time.perf_counter() + 0.6, 0
         while time.perf_counter() < t_end:
             step(i)
             i += 1
-            if i % 50 == 0:
+            if i % 20 == 0:
                 torch.cuda.synchronize()
         torch.cuda.synchronize()
         t_host1 = time.perf_counter()
@@ -284,41 +352,32 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = world * args.steps / (ms / 1e3)
+    del sets
+    torch.cuda.empty_cache()
 
-    # ---- end-to-end arm: Level-B C ABI, pinned host buffers, H2D + D2H inside the timed region ----------
-    ctx = lib.Context(local, width, height)
-    h_src, h_out = ctx.pinned_planes(), ctx.pinned_planes()
-    for s, b in zip(h_src, base):
-        s[...] = b
-    h_levels = ctx.pinned(pic["levels"].shape, np.int16)
-    h_levels[...] = pic["levels"]
-    h_tbs = ctx.pinned(pic["tbs"].shape, abi.TB_DTYPE)
-    h_tbs[...] = pic["tbs"]
-
-    def e2e_step():
-        ctx.begin()
-        ctx.upload(h_src)
-        ctx.residual(h_levels, h_tbs, pic["params"])
-        ctx.download(h_out)
-
-    e2e_steps = max(3, min(args.steps, 50))
+    # ---- end-to-end arm: Level-B C ABI, pinned host buffers, H2D + D2H inside the timed region ------------------
+    ctx = lib.Context(local, width, height, dpb_size=len(it["refs"]) + 1)
+    ep = pipeline.EnginePicture(ctx, pic)
+    ep.upload_refs()                       # reference pictures are earlier outputs of the same decoder: resident
+    e2e_steps = max(3, min(args.steps, 40))
     for _ in range(3):
-        e2e_step()
+        ep.run()
     ctx.sync()
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        e2e_step()
+        ep.run()
     ctx.sync()
     e2e_s = time.perf_counter() - t0
     if world > 1:
         t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
-    e2e = {"value": world * e2e_steps / e2e_s, "unit": "frames/s",
-           "h2d_bytes_per_step": int(frame_bytes + pic["levels"].nbytes + pic["tbs"].nbytes),
-           "d2h_bytes_per_step": int(frame_bytes), "steps": e2e_steps,
-           "api": "vvcb200_pic_upload + vvcb200_pic_residual + vvcb200_pic_download (include/vvc_b200.h), pinned host buffers"}
+    e2e = {"value": world * e2e_steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": ep.h2d_bytes(),
+           "d2h_bytes_per_step": ep.d2h_bytes(), "steps": e2e_steps,
+           "api": "vvcb200_pic_begin/inter/residual/deblock/sao_alf/download (include/vvc_b200.h), pinned host buffers; "
+                  "reference pictures stay in the context's DPB"}
+    e2e_ok = util.plane_md5(ep.out)
     ctx.close()
 
     if rank != 0:
@@ -327,21 +386,29 @@ def main():
         return 0
 
     peak, peak_kind = measured_peaks()
-    kernel_ms = ms_rank0 = ev0.elapsed_time(ev1) / args.steps        # one launch per step: the step IS the kernel
-    achieved = algo_bytes / (kernel_ms * 1e-3) / 1e9
+    top = max(stage_ms, key=stage_ms.get)
+    launches_per_stage = {"inter": 1, "residual": 1, "deblock": 2, "sao": 1, "alf": 2}
+    kernel_ms = stage_ms[top] / launches_per_stage[top]
+    algo = st["stage_bytes"][top] / launches_per_stage[top]
+    achieved = algo / (kernel_ms * 1e-3) / 1e9
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "roofline_traffic.json")) as f:
-            traffic = json.load(f).get(args.workload)
+            traffic = json.load(f).get(args.workload, {}).get(top)
     except Exception:
         pass
-    roofline = {"bound": "hbm", "kernel": "residual_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
+    step_ms = ms / args.steps
+    roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
                 "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
-                "algorithmic_bytes_per_launch": algo_bytes, "kernel_ms": kernel_ms}
+                "algorithmic_bytes_per_launch": algo, "kernel_ms": kernel_ms,
+                "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
+                "stage_frac_of_peak": {k: round(st["stage_bytes"][k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) for k in STAGES},
+                "picture": {"algorithmic_bytes": st["a_pic"], "achieved": st["a_pic"] / (step_ms * 1e-3) / 1e9,
+                            "frac": st["a_pic"] / (step_ms * 1e-3) / 1e9 / peak}}
     out = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
-           "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
            "dtype": "int32", "data": "synthetic", "config": config, "clocks": clocks, "e2e": e2e,
-           "gpu_launches": int(launches), "roofline": roofline}
+           "gpu_launches": int(launches), "roofline": roofline, "e2e_plane_md5": e2e_ok}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"] = cpu_baseline(pic)
     print(json.dumps(out))

@@ -1,11 +1,15 @@
-// engine.cu — Level B of the C ABI: the per-GPU picture engine (context, device planes, staging, stage order).
+// engine.cu — Level B of the C ABI: the per-GPU picture engine (context, DPB planes, staging, stage order).
 // Host-side C++ only; the kernels live in the stage files and are reached through their Level-A entries,
-// so both levels run exactly the same device code.
+// so both levels run exactly the same device code.  Everything is enqueued on the context's stream; the
+// caller's host buffers are read by asynchronous copies (pinned memory gives real overlap).
 #include <new>
 #include <string.h>
+#include <vector>
 #include "common.cuh"
 
 using namespace vvcb200;
+
+namespace {
 
 struct DevBuffer {
     void *p = nullptr;
@@ -32,16 +36,10 @@ struct DevBuffer {
     }
 };
 
-struct VVCB200Ctx {
-    int device = 0;
-    int width = 0, height = 0, bit_depth = 10, hshift = 1, vshift = 1;
-    cudaStream_t stream = nullptr;
-    VVCB200Planes cur = {};        // picture under reconstruction
-    void *cur_base = nullptr;
-    DevBuffer levels, tbs;
+struct DevPicture {
+    VVCB200Planes planes = {};
+    void *base = nullptr;
 };
-
-namespace {
 
 struct DeviceGuard {
     int prev = -1;
@@ -60,23 +58,53 @@ struct DeviceGuard {
     }
 };
 
-int alloc_planes(VVCB200Ctx *c, VVCB200Planes *pl, void **base)
+}  // namespace
+
+struct VVCB200Ctx {
+    int device = 0;
+    int width = 0, height = 0, bit_depth = 10, hshift = 1, vshift = 1;
+    cudaStream_t stream = nullptr;
+    std::vector<DevPicture> dpb;   // reference pictures + the picture under reconstruction
+    DevPicture scratch;            // SAO output / ALF input
+    int cur = 0;
+    // per-stage device copies of the host descriptor batches
+    DevBuffer levels, tbs, blocks, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
+};
+
+namespace {
+
+int alloc_picture(VVCB200Ctx *c, DevPicture *pic)
 {
     size_t off[3], total = 0;
     for (int i = 0; i < 3; i++) {
         const int w = i ? c->width >> c->hshift : c->width;
         const int h = i ? c->height >> c->vshift : c->height;
         const int pitch = (w * 2 + 255) & ~255;          // 256-byte rows: every row start is 128-bit/TMA aligned
-        pl->width[i] = w;
-        pl->height[i] = h;
-        pl->stride[i] = pitch;
+        pic->planes.width[i] = w;
+        pic->planes.height[i] = h;
+        pic->planes.stride[i] = pitch;
         off[i] = total;
         total += (size_t)pitch * h;
     }
-    VVC_CUDA(cudaMalloc(base, total));
-    VVC_CUDA(cudaMemsetAsync(*base, 0, total, c->stream));
+    VVC_CUDA(cudaMalloc(&pic->base, total));
+    VVC_CUDA(cudaMemsetAsync(pic->base, 0, total, c->stream));
     for (int i = 0; i < 3; i++)
-        pl->d_plane[i] = (uint8_t *)*base + off[i];
+        pic->planes.d_plane[i] = (uint8_t *)pic->base + off[i];
+    return 0;
+}
+
+DevPicture *slot_of(VVCB200Ctx *c, int slot)
+{
+    if (slot < 0)
+        return &c->dpb[c->cur];
+    return slot < (int)c->dpb.size() ? &c->dpb[slot] : nullptr;
+}
+
+int upload(VVCB200Ctx *c, DevBuffer &b, const void *host, size_t bytes)
+{
+    if (int r = b.reserve(bytes))
+        return r;
+    VVC_CUDA(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, c->stream));
     return 0;
 }
 
@@ -84,7 +112,8 @@ int alloc_planes(VVCB200Ctx *c, VVCB200Planes *pl, void **base)
 
 extern "C" {
 
-int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int chroma_format_idc, int bit_depth)
+int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int chroma_format_idc, int bit_depth,
+                       int dpb_size)
 {
     if (!out || width <= 0 || height <= 0 || width > 16384 || height > 16384 || (width & 7) || (height & 7)) {
         set_error("vvcb200_ctx_create: bad dimensions %dx%d (multiples of 8 up to 16384)", width, height);
@@ -93,6 +122,10 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     if (bit_depth != 8 && bit_depth != 10 && bit_depth != 12) {
         set_error("vvcb200_ctx_create: unsupported bit depth %d", bit_depth);
         return VVCB200_ERR_ARG;
+    }
+    if (dpb_size < 1 || dpb_size > 17) {
+        set_error("vvcb200_ctx_create: dpb_size %d out of range (1..17)", dpb_size);
+        return VVCB200_ERR_TOO_BIG;
     }
     if (chroma_format_idc != 1) {
         set_error("vvcb200_ctx_create: chroma_format_idc %d not built (4:2:0 only)", chroma_format_idc);
@@ -121,7 +154,11 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
         delete c;
         return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__);
     }
-    if (int r = alloc_planes(c, &c->cur, &c->cur_base)) {
+    c->dpb.resize(dpb_size);
+    int r = alloc_picture(c, &c->scratch);
+    for (int i = 0; !r && i < dpb_size; i++)
+        r = alloc_picture(c, &c->dpb[i]);
+    if (r) {
         vvcb200_ctx_destroy(c);
         return r;
     }
@@ -136,10 +173,15 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     DeviceGuard g(c->device);
     if (c->stream)
         cudaStreamSynchronize(c->stream);
-    c->levels.release();
-    c->tbs.release();
-    if (c->cur_base)
-        cudaFree(c->cur_base);
+    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
+                          &c->alf_params };
+    for (DevBuffer *b : bufs)
+        b->release();
+    for (DevPicture &p : c->dpb)
+        if (p.base)
+            cudaFree(p.base);
+    if (c->scratch.base)
+        cudaFree(c->scratch.base);
     if (c->stream)
         cudaStreamDestroy(c->stream);
     delete c;
@@ -155,11 +197,14 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
 
 void *vvcb200_ctx_stream(VVCB200Ctx *c) { return c ? (void *)c->stream : nullptr; }
 
-int vvcb200_ctx_current(VVCB200Ctx *c, VVCB200Planes *out)
+int vvcb200_ctx_planes(VVCB200Ctx *c, int slot, VVCB200Planes *out)
 {
-    if (!c || !out)
+    DevPicture *p = c ? slot_of(c, slot) : nullptr;
+    if (!p || !out) {
+        set_error("vvcb200_ctx_planes: bad context or slot %d", slot);
         return VVCB200_ERR_ARG;
-    *out = c->cur;
+    }
+    *out = p->planes;
     return 0;
 }
 
@@ -179,33 +224,74 @@ void vvcb200_host_free(void *p)
         cudaFreeHost(p);
 }
 
-int vvcb200_pic_begin(VVCB200Ctx *c)
+int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
 {
-    if (!c)
+    if (!c || slot < 0 || slot >= (int)c->dpb.size()) {
+        set_error("vvcb200_pic_begin: bad context or slot %d", slot);
         return VVCB200_ERR_ARG;
+    }
+    c->cur = slot;
     return 0;
 }
 
-int vvcb200_pic_upload(VVCB200Ctx *c, const uint16_t *const planes[3], const int32_t strides[3])
+int vvcb200_pic_upload(VVCB200Ctx *c, int slot, const uint16_t *const planes[3], const int32_t strides[3])
 {
-    if (!c || !planes || !strides)
+    DevPicture *p = c ? slot_of(c, slot) : nullptr;
+    if (!p || !planes || !strides) {
+        set_error("vvcb200_pic_upload: bad argument");
         return VVCB200_ERR_ARG;
+    }
     DeviceGuard g(c->device);
     for (int i = 0; i < 3; i++)
-        VVC_CUDA(cudaMemcpy2DAsync(c->cur.d_plane[i], c->cur.stride[i], planes[i], strides[i],
-                                   (size_t)c->cur.width[i] * 2, c->cur.height[i], cudaMemcpyHostToDevice, c->stream));
+        VVC_CUDA(cudaMemcpy2DAsync(p->planes.d_plane[i], p->planes.stride[i], planes[i], strides[i],
+                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyHostToDevice, c->stream));
     return 0;
 }
 
-int vvcb200_pic_download(VVCB200Ctx *c, uint16_t *const planes[3], const int32_t strides[3])
+int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], const int32_t strides[3])
 {
-    if (!c || !planes || !strides)
+    DevPicture *p = c ? slot_of(c, slot) : nullptr;
+    if (!p || !planes || !strides) {
+        set_error("vvcb200_pic_download: bad argument");
         return VVCB200_ERR_ARG;
+    }
     DeviceGuard g(c->device);
     for (int i = 0; i < 3; i++)
-        VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], c->cur.d_plane[i], c->cur.stride[i],
-                                   (size_t)c->cur.width[i] * 2, c->cur.height[i], cudaMemcpyDeviceToHost, c->stream));
+        VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
+                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->stream));
     return 0;
+}
+
+int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *params,
+                      const uint16_t *lmcs_fwd_lut)
+{
+    if (!c || !params || n < 0 || (n && !blocks)) {
+        set_error("vvcb200_pic_inter: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    if (n == 0)
+        return 0;
+    DeviceGuard g(c->device);
+    if (int r = upload(c, c->blocks, blocks, (size_t)n * sizeof(*blocks)))
+        return r;
+    const uint16_t *d_lut = nullptr;
+    if (lmcs_fwd_lut) {
+        if (int r = upload(c, c->lut_fwd, lmcs_fwd_lut, sizeof(uint16_t) << c->bit_depth))
+            return r;
+        d_lut = (const uint16_t *)c->lut_fwd.p;
+    }
+    VVCB200Planes refs[16];
+    const int n_refs = (int)c->dpb.size() < 16 ? (int)c->dpb.size() : 16;
+    for (int i = 0; i < n_refs; i++)
+        refs[i] = c->dpb[i].planes;
+    for (int l = 0; l < 2; l++)
+        for (int i = 0; i < 16; i++)
+            if (params->ref_slot[l][i] >= n_refs) {
+                set_error("vvcb200_pic_inter: ref_slot[%d][%d] = %d is not a DPB slot of this context", l, i, params->ref_slot[l][i]);
+                return VVCB200_ERR_ARG;
+            }
+    return vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)c->blocks.p, n, params,
+                               d_lut, nullptr, c->stream);
 }
 
 int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
@@ -222,14 +308,103 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
     if (n == 0)
         return 0;
     DeviceGuard g(c->device);
-    if (int r = c->levels.reserve(n_levels * sizeof(int16_t)))
+    if (int r = upload(c, c->levels, levels, n_levels * sizeof(int16_t)))
         return r;
-    if (int r = c->tbs.reserve((size_t)n * sizeof(VVCB200TransformBlock)))
+    if (int r = upload(c, c->tbs, tbs, (size_t)n * sizeof(VVCB200TransformBlock)))
         return r;
-    VVC_CUDA(cudaMemcpyAsync(c->levels.p, levels, n_levels * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream));
-    VVC_CUDA(cudaMemcpyAsync(c->tbs.p, tbs, (size_t)n * sizeof(VVCB200TransformBlock), cudaMemcpyHostToDevice, c->stream));
-    return vvcb200_residual_batch(&c->cur, nullptr, (const int16_t *)c->levels.p,
+    return vvcb200_residual_batch(&c->dpb[c->cur].planes, nullptr, (const int16_t *)c->levels.p,
                                   (const VVCB200TransformBlock *)c->tbs.p, n, params, c->stream);
+}
+
+int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
+{
+    if (!c || !inv_lut) {
+        set_error("vvcb200_pic_lmcs: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    DeviceGuard g(c->device);
+    if (int r = upload(c, c->lut_inv, inv_lut, sizeof(uint16_t) << c->bit_depth))
+        return r;
+    return vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)c->lut_inv.p, c->bit_depth, c->stream);
+}
+
+int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB200DeblockParams *params)
+{
+    if (!c || !t || !params || t->stride4 <= 0 || !t->d_ctb_offsets) {
+        set_error("vvcb200_pic_deblock: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    DeviceGuard g(c->device);
+    const size_t rows4 = (size_t)(c->height + 3) >> 2;
+    const size_t units = (size_t)t->stride4 * rows4;
+    const int shift = params->ctb_log2_size;
+    const size_t n_ctb = (size_t)((c->width + (1 << shift) - 1) >> shift) * ((c->height + (1 << shift) - 1) >> shift);
+    // one device arena: 6 edge tables, 3 qp tables, the per-CTB offsets
+    if (int r = c->db_tables.reserve(units * 9 + n_ctb * 6 + 64))
+        return r;
+    uint8_t *d = (uint8_t *)c->db_tables.p;
+    VVCB200DeblockTables dt = *t;
+    for (int dir = 0; dir < 2; dir++)
+        for (int k = 0; k < 3; k++) {
+            if (!t->d_edge[dir][k]) {
+                set_error("vvcb200_pic_deblock: missing edge table");
+                return VVCB200_ERR_ARG;
+            }
+            VVC_CUDA(cudaMemcpyAsync(d, t->d_edge[dir][k], units, cudaMemcpyHostToDevice, c->stream));
+            dt.d_edge[dir][k] = d;
+            d += units;
+        }
+    for (int k = 0; k < 3; k++) {
+        if (!t->d_qp[k]) {
+            set_error("vvcb200_pic_deblock: missing qp table");
+            return VVCB200_ERR_ARG;
+        }
+        VVC_CUDA(cudaMemcpyAsync(d, t->d_qp[k], units, cudaMemcpyHostToDevice, c->stream));
+        dt.d_qp[k] = (const int8_t *)d;
+        d += units;
+    }
+    VVC_CUDA(cudaMemcpyAsync(d, t->d_ctb_offsets, n_ctb * 6, cudaMemcpyHostToDevice, c->stream));
+    dt.d_ctb_offsets = (const int8_t *)d;
+    return vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, c->stream);
+}
+
+int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200AlfCtb *alf,
+                        const VVCB200AlfParams *alf_params, int ctb_log2_size)
+{
+    if (!c || ctb_log2_size < 5 || ctb_log2_size > 7 || (alf && !alf_params)) {
+        set_error("vvcb200_pic_sao_alf: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    DeviceGuard g(c->device);
+    const int sh = ctb_log2_size;
+    const size_t n_ctb = (size_t)((c->width + (1 << sh) - 1) >> sh) * ((c->height + (1 << sh) - 1) >> sh);
+    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &c->scratch.planes;
+    if (sao) {
+        if (int r = upload(c, c->sao, sao, n_ctb * sizeof(*sao)))
+            return r;
+        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)c->sao.p, ctb_log2_size, c->bit_depth, c->stream))
+            return r;
+    }
+    if (alf) {
+        if (int r = upload(c, c->alf, alf, n_ctb * sizeof(*alf)))
+            return r;
+        if (int r = upload(c, c->alf_params, alf_params, sizeof(*alf_params)))
+            return r;
+        if (!sao) {
+            // ALF reads `tmp`: without SAO the source is the current picture itself
+            const size_t bytes = (size_t)cur->stride[0] * cur->height[0] + 2 * (size_t)cur->stride[1] * cur->height[1];
+            VVC_CUDA(cudaMemcpyAsync(c->scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, c->stream));
+        }
+        return vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)c->alf.p, (const VVCB200AlfParams *)c->alf_params.p,
+                                   ctb_log2_size, c->bit_depth, c->stream);
+    }
+    if (sao) {
+        // SAO only: its output becomes the picture (swap the buffers instead of copying back)
+        DevPicture t = c->dpb[c->cur];
+        c->dpb[c->cur] = c->scratch;
+        c->scratch = t;
+    }
+    return 0;
 }
 
 }  // extern "C"

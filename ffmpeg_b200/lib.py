@@ -93,12 +93,13 @@ class Context:
     """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use
     pinned() to allocate page-locked ones (needed for asynchronous copies)."""
 
-    def __init__(self, device, width, height, bit_depth=10, chroma_format_idc=1):
+    def __init__(self, device, width, height, bit_depth=10, chroma_format_idc=1, dpb_size=3):
         self._h = C.c_void_p()
         check(load().vvcb200_ctx_create(C.byref(self._h), int(device), int(width), int(height),
-                                        int(chroma_format_idc), int(bit_depth)))
+                                        int(chroma_format_idc), int(bit_depth), int(dpb_size)))
         self.width, self.height, self.bit_depth = width, height, bit_depth
         self._pinned = []
+        self._keep = []
 
     def close(self):
         if self._h:
@@ -124,7 +125,12 @@ class Context:
             raise VVCB200Error(l.vvcb200_last_error().decode())
         self._pinned.append(p)
         buf = (C.c_uint8 * max(n, 1)).from_address(p)
-        return np.frombuffer(buf, dtype=dtype, count=int(np.prod(shape))).reshape(shape)
+        return np.frombuffer(buf, dtype=np.uint8, count=n).view(dtype).reshape(shape)
+
+    def pinned_copy(self, a):
+        out = self.pinned(a.shape, a.dtype)
+        out[...] = a
+        return out
 
     def pinned_planes(self):
         dims = [(self.width, self.height), (self.width // 2, self.height // 2), (self.width // 2, self.height // 2)]
@@ -135,16 +141,17 @@ class Context:
         l.vvcb200_ctx_stream.restype = C.c_void_p
         return l.vvcb200_ctx_stream(self._h)
 
-    def current(self):
+    def planes(self, slot=-1):
         p = abi.Planes()
-        check(load().vvcb200_ctx_current(self._h, C.byref(p)))
+        check(load().vvcb200_ctx_planes(self._h, int(slot), C.byref(p)))
         return p
 
     def sync(self):
         check(load().vvcb200_ctx_sync(self._h))
+        self._keep = []
 
-    def begin(self):
-        check(load().vvcb200_pic_begin(self._h))
+    def begin(self, slot=0):
+        check(load().vvcb200_pic_begin(self._h, int(slot)))
 
     @staticmethod
     def _plane_args(planes):
@@ -152,18 +159,33 @@ class Context:
         strides = (C.c_int32 * 3)(*[p.strides[0] for p in planes])
         return ptrs, strides
 
-    def upload(self, planes):
+    def upload(self, planes, slot=-1):
         ptrs, strides = self._plane_args(planes)
-        check(load().vvcb200_pic_upload(self._h, ptrs, strides))
+        check(load().vvcb200_pic_upload(self._h, int(slot), ptrs, strides))
 
-    def download(self, planes):
+    def download(self, planes, slot=-1):
         ptrs, strides = self._plane_args(planes)
-        check(load().vvcb200_pic_download(self._h, ptrs, strides))
+        check(load().vvcb200_pic_download(self._h, int(slot), ptrs, strides))
+
+    def inter(self, blocks, params, lmcs_fwd_lut=None):
+        assert blocks.dtype == abi.PB_DTYPE
+        check(load().vvcb200_pic_inter(self._h, _ptr(blocks), len(blocks), C.byref(params), _ptr(lmcs_fwd_lut)))
 
     def residual(self, levels, tbs, params):
         assert levels.dtype == np.int16 and tbs.dtype == abi.TB_DTYPE
         check(load().vvcb200_pic_residual(self._h, _ptr(levels), C.c_size_t(levels.size), _ptr(tbs), len(tbs),
                                           C.byref(params)))
+
+    def lmcs(self, inv_lut):
+        check(load().vvcb200_pic_lmcs(self._h, _ptr(inv_lut)))
+
+    def deblock(self, edge, qp, ctb_offsets, stride4, params):
+        t = deblock_tables(edge, qp, ctb_offsets, stride4)
+        self._keep.append(t)
+        check(load().vvcb200_pic_deblock(self._h, C.byref(t), C.byref(params)))
+
+    def sao_alf(self, sao, alf, alf_params, ctb_log2):
+        check(load().vvcb200_pic_sao_alf(self._h, _ptr(sao), _ptr(alf), _ptr(alf_params), int(ctb_log2)))
 
 
 def inter_batch(dst, refs, blocks, n, params, lmcs_fwd_lut=None, tmp14=None, stream=None):

@@ -422,3 +422,27 @@ def lmcs_luts(seed, bd=10):
     fwd = np.clip(np.rint(np.cumsum(steps) / steps.sum() * (n - 1)), 0, n - 1).astype(np.uint16)
     inv = np.clip(np.searchsorted(fwd, np.arange(n)), 0, n - 1).astype(np.uint16)
     return fwd, inv
+
+
+# ---- a whole picture --------------------------------------------------------------------------------------------
+def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, lmcs=False, n_slices=1, lfase=1,
+                 residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3):
+    """All descriptor batches of one inter picture (BASELINE config 2/3 shape): prediction sub-blocks, residual TBs,
+    deblocking tables, SAO/ALF CTB parameters.  Stage inputs are generated independently of each other (the
+    arithmetic of every stage takes its tables as given); see DESIGN.md for what a real parser adds."""
+    inter = inter_picture(seed, width, height, n_refs=n_refs)
+    res = residual_picture(seed + 1, width, height, coded_fraction=coded_fraction, tools=residual_tools,
+                           mean_log2=mean_log2)
+    # every residual TB of an inter picture belongs to an inter CU
+    res["tbs"]["flags"] |= abi.TB_INTER
+    res["tbs"]["flags"] &= ~np.uint16(abi.TB_BDPCM | abi.TB_BDPCM_VERT)
+    nolf = res["tbs"]["lfnst"] != 0
+    res["tbs"]["lfnst"] = 0          # LFNST is intra-only; its TBs stay as plain DCT2 blocks
+    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
+    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
+    out = dict(inter=inter, residual=res, deblock=db, lf=lf, dims=inter["dims"], ctb_log2=ctb_log2, seed=seed,
+               width=width, height=height, lmcs=None)
+    if lmcs:
+        out["lmcs"] = lmcs_luts(seed + 4)
+        inter["blocks"]["flags"] |= abi.PB_LMCS
+    return out

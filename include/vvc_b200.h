@@ -293,29 +293,45 @@ VVCB200_API int vvcb200_lmcs_picture(const VVCB200Planes *pic, const uint16_t *d
  * ---------------------------------------------------------------------------------------------- */
 typedef struct VVCB200Ctx VVCB200Ctx;
 
-/* chroma_format_idc: 1 (4:2:0) is what the engine builds today; others return VVCB200_ERR_UNSUP. */
+/* chroma_format_idc: 1 (4:2:0) is what the engine builds today; others return VVCB200_ERR_UNSUP.
+ * dpb_size: number of picture buffers the context owns (1..17: VVC_MAX_DPB_SIZE + 1, vvcdec.h:82-83). */
 VVCB200_API int  vvcb200_ctx_create(VVCB200Ctx **ctx, int device, int width, int height,
-                                    int chroma_format_idc, int bit_depth);
+                                    int chroma_format_idc, int bit_depth, int dpb_size);
 VVCB200_API void vvcb200_ctx_destroy(VVCB200Ctx *ctx);
 VVCB200_API int  vvcb200_ctx_sync(VVCB200Ctx *ctx);
 /* cudaStream_t of the context (for callers that enqueue their own work or record events on it). */
 VVCB200_API void *vvcb200_ctx_stream(VVCB200Ctx *ctx);
-/* Device planes of the picture under reconstruction (fc->frame, vvcdec.h:96). */
-VVCB200_API int  vvcb200_ctx_current(VVCB200Ctx *ctx, VVCB200Planes *out);
+/* Device planes of DPB slot `slot` (slot < 0: the picture under reconstruction, fc->frame, vvcdec.h:96). */
+VVCB200_API int  vvcb200_ctx_planes(VVCB200Ctx *ctx, int slot, VVCB200Planes *out);
 
 /* Pinned host memory for descriptor batches and frames. */
 VVCB200_API void *vvcb200_host_alloc(size_t bytes);
 VVCB200_API void  vvcb200_host_free(void *p);
 
-/* Start a picture: forgets the previous picture's batches (the planes keep their content). */
-VVCB200_API int vvcb200_pic_begin(VVCB200Ctx *ctx);
-/* Copy host samples into the current picture (prediction produced elsewhere, or test input). strides in bytes. */
-VVCB200_API int vvcb200_pic_upload(VVCB200Ctx *ctx, const uint16_t *const planes[3], const int32_t strides[3]);
-/* Residual stage of the picture: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
+/* Start a picture that will be reconstructed into DPB slot `slot` (its old content is dead from here on). */
+VVCB200_API int vvcb200_pic_begin(VVCB200Ctx *ctx, int slot);
+/* Copy host samples into DPB slot `slot` (slot < 0: current picture): a reference picture decoded elsewhere,
+ * prediction samples produced elsewhere, or test input.  strides in bytes. */
+VVCB200_API int vvcb200_pic_upload(VVCB200Ctx *ctx, int slot, const uint16_t *const planes[3], const int32_t strides[3]);
+/* Stage INTER: upload the sub-block batch and predict into the current picture.  params->ref_slot[][] are DPB slots
+ * of this context.  lmcs_fwd_lut: host, 1 << bit_depth entries, or NULL. */
+VVCB200_API int vvcb200_pic_inter(VVCB200Ctx *ctx, const VVCB200PredBlock *blocks, int n,
+                                  const VVCB200InterParams *params, const uint16_t *lmcs_fwd_lut);
+/* Stage RECON, residual part: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
 VVCB200_API int vvcb200_pic_residual(VVCB200Ctx *ctx, const int16_t *levels, size_t n_levels,
                                      const VVCB200TransformBlock *tbs, int n, const VVCB200ResidualParams *params);
-/* Copy the current picture back to host memory (the AVFrame the decoder outputs). strides in bytes. */
-VVCB200_API int vvcb200_pic_download(VVCB200Ctx *ctx, uint16_t *const planes[3], const int32_t strides[3]);
+/* Stage LMCS: inverse luma mapping of the whole picture (host LUT of 1 << bit_depth entries). */
+VVCB200_API int vvcb200_pic_lmcs(VVCB200Ctx *ctx, const uint16_t *inv_lut);
+/* Stages DEBLOCK_V + DEBLOCK_H.  All table pointers are HOST memory (stride4 x rows4 bytes each; ctb_offsets 6 bytes
+ * per CTB); the struct is the one vvcb200_deblock_picture takes, filled with host pointers. */
+VVCB200_API int vvcb200_pic_deblock(VVCB200Ctx *ctx, const VVCB200DeblockTables *host_tables,
+                                    const VVCB200DeblockParams *params);
+/* Stages SAO + ALF.  sao / alf: one record per CTB (raster), host memory; either may be NULL (stage skipped).
+ * alf_params: host.  The filtered picture ends up in the current DPB slot. */
+VVCB200_API int vvcb200_pic_sao_alf(VVCB200Ctx *ctx, const VVCB200SaoCtb *sao, const VVCB200AlfCtb *alf,
+                                    const VVCB200AlfParams *alf_params, int ctb_log2_size);
+/* Copy DPB slot `slot` (slot < 0: current picture) back to host memory (the AVFrame the decoder outputs). */
+VVCB200_API int vvcb200_pic_download(VVCB200Ctx *ctx, int slot, uint16_t *const planes[3], const int32_t strides[3]);
 
 #ifdef __cplusplus
 }

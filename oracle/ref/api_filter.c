@@ -91,11 +91,15 @@ static void filter_env_free(FilterEnv *e)
  * visits no TB and leaves the planted tables as they are.
  *   bs[dir][c], len_p[dir], len_q[dir], tb_w_c, tb_h_c, qp[c]: stride4 x rows4 bytes, luma 4x4 units
  *   ctb_offsets: per CTB beta_offset[3], tc_offset[3]
+ *   pass_mask bit0 = vertical-edge pass, bit1 = horizontal-edge pass; CTB rows [ry0, ry1) (ry1 < 0: all) — lets the
+ *   timed CPU baseline run CTB rows on several threads with a join between the passes, like the reference's
+ *   own scheduler does (vvc_thread.c:156-184).
  */
 VVCREF_EXPORT int vvcref_deblock_picture(const VVCRefPlanes *pl, const uint8_t *const bs[2][3],
                                          const uint8_t *const len_p[2], const uint8_t *const len_q[2],
                                          const uint8_t *tb_w_c, const uint8_t *tb_h_c, const int8_t *const qp[3],
-                                         const int8_t *ctb_offsets, const VVCB200DeblockParams *p)
+                                         const int8_t *ctb_offsets, const VVCB200DeblockParams *p,
+                                         int pass_mask, int ry0, int ry1)
 {
     FilterEnv *e = filter_env_new(pl, p->bit_depth, p->ctb_log2_size);
     const size_t units = (size_t)e->pps.min_tu_width * e->pps.min_tu_height;
@@ -136,8 +140,10 @@ VVCREF_EXPORT int vvcref_deblock_picture(const VVCRefPlanes *pl, const uint8_t *
     for (int i = 0; i < 5; i++)
         e->sps.ladf_interval_lower_bound[i] = p->ladf_interval_lower_bound[i];
 
+    if (ry1 < 0 || ry1 > e->pps.ctb_height)
+        ry1 = e->pps.ctb_height;
     for (int pass = 0; pass < 2; pass++)
-        for (int ry = 0; ry < e->pps.ctb_height; ry++)
+        for (int ry = ry0; (pass_mask & (1 << pass)) && ry < ry1; ry++)
             for (int rx = 0; rx < e->pps.ctb_width; rx++) {
                 const int x0 = rx << p->ctb_log2_size, y0 = ry << p->ctb_log2_size;
                 ff_vvc_decode_neighbour(e->lc, x0, y0, rx, ry, ry * e->pps.ctb_width + rx);
@@ -171,8 +177,20 @@ static void plant_slices(FilterEnv *e, const int16_t *slice_idx, int lfase)
  * then every CTB is filtered (run_sao).  ctbs: VVCB200SaoCtb per CTB (no_filter is NOT read: the reference
  * derives those flags itself from slice_idx / lfase).
  */
+VVCREF_EXPORT size_t vvcref_sao_scratch_bytes(const VVCRefPlanes *pl, int ctb_log2)
+{
+    const int cw = (pl->width[0] + (1 << ctb_log2) - 1) >> ctb_log2, ch = (pl->height[0] + (1 << ctb_log2) - 1) >> ctb_log2;
+    size_t n = 0;
+    for (int c = 0; c < 3; c++)
+        n += ((size_t)pl->width[c] * 2 * ch + (size_t)pl->height[c] * 2 * cw) * 2;
+    return n;
+}
+
+/* scratch: vvcref_sao_scratch_bytes() bytes shared by all calls of one picture; phase_mask bit0 = save borders,
+ * bit1 = filter; CTB rows [ry0, ry1) (ry1 < 0: all). */
 VVCREF_EXPORT int vvcref_sao_picture(const VVCRefPlanes *pl, const VVCB200SaoCtb *ctbs, const int16_t *slice_idx,
-                                     int lfase, int ctb_log2, int bit_depth)
+                                     int lfase, int ctb_log2, int bit_depth, uint8_t *scratch, int phase_mask,
+                                     int ry0, int ry1)
 {
     FilterEnv *e = filter_env_new(pl, bit_depth, ctb_log2);
     SAOParams *sao = calloc(e->pps.ctb_count, sizeof(*sao));
@@ -189,21 +207,22 @@ VVCREF_EXPORT int vvcref_sao_picture(const VVCRefPlanes *pl, const VVCB200SaoCtb
     e->fc.tab.sao = sao;
     for (int c = 0; c < 3; c++) {
         const int w = pl->width[c], h = pl->height[c];
-        e->fc.tab.sao_pixel_buffer_h[c] = calloc((size_t)w * 2 * e->pps.ctb_height, 2);
-        e->fc.tab.sao_pixel_buffer_v[c] = calloc((size_t)h * 2 * e->pps.ctb_width, 2);
+        e->fc.tab.sao_pixel_buffer_h[c] = scratch;
+        scratch += (size_t)w * 2 * e->pps.ctb_height * 2;
+        e->fc.tab.sao_pixel_buffer_v[c] = scratch;
+        scratch += (size_t)h * 2 * e->pps.ctb_width * 2;
     }
-    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+    if (ry1 < 0 || ry1 > e->pps.ctb_height)
+        ry1 = e->pps.ctb_height;
+    /* saving the borders of row ry also saves the bottom of row ry - 1 (vvc_filter.c:143-152) */
+    for (int ry = ry0; (phase_mask & 1) && ry < ry1; ry++)
         for (int rx = 0; rx < e->pps.ctb_width; rx++)
             ff_vvc_sao_copy_ctb_to_hv(e->lc, rx, ry, ry == e->pps.ctb_height - 1);
-    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+    for (int ry = ry0; (phase_mask & 2) && ry < ry1; ry++)
         for (int rx = 0; rx < e->pps.ctb_width; rx++) {
             ff_vvc_decode_neighbour(e->lc, rx << ctb_log2, ry << ctb_log2, rx, ry, ry * e->pps.ctb_width + rx);
             ff_vvc_sao_filter(e->lc, rx << ctb_log2, ry << ctb_log2);
         }
-    for (int c = 0; c < 3; c++) {
-        free(e->fc.tab.sao_pixel_buffer_h[c]);
-        free(e->fc.tab.sao_pixel_buffer_v[c]);
-    }
     free(sao);
     filter_env_free(e);
     return 0;
@@ -214,8 +233,18 @@ VVCREF_EXPORT int vvcref_sao_picture(const VVCRefPlanes *pl, const VVCB200SaoCtb
  * (vvc_filter.c:1230-1319).  `p` is the slice's resolved APS content (include/vvc_b200.h); it is unfolded into
  * the VVCALF APS list the reference indexes through the slice header (luma set k -> APS id k, chroma -> id 7 ...).
  */
+VVCREF_EXPORT size_t vvcref_alf_scratch_bytes(const VVCRefPlanes *pl, int ctb_log2)
+{
+    const int cw = (pl->width[0] + (1 << ctb_log2) - 1) >> ctb_log2, ch = (pl->height[0] + (1 << ctb_log2) - 1) >> ctb_log2;
+    size_t n = 0;
+    for (int c = 0; c < 3; c++)
+        n += 2 * ((size_t)pl->width[c] * (c ? ALF_BORDER_CHROMA : ALF_BORDER_LUMA) * ch * 2 + (size_t)pl->height[c] * ALF_PADDING_SIZE * cw);
+    return n;
+}
+
 VVCREF_EXPORT int vvcref_alf_picture(const VVCRefPlanes *pl, const VVCB200AlfCtb *ctbs, const VVCB200AlfParams *p,
-                                     const int16_t *slice_idx, int lfase)
+                                     const int16_t *slice_idx, int lfase, uint8_t *scratch, int phase_mask,
+                                     int ry0, int ry1)
 {
     FilterEnv *e = filter_env_new(pl, p->bit_depth, p->ctb_log2_size);
     ALFParams *alf = calloc(e->pps.ctb_count, sizeof(*alf));
@@ -254,22 +283,21 @@ VVCREF_EXPORT int vvcref_alf_picture(const VVCRefPlanes *pl, const VVCB200AlfCtb
     for (int c = 0; c < 3; c++) {
         const int w = pl->width[c], h = pl->height[c], b = c ? ALF_BORDER_CHROMA : ALF_BORDER_LUMA;
         for (int i = 0; i < 2; i++) {
-            e->fc.tab.alf_pixel_buffer_h[c][i] = calloc((size_t)w * b * e->pps.ctb_height, 2);
-            e->fc.tab.alf_pixel_buffer_v[c][i] = calloc((size_t)h * ALF_PADDING_SIZE * e->pps.ctb_width, 1);
+            e->fc.tab.alf_pixel_buffer_h[c][i] = scratch;
+            scratch += (size_t)w * b * e->pps.ctb_height * 2;
+            e->fc.tab.alf_pixel_buffer_v[c][i] = scratch;
+            scratch += (size_t)h * ALF_PADDING_SIZE * e->pps.ctb_width;
         }
     }
-    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+    if (ry1 < 0 || ry1 > e->pps.ctb_height)
+        ry1 = e->pps.ctb_height;
+    for (int ry = ry0; (phase_mask & 1) && ry < ry1; ry++)
         for (int rx = 0; rx < e->pps.ctb_width; rx++)
             ff_vvc_alf_copy_ctu_to_hv(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size);
-    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+    for (int ry = ry0; (phase_mask & 2) && ry < ry1; ry++)
         for (int rx = 0; rx < e->pps.ctb_width; rx++) {
             ff_vvc_decode_neighbour(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size, rx, ry, ry * e->pps.ctb_width + rx);
             ff_vvc_alf_filter(e->lc, rx << p->ctb_log2_size, ry << p->ctb_log2_size);
-        }
-    for (int c = 0; c < 3; c++)
-        for (int i = 0; i < 2; i++) {
-            free(e->fc.tab.alf_pixel_buffer_h[c][i]);
-            free(e->fc.tab.alf_pixel_buffer_v[c][i]);
         }
     free(aps);
     free(alf);
@@ -278,12 +306,15 @@ VVCREF_EXPORT int vvcref_alf_picture(const VVCRefPlanes *pl, const VVCB200AlfCtb
 }
 
 /* Stage LMCS (inverse luma mapping of the whole picture) through ff_vvc_lmcs_filter (vvc_filter.c:1322-1332). */
-VVCREF_EXPORT int vvcref_lmcs_picture(const VVCRefPlanes *pl, const uint16_t *inv_lut, int ctb_log2, int bit_depth)
+VVCREF_EXPORT int vvcref_lmcs_picture(const VVCRefPlanes *pl, const uint16_t *inv_lut, int ctb_log2, int bit_depth,
+                                      int ry0, int ry1)
 {
     FilterEnv *e = filter_env_new(pl, bit_depth, ctb_log2);
     e->rsh.sh_lmcs_used_flag = 1;
     memcpy(e->fc.ps.lmcs.inv_lut, inv_lut, sizeof(uint16_t) << bit_depth);
-    for (int ry = 0; ry < e->pps.ctb_height; ry++)
+    if (ry1 < 0 || ry1 > e->pps.ctb_height)
+        ry1 = e->pps.ctb_height;
+    for (int ry = ry0; ry < ry1; ry++)
         for (int rx = 0; rx < e->pps.ctb_width; rx++)
             ff_vvc_lmcs_filter(e->lc, rx << ctb_log2, ry << ctb_log2);
     filter_env_free(e);

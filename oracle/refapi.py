@@ -85,36 +85,78 @@ def _ptr_grid(tabs, shape):
     return (inner * shape[0])(*[inner(*[tabs[i, j].ctypes.data for j in range(shape[1])]) for i in range(shape[0])])
 
 
-def deblock_picture(planes, t):
-    """Reference ff_vvc_deblock_vertical/horizontal over the picture; `t` is synth.deblock_picture()."""
+def _row_chunks(n_rows, threads):
+    threads = max(1, min(threads, n_rows))
+    edges = [round(i * n_rows / threads) for i in range(threads + 1)]
+    return [(edges[i], edges[i + 1]) for i in range(threads) if edges[i + 1] > edges[i]]
+
+
+def _parallel(fn, chunks):
+    """Run fn(ry0, ry1) for every CTB-row chunk on its own thread (ctypes drops the GIL) and join."""
+    import threading
+    if len(chunks) == 1:
+        fn(*chunks[0])
+        return
+    ths = [threading.Thread(target=fn, args=c) for c in chunks]
+    for t in ths:
+        t.start()
+    for t in ths:
+        t.join()
+
+
+def _ctb_rows(planes, ctb_log2):
+    return (planes[0].shape[0] + (1 << ctb_log2) - 1) >> ctb_log2
+
+
+def deblock_picture(planes, t, threads=1):
+    """Reference ff_vvc_deblock_vertical/horizontal over the picture; `t` is synth.deblock_picture().
+    threads > 1: CTB rows in parallel, with a join between the vertical-edge and the horizontal-edge pass."""
     pl = abi.host_planes(planes)
     for k in ("bs", "len_p", "len_q", "tb_w_c", "tb_h_c", "qp", "ctb_offsets"):
         assert t[k].flags.c_contiguous
-    lib().vvcref_deblock_picture(C.byref(pl), _ptr_grid(t["bs"], (2, 3)), _ptr_grid(t["len_p"], (2,)),
-                                 _ptr_grid(t["len_q"], (2,)), C.c_void_p(t["tb_w_c"].ctypes.data),
-                                 C.c_void_p(t["tb_h_c"].ctypes.data), _ptr_grid(t["qp"], (3,)),
-                                 C.c_void_p(t["ctb_offsets"].ctypes.data), C.byref(t["params"]))
+    args = (C.byref(pl), _ptr_grid(t["bs"], (2, 3)), _ptr_grid(t["len_p"], (2,)),
+            _ptr_grid(t["len_q"], (2,)), C.c_void_p(t["tb_w_c"].ctypes.data),
+            C.c_void_p(t["tb_h_c"].ctypes.data), _ptr_grid(t["qp"], (3,)),
+            C.c_void_p(t["ctb_offsets"].ctypes.data), C.byref(t["params"]))
+    chunks = _row_chunks(_ctb_rows(planes, t["params"].ctb_log2_size), threads)
+    for mask in (1, 2):
+        _parallel(lambda a, b: lib().vvcref_deblock_picture(*args, mask, a, b), chunks)
 
 
-def sao_picture(planes, lf, bit_depth=10):
-    """Reference SAO stage in place; `lf` is synth.loopfilter_ctbs()."""
+def sao_picture(planes, lf, bit_depth=10, threads=1):
+    """Reference SAO stage in place; `lf` is synth.loopfilter_ctbs().  Phase 1 saves every CTB's pre-SAO borders,
+    phase 2 filters; each phase may run CTB rows on several threads."""
     pl = abi.host_planes(planes)
     sao = np.ascontiguousarray(lf["sao"])
     sl = np.ascontiguousarray(lf["slice_idx"], np.int16)
-    lib().vvcref_sao_picture(C.byref(pl), C.c_void_p(sao.ctypes.data), C.c_void_p(sl.ctypes.data), int(lf["lfase"]),
-                             int(lf["ctb_log2"]), bit_depth)
+    l = lib()
+    l.vvcref_sao_scratch_bytes.restype = C.c_size_t
+    scratch = np.zeros(l.vvcref_sao_scratch_bytes(C.byref(pl), int(lf["ctb_log2"])), np.uint8)
+    chunks = _row_chunks(_ctb_rows(planes, lf["ctb_log2"]), threads)
+    for phase in (1, 2):
+        _parallel(lambda a, b: l.vvcref_sao_picture(C.byref(pl), C.c_void_p(sao.ctypes.data), C.c_void_p(sl.ctypes.data),
+                                                    int(lf["lfase"]), int(lf["ctb_log2"]), bit_depth,
+                                                    C.c_void_p(scratch.ctypes.data), phase, a, b), chunks)
 
 
-def alf_picture(planes, lf):
+def alf_picture(planes, lf, threads=1):
     pl = abi.host_planes(planes)
     alf = np.ascontiguousarray(lf["alf"])
     sl = np.ascontiguousarray(lf["slice_idx"], np.int16)
     p = np.ascontiguousarray(lf["alf_params"])
-    lib().vvcref_alf_picture(C.byref(pl), C.c_void_p(alf.ctypes.data), C.c_void_p(p.ctypes.data),
-                             C.c_void_p(sl.ctypes.data), int(lf["lfase"]))
+    l = lib()
+    l.vvcref_alf_scratch_bytes.restype = C.c_size_t
+    scratch = np.zeros(l.vvcref_alf_scratch_bytes(C.byref(pl), int(lf["ctb_log2"])), np.uint8)
+    chunks = _row_chunks(_ctb_rows(planes, lf["ctb_log2"]), threads)
+    for phase in (1, 2):
+        _parallel(lambda a, b: l.vvcref_alf_picture(C.byref(pl), C.c_void_p(alf.ctypes.data), C.c_void_p(p.ctypes.data),
+                                                    C.c_void_p(sl.ctypes.data), int(lf["lfase"]),
+                                                    C.c_void_p(scratch.ctypes.data), phase, a, b), chunks)
 
 
-def lmcs_picture(planes, inv_lut, ctb_log2=7, bit_depth=10):
+def lmcs_picture(planes, inv_lut, ctb_log2=7, bit_depth=10, threads=1):
     pl = abi.host_planes(planes)
     lut = np.ascontiguousarray(inv_lut, np.uint16)
-    lib().vvcref_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data), ctb_log2, bit_depth)
+    chunks = _row_chunks(_ctb_rows(planes, ctb_log2), threads)
+    _parallel(lambda a, b: lib().vvcref_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data), ctb_log2, bit_depth, a, b),
+              chunks)

@@ -1,0 +1,79 @@
+"""The whole reconstruction + loop-filter chain of one picture, on the oracle and on the GPU engine."""
+import numpy as np
+
+from ffmpeg_b200 import lib
+from oracle import portapi, refapi
+
+
+def oracle_picture(pic):
+    """Reference stage functions in stage order (vvc_thread.c:41-51): INTER, RECON (residual), LMCS, DEBLOCK_V,
+    DEBLOCK_H, SAO, ALF.  Uses the compiled reference when present, else the C port."""
+    planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
+    it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+    fwd, inv = pic["lmcs"] if pic["lmcs"] is not None else (None, None)
+    edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+    if refapi.available():
+        refapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+        refapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], rs["intra_mode"])
+        if inv is not None:
+            refapi.lmcs_picture(planes, inv, pic["ctb_log2"])
+        refapi.deblock_picture(planes, db)
+        refapi.sao_picture(planes, lf)
+        refapi.alf_picture(planes, lf)
+        return planes
+    portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+    portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"])
+    if inv is not None:
+        portapi.lmcs_picture(planes, inv)
+    portapi.deblock_picture(planes, edge, db["qp"], db["ctb_offsets"], db["stride4"], db["params"])
+    tmp = [np.zeros_like(p) for p in planes]
+    portapi.sao_picture(tmp, planes, lf)
+    portapi.alf_picture(planes, tmp, lf)
+    return planes
+
+
+class EnginePicture:
+    """Pinned host copies of one picture's batches + the Level-B call sequence (HOST buffers in, HOST planes out)."""
+
+    def __init__(self, ctx, pic):
+        it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+        self.ctx, self.pic = ctx, pic
+        self.n_refs = len(it["refs"])
+        self.refs = [[ctx.pinned_copy(np.ascontiguousarray(p)) for p in r] for r in it["refs"]]
+        self.blocks = ctx.pinned_copy(it["blocks"])
+        self.levels = ctx.pinned_copy(rs["levels"])
+        self.tbs = ctx.pinned_copy(rs["tbs"])
+        edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+        self.edge = ctx.pinned_copy(edge)
+        self.qp = ctx.pinned_copy(db["qp"])
+        self.ctb_offsets = ctx.pinned_copy(db["ctb_offsets"])
+        self.sao = ctx.pinned_copy(lf["sao"])
+        self.alf = ctx.pinned_copy(lf["alf"])
+        self.alf_params = ctx.pinned_copy(lf["alf_params"])
+        self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
+        self.out = ctx.pinned_planes()
+        # the picture is reconstructed into the slot after the references; ref_slot[][] already maps to 0..n_refs-1
+        self.cur_slot = self.n_refs
+
+    def h2d_bytes(self):
+        return int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
+                   self.ctb_offsets.nbytes + self.sao.nbytes + self.alf.nbytes + self.alf_params.nbytes)
+
+    def d2h_bytes(self):
+        return int(sum(p.nbytes for p in self.out))
+
+    def upload_refs(self):
+        for i, r in enumerate(self.refs):
+            self.ctx.upload(r, slot=i)
+
+    def run(self, download=True):
+        ctx, pic = self.ctx, self.pic
+        ctx.begin(self.cur_slot)
+        ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0])
+        ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
+        if self.luts is not None:
+            ctx.lmcs(self.luts[1])
+        ctx.deblock(self.edge, self.qp, self.ctb_offsets, pic["deblock"]["stride4"], pic["deblock"]["params"])
+        ctx.sao_alf(self.sao, self.alf, self.alf_params, pic["ctb_log2"])
+        if download:
+            ctx.download(self.out)

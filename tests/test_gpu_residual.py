@@ -147,8 +147,8 @@ def test_level_b_context_host_buffers():
         levels[...] = pic["levels"]
         tbs = ctx.pinned(pic["tbs"].shape, abi.TB_DTYPE)
         tbs[...] = pic["tbs"]
-        for _ in range(2):                      # twice: the second picture reuses the device buffers
-            ctx.begin()
+        for k in range(2):                      # twice: the second picture reuses the device buffers
+            ctx.begin(k)
             ctx.upload(src)
             ctx.residual(levels, tbs, pic["params"])
             ctx.download(out)
