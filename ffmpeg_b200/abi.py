@@ -77,7 +77,8 @@ assert PB_DTYPE.itemsize == 32
 
 class InterParams(C.Structure):
     _fields_ = [
-        ("bit_depth", C.c_int32), ("log2_denom", C.c_int32 * 2), ("reserved", C.c_int32),
+        ("bit_depth", C.c_int32), ("log2_denom", C.c_int32 * 2), ("n_w16", C.c_int32), ("n_w8", C.c_int32),
+        ("reserved", C.c_int32 * 3),
         ("weight", ((C.c_int16 * 16) * 3) * 2), ("offset", ((C.c_int16 * 16) * 3) * 2),
         ("ref_slot", (C.c_uint8 * 16) * 2),
     ]
@@ -97,6 +98,15 @@ def inter_params(bit_depth=10, log2_denom=(0, 0), weight=None, offset=None, ref_
     C.memmove(p.offset, o.ctypes.data, o.nbytes)
     C.memmove(p.ref_slot, r.ctypes.data, r.nbytes)
     return p
+
+
+def order_blocks_by_width(blocks, params):
+    """Sort a prediction-block batch into the width order the engine wants and record the class sizes."""
+    order = np.argsort(-blocks["w"].astype(np.int32), kind="stable")
+    blocks = np.ascontiguousarray(blocks[order])
+    params.n_w16 = int(np.sum(blocks["w"] == 16))
+    params.n_w8 = int(np.sum(blocks["w"] == 8))
+    return blocks
 
 
 def planes_array(list_of_planes):

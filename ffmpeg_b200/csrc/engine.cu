@@ -271,6 +271,14 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     }
     if (n == 0)
         return 0;
+    for (int i = 0; i < n; i++) {           // the batch must come in width order (cheap to check, fatal to get wrong)
+        const int want = i < params->n_w16 ? 16 : i < params->n_w16 + params->n_w8 ? 8 : 4;
+        if (blocks[i].w != want) {
+            set_error("vvcb200_pic_inter: block %d has width %d where the width order (n_w16 %d, n_w8 %d) wants %d",
+                      i, blocks[i].w, params->n_w16, params->n_w8, want);
+            return VVCB200_ERR_ARG;
+        }
+    }
     DeviceGuard g(c->device);
     if (int r = upload(c, c->blocks, blocks, (size_t)n * sizeof(*blocks)))
         return r;

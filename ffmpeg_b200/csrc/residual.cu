@@ -16,13 +16,17 @@
 namespace vvcb200 {
 
 constexpr int kWarpsPerCta = 4;
-constexpr int kChunk       = 32;            // transform blocks per CTA
-constexpr int kDct2Bytes   = 3412;
-constexpr int kDstBytes    = 1360;
-constexpr int kMatBytes    = kDct2Bytes + 2 * kDstBytes;   // DCT2 | DST7 | DCT8
-constexpr int kMatPad      = (kMatBytes + 15) & ~15;
-constexpr int kInElems     = 32 * 32;       // non-zero input box (zero-out keeps <= 32 x 32)
-constexpr int kMidElems    = 64 * 32;       // after the column pass: h rows x nzw columns
+constexpr int kChunk       = 32;            // transform blocks per CTA (Level-A kernels)
+constexpr int kPackedWords = 1536;          // VVC_TX_PACKED: every transform matrix, dp2a-packed (6 KB)
+constexpr int kMatPad      = kPackedWords * 4;
+constexpr int kInElems     = 32 * 32;       // generic path: non-zero input box (zero-out keeps <= 32 x 32)
+constexpr int kMidElems    = 64 * 32;       // generic path: after the column pass, h rows x nzw columns
+constexpr int kPairStride  = 34;            // fast path: int16 row stride of the transposed input / the middle
+                                            // block; 17 words -> lanes on different rows hit different banks
+constexpr int kFastIn      = 32 * kPairStride;     // inT[x][k]
+constexpr int kFastMid     = 64 * kPairStride;     // mid[y][x]
+constexpr int kWarpElems   = kFastIn + kFastMid;   // 3264 int16 per warp (>= kInElems + kMidElems = 3072)
+static_assert(kWarpElems >= kInElems + kMidElems, "generic path must fit");
 
 struct ScalingLists {                        // passed by value (kernel parameter space, uniform reads)
     uint8_t rec[28][64];
@@ -39,27 +43,36 @@ struct ResidualArgs {
     int to_residual;
 };
 
-__device__ __forceinline__ const int8_t *tx_matrix(const int8_t *smat, int type, int log2n)
+// Packed matrix of (type, log2N) in shared memory: word [kp * (N/2) + jp], see tools/gen_tables.py
+__device__ __forceinline__ const uint32_t *tx_packed(const uint32_t *smat, int type, int log2n)
 {
-    if (type == VVCB200_DCT2)
-        return smat + VVC_DCT2_OFF[log2n - 1];
-    return smat + kDct2Bytes + (type == VVCB200_DCT8 ? kDstBytes : 0) + VVC_DST7_OFF[log2n - 2];
+    return smat + VVC_TX_PACKED_OFF[type * 8 + log2n];
 }
 
-__device__ __forceinline__ void load_matrices(int8_t *smat)
-{
-    // 16-byte vector copy of the three matrix families into shared memory
-    static_assert(kDct2Bytes % 4 == 0 && kDstBytes % 4 == 0, "word copy");
-    uint32_t *d = reinterpret_cast<uint32_t *>(smat);
-    const uint32_t *s0 = reinterpret_cast<const uint32_t *>(VVC_DCT2_MAT);
-    const uint32_t *s1 = reinterpret_cast<const uint32_t *>(VVC_DST7_MAT);
-    const uint32_t *s2 = reinterpret_cast<const uint32_t *>(VVC_DCT8_MAT);
-    for (int i = threadIdx.x; i < kDct2Bytes / 4; i += blockDim.x)
-        d[i] = s0[i];
-    for (int i = threadIdx.x; i < kDstBytes / 4; i += blockDim.x) {
-        d[kDct2Bytes / 4 + i] = s1[i];
-        d[(kDct2Bytes + kDstBytes) / 4 + i] = s2[i];
+// Element M[k][j] of a packed matrix (generic path only)
+struct TxMatrix {
+    const int8_t *bytes;
+    int half_n;
+    __device__ __forceinline__ int at(int k, int j) const
+    {
+        return bytes[(((k >> 1) * half_n + (j >> 1)) << 2) + (k & 1) + ((j & 1) << 1)];
     }
+};
+
+__device__ __forceinline__ TxMatrix tx_matrix(const uint32_t *smat, int type, int log2n)
+{
+    TxMatrix m;
+    m.bytes = reinterpret_cast<const int8_t *>(tx_packed(smat, type, log2n));
+    m.half_n = 1 << (log2n - 1);
+    return m;
+}
+
+__device__ __forceinline__ void load_matrices(uint32_t *smat)
+{
+    const uint4 *src = reinterpret_cast<const uint4 *>(VVC_TX_PACKED);
+    uint4 *dst = reinterpret_cast<uint4 *>(smat);
+    for (int i = threadIdx.x; i < kPackedWords / 4; i += blockDim.x)
+        dst[i] = src[i];
 }
 
 // The 2-D / 1-D inverse transform of one block by one warp (vvcdsp.c:94-138).
@@ -67,7 +80,7 @@ __device__ __forceinline__ void load_matrices(int8_t *smat)
 //   mid: scratch for the column-pass result (h x nzw)
 //   emit(y, x, r) receives every residual sample of the w x h block exactly once.
 template <typename T, typename Emit>
-__device__ __forceinline__ void inverse_transform(const T *in, int in_stride, T *mid, const int8_t *smat,
+__device__ __forceinline__ void inverse_transform(const T *in, int in_stride, T *mid, const uint32_t *smat,
                                                   int trh, int trv, int log2w, int log2h, int nzw, int nzh,
                                                   int range, int bd, int lane, Emit emit)
 {
@@ -83,21 +96,21 @@ __device__ __forceinline__ void inverse_transform(const T *in, int in_stride, T 
                 emit(i >> log2w, i & (w - 1), dc);
             return;
         }
-        const int8_t *mv = tx_matrix(smat, trv, log2h);
+        const TxMatrix mv = tx_matrix(smat, trv, log2h);
         for (int i = lane; i < h * nzw; i += 32) {
             const int j = i / nzw, x = i - j * nzw;
             unsigned acc = 0;
             for (int k = 0; k < nzh; k++)
-                acc += (unsigned)(int)in[k * in_stride + x] * (unsigned)(int)mv[k * h + j];
+                acc += (unsigned)(int)in[k * in_stride + x] * (unsigned)mv.at(k, j);
             mid[i] = (T)clip_intp2(((int)acc + 64) >> 7, range);
         }
         __syncwarp();
-        const int8_t *mh = tx_matrix(smat, trh, log2w);
+        const TxMatrix mh = tx_matrix(smat, trh, log2w);
         for (int i = lane; i < w * h; i += 32) {
             const int y = i >> log2w, x = i & (w - 1);
             unsigned acc = 0;
             for (int k = 0; k < nzw; k++)
-                acc += (unsigned)(int)mid[y * nzw + k] * (unsigned)(int)mh[k * w + x];
+                acc += (unsigned)(int)mid[y * nzw + k] * (unsigned)mh.at(k, x);
             emit(y, x, (int)(acc + (1u << (sh1 - 1))) >> sh1);
         }
     } else {
@@ -112,14 +125,86 @@ __device__ __forceinline__ void inverse_transform(const T *in, int in_stride, T 
         const int type = w > 1 ? trh : trv;
         const int nz   = w > 1 ? nzw : nzh;
         const int step = w > 1 ? 1 : in_stride;
-        const int8_t *m = tx_matrix(smat, type, w > 1 ? log2w : log2h);
+        const TxMatrix m = tx_matrix(smat, type, w > 1 ? log2w : log2h);
         for (int i = lane; i < n; i += 32) {
             unsigned acc = 0;
             for (int k = 0; k < nz; k++)
-                acc += (unsigned)(int)in[k * step] * (unsigned)(int)m[k * n + i];
+                acc += (unsigned)(int)in[k * step] * (unsigned)m.at(k, i);
             emit(w > 1 ? 0 : i, w > 1 ? i : 0, (int)(acc + (1u << (sh - 1))) >> sh);
         }
     }
+}
+
+// ---- fast path: dp2a register-tiled passes ---------------------------------------------------------------------
+// One 1-D pass for one lane: R consecutive outputs (first output j0, even) from n_kp input pairs.
+//   src : this lane's input pairs, word kp = (x[2kp], x[2kp+1]) as int16x2
+//   mat : packed matrix of the pass, row kp has half_n words, word jp serves outputs 2jp (lo bytes) and 2jp+1 (hi bytes)
+// 16-bit inputs x 8-bit matrix entries accumulate exactly in int32 (32 terms * 2^15 * 90 < 2^31).
+template <int R>
+__device__ __forceinline__ void dp2a_pass(int (&acc)[R], const uint32_t *src, int n_kp, const uint32_t *mat, int half_n, int j0)
+{
+#pragma unroll
+    for (int r = 0; r < R; r++)
+        acc[r] = 0;
+    const uint32_t *m = mat + (j0 >> 1);
+    for (int kp = 0; kp < n_kp; kp++, m += half_n) {
+        const int a = (int)src[kp];
+        if constexpr (R >= 8) {
+#pragma unroll
+            for (int q = 0; q < R / 8; q++) {
+                const uint4 w = *reinterpret_cast<const uint4 *>(m + 4 * q);
+                acc[8 * q + 0] = __dp2a_lo(a, (int)w.x, acc[8 * q + 0]);
+                acc[8 * q + 1] = __dp2a_hi(a, (int)w.x, acc[8 * q + 1]);
+                acc[8 * q + 2] = __dp2a_lo(a, (int)w.y, acc[8 * q + 2]);
+                acc[8 * q + 3] = __dp2a_hi(a, (int)w.y, acc[8 * q + 3]);
+                acc[8 * q + 4] = __dp2a_lo(a, (int)w.z, acc[8 * q + 4]);
+                acc[8 * q + 5] = __dp2a_hi(a, (int)w.z, acc[8 * q + 5]);
+                acc[8 * q + 6] = __dp2a_lo(a, (int)w.w, acc[8 * q + 6]);
+                acc[8 * q + 7] = __dp2a_hi(a, (int)w.w, acc[8 * q + 7]);
+            }
+        } else if constexpr (R == 4) {
+            const uint2 w = *reinterpret_cast<const uint2 *>(m);
+            acc[0] = __dp2a_lo(a, (int)w.x, acc[0]);
+            acc[1] = __dp2a_hi(a, (int)w.x, acc[1]);
+            acc[2] = __dp2a_lo(a, (int)w.y, acc[2]);
+            acc[3] = __dp2a_hi(a, (int)w.y, acc[3]);
+        } else {
+            const uint32_t w = m[0];
+            acc[0] = __dp2a_lo(a, (int)w, acc[0]);
+            acc[1] = __dp2a_hi(a, (int)w, acc[1]);
+        }
+    }
+}
+
+// Column pass of one block: the lane computes outputs j0 .. j0 + R - 1 of column x and stores them,
+// scaled and clipped to 16 bits, into mid[j][x] (scale_clip, vvcdsp.c:67-80).
+template <int R>
+__device__ __forceinline__ void fast_column_pass(const int16_t *inT, int16_t *mid, const uint32_t *mat, int half_n,
+                                                 int x, int j0, int nzw, int n_kp, int range)
+{
+    int acc[R];
+    dp2a_pass<R>(acc, reinterpret_cast<const uint32_t *>(inT + x * kPairStride), n_kp, mat, half_n, j0);
+#pragma unroll
+    for (int r = 0; r < R; r++) {
+        const int j = j0 + r;
+        mid[j * kPairStride + x] = (int16_t)clip_intp2((acc[r] + 64) >> 7, range);
+        if ((nzw & 1) && x == nzw - 1)
+            mid[j * kPairStride + nzw] = 0;          // pad the last input pair of the row pass
+    }
+}
+
+// Row pass: the lane computes outputs x0 .. x0 + R - 1 of row y and hands them to the epilogue in
+// groups of two adjacent samples.
+template <int R, typename Emit2>
+__device__ __forceinline__ void fast_row_pass(const int16_t *mid, const uint32_t *mat, int half_n, int y, int x0,
+                                              int n_kp, int sh1, Emit2 emit2)
+{
+    int acc[R];
+    dp2a_pass<R>(acc, reinterpret_cast<const uint32_t *>(mid + y * kPairStride), n_kp, mat, half_n, x0);
+    const int add = 1 << (sh1 - 1);
+#pragma unroll
+    for (int r = 0; r < R; r += 2)
+        emit2(y, x0 + r, (acc[r] + add) >> sh1, (acc[r + 1] + add) >> sh1);
 }
 
 // Table 38 (vvc_intra.c:342-362)
@@ -141,28 +226,185 @@ __device__ __forceinline__ int lmcs_scale_residual(int r, int scale, int bd)
     return c < 0 ? -s : s;
 }
 
-__global__ void __launch_bounds__(kWarpsPerCta * 32)
+// dequantisation of one level (scale_coeff, vvc_intra.c:389-395); products wrap mod 2^32 like the reference's int
+struct Dequant {
+    unsigned scale, bd_off;
+    int bd_shift, id, l2m, log2_w, log2_h, range;
+    bool use_sl;
+    __device__ __forceinline__ int apply(int c, int x, int y, const ScalingLists &sl) const
+    {
+        unsigned m = 16;
+        if (use_sl) {
+            const int off = ((y << l2m) >> log2_h) << l2m;
+            m = sl.rec[id][off + ((x << l2m) >> log2_w)];
+            if (id >= 14 && !(x | y))
+                m = sl.dc[id - 14];
+        }
+        const int v = (int)((unsigned)c * scale * m + bd_off) >> bd_shift;
+        return clip_intp2(v, range);
+    }
+};
+
+__device__ __forceinline__ Dequant make_dequant(const VVCB200TransformBlock &d, bool ts, int bd, int range)
+{
+    Dequant q;
+    const int log_sum = d.log2_w + d.log2_h;
+    const int rect = ts ? 0 : (log_sum & 1);
+    const int dq = (d.flags & VVCB200_TB_DEP_QUANT) ? 1 : 0;
+    q.bd_shift = ts ? 10 : bd + rect + (log_sum >> 1) + 10 - range + dq;
+    q.bd_off = (1u << q.bd_shift) >> 1;
+    const int qp = d.qp + (ts ? 0 : dq);
+    const int rem = qp % 6;
+    const int ls0 = rem == 0 ? 40 : rem == 1 ? 45 : rem == 2 ? 51 : rem == 3 ? 57 : rem == 4 ? 64 : 72;
+    const int ls1 = rem == 0 ? 57 : rem == 1 ? 64 : rem == 2 ? 72 : rem == 3 ? 80 : rem == 4 ? 90 : 102;
+    q.scale = (unsigned)(rect ? ls1 : ls0) << (qp / 6);
+    q.use_sl = (d.flags & VVCB200_TB_SCALING) && !ts;
+    q.id = scaling_id((d.flags & VVCB200_TB_INTER) != 0, d.c_idx, max(d.log2_w, d.log2_h));
+    q.l2m = q.id < 2 ? 1 : q.id < 8 ? 2 : 3;
+    q.log2_w = d.log2_w;
+    q.log2_h = d.log2_h;
+    q.range = range;
+    return q;
+}
+
+__global__ void __launch_bounds__(kWarpsPerCta * 32, 7)      // 7 CTAs/SM is also the shared-memory limit (32 KB each)
 residual_kernel(const ResidualArgs a, const ScalingLists sl)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    int8_t *smat = reinterpret_cast<int8_t *>(smem_raw);
+    uint32_t *smat = reinterpret_cast<uint32_t *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int16_t *in  = reinterpret_cast<int16_t *>(smem_raw + kMatPad) + warp * (kInElems + kMidElems);
-    int16_t *mid = in + kInElems;
+    int16_t *in  = reinterpret_cast<int16_t *>(smem_raw + kMatPad) + warp * kWarpElems;
+    int16_t *mid = in + kInElems;                 // generic path layout
+    int16_t *inT = in, *fmid = in + kFastIn;      // fast path layout (same memory)
 
     load_matrices(smat);
     __syncthreads();
 
     // The list is sorted by block area (largest first).  CTA b takes blocks b, b + grid, b + 2*grid, ... so
     // every CTA gets the same size profile (no tail of CTAs stuck with the 64x64 blocks).
-    for (int t = blockIdx.x + warp * gridDim.x; t < a.n; t += kWarpsPerCta * gridDim.x) {
-        const VVCB200TransformBlock d = a.tbs[t];
+    const int t_step = kWarpsPerCta * gridDim.x;
+    int t = blockIdx.x + warp * gridDim.x;
+    VVCB200TransformBlock d_next = {};
+    if (t < a.n)
+        d_next = a.tbs[t];
+    for (; t < a.n; t += t_step) {
+        const VVCB200TransformBlock d = d_next;
         const int w = 1 << d.log2_w, h = 1 << d.log2_h;
         const bool ts = d.flags & VVCB200_TB_TS;
         const int16_t *lv = a.levels + d.coeff_off;
         int nzw = d.nzw, nzh = d.nzh, in_stride = d.nzw;
+        const Dequant q = make_dequant(d, ts, a.bd, a.range);
+        // software pipeline: fetch the next descriptor and pull its levels and this block's destination rows
+        // towards the SM while this block is being transformed
+        if (t + t_step < a.n) {
+            d_next = a.tbs[t + t_step];
+            if (lane == 0)
+                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.levels + d_next.coeff_off));
+        }
+        if (!a.to_residual && lane < h)
+            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.dst.p[d.c_idx] + (size_t)(d.y0 + lane) * a.dst.stride[d.c_idx] + d.x0));
+
+        // ---- epilogue shared by both paths (add_residual / joint CbCr / LMCS chroma scale, vvc_intra.c:166-186,451-477)
+        const int other = 3 - d.c_idx;
+        const bool joint = (d.flags & VVCB200_TB_JOINT) && d.c_idx;
+        const int jshift = (d.flags & VVCB200_TB_JOINT_SHIFT) ? 1 : 0;
+        const bool lmcs = d.flags & VVCB200_TB_LMCS_SCALE;
+        const int lscale = d.lmcs_scale;
+        auto emit = [&](int y, int x, int r) {
+            int r2 = joint ? (r * a.c_sign) >> jshift : 0;
+            if (lmcs) {
+                r = lmcs_scale_residual(r, lscale, a.bd);
+                r2 = lmcs_scale_residual(r2, lscale, a.bd);
+            }
+            if (a.to_residual) {
+                int16_t *p = reinterpret_cast<int16_t *>(a.res.p[d.c_idx]) + (size_t)(d.y0 + y) * a.res.stride[d.c_idx] + d.x0 + x;
+                *p = (int16_t)clip_intp2(r, 15);
+                if (joint) {
+                    int16_t *p2 = reinterpret_cast<int16_t *>(a.res.p[other]) + (size_t)(d.y0 + y) * a.res.stride[other] + d.x0 + x;
+                    *p2 = (int16_t)clip_intp2(r2, 15);
+                }
+            } else {
+                uint16_t *p = a.dst.p[d.c_idx] + (size_t)(d.y0 + y) * a.dst.stride[d.c_idx] + d.x0 + x;
+                *p = (uint16_t)clip_pixel(*p + r, a.bd);
+                if (joint) {
+                    uint16_t *p2 = a.dst.p[other] + (size_t)(d.y0 + y) * a.dst.stride[other] + d.x0 + x;
+                    *p2 = (uint16_t)clip_pixel(*p2 + r2, a.bd);
+                }
+            }
+        };
+        // two horizontally adjacent samples at once: 32-bit read-modify-write (x is even, planes are 4-byte aligned)
+        auto emit2 = [&](int y, int x, int r0, int r1) {
+            if (joint || lmcs || a.to_residual) {
+                emit(y, x, r0);
+                emit(y, x + 1, r1);
+                return;
+            }
+            uint32_t *p = reinterpret_cast<uint32_t *>(a.dst.p[d.c_idx] + (size_t)(d.y0 + y) * a.dst.stride[d.c_idx] + d.x0 + x);
+            const uint32_t v = *p;
+            *p = (uint32_t)clip_pixel((int)(v & 0xffff) + r0, a.bd) | ((uint32_t)clip_pixel((int)(v >> 16) + r1, a.bd) << 16);
+        };
 
         __syncwarp();
+        const bool dconly = d.trh == VVCB200_DCT2 && d.trv == VVCB200_DCT2 && nzw == 1 && nzh == 1 && w == h;
+        if (!ts && !d.lfnst && w > 1 && h > 1 && !dconly && !(d.flags & VVCB200_TB_BDPCM)) {
+            // ================= fast path: 2-D transform with dp2a register tiles =================
+            // levels -> dequant -> inT[x][k] (transposed so that pairs along k are one 32-bit word)
+            if (lane < nzw) {
+                for (int y = 0; y < nzh; y++) {
+                    const int c = lv[y * nzw + lane];
+                    inT[lane * kPairStride + y] = (int16_t)(c ? q.apply(c, lane, y, sl) : 0);
+                }
+                if (nzh & 1)
+                    inT[lane * kPairStride + nzh] = 0;
+            }
+            __syncwarp();
+            {   // column pass: lane = g * cw + x owns column x and the outputs [g * per_lane, (g + 1) * per_lane)
+                const int cw = nzw <= 1 ? 1 : 1 << (32 - __clz(nzw - 1));      // nzw rounded up to a power of two
+                const int groups = min(32 / cw, h >> 1);
+                const int per_lane = h / groups;                                // even
+                const int x = lane & (cw - 1), g = lane / cw;
+                const uint32_t *mat = tx_packed(smat, d.trv, d.log2_h);
+                const int n_kp = (nzh + 1) >> 1, half = h >> 1;
+                if (x < nzw && g < groups) {
+                    // at most 16 accumulators live at a time (register budget = occupancy)
+                    switch (per_lane) {
+                    case 2:  fast_column_pass<2>(inT, fmid, mat, half, x, g * 2, nzw, n_kp, a.range); break;
+                    case 4:  fast_column_pass<4>(inT, fmid, mat, half, x, g * 4, nzw, n_kp, a.range); break;
+                    case 8:  fast_column_pass<8>(inT, fmid, mat, half, x, g * 8, nzw, n_kp, a.range); break;
+                    default:
+                        for (int j0 = g * per_lane; j0 < (g + 1) * per_lane; j0 += 16)
+                            fast_column_pass<16>(inT, fmid, mat, half, x, j0, nzw, n_kp, a.range);
+                        break;
+                    }
+                }
+            }
+            __syncwarp();
+            {   // row pass + epilogue: lane = g * rows + y owns row y and the outputs [g * per_lane, (g + 1) * per_lane)
+                const int rows = min(h, 32);
+                const int groups = min(32 / rows, w >> 1);
+                const int per_lane = w / groups;
+                const int yl = lane & (rows - 1), g = lane / rows;
+                const uint32_t *mat = tx_packed(smat, d.trh, d.log2_w);
+                const int n_kp = (nzw + 1) >> 1, half = w >> 1;
+                const int sh1 = 5 + a.range - a.bd;
+                if (g < groups) {
+                    for (int y = yl; y < h; y += 32) {
+                        switch (per_lane) {
+                        case 2:  fast_row_pass<2>(fmid, mat, half, y, g * 2, n_kp, sh1, emit2); break;
+                        case 4:  fast_row_pass<4>(fmid, mat, half, y, g * 4, n_kp, sh1, emit2); break;
+                        case 8:  fast_row_pass<8>(fmid, mat, half, y, g * 8, n_kp, sh1, emit2); break;
+                        default:
+                            for (int x0 = g * per_lane; x0 < (g + 1) * per_lane; x0 += 16)
+                                fast_row_pass<16>(fmid, mat, half, y, x0, n_kp, sh1, emit2);
+                            break;
+                        }
+                    }
+                }
+            }
+            continue;
+        }
+
+        // ================= generic path: TS, BDPCM, LFNST, 1-D blocks, DC-only =================
         // ---- levels into shared memory (+ BDPCM prefix sums on the raw levels)
         if (d.flags & VVCB200_TB_BDPCM) {
             in_stride = w;
@@ -197,37 +439,13 @@ residual_kernel(const ResidualArgs a, const ScalingLists sl)
             __syncwarp();
         }
         // ---- dequant (vvc_intra.c:277-417)
-        {
-            const int log_sum = d.log2_w + d.log2_h;
-            const int rect = ts ? 0 : (log_sum & 1);
-            const int dq = (d.flags & VVCB200_TB_DEP_QUANT) ? 1 : 0;
-            const int bd_shift = ts ? 10 : a.bd + rect + (log_sum >> 1) + 10 - a.range + dq;
-            const unsigned bd_off = (1u << bd_shift) >> 1;
-            const int qp = d.qp + (ts ? 0 : dq);
-            const int rem = qp % 6;
-            const int ls0 = rem == 0 ? 40 : rem == 1 ? 45 : rem == 2 ? 51 : rem == 3 ? 57 : rem == 4 ? 64 : 72;
-            const int ls1 = rem == 0 ? 57 : rem == 1 ? 64 : rem == 2 ? 72 : rem == 3 ? 80 : rem == 4 ? 90 : 102;
-            const unsigned scale = (unsigned)(rect ? ls1 : ls0) << (qp / 6);
-            const bool use_sl = (d.flags & VVCB200_TB_SCALING) && !ts;
-            const int id = scaling_id((d.flags & VVCB200_TB_INTER) != 0, d.c_idx, max(d.log2_w, d.log2_h));
-            const int l2m = id < 2 ? 1 : id < 8 ? 2 : 3;
-            for (int i = lane; i < nzw * nzh; i += 32) {
-                const int y = i / nzw, x = i - y * nzw;
-                const int c = in[y * in_stride + x];
-                if (c) {
-                    unsigned m = 16;
-                    if (use_sl) {
-                        const int off = ((y << l2m) >> d.log2_h) << l2m;
-                        m = sl.rec[id][off + ((x << l2m) >> d.log2_w)];
-                        if (id >= 14 && i == 0)
-                            m = sl.dc[id - 14];
-                    }
-                    const int v = (int)((unsigned)c * scale * m + bd_off) >> bd_shift;
-                    in[y * in_stride + x] = (int16_t)clip_intp2(v, a.range);
-                }
-            }
-            __syncwarp();
+        for (int i = lane; i < nzw * nzh; i += 32) {
+            const int y = i / nzw, x = i - y * nzw;
+            const int c = in[y * in_stride + x];
+            if (c)
+                in[y * in_stride + x] = (int16_t)q.apply(c, x, y, sl);
         }
+        __syncwarp();
         // ---- inverse LFNST (vvc_intra.c:65-127, vvc_itx_1d.c:708-721)
         if (d.lfnst && !ts) {
             const int idx = (d.lfnst & 3) - 1, set = (d.lfnst >> 2) & 3;
@@ -248,7 +466,7 @@ residual_kernel(const ResidualArgs a, const ScalingLists sl)
                 int y = i / size, x = i - y * size;
                 out[r] = 0;
                 if (i < size * size) {
-                    if (transpose) { const int s = x; x = y; y = s; }
+                    if (transpose) { const int sw = x; x = y; y = sw; }
                     const int j = size == 4 ? y * 4 + x : (y < 4 ? y * 8 + x : (x < 4 ? 32 + (y - 4) * 4 + x : -1));
                     if (j >= 0) {
                         int acc = 0;
@@ -266,33 +484,6 @@ residual_kernel(const ResidualArgs a, const ScalingLists sl)
             __syncwarp();
         }
         // ---- inverse transform + epilogue
-        const int other = 3 - d.c_idx;
-        const bool joint = (d.flags & VVCB200_TB_JOINT) && d.c_idx;
-        const int jshift = (d.flags & VVCB200_TB_JOINT_SHIFT) ? 1 : 0;
-        const bool lmcs = d.flags & VVCB200_TB_LMCS_SCALE;
-        const int lscale = d.lmcs_scale;
-        auto emit = [&](int y, int x, int r) {
-            int r2 = joint ? (r * a.c_sign) >> jshift : 0;
-            if (lmcs) {
-                r = lmcs_scale_residual(r, lscale, a.bd);
-                r2 = lmcs_scale_residual(r2, lscale, a.bd);
-            }
-            if (a.to_residual) {
-                int16_t *p = reinterpret_cast<int16_t *>(a.res.p[d.c_idx]) + (size_t)(d.y0 + y) * a.res.stride[d.c_idx] + d.x0 + x;
-                *p = (int16_t)clip_intp2(r, 15);
-                if (joint) {
-                    int16_t *q = reinterpret_cast<int16_t *>(a.res.p[other]) + (size_t)(d.y0 + y) * a.res.stride[other] + d.x0 + x;
-                    *q = (int16_t)clip_intp2(r2, 15);
-                }
-            } else {
-                uint16_t *p = a.dst.p[d.c_idx] + (size_t)(d.y0 + y) * a.dst.stride[d.c_idx] + d.x0 + x;
-                *p = (uint16_t)clip_pixel(*p + r, a.bd);
-                if (joint) {
-                    uint16_t *q = a.dst.p[other] + (size_t)(d.y0 + y) * a.dst.stride[other] + d.x0 + x;
-                    *q = (uint16_t)clip_pixel(*q + r2, a.bd);
-                }
-            }
-        };
         if (ts) {
             for (int i = lane; i < w * h; i += 32) {
                 const int y = i >> d.log2_w, x = i & (w - 1);
@@ -317,7 +508,7 @@ __global__ void __launch_bounds__(kWarpsPerCta * 32)
 itx_kernel(const ItxArgs a)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
-    int8_t *smat = reinterpret_cast<int8_t *>(smem_raw);
+    uint32_t *smat = reinterpret_cast<uint32_t *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     int32_t *in  = reinterpret_cast<int32_t *>(smem_raw + kMatPad) + warp * (kInElems + kMidElems);
     int32_t *mid = in + kInElems;
@@ -415,7 +606,7 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
     memset(sl.dc, 16, sizeof(sl.dc));
     memcpy(sl.dc, params->scaling_matrix_dc_rec, 14);
 
-    const size_t smem = kMatPad + kWarpsPerCta * (kInElems + kMidElems) * sizeof(int16_t);
+    const size_t smem = kMatPad + kWarpsPerCta * kWarpElems * sizeof(int16_t);
     static bool ready[64];
     if (int r = opt_in_smem(residual_kernel, smem, ready))
         return r;

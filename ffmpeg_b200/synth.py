@@ -248,6 +248,7 @@ def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
     params = abi.inter_params(10, ld, weight, offset, ref_slot)
+    b = abi.order_blocks_by_width(b, params)
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     return dict(blocks=b, params=params, refs=refs, dims=dims, seed=seed)

@@ -135,7 +135,8 @@ VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pl
 
 /* ------------------------------------------------------------------------------------------------
  * Inter prediction descriptors (stage INTER, ff_vvc_predict_inter, vvc_inter.c:899-913).
- * One record per prediction sub-block of at most 16x16 luma samples: the host emitter splits larger
+ * One record per prediction sub-block of at most 16x16 luma samples, ordered by width (see VVCB200InterParams
+ * n_w16 / n_w8; an emitter simply keeps three lists): the host emitter splits larger
  * prediction units (translational MC is separable per sample, and 16x16 is the reference's own DMVR/BDOF
  * sub-block, vvc_mvs.c num_sb_x/y), and emits affine CUs as 4x4 luma + 8x8-luma-footprint chroma records.
  * ---------------------------------------------------------------------------------------------- */
@@ -166,7 +167,9 @@ typedef struct VVCB200PredBlock {
 typedef struct VVCB200InterParams {
     int32_t  bit_depth;
     int32_t  log2_denom[2];         /* luma, chroma                                            */
-    int32_t  reserved;
+    int32_t  n_w16, n_w8;           /* the batch is ordered by block width: n_w16 blocks of width 16, then n_w8 of
+                                       width 8, then the width-4 ones (lets a warp own equal-width blocks)      */
+    int32_t  reserved[3];
     int16_t  weight[2][3][16];      /* [list][c_idx][ref_idx]                                  */
     int16_t  offset[2][3][16];
     uint8_t  ref_slot[2][16];       /* index into the `refs` array of (list, ref_idx)          */

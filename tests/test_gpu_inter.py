@@ -16,8 +16,19 @@ def oracle_inter(dst, pic, lut=None):
         portapi.inter_batch(dst, pic["refs"], pic["blocks"], pic["params"], lut)
 
 
+def _params_for(pic):
+    """InterParams with the width-class counts of exactly the blocks being submitted (subsets stay width-ordered)."""
+    import ctypes as C
+    p = abi.InterParams.from_buffer_copy(bytes(pic["params"]))
+    b = pic["blocks"]
+    assert np.all(np.diff(b["w"].astype(np.int32)) <= 0)
+    p.n_w16, p.n_w8 = int(np.sum(b["w"] == 16)), int(np.sum(b["w"] == 8))
+    return p
+
+
 def gpu_inter(pic, base, lut=None, tmp14=False):
     import torch
+    pic = dict(pic, params=_params_for(pic))
     dst = util.to_device_planes(base, torch)
     refs = [util.to_device_planes(r, torch) for r in pic["refs"]]
     blocks = torch.from_numpy(pic["blocks"].view(np.uint8).reshape(-1)).cuda()
