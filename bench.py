@@ -57,7 +57,7 @@ def measured_peaks():
 def make_picture(seed, width, height):
     """Synthetic parsed inter picture (SURVEY.md §8d config 2/3 shape).  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v2_%dx%d_%d.pkl" % (width, height, seed)
+    cache = "/tmp/vvcb200_bench_v3_%dx%d_%d.pkl" % (width, height, seed)
     if os.path.exists(cache):
         try:
             with open(cache, "rb") as f:

@@ -26,7 +26,7 @@ assert TB_DTYPE.itemsize == 24
 class ResidualParams(C.Structure):
     _fields_ = [
         ("bit_depth", C.c_int32), ("log2_transform_range", C.c_int32),
-        ("joint_c_sign", C.c_int32), ("reserved", C.c_int32),
+        ("joint_c_sign", C.c_int32), ("reserved", C.c_int32), ("n_class", C.c_int32 * 4),
         ("scaling_matrix_rec", (C.c_uint8 * 64) * 28),
         ("scaling_matrix_dc_rec", C.c_uint8 * 14),
         ("pad", C.c_uint8 * 2),
@@ -49,6 +49,25 @@ def residual_params(bit_depth=10, joint_c_sign=1, scaling=None, dc=None):
     C.memmove(p.scaling_matrix_rec, m.ctypes.data, 28 * 64)
     C.memmove(p.scaling_matrix_dc_rec, d.ctypes.data, 14)
     return p
+
+
+def residual_class(tbs):
+    """Vectorised vvcb200_residual_class() (include/vvc_b200.h) for a TB_DTYPE array."""
+    fast = ((tbs["flags"] & (TB_TS | TB_BDPCM)) == 0) & (tbs["lfnst"] == 0) & (tbs["log2_w"] >= 1) & (tbs["log2_h"] >= 1)
+    m = np.maximum(tbs["log2_w"], tbs["log2_h"]).astype(np.int32)
+    cls = np.where(m >= 5, 0, np.where(m == 4, 1, np.where(m == 3, 2, 3)))
+    return np.where(fast, cls, 4).astype(np.int32)
+
+
+def order_tbs_by_class(tbs, params, extra=()):
+    """Sort a TB batch into class order (ties: larger area first) and record the class sizes in `params`.
+    `extra` arrays (one entry per TB) are permuted alongside.  Returns (tbs, *extra)."""
+    cls = residual_class(tbs)
+    area = tbs["log2_w"].astype(np.int32) + tbs["log2_h"]
+    order = np.lexsort((-area, cls))
+    for c in range(4):
+        params.n_class[c] = int(np.sum(cls == c))
+    return (np.ascontiguousarray(tbs[order]),) + tuple(np.ascontiguousarray(e[order]) for e in extra)
 
 
 def host_planes(arrays):

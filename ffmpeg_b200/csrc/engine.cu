@@ -315,6 +315,24 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
     }
     if (n == 0)
         return 0;
+    {   // the batch must come in class order (see vvcb200_residual_class)
+        int bound[5], acc = 0;
+        for (int k = 0; k < 4; k++) {
+            acc += params->n_class[k];
+            bound[k] = acc;
+        }
+        bound[4] = n;
+        for (int i = 0, k = 0; i < n; i++) {
+            while (k < 4 && i >= bound[k])
+                k++;
+            if (vvcb200_residual_class(&tbs[i]) != k) {
+                set_error("vvcb200_pic_residual: block %d is of class %d where the class order (n_class %d %d %d %d) wants %d",
+                          i, vvcb200_residual_class(&tbs[i]), params->n_class[0], params->n_class[1], params->n_class[2],
+                          params->n_class[3], k);
+                return VVCB200_ERR_ARG;
+            }
+        }
+    }
     DeviceGuard g(c->device);
     if (int r = upload(c, c->levels, levels, n_levels * sizeof(int16_t)))
         return r;

@@ -39,6 +39,7 @@ struct ResidualArgs {
     const int16_t *levels;
     const VVCB200TransformBlock *tbs;
     int n;
+    int n_class[4];                          // blocks per lane-group class (32/16/8/4 lanes per block); the rest is generic
     int bd, range, c_sign;
     int to_residual;
 };
@@ -267,233 +268,307 @@ __device__ __forceinline__ Dequant make_dequant(const VVCB200TransformBlock &d, 
     return q;
 }
 
+// Everything the epilogue of one block needs (add_residual / joint CbCr / LMCS chroma scale, vvc_intra.c:166-186,451-477)
+struct Epilogue {
+    uint16_t *dst, *dst2;       // first sample of the block in its plane / in the joint plane (pixels or int16 residual)
+    int stride, stride2;
+    int bd, c_sign, jshift, lscale;
+    bool joint, lmcs, to_residual;
+
+    __device__ __forceinline__ void one(int y, int x, int r) const
+    {
+        int r2 = joint ? (r * c_sign) >> jshift : 0;
+        if (lmcs) {
+            r = lmcs_scale_residual(r, lscale, bd);
+            r2 = lmcs_scale_residual(r2, lscale, bd);
+        }
+        if (to_residual) {
+            reinterpret_cast<int16_t *>(dst)[y * stride + x] = (int16_t)clip_intp2(r, 15);
+            if (joint)
+                reinterpret_cast<int16_t *>(dst2)[y * stride2 + x] = (int16_t)clip_intp2(r2, 15);
+        } else {
+            dst[y * stride + x] = (uint16_t)clip_pixel(dst[y * stride + x] + r, bd);
+            if (joint)
+                dst2[y * stride2 + x] = (uint16_t)clip_pixel(dst2[y * stride2 + x] + r2, bd);
+        }
+    }
+    // two horizontally adjacent samples: one 32-bit read-modify-write (x even, planes 4-byte aligned)
+    __device__ __forceinline__ void two(int y, int x, int r0, int r1) const
+    {
+        if (joint || lmcs || to_residual) {
+            one(y, x, r0);
+            one(y, x + 1, r1);
+            return;
+        }
+        uint32_t *p = reinterpret_cast<uint32_t *>(dst + y * stride + x);
+        const uint32_t v = *p;
+        *p = (uint32_t)clip_pixel((int)(v & 0xffff) + r0, bd) | ((uint32_t)clip_pixel((int)(v >> 16) + r1, bd) << 16);
+    }
+};
+
+__device__ __forceinline__ Epilogue make_epilogue(const ResidualArgs &a, const VVCB200TransformBlock &d)
+{
+    Epilogue e;
+    const PlanesView &pv = a.to_residual ? a.res : a.dst;
+    const int other = d.c_idx ? 3 - d.c_idx : 0;
+    e.stride = pv.stride[d.c_idx];
+    e.stride2 = pv.stride[other];
+    e.dst = pv.p[d.c_idx] + (size_t)d.y0 * e.stride + d.x0;
+    e.dst2 = pv.p[other] + (size_t)d.y0 * e.stride2 + d.x0;
+    e.bd = a.bd;
+    e.c_sign = a.c_sign;
+    e.jshift = (d.flags & VVCB200_TB_JOINT_SHIFT) ? 1 : 0;
+    e.lscale = d.lmcs_scale;
+    e.joint = (d.flags & VVCB200_TB_JOINT) && d.c_idx;
+    e.lmcs = d.flags & VVCB200_TB_LMCS_SCALE;
+    e.to_residual = a.to_residual;
+    return e;
+}
+
+// ---- fast classes: `lpt` lanes per block (32, 16, 8 or 4), all blocks of the warp transformed side by side ---------
+// li = lane inside the block's lane group; inT / fmid = this block's staging areas.  Called by all lanes of the warp.
+__device__ __forceinline__ void fast_block(const ResidualArgs &a, const ScalingLists &sl, const VVCB200TransformBlock &d,
+                                           bool active, int li, int lpt, int log2lpt, int16_t *inT, int16_t *fmid,
+                                           const uint32_t *smat)
+{
+    const int w = 1 << d.log2_w, h = 1 << d.log2_h;
+    const int nzw = d.nzw, nzh = d.nzh;
+    const int16_t *lv = a.levels + d.coeff_off;
+    const Epilogue ep = make_epilogue(a, d);
+    const int sh1 = 5 + a.range - a.bd;
+    const bool dconly = d.trh == VVCB200_DCT2 && d.trv == VVCB200_DCT2 && nzw == 1 && nzh == 1 && w == h;
+
+    if (active && !a.to_residual && li < h)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(ep.dst + li * ep.stride));
+    // levels: coalesced fetch into the (still free) middle buffer
+    if (active)
+        for (int i = li; i < nzw * nzh; i += lpt)
+            fmid[i] = lv[i];
+    __syncwarp();
+    if (active && dconly) {
+        // DC-only square DCT-II block (vvcdsp.c:101-108): one value for the whole block
+        const Dequant q = make_dequant(d, false, a.bd, a.range);
+        const int c = fmid[0] ? q.apply(fmid[0], 0, 0, sl) : 0;
+        const int t = (c * 64 + 64) >> 7;
+        const int dc = (t * 64 + (1 << (sh1 - 1))) >> sh1;
+        for (int i = li; i < (w * h) >> 1; i += lpt) {
+            const int y = i >> (d.log2_w - 1), x = (i & ((w >> 1) - 1)) << 1;
+            ep.two(y, x, dc, dc);
+        }
+    }
+    // dequant + transpose: lane x owns column x of the non-zero box
+    if (active && !dconly && li < nzw) {
+        const Dequant q = make_dequant(d, false, a.bd, a.range);
+        for (int y = 0; y < nzh; y++) {
+            const int c = fmid[y * nzw + li];
+            inT[li * kPairStride + y] = (int16_t)(c ? q.apply(c, li, y, sl) : 0);
+        }
+        if (nzh & 1)
+            inT[li * kPairStride + nzh] = 0;
+    }
+    __syncwarp();
+    if (active && !dconly) {
+        // column pass: lane = g * cw + x owns column x and outputs [g * per_lane, (g + 1) * per_lane)
+        const int log2cw = nzw <= 1 ? 0 : 32 - __clz(nzw - 1);             // nzw rounded up to a power of two
+        const int lg = min(log2lpt - log2cw, d.log2_h - 1);                // log2(lane groups per column)
+        const int per_lane = h >> lg;                                      // even
+        const int x = li & ((1 << log2cw) - 1), g = li >> log2cw;
+        const uint32_t *mat = tx_packed(smat, d.trv, d.log2_h);
+        const int n_kp = (nzh + 1) >> 1, half = h >> 1;
+        if (x < nzw && g < (1 << lg)) {
+            switch (per_lane) {                    // at most 16 accumulators live at a time (registers = occupancy)
+            case 2:  fast_column_pass<2>(inT, fmid, mat, half, x, g * 2, nzw, n_kp, a.range); break;
+            case 4:  fast_column_pass<4>(inT, fmid, mat, half, x, g * 4, nzw, n_kp, a.range); break;
+            case 8:  fast_column_pass<8>(inT, fmid, mat, half, x, g * 8, nzw, n_kp, a.range); break;
+            default:
+                for (int j0 = g * per_lane; j0 < (g + 1) * per_lane; j0 += 16)
+                    fast_column_pass<16>(inT, fmid, mat, half, x, j0, nzw, n_kp, a.range);
+                break;
+            }
+        }
+    }
+    __syncwarp();
+    if (active && !dconly) {
+        // row pass + epilogue: lane = g * rows + y owns row y and outputs [g * per_lane, (g + 1) * per_lane)
+        const int log2rows = min((int)d.log2_h, log2lpt);
+        const int lg = min(log2lpt - log2rows, d.log2_w - 1);
+        const int per_lane = w >> lg;
+        const int yl = li & ((1 << log2rows) - 1), g = li >> log2rows;
+        const uint32_t *mat = tx_packed(smat, d.trh, d.log2_w);
+        const int n_kp = (nzw + 1) >> 1, half = w >> 1;
+        auto emit2 = [&](int y, int x, int r0, int r1) { ep.two(y, x, r0, r1); };
+        if (g < (1 << lg)) {
+            for (int y = yl; y < h; y += lpt) {
+                switch (per_lane) {
+                case 2:  fast_row_pass<2>(fmid, mat, half, y, g * 2, n_kp, sh1, emit2); break;
+                case 4:  fast_row_pass<4>(fmid, mat, half, y, g * 4, n_kp, sh1, emit2); break;
+                case 8:  fast_row_pass<8>(fmid, mat, half, y, g * 8, n_kp, sh1, emit2); break;
+                default:
+                    for (int x0 = g * per_lane; x0 < (g + 1) * per_lane; x0 += 16)
+                        fast_row_pass<16>(fmid, mat, half, y, x0, n_kp, sh1, emit2);
+                    break;
+                }
+            }
+        }
+    }
+}
+
+// ---- generic class: TS, BDPCM, LFNST, 1-D blocks — one warp per block ---------------------------------------------
+__device__ __forceinline__ void generic_block(const ResidualArgs &a, const ScalingLists &sl, const VVCB200TransformBlock &d,
+                                              int lane, int16_t *in, int16_t *mid, const uint32_t *smat)
+{
+    const int w = 1 << d.log2_w, h = 1 << d.log2_h;
+    const bool ts = d.flags & VVCB200_TB_TS;
+    const int16_t *lv = a.levels + d.coeff_off;
+    int nzw = d.nzw, nzh = d.nzh, in_stride = d.nzw;
+    const Dequant q = make_dequant(d, ts, a.bd, a.range);
+    const Epilogue ep = make_epilogue(a, d);
+    auto emit = [&](int y, int x, int r) { ep.one(y, x, r); };
+
+    // ---- levels into shared memory (+ BDPCM prefix sums on the raw levels)
+    if (d.flags & VVCB200_TB_BDPCM) {
+        in_stride = w;
+        for (int i = lane; i < w * h; i += 32) {
+            const int y = i >> d.log2_w, x = i & (w - 1);
+            in[i] = (x < nzw && y < nzh) ? lv[y * nzw + x] : (int16_t)0;
+        }
+        __syncwarp();
+        if (d.flags & VVCB200_TB_BDPCM_VERT) {
+            for (int x = lane; x < w; x += 32) {
+                int run = in[x];
+                for (int y = 1; y < h; y++) {
+                    run = clip_intp2(run + in[y * w + x], a.range);
+                    in[y * w + x] = (int16_t)run;
+                }
+            }
+            nzh = h;
+        } else {
+            for (int y = lane; y < h; y += 32) {
+                int run = in[y * w];
+                for (int x = 1; x < w; x++) {
+                    run = clip_intp2(run + in[y * w + x], a.range);
+                    in[y * w + x] = (int16_t)run;
+                }
+            }
+            nzw = w;
+        }
+        __syncwarp();
+    } else {
+        for (int i = lane; i < nzw * nzh; i += 32)
+            in[i] = lv[i];
+        __syncwarp();
+    }
+    // ---- dequant (vvc_intra.c:277-417)
+    for (int i = lane; i < nzw * nzh; i += 32) {
+        const int y = i / nzw, x = i - y * nzw;
+        const int c = in[y * in_stride + x];
+        if (c)
+            in[y * in_stride + x] = (int16_t)q.apply(c, x, y, sl);
+    }
+    __syncwarp();
+    // ---- inverse LFNST (vvc_intra.c:65-127, vvc_itx_1d.c:708-721)
+    if (d.lfnst && !ts) {
+        const int idx = (d.lfnst & 3) - 1, set = (d.lfnst >> 2) & 3;
+        const bool transpose = (d.lfnst >> 4) & 1;
+        const bool big = w >= 8 && h >= 8;
+        const int n_out = big ? 48 : 16, size = big ? 8 : 4;
+        const int nz = ((w == 8 && h == 8) || (w == 4 && h == 4)) ? 8 : 16;
+        const int8_t *m = big ? VVC_LFNST_8X8 + (set * 2 + idx) * 16 * 48 : VVC_LFNST_4X4 + (set * 2 + idx) * 16 * 16;
+        if (lane < 16) {
+            const int p = VVC_DIAG_SCAN_4X4[lane];
+            const int x = p & 3, y = p >> 2;
+            mid[lane] = (lane < nz && x < nzw && y < nzh) ? in[y * in_stride + x] : (int16_t)0;
+        }
+        __syncwarp();
+        int out[2];
+        for (int r = 0; r < 2; r++) {
+            const int i = lane + 32 * r;             // raster position in the size x size region
+            int y = i / size, x = i - y * size;
+            out[r] = 0;
+            if (i < size * size) {
+                if (transpose) { const int sw = x; x = y; y = sw; }
+                const int j = size == 4 ? y * 4 + x : (y < 4 ? y * 8 + x : (x < 4 ? 32 + (y - 4) * 4 + x : -1));
+                if (j >= 0) {
+                    int acc = 0;
+                    for (int k = 0; k < nz; k++)
+                        acc += mid[k] * m[k * n_out + j];
+                    out[r] = clip_intp2((acc + 64) >> 7, a.range);
+                }
+            }
+        }
+        __syncwarp();
+        for (int r = 0; r < 2; r++)
+            if (lane + 32 * r < size * size)
+                in[lane + 32 * r] = (int16_t)out[r];
+        nzw = nzh = in_stride = size;
+        __syncwarp();
+    }
+    // ---- inverse transform + epilogue
+    if (ts) {
+        for (int i = lane; i < w * h; i += 32) {
+            const int y = i >> d.log2_w, x = i & (w - 1);
+            emit(y, x, (x < nzw && y < nzh) ? (int)in[y * in_stride + x] : 0);
+        }
+    } else {
+        inverse_transform<int16_t>(in, in_stride, mid, smat, d.trh, d.trv, d.log2_w, d.log2_h, nzw, nzh,
+                                   a.range, a.bd, lane, emit);
+    }
+}
+
+// Does block d take the dp2a path, and with how many lanes?  Returns the class (0: 32 lanes ... 3: 4 lanes, 4: generic).
+// The host orders the batch by this class (vvcb200_residual_class, exported for emitters).
+__host__ __device__ inline int residual_class(const VVCB200TransformBlock &d)
+{
+    const bool fast = !(d.flags & (VVCB200_TB_TS | VVCB200_TB_BDPCM)) && !d.lfnst && d.log2_w >= 1 && d.log2_h >= 1;
+    if (!fast)
+        return 4;
+    const int m = d.log2_w > d.log2_h ? d.log2_w : d.log2_h;
+    return m >= 5 ? 0 : m == 4 ? 1 : m == 3 ? 2 : 3;
+}
+
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 7)      // 7 CTAs/SM is also the shared-memory limit (32 KB each)
 residual_kernel(const ResidualArgs a, const ScalingLists sl)
 {
     extern __shared__ __align__(16) uint8_t smem_raw[];
     uint32_t *smat = reinterpret_cast<uint32_t *>(smem_raw);
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    int16_t *in  = reinterpret_cast<int16_t *>(smem_raw + kMatPad) + warp * kWarpElems;
-    int16_t *mid = in + kInElems;                 // generic path layout
-    int16_t *inT = in, *fmid = in + kFastIn;      // fast path layout (same memory)
+    int16_t *buf = reinterpret_cast<int16_t *>(smem_raw + kMatPad) + warp * kWarpElems;
 
     load_matrices(smat);
     __syncthreads();
 
-    // The list is sorted by block area (largest first).  CTA b takes blocks b, b + grid, b + 2*grid, ... so
-    // every CTA gets the same size profile (no tail of CTAs stuck with the 64x64 blocks).
-    const int t_step = kWarpsPerCta * gridDim.x;
-    int t = blockIdx.x + warp * gridDim.x;
-    VVCB200TransformBlock d_next = {};
-    if (t < a.n)
-        d_next = a.tbs[t];
-    for (; t < a.n; t += t_step) {
-        const VVCB200TransformBlock d = d_next;
-        const int w = 1 << d.log2_w, h = 1 << d.log2_h;
-        const bool ts = d.flags & VVCB200_TB_TS;
-        const int16_t *lv = a.levels + d.coeff_off;
-        int nzw = d.nzw, nzh = d.nzh, in_stride = d.nzw;
-        const Dequant q = make_dequant(d, ts, a.bd, a.range);
-        // software pipeline: fetch the next descriptor and pull its levels and this block's destination rows
-        // towards the SM while this block is being transformed
-        if (t + t_step < a.n) {
-            d_next = a.tbs[t + t_step];
-            if (lane == 0)
-                asm volatile("prefetch.global.L2 [%0];" ::"l"(a.levels + d_next.coeff_off));
+    // Warp -> (class, first block).  Classes come in batch order: 32-, 16-, 8-, 4-lane blocks, then the generic ones;
+    // the heavy 32-lane blocks are scheduled first, the light ones fill the tail.
+    const int wi = blockIdx.x * kWarpsPerCta + warp;
+    int cls = 0, first = 0, base_w = 0, base_b = 0;
+    bool found = false;
+#pragma unroll
+    for (int c = 0; c < 4; c++) {
+        const int per_warp = 1 << c, warps = (a.n_class[c] + per_warp - 1) >> c;
+        if (!found && wi < base_w + warps) {
+            found = true;
+            cls = c;
+            first = base_b + ((wi - base_w) << c);
         }
-        if (!a.to_residual && lane < h)
-            asm volatile("prefetch.global.L1 [%0];" ::"l"(a.dst.p[d.c_idx] + (size_t)(d.y0 + lane) * a.dst.stride[d.c_idx] + d.x0));
-
-        // ---- epilogue shared by both paths (add_residual / joint CbCr / LMCS chroma scale, vvc_intra.c:166-186,451-477)
-        const int other = 3 - d.c_idx;
-        const bool joint = (d.flags & VVCB200_TB_JOINT) && d.c_idx;
-        const int jshift = (d.flags & VVCB200_TB_JOINT_SHIFT) ? 1 : 0;
-        const bool lmcs = d.flags & VVCB200_TB_LMCS_SCALE;
-        const int lscale = d.lmcs_scale;
-        auto emit = [&](int y, int x, int r) {
-            int r2 = joint ? (r * a.c_sign) >> jshift : 0;
-            if (lmcs) {
-                r = lmcs_scale_residual(r, lscale, a.bd);
-                r2 = lmcs_scale_residual(r2, lscale, a.bd);
-            }
-            if (a.to_residual) {
-                int16_t *p = reinterpret_cast<int16_t *>(a.res.p[d.c_idx]) + (size_t)(d.y0 + y) * a.res.stride[d.c_idx] + d.x0 + x;
-                *p = (int16_t)clip_intp2(r, 15);
-                if (joint) {
-                    int16_t *p2 = reinterpret_cast<int16_t *>(a.res.p[other]) + (size_t)(d.y0 + y) * a.res.stride[other] + d.x0 + x;
-                    *p2 = (int16_t)clip_intp2(r2, 15);
-                }
-            } else {
-                uint16_t *p = a.dst.p[d.c_idx] + (size_t)(d.y0 + y) * a.dst.stride[d.c_idx] + d.x0 + x;
-                *p = (uint16_t)clip_pixel(*p + r, a.bd);
-                if (joint) {
-                    uint16_t *p2 = a.dst.p[other] + (size_t)(d.y0 + y) * a.dst.stride[other] + d.x0 + x;
-                    *p2 = (uint16_t)clip_pixel(*p2 + r2, a.bd);
-                }
-            }
-        };
-        // two horizontally adjacent samples at once: 32-bit read-modify-write (x is even, planes are 4-byte aligned)
-        auto emit2 = [&](int y, int x, int r0, int r1) {
-            if (joint || lmcs || a.to_residual) {
-                emit(y, x, r0);
-                emit(y, x + 1, r1);
-                return;
-            }
-            uint32_t *p = reinterpret_cast<uint32_t *>(a.dst.p[d.c_idx] + (size_t)(d.y0 + y) * a.dst.stride[d.c_idx] + d.x0 + x);
-            const uint32_t v = *p;
-            *p = (uint32_t)clip_pixel((int)(v & 0xffff) + r0, a.bd) | ((uint32_t)clip_pixel((int)(v >> 16) + r1, a.bd) << 16);
-        };
-
-        __syncwarp();
-        const bool dconly = d.trh == VVCB200_DCT2 && d.trv == VVCB200_DCT2 && nzw == 1 && nzh == 1 && w == h;
-        if (!ts && !d.lfnst && w > 1 && h > 1 && !dconly && !(d.flags & VVCB200_TB_BDPCM)) {
-            // ================= fast path: 2-D transform with dp2a register tiles =================
-            // levels -> dequant -> inT[x][k] (transposed so that pairs along k are one 32-bit word)
-            if (lane < nzw) {
-                for (int y = 0; y < nzh; y++) {
-                    const int c = lv[y * nzw + lane];
-                    inT[lane * kPairStride + y] = (int16_t)(c ? q.apply(c, lane, y, sl) : 0);
-                }
-                if (nzh & 1)
-                    inT[lane * kPairStride + nzh] = 0;
-            }
-            __syncwarp();
-            {   // column pass: lane = g * cw + x owns column x and the outputs [g * per_lane, (g + 1) * per_lane)
-                const int cw = nzw <= 1 ? 1 : 1 << (32 - __clz(nzw - 1));      // nzw rounded up to a power of two
-                const int groups = min(32 / cw, h >> 1);
-                const int per_lane = h / groups;                                // even
-                const int x = lane & (cw - 1), g = lane / cw;
-                const uint32_t *mat = tx_packed(smat, d.trv, d.log2_h);
-                const int n_kp = (nzh + 1) >> 1, half = h >> 1;
-                if (x < nzw && g < groups) {
-                    // at most 16 accumulators live at a time (register budget = occupancy)
-                    switch (per_lane) {
-                    case 2:  fast_column_pass<2>(inT, fmid, mat, half, x, g * 2, nzw, n_kp, a.range); break;
-                    case 4:  fast_column_pass<4>(inT, fmid, mat, half, x, g * 4, nzw, n_kp, a.range); break;
-                    case 8:  fast_column_pass<8>(inT, fmid, mat, half, x, g * 8, nzw, n_kp, a.range); break;
-                    default:
-                        for (int j0 = g * per_lane; j0 < (g + 1) * per_lane; j0 += 16)
-                            fast_column_pass<16>(inT, fmid, mat, half, x, j0, nzw, n_kp, a.range);
-                        break;
-                    }
-                }
-            }
-            __syncwarp();
-            {   // row pass + epilogue: lane = g * rows + y owns row y and the outputs [g * per_lane, (g + 1) * per_lane)
-                const int rows = min(h, 32);
-                const int groups = min(32 / rows, w >> 1);
-                const int per_lane = w / groups;
-                const int yl = lane & (rows - 1), g = lane / rows;
-                const uint32_t *mat = tx_packed(smat, d.trh, d.log2_w);
-                const int n_kp = (nzw + 1) >> 1, half = w >> 1;
-                const int sh1 = 5 + a.range - a.bd;
-                if (g < groups) {
-                    for (int y = yl; y < h; y += 32) {
-                        switch (per_lane) {
-                        case 2:  fast_row_pass<2>(fmid, mat, half, y, g * 2, n_kp, sh1, emit2); break;
-                        case 4:  fast_row_pass<4>(fmid, mat, half, y, g * 4, n_kp, sh1, emit2); break;
-                        case 8:  fast_row_pass<8>(fmid, mat, half, y, g * 8, n_kp, sh1, emit2); break;
-                        default:
-                            for (int x0 = g * per_lane; x0 < (g + 1) * per_lane; x0 += 16)
-                                fast_row_pass<16>(fmid, mat, half, y, x0, n_kp, sh1, emit2);
-                            break;
-                        }
-                    }
-                }
-            }
-            continue;
-        }
-
-        // ================= generic path: TS, BDPCM, LFNST, 1-D blocks, DC-only =================
-        // ---- levels into shared memory (+ BDPCM prefix sums on the raw levels)
-        if (d.flags & VVCB200_TB_BDPCM) {
-            in_stride = w;
-            for (int i = lane; i < w * h; i += 32) {
-                const int y = i >> d.log2_w, x = i & (w - 1);
-                in[i] = (x < nzw && y < nzh) ? lv[y * nzw + x] : (int16_t)0;
-            }
-            __syncwarp();
-            if (d.flags & VVCB200_TB_BDPCM_VERT) {
-                for (int x = lane; x < w; x += 32) {
-                    int run = in[x];
-                    for (int y = 1; y < h; y++) {
-                        run = clip_intp2(run + in[y * w + x], a.range);
-                        in[y * w + x] = (int16_t)run;
-                    }
-                }
-                nzh = h;
-            } else {
-                for (int y = lane; y < h; y += 32) {
-                    int run = in[y * w];
-                    for (int x = 1; x < w; x++) {
-                        run = clip_intp2(run + in[y * w + x], a.range);
-                        in[y * w + x] = (int16_t)run;
-                    }
-                }
-                nzw = w;
-            }
-            __syncwarp();
-        } else {
-            for (int i = lane; i < nzw * nzh; i += 32)
-                in[i] = lv[i];
-            __syncwarp();
-        }
-        // ---- dequant (vvc_intra.c:277-417)
-        for (int i = lane; i < nzw * nzh; i += 32) {
-            const int y = i / nzw, x = i - y * nzw;
-            const int c = in[y * in_stride + x];
-            if (c)
-                in[y * in_stride + x] = (int16_t)q.apply(c, x, y, sl);
-        }
-        __syncwarp();
-        // ---- inverse LFNST (vvc_intra.c:65-127, vvc_itx_1d.c:708-721)
-        if (d.lfnst && !ts) {
-            const int idx = (d.lfnst & 3) - 1, set = (d.lfnst >> 2) & 3;
-            const bool transpose = (d.lfnst >> 4) & 1;
-            const bool big = w >= 8 && h >= 8;
-            const int n_out = big ? 48 : 16, size = big ? 8 : 4;
-            const int nz = ((w == 8 && h == 8) || (w == 4 && h == 4)) ? 8 : 16;
-            const int8_t *m = big ? VVC_LFNST_8X8 + (set * 2 + idx) * 16 * 48 : VVC_LFNST_4X4 + (set * 2 + idx) * 16 * 16;
-            if (lane < 16) {
-                const int p = VVC_DIAG_SCAN_4X4[lane];
-                const int x = p & 3, y = p >> 2;
-                mid[lane] = (lane < nz && x < nzw && y < nzh) ? in[y * in_stride + x] : (int16_t)0;
-            }
-            __syncwarp();
-            int out[2];
-            for (int r = 0; r < 2; r++) {
-                const int i = lane + 32 * r;             // raster position in the size x size region
-                int y = i / size, x = i - y * size;
-                out[r] = 0;
-                if (i < size * size) {
-                    if (transpose) { const int sw = x; x = y; y = sw; }
-                    const int j = size == 4 ? y * 4 + x : (y < 4 ? y * 8 + x : (x < 4 ? 32 + (y - 4) * 4 + x : -1));
-                    if (j >= 0) {
-                        int acc = 0;
-                        for (int k = 0; k < nz; k++)
-                            acc += mid[k] * m[k * n_out + j];
-                        out[r] = clip_intp2((acc + 64) >> 7, a.range);
-                    }
-                }
-            }
-            __syncwarp();
-            for (int r = 0; r < 2; r++)
-                if (lane + 32 * r < size * size)
-                    in[lane + 32 * r] = (int16_t)out[r];
-            nzw = nzh = in_stride = size;
-            __syncwarp();
-        }
-        // ---- inverse transform + epilogue
-        if (ts) {
-            for (int i = lane; i < w * h; i += 32) {
-                const int y = i >> d.log2_w, x = i & (w - 1);
-                emit(y, x, (x < nzw && y < nzh) ? (int)in[y * in_stride + x] : 0);
-            }
-        } else {
-            inverse_transform<int16_t>(in, in_stride, mid, smat, d.trh, d.trv, d.log2_w, d.log2_h, nzw, nzh,
-                                       a.range, a.bd, lane, emit);
+        if (!found) {
+            base_w += warps;
+            base_b += a.n_class[c];
         }
     }
+    if (found) {
+        const int last = base_b + a.n_class[cls];
+        const int log2lpt = 5 - cls, lpt = 32 >> cls;
+        const int g = lane >> log2lpt, li = lane & (lpt - 1);
+        const bool active = first + g < last;
+        const VVCB200TransformBlock d = a.tbs[active ? first + g : first];
+        // per-block staging: transposed input (lpt columns) + middle block (lpt rows; 64 for the 32-lane class)
+        const int in_sz = lpt * kPairStride, region = cls == 0 ? kWarpElems : 2 * in_sz;
+        fast_block(a, sl, d, active, li, lpt, log2lpt, buf + g * region, buf + g * region + in_sz, smat);
+        return;
+    }
+    const int t = base_b + (wi - base_w);
+    if (t < a.n)
+        generic_block(a, sl, a.tbs[t], lane, buf, buf + kInElems, smat);
 }
 
 // ---- Level A: itx.itx[...] on int32 blocks in place, add_residual on int32 blocks --------------------
@@ -606,14 +681,30 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
     memset(sl.dc, 16, sizeof(sl.dc));
     memcpy(sl.dc, params->scaling_matrix_dc_rec, 14);
 
+    int rest = n, warps = 0;
+    for (int c = 0; c < 4; c++) {
+        a.n_class[c] = params->n_class[c];
+        if (a.n_class[c] < 0 || a.n_class[c] > rest) {
+            set_error("vvcb200_residual_batch: n_class[%d] = %d does not fit the batch of %d blocks", c, a.n_class[c], n);
+            return VVCB200_ERR_ARG;
+        }
+        rest -= a.n_class[c];
+        warps += (a.n_class[c] + (1 << c) - 1) >> c;
+    }
+    warps += rest;                              // generic blocks: one warp each
     const size_t smem = kMatPad + kWarpsPerCta * kWarpElems * sizeof(int16_t);
     static bool ready[64];
     if (int r = opt_in_smem(residual_kernel, smem, ready))
         return r;
-    const int grid = (n + kChunk - 1) / kChunk;
+    const int grid = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
     residual_kernel<<<grid, kWarpsPerCta * 32, smem, (cudaStream_t)stream>>>(a, sl);
     VVC_LAUNCH_CHECK();
     return 0;
+}
+
+extern "C" int vvcb200_residual_class(const VVCB200TransformBlock *tb)
+{
+    return tb ? residual_class(*tb) : VVCB200_ERR_ARG;
 }
 
 extern "C" int vvcb200_dsp_itx_batch(int32_t *d_coeffs, const uint32_t *d_block_off,

@@ -92,6 +92,117 @@ __global__ void __launch_bounds__(256) sao_kernel(const SaoArgs a)
         *d = (uint16_t)v0;
 }
 
+// Vectorised variant: one thread per 8 horizontally adjacent samples (128-bit accesses).  Threads whose samples
+// touch a picture border or a no-filter CTB side take the per-sample routine above; everything else runs the
+// straight-line code below.  Needs 16-byte aligned planes and strides.
+template <int EO>
+__device__ __forceinline__ void sao_edge8(uint32_t (&out)[4], const uint16_t *src, int stride, int x, int y,
+                                          const int16_t *ov, int bd)
+{
+    // neighbour a = (x + AX, y + AY), b = (x - AX, y - AY)
+    constexpr int AX = EO == 1 ? 0 : (EO == 3 ? 1 : -1), AY = EO == 0 ? 0 : -1;
+    const uint16_t *rc = src + (size_t)y * stride + x;
+    const uint16_t *ra = rc + AY * stride, *rb = rc - AY * stride;
+    uint16_t c[8], a[8], b[8];
+    *reinterpret_cast<uint4 *>(c) = *reinterpret_cast<const uint4 *>(rc);
+    if (AX == 0) {
+        *reinterpret_cast<uint4 *>(a) = *reinterpret_cast<const uint4 *>(ra);
+        *reinterpret_cast<uint4 *>(b) = *reinterpret_cast<const uint4 *>(rb);
+    } else {
+        uint16_t ta[8], tb[8];
+        if (AY == 0) {
+#pragma unroll
+            for (int j = 0; j < 8; j++) { ta[j] = c[j]; tb[j] = c[j]; }
+        } else {
+            *reinterpret_cast<uint4 *>(ta) = *reinterpret_cast<const uint4 *>(ra);
+            *reinterpret_cast<uint4 *>(tb) = *reinterpret_cast<const uint4 *>(rb);
+        }
+        // shift by one sample: a[j] = rowA[j + AX], b[j] = rowB[j - AX]
+        const uint16_t ea = AX < 0 ? ra[-1] : ra[8], eb = AX < 0 ? rb[8] : rb[-1];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int ja = j + AX, jb = j - AX;
+            a[j] = ja < 0 || ja > 7 ? ea : ta[ja];
+            b[j] = jb < 0 || jb > 7 ? eb : tb[jb];
+        }
+    }
+    const int o0 = ov[0], o1 = ov[1], o2 = ov[2], o3 = ov[3], o4 = ov[4];
+    const int pmax = (1 << bd) - 1;
+    int r[8];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const int s = c[j];
+        const int d = (s > a[j]) - (s < a[j]) + (s > b[j]) - (s < b[j]);
+        const int off = d == 0 ? o0 : d == -2 ? o1 : d == -1 ? o2 : d == 1 ? o3 : o4;
+        r[j] = min(max(s + off, 0), pmax);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; j++)
+        out[j] = (uint32_t)r[2 * j] | ((uint32_t)r[2 * j + 1] << 16);
+}
+
+__global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
+{
+    const int c = blockIdx.z;
+    const int w = a.src.w[c], h = a.src.h[c];
+    const int x = (blockIdx.x * blockDim.x + threadIdx.x) * 8;
+    const int y = blockIdx.y;
+    if (x >= w || y >= h)
+        return;
+    const int l2 = a.ctb_log2 - (c ? 1 : 0);
+    const int cx = x >> l2, cy = y >> l2;
+    const VVCB200SaoCtb *pp = a.ctbs + cy * a.ctb_width + cx;
+    const int type = pp->type_idx[c];
+    const uint16_t *src = a.src.p[c];
+    const int stride = a.src.stride[c];
+    uint16_t *d = a.dst.p[c] + (size_t)y * a.dst.stride[c] + x;
+    const int cx0 = cx << l2, cy0 = cy << l2;
+    const int cw = min(1 << l2, w - cx0), ch = min(1 << l2, h - cy0);
+    bool slow = x + 8 > w;
+    if (type == VVCB200_SAO_EDGE) {
+        // samples on a CTB side that is a picture border or must not be filtered across need the per-sample rules
+        const bool side = x == cx0 || x + 8 >= cx0 + cw || y == cy0 || y == cy0 + ch - 1;
+        const bool border = cx0 == 0 || cy0 == 0 || cx0 + cw == w || cy0 + ch == h;
+        slow = slow || (side && (border || pp->no_filter));
+    }
+    if (slow) {
+        const VVCB200SaoCtb p = *pp;
+        for (int j = 0; j < 8 && x + j < w; j++)
+            d[j] = (uint16_t)sao_sample(a, p, c, x + j, y, cx0, cy0, cw, ch);
+        return;
+    }
+    uint32_t out[4];
+    if (type == VVCB200_SAO_OFF) {
+        *reinterpret_cast<uint4 *>(d) = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
+        return;
+    }
+    const int16_t *ov = pp->offset_val[c];
+    if (type == VVCB200_SAO_BAND) {
+        uint16_t s[8];
+        *reinterpret_cast<uint4 *>(s) = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
+        const int pos = pp->band_position[c], sh = a.bd - 5, pmax = (1 << a.bd) - 1;
+        const int o1 = ov[1], o2 = ov[2], o3 = ov[3], o4 = ov[4];
+        int r[8];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const int k = ((s[j] >> sh) - pos) & 31;
+            const int off = k == 0 ? o1 : k == 1 ? o2 : k == 2 ? o3 : k == 3 ? o4 : 0;
+            r[j] = min(max(s[j] + off, 0), pmax);
+        }
+#pragma unroll
+        for (int j = 0; j < 4; j++)
+            out[j] = (uint32_t)r[2 * j] | ((uint32_t)r[2 * j + 1] << 16);
+    } else {
+        switch (pp->eo_class[c]) {
+        case 0:  sao_edge8<0>(out, src, stride, x, y, ov, a.bd); break;
+        case 1:  sao_edge8<1>(out, src, stride, x, y, ov, a.bd); break;
+        case 2:  sao_edge8<2>(out, src, stride, x, y, ov, a.bd); break;
+        default: sao_edge8<3>(out, src, stride, x, y, ov, a.bd); break;
+        }
+    }
+    *reinterpret_cast<uint4 *>(d) = make_uint4(out[0], out[1], out[2], out[3]);
+}
+
 __global__ void __launch_bounds__(256) lmcs_kernel(PlanesView pic, const uint16_t *lut, int mask)
 {
     __shared__ uint16_t s_lut[4096];
@@ -136,8 +247,17 @@ extern "C" int vvcb200_sao_picture(const VVCB200Planes *dst, const VVCB200Planes
     a.ctb_log2 = ctb_log2_size;
     a.ctb_width = (src->width[0] + (1 << ctb_log2_size) - 1) >> ctb_log2_size;
     a.bd = bit_depth;
-    dim3 grid((src->width[0] / 2 + 255) / 256, src->height[0], 3);
-    sao_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    bool aligned = true;
+    for (int c = 0; c < 3; c++)
+        aligned = aligned && !(((uintptr_t)a.src.p[c] | (uintptr_t)a.dst.p[c]) & 15) && !((a.src.stride[c] | a.dst.stride[c]) & 7);
+    if (aligned) {
+        dim3 grid((src->width[0] / 8 + 127) / 128, src->height[0], 3);
+        sao_kernel_v8<<<grid, 128, 0, (cudaStream_t)stream>>>(a);
+    } else {
+        // same arithmetic, scalar accesses: planes that do not meet the 16-byte alignment of the engine's own pictures
+        dim3 grid((src->width[0] / 2 + 255) / 256, src->height[0], 3);
+        sao_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    }
     VVC_LAUNCH_CHECK();
     return 0;
 }

@@ -164,12 +164,10 @@ def residual_picture(seed, width, height, coded_fraction=1.0, levels="realistic"
         lv_chunks.append(lv.reshape(-1))
         off += lv.size
     level_buf = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
-    if sort and n:
-        order = np.argsort(-(tbs["log2_w"].astype(np.int32) + tbs["log2_h"]), kind="stable")
-        tbs, intra_mode = tbs[order], intra_mode[order]
     sl = rng.integers(4, 65, (28, 64)).astype(np.uint8)
     dc = rng.integers(4, 65, 14).astype(np.uint8)
     params = abi.residual_params(10, 1 if rng.random() < 0.5 else -1, sl, dc)
+    tbs, intra_mode = abi.order_tbs_by_class(tbs, params, (intra_mode,))
     return dict(tbs=tbs, levels=level_buf, params=params, intra_mode=intra_mode, seed=seed, dims=dims)
 
 
@@ -437,8 +435,8 @@ def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, 
     # every residual TB of an inter picture belongs to an inter CU
     res["tbs"]["flags"] |= abi.TB_INTER
     res["tbs"]["flags"] &= ~np.uint16(abi.TB_BDPCM | abi.TB_BDPCM_VERT)
-    nolf = res["tbs"]["lfnst"] != 0
     res["tbs"]["lfnst"] = 0          # LFNST is intra-only; its TBs stay as plain DCT2 blocks
+    res["tbs"], res["intra_mode"] = abi.order_tbs_by_class(res["tbs"], res["params"], (res["intra_mode"],))
     db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
     lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
     out = dict(inter=inter, residual=res, deblock=db, lf=lf, dims=inter["dims"], ctb_log2=ctb_log2, seed=seed,

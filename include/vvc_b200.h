@@ -93,6 +93,8 @@ typedef struct VVCB200ResidualParams {
     int32_t  log2_transform_range;  /* 15 (sps->log2_transform_range; extended precision is not built)  */
     int32_t  joint_c_sign;          /* 1 - 2 * ph_joint_cbcr_sign_flag (vvc_intra.c:171)                */
     int32_t  reserved;
+    int32_t  n_class[4];            /* The batch is ordered by vvcb200_residual_class(): n_class[0] blocks of class 0, then
+                                       class 1, 2, 3; the rest (class 4) follows.  Equal-class blocks share a warp.       */
     uint8_t  scaling_matrix_rec[28][64];   /* VVCScalingList.scaling_matrix_rec, vvc_ps.h:187-190      */
     uint8_t  scaling_matrix_dc_rec[14];    /* VVCScalingList.scaling_matrix_dc_rec                      */
     uint8_t  pad[2];
@@ -129,6 +131,10 @@ VVCB200_API int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const i
  * If `d_residual` is non-NULL the clipped-to-int16 residual is stored there instead (same geometry as
  * `dst`, int16 samples) and `dst` is left untouched (used by the wavefront intra path).
  */
+/* Lane-group class of a transform block (host helper, no CUDA): 0..3 = 2-D transform done with 32 / 16 / 8 / 4 lanes
+ * (largest side >= 32 / 16 / 8 / <= 4), 4 = generic (transform skip, BDPCM, LFNST, 1-D).  Emitters keep one list per class. */
+VVCB200_API int vvcb200_residual_class(const VVCB200TransformBlock *tb);
+
 VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
                            const int16_t *d_levels, const VVCB200TransformBlock *d_tbs, int n,
                            const VVCB200ResidualParams *params /* host */, void *stream);

@@ -9,8 +9,19 @@ from tests import util
 pytestmark = pytest.mark.gpu
 
 
+def _params_for(pic):
+    """ResidualParams with the class counts of exactly the TBs being submitted (subsets stay class-ordered)."""
+    p = abi.ResidualParams.from_buffer_copy(bytes(pic["params"]))
+    cls = abi.residual_class(pic["tbs"])
+    assert np.all(np.diff(cls) >= 0)
+    for c in range(4):
+        p.n_class[c] = int(np.sum(cls == c))
+    return p
+
+
 def _run_gpu(pic, planes_np, to_residual=False):
     import torch
+    pic = dict(pic, params=_params_for(pic))
     dev = util.to_device_planes(planes_np, torch)
     tbs = torch.from_numpy(pic["tbs"].view(np.uint8).reshape(-1)).cuda()
     levels = torch.from_numpy(pic["levels"]).cuda()
@@ -150,7 +161,7 @@ def test_level_b_context_host_buffers():
         for k in range(2):                      # twice: the second picture reuses the device buffers
             ctx.begin(k)
             ctx.upload(src)
-            ctx.residual(levels, tbs, pic["params"])
+            ctx.residual(levels, tbs, _params_for(pic))
             ctx.download(out)
             ctx.sync()
             assert util.plane_md5(out) == util.plane_md5(want)
