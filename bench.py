@@ -57,7 +57,7 @@ def measured_peaks():
 def make_picture(seed, width, height):
     """Synthetic parsed inter picture (SURVEY.md §8d config 2/3 shape).  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v3_%dx%d_%d.pkl" % (width, height, seed)
+    cache = "/tmp/vvcb200_bench_v4_%dx%d_%d.pkl" % (width, height, seed)
     if os.path.exists(cache):
         try:
             with open(cache, "rb") as f:
@@ -218,10 +218,10 @@ def main():
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     config = {"workload": "%s 4:2:0 10-bit synthetic inter picture (%dx%d), CTU 128, 2 reference pictures"
                           % (args.workload, width, height),
-              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW)",
+              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW, DMVR, BDOF)",
                          "residual (dequant, inverse DCT2/DST7/DCT8, TS, joint CbCr, add)",
                          "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
-              "not_in_step": "intra prediction, DMVR/BDOF/PROF/affine/GPM/CIIP (not built yet, see DESIGN.md)",
+              "not_in_step": "intra prediction, PROF/affine/GPM/CIIP (not built yet, see DESIGN.md)",
               "streams": "one independent picture stream per GPU (replicas, no collective)"}
 
     if args.impl == "reference":

@@ -68,7 +68,7 @@ struct VVCB200Ctx {
     DevPicture scratch;            // SAO output / ALF input
     int cur = 0;
     // per-stage device copies of the host descriptor batches
-    DevBuffer levels, tbs, blocks, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
+    DevBuffer levels, tbs, blocks, refined, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
 };
 
 namespace {
@@ -173,7 +173,7 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     DeviceGuard g(c->device);
     if (c->stream)
         cudaStreamSynchronize(c->stream);
-    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
+    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->refined, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
                           &c->alf_params };
     for (DevBuffer *b : bufs)
         b->release();
@@ -263,7 +263,7 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
 }
 
 int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *params,
-                      const uint16_t *lmcs_fwd_lut)
+                      const uint16_t *lmcs_fwd_lut, int32_t *refined_mv)
 {
     if (!c || !params || n < 0 || (n && !blocks)) {
         set_error("vvcb200_pic_inter: bad argument");
@@ -298,8 +298,18 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
                 set_error("vvcb200_pic_inter: ref_slot[%d][%d] = %d is not a DPB slot of this context", l, i, params->ref_slot[l][i]);
                 return VVCB200_ERR_ARG;
             }
-    return vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)c->blocks.p, n, params,
-                               d_lut, nullptr, c->stream);
+    int32_t *d_mv = nullptr;
+    if (refined_mv) {
+        if (int r = c->refined.reserve((size_t)n * 4 * sizeof(int32_t)))
+            return r;
+        d_mv = (int32_t *)c->refined.p;
+    }
+    if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)c->blocks.p, n, params,
+                                    d_lut, nullptr, d_mv, c->stream))
+        return r;
+    if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
+        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    return 0;
 }
 
 int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,

@@ -28,6 +28,7 @@ constexpr int kInterWarps = 8;
 constexpr int kMaxRefs    = 16;
 constexpr int kWinElems   = 1288 + 24;          // staged windows of one warp (u16), largest class + slack
 constexpr int kTmpElems   = 16 * 26 + 16;       // transposed horizontal-pass rows of one warp (int16)
+constexpr int kBufElems   = kWinElems + kTmpElems;   // 1744: also exactly what BDOF needs (2 ringed blocks + 4 gradients)
 
 struct InterArgs {
     PlanesView dst;
@@ -35,9 +36,25 @@ struct InterArgs {
     PlanesView refs[kMaxRefs];
     const VVCB200PredBlock *blocks;
     const uint16_t *lmcs_fwd;
+    int32_t *refined_mv;                         // optional: the vectors actually used (DMVR feedback), n x 2 x 2
     int n, n16, n8;                              // blocks of width 16 come first, then width 8, then width 4
     int bd, to_tmp14;
 };
+
+struct Window { int x0, x1, y0, y1; };           // valid sample coordinates of one fetch (picture, or DMVR window)
+
+__device__ __forceinline__ Window fetch_window(int pw, int ph, bool dmvr, int x_sb, int y_sb, int bw, int bh, int before, int after)
+{
+    Window w = { 0, pw - 1, 0, ph - 1 };
+    if (dmvr) {
+        // emulated_edge_dmvr (vvc_inter.c:60-89): fetches are confined to what the un-refined vector would have read
+        w.x0 = clip3(x_sb - before, 0, pw - 1);
+        w.y0 = clip3(y_sb - before, 0, ph - 1);
+        w.x1 = w.x0 + max(min(pw, x_sb + bw + after) - w.x0, 1) - 1;
+        w.y1 = w.y0 + max(min(ph, y_sb + bh + after) - w.y0, 1) - 1;
+    }
+    return w;
+}
 
 __device__ __forceinline__ int bcw_weight(int idx)
 {
@@ -91,7 +108,7 @@ __device__ __forceinline__ void filter8(int (&out)[8], const int (&wd)[8], const
 //   win / tmp: this group's staging areas; ws / ts their row strides (even, odd number of words)
 template <int TAPS>
 __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, int gs, int w, int h, int log2w,
-                                            const uint16_t *src, int stride, int pw, int ph, int xi, int yi,
+                                            const uint16_t *src, int stride, const Window &fw, int xi, int yi,
                                             const int8_t *hf, const int8_t *vf, int bd,
                                             uint16_t *win, int ws, int16_t *tmp, int ts)
 {
@@ -102,9 +119,9 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
     if (active) {
         // stage the window: a lane owns columns li, li + gs, ... and walks down the rows
         for (int c = li; c < cols; c += gs) {
-            const int sx = clip3(xi - BEFORE + c, 0, pw - 1);
+            const int sx = clip3(xi - BEFORE + c, fw.x0, fw.x1);
             for (int r = 0; r < rows; r++) {
-                const int sy = clip3(yi - BEFORE + r, 0, ph - 1);
+                const int sy = clip3(yi - BEFORE + r, fw.y0, fw.y1);
                 win[r * ws + c] = __ldg(src + (size_t)sy * stride + sx);
             }
         }
@@ -150,11 +167,263 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
     }
 }
 
+// ---- DMVR (8.5.3): dmvr_mv_refine / parametric_mv_refine (vvc_inter.c:642-748), bilinear dmvr[][] (vvc_inter_template.c:
+// 324-413), sad (vvcdsp.c:49-65).  One lane group refines one block; `buf` holds the two (w+4)x(h+4) bilinear
+// predictions and the 25 SADs.  mv[][] is updated in place (all lanes of the group get the result); returns false if
+// BDOF must be switched off for the block.  Called by whole warps; `go` selects the groups that really refine.
+// Reductions over aligned lane groups of `gs` lanes.  The group size may differ between the lanes of a warp (blocks of
+// different height share a warp), so every lane executes every shuffle and only the add is conditional.
+__device__ __forceinline__ int group_sum(int v, int gs)
+{
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const int t = __shfl_xor_sync(0xffffffffu, v, o);
+        if (o < gs)
+            v += t;
+    }
+    return v;
+}
+
+__device__ __forceinline__ int group_min(int v, int gs)
+{
+#pragma unroll
+    for (int o = 16; o; o >>= 1) {
+        const int t = __shfl_xor_sync(0xffffffffu, v, o);
+        if (o < gs)
+            v = min(v, t);
+    }
+    return v;
+}
+
+__device__ __forceinline__ int dmvr_parabola(int sm, int sc, int sp)
+{
+    int denom = ((sm + sp) - (sc << 1)) << 3;
+    if (!denom)
+        return 0;
+    if (sm == sc)
+        return -8;
+    if (sp == sc)
+        return 8;
+    int num = (sm - sp) * 16, q = 0;
+    const bool neg = num < 0;
+    if (neg)
+        num = -num;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        q <<= 1;
+        if (num >= denom) {
+            num -= denom;
+            q++;
+        }
+        denom >>= 1;
+    }
+    return neg ? -q : q;
+}
+
+__device__ __forceinline__ bool dmvr_refine(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
+                                            bool go, int li, int gs, int16_t *buf, int (&mv)[2][2])
+{
+    const int w = b.w, h = b.h, bd = a.bd;
+    const int pw4 = w + 4, ph4 = h + 4;
+    int16_t *pred[2] = { buf, buf + 20 * pw4 };
+    int *sads = reinterpret_cast<int *>(buf + 40 * pw4 + ((40 * pw4) & 1));
+    __syncwarp();
+    if (go) {
+#pragma unroll
+        for (int l = 0; l < 2; l++) {
+            const PlanesView &ref = a.refs[p.ref_slot[l][b.ref_idx[l] & 15] & (kMaxRefs - 1)];
+            const uint16_t *src = ref.p[0];
+            const int stride = ref.stride[0], pw = ref.w[0], ph = ref.h[0];
+            const int mx = mv[l][0] & 15, my = mv[l][1] & 15;
+            const int xi = b.x0 + (mv[l][0] >> 4) - 2, yi = b.y0 + (mv[l][1] >> 4) - 2;
+            const int fx0 = VVC_DMVR_FILTERS[mx * 2], fx1 = VVC_DMVR_FILTERS[mx * 2 + 1];
+            const int fy0 = VVC_DMVR_FILTERS[my * 2], fy1 = VVC_DMVR_FILTERS[my * 2 + 1];
+            const int sh1 = bd - 6, of1 = 1 << (sh1 - 1);
+            if (li < pw4) {
+                const int sx0 = clip3(xi + li, 0, pw - 1), sx1 = clip3(xi + li + 1, 0, pw - 1);
+                for (int r = 0; r < ph4; r++) {
+                    const uint16_t *r0 = src + (size_t)clip3(yi + r, 0, ph - 1) * stride;
+                    const uint16_t *r1 = src + (size_t)clip3(yi + r + 1, 0, ph - 1) * stride;
+                    int v;
+                    if (!mx && !my)
+                        v = bd > 10 ? (r0[sx0] + (1 << (bd - 11))) >> (bd - 10) : r0[sx0] << (10 - bd);
+                    else if (!my)
+                        v = (fx0 * r0[sx0] + fx1 * r0[sx1] + of1) >> sh1;
+                    else if (!mx)
+                        v = (fy0 * r0[sx0] + fy1 * r1[sx0] + of1) >> sh1;
+                    else {
+                        const int t0 = (fx0 * r0[sx0] + fx1 * r0[sx1] + of1) >> sh1;
+                        const int t1 = (fx0 * r1[sx0] + fx1 * r1[sx1] + of1) >> sh1;
+                        v = (fy0 * t0 + fy1 * t1 + 8) >> 4;
+                    }
+                    pred[l][r * pw4 + li] = (int16_t)v;
+                }
+            }
+        }
+    }
+    __syncwarp();
+    // centre SAD, every other row (vvcdsp.c:49-65), all lanes of the group share the samples
+    int part = 0;
+    if (go) {
+        const int log2w = 31 - __clz(w);
+        for (int i = li; i < (w * h) >> 1; i += gs) {
+            const int x = i & (w - 1), y = (i >> log2w) << 1;
+            part += abs(pred[0][(2 + y) * pw4 + 2 + x] - pred[1][(2 + y) * pw4 + 2 + x]);
+        }
+    }
+    int min_sad = group_sum(part, gs);
+    min_sad -= min_sad >> 2;
+    const bool search = go && min_sad >= w * h;
+    if (search) {
+        // one search position per lane (24 besides the centre)
+        for (int pos = li; pos < 25; pos += gs) {
+            int sad = min_sad;
+            if (pos != 12) {
+                const int dx = pos % 5 - 2, dy = pos / 5 - 2;
+                const int16_t *p0 = pred[0] + (2 + dy) * pw4 + 2 + dx, *p1 = pred[1] + (2 - dy) * pw4 + 2 - dx;
+                sad = 0;
+                for (int y = 0; y < h; y += 2)
+                    for (int x = 0; x < w; x++)
+                        sad += abs(p0[y * pw4 + x] - p1[y * pw4 + x]);
+            }
+            sads[pos] = sad;
+        }
+    }
+    __syncwarp();
+    int best = 0x7fffffff;
+    if (search)
+        for (int pos = li; pos < 25; pos += gs)
+            best = min(best, sads[pos] * 32 + (pos == 12 ? 0 : pos + 1));   // centre wins ties, then raster order
+    best = group_min(best, gs);
+    if (search) {
+        const int pos = (best & 31) ? (best & 31) - 1 : 12;
+        const int min_dx = pos % 5, min_dy = pos / 5;
+        min_sad = best >> 5;
+        int dmx = (min_dx - 2) * 16, dmy = (min_dy - 2) * 16;
+        if (min_dx != 0 && min_dx != 4 && min_dy != 0 && min_dy != 4) {
+            dmx += dmvr_parabola(sads[pos - 1], sads[pos], sads[pos + 1]);
+            dmy += dmvr_parabola(sads[pos - 5], sads[pos], sads[pos + 5]);
+        }
+        mv[0][0] = clip3(mv[0][0] + dmx, -(1 << 17), (1 << 17) - 1);
+        mv[0][1] = clip3(mv[0][1] + dmy, -(1 << 17), (1 << 17) - 1);
+        mv[1][0] = clip3(mv[1][0] - dmx, -(1 << 17), (1 << 17) - 1);
+        mv[1][1] = clip3(mv[1][1] - dmy, -(1 << 17), (1 << 17) - 1);
+    }
+    __syncwarp();
+    return !go || min_sad >= 2 * w * h;
+}
+
+// ---- BDOF: bdof_fetch_samples / prof_grad_filter / derive_bdof_vx_vy / apply_bdof (vvc_inter_template.c:101-128, 135-158,
+// 237-317).  `buf`: the two 14-bit predictions with a one-sample ring of integer reference samples, then the four
+// gradient blocks.  The reference pads ring and gradients with replicated edge values after the gradients are formed;
+// here that is an index clamp on read.  v0 / v1: the lane's own prediction samples (x = li % w, rows chunk * outs + k).
+__device__ __forceinline__ void bdof_block(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
+                                           bool go, int li, int gs, int16_t *buf, int8_t *vxy, const int (&v0)[8],
+                                           const int (&v1)[8], const int (&mv)[2][2], const Window (&fw)[2])
+{
+    const int w = b.w, h = b.h, bd = a.bd;
+    const int log2w = 31 - __clz(w);
+    const int ps = w + 2;                                   // ringed row stride
+    int16_t *pa[2] = { buf, buf + (h + 2) * ps };
+    int16_t *gh[2] = { buf + 2 * (h + 2) * ps, buf + 2 * (h + 2) * ps + w * h };
+    int16_t *gv[2] = { gh[1] + w * h, gh[1] + 2 * w * h };
+    const int outs = h >> 1;
+    __syncwarp();
+    if (go) {
+        const int x = li & (w - 1), chunk = li >> log2w;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (k < outs) {
+                pa[0][(chunk * outs + k + 1) * ps + x + 1] = (int16_t)v0[k];
+                pa[1][(chunk * outs + k + 1) * ps + x + 1] = (int16_t)v1[k];
+            }
+        // ring: integer samples at the rounded position, << (14 - bd)
+#pragma unroll
+        for (int l = 0; l < 2; l++) {
+            const PlanesView &ref = a.refs[p.ref_slot[l][b.ref_idx[l] & 15] & (kMaxRefs - 1)];
+            const int ox = b.x0 + (mv[l][0] >> 4) + ((mv[l][0] & 15) >> 3), oy = b.y0 + (mv[l][1] >> 4) + ((mv[l][1] & 15) >> 3);
+            const int n_ring = 2 * (w + 2) + 2 * h;
+            for (int i = li; i < n_ring; i += gs) {
+                int rx, ry;
+                if (i < w + 2) { rx = i - 1; ry = -1; }
+                else if (i < 2 * (w + 2)) { rx = i - (w + 2) - 1; ry = h; }
+                else { const int j = i - 2 * (w + 2); rx = (j & 1) ? w : -1; ry = j >> 1; }
+                const int sx = clip3(ox + rx, fw[l].x0, fw[l].x1), sy = clip3(oy + ry, fw[l].y0, fw[l].y1);
+                pa[l][(ry + 1) * ps + rx + 1] = (int16_t)(ref.p[0][(size_t)sy * ref.stride[0] + sx] << (14 - bd));
+            }
+        }
+    }
+    __syncwarp();
+    if (go) {
+        for (int i = li; i < w * h; i += gs) {
+            const int x = i & (w - 1), y = i >> log2w;
+#pragma unroll
+            for (int l = 0; l < 2; l++) {
+                const int16_t *c = pa[l] + (y + 1) * ps + x + 1;
+                gh[l][i] = (int16_t)((c[1] >> 6) - (c[-1] >> 6));
+                gv[l][i] = (int16_t)((c[ps] >> 6) - (c[-ps] >> 6));
+            }
+        }
+    }
+    __syncwarp();
+    {
+        // per 4x4: sums over its 6x6 neighbourhood, `lps` lanes per 4x4
+        const int nsb = (w * h) >> 4, lps = gs / nsb;
+        const int sb = li / lps, sub = li - sb * lps;
+        const int bx = (sb & ((w >> 2) - 1)) << 2, by = (sb / (w >> 2)) << 2;
+        int sgx2 = 0, sgy2 = 0, sgxgy = 0, sgxdi = 0, sgydi = 0;
+        if (go) {
+            for (int j = sub; j < 36; j += lps) {
+                const int cy = clip3(by - 1 + j / 6, 0, h - 1), cx = clip3(bx - 1 + j % 6, 0, w - 1);
+                const int i = (cy << log2w) + cx;
+                const int diff = (pa[0][(cy + 1) * ps + cx + 1] >> 4) - (pa[1][(cy + 1) * ps + cx + 1] >> 4);
+                const int th = (gh[0][i] + gh[1][i]) >> 1, tv = (gv[0][i] + gv[1][i]) >> 1;
+                const int sh_ = (th > 0) - (th < 0), sv = (tv > 0) - (tv < 0);
+                sgx2 += abs(th);
+                sgy2 += abs(tv);
+                sgxgy += sv * th;
+                sgxdi -= sh_ * diff;
+                sgydi -= sv * diff;
+            }
+        }
+        sgx2 = group_sum(sgx2, lps);
+        sgy2 = group_sum(sgy2, lps);
+        sgxgy = group_sum(sgxgy, lps);
+        sgxdi = group_sum(sgxdi, lps);
+        sgydi = group_sum(sgydi, lps);
+        if (go && sub == 0) {
+            int vx = 0, vy = 0;
+            if (sgx2 > 0)
+                vx = clip3((sgxdi * 4) >> (31 - __clz(sgx2)), -15, 15);
+            if (sgy2 > 0)
+                vy = clip3(((sgydi * 4) - ((vx * sgxgy) >> 1)) >> (31 - __clz(sgy2)), -15, 15);
+            vxy[2 * sb] = (int8_t)vx;
+            vxy[2 * sb + 1] = (int8_t)vy;
+        }
+    }
+    __syncwarp();
+    if (go) {
+        const int sh4 = 15 - bd, of4 = 1 << (sh4 - 1);
+        for (int i = li; i < w * h; i += gs) {
+            const int x = i & (w - 1), y = i >> log2w;
+            const int sb = (y >> 2) * (w >> 2) + (x >> 2);
+            const int vx = vxy[2 * sb], vy = vxy[2 * sb + 1];
+            const int off = vx * (gh[0][i] - gh[1][i]) + vy * (gv[0][i] - gv[1][i]);
+            int r = clip_pixel((pa[0][(y + 1) * ps + x + 1] + of4 + pa[1][(y + 1) * ps + x + 1] + off) >> sh4, bd);
+            if ((b.flags & VVCB200_PB_LMCS) && a.lmcs_fwd)
+                r = __ldg(a.lmcs_fwd + r);
+            a.dst.p[0][(size_t)(b.y0 + y) * a.dst.stride[0] + b.x0 + x] = (uint16_t)r;
+        }
+    }
+    __syncwarp();
+}
+
 // One component of one block by one lane group (both lists + weighting + store).
 template <int TAPS>
 __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
                                                   bool active, int c, int li, int gs, uint16_t *win, int ws,
-                                                  int16_t *tmp, int ts)
+                                                  int16_t *tmp, int ts, const int (&mv)[2][2], bool dmvr, bool bdof,
+                                                  int16_t *bdof_buf, int8_t *bdof_vxy)
 {
     const int bd = a.bd;
     const int hs = c ? 1 : 0;
@@ -163,25 +432,30 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
     const int log2w = 31 - __clz(w);
     const int set = c ? 0 : (b.flags & VVCB200_PB_AFFINE) ? 2 : (b.flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
     int v0[8], v1[8];
+    Window fw[2];
 
 #pragma unroll
     for (int l = 0; l < 2; l++) {
         const bool use = active && (b.pred_flag & (1 << l));
-        const int mvx = b.mv[l][0], mvy = b.mv[l][1];
+        const int mvx = mv[l][0], mvy = mv[l][1];
         const int mx = c ? (mvx & 31) : (mvx & 15);
         const int my = c ? (mvy & 31) : (mvy & 15);
         const int xi = x0 + (mvx >> (4 + hs)), yi = y0 + (mvy >> (4 + hs));
         const int8_t *hf = c ? VVC_CHROMA_FILTERS + (set * 32 + mx) * 4 : VVC_LUMA_FILTERS + (set * 16 + mx) * 8;
         const int8_t *vf = c ? VVC_CHROMA_FILTERS + (set * 32 + my) * 4 : VVC_LUMA_FILTERS + (set * 16 + my) * 8;
         const PlanesView &ref = a.refs[p.ref_slot[l][b.ref_idx[l] & 15] & (kMaxRefs - 1)];
+        fw[l] = fetch_window(ref.w[c], ref.h[c], dmvr, x0 + (b.mv[l][0] >> (4 + hs)), y0 + (b.mv[l][1] >> (4 + hs)), w, h,
+                             TAPS / 2 - 1, TAPS / 2);
         if (l == 0)
-            interpolate<TAPS>(v0, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], ref.w[c], ref.h[c], xi, yi, hf, vf, bd,
+            interpolate<TAPS>(v0, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
                               win, ws, tmp, ts);
         else
-            interpolate<TAPS>(v1, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], ref.w[c], ref.h[c], xi, yi, hf, vf, bd,
+            interpolate<TAPS>(v1, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
                               win, ws, tmp, ts);
     }
-    if (!active)
+    if (TAPS == 8 && !a.to_tmp14 && __any_sync(0xffffffffu, active && bdof))
+        bdof_block(a, p, b, active && bdof, li, gs, bdof_buf, bdof_vxy, v0, v1, mv, fw);
+    if (!active || (TAPS == 8 && bdof && !a.to_tmp14))
         return;
 
     // ---- combine (weights are uniform inside a lane group)
@@ -258,8 +532,9 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
 __global__ void __launch_bounds__(kInterWarps * 32)
 inter_kernel(const InterArgs a, const VVCB200InterParams p)
 {
-    __shared__ __align__(16) uint16_t s_win[kInterWarps][kWinElems];
-    __shared__ __align__(16) int16_t  s_tmp[kInterWarps][kTmpElems];
+    __shared__ __align__(16) uint16_t s_buf[kInterWarps][kBufElems];
+    __shared__ int s_mv[kInterWarps][4][4];             // refined vectors of the warp's blocks, luma phase -> chroma phase
+    __shared__ int8_t s_vxy[kInterWarps][2][32];        // BDOF (vx, vy) per 4x4 of the warp's (up to two) blocks
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x * kInterWarps + warp;
 
@@ -276,29 +551,55 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
     } else {
         return;
     }
-    uint16_t *win = s_win[warp];
-    int16_t *tmp = s_tmp[warp];
+    uint16_t *win = s_buf[warp];
+    int16_t *tmp = reinterpret_cast<int16_t *>(s_buf[warp]) + kWinElems;
 
     {   // luma: groups of 2 * w lanes
         const int gs = 32 >> cls, g = lane >> (5 - cls), li = lane & (gs - 1);
         const int bi = first + g;
         const bool active = bi < last;
         const VVCB200PredBlock b = a.blocks[active ? bi : first];
+        const bool luma = active && !(b.flags & VVCB200_PB_CHROMA_ONLY);
+        int mv[2][2] = { { b.mv[0][0], b.mv[0][1] }, { b.mv[1][0], b.mv[1][1] } };
+        const bool dmvr = (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
+        bool bdof = luma && (b.flags & VVCB200_PB_BDOF) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
+        if (__any_sync(0xffffffffu, active && dmvr)) {
+            // each group's scratch: 2 predictions of (w+4) x 20 samples + 25 SADs
+            const int region = cls == 0 ? kBufElems : kBufElems / 2;
+            if (!dmvr_refine(a, p, b, active && dmvr, li, gs, reinterpret_cast<int16_t *>(s_buf[warp]) + g * region, mv))
+                bdof = false;
+        }
+        if (active && li == 0) {
+#pragma unroll
+            for (int k = 0; k < 4; k++)
+                s_mv[warp][g][k] = mv[k >> 1][k & 1];
+            if (a.refined_mv)
+#pragma unroll
+                for (int k = 0; k < 4; k++)
+                    a.refined_mv[(size_t)bi * 4 + k] = mv[k >> 1][k & 1];
+        }
         const int ws = (16 >> cls) + 10;                // 26 / 18 / 14 samples: an odd number of words
         const int win_sz = 23 * ws, tmp_sz = (16 >> cls) * 26;
-        predict_component<8>(a, p, b, active && !(b.flags & VVCB200_PB_CHROMA_ONLY), 0, li, gs,
-                             win + g * win_sz, ws, tmp + g * tmp_sz, 26);
+        const int bdof_region = cls == 0 ? 0 : kBufElems / 2;
+        predict_component<8>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
+                             reinterpret_cast<int16_t *>(s_buf[warp]) + g * bdof_region, s_vxy[warp][g & 1]);
     }
+    __syncwarp();
     {   // chroma: each luma group splits into a Cb half and a Cr half
         const int gs = 16 >> cls, g = lane / gs, li = lane & (gs - 1);
         const int bi = first + (g >> 1);
         const bool active = bi < last;
         const VVCB200PredBlock b = a.blocks[active ? bi : first];
+        int mv[2][2];
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            mv[k >> 1][k & 1] = s_mv[warp][(g >> 1) & 3][k];
+        const bool dmvr = active && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
         const int wc = 8 >> cls;
         const int ws = wc + 6;                          // 14 / 10 / 8 samples
         const int win_sz = 11 * ws + 8, tmp_sz = wc * 14;
         predict_component<4>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
-                             win + g * win_sz, ws, tmp + g * tmp_sz, 14);
+                             win + g * win_sz, ws, tmp + g * tmp_sz, 14, mv, dmvr, false, nullptr, nullptr);
     }
 }
 
@@ -308,7 +609,8 @@ using namespace vvcb200;
 
 extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes *refs, int n_refs,
                                    const VVCB200PredBlock *d_blocks, int n, const VVCB200InterParams *params,
-                                   const uint16_t *d_lmcs_fwd_lut, const VVCB200Planes *d_tmp14, void *stream)
+                                   const uint16_t *d_lmcs_fwd_lut, const VVCB200Planes *d_tmp14, int32_t *d_refined_mv,
+                                   void *stream)
 {
     if (!params || (!dst && !d_tmp14) || !refs || n_refs <= 0 || n_refs > kMaxRefs || n < 0 || (n && !d_blocks)) {
         set_error("vvcb200_inter_batch: bad argument (n_refs must be 1..%d)", kMaxRefs);
@@ -341,6 +643,7 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
         a.refs[i] = make_view(&refs[i < n_refs ? i : 0]);
     a.blocks = d_blocks;
     a.lmcs_fwd = d_lmcs_fwd_lut;
+    a.refined_mv = d_refined_mv;
     a.n = n;
     a.n16 = params->n_w16;
     a.n8 = params->n_w8;

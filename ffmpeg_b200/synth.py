@@ -238,6 +238,16 @@ def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel
     b["flags"] = flags
     if "bcw" in tools:
         b["bcw_idx"] = np.where((pf == 3) & (rng.random(n) < 0.3), rng.integers(1, 5, n), 0)
+    # decoder-side tools on plain bi-predicted blocks of at least 8x8 (the conditions the parser enforces,
+    # vvc_ctu.c derive_dmvr_bdof_flag: no BCW, no weighted prediction)
+    big = (pf == 3) & (b["w"] >= 8) & (b["h"] >= 8)
+    for tool, flag, prob in (("dmvr", abi.PB_DMVR, 0.5), ("bdof", abi.PB_BDOF, 0.5)):
+        if tool in tools:
+            pick = big & (rng.random(n) < prob)
+            if tool == "dmvr":
+                pick &= b["w"].astype(np.int32) * b["h"] >= 128
+            b["flags"] = np.where(pick, (b["flags"] | flag) & ~np.uint16(abi.PB_WP), b["flags"])
+            b["bcw_idx"] = np.where(pick, 0, b["bcw_idx"])
     ld = (int(rng.integers(0, 8)), int(rng.integers(0, 8)))
     weight = np.zeros((2, 3, 16), np.int16)
     offset = rng.integers(-64, 64, (2, 3, 16)).astype(np.int16)
@@ -429,7 +439,7 @@ def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, 
     """All descriptor batches of one inter picture (BASELINE config 2/3 shape): prediction sub-blocks, residual TBs,
     deblocking tables, SAO/ALF CTB parameters.  Stage inputs are generated independently of each other (the
     arithmetic of every stage takes its tables as given); see DESIGN.md for what a real parser adds."""
-    inter = inter_picture(seed, width, height, n_refs=n_refs)
+    inter = inter_picture(seed, width, height, n_refs=n_refs, tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"))
     res = residual_picture(seed + 1, width, height, coded_fraction=coded_fraction, tools=residual_tools,
                            mean_log2=mean_log2)
     # every residual TB of an inter picture belongs to an inter CU

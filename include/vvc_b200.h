@@ -189,11 +189,16 @@ typedef struct VVCB200InterParams {
  * If `d_tmp14` is non-NULL the 14-bit intermediate of list 0 (what inter.put writes, int16) is stored
  * there instead of pixels (plane geometry of `dst`) — the checkasm-style view of inter.put.
  * Blocks flagged VVCB200_PB_LMCS get lmcs.filter (vvcdsp.h:124) with the forward LUT on their luma.
+ * Bi-predicted blocks of at least 8x8 flagged VVCB200_PB_DMVR run the decoder-side refinement (inter.dmvr[][] + inter.sad
+ * + dmvr_mv_refine, vvc_inter.c:642-748) and those flagged VVCB200_PB_BDOF the optical-flow blend (inter.bdof_fetch_samples
+ * + inter.apply_bdof); d_refined_mv receives the vectors actually used — what the reference stores in tab_dmvr_mvf
+ * (vvc_inter.c:750-762) for the host's later MV derivation.
  */
 VVCB200_API int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes *refs, int n_refs,
                                     const VVCB200PredBlock *d_blocks, int n, const VVCB200InterParams *params /* host */,
                                     const uint16_t *d_lmcs_fwd_lut /* 1 << bit_depth entries, or NULL */,
-                                    const VVCB200Planes *d_tmp14, void *stream);
+                                    const VVCB200Planes *d_tmp14, int32_t *d_refined_mv /* n x 2 x 2, or NULL */,
+                                    void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Deblocking (stages DEBLOCK_V / DEBLOCK_H, ff_vvc_deblock_vertical/horizontal, vvc_filter.c:861-1003,
@@ -325,7 +330,8 @@ VVCB200_API int vvcb200_pic_upload(VVCB200Ctx *ctx, int slot, const uint16_t *co
 /* Stage INTER: upload the sub-block batch and predict into the current picture.  params->ref_slot[][] are DPB slots
  * of this context.  lmcs_fwd_lut: host, 1 << bit_depth entries, or NULL. */
 VVCB200_API int vvcb200_pic_inter(VVCB200Ctx *ctx, const VVCB200PredBlock *blocks, int n,
-                                  const VVCB200InterParams *params, const uint16_t *lmcs_fwd_lut);
+                                  const VVCB200InterParams *params, const uint16_t *lmcs_fwd_lut,
+                                  int32_t *refined_mv /* host, n x 2 x 2, valid after vvcb200_ctx_sync(); or NULL */);
 /* Stage RECON, residual part: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
 VVCB200_API int vvcb200_pic_residual(VVCB200Ctx *ctx, const int16_t *levels, size_t n_levels,
                                      const VVCB200TransformBlock *tbs, int n, const VVCB200ResidualParams *params);

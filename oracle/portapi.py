@@ -45,7 +45,7 @@ def residual_batch(planes, levels, tbs, params, want_residual=False):
     return res
 
 
-def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None):
+def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None, want_refined_mv=False):
     pl = abi.host_planes(dst)
     ra = abi.planes_array([abi.host_planes(r) for r in refs])
     blocks = np.ascontiguousarray(blocks, abi.PB_DTYPE)
@@ -53,9 +53,12 @@ def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None):
     t14 = None
     if tmp14 is not None:
         t14 = abi.host_planes([t.view(np.uint16) for t in tmp14])
+    mv = np.zeros((len(blocks), 2, 2), np.int32) if want_refined_mv else None
     lib().port_inter_batch(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks), C.byref(params),
                            C.c_void_p(lut.ctypes.data) if lut is not None else None,
-                           C.byref(t14) if t14 is not None else None)
+                           C.byref(t14) if t14 is not None else None,
+                           C.c_void_p(mv.ctypes.data) if mv is not None else None)
+    return mv
 
 
 def deblock_picture(planes, edge, qp, ctb_offsets, stride4, params):

@@ -102,3 +102,30 @@ def test_inter_full_size_properties_4k():
     oracle_inter(want, sample)
     got = gpu_inter(sample, base)
     assert util.plane_md5(got) == util.plane_md5(want)
+
+
+@pytest.mark.parametrize("seed", range(6))
+def test_dmvr_bdof_match_oracle(seed):
+    """DMVR + BDOF on the GPU: pixels and the refined vectors (the host's tab_dmvr_mvf feedback) against the oracle."""
+    import torch
+    tools = ("bi", "wp", "bcw", "hpel") + (("dmvr",) if seed % 3 != 1 else ()) + (("bdof",) if seed % 3 != 0 else ())
+    pic = synth.inter_picture(40 + seed, 416, 240, tools=tools, sizes=(8, 16) if seed & 1 else (4, 8, 16),
+                              mv_range=(64 * 16 if seed < 4 else 24))
+    if seed >= 4:
+        pic["refs"][1] = [p.copy() for p in pic["refs"][0]]
+        pic["blocks"]["mv"][:, 1, :] = -pic["blocks"]["mv"][:, 0, :]
+    base = util.noise_planes(seed, pic["dims"])
+    want = [p.copy() for p in base]
+    orc = refapi if refapi.available() else portapi
+    want_mv = orc.inter_batch(want, pic["refs"], pic["blocks"], pic["params"], want_refined_mv=True)
+    dst = util.to_device_planes(base, torch)
+    refs = [util.to_device_planes(r, torch) for r in pic["refs"]]
+    blocks = torch.from_numpy(pic["blocks"].view(np.uint8).reshape(-1)).cuda()
+    mv_d = torch.zeros((len(pic["blocks"]), 2, 2), dtype=torch.int32, device="cuda")
+    lib.inter_batch(lib.device_planes(dst), [lib.device_planes(r) for r in refs], blocks, len(pic["blocks"]),
+                    _params_for(pic), refined_mv=mv_d)
+    torch.cuda.synchronize()
+    got = util.from_device_planes(dst)
+    assert np.array_equal(mv_d.cpu().numpy(), want_mv)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs" % c

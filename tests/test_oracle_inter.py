@@ -75,3 +75,25 @@ def test_port_inter_matches_golden():
         planes = util.noise_planes(seed, pic["dims"])
         portapi.inter_batch(planes, pic["refs"], pic["blocks"], pic["params"])
         assert util.plane_md5(planes) == list(g[name + "_plane_md5"])
+
+
+@needs_ref
+@pytest.mark.parametrize("seed", range(6))
+def test_port_dmvr_bdof_match_reference(seed):
+    """DMVR (bilinear search + parametric refinement, window-confined final MC) and BDOF through the reference's own
+    predict_inter(); seeds 4-5 use identical references with mirrored vectors to hit the early exits
+    (vvc_inter.c:716, 745-747).  The refined vectors (tab_dmvr_mvf) must match too."""
+    tools = ("bi", "wp", "bcw", "hpel") + (("dmvr",) if seed % 3 != 1 else ()) + (("bdof",) if seed % 3 != 0 else ())
+    pic = synth.inter_picture(300 + seed, 208, 120, tools=tools, sizes=(8, 16), mv_range=(64 * 16 if seed < 4 else 24))
+    if seed >= 4:
+        pic["refs"][1] = [p.copy() for p in pic["refs"][0]]
+        pic["blocks"]["mv"][:, 1, :] = -pic["blocks"]["mv"][:, 0, :]
+    base = util.noise_planes(seed, pic["dims"])
+    a, b = [p.copy() for p in base], [p.copy() for p in base]
+    mva = refapi.inter_batch(a, pic["refs"], pic["blocks"], pic["params"], want_refined_mv=True)
+    mvb = portapi.inter_batch(b, pic["refs"], pic["blocks"], pic["params"], want_refined_mv=True)
+    assert np.array_equal(mva, mvb)
+    if "dmvr" in tools and seed < 4:
+        assert (mva != pic["blocks"]["mv"]).any()
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
