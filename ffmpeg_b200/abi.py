@@ -85,11 +85,22 @@ def host_planes(arrays):
 # ---- inter prediction -----------------------------------------------------------------------------------
 PB_WP, PB_HPEL_IF, PB_AFFINE, PB_LUMA_ONLY, PB_CHROMA_ONLY = 1, 2, 4, 8, 16
 PB_BDOF, PB_DMVR, PB_CIIP, PB_LMCS = 32, 64, 128, 256
+PB_GPM, PB_PROF0, PB_PROF1 = 512, 1024, 2048
+
+
+def gpm_aux(partition_idx, log2_cb_w, log2_cb_h, off_x, off_y, list0, list1):
+    """VVCB200_GPM_AUX of include/vvc_b200.h"""
+    return (partition_idx | ((log2_cb_w - 3) << 6) | ((log2_cb_h - 3) << 8) | ((off_x >> 2) << 10) |
+            ((off_y >> 2) << 14) | (list0 << 18) | (list1 << 19))
+
+
+PROF_DTYPE = np.dtype([("diff_mv_x", "i1", (2, 16)), ("diff_mv_y", "i1", (2, 16))])
+assert PROF_DTYPE.itemsize == 64
 PF_L0, PF_L1, PF_BI = 1, 2, 3
 
 PB_DTYPE = np.dtype([
     ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("pred_flag", "u1"), ("bcw_idx", "u1"),
-    ("ref_idx", "i1", (2,)), ("flags", "<u2"), ("mv", "<i4", (2, 2)), ("reserved", "<u4"),
+    ("ref_idx", "i1", (2,)), ("flags", "<u2"), ("mv", "<i4", (2, 2)), ("aux", "<u4"),
 ], align=False)
 assert PB_DTYPE.itemsize == 32
 

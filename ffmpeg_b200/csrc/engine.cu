@@ -68,7 +68,7 @@ struct VVCB200Ctx {
     DevPicture scratch;            // SAO output / ALF input
     int cur = 0;
     // per-stage device copies of the host descriptor batches
-    DevBuffer levels, tbs, blocks, refined, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
+    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
 };
 
 namespace {
@@ -173,7 +173,7 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     DeviceGuard g(c->device);
     if (c->stream)
         cudaStreamSynchronize(c->stream);
-    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->refined, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
+    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->refined, &c->prof, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
                           &c->alf_params };
     for (DevBuffer *b : bufs)
         b->release();
@@ -263,7 +263,7 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
 }
 
 int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *params,
-                      const uint16_t *lmcs_fwd_lut, int32_t *refined_mv)
+                      const uint16_t *lmcs_fwd_lut, int32_t *refined_mv, const VVCB200ProfTable *prof, int n_prof)
 {
     if (!c || !params || n < 0 || (n && !blocks)) {
         set_error("vvcb200_pic_inter: bad argument");
@@ -304,8 +304,14 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
             return r;
         d_mv = (int32_t *)c->refined.p;
     }
+    const VVCB200ProfTable *d_prof = nullptr;
+    if (prof && n_prof > 0) {
+        if (int r = upload(c, c->prof, prof, (size_t)n_prof * sizeof(*prof)))
+            return r;
+        d_prof = (const VVCB200ProfTable *)c->prof.p;
+    }
     if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)c->blocks.p, n, params,
-                                    d_lut, nullptr, d_mv, c->stream))
+                                    d_lut, nullptr, d_mv, d_prof, c->stream))
         return r;
     if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
         VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));

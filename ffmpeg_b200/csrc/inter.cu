@@ -20,6 +20,7 @@
 #include "common.cuh"
 
 #define VVC_TABLE_QUAL static __device__ const
+#define VVC_TABLES_WITH_GPM_WEIGHTS
 #include "vvc_tables.h"
 
 namespace vvcb200 {
@@ -37,6 +38,7 @@ struct InterArgs {
     const VVCB200PredBlock *blocks;
     const uint16_t *lmcs_fwd;
     int32_t *refined_mv;                         // optional: the vectors actually used (DMVR feedback), n x 2 x 2
+    const VVCB200ProfTable *prof;                // optional: PROF offset tables of the affine coding units
     int n, n16, n8;                              // blocks of width 16 come first, then width 8, then width 4
     int bd, to_tmp14;
 };
@@ -418,6 +420,44 @@ __device__ __forceinline__ void bdof_block(const InterArgs &a, const VVCB200Inte
     __syncwarp();
 }
 
+// ---- PROF (fetch_samples + apply_prof / apply_prof_uni[_w], vvc_inter_template.c:130-235) on a 4x4 affine sub-block:
+// the 14-bit prediction gets a ring of integer reference samples, gradients are taken on the ringed block and every
+// sample moves by gh * diff_mv_x + gv * diff_mv_y (clipped); the usual uni / bi combination follows.
+__device__ __forceinline__ void prof_block(const InterArgs &a, const VVCB200PredBlock &b, bool go, int li, int gs, int l,
+                                           int16_t *r /* 6 x 6 */, int (&v)[8], const PlanesView &ref, const int (&mv)[2][2],
+                                           const Window &fw)
+{
+    const int x = li & 3, chunk = li >> 2;               // 8 lanes per 4x4 block: two rows each
+    __syncwarp();
+    if (go) {
+        r[(chunk * 2 + 1) * 6 + x + 1] = (int16_t)v[0];
+        r[(chunk * 2 + 2) * 6 + x + 1] = (int16_t)v[1];
+        const int ox = b.x0 + (mv[l][0] >> 4) + ((mv[l][0] & 15) >> 3), oy = b.y0 + (mv[l][1] >> 4) + ((mv[l][1] & 15) >> 3);
+        for (int i = li; i < 20; i += gs) {
+            int rx, ry;
+            if (i < 6) { rx = i - 1; ry = -1; }
+            else if (i < 12) { rx = i - 7; ry = 4; }
+            else { rx = (i & 1) ? 4 : -1; ry = (i - 12) >> 1; }
+            const int sx = clip3(ox + rx, fw.x0, fw.x1), sy = clip3(oy + ry, fw.y0, fw.y1);
+            r[(ry + 1) * 6 + rx + 1] = (int16_t)(ref.p[0][(size_t)sy * ref.stride[0] + sx] << (14 - a.bd));
+        }
+    }
+    __syncwarp();
+    if (go) {
+        const VVCB200ProfTable *pt = a.prof + b.aux;
+        const int limit = 1 << max(13, a.bd + 1);
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            const int y = chunk * 2 + k;
+            const int16_t *q = r + (y + 1) * 6 + x + 1;
+            const int gh = (q[1] >> 6) - (q[-1] >> 6), gv = (q[6] >> 6) - (q[-6] >> 6);
+            const int di = gh * pt->diff_mv_x[l][y * 4 + x] + gv * pt->diff_mv_y[l][y * 4 + x];
+            v[k] = q[0] + clip3(di, -limit, limit - 1);
+        }
+    }
+    __syncwarp();
+}
+
 // One component of one block by one lane group (both lists + weighting + store).
 template <int TAPS>
 __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
@@ -430,7 +470,8 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
     const int w = max(b.w >> hs, 1), h = max(b.h >> hs, 1);
     const int x0 = b.x0 >> hs, y0 = b.y0 >> hs;
     const int log2w = 31 - __clz(w);
-    const int set = c ? 0 : (b.flags & VVCB200_PB_AFFINE) ? 2 : (b.flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
+    const bool gpm = b.flags & VVCB200_PB_GPM;
+    const int set = (c || gpm) ? 0 : (b.flags & VVCB200_PB_AFFINE) ? 2 : (b.flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
     int v0[8], v1[8];
     Window fw[2];
 
@@ -443,7 +484,9 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
         const int xi = x0 + (mvx >> (4 + hs)), yi = y0 + (mvy >> (4 + hs));
         const int8_t *hf = c ? VVC_CHROMA_FILTERS + (set * 32 + mx) * 4 : VVC_LUMA_FILTERS + (set * 16 + mx) * 8;
         const int8_t *vf = c ? VVC_CHROMA_FILTERS + (set * 32 + my) * 4 : VVC_LUMA_FILTERS + (set * 16 + my) * 8;
-        const PlanesView &ref = a.refs[p.ref_slot[l][b.ref_idx[l] & 15] & (kMaxRefs - 1)];
+        // GPM: prediction l is gpm_mv[l], which names its own reference list (vvc_inter.c:507-509)
+        const int list = gpm ? (b.aux >> (18 + l)) & 1 : l;
+        const PlanesView &ref = a.refs[p.ref_slot[list][b.ref_idx[l] & 15] & (kMaxRefs - 1)];
         fw[l] = fetch_window(ref.w[c], ref.h[c], dmvr, x0 + (b.mv[l][0] >> (4 + hs)), y0 + (b.mv[l][1] >> (4 + hs)), w, h,
                              TAPS / 2 - 1, TAPS / 2);
         if (l == 0)
@@ -452,6 +495,15 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
         else
             interpolate<TAPS>(v1, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
                               win, ws, tmp, ts);
+        if (TAPS == 8 && a.prof) {
+            const bool go = use && w == 4 && h == 4 && (b.flags & (l ? VVCB200_PB_PROF1 : VVCB200_PB_PROF0));
+            if (__any_sync(0xffffffffu, go)) {
+                if (l == 0)
+                    prof_block(a, b, go, li, gs, l, tmp, v0, ref, mv, fw[l]);
+                else
+                    prof_block(a, b, go, li, gs, l, tmp, v1, ref, mv, fw[l]);
+            }
+        }
     }
     if (TAPS == 8 && !a.to_tmp14 && __any_sync(0xffffffffu, active && bdof))
         bdof_block(a, p, b, active && bdof, li, gs, bdof_buf, bdof_vxy, v0, v1, mv, fw);
@@ -459,10 +511,25 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
         return;
 
     // ---- combine (weights are uniform inside a lane group)
-    int mode;                       // 0 uni, 1 uni_w, 2 avg, 3 w_avg
+    int mode;                       // 0 uni, 1 uni_w, 2 avg, 3 w_avg, 4 GPM blend
     int wgt0 = 0, wgt1 = 0, off = 0, sh = 0, ox = 0;
     const int l_uni = (b.pred_flag & 1) ? 0 : 1;
-    if (b.pred_flag != 3) {
+    // GPM weight addressing of pred_gpm_blk (vvc_inter.c:466-505): weight of luma position (X, Y) inside the coding unit
+    const uint8_t *gpm_w = nullptr;
+    int gpm_x = 0, gpm_y = 0, gpm_sx = 1, gpm_sy = 1;
+    if (gpm) {
+        const int pidx = b.aux & 63, lw = (b.aux >> 6) & 3, lh = (b.aux >> 8) & 3;
+        const int angle = VVC_GPM_ANGLE_IDX[pidx], mirror = VVC_GPM_ANGLE_TO_MIRROR[angle];
+        const int off_x = VVC_GPM_WEIGHTS_OFFSET_X[(pidx * 4 + lh) * 4 + lw], off_y = VVC_GPM_WEIGHTS_OFFSET_Y[(pidx * 4 + lh) * 4 + lw];
+        gpm_w = VVC_GPM_WEIGHTS + VVC_GPM_ANGLE_TO_WEIGHTS_IDX[angle] * 112 * 112;
+        gpm_sx = mirror == 1 ? -1 : 1;
+        gpm_sy = mirror == 2 ? -1 : 1;
+        gpm_x = (mirror == 1 ? 111 - off_x : off_x) + gpm_sx * (int)(((b.aux >> 10) & 15) << 2);
+        gpm_y = (mirror == 2 ? 111 - off_y : off_y) + gpm_sy * (int)(((b.aux >> 14) & 15) << 2);
+        mode = 4;
+        sh = max(5, 17 - bd);
+        off = 1 << (sh - 1);
+    } else if (b.pred_flag != 3) {
         sh = 14 - bd;
         if (b.flags & VVCB200_PB_WP) {
             mode = 1;
@@ -519,8 +586,12 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
                 r = (((l_uni == 0 ? v0[k] : v1[k]) * wgt0 + off) >> sh) + ox;
             else if (mode == 2)
                 r = (v0[k] + v1[k] + off) >> sh;
-            else
+            else if (mode == 3)
                 r = (v0[k] * wgt0 + v1[k] * wgt1 + off) >> sh;
+            else {
+                const int wg = gpm_w[(gpm_y + gpm_sy * (y << hs)) * 112 + gpm_x + gpm_sx * (x << hs)];
+                r = (v0[k] * wg + v1[k] * (8 - wg) + off) >> sh;
+            }
             r = clip_pixel(r, bd);
             if (lmcs)
                 r = __ldg(a.lmcs_fwd + r);
@@ -610,7 +681,7 @@ using namespace vvcb200;
 extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes *refs, int n_refs,
                                    const VVCB200PredBlock *d_blocks, int n, const VVCB200InterParams *params,
                                    const uint16_t *d_lmcs_fwd_lut, const VVCB200Planes *d_tmp14, int32_t *d_refined_mv,
-                                   void *stream)
+                                   const VVCB200ProfTable *d_prof, void *stream)
 {
     if (!params || (!dst && !d_tmp14) || !refs || n_refs <= 0 || n_refs > kMaxRefs || n < 0 || (n && !d_blocks)) {
         set_error("vvcb200_inter_batch: bad argument (n_refs must be 1..%d)", kMaxRefs);
@@ -644,6 +715,7 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     a.blocks = d_blocks;
     a.lmcs_fwd = d_lmcs_fwd_lut;
     a.refined_mv = d_refined_mv;
+    a.prof = d_prof;
     a.n = n;
     a.n16 = params->n_w16;
     a.n8 = params->n_w8;

@@ -167,10 +167,11 @@ class Context:
         ptrs, strides = self._plane_args(planes)
         check(load().vvcb200_pic_download(self._h, int(slot), ptrs, strides))
 
-    def inter(self, blocks, params, lmcs_fwd_lut=None, refined_mv=None):
+    def inter(self, blocks, params, lmcs_fwd_lut=None, refined_mv=None, prof=None):
         assert blocks.dtype == abi.PB_DTYPE
         check(load().vvcb200_pic_inter(self._h, _ptr(blocks), len(blocks), C.byref(params), _ptr(lmcs_fwd_lut),
-                                       _ptr(refined_mv)))
+                                       _ptr(refined_mv), _ptr(prof) if prof is not None and len(prof) else None,
+                                       len(prof) if prof is not None else 0))
 
     def residual(self, levels, tbs, params):
         assert levels.dtype == np.int16 and tbs.dtype == abi.TB_DTYPE
@@ -189,12 +190,12 @@ class Context:
         check(load().vvcb200_pic_sao_alf(self._h, _ptr(sao), _ptr(alf), _ptr(alf_params), int(ctb_log2)))
 
 
-def inter_batch(dst, refs, blocks, n, params, lmcs_fwd_lut=None, tmp14=None, refined_mv=None, stream=None):
+def inter_batch(dst, refs, blocks, n, params, lmcs_fwd_lut=None, tmp14=None, refined_mv=None, prof=None, stream=None):
     """vvcb200_inter_batch: dst/tmp14 device_planes() structs, refs list of device_planes(), blocks device tensor."""
     ra = abi.planes_array(refs)
     check(load().vvcb200_inter_batch(
         C.byref(dst) if dst is not None else None, ra, len(refs), _ptr(blocks), int(n), C.byref(params),
-        _ptr(lmcs_fwd_lut), C.byref(tmp14) if tmp14 is not None else None, _ptr(refined_mv), _stream(stream)))
+        _ptr(lmcs_fwd_lut), C.byref(tmp14) if tmp14 is not None else None, _ptr(refined_mv), _ptr(prof), _stream(stream)))
 
 
 def _ptr_grid(tabs, shape):

@@ -455,3 +455,112 @@ def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, 
         out["lmcs"] = lmcs_luts(seed + 4)
         inter["blocks"]["flags"] |= abi.PB_LMCS
     return out
+
+
+# ---- CU-level inter description (affine + PROF, GPM) and its expansion into engine records ------------------------
+CU_DTYPE = np.dtype([
+    ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("kind", "<i4"), ("flags", "<i4"), ("pred_flag", "<i4"),
+    ("bcw_idx", "<i4"), ("ref_idx", "<i4", (2,)), ("mv", "<i4", (2, 2)), ("gpm_partition_idx", "<i4"),
+    ("gpm_list", "<i4", (2,)), ("cb_prof_flag", "<i4", (2,)), ("diff_mv_x", "i1", (2, 16)), ("diff_mv_y", "i1", (2, 16)),
+    ("sb_mv_off", "<i4"),
+])                                  # mirrors VVCRefInterCU (oracle/ref/api_common.h)
+CU_REGULAR, CU_AFFINE, CU_GPM = 0, 1, 2
+
+
+def _round_mv_half(v):
+    """ff_vvc_round_mv(mv, 0, 1): halve, rounding half away from zero (reference vvc_mvs.c:1739-1749)."""
+    return (v + 1 - (v >= 0)) >> 1
+
+
+def inter_cu_picture(seed, width, height, n_refs=2, kinds=(CU_REGULAR, CU_AFFINE, CU_GPM), lmcs=False):
+    """Random coding units of all three inter kinds tiling the picture; returns the CU-level arrays the reference
+    harness consumes (`cus`, `sb_mv`) and the expanded engine batch (`blocks`, `prof`), plus params / refs."""
+    rng = np.random.default_rng(seed)
+    tiles = random_tiling(rng, width, height, 64, 8, mean_log2=4.2)
+    cus = np.zeros(len(tiles), CU_DTYPE)
+    sb_mv, blocks, prof = [], [], []
+    ld = (int(rng.integers(0, 8)), int(rng.integers(0, 8)))
+    for i, (x, y, w, h) in enumerate(tiles):
+        c = cus[i]
+        c["x0"], c["y0"], c["w"], c["h"] = x, y, w, h
+        ratio_ok = max(w, h) // min(w, h) < 8
+        kind = int(rng.choice(kinds))
+        if kind == CU_GPM and not ratio_ok:
+            kind = CU_AFFINE if CU_AFFINE in kinds else CU_REGULAR
+        if kind == CU_REGULAR and (w > 16 or h > 16):
+            kind = CU_AFFINE if CU_AFFINE in kinds else CU_GPM
+            if kind == CU_GPM and not ratio_ok:
+                kind = CU_REGULAR
+        c["kind"] = kind
+        pf = int(rng.integers(1, 4))
+        c["pred_flag"] = pf if kind != CU_GPM else 3
+        c["ref_idx"] = rng.integers(0, n_refs, 2)
+        c["mv"] = rng.integers(-48 * 16, 48 * 16 + 1, (2, 2))
+        flags = (abi.PB_WP if rng.random() < 0.3 and kind != CU_GPM else 0) | (abi.PB_LMCS if lmcs else 0)
+        if kind == CU_REGULAR and rng.random() < 0.3:
+            flags |= abi.PB_HPEL_IF
+        c["flags"] = flags
+        if pf == 3 and kind != CU_GPM and rng.random() < 0.3:
+            c["bcw_idx"] = int(rng.integers(1, 5))
+        if kind == CU_REGULAR:
+            if w > 16 or h > 16:        # only reached when no other kind is allowed: keep the reference's one-sub-block view legal
+                c["w"], c["h"] = w, h = min(w, 16), min(h, 16)
+            b = np.zeros(1, abi.PB_DTYPE)
+            b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x, y, w, h, pf, c["bcw_idx"]
+            b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags
+            blocks.append(b)
+        elif kind == CU_GPM:
+            c["gpm_partition_idx"] = int(rng.integers(0, 64))
+            c["gpm_list"] = rng.integers(0, 2, 2)
+            for ty in range(0, h, 16):
+                for tx in range(0, w, 16):
+                    b = np.zeros(1, abi.PB_DTYPE)
+                    b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), 3
+                    b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags | abi.PB_GPM
+                    b["aux"] = abi.gpm_aux(int(c["gpm_partition_idx"]), int(np.log2(w)), int(np.log2(h)), tx, ty,
+                                           int(c["gpm_list"][0]), int(c["gpm_list"][1]))
+                    blocks.append(b)
+        else:
+            nsx, nsy = w // 4, h // 4
+            c["sb_mv_off"] = len(sb_mv)
+            base = c["mv"].astype(np.int64)
+            gx = rng.integers(-6, 7, (2, 2))
+            gy = rng.integers(-6, 7, (2, 2))
+            prof_idx = len(prof)
+            c["cb_prof_flag"] = rng.integers(0, 2, 2)
+            pt = np.zeros(1, abi.PROF_DTYPE)
+            pt["diff_mv_x"] = c["diff_mv_x"] = rng.integers(-31, 32, (2, 16))
+            pt["diff_mv_y"] = c["diff_mv_y"] = rng.integers(-31, 32, (2, 16))
+            prof.append(pt)
+            mvs = np.zeros((nsy, nsx, 2, 2), np.int64)
+            for sy in range(nsy):
+                for sx in range(nsx):
+                    mvs[sy, sx] = np.clip(base + gx * sx + gy * sy, -(1 << 17), (1 << 17) - 1)
+                    sb_mv.append(mvs[sy, sx].astype(np.int32))
+            pflags = (abi.PB_PROF0 if c["cb_prof_flag"][0] else 0) | (abi.PB_PROF1 if c["cb_prof_flag"][1] else 0)
+            for sy in range(nsy):
+                for sx in range(nsx):
+                    b = np.zeros(1, abi.PB_DTYPE)
+                    b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 4, 4, pf, c["bcw_idx"]
+                    b["ref_idx"], b["mv"] = c["ref_idx"], mvs[sy, sx]
+                    b["flags"] = flags | abi.PB_AFFINE | abi.PB_LUMA_ONLY | pflags
+                    b["aux"] = prof_idx
+                    blocks.append(b)
+                    if not (sx & 1) and not (sy & 1):       # derive_affine_mvc: average with the diagonal neighbour
+                        b = np.zeros(1, abi.PB_DTYPE)
+                        b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 8, 8, pf, c["bcw_idx"]
+                        b["ref_idx"], b["mv"] = c["ref_idx"], _round_mv_half(mvs[sy, sx] + mvs[sy + 1, sx + 1])
+                        b["flags"] = (flags & ~abi.PB_LMCS) | abi.PB_CHROMA_ONLY
+                        blocks.append(b)
+    weight = np.zeros((2, 3, 16), np.int16)
+    offset = rng.integers(-64, 64, (2, 3, 16)).astype(np.int16)
+    weight[:, 0, :] = (1 << ld[0]) + rng.integers(-128, 128, (2, 16))
+    weight[:, 1:, :] = (1 << ld[1]) + rng.integers(-128, 128, (2, 2, 16))
+    ref_slot = np.zeros((2, 16), np.uint8)
+    ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
+    params = abi.inter_params(10, ld, weight, offset, ref_slot)
+    blocks = abi.order_blocks_by_width(np.concatenate(blocks), params)
+    dims = plane_dims(width, height)
+    refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
+    return dict(cus=cus, sb_mv=np.array(sb_mv, np.int32).reshape(-1, 2, 2), blocks=blocks,
+                prof=np.concatenate(prof) if prof else np.zeros(0, abi.PROF_DTYPE), params=params, refs=refs, dims=dims, seed=seed)

@@ -156,7 +156,17 @@ enum {
     VVCB200_PB_DMVR        = 1 << 6,  /* pu->dmvr_flag                                                                 */
     VVCB200_PB_CIIP        = 1 << 7,  /* cu->ciip_flag: BCW is ignored (vvc_inter.c:151), blend happens in RECON       */
     VVCB200_PB_LMCS        = 1 << 8,  /* forward LMCS on the luma prediction (vvc_inter.c:888-891)                     */
+    VVCB200_PB_GPM         = 1 << 9,  /* geometric partition (pred_gpm_blk, vvc_inter.c:466-521): `aux` is VVCB200_GPM_AUX  */
+    VVCB200_PB_PROF0       = 1 << 10, /* pu->cb_prof_flag[0]: PROF on list 0 (affine 4x4 luma records); `aux` = table index */
+    VVCB200_PB_PROF1       = 1 << 11, /* pu->cb_prof_flag[1]                                                               */
 };
+
+/* `aux` of a GPM record.  A GPM coding unit is emitted as <= 16x16 records that all carry the CU's partition and
+ * size plus their own offset inside the CU (the blend weight depends on the position inside the CU).  mv[i] / ref_idx[i]
+ * are gpm_mv[i] (PredictionUnit.gpm_mv, vvc_ctu.h:258); list_i says which reference list gpm_mv[i] uses. */
+#define VVCB200_GPM_AUX(partition_idx, log2_cb_w, log2_cb_h, off_x, off_y, list0, list1)               \
+    ((uint32_t)(partition_idx) | ((uint32_t)((log2_cb_w) - 3) << 6) | ((uint32_t)((log2_cb_h) - 3) << 8) |   \
+     ((uint32_t)((off_x) >> 2) << 10) | ((uint32_t)((off_y) >> 2) << 14) | ((uint32_t)(list0) << 18) | ((uint32_t)(list1) << 19))
 
 typedef struct VVCB200PredBlock {
     uint16_t x0, y0;        /* luma position                                                   */
@@ -166,8 +176,15 @@ typedef struct VVCB200PredBlock {
     int8_t   ref_idx[2];    /* MvField.ref_idx                                                 */
     uint16_t flags;         /* VVCB200_PB_*                                                    */
     int32_t  mv[2][2];      /* MvField.mv[list] = {x, y} in 1/16 luma sample, 18-bit           */
-    uint32_t reserved;
+    uint32_t aux;           /* GPM: VVCB200_GPM_AUX(...); PROF: index of the CU's table in d_prof */
 } VVCB200PredBlock;         /* 32 bytes */
+
+/* PROF offsets of one affine coding unit: PredictionUnit.diff_mv_x / diff_mv_y (vvc_ctu.h:266-267, derived by the
+ * host in vvc_mvs.c:361-378), values in [-31, 31]. */
+typedef struct VVCB200ProfTable {
+    int8_t diff_mv_x[2][16];    /* [list][y * 4 + x] */
+    int8_t diff_mv_y[2][16];
+} VVCB200ProfTable;             /* 64 bytes */
 
 /* Per-slice constants of inter prediction: PredWeightTable (vvc_ps.h:135-143) and the RefPicList -> DPB map. */
 typedef struct VVCB200InterParams {
@@ -193,12 +210,15 @@ typedef struct VVCB200InterParams {
  * + dmvr_mv_refine, vvc_inter.c:642-748) and those flagged VVCB200_PB_BDOF the optical-flow blend (inter.bdof_fetch_samples
  * + inter.apply_bdof); d_refined_mv receives the vectors actually used — what the reference stores in tab_dmvr_mvf
  * (vvc_inter.c:750-762) for the host's later MV derivation.
+ * Affine coding units arrive as 4x4 luma-only records (filter set 2, optional PROF: inter.fetch_samples + apply_prof*,
+ * vvc_inter.c:369-445) plus chroma-only records carrying the averaged vector of derive_affine_mvc (vvc_inter.c:813-826);
+ * GPM coding units as VVCB200_PB_GPM records (inter.put_gpm, vvc_inter_template.c:78-98).
  */
 VVCB200_API int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes *refs, int n_refs,
                                     const VVCB200PredBlock *d_blocks, int n, const VVCB200InterParams *params /* host */,
                                     const uint16_t *d_lmcs_fwd_lut /* 1 << bit_depth entries, or NULL */,
                                     const VVCB200Planes *d_tmp14, int32_t *d_refined_mv /* n x 2 x 2, or NULL */,
-                                    void *stream);
+                                    const VVCB200ProfTable *d_prof /* PROF tables, or NULL */, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Deblocking (stages DEBLOCK_V / DEBLOCK_H, ff_vvc_deblock_vertical/horizontal, vvc_filter.c:861-1003,
@@ -331,7 +351,8 @@ VVCB200_API int vvcb200_pic_upload(VVCB200Ctx *ctx, int slot, const uint16_t *co
  * of this context.  lmcs_fwd_lut: host, 1 << bit_depth entries, or NULL. */
 VVCB200_API int vvcb200_pic_inter(VVCB200Ctx *ctx, const VVCB200PredBlock *blocks, int n,
                                   const VVCB200InterParams *params, const uint16_t *lmcs_fwd_lut,
-                                  int32_t *refined_mv /* host, n x 2 x 2, valid after vvcb200_ctx_sync(); or NULL */);
+                                  int32_t *refined_mv /* host, n x 2 x 2, valid after vvcb200_ctx_sync(); or NULL */,
+                                  const VVCB200ProfTable *prof, int n_prof /* host PROF tables, or NULL / 0 */);
 /* Stage RECON, residual part: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
 VVCB200_API int vvcb200_pic_residual(VVCB200Ctx *ctx, const int16_t *levels, size_t n_levels,
                                      const VVCB200TransformBlock *tbs, int n, const VVCB200ResidualParams *params);

@@ -7,6 +7,7 @@
  *   replicate-edge reference fetch                          libavcodec/videodsp_template.c:27-105 (== coordinate clamp)
  *   forward LMCS on the luma prediction                     libavcodec/vvc/vvc_filter_template.c:25-36, vvc_inter.c:888-891
  */
+#define VVC_TABLES_WITH_GPM_WEIGHTS
 #include "port_common.h"
 
 #define TMP_STRIDE 128          /* MAX_PB_SIZE */
@@ -251,14 +252,15 @@ static const int bcw_w_lut[5] = { 4, 5, 3, 10, -2 };
 
 static void predict_component(const PortPlanes *dst, const PortPlanes *refs, const VVCB200PredBlock *b,
                               const VVCB200InterParams *p, int c, const PortPlanes *tmp14,
-                              const int mv[2][2], int dmvr, int bdof)
+                              const int mv[2][2], int dmvr, int bdof, const VVCB200ProfTable *prof)
 {
     const int bd = p->bit_depth;
     const int hs = c ? 1 : 0, vs = c ? 1 : 0;
     const int w = b->w >> hs, h = b->h >> vs;
     const int x0 = b->x0 >> hs, y0 = b->y0 >> vs;
     const int taps = c ? 4 : 8;
-    const int set = c ? 0 : (b->flags & VVCB200_PB_AFFINE) ? 2 : (b->flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
+    const int gpm = !!(b->flags & VVCB200_PB_GPM);
+    const int set = (c || gpm) ? 0 : (b->flags & VVCB200_PB_AFFINE) ? 2 : (b->flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
     int16_t tmp[2][16 * TMP_STRIDE];
     uint16_t *out = (uint16_t *)(dst->plane[c] + (size_t)y0 * dst->stride[c]) + x0;
     const int ostride = dst->stride[c] / 2;
@@ -273,12 +275,33 @@ static void predict_component(const PortPlanes *dst, const PortPlanes *refs, con
         const int xi = x0 + (mvx >> (4 + hs)), yi = y0 + (mvy >> (4 + vs));
         const int8_t *hf = c ? VVC_CHROMA_FILTERS + (set * 32 + mx) * 4 : VVC_LUMA_FILTERS + (set * 16 + mx) * 8;
         const int8_t *vf = c ? VVC_CHROMA_FILTERS + (set * 32 + my) * 4 : VVC_LUMA_FILTERS + (set * 16 + my) * 8;
-        const PortPlanes *ref = &refs[p->ref_slot[l][b->ref_idx[l]]];
+        /* GPM: prediction l comes from gpm_mv[l], which names its own reference list (vvc_inter.c:507-509) */
+        const int list = gpm ? (b->aux >> (18 + l)) & 1 : l;
+        const PortPlanes *ref = &refs[p->ref_slot[list][b->ref_idx[l]]];
         Win win = full_window(ref, c);
         if (dmvr)       /* fetches are confined to what the un-refined vector would have read */
             win = dmvr_window(ref, c, x0 + (b->mv[l][0] >> (4 + hs)), y0 + (b->mv[l][1] >> (4 + vs)), w, h,
                               taps / 2 - 1, taps / 2);
         put_block(tmp[l], ref, c, xi, yi, w, h, hf, vf, mx, my, taps, bd, &win);
+        if (!c && prof && (b->flags & (l ? VVCB200_PB_PROF1 : VVCB200_PB_PROF0))) {
+            /* PROF (fetch_samples + apply_prof*, vvc_inter_template.c:130-235): the 4x4 prediction gets a ring of integer
+             * samples, gradients of the ringed block, and a per-sample offset gh * dmv_x + gv * dmv_y */
+            const VVCB200ProfTable *pt = &prof[b->aux];
+            const int ox = xi + (mx >> 3) - 1, oy = yi + (my >> 3) - 1;
+            const int limit = 1 << (bd + 1 > 13 ? bd + 1 : 13);
+            int16_t r[6 * 6];
+            for (int y = -1; y <= 4; y++)
+                for (int x = -1; x <= 4; x++)
+                    r[(y + 1) * 6 + x + 1] = (x < 0 || y < 0 || x >= 4 || y >= 4)
+                        ? ref_sample(ref, 0, ox + x + 1, oy + y + 1, &win) << (14 - bd) : tmp[l][y * TMP_STRIDE + x];
+            for (int y = 0; y < 4; y++)
+                for (int x = 0; x < 4; x++) {
+                    const int16_t *q = &r[(y + 1) * 6 + x + 1];
+                    const int gh = (q[1] >> 6) - (q[-1] >> 6), gv = (q[6] >> 6) - (q[-6] >> 6);
+                    const int di = gh * pt->diff_mv_x[l][y * 4 + x] + gv * pt->diff_mv_y[l][y * 4 + x];
+                    tmp[l][y * TMP_STRIDE + x] = q[0] + port_clip(di, -limit, limit - 1);
+                }
+        }
         if (bdof && !c) {
             /* the 14-bit prediction plus a ring of integer samples at the rounded position (bdof_fetch_samples) */
             const int ox = xi + (mx >> 3) - 1, oy = yi + (my >> 3) - 1;
@@ -299,6 +322,25 @@ static void predict_component(const PortPlanes *dst, const PortPlanes *refs, con
     }
     if (bdof && !c) {
         bdof_block(out, ostride, (const int16_t (*)[BS * BS])ring, w, h, bd);
+        return;
+    }
+    if (gpm) {
+        /* put_gpm (vvc_inter_template.c:78-98) with the weight addressing of pred_gpm_blk (vvc_inter.c:466-505) */
+        const int pidx = b->aux & 63, lw = (b->aux >> 6) & 3, lh = (b->aux >> 8) & 3;
+        const int cu_x = ((b->aux >> 10) & 15) << 2, cu_y = ((b->aux >> 14) & 15) << 2;     /* luma offset inside the CU */
+        const int angle = VVC_GPM_ANGLE_IDX[pidx];
+        const uint8_t *wt = VVC_GPM_WEIGHTS + VVC_GPM_ANGLE_TO_WEIGHTS_IDX[angle] * 112 * 112;
+        const int off_x = VVC_GPM_WEIGHTS_OFFSET_X[(pidx * 4 + lh) * 4 + lw], off_y = VVC_GPM_WEIGHTS_OFFSET_Y[(pidx * 4 + lh) * 4 + lw];
+        const int mirror = VVC_GPM_ANGLE_TO_MIRROR[angle];
+        const int shift = 17 - bd > 5 ? 17 - bd : 5, offset = 1 << (shift - 1);
+        for (int y = 0; y < h; y++)
+            for (int x = 0; x < w; x++) {
+                const int X = cu_x + (x << hs), Y = cu_y + (y << vs);              /* luma position inside the CU */
+                const int wx = mirror == 1 ? 111 - off_x - X : off_x + X;
+                const int wy = mirror == 2 ? 111 - off_y - Y : off_y + Y;
+                const int wgt = wt[wy * 112 + wx];
+                out[y * ostride + x] = port_clip_pixel((tmp[0][y * TMP_STRIDE + x] * wgt + tmp[1][y * TMP_STRIDE + x] * (8 - wgt) + offset) >> shift, bd);
+            }
         return;
     }
     if (b->pred_flag != 3) {
@@ -347,7 +389,8 @@ static void predict_component(const PortPlanes *dst, const PortPlanes *refs, con
 /* refined_mv (optional, n x 2 x 2): the vectors actually used, i.e. what the reference stores in tab_dmvr_mvf */
 PORT_EXPORT int port_inter_batch(const PortPlanes *dst, const PortPlanes *refs, int n_refs,
                                  const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *p,
-                                 const uint16_t *lmcs_fwd_lut, const PortPlanes *tmp14, int32_t *refined_mv)
+                                 const uint16_t *lmcs_fwd_lut, const PortPlanes *tmp14, int32_t *refined_mv,
+                                 const VVCB200ProfTable *prof)
 {
     (void)n_refs;
     for (int i = 0; i < n; i++) {
@@ -361,7 +404,7 @@ PORT_EXPORT int port_inter_batch(const PortPlanes *dst, const PortPlanes *refs, 
             for (int k = 0; k < 4; k++)
                 refined_mv[i * 4 + k] = mv[k >> 1][k & 1];
         if (!(b->flags & VVCB200_PB_CHROMA_ONLY)) {
-            predict_component(dst, refs, b, p, 0, tmp14, mv, dmvr, bdof);
+            predict_component(dst, refs, b, p, 0, tmp14, mv, dmvr, bdof, prof);
             if ((b->flags & VVCB200_PB_LMCS) && lmcs_fwd_lut && !tmp14) {
                 for (int y = 0; y < b->h; y++) {
                     uint16_t *o = (uint16_t *)(dst->plane[0] + (size_t)(b->y0 + y) * dst->stride[0]) + b->x0;
@@ -371,8 +414,8 @@ PORT_EXPORT int port_inter_batch(const PortPlanes *dst, const PortPlanes *refs, 
             }
         }
         if (!(b->flags & VVCB200_PB_LUMA_ONLY)) {
-            predict_component(dst, refs, b, p, 1, tmp14, mv, dmvr, 0);
-            predict_component(dst, refs, b, p, 2, tmp14, mv, dmvr, 0);
+            predict_component(dst, refs, b, p, 1, tmp14, mv, dmvr, 0, prof);
+            predict_component(dst, refs, b, p, 2, tmp14, mv, dmvr, 0, prof);
         }
     }
     return 0;

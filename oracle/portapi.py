@@ -45,7 +45,7 @@ def residual_batch(planes, levels, tbs, params, want_residual=False):
     return res
 
 
-def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None, want_refined_mv=False):
+def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None, want_refined_mv=False, prof=None):
     pl = abi.host_planes(dst)
     ra = abi.planes_array([abi.host_planes(r) for r in refs])
     blocks = np.ascontiguousarray(blocks, abi.PB_DTYPE)
@@ -57,7 +57,8 @@ def inter_batch(dst, refs, blocks, params, lmcs_fwd_lut=None, tmp14=None, want_r
     lib().port_inter_batch(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks), C.byref(params),
                            C.c_void_p(lut.ctypes.data) if lut is not None else None,
                            C.byref(t14) if t14 is not None else None,
-                           C.c_void_p(mv.ctypes.data) if mv is not None else None)
+                           C.c_void_p(mv.ctypes.data) if mv is not None else None,
+                           C.c_void_p(np.ascontiguousarray(prof).ctypes.data) if prof is not None and len(prof) else None)
     return mv
 
 

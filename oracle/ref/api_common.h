@@ -15,4 +15,19 @@ typedef struct VVCRefPlanes {
     int32_t   width[3];
     int32_t   height[3];
 } VVCRefPlanes;
+
+/* CU-level description of an inter coding unit, for driving predict_inter() (vvc_inter.c:875-892) on affine and GPM
+ * units, which the reference expands into sub-blocks itself.  Test-side only; the engine receives the expanded records. */
+typedef struct VVCRefInterCU {
+    int32_t x0, y0, w, h;
+    int32_t kind;               /* 0 regular (one sub-block), 1 affine, 2 GPM */
+    int32_t flags;              /* VVCB200_PB_WP / HPEL_IF / BDOF / DMVR / LMCS */
+    int32_t pred_flag, bcw_idx;
+    int32_t ref_idx[2];
+    int32_t mv[2][2];           /* regular: MvField.mv; GPM: gpm_mv[i].mv[gpm_list[i]] */
+    int32_t gpm_partition_idx, gpm_list[2];
+    int32_t cb_prof_flag[2];
+    int8_t  diff_mv_x[2][16], diff_mv_y[2][16];
+    int32_t sb_mv_off;          /* affine: first entry of this CU's 4x4 sub-block vectors in `sb_mv` (raster, int32[2][2] each) */
+} VVCRefInterCU;
 #endif

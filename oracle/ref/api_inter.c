@@ -160,3 +160,148 @@ VVCREF_EXPORT void vvcref_put(int bd, int is_chroma, int16_t *dst, const uint8_t
     ff_vvc_dsp_init(&c, bd);
     c.inter.put[is_chroma][av_log2(w) - 1][!!my][!!mx](dst, src, src_stride, h, hf, vf, w);
 }
+
+/*
+ * INTER stage for CU-level descriptions (regular, affine + PROF, GPM) through the reference's own predict_inter():
+ * the reference splits affine units into 4x4 sub-blocks, averages vectors for chroma (derive_affine_mvc) and blends
+ * GPM partitions itself.  sb_mv: affine sub-block vectors, see VVCRefInterCU.sb_mv_off.
+ */
+VVCREF_EXPORT int vvcref_inter_cus(const VVCRefPlanes *dst, const VVCRefPlanes *refs, int n_refs,
+                                   const VVCRefInterCU *cus, int n, const int32_t *sb_mv,
+                                   const VVCB200InterParams *p, const uint16_t *lmcs_fwd_lut)
+{
+    InterEnv *e         = calloc(1, sizeof(*e));
+    VVCLocalContext *lc = NULL;
+    int ret             = -1;
+    int min_pu_width, min_pu_height;
+
+    if (!e || n_refs > 16 || !(lc = aligned_alloc(64, (sizeof(*lc) + 63) & ~(size_t)63)))
+        return -1;
+    memset(lc, 0, sizeof(*lc));
+    e->fc.frame   = &e->frame;
+    e->fc.ps.sps  = &e->sps;
+    e->fc.ps.pps  = &e->pps;
+    e->fc.ps.ph.r = &e->rph;
+    e->fc.ref     = &e->cur;
+    e->sps.r      = &e->rsps;
+    e->pps.r      = &e->rpps;
+    e->sc.sh.r    = &e->rsh;
+    e->sc.rpl     = e->rpl;
+    lc->fc        = &e->fc;
+    lc->sc        = &e->sc;
+    lc->cu        = &e->cu;
+    for (int c = 0; c < 3; c++) {
+        e->frame.data[c]     = dst->plane[c];
+        e->frame.linesize[c] = dst->stride[c];
+    }
+    e->sps.width  = e->pps.width  = dst->width[0];
+    e->sps.height = e->pps.height = dst->height[0];
+    e->sps.bit_depth        = p->bit_depth;
+    e->sps.pixel_shift      = 1;
+    e->sps.hshift[1] = e->sps.hshift[2] = 1;
+    e->sps.vshift[1] = e->sps.vshift[2] = 1;
+    e->sps.ctb_log2_size_y  = 7;
+    e->sps.ctb_size_y       = 128;
+    e->rsps.sps_chroma_format_idc = 1;
+    e->rsh.sh_slice_type    = VVC_SLICE_TYPE_B;
+    min_pu_width  = e->pps.min_pu_width  = (dst->width[0]  + 3) >> 2;
+    min_pu_height = e->pps.min_pu_height = (dst->height[0] + 3) >> 2;
+    e->fc.tab.mvf        = calloc((size_t)min_pu_width * min_pu_height, sizeof(MvField));
+    e->cur.tab_dmvr_mvf  = calloc((size_t)min_pu_width * min_pu_height, sizeof(MvField));
+    if (!e->fc.tab.mvf || !e->cur.tab_dmvr_mvf)
+        goto end;
+    ff_vvc_dsp_init(&e->fc.vvcdsp, p->bit_depth);
+    ff_videodsp_init(&e->fc.vdsp, p->bit_depth);
+    for (int i = 0; i < n_refs; i++) {
+        for (int c = 0; c < 3; c++) {
+            e->ref_frames[i].data[c]     = refs[i].plane[c];
+            e->ref_frames[i].linesize[c] = refs[i].stride[c];
+        }
+        e->refs[i].frame = &e->ref_frames[i];
+    }
+    for (int l = 0; l < 2; l++)
+        for (int i = 0; i < 15; i++)
+            e->rpl[l].ref[i] = p->ref_slot[l][i] < n_refs ? &e->refs[p->ref_slot[l][i]] : NULL;
+    {
+        PredWeightTable *w = &e->sc.sh.pwt;
+        w->log2_denom[0] = p->log2_denom[0];
+        w->log2_denom[1] = p->log2_denom[1];
+        for (int l = 0; l < 2; l++)
+            for (int c = 0; c < 3; c++)
+                for (int i = 0; i < MAX_WEIGHTS; i++) {
+                    w->weight[l][c][i] = p->weight[l][c][i];
+                    w->offset[l][c][i] = p->offset[l][c][i];
+                }
+    }
+    if (lmcs_fwd_lut)
+        memcpy(e->fc.ps.lmcs.fwd_lut, lmcs_fwd_lut, sizeof(uint16_t) << p->bit_depth);
+
+    for (int i = 0; i < n; i++) {
+        const VVCRefInterCU *d = &cus[i];
+        CodingUnit *cu = &e->cu;
+        PredictionUnit *pu = &cu->pu;
+        MvField mvf = { 0 };
+
+        memset(cu, 0, sizeof(*cu));
+        cu->x0 = d->x0; cu->y0 = d->y0; cu->cb_width = d->w; cu->cb_height = d->h;
+        cu->pred_mode = MODE_INTER;
+        pu->mi.hpel_if_idx = !!(d->flags & VVCB200_PB_HPEL_IF);
+        pu->mi.pred_flag   = d->pred_flag;
+        pu->bdof_flag      = !!(d->flags & VVCB200_PB_BDOF);
+        pu->dmvr_flag      = !!(d->flags & VVCB200_PB_DMVR);
+        e->rpps.pps_weighted_bipred_flag = !!(d->flags & VVCB200_PB_WP);
+        e->rsh.sh_lmcs_used_flag         = !!(d->flags & VVCB200_PB_LMCS);
+        mvf.pred_flag   = d->pred_flag;
+        mvf.bcw_idx     = d->bcw_idx;
+        mvf.hpel_if_idx = pu->mi.hpel_if_idx;
+        for (int l = 0; l < 2; l++) {
+            mvf.mv[l].x    = d->mv[l][0];
+            mvf.mv[l].y    = d->mv[l][1];
+            mvf.ref_idx[l] = d->ref_idx[l];
+        }
+        if (d->kind == 1) {
+            const int32_t *sb = sb_mv + (size_t)d->sb_mv_off * 4;
+            pu->inter_affine_flag = 1;
+            pu->mi.num_sb_x = d->w >> 2;
+            pu->mi.num_sb_y = d->h >> 2;
+            for (int l = 0; l < 2; l++) {
+                pu->cb_prof_flag[l] = d->cb_prof_flag[l];
+                for (int k = 0; k < 16; k++) {
+                    pu->diff_mv_x[l][k] = d->diff_mv_x[l][k];
+                    pu->diff_mv_y[l][k] = d->diff_mv_y[l][k];
+                }
+            }
+            for (int sy = 0; sy < pu->mi.num_sb_y; sy++)
+                for (int sx = 0; sx < pu->mi.num_sb_x; sx++, sb += 4) {
+                    MvField m = mvf;
+                    m.mv[0].x = sb[0]; m.mv[0].y = sb[1]; m.mv[1].x = sb[2]; m.mv[1].y = sb[3];
+                    e->fc.tab.mvf[((d->y0 >> 2) + sy) * min_pu_width + (d->x0 >> 2) + sx] = m;
+                }
+        } else {
+            pu->mi.num_sb_x = pu->mi.num_sb_y = 1;
+            if (d->kind == 2) {
+                pu->merge_gpm_flag    = 1;
+                pu->gpm_partition_idx = d->gpm_partition_idx;
+                for (int k = 0; k < 2; k++) {
+                    const int lx = d->gpm_list[k];
+                    memset(&pu->gpm_mv[k], 0, sizeof(pu->gpm_mv[k]));
+                    pu->gpm_mv[k].pred_flag   = lx + PF_L0;
+                    pu->gpm_mv[k].ref_idx[lx] = d->ref_idx[k];
+                    pu->gpm_mv[k].mv[lx].x    = d->mv[k][0];
+                    pu->gpm_mv[k].mv[lx].y    = d->mv[k][1];
+                }
+            }
+            for (int y = d->y0 >> 2; y < (d->y0 + d->h) >> 2; y++)
+                for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++)
+                    e->fc.tab.mvf[y * min_pu_width + x] = mvf;
+        }
+        predict_inter(lc);
+    }
+    ret = 0;
+end:
+    free(e->fc.tab.mvf);
+    free(e->cur.tab_dmvr_mvf);
+    free(lc);
+    free(e);
+    return ret;
+}

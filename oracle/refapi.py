@@ -160,3 +160,17 @@ def lmcs_picture(planes, inv_lut, ctb_log2=7, bit_depth=10, threads=1):
     chunks = _row_chunks(_ctb_rows(planes, ctb_log2), threads)
     _parallel(lambda a, b: lib().vvcref_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data), ctb_log2, bit_depth, a, b),
               chunks)
+
+
+def inter_cus(dst, refs, cus, sb_mv, params, lmcs_fwd_lut=None):
+    """Reference predict_inter() over CU-level descriptions (synth.inter_cu_picture)."""
+    pl = abi.host_planes(dst)
+    ra = abi.planes_array([abi.host_planes(r) for r in refs])
+    cus = np.ascontiguousarray(cus)
+    sb = np.ascontiguousarray(sb_mv, np.int32)
+    lut = None if lmcs_fwd_lut is None else np.ascontiguousarray(lmcs_fwd_lut, np.uint16)
+    r = lib().vvcref_inter_cus(C.byref(pl), ra, len(refs), C.c_void_p(cus.ctypes.data), len(cus),
+                               C.c_void_p(sb.ctypes.data) if sb.size else None, C.byref(params),
+                               C.c_void_p(lut.ctypes.data) if lut is not None else None)
+    if r != 0:
+        raise RuntimeError("vvcref_inter_cus failed")

@@ -129,3 +129,29 @@ def test_dmvr_bdof_match_oracle(seed):
     assert np.array_equal(mv_d.cpu().numpy(), want_mv)
     for c in range(3):
         assert np.array_equal(got[c], want[c]), "plane %d differs" % c
+
+
+@pytest.mark.parametrize("seed,kinds,lmcs", [(0, (0, 2), False), (1, (0, 1), False), (2, (0, 1, 2), True), (3, (2,), False),
+                                             (4, (1,), True)])
+def test_affine_prof_gpm_match_oracle(seed, kinds, lmcs):
+    """Affine + PROF and GPM coding units on the GPU (expanded records) against the reference's CU-level predict_inter()."""
+    import torch
+    pic = synth.inter_cu_picture(70 + seed, 416, 240, kinds=kinds, lmcs=lmcs)
+    lut = np.sort(np.random.default_rng(seed).integers(0, 1024, 1024)).astype(np.uint16) if lmcs else None
+    base = util.noise_planes(seed, pic["dims"])
+    want = [p.copy() for p in base]
+    if refapi.available():
+        refapi.inter_cus(want, pic["refs"], pic["cus"], pic["sb_mv"], pic["params"], lut)
+    else:
+        portapi.inter_batch(want, pic["refs"], pic["blocks"], pic["params"], lut, prof=pic["prof"])
+    dst = util.to_device_planes(base, torch)
+    refs = [util.to_device_planes(r, torch) for r in pic["refs"]]
+    blocks = torch.from_numpy(pic["blocks"].view(np.uint8).reshape(-1)).cuda()
+    prof = torch.from_numpy(pic["prof"].view(np.uint8).reshape(-1)).cuda() if len(pic["prof"]) else None
+    lib.inter_batch(lib.device_planes(dst), [lib.device_planes(r) for r in refs], blocks, len(pic["blocks"]),
+                    _params_for(pic), lmcs_fwd_lut=None if lut is None else torch.from_numpy(lut.view(np.int16)).cuda(),
+                    prof=prof)
+    torch.cuda.synchronize()
+    got = util.from_device_planes(dst)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs" % c

@@ -97,3 +97,17 @@ def test_port_dmvr_bdof_match_reference(seed):
         assert (mva != pic["blocks"]["mv"]).any()
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
+
+
+@needs_ref
+@pytest.mark.parametrize("seed,kinds", [(0, (0, 2)), (1, (0, 1)), (2, (0, 1, 2)), (3, (2,)), (4, (1,))])
+def test_port_affine_prof_gpm_match_reference(seed, kinds):
+    """Affine (4x4 sub-blocks, filter set 2, PROF, averaged chroma vectors) and GPM coding units: the reference expands
+    CU-level descriptions itself (pred_affine_blk / pred_gpm_blk); the port consumes the host-expanded records."""
+    pic = synth.inter_cu_picture(600 + seed, 208, 120, kinds=kinds)
+    base = util.noise_planes(seed, pic["dims"])
+    a, b = [p.copy() for p in base], [p.copy() for p in base]
+    refapi.inter_cus(a, pic["refs"], pic["cus"], pic["sb_mv"], pic["params"])
+    portapi.inter_batch(b, pic["refs"], pic["blocks"], pic["params"], prof=pic["prof"])
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
