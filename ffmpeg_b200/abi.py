@@ -182,3 +182,20 @@ ALF_PARAMS_DTYPE = np.dtype([
     ("chroma_coeff", "<i2", (8, 6)), ("chroma_clip_idx", "u1", (8, 6)),
     ("cc_coeff", "<i2", (2, 4, 7)), ("cc_enabled", "<i4", (2,)),
 ], align=True)
+
+
+# ---- intra --------------------------------------------------------------------------------------------------------
+IB_MIP, IB_MIP_TRANSPOSED, IB_ISP, IB_BDPCM, IB_RESIDUAL, IB_CIIP = 1, 2, 4, 8, 16, 32
+TB_TO_RESIDUAL = 512
+
+IB_DTYPE = np.dtype([
+    ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("c_idx", "u1"), ("mode", "i1"), ("ref_idx", "u1"),
+    ("flags", "u1"), ("mip_mode", "u1"), ("up_left", "u1"), ("avail_top", "<u2"), ("avail_left", "<u2"),
+    ("cb_w", "u1"), ("cb_h", "u1"), ("ciip_weight", "u1"), ("res_planes", "u1"), ("reserved2", "<u4", (2,)),
+], align=False)
+assert IB_DTYPE.itemsize == 28
+
+
+class IntraParams(C.Structure):
+    _fields_ = [("bit_depth", C.c_int32), ("ctb_log2_size", C.c_int32), ("chroma_vertical_collocated", C.c_int32),
+                ("reserved", C.c_int32)]

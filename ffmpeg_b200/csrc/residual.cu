@@ -309,7 +309,8 @@ struct Epilogue {
 __device__ __forceinline__ Epilogue make_epilogue(const ResidualArgs &a, const VVCB200TransformBlock &d)
 {
     Epilogue e;
-    const PlanesView &pv = a.to_residual ? a.res : a.dst;
+    const bool to_res = a.to_residual || (d.flags & VVCB200_TB_TO_RESIDUAL);
+    const PlanesView &pv = to_res ? a.res : a.dst;
     const int other = d.c_idx ? 3 - d.c_idx : 0;
     e.stride = pv.stride[d.c_idx];
     e.stride2 = pv.stride[other];
@@ -321,7 +322,7 @@ __device__ __forceinline__ Epilogue make_epilogue(const ResidualArgs &a, const V
     e.lscale = d.lmcs_scale;
     e.joint = (d.flags & VVCB200_TB_JOINT) && d.c_idx;
     e.lmcs = d.flags & VVCB200_TB_LMCS_SCALE;
-    e.to_residual = a.to_residual;
+    e.to_residual = to_res;
     return e;
 }
 
@@ -338,7 +339,7 @@ __device__ __forceinline__ void fast_block(const ResidualArgs &a, const ScalingL
     const int sh1 = 5 + a.range - a.bd;
     const bool dconly = d.trh == VVCB200_DCT2 && d.trv == VVCB200_DCT2 && nzw == 1 && nzh == 1 && w == h;
 
-    if (active && !a.to_residual && li < h)
+    if (active && !ep.to_residual && li < h)
         asm volatile("prefetch.global.L1 [%0];" ::"l"(ep.dst + li * ep.stride));
     // levels: coalesced fetch into the (still free) middle buffer
     if (active)
@@ -669,7 +670,7 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
         a.dst = make_view(dst);
     if (d_residual)
         a.res = make_view(d_residual);
-    a.to_residual = d_residual != nullptr;
+    a.to_residual = dst == nullptr;          // otherwise only the TBs flagged VVCB200_TB_TO_RESIDUAL go to the residual planes
     a.levels = d_levels;
     a.tbs = d_tbs;
     a.n = n;

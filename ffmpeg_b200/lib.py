@@ -88,6 +88,28 @@ def dsp_add_residual_batch(dst, res, block_off, tbs, n, bit_depth=10, stream=Non
                                                 int(bit_depth), _stream(stream)))
 
 
+def intra_scratch_bytes(width, height):
+    f = load().vvcb200_intra_scratch_bytes
+    f.restype = C.c_size_t
+    return int(f(int(width), int(height)))
+
+
+def intra_schedule(blocks, ctu_first, ctus_w, ctus_h):
+    """vvcb200_intra_schedule: per-CTU decoding-order records -> wavefront order (host helper, no GPU involved)."""
+    blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
+    ctu_first = np.ascontiguousarray(ctu_first, np.uint32)
+    assert len(ctu_first) == ctus_w * ctus_h + 1 and ctu_first[-1] == len(blocks)
+    out = np.zeros(len(blocks), abi.IB_DTYPE)
+    check(load().vvcb200_intra_schedule(_ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), _ptr(out)))
+    return out
+
+
+def intra_picture(pic, residual, blocks, n, params, scratch, stream=None):
+    """vvcb200_intra_picture: pic/residual are device_planes() structs, blocks/scratch device tensors."""
+    check(load().vvcb200_intra_picture(C.byref(pic), C.byref(residual) if residual is not None else None,
+                                       _ptr(blocks), int(n), C.byref(params), _ptr(scratch), _stream(stream)))
+
+
 # ---- Level B: picture engine ---------------------------------------------------------------------------
 class Context:
     """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use

@@ -564,3 +564,213 @@ def inter_cu_picture(seed, width, height, n_refs=2, kinds=(CU_REGULAR, CU_AFFINE
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     return dict(cus=cus, sb_mv=np.array(sb_mv, np.int32).reshape(-1, 2, 2), blocks=blocks,
                 prof=np.concatenate(prof) if prof else np.zeros(0, abi.PROF_DTYPE), params=params, refs=refs, dims=dims, seed=seed)
+
+
+# ---- pictures with intra coding units (CTU / CU / TU structure in decoding order) ---------------------------------------
+REF_CU_DTYPE = np.dtype([
+    ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("ctu", "<i4"), ("pred_mode", "<i4"),
+    ("intra_pred_mode_y", "<i4"), ("intra_pred_mode_c", "<i4"), ("intra_luma_ref_idx", "<i4"),
+    ("mip_flag", "<i4"), ("mip_transposed", "<i4"), ("mip_mode", "<i4"), ("mip_chroma_direct", "<i4"),
+    ("isp_split_type", "<i4"), ("num_intra_subpartitions", "<i4"), ("bdpcm_flag", "<i4", (3,)), ("ciip_flag", "<i4"),
+    ("coded_flag", "<i4"), ("first_tu", "<i4"), ("n_tu", "<i4"), ("mts_idx", "<i4"),
+])                                  # mirrors VVCRefCU (oracle/ref/api_common.h)
+REF_TU_DTYPE = np.dtype([
+    ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("coded_flag", "<i4", (3,)), ("joint", "<i4"),
+    ("tb", "<i4", (3,)),
+])                                  # mirrors VVCRefTU
+MODE_INTER, MODE_INTRA = 0, 1
+CCLM_LT, CCLM_L, CCLM_T = 81, 82, 83
+_MTS_OF = {(0, 0): 0, (1, 1): 1, (2, 1): 2, (1, 2): 3, (2, 2): 4}      # (trh, trv) -> mts_idx (vvc_intra.c:133-134)
+
+
+def _split_cu(rng, x, y, w, h, pw, ph, min_size, mean_log2, out):
+    """Recursive quad / binary partition of one CTU region in decoding (z) order, clipped to the picture."""
+    if x >= pw or y >= ph:
+        return
+    over = x + w > pw or y + h > ph
+    can_h, can_v = h > min_size, w > min_size
+    p = min(0.95, max(0.05, 0.5 + 0.35 * (np.log2(max(w, h)) - mean_log2)))
+    if not over and (max(w, h) <= 64) and (not (can_h or can_v) or rng.random() >= p):
+        out.append((x, y, w, h))
+        return
+    r = rng.random()
+    if w == h and can_h and can_v and (r < 0.5 or over or max(w, h) > 64):
+        for dy in (0, h // 2):
+            for dx in (0, w // 2):
+                _split_cu(rng, x + dx, y + dy, w // 2, h // 2, pw, ph, min_size, mean_log2, out)
+    elif can_h and (r < 0.75 or not can_v):
+        _split_cu(rng, x, y, w, h // 2, pw, ph, min_size, mean_log2, out)
+        _split_cu(rng, x, y + h // 2, w, h // 2, pw, ph, min_size, mean_log2, out)
+    else:
+        _split_cu(rng, x, y, w // 2, h, pw, ph, min_size, mean_log2, out)
+        _split_cu(rng, x + w // 2, y, w // 2, h, pw, ph, min_size, mean_log2, out)
+
+
+def _avail(mask, x, y, horizontal, limit):
+    """Run of reconstructed 4x4 units starting at unit (x, y) going right (horizontal) or down, in units, < limit."""
+    n = 0
+    if horizontal:
+        while x + n < limit and mask[y, x + n]:
+            n += 1
+    else:
+        while y + n < limit and mask[y + n, x]:
+            n += 1
+    return n
+
+
+def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
+                  mean_log2=4.3):
+    """A picture with intra and inter coding units.  Returns
+         ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
+         inter: prediction sub-block batch of the inter CUs (stage INTER),
+         residual: TB batch (TBs of intra CUs flagged TB_TO_RESIDUAL),
+         intra: VVCB200IntraBlock records + per-CTU ranges (stage RECON wavefront).
+    Neighbour availability follows the reference's rules (vvc_intra.c:593-648) on a 4x4-unit reconstruction mask."""
+    rng = np.random.default_rng(seed)
+    tools = set(tools)
+    ctb = 1 << ctb_log2
+    cw, ch = (width + ctb - 1) >> ctb_log2, (height + ctb - 1) >> ctb_log2
+    u4w, u4h = (width + 3) >> 2, (height + 3) >> 2
+    done = np.zeros((u4h, u4w), bool)               # luma and chroma become available together (single tree)
+    cus, tus, tbs, lv_chunks, intra_mode_tb = [], [], [], [], []
+    pblocks, iblocks, ctu_first = [], [], [0]
+    lv_off = 0
+
+    def new_tb(x, y, c, w, h, inter, trh=0, trv=0, qp=30, to_res=False):
+        nonlocal lv_off
+        nzw = int(rng.integers(1, min(w, 32 if trh == 0 else 16) + 1))
+        nzh = int(rng.integers(1, min(h, 32 if trv == 0 else 16) + 1))
+        lv = np.clip(np.rint(rng.laplace(0, 10, (nzh, nzw))), -200, 200).astype(np.int16)
+        lv[nzh - 1, nzw - 1] = lv[nzh - 1, nzw - 1] or 1
+        t = np.zeros(1, abi.TB_DTYPE)
+        t["x0"], t["y0"], t["c_idx"], t["log2_w"], t["log2_h"] = x, y, c, int(np.log2(w)), int(np.log2(h))
+        t["nzw"], t["nzh"], t["trh"], t["trv"], t["qp"] = nzw, nzh, trh, trv, qp
+        t["flags"] = (abi.TB_INTER if inter else 0) | (abi.TB_TO_RESIDUAL if to_res else 0)
+        t["coeff_off"] = lv_off
+        lv_chunks.append(lv.reshape(-1))
+        lv_off += lv.size
+        tbs.append(t)
+        return len(tbs) - 1
+
+    for ry in range(ch):
+        for rx in range(cw):
+            rs = ry * cw + rx
+            regions = []
+            _split_cu(rng, rx * ctb, ry * ctb, ctb, ctb, width, height, 8, mean_log2, regions)
+            ctb_left, ctb_up = rx > 0, ry > 0
+            for (x, y, w, h) in regions:
+                cu = np.zeros(1, REF_CU_DTYPE)
+                tu = np.zeros(1, REF_TU_DTYPE)
+                intra = rng.random() < intra_fraction
+                cu["x0"], cu["y0"], cu["w"], cu["h"], cu["ctu"] = x, y, w, h, rs
+                cu["pred_mode"] = MODE_INTRA if intra else MODE_INTER
+                cu["first_tu"], cu["n_tu"] = len(tus), 1
+                tu["x0"], tu["y0"], tu["w"], tu["h"] = x, y, w, h
+                coded = rng.random(3) < 0.8
+                tu["coded_flag"] = coded
+                cu["coded_flag"] = 1                    # the reference only skips reconstruct() for uncoded CUs
+                qp_y, qp_c = int(rng.integers(14, 60)), int(rng.integers(14, 60))
+                trh = trv = 0
+                if not intra or "mts" in tools:
+                    if 4 <= w <= 32 and 4 <= h <= 32 and rng.random() < 0.3:
+                        trh, trv = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
+                cu["mts_idx"] = _MTS_OF[(trh, trv)]
+                tu["tb"] = -1
+                if coded[0]:
+                    tu["tb"][0, 0] = new_tb(x, y, 0, w, h, not intra, trh, trv, qp_y, intra)
+                for c in (1, 2):
+                    if coded[c]:
+                        tu["tb"][0, c] = new_tb(x >> 1, y >> 1, c, w >> 1, h >> 1, not intra, 0, 0, qp_c, intra)
+                ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
+                if not intra:
+                    pf = int(rng.integers(1, 4))
+                    mv = rng.integers(-40 * 16, 40 * 16 + 1, (2, 2))
+                    ridx = rng.integers(0, n_refs, 2)
+                    for ty in range(0, h, 16):
+                        for tx in range(0, w, 16):
+                            b = np.zeros(1, abi.PB_DTYPE)
+                            b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
+                            b["ref_idx"], b["mv"] = ridx, mv
+                            pblocks.append(b)
+                else:
+                    x0b, y0b = x & (ctb - 1), y & (ctb - 1)
+                    cand_up, cand_left = ctb_up or y0b > 0, ctb_left or x0b > 0
+                    up_left = (cand_left and cand_up) if (x0b or y0b) else (ctb_left and ctb_up)
+                    end_x4 = min(width, (rx + 1) * ctb) >> 2
+                    end_y4 = min(height, (ry + 1) * ctb) >> 2
+                    if y0b == 0:
+                        top4 = (u4w - ux) if ctb_up else 0
+                    else:
+                        top4 = _avail(done, ux, uy - 1, True, end_x4)
+                    if x0b == 0:
+                        left4 = (end_y4 - uy) if ctb_left else 0
+                    else:
+                        left4 = _avail(done, ux - 1, uy, False, end_y4)
+                    # ---- luma mode
+                    mip = "mip" in tools and rng.random() < 0.15
+                    mode_y = int(rng.choice([0, 1, 18, 50] + list(range(2, 67))))
+                    ref_idx = 0
+                    if mip:
+                        cu["mip_flag"], cu["mip_transposed"] = 1, int(rng.integers(0, 2))
+                        size_id = 0 if (w == 4 and h == 4) else 1 if (w == 4 or h == 4 or (w == 8 and h == 8)) else 2
+                        cu["mip_mode"] = int(rng.integers(0, (16, 8, 6)[size_id]))
+                        mode_y = 0
+                    elif "mrl" in tools and y0b > 0 and mode_y != 0 and rng.random() < 0.2:
+                        ref_idx = int(rng.choice([1, 3]))
+                    cu["intra_pred_mode_y"], cu["intra_luma_ref_idx"] = mode_y, ref_idx
+                    # ---- chroma mode: planar / DC / hor / ver / DM / CCLM
+                    choices = [0, 1, 18, 50, mode_y] + ([CCLM_LT, CCLM_L, CCLM_T] if "cclm" in tools else [])
+                    mode_c = int(rng.choice(choices))
+                    cu["intra_pred_mode_c"] = mode_c
+                    for c in (0, 1, 2):
+                        hs = 1 if c else 0
+                        bw, bh = w >> hs, h >> hs
+                        raw = mode_y if c == 0 else mode_c
+                        if c == 2 and raw >= CCLM_LT:
+                            continue                      # the CCLM record of c_idx 1 covers Cr too
+                        ib = np.zeros(1, abi.IB_DTYPE)
+                        ib["x0"], ib["y0"], ib["w"], ib["h"], ib["c_idx"] = x >> hs, y >> hs, bw, bh, c
+                        ib["mode"] = raw if raw >= CCLM_LT else wide_angle_mode(raw, bw, bh, c)
+                        ib["ref_idx"] = ref_idx if c == 0 else 0
+                        fl = 0
+                        if c == 0 and mip:
+                            fl |= abi.IB_MIP | (abi.IB_MIP_TRANSPOSED if cu["mip_transposed"][0] else 0)
+                            ib["mip_mode"] = cu["mip_mode"][0]
+                        if raw >= CCLM_LT:
+                            fl |= (abi.IB_RESIDUAL if (coded[1] or coded[2]) else 0)
+                            ib["res_planes"] = (1 if coded[1] else 0) | (2 if coded[2] else 0)
+                        elif coded[c]:
+                            fl |= abi.IB_RESIDUAL
+                        ib["flags"] = fl
+                        ib["up_left"] = up_left
+                        ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
+                        ib["cb_w"], ib["cb_h"] = w, h
+                        iblocks.append(ib)
+                done[uy:uy + uh, ux:ux + uw] = True
+                cus.append(cu)
+                tus.append(tu)
+            ctu_first.append(len(iblocks))
+    tbs = np.concatenate(tbs) if tbs else np.zeros(0, abi.TB_DTYPE)
+    levels = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
+    rparams = abi.residual_params(10, 1)
+    order_cls = abi.residual_class(tbs)
+    area = tbs["log2_w"].astype(np.int32) + tbs["log2_h"]
+    order = np.lexsort((-area, order_cls))
+    for c in range(4):
+        rparams.n_class[c] = int(np.sum(order_cls == c))
+    ld = (0, 0)
+    ref_slot = np.zeros((2, 16), np.uint8)
+    ref_slot[:, :n_refs] = np.arange(n_refs)
+    iparams = abi.inter_params(10, ld, None, None, ref_slot)
+    pb = abi.order_blocks_by_width(np.concatenate(pblocks), iparams) if pblocks else np.zeros(0, abi.PB_DTYPE)
+    dims = plane_dims(width, height)
+    refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
+    ip = abi.IntraParams()
+    ip.bit_depth, ip.ctb_log2_size, ip.chroma_vertical_collocated = 10, ctb_log2, int(rng.integers(0, 2))
+    return dict(
+        ref=dict(cus=np.concatenate(cus), tus=np.concatenate(tus), tbs=tbs, levels=levels, params=rparams),
+        inter=dict(blocks=pb, params=iparams, refs=refs),
+        residual=dict(tbs=np.ascontiguousarray(tbs[order]), levels=levels, params=rparams),
+        intra=dict(blocks=np.concatenate(iblocks) if iblocks else np.zeros(0, abi.IB_DTYPE),
+                   ctu_first=np.array(ctu_first, np.uint32), params=ip),
+        dims=dims, ctb_log2=ctb_log2, width=width, height=height, seed=seed)

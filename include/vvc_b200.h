@@ -69,6 +69,8 @@ enum {
     VVCB200_TB_JOINT       = 1 << 6,  /* chroma TB carrying a joint CbCr residual: also rebuilt into plane 3 - c_idx      */
     VVCB200_TB_JOINT_SHIFT = 1 << 7,  /* tu->coded_flag[1] ^ tu->coded_flag[2] (vvc_intra.c:172)                          */
     VVCB200_TB_LMCS_SCALE  = 1 << 8,  /* LMCS chroma residual scaling applies (vvc_intra.c:451); scale in `lmcs_scale`    */
+    VVCB200_TB_TO_RESIDUAL = 1 << 9,  /* store the residual in the int16 residual planes instead of adding it to dst: the
+                                         TB belongs to an intra / CIIP block whose prediction is not there yet            */
 };
 
 typedef struct VVCB200TransformBlock {
@@ -128,8 +130,9 @@ VVCB200_API int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const i
  * Fused residual stage = itransform() for a whole picture (vvc_intra.c:432-478): BDPCM, dequant, LFNST,
  * 2-D/1-D inverse transform, LMCS chroma scaling factor, add_residual, joint CbCr — one launch.
  * d_levels: int16 level buffer (see coeff_off).  The TBs of one launch must not overlap in the planes.
- * If `d_residual` is non-NULL the clipped-to-int16 residual is stored there instead (same geometry as
- * `dst`, int16 samples) and `dst` is left untouched (used by the wavefront intra path).
+ * TBs flagged VVCB200_TB_TO_RESIDUAL (all TBs if `dst` is NULL) store their residual, clipped to int16, in
+ * `d_residual` (same geometry as `dst`, int16 samples) instead of adding it: the wavefront intra stage adds it
+ * once the prediction exists.
  */
 /* Lane-group class of a transform block (host helper, no CUDA): 0..3 = 2-D transform done with 32 / 16 / 8 / 4 lanes
  * (largest side >= 32 / 16 / 8 / <= 4), 4 = generic (transform skip, BDPCM, LFNST, 1-D).  Emitters keep one list per class. */
@@ -314,6 +317,70 @@ VVCB200_API int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Plane
 
 /* lmcs.filter (vvcdsp.h:124) over whole luma plane in place: pix = lut[pix] (ff_vvc_lmcs_filter, vvc_filter.c:1322-1332). */
 VVCB200_API int vvcb200_lmcs_picture(const VVCB200Planes *pic, const uint16_t *d_lut, int bit_depth, void *stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Intra prediction + reconstruction of intra (and CIIP) blocks: stage RECON, ff_vvc_reconstruct
+ * (vvc_intra.c:498-527) -> predict_intra (245-275) -> intra.intra_pred / intra_cclm_pred / pred_* (vvcdsp.h:98-110,
+ * vvc_intra_template.c).  Intra blocks depend on their reconstructed neighbours, so they run as a wavefront over CTUs
+ * (vvc_thread.c:161) after everything that has no spatial dependency (inter prediction, all inverse transforms).
+ * One record per prediction block and component, in decoding order, grouped per CTU.
+ * Neighbour availability is host-side bookkeeping (the ReconstructedArea lists, vvc_intra.c:574-648): the host states how
+ * many neighbour samples are reconstructed; the device does the substitution / filtering / prediction arithmetic.
+ * ---------------------------------------------------------------------------------------------- */
+enum {
+    VVCB200_IB_MIP            = 1 << 0,  /* matrix-based intra prediction (intra_mip_flag, luma or mip_chroma_direct)       */
+    VVCB200_IB_MIP_TRANSPOSED = 1 << 1,  /* intra_mip_transposed_flag                                                       */
+    VVCB200_IB_ISP            = 1 << 2,  /* cu->isp_split_type != ISP_NO_SPLIT (reference-sample rules, vvc_intra_template.c:474,511) */
+    VVCB200_IB_BDPCM          = 1 << 3,  /* cu->bdpcm_flag[c_idx]: no PDPC (vvc_intra.c:564)                                */
+    VVCB200_IB_RESIDUAL       = 1 << 4,  /* add the int16 residual plane to the prediction (the TB was coded)               */
+    VVCB200_IB_CIIP           = 1 << 5,  /* CIIP blend of this (planar) prediction with the inter prediction already in dst */
+};
+
+typedef struct VVCB200IntraBlock {
+    uint16_t x0, y0;            /* top-left corner in samples of the plane c_idx                                          */
+    uint8_t  w, h;              /* size in samples of that plane (1..64)                                                  */
+    uint8_t  c_idx;             /* 0 Y, 1 Cb, 2 Cr; a CCLM record has c_idx 1 and covers both chroma planes               */
+    int8_t   mode;              /* intra mode after wide-angle mapping (-14..80, vvc_intra.c:693-714); 81..83 = LT/L/T CCLM */
+    uint8_t  ref_idx;           /* cu->intra_luma_ref_idx as the reference stores it (0, 1 or 3)                          */
+    uint8_t  flags;             /* VVCB200_IB_*                                                                           */
+    uint8_t  mip_mode;          /* intra_mip_mode                                                                         */
+    uint8_t  up_left;           /* lc->na.cand_up_left                                                                    */
+    uint16_t avail_top;         /* reconstructed samples to the right of (x0, y0 - 1), as ff_vvc_get_top_available() would
+                                   report for an unbounded request (the device takes min(needed, avail))                  */
+    uint16_t avail_left;        /* same downwards from (x0 - 1, y0), ff_vvc_get_left_available()                          */
+    uint8_t  cb_w, cb_h;        /* ISP: the coding block's size in luma samples (refw = cb_w + w, vvc_intra_template.c:511-514) */
+    uint8_t  ciip_weight;       /* CIIP: intra weight 1..3 (ciip_derive_intra_weight, vvc_inter.c:523-543)                */
+    uint8_t  res_planes;        /* CCLM record with VVCB200_IB_RESIDUAL: bit 0 = Cb has a coded residual, bit 1 = Cr     */
+    uint32_t reserved2[2];
+} VVCB200IntraBlock;            /* 28 bytes */
+
+typedef struct VVCB200IntraParams {
+    int32_t bit_depth;
+    int32_t ctb_log2_size;
+    int32_t chroma_vertical_collocated;   /* sps_chroma_vertical_collocated_flag (CCLM down-sampling filter)              */
+    int32_t reserved;
+} VVCB200IntraParams;
+
+/*
+ * Reconstruction of the intra blocks of one picture, in place on `pic` (which already holds the inter prediction +
+ * residual of every inter block).  One launch; warps draw records from a ticket counter in array order and each
+ * record waits, on per-4x4 "pending" marks in `d_scratch`, for exactly the neighbour samples it reads.  The array order
+ * must therefore be topological (every record after the records it reads from): the decoding order is one, and
+ * vvcb200_intra_schedule() builds the order the engine prefers (CTU anti-diagonals x + 2y of vvc_thread.c:161,
+ * CTUs of a diagonal interleaved) from per-CTU decoding-order records.
+ * d_residual: int16 residual planes written by vvcb200_residual_batch for TBs flagged VVCB200_TB_TO_RESIDUAL (may be
+ * NULL if no record has VVCB200_IB_RESIDUAL).
+ * d_scratch: vvcb200_intra_scratch_bytes() bytes of device memory, zeroed once after allocation; a successful call
+ * leaves the marks zero again.  Two calls may not share a scratch buffer concurrently.
+ */
+VVCB200_API size_t vvcb200_intra_scratch_bytes(int width, int height /* luma samples */);
+/* Host helper: `in` holds the records of CTU i (raster index) at ctu_first[i] .. ctu_first[i + 1], in decoding order;
+ * `out` (same length, must not alias) receives them in wavefront order. */
+VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
+                                       VVCB200IntraBlock *out);
+VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
+                                      const VVCB200IntraBlock *d_blocks, int n,
+                                      const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);

@@ -219,8 +219,21 @@ static int lmcs_scale_one(int c, int scale, int bd)
  * The whole residual stage on host planes; same arguments as vvcb200_residual_batch.
  * residual_out (optional): int32 residual blocks appended back to back (pre-LMCS-scaling, pre-joint).
  */
+/* the TO_RESIDUAL variant of add_block: store the int16-clipped residual instead of adding it */
+static void store_block(const PortPlanes *rp, int c_idx, int x0, int y0, int w, int h, const int32_t *res,
+                        int c_sign, int shift, int joint)
+{
+    for (int y = 0; y < h; y++) {
+        int16_t *dst = (int16_t *)(rp->plane[c_idx] + (size_t)(y0 + y) * rp->stride[c_idx]) + x0;
+        for (int x = 0; x < w; x++) {
+            const int r = joint ? (res[y * w + x] * c_sign) >> shift : res[y * w + x];
+            dst[x] = port_clip_intp2(r, 15);
+        }
+    }
+}
+
 PORT_EXPORT int port_residual_batch(const PortPlanes *pl, const int16_t *levels, const VVCB200TransformBlock *tbs,
-                                    int n, const VVCB200ResidualParams *p, int32_t *residual_out)
+                                    int n, const VVCB200ResidualParams *p, int32_t *residual_out, const PortPlanes *rplanes)
 {
     int32_t res[64 * 64], tmp[64 * 64];
     for (int i = 0; i < n; i++) {
@@ -236,6 +249,13 @@ PORT_EXPORT int port_residual_batch(const PortPlanes *pl, const int16_t *levels,
             for (int k = 0; k < w * h; k++)
                 tmp[k] = lmcs_scale_one(res[k], d->lmcs_scale, p->bit_depth);
             src = tmp;
+        }
+        if ((d->flags & VVCB200_TB_TO_RESIDUAL) && rplanes) {
+            store_block(rplanes, d->c_idx, d->x0, d->y0, w, h, src, 1, 0, 0);
+            if ((d->flags & VVCB200_TB_JOINT) && d->c_idx)
+                store_block(rplanes, 3 - d->c_idx, d->x0, d->y0, w, h, res, p->joint_c_sign,
+                            !!(d->flags & VVCB200_TB_JOINT_SHIFT), 1);
+            continue;
         }
         add_block(pl, d->c_idx, d->x0, d->y0, w, h, src, p->bit_depth, 1, 0, 0);
         if ((d->flags & VVCB200_TB_JOINT) && d->c_idx) {

@@ -32,8 +32,10 @@ def itx(coeffs, trh, trv, log2w, log2h, nzw, nzh, bd=10, log2_range=15):
     return True
 
 
-def residual_batch(planes, levels, tbs, params, want_residual=False):
+def residual_batch(planes, levels, tbs, params, want_residual=False, residual_planes=None):
+    """residual_planes: int16 planes receiving the residual of TBs flagged TB_TO_RESIDUAL (else they are added too)."""
     pl = abi.host_planes(planes)
+    rp = None if residual_planes is None else abi.host_planes([r.view(np.uint16) for r in residual_planes])
     levels = np.ascontiguousarray(levels, np.int16)
     tbs = np.ascontiguousarray(tbs, abi.TB_DTYPE)
     res = None
@@ -41,7 +43,8 @@ def residual_batch(planes, levels, tbs, params, want_residual=False):
         total = int(np.sum(1 << (tbs["log2_w"].astype(np.int64) + tbs["log2_h"])))
         res = np.zeros(total, np.int32)
     lib().port_residual_batch(C.byref(pl), C.c_void_p(levels.ctypes.data), C.c_void_p(tbs.ctypes.data), len(tbs),
-                              C.byref(params), C.c_void_p(res.ctypes.data) if res is not None else None)
+                              C.byref(params), C.c_void_p(res.ctypes.data) if res is not None else None,
+                              C.byref(rp) if rp is not None else None)
     return res
 
 
@@ -87,3 +90,10 @@ def lmcs_picture(planes, lut):
     pl = abi.host_planes(planes)
     lut = np.ascontiguousarray(lut, np.uint16)
     lib().port_lmcs_picture(C.byref(pl), C.c_void_p(lut.ctypes.data))
+
+
+def intra_picture(planes, residual_planes, blocks, params):
+    pl = abi.host_planes(planes)
+    rp = abi.host_planes([r.view(np.uint16) for r in residual_planes])
+    blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
+    lib().port_intra_picture(C.byref(pl), C.byref(rp), C.c_void_p(blocks.ctypes.data), len(blocks), C.byref(params))

@@ -30,4 +30,24 @@ typedef struct VVCRefInterCU {
     int8_t  diff_mv_x[2][16], diff_mv_y[2][16];
     int32_t sb_mv_off;          /* affine: first entry of this CU's 4x4 sub-block vectors in `sb_mv` (raster, int32[2][2] each) */
 } VVCRefInterCU;
+
+/* CU / TU lists of a picture in decoding order, for driving ff_vvc_reconstruct() (vvc_intra.c:498-527). Test-side only. */
+typedef struct VVCRefCU {
+    int32_t x0, y0, w, h, ctu;          /* luma geometry, raster index of the CTU it belongs to */
+    int32_t pred_mode;                  /* 0 MODE_INTER, 1 MODE_INTRA */
+    int32_t intra_pred_mode_y, intra_pred_mode_c, intra_luma_ref_idx;
+    int32_t mip_flag, mip_transposed, mip_mode, mip_chroma_direct;
+    int32_t isp_split_type, num_intra_subpartitions;
+    int32_t bdpcm_flag[3];
+    int32_t ciip_flag, coded_flag;
+    int32_t first_tu, n_tu;
+    int32_t mts_idx;
+} VVCRefCU;
+
+typedef struct VVCRefTU {
+    int32_t x0, y0, w, h;
+    int32_t coded_flag[3];
+    int32_t joint;
+    int32_t tb[3];                      /* index into the VVCB200TransformBlock array, or -1 */
+} VVCRefTU;
 #endif

@@ -67,3 +67,14 @@ VVCREF_EXPORT const void *vvcref_table(const char *id, size_t *size)
     *size = 0;
     return NULL;
 }
+
+/* MIP weight matrices (vvc_data.c:310-1155) and the angle derivations of vvc_intra.c:662-690, for tools/gen_tables.py */
+VVCREF_EXPORT const uint8_t *vvcref_mip_matrix(int size_id, int mode_id)
+{
+    return ff_vvc_get_mip_matrix(size_id, mode_id);
+}
+
+int ff_vvc_intra_pred_angle_derive(const int pred_mode);
+int ff_vvc_intra_inv_angle_derive(const int pred_mode);
+VVCREF_EXPORT int vvcref_intra_angle(int mode)     { return ff_vvc_intra_pred_angle_derive(mode); }
+VVCREF_EXPORT int vvcref_intra_inv_angle(int angle) { return ff_vvc_intra_inv_angle_derive(angle); }

@@ -55,6 +55,8 @@ static ReconEnv *env_new(const VVCRefPlanes *pl, const VVCB200ResidualParams *p)
     e->sps.qp_bd_offset         = 6 * (p->bit_depth - 8);
     e->sps.log2_transform_range = p->log2_transform_range;
     e->sps.min_cb_log2_size_y   = 2;
+    e->sps.hshift[1] = e->sps.hshift[2] = 1;
+    e->sps.vshift[1] = e->sps.vshift[2] = 1;
     e->sps.ctb_log2_size_y      = 7;
     e->sps.ctb_size_y           = 128;
     e->pps.min_cb_width         = (pl->width[0] + 3) >> 2;
@@ -108,8 +110,6 @@ VVCREF_EXPORT int vvcref_residual_batch(const VVCRefPlanes *pl, const int16_t *l
             for (int x = 0; x < d->nzw; x++)
                 coeffs[y * w + x] = lv[y * d->nzw + x];
 
-        e->sps.hshift[1] = e->sps.hshift[2] = 1;
-        e->sps.vshift[1] = e->sps.vshift[2] = 1;
         e->rsh.sh_dep_quant_used_flag              = !!(d->flags & VVCB200_TB_DEP_QUANT);
         e->rsh.sh_explicit_scaling_list_used_flag  = !!(d->flags & VVCB200_TB_SCALING);
         e->rsh.sh_lmcs_used_flag                   = 0;   /* chroma scaling is exercised by the picture-level harness */
@@ -187,5 +187,153 @@ VVCREF_EXPORT int vvcref_residual_batch(const VVCRefPlanes *pl, const int16_t *l
     free(imf);
     free(coeffs);
     free(e);
+    return 0;
+}
+
+/*
+ * Stage RECON of a whole picture through ff_vvc_reconstruct() (vvc_intra.c:498-527): for every CTU in raster order the
+ * CU / TU lists are rebuilt from the flat arrays, the per-min-CB tables the intra code peeks at (imf / imtf / imm / ipm /
+ * cpm) are filled, and the reference predicts every intra block from its reconstructed neighbours and adds every
+ * residual, exactly as the decoder does after parsing.  Inter prediction must already be in the planes (stage INTER).
+ */
+VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *cus, int n_cus, const VVCRefTU *tus,
+                                       const VVCB200TransformBlock *tbs, const int16_t *levels,
+                                       const VVCB200ResidualParams *params, const VVCB200IntraParams *ip)
+{
+    ReconEnv *e = env_new(pl, params);
+    const int ctb_log2 = ip->ctb_log2_size, ctb = 1 << ctb_log2;
+    const int ctb_w = (pl->width[0] + ctb - 1) >> ctb_log2, ctb_h = (pl->height[0] + ctb - 1) >> ctb_log2;
+    const int mcw = (pl->width[0] + 3) >> 2, mch = (pl->height[0] + 3) >> 2;
+    CTU *ctus = calloc((size_t)ctb_w * ctb_h, sizeof(*ctus));
+    CodingUnit *cu_store = calloc(n_cus, sizeof(*cu_store));
+    uint8_t *tabs = calloc((size_t)mcw * mch, 5);
+    uint16_t *col_bd = calloc(ctb_w + 2, sizeof(*col_bd)), *row_bd = calloc(ctb_h + 2, sizeof(*row_bd));
+    int16_t *slice_idx = calloc((size_t)ctb_w * ctb_h, sizeof(*slice_idx));
+    VVCLocalContext *lc = aligned_alloc(64, (sizeof(*lc) + 63) & ~(size_t)63);
+    int n_tu_total = 0, n_tb_total = 0;
+    TransformUnit *tu_store;
+    int *coeff_store;
+    size_t coeff_total = 0;
+
+    for (int i = 0; i < n_cus; i++)
+        n_tu_total += cus[i].n_tu;
+    tu_store = calloc(n_tu_total ? n_tu_total : 1, sizeof(*tu_store));
+    for (int i = 0; i < n_tu_total; i++)
+        for (int c = 0; c < 3; c++)
+            if (tus[i].tb[c] >= 0) {
+                const VVCB200TransformBlock *d = &tbs[tus[i].tb[c]];
+                coeff_total += (size_t)1 << (d->log2_w + d->log2_h);
+                n_tb_total++;
+            }
+    coeff_store = calloc(coeff_total ? coeff_total : 1, sizeof(int));
+
+    memset(lc, 0, sizeof(*lc));
+    lc->fc = &e->fc;
+    lc->sc = &e->sc;
+    e->sps.ctb_log2_size_y = ctb_log2;
+    e->sps.ctb_size_y      = ctb;
+    e->pps.width = pl->width[0];
+    e->pps.height = pl->height[0];
+    e->pps.ctb_width = ctb_w;
+    e->pps.ctb_height = ctb_h;
+    e->pps.min_cb_width = e->pps.min_pu_width = e->pps.min_tu_width = mcw;
+    e->pps.ctb_to_col_bd = col_bd;
+    e->pps.ctb_to_row_bd = row_bd;
+    e->rsps.sps_chroma_vertical_collocated_flag = ip->chroma_vertical_collocated;
+    e->fc.tab.slice_idx = slice_idx;
+    e->fc.tab.ctus = ctus;
+    e->fc.tab.imf    = tabs;
+    e->fc.tab.imtf   = tabs + (size_t)mcw * mch;
+    e->fc.tab.imm    = tabs + (size_t)mcw * mch * 2;
+    e->fc.tab.ipm    = tabs + (size_t)mcw * mch * 3;
+    e->fc.tab.cpm[0] = tabs + (size_t)mcw * mch * 4;
+
+    {
+        int *cp = coeff_store;
+        CodingUnit **tail = NULL;
+        int last_ctu = -1, tu_i = 0;
+        for (int i = 0; i < n_cus; i++) {
+            const VVCRefCU *d = &cus[i];
+            CodingUnit *cu = &cu_store[i];
+            TransformUnit **tu_tail = &cu->tus.head;
+            if (d->ctu != last_ctu) {
+                tail = &ctus[d->ctu].cus;
+                last_ctu = d->ctu;
+            }
+            *tail = cu;
+            tail = &cu->next;
+            cu->tree_type = SINGLE_TREE;
+            cu->x0 = d->x0; cu->y0 = d->y0; cu->cb_width = d->w; cu->cb_height = d->h;
+            cu->pred_mode = d->pred_mode ? MODE_INTRA : MODE_INTER;
+            cu->coded_flag = d->coded_flag;
+            cu->intra_pred_mode_y = d->intra_pred_mode_y;
+            cu->intra_pred_mode_c = d->intra_pred_mode_c;
+            cu->intra_luma_ref_idx = d->intra_luma_ref_idx;
+            cu->intra_mip_flag = d->mip_flag;
+            cu->mip_chroma_direct_flag = d->mip_chroma_direct;
+            cu->isp_split_type = d->isp_split_type;
+            cu->num_intra_subpartitions = d->num_intra_subpartitions;
+            cu->ciip_flag = d->ciip_flag;
+            cu->mts_idx = d->mts_idx;
+            for (int c = 0; c < 3; c++)
+                cu->bdpcm_flag[c] = d->bdpcm_flag[c];
+            for (int y = d->y0 >> 2; y < (d->y0 + d->h) >> 2; y++)
+                for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++) {
+                    const size_t o = (size_t)y * mcw + x;
+                    e->fc.tab.imf[o]    = d->mip_flag;
+                    e->fc.tab.imtf[o]   = d->mip_transposed;
+                    e->fc.tab.imm[o]    = d->mip_mode;
+                    e->fc.tab.ipm[o]    = d->intra_pred_mode_y;
+                    e->fc.tab.cpm[0][o] = cu->pred_mode;
+                }
+            for (int k = 0; k < d->n_tu; k++, tu_i++) {
+                const VVCRefTU *t = &tus[d->first_tu + k];
+                TransformUnit *tu = &tu_store[tu_i];
+                *tu_tail = tu;
+                tu_tail = &tu->next;
+                cu->tus.tail = tu;
+                tu->x0 = t->x0; tu->y0 = t->y0; tu->width = t->w; tu->height = t->h;
+                tu->joint_cbcr_residual_flag = t->joint;
+                tu->nb_tbs = 3;
+                for (int c = 0; c < 3; c++) {
+                    TransformBlock *tb = &tu->tbs[c];
+                    tu->coded_flag[c] = t->coded_flag[c];
+                    tb->c_idx = c;
+                    tb->x0 = t->x0; tb->y0 = t->y0;
+                    tb->tb_width = t->w >> (c ? 1 : 0);
+                    tb->tb_height = t->h >> (c ? 1 : 0);
+                    tb->log2_tb_width = av_log2(tb->tb_width);
+                    tb->log2_tb_height = av_log2(tb->tb_height);
+                    if (t->tb[c] >= 0) {
+                        const VVCB200TransformBlock *s = &tbs[t->tb[c]];
+                        const int w = 1 << s->log2_w;
+                        const int16_t *lv = levels + s->coeff_off;
+                        tb->has_coeffs = 1;
+                        tb->ts = !!(s->flags & VVCB200_TB_TS);
+                        tb->max_scan_x = s->nzw - 1; tb->max_scan_y = s->nzh - 1;
+                        tb->coeffs = cp;
+                        for (int y = 0; y < s->nzh; y++)
+                            for (int x = 0; x < s->nzw; x++)
+                                cp[y * w + x] = lv[y * s->nzw + x];
+                        cp += (size_t)1 << (s->log2_w + s->log2_h);
+                        /* derive_qp(): luma adds qp_bd_offset, chroma takes cu->qp[idx] as is */
+                        if (c == 0)
+                            cu->qp[LUMA] = (int)s->qp - e->sps.qp_bd_offset;
+                        else
+                            cu->qp[c] = cu->qp[JCBCR] = s->qp;
+                    }
+                }
+            }
+        }
+    }
+    e->rsh.sh_dep_quant_used_flag = 0;
+    e->rsh.sh_explicit_scaling_list_used_flag = 0;
+    for (int ry = 0; ry < ctb_h; ry++)
+        for (int rx = 0; rx < ctb_w; rx++)
+            ff_vvc_reconstruct(lc, ry * ctb_w + rx, rx, ry);
+
+    free(coeff_store); free(tu_store); free(lc); free(slice_idx); free(col_bd); free(row_bd); free(tabs);
+    free(cu_store); free(ctus); free(e);
+    (void)n_tb_total;
     return 0;
 }

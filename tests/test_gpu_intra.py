@@ -1,0 +1,94 @@
+"""GPU parity: vvcb200_intra_picture (through the C ABI) against the oracle — the compiled reference's
+ff_vvc_reconstruct where oracle/_ref exists, else the C port — on identical seeded pictures.  Bit-exact."""
+import numpy as np
+import pytest
+
+from ffmpeg_b200 import abi, lib, synth
+from tests import util
+
+pytestmark = pytest.mark.gpu
+
+
+def run_gpu(pic, schedule=True, repeat=1):
+    """INTER -> RESIDUAL -> INTRA on the device, Level A calls only."""
+    import torch
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+    dev = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
+    dpl = lib.device_planes(dev)
+    if len(it["blocks"]):
+        refs = [util.to_device_planes(r, torch) for r in it["refs"]]
+        blocks = torch.from_numpy(it["blocks"].view(np.uint8).reshape(-1)).cuda()
+        lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], blocks, len(it["blocks"]), it["params"])
+    res = [torch.zeros_like(t) for t in dev]
+    rpl = lib.device_planes(res)
+    if len(rs["tbs"]):
+        tbs = torch.from_numpy(rs["tbs"].view(np.uint8).reshape(-1)).cuda()
+        levels = torch.from_numpy(rs["levels"]).cuda()
+        lib.residual_batch(dpl, levels, tbs, len(rs["tbs"]), rs["params"], residual=rpl)
+    w, h, ctb = pic["width"], pic["height"], pic["ctb_log2"]
+    recs = ia["blocks"]
+    if schedule:
+        recs = lib.intra_schedule(recs, ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb)
+    scratch = torch.zeros(lib.intra_scratch_bytes(w, h), dtype=torch.uint8, device="cuda")
+    out = []
+    if len(recs):
+        d_recs = torch.from_numpy(recs.view(np.uint8).reshape(-1)).cuda()
+        base = [t.clone() for t in dev]
+        for _ in range(repeat):
+            for t, b in zip(dev, base):
+                t.copy_(b)
+            lib.intra_picture(dpl, rpl, d_recs, len(recs), ia["params"], scratch)
+            torch.cuda.synchronize()
+            out.append(util.from_device_planes(dev))
+        assert int(scratch[256:].max()) == 0, "pending marks must be back to zero after the call"
+    else:
+        out.append(util.from_device_planes(dev))
+    return out
+
+
+CASES = [
+    (1, 208, 120, 6, ("pdpc",), 0.6),
+    (2, 208, 120, 5, ("pdpc", "mrl"), 0.6),
+    (3, 208, 120, 7, ("pdpc", "mrl", "mip"), 0.6),
+    (4, 208, 120, 6, ("pdpc", "mrl", "mip", "cclm"), 0.6),
+    (5, 416, 240, 7, ("pdpc", "mrl", "mip", "cclm", "mts"), 1.0),
+    (6, 136, 72, 5, ("pdpc", "mrl", "mip", "cclm"), 0.3),
+    (7, 832, 480, 7, ("pdpc", "mrl", "mip", "cclm", "mts"), 0.5),
+]
+
+
+@pytest.mark.parametrize("seed,w,h,ctb,tools,frac", CASES)
+def test_intra_picture_matches_oracle(seed, w, h, ctb, tools, frac):
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    got = run_gpu(pic)[0]
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)
+    assert util.plane_md5(got) == util.plane_md5(want)
+
+
+def test_decoding_order_and_repeat_give_the_same_picture():
+    """Any topological order works (plain decoding order included), and the scratch is reusable call after call."""
+    pic = synth.recon_picture(21, 416, 240, ctb_log2=6, intra_fraction=0.7)
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    for got in run_gpu(pic, schedule=False) + run_gpu(pic, schedule=True, repeat=3):
+        for c in range(3):
+            assert np.array_equal(got[c], want[c])
+
+
+def test_all_intra_1080p_property():
+    """Full-size picture: no oracle run; the two orders must agree with each other bit for bit."""
+    pic = synth.recon_picture(31, 1920, 1080, ctb_log2=7, intra_fraction=1.0)
+    a = run_gpu(pic, schedule=False)[0]
+    b = run_gpu(pic, schedule=True)[0]
+    assert util.plane_md5(a) == util.plane_md5(b)
+
+
+def test_empty_picture_is_a_noop():
+    import torch
+    dev = util.to_device_planes(util.noise_planes(1, [(64, 64), (32, 32), (32, 32)]), torch)
+    before = util.from_device_planes(dev)
+    ip = abi.IntraParams()
+    ip.bit_depth, ip.ctb_log2_size = 10, 7
+    lib.intra_picture(lib.device_planes(dev), None, None, 0, ip, None)
+    assert all(np.array_equal(a, b) for a, b in zip(util.from_device_planes(dev), before))

@@ -1,0 +1,71 @@
+"""CPU tests of the intra oracle: the C port (oracle/port/port_intra.c) against the compiled reference's
+ff_vvc_reconstruct (oracle/_ref) on seeded pictures and against the committed golden picture; and the host-side
+wavefront scheduler (vvcb200_intra_schedule), which must yield an order the port reconstructs identically from."""
+import os
+
+import numpy as np
+import pytest
+
+from ffmpeg_b200 import abi, lib, synth
+from oracle import portapi, refapi
+from tests import util
+
+CASES = [
+    (1, 208, 120, 6, ("pdpc",), 0.6),
+    (2, 208, 120, 5, ("pdpc", "mrl"), 0.6),
+    (3, 208, 120, 7, ("pdpc", "mrl", "mip"), 0.6),
+    (4, 208, 120, 6, ("pdpc", "mrl", "mip", "cclm"), 0.6),
+    (5, 416, 240, 7, ("pdpc", "mrl", "mip", "cclm", "mts"), 1.0),
+    (6, 136, 72, 5, ("pdpc", "mrl", "mip", "cclm"), 0.3),
+]
+
+
+def _port(pic, order=None):
+    planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+    if len(it["blocks"]):
+        portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"])
+    res = [np.zeros(p.shape, np.int16) for p in planes]
+    portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
+    portapi.intra_picture(planes, res, ia["blocks"] if order is None else order, ia["params"])
+    return planes
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("seed,w,h,ctb,tools,frac", CASES)
+def test_port_matches_reference_reconstruct(seed, w, h, ctb, tools, frac):
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
+    want = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+    if len(pic["inter"]["blocks"]):
+        refapi.inter_batch(want, pic["inter"]["refs"], pic["inter"]["blocks"], pic["inter"]["params"])
+    refapi.recon_picture(want, pic["ref"], pic["intra"]["params"])
+    got = _port(pic)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs" % c
+
+
+def test_port_matches_golden():
+    g = np.load(os.path.join(util.GOLDEN, "intra.npz"))
+    pic = synth.recon_picture(int(g["seed"]), int(g["width"]), int(g["height"]), ctb_log2=int(g["ctb_log2"]),
+                              tools=tuple(str(t) for t in g["tools"]), intra_fraction=float(g["intra_fraction"]))
+    assert util.md5(pic["intra"]["blocks"]) == str(g["blocks_md5"]), "synthetic generator drifted from the fixture"
+    got = _port(pic)
+    for c in range(3):
+        assert np.array_equal(got[c], g["plane%d" % c])
+
+
+@pytest.mark.parametrize("seed,w,h,ctb", [(11, 416, 240, 5), (12, 416, 240, 6), (13, 300, 200, 7), (14, 64, 64, 6)])
+def test_schedule_is_a_topological_permutation(seed, w, h, ctb):
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, intra_fraction=0.8)
+    ia = pic["intra"]
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    order = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch)
+    assert sorted(order.tobytes()[i:i + 28] for i in range(0, order.nbytes, 28)) == \
+        sorted(ia["blocks"].tobytes()[i:i + 28] for i in range(0, ia["blocks"].nbytes, 28))
+    a, b = _port(pic), _port(pic, order)
+    for c in range(3):
+        assert np.array_equal(a[c], b[c])
+    if cw > 2 and ch > 1:                                   # really a wavefront: CTU (0, 1) is drawn before the end of row 0
+        first_row1 = next(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 1)
+        last_row0 = max(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 0)
+        assert first_row1 < last_row0

@@ -44,3 +44,20 @@ def to_device_planes(planes_np, torch, align=64):
 
 def from_device_planes(tensors):
     return [t.cpu().numpy().view(np.uint16) for t in tensors]
+
+
+def oracle_recon(planes, pic, order=None):
+    """Stage INTER + RECON of a synth.recon_picture(): the compiled reference's ff_vvc_reconstruct when present,
+    else the C port's inter -> residual planes -> intra chain.  `order`: intra records to use with the port
+    (e.g. the wavefront order) instead of the decoding order."""
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+    use_ref = refapi.available() and order is None
+    if len(it["blocks"]):
+        (refapi if use_ref else portapi).inter_batch(planes, it["refs"], it["blocks"], it["params"])
+    if use_ref:
+        refapi.recon_picture(planes, pic["ref"], ia["params"])
+        return planes
+    res = [np.zeros(p.shape, np.int16) for p in planes]
+    portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
+    portapi.intra_picture(planes, res, ia["blocks"] if order is None else order, ia["params"])
+    return planes

@@ -86,10 +86,24 @@ def golden_loopfilter():
     return out
 
 
+def golden_intra():
+    """One small picture through the reference's ff_vvc_reconstruct (inter CUs predicted first), planes kept whole."""
+    seed, w, h, ctb, tools, frac = 20261107, 136, 72, 5, ("pdpc", "mrl", "mip", "cclm", "mts"), 0.7
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
+    planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+    if len(pic["inter"]["blocks"]):
+        refapi.inter_batch(planes, pic["inter"]["refs"], pic["inter"]["blocks"], pic["inter"]["params"])
+    refapi.recon_picture(planes, pic["ref"], pic["intra"]["params"])
+    return dict(seed=seed, width=w, height=h, ctb_log2=ctb, tools=np.array(tools), intra_fraction=frac,
+                blocks_md5=np.array(util.md5(pic["intra"]["blocks"])),
+                plane0=planes[0], plane1=planes[1], plane2=planes[2])
+
+
 def main():
     check = "--check" in sys.argv
     os.makedirs(util.GOLDEN, exist_ok=True)
-    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter), ("deblock", golden_deblock), ("loopfilter", golden_loopfilter)):
+    for name, fn in (("itx", golden_itx), ("residual", golden_residual), ("inter", golden_inter), ("deblock", golden_deblock), ("loopfilter", golden_loopfilter),
+                     ("intra", golden_intra)):
         data = fn()
         path = os.path.join(util.GOLDEN, name + ".npz")
         if check:
