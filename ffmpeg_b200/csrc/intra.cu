@@ -722,3 +722,62 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     VVC_LAUNCH_CHECK();
     return 0;
 }
+
+// ---- the same reconstruction with the scratch living in the module image instead of caller memory ---------------
+// Some integrations cannot hand us scratch memory or let us create any: a decoder thread sitting between two pictures
+// must not call the CUDA allocator, because every allocation and release serialises against all work in flight on
+// the device and would stall the other frame contexts' streams; and a player that has given the whole card to its
+// own pool at start-up can see a late driver allocation fail outright.  For those callers the marks and the ticket
+// counter live in a fixed array that is part of the loaded module, sized for pictures up to 1920x1088.
+// Nothing here allocates.  The address of the array is looked up once per device (with that device current) and
+// remembered; that first call should happen before the application starts capturing a stream.  The array is shared
+// by every caller on the device: two of these calls overlapping in time (different streams or threads) race on it.
+namespace vvcb200 {
+namespace {
+constexpr size_t kStaticScratchBytes = 256 * 1024;                        // enough for 1920x1088 (261376 bytes)
+constexpr int kMaxDevices = 64;
+static __device__ __align__(256) unsigned char g_intra_scratch[kStaticScratchBytes];
+void *g_intra_scratch_ptr[kMaxDevices];                                   // per device, filled on first use
+}  // namespace
+}  // namespace vvcb200
+
+#include <mutex>
+
+extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
+                                            const VVCB200IntraBlock *d_blocks, int n,
+                                            const VVCB200IntraParams *params, void *stream)
+{
+    static std::mutex lock;
+    if (!pic || !params || n < 0 || (n && !d_blocks)) {
+        set_error("vvcb200_intra_picture_static: bad arguments");
+        return VVCB200_ERR_ARG;
+    }
+    if (!n)
+        return 0;
+    const size_t need = vvcb200_intra_scratch_bytes(pic->width[0], pic->height[0]);
+    if (!need || need > kStaticScratchBytes) {
+        set_error("vvcb200_intra_picture_static: a %dx%d picture needs %zu bytes of marks, the built-in scratch holds %zu "
+                  "(pictures up to 1920x1088); use vvcb200_intra_picture with caller memory",
+                  pic->width[0], pic->height[0], need, kStaticScratchBytes);
+        return VVCB200_ERR_ARG;
+    }
+    int dev = -1;
+    VVC_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= kMaxDevices) {
+        set_error("vvcb200_intra_picture_static: device index %d out of range", dev);
+        return VVCB200_ERR_ARG;
+    }
+    void *ptr;
+    {
+        std::lock_guard<std::mutex> g(lock);
+        if (!g_intra_scratch_ptr[dev]) {
+            void *p = nullptr;
+            VVC_CUDA(cudaGetSymbolAddress((void **)&p, g_intra_scratch));
+            g_intra_scratch_ptr[dev] = p;
+        }
+        ptr = g_intra_scratch_ptr[dev];
+    }
+    // the marks have to read zero when the mark kernel starts; an earlier call that failed half-way may have left some
+    VVC_CUDA(cudaMemsetAsync(ptr, 0, need, (cudaStream_t)stream));
+    return vvcb200_intra_picture(pic, d_residual, d_blocks, n, params, ptr, stream);
+}

@@ -110,6 +110,12 @@ def intra_picture(pic, residual, blocks, n, params, scratch, stream=None):
                                        _ptr(blocks), int(n), C.byref(params), _ptr(scratch), _stream(stream)))
 
 
+def intra_picture_static(pic, residual, blocks, n, params, stream=None):
+    """vvcb200_intra_picture_static: as intra_picture, marks in the library's built-in scratch (<= 1920x1088)."""
+    check(load().vvcb200_intra_picture_static(C.byref(pic), C.byref(residual) if residual is not None else None,
+                                              _ptr(blocks), int(n), C.byref(params), _stream(stream)))
+
+
 # ---- Level B: picture engine ---------------------------------------------------------------------------
 class Context:
     """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use

@@ -382,6 +382,17 @@ VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Pla
                                       const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);
 
+/*
+ * vvcb200_intra_picture without caller scratch and without any allocation: the marks live in a fixed array inside
+ * the library's device image (256 KiB, pictures up to 1920x1088 luma samples; larger ones return VVCB200_ERR_ARG).
+ * This entry point has no counterpart in the reference; it exists for callers that may not allocate device memory.
+ * The array is per device and shared by all callers: calls that overlap in time on one device race.  The first call
+ * on a device looks the array's address up; make that call before starting a stream capture.
+ */
+VVCB200_API int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
+                                             const VVCB200IntraBlock *d_blocks, int n,
+                                             const VVCB200IntraParams *params /* host */, void *stream);
+
 /* ------------------------------------------------------------------------------------------------
  * Level B: the picture-level engine.  One context per GPU per stream of pictures (one decoder instance);
  * a context is not thread-safe, different contexts are independent (replicas only).
