@@ -66,9 +66,11 @@ struct VVCB200Ctx {
     cudaStream_t stream = nullptr;
     std::vector<DevPicture> dpb;   // reference pictures + the picture under reconstruction
     DevPicture scratch;            // SAO output / ALF input
+    DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
+    std::vector<VVCB200IntraBlock> intra_order;   // host: the picture's intra records in wavefront order
     int cur = 0;
     // per-stage device copies of the host descriptor batches
-    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params;
+    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks, intra_marks;
 };
 
 namespace {
@@ -174,7 +176,7 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     if (c->stream)
         cudaStreamSynchronize(c->stream);
     DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->refined, &c->prof, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
-                          &c->alf_params };
+                          &c->alf_params, &c->iblocks, &c->intra_marks };
     for (DevBuffer *b : bufs)
         b->release();
     for (DevPicture &p : c->dpb)
@@ -182,6 +184,8 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
             cudaFree(p.base);
     if (c->scratch.base)
         cudaFree(c->scratch.base);
+    if (c->residual.base)
+        cudaFree(c->residual.base);
     if (c->stream)
         cudaStreamDestroy(c->stream);
     delete c;
@@ -354,8 +358,71 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
         return r;
     if (int r = upload(c, c->tbs, tbs, (size_t)n * sizeof(VVCB200TransformBlock)))
         return r;
-    return vvcb200_residual_batch(&c->dpb[c->cur].planes, nullptr, (const int16_t *)c->levels.p,
+    const VVCB200Planes *res = nullptr;
+    for (int i = 0; i < n && !res; i++)
+        if (tbs[i].flags & VVCB200_TB_TO_RESIDUAL) {
+            if (!c->residual.base)
+                if (int r = alloc_picture(c, &c->residual))
+                    return r;
+            res = &c->residual.planes;
+        }
+    return vvcb200_residual_batch(&c->dpb[c->cur].planes, res, (const int16_t *)c->levels.p,
                                   (const VVCB200TransformBlock *)c->tbs.p, n, params, c->stream);
+}
+
+int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint32_t *ctu_first, int ctus_w, int ctus_h,
+                      const VVCB200IntraParams *params)
+{
+    if (!c || !params || !ctu_first || ctus_w <= 0 || ctus_h <= 0) {
+        set_error("vvcb200_pic_intra: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    const int shift = params->ctb_log2_size;
+    if (shift < 5 || shift > 7 || ctus_w != (c->width + (1 << shift) - 1) >> shift ||
+        ctus_h != (c->height + (1 << shift) - 1) >> shift) {
+        set_error("vvcb200_pic_intra: %dx%d CTUs of 2^%d do not tile the context's %dx%d picture", ctus_w, ctus_h, shift,
+                  c->width, c->height);
+        return VVCB200_ERR_ARG;
+    }
+    const int n = (int)ctu_first[ctus_w * ctus_h];
+    if (n == 0)
+        return 0;
+    if (!blocks || ctu_first[0] != 0) {
+        set_error("vvcb200_pic_intra: bad record ranges");
+        return VVCB200_ERR_ARG;
+    }
+    bool needs_res = false;
+    for (int i = 0; i < n; i++) {
+        const VVCB200IntraBlock &b = blocks[i];
+        const int pw = b.c_idx ? c->width >> c->hshift : c->width, ph = b.c_idx ? c->height >> c->vshift : c->height;
+        if (b.c_idx > 2 || !b.w || !b.h || b.w > 64 || b.h > 64 || (b.w & (b.w - 1)) || (b.h & (b.h - 1)) ||
+            b.x0 + b.w > pw || b.y0 + b.h > ph || (b.x0 & 3) || (b.y0 & (b.c_idx ? 1 : 3)) || b.mode > 83 || b.mode < -14 ||
+            (b.mode >= 81 && b.c_idx != 1)) {
+            set_error("vvcb200_pic_intra: record %d (plane %d, %dx%d at %d,%d, mode %d) is malformed or outside the picture",
+                      i, b.c_idx, b.w, b.h, b.x0, b.y0, b.mode);
+            return VVCB200_ERR_ARG;
+        }
+        needs_res |= (b.flags & VVCB200_IB_RESIDUAL) != 0;
+    }
+    if (needs_res && !c->residual.base) {
+        set_error("vvcb200_pic_intra: records add a residual but vvcb200_pic_residual stored none for this picture");
+        return VVCB200_ERR_ARG;
+    }
+    DeviceGuard g(c->device);
+    c->intra_order.resize(n);
+    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, c->intra_order.data()))
+        return r;
+    // the copy below is from pageable memory: the driver stages it before returning, so the vector may be reused
+    if (int r = upload(c, c->iblocks, c->intra_order.data(), (size_t)n * sizeof(VVCB200IntraBlock)))
+        return r;
+    const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
+    if (!c->intra_marks.p) {
+        if (int r = c->intra_marks.reserve(marks))
+            return r;
+        VVC_CUDA(cudaMemsetAsync(c->intra_marks.p, 0, c->intra_marks.cap, c->stream));
+    }
+    return vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr,
+                                 (const VVCB200IntraBlock *)c->iblocks.p, n, params, c->intra_marks.p, c->stream);
 }
 
 int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)

@@ -85,6 +85,14 @@ __device__ void set_marks(const IntraArgs &a, int c, int x0, int y0, int w, int 
         *((volatile uint8_t *)a.marks[c] + (size_t)(uy + i / nx) * a.mpitch[c] + ux + i % nx) = v;
 }
 
+// the samples a record writes: an ISP luma record stands for its whole coding block
+__device__ __forceinline__ void record_extent(const VVCB200IntraBlock &b, int &w, int &h)
+{
+    const bool isp = (b.flags & VVCB200_IB_ISP) && !b.c_idx;
+    w = isp ? b.cb_w : b.w;
+    h = isp ? b.cb_h : b.h;
+}
+
 __global__ void intra_mark_kernel(IntraArgs a)
 {
     const int lane = threadIdx.x & 31;
@@ -94,9 +102,11 @@ __global__ void intra_mark_kernel(IntraArgs a)
     if (t >= a.n)
         return;
     const VVCB200IntraBlock b = load_record(a.blocks + t);
-    set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 1, lane);
+    int w, h;
+    record_extent(b, w, h);
+    set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane);
     if (b.mode >= 81)
-        set_marks(a, 2, b.x0, b.y0, b.w, b.h, 1, lane);
+        set_marks(a, 2, b.x0, b.y0, w, h, 1, lane);
 }
 
 // ---- mode helpers (vvc_intra.c:538-660) ---------------------------------------------------------------------------
@@ -156,7 +166,9 @@ struct Store {                    // what happens to a predicted sample on its w
     }
 };
 
-__device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane)
+// skip_wait: bit 0 = the row above (and the corner), bit 1 = the column to the left (and the corner) were written by
+// this warp itself (earlier ISP sub-partitions) and carry this record's own marks
+__device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, int skip_wait = 0)
 {
     const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode, ref_idx = b.ref_idx, bd = a.bd;
     const int lw = ilog2(w), lh = ilog2(h);
@@ -197,9 +209,9 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
         const int nl = unit_count(b.y0, la, s), nt = unit_count(b.x0, ta, 2);
         for (;;) {
             bool p = false;
-            if (nl) p |= col_pending(a, c, ux - 1, uy, nl, lane);
-            if (nt) p |= row_pending(a, c, uy - 1, ux, nt, lane);
-            if (b.up_left) p |= row_pending(a, c, uy - 1, ux - 1, 1, lane);
+            if (nl && !(skip_wait & 2)) p |= col_pending(a, c, ux - 1, uy, nl, lane);
+            if (nt && !(skip_wait & 1)) p |= row_pending(a, c, uy - 1, ux, nt, lane);
+            if (b.up_left && !skip_wait) p |= row_pending(a, c, uy - 1, ux - 1, 1, lane);
             if (!__any_sync(kFull, p))
                 break;
             __nanosleep(64);
@@ -608,15 +620,38 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
         if (t >= a.n)
             break;
         const VVCB200IntraBlock b = load_record(a.blocks + t);
-        if (b.mode >= 81)
+        if (b.mode >= 81) {
             cclm_record(a, b, lane);
-        else
+        } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
+            // ISP: the sub-partitions of the coding block one after the other, each predicted from its reconstructed
+            // predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit
+            const bool hor = b.w == b.cb_w;
+            const int n_parts = hor ? b.cb_h / b.h : b.cb_w / b.w;
+            for (int k = 0; k < n_parts; k++) {
+                VVCB200IntraBlock s = b;
+                if (hor) {
+                    s.y0 += k * b.h;
+                    s.avail_left = max((int)b.avail_left - k * b.h, 0);
+                    if (k) { s.avail_top = b.w; s.up_left = b.avail_left > 0; }
+                } else {
+                    s.x0 += k * b.w;
+                    s.avail_top = max((int)b.avail_top - k * b.w, 0);
+                    if (k) { s.avail_left = b.h; s.up_left = b.avail_top > 0; }
+                }
+                predict_record(a, s, ws, lane, k ? (hor ? 1 : 2) : 0);
+                __threadfence();                                          // the next sub-partition reads these samples
+                __syncwarp();
+            }
+        } else {
             predict_record(a, b, ws, lane);
+        }
         __threadfence();                                                  // samples before marks
         __syncwarp();
-        set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 0, lane);
+        int ew, eh;
+        record_extent(b, ew, eh);
+        set_marks(a, b.c_idx, b.x0, b.y0, ew, eh, 0, lane);
         if (b.mode >= 81)
-            set_marks(a, 2, b.x0, b.y0, b.w, b.h, 0, lane);
+            set_marks(a, 2, b.x0, b.y0, ew, eh, 0, lane);
         __syncwarp();
     }
 }

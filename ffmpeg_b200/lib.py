@@ -206,6 +206,11 @@ class Context:
         check(load().vvcb200_pic_residual(self._h, _ptr(levels), C.c_size_t(levels.size), _ptr(tbs), len(tbs),
                                           C.byref(params)))
 
+    def intra(self, blocks, ctu_first, ctus_w, ctus_h, params):
+        blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
+        ctu_first = np.ascontiguousarray(ctu_first, np.uint32)
+        check(load().vvcb200_pic_intra(self._h, _ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), C.byref(params)))
+
     def lmcs(self, inv_lut):
         check(load().vvcb200_pic_lmcs(self._h, _ptr(inv_lut)))
 

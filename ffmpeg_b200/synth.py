@@ -208,28 +208,24 @@ def smooth_planes(seed, dims, bd=10):
     return out
 
 
-def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel"), mv_range=64 * 16, far_mv=0.02,
-                  inter_fraction=1.0, sizes=(4, 8, 16)):
-    """Prediction sub-block batch (<= 16x16) tiling the picture + per-slice InterParams."""
-    rng = np.random.default_rng(seed)
-    tools = set(tools)
-    tiles = random_tiling(rng, width, height, 16, min(sizes), mean_log2=3.6)
-    if inter_fraction < 1.0:
-        tiles = tiles[rng.random(len(tiles)) < inter_fraction]
-    n = len(tiles)
-    b = np.zeros(n, abi.PB_DTYPE)
-    b["x0"], b["y0"], b["w"], b["h"] = tiles[:, 0], tiles[:, 1], tiles[:, 2], tiles[:, 3]
-    pf = rng.integers(1, 4 if "bi" in tools else 3, n)
-    b["pred_flag"] = pf
-    b["ref_idx"] = rng.integers(0, n_refs, (n, 2))
-    mv = rng.integers(-mv_range, mv_range + 1, (n, 2, 2))
-    far = rng.random(n) < far_mv                      # a few vectors pointing far outside the picture
-    mv[far] = rng.integers(-(1 << 17), 1 << 17, (int(far.sum()), 2, 2))
-    integer = rng.random((n, 2, 2)) < 0.2             # plenty of integer / half-pel components
-    mv[integer] &= ~15
-    half = rng.random((n, 2, 2)) < 0.15
-    mv[half] = (mv[half] & ~15) | 8
-    b["mv"] = mv
+def _decorate_blocks(rng, b, tools, n_refs, mv_range=64 * 16, far_mv=0.02, keep_mv=False):
+    """Fill prediction mode, vectors and tool flags of the sub-blocks `b` (geometry already set) and build the
+    slice's InterParams.  keep_mv: pred_flag / ref_idx / mv are already there (one vector per coding unit)."""
+    n = len(b)
+    if keep_mv:
+        pf = b["pred_flag"].astype(np.int64)
+    else:
+        pf = rng.integers(1, 4 if "bi" in tools else 3, n)
+        b["pred_flag"] = pf
+        b["ref_idx"] = rng.integers(0, n_refs, (n, 2))
+        mv = rng.integers(-mv_range, mv_range + 1, (n, 2, 2))
+        far = rng.random(n) < far_mv                      # a few vectors pointing far outside the picture
+        mv[far] = rng.integers(-(1 << 17), 1 << 17, (int(far.sum()), 2, 2))
+        integer = rng.random((n, 2, 2)) < 0.2             # plenty of integer / half-pel components
+        mv[integer] &= ~15
+        half = rng.random((n, 2, 2)) < 0.15
+        mv[half] = (mv[half] & ~15) | 8
+        b["mv"] = mv
     flags = np.zeros(n, np.uint16)
     if "wp" in tools:
         flags |= np.where(rng.random(n) < 0.3, abi.PB_WP, 0).astype(np.uint16)
@@ -256,7 +252,21 @@ def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
     params = abi.inter_params(10, ld, weight, offset, ref_slot)
-    b = abi.order_blocks_by_width(b, params)
+    return abi.order_blocks_by_width(b, params), params
+
+
+def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel"), mv_range=64 * 16, far_mv=0.02,
+                  inter_fraction=1.0, sizes=(4, 8, 16)):
+    """Prediction sub-block batch (<= 16x16) tiling the picture + per-slice InterParams."""
+    rng = np.random.default_rng(seed)
+    tools = set(tools)
+    tiles = random_tiling(rng, width, height, 16, min(sizes), mean_log2=3.6)
+    if inter_fraction < 1.0:
+        tiles = tiles[rng.random(len(tiles)) < inter_fraction]
+    n = len(tiles)
+    b = np.zeros(n, abi.PB_DTYPE)
+    b["x0"], b["y0"], b["w"], b["h"] = tiles[:, 0], tiles[:, 1], tiles[:, 2], tiles[:, 3]
+    b, params = _decorate_blocks(rng, b, tools, n_refs, mv_range, far_mv)
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     return dict(blocks=b, params=params, refs=refs, dims=dims, seed=seed)
@@ -435,10 +445,13 @@ def lmcs_luts(seed, bd=10):
 
 # ---- a whole picture --------------------------------------------------------------------------------------------
 def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, lmcs=False, n_slices=1, lfase=1,
-                 residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3):
+                 residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3, intra_fraction=0.0):
     """All descriptor batches of one inter picture (BASELINE config 2/3 shape): prediction sub-blocks, residual TBs,
     deblocking tables, SAO/ALF CTB parameters.  Stage inputs are generated independently of each other (the
     arithmetic of every stage takes its tables as given); see DESIGN.md for what a real parser adds."""
+    if intra_fraction > 0:
+        return _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2,
+                                        intra_fraction)
     inter = inter_picture(seed, width, height, n_refs=n_refs, tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"))
     res = residual_picture(seed + 1, width, height, coded_fraction=coded_fraction, tools=residual_tools,
                            mean_log2=mean_log2)
@@ -454,6 +467,24 @@ def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, 
     if lmcs:
         out["lmcs"] = lmcs_luts(seed + 4)
         inter["blocks"]["flags"] |= abi.PB_LMCS
+    return out
+
+
+def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2, intra_fraction):
+    """full_picture() over ONE coding-unit partition: every CU is inter (prediction sub-blocks, TBs added in place) or
+    intra (records for the wavefront, TBs routed through the residual planes), as in a P/B picture with intra CUs."""
+    rp = recon_picture(seed, width, height, ctb_log2=ctb_log2, intra_fraction=intra_fraction, n_refs=n_refs,
+                       tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "mts", "ts", "lfnst", "joint", "dep_quant",
+                              "scaling"), mean_log2=mean_log2,
+                       inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"))
+    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
+    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
+    out = dict(inter=rp["inter"], residual=rp["residual"], intra=rp["intra"], ref=rp["ref"], deblock=db, lf=lf,
+               dims=rp["dims"], ctb_log2=ctb_log2, seed=seed, width=width, height=height, lmcs=None)
+    out["residual"]["intra_mode"] = np.zeros(len(rp["residual"]["tbs"]), np.int32)
+    if lmcs:
+        out["lmcs"] = lmcs_luts(seed + 4)
+        out["inter"]["blocks"]["flags"] |= abi.PB_LMCS
     return out
 
 
@@ -572,7 +603,7 @@ REF_CU_DTYPE = np.dtype([
     ("intra_pred_mode_y", "<i4"), ("intra_pred_mode_c", "<i4"), ("intra_luma_ref_idx", "<i4"),
     ("mip_flag", "<i4"), ("mip_transposed", "<i4"), ("mip_mode", "<i4"), ("mip_chroma_direct", "<i4"),
     ("isp_split_type", "<i4"), ("num_intra_subpartitions", "<i4"), ("bdpcm_flag", "<i4", (3,)), ("ciip_flag", "<i4"),
-    ("coded_flag", "<i4"), ("first_tu", "<i4"), ("n_tu", "<i4"), ("mts_idx", "<i4"),
+    ("coded_flag", "<i4"), ("first_tu", "<i4"), ("n_tu", "<i4"), ("mts_idx", "<i4"), ("lfnst_idx", "<i4"),
 ])                                  # mirrors VVCRefCU (oracle/ref/api_common.h)
 REF_TU_DTYPE = np.dtype([
     ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("coded_flag", "<i4", (3,)), ("joint", "<i4"),
@@ -619,12 +650,14 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3):
+                  mean_log2=4.3, inter_tools=None):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
          residual: TB batch (TBs of intra CUs flagged TB_TO_RESIDUAL),
          intra: VVCB200IntraBlock records + per-CTU ranges (stage RECON wavefront).
+    tools: intra side "mrl", "mip", "cclm", "isp", "bdpcm"; residual side "mts", "ts", "lfnst", "joint", "dep_quant",
+    "scaling" ("pdpc" is always on, it is not signalled).
     Neighbour availability follows the reference's rules (vvc_intra.c:593-648) on a 4x4-unit reconstruction mask."""
     rng = np.random.default_rng(seed)
     tools = set(tools)
@@ -632,25 +665,68 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     cw, ch = (width + ctb - 1) >> ctb_log2, (height + ctb - 1) >> ctb_log2
     u4w, u4h = (width + 3) >> 2, (height + 3) >> 2
     done = np.zeros((u4h, u4w), bool)               # luma and chroma become available together (single tree)
-    cus, tus, tbs, lv_chunks, intra_mode_tb = [], [], [], [], []
+    cus, tus, tbs, lv_chunks = [], [], [], []
     pblocks, iblocks, ctu_first = [], [], [0]
     lv_off = 0
+    pic_flags = (abi.TB_DEP_QUANT if "dep_quant" in tools and rng.random() < 0.5 else 0) | \
+                (abi.TB_SCALING if "scaling" in tools and rng.random() < 0.6 else 0)
 
-    def new_tb(x, y, c, w, h, inter, trh=0, trv=0, qp=30, to_res=False):
+    def new_tb(x, y, c, w, h, inter, trh=0, trv=0, qp=30, to_res=False, ts=False, bdpcm=0, lfnst=0, joint=0):
         nonlocal lv_off
-        nzw = int(rng.integers(1, min(w, 32 if trh == 0 else 16) + 1))
-        nzh = int(rng.integers(1, min(h, 32 if trv == 0 else 16) + 1))
+        flags = pic_flags | (abi.TB_INTER if inter else 0) | (abi.TB_TO_RESIDUAL if to_res else 0)
+        mask = None
+        if ts:
+            flags |= abi.TB_TS
+            if bdpcm:
+                flags |= abi.TB_BDPCM | (abi.TB_BDPCM_VERT if bdpcm == 2 else 0)
+            nzw, nzh = int(rng.integers(1, w + 1)), int(rng.integers(1, h + 1))
+        elif lfnst:
+            nz = 8 if (w, h) in ((4, 4), (8, 8)) else 16
+            pos = _DIAG4[:int(rng.integers(1, nz + 1))]
+            nzw, nzh = max(q[0] for q in pos) + 1, max(q[1] for q in pos) + 1
+            mask = np.zeros((nzh, nzw), bool)
+            for (px, py) in pos:
+                mask[py, px] = True
+        else:
+            nzw = int(rng.integers(1, min(w, 32 if trh == 0 else 16) + 1))
+            nzh = int(rng.integers(1, min(h, 32 if trv == 0 else 16) + 1))
         lv = np.clip(np.rint(rng.laplace(0, 10, (nzh, nzw))), -200, 200).astype(np.int16)
-        lv[nzh - 1, nzw - 1] = lv[nzh - 1, nzw - 1] or 1
+        if mask is not None:
+            lv[~mask] = 0
+            if not lv.any():
+                lv[0, 0] = 3
+        else:
+            lv[nzh - 1, nzw - 1] = lv[nzh - 1, nzw - 1] or 1
+        if joint:
+            flags |= abi.TB_JOINT | (abi.TB_JOINT_SHIFT if joint >= 2 else 0)
         t = np.zeros(1, abi.TB_DTYPE)
         t["x0"], t["y0"], t["c_idx"], t["log2_w"], t["log2_h"] = x, y, c, int(np.log2(w)), int(np.log2(h))
         t["nzw"], t["nzh"], t["trh"], t["trv"], t["qp"] = nzw, nzh, trh, trv, qp
-        t["flags"] = (abi.TB_INTER if inter else 0) | (abi.TB_TO_RESIDUAL if to_res else 0)
-        t["coeff_off"] = lv_off
+        t["flags"], t["lfnst"], t["coeff_off"] = flags, lfnst, lv_off
         lv_chunks.append(lv.reshape(-1))
         lv_off += lv.size
         tbs.append(t)
         return len(tbs) - 1
+
+    def chroma_tbs(tu, x, y, w, h, inter, qp_c, coded, to_res, bdpcm_c):
+        """Chroma TBs of a TU (luma geometry in): separate Cb / Cr, or one joint TB standing for both."""
+        jm = 0
+        if "joint" in tools and (coded[1] or coded[2]) and not bdpcm_c and rng.random() < 0.3:
+            jm = int(rng.integers(1, 4))     # 1: Cb carries, both coded; 2: Cb carries, Cr halved; 3: Cr carries, Cb halved
+        if jm:
+            carrier = 2 if jm == 3 else 1
+            tu["joint"] = 1
+            tu["coded_flag"][0, 1], tu["coded_flag"][0, 2] = int(jm != 3), int(jm != 2)
+            ts = "ts" in tools and rng.random() < 0.1
+            tu["tb"][0, carrier] = new_tb(x >> 1, y >> 1, carrier, w >> 1, h >> 1, inter, 0, 0, qp_c, to_res, ts=ts, joint=jm)
+            return 3
+        got = 0
+        for c in (1, 2):
+            if coded[c]:
+                ts = bool(bdpcm_c) or ("ts" in tools and rng.random() < 0.1)
+                tu["tb"][0, c] = new_tb(x >> 1, y >> 1, c, w >> 1, h >> 1, inter, 0, 0, qp_c, to_res, ts=ts, bdpcm=bdpcm_c)
+                got |= 1 << (c - 1)
+        return got
 
     for ry in range(ch):
         for rx in range(cw):
@@ -660,29 +736,28 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
             ctb_left, ctb_up = rx > 0, ry > 0
             for (x, y, w, h) in regions:
                 cu = np.zeros(1, REF_CU_DTYPE)
-                tu = np.zeros(1, REF_TU_DTYPE)
                 intra = rng.random() < intra_fraction
                 cu["x0"], cu["y0"], cu["w"], cu["h"], cu["ctu"] = x, y, w, h, rs
                 cu["pred_mode"] = MODE_INTRA if intra else MODE_INTER
                 cu["first_tu"], cu["n_tu"] = len(tus), 1
-                tu["x0"], tu["y0"], tu["w"], tu["h"] = x, y, w, h
-                coded = rng.random(3) < 0.8
-                tu["coded_flag"] = coded
                 cu["coded_flag"] = 1                    # the reference only skips reconstruct() for uncoded CUs
+                coded = rng.random(3) < 0.8
                 qp_y, qp_c = int(rng.integers(14, 60)), int(rng.integers(14, 60))
-                trh = trv = 0
-                if not intra or "mts" in tools:
-                    if 4 <= w <= 32 and 4 <= h <= 32 and rng.random() < 0.3:
-                        trh, trv = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
-                cu["mts_idx"] = _MTS_OF[(trh, trv)]
-                tu["tb"] = -1
-                if coded[0]:
-                    tu["tb"][0, 0] = new_tb(x, y, 0, w, h, not intra, trh, trv, qp_y, intra)
-                for c in (1, 2):
-                    if coded[c]:
-                        tu["tb"][0, c] = new_tb(x >> 1, y >> 1, c, w >> 1, h >> 1, not intra, 0, 0, qp_c, intra)
                 ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
                 if not intra:
+                    tu = np.zeros(1, REF_TU_DTYPE)
+                    tu["x0"], tu["y0"], tu["w"], tu["h"] = x, y, w, h
+                    tu["coded_flag"] = coded
+                    tu["tb"] = -1
+                    trh = trv = 0
+                    ts = "ts" in tools and w <= 32 and h <= 32 and rng.random() < 0.08
+                    if not ts and "mts" in tools and w <= 32 and h <= 32 and rng.random() < 0.3:
+                        trh, trv = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
+                    cu["mts_idx"] = _MTS_OF[(trh, trv)]
+                    if coded[0]:
+                        tu["tb"][0, 0] = new_tb(x, y, 0, w, h, True, trh, trv, qp_y, False, ts=ts)
+                    chroma_tbs(tu, x, y, w, h, True, qp_c, coded, False, 0)
+                    tus.append(tu)
                     pf = int(rng.integers(1, 4))
                     mv = rng.integers(-40 * 16, 40 * 16 + 1, (2, 2))
                     ridx = rng.integers(0, n_refs, 2)
@@ -692,67 +767,123 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                             b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
                             b["ref_idx"], b["mv"] = ridx, mv
                             pblocks.append(b)
+                    done[uy:uy + uh, ux:ux + uw] = True
+                    cus.append(cu)
+                    continue
+                # ---- intra CU: neighbour availability of the whole coding block
+                x0b, y0b = x & (ctb - 1), y & (ctb - 1)
+                cand_up, cand_left = ctb_up or y0b > 0, ctb_left or x0b > 0
+                up_left = (cand_left and cand_up) if (x0b or y0b) else (ctb_left and ctb_up)
+                end_x4 = min(width, (rx + 1) * ctb) >> 2
+                end_y4 = min(height, (ry + 1) * ctb) >> 2
+                top4 = ((u4w - ux) if ctb_up else 0) if y0b == 0 else _avail(done, ux, uy - 1, True, end_x4)
+                left4 = ((end_y4 - uy) if ctb_left else 0) if x0b == 0 else _avail(done, ux - 1, uy, False, end_y4)
+                # ---- luma tool: MIP | MRL | ISP | BDPCM | plain
+                mode_y = int(rng.choice([0, 1, 18, 50] + list(range(2, 67))))
+                ref_idx, isp, bdpcm_y, lfnst_idx = 0, 0, 0, 0
+                mip = "mip" in tools and rng.random() < 0.15
+                r = rng.random()
+                if mip:
+                    cu["mip_flag"], cu["mip_transposed"] = 1, int(rng.integers(0, 2))
+                    size_id = 0 if (w == 4 and h == 4) else 1 if (w == 4 or h == 4 or (w == 8 and h == 8)) else 2
+                    cu["mip_mode"] = int(rng.integers(0, (16, 8, 6)[size_id]))
+                    mode_y = 0
+                elif "mrl" in tools and y0b > 0 and mode_y != 0 and r < 0.2:
+                    ref_idx = int(rng.choice([1, 3]))
+                elif "isp" in tools and w * h > 16 and r < 0.4:
+                    isp = int(rng.integers(1, 3))            # 1 horizontal, 2 vertical split (vvc_ctu.h:113-117)
+                elif "bdpcm" in tools and w <= 32 and h <= 32 and r < 0.55:
+                    bdpcm_y = int(rng.integers(1, 3))        # 1 horizontal, 2 vertical
+                    mode_y = 18 if bdpcm_y == 1 else 50
+                cu["intra_pred_mode_y"], cu["intra_luma_ref_idx"] = mode_y, ref_idx
+                cu["bdpcm_flag"][0, 0] = int(bdpcm_y > 0)
+                # ---- chroma mode: planar / DC / hor / ver / DM / CCLM, or chroma BDPCM
+                choices = [0, 1, 18, 50, mode_y] + ([CCLM_LT, CCLM_L, CCLM_T] if "cclm" in tools else [])
+                mode_c = int(rng.choice(choices))
+                bdpcm_c = 0
+                if "bdpcm" in tools and w <= 64 and h <= 64 and rng.random() < 0.12:
+                    bdpcm_c = int(rng.integers(1, 3))
+                    mode_c = 18 if bdpcm_c == 1 else 50
+                cu["intra_pred_mode_c"] = mode_c
+                cu["bdpcm_flag"][0, 1] = cu["bdpcm_flag"][0, 2] = int(bdpcm_c > 0)
+                # ---- luma transform: TS | LFNST | explicit MTS | DCT2 (ISP: implicit MTS per sub-partition)
+                trh = trv = 0
+                ts_y = bool(bdpcm_y) or ("ts" in tools and not isp and w <= 32 and h <= 32 and rng.random() < 0.08)
+                if not ts_y and not isp:
+                    if "lfnst" in tools and (not mip or min(w, h) >= 16) and rng.random() < 0.3:
+                        lfnst_idx = int(rng.integers(1, 3))
+                    elif "mts" in tools and w <= 32 and h <= 32 and rng.random() < 0.3:
+                        trh, trv = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
+                cu["mts_idx"] = _MTS_OF[(trh, trv)]
+                cu["lfnst_idx"] = lfnst_idx
+                # ---- transform units: one, or the ISP sub-partitions (chroma rides on the last one)
+                if isp:
+                    n_parts = 2 if (w, h) in ((4, 8), (8, 4)) else 4
+                    pw, ph = (w, h // n_parts) if isp == 1 else (w // n_parts, h)
+                    cu["isp_split_type"], cu["num_intra_subpartitions"] = isp, n_parts
+                    cu["n_tu"] = n_parts
+                    trh = 1 if 4 <= pw <= 16 else 0          # implicit MTS (vvc_intra.c:143-160)
+                    trv = 1 if 4 <= ph <= 16 else 0
                 else:
-                    x0b, y0b = x & (ctb - 1), y & (ctb - 1)
-                    cand_up, cand_left = ctb_up or y0b > 0, ctb_left or x0b > 0
-                    up_left = (cand_left and cand_up) if (x0b or y0b) else (ctb_left and ctb_up)
-                    end_x4 = min(width, (rx + 1) * ctb) >> 2
-                    end_y4 = min(height, (ry + 1) * ctb) >> 2
-                    if y0b == 0:
-                        top4 = (u4w - ux) if ctb_up else 0
-                    else:
-                        top4 = _avail(done, ux, uy - 1, True, end_x4)
-                    if x0b == 0:
-                        left4 = (end_y4 - uy) if ctb_left else 0
-                    else:
-                        left4 = _avail(done, ux - 1, uy, False, end_y4)
-                    # ---- luma mode
-                    mip = "mip" in tools and rng.random() < 0.15
-                    mode_y = int(rng.choice([0, 1, 18, 50] + list(range(2, 67))))
-                    ref_idx = 0
-                    if mip:
-                        cu["mip_flag"], cu["mip_transposed"] = 1, int(rng.integers(0, 2))
-                        size_id = 0 if (w == 4 and h == 4) else 1 if (w == 4 or h == 4 or (w == 8 and h == 8)) else 2
-                        cu["mip_mode"] = int(rng.integers(0, (16, 8, 6)[size_id]))
-                        mode_y = 0
-                    elif "mrl" in tools and y0b > 0 and mode_y != 0 and rng.random() < 0.2:
-                        ref_idx = int(rng.choice([1, 3]))
-                    cu["intra_pred_mode_y"], cu["intra_luma_ref_idx"] = mode_y, ref_idx
-                    # ---- chroma mode: planar / DC / hor / ver / DM / CCLM
-                    choices = [0, 1, 18, 50, mode_y] + ([CCLM_LT, CCLM_L, CCLM_T] if "cclm" in tools else [])
-                    mode_c = int(rng.choice(choices))
-                    cu["intra_pred_mode_c"] = mode_c
-                    for c in (0, 1, 2):
-                        hs = 1 if c else 0
-                        bw, bh = w >> hs, h >> hs
-                        raw = mode_y if c == 0 else mode_c
-                        if c == 2 and raw >= CCLM_LT:
-                            continue                      # the CCLM record of c_idx 1 covers Cr too
-                        ib = np.zeros(1, abi.IB_DTYPE)
-                        ib["x0"], ib["y0"], ib["w"], ib["h"], ib["c_idx"] = x >> hs, y >> hs, bw, bh, c
-                        ib["mode"] = raw if raw >= CCLM_LT else wide_angle_mode(raw, bw, bh, c)
-                        ib["ref_idx"] = ref_idx if c == 0 else 0
-                        fl = 0
-                        if c == 0 and mip:
-                            fl |= abi.IB_MIP | (abi.IB_MIP_TRANSPOSED if cu["mip_transposed"][0] else 0)
-                            ib["mip_mode"] = cu["mip_mode"][0]
-                        if raw >= CCLM_LT:
-                            fl |= (abi.IB_RESIDUAL if (coded[1] or coded[2]) else 0)
-                            ib["res_planes"] = (1 if coded[1] else 0) | (2 if coded[2] else 0)
-                        elif coded[c]:
-                            fl |= abi.IB_RESIDUAL
-                        ib["flags"] = fl
-                        ib["up_left"] = up_left
-                        ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
-                        ib["cb_w"], ib["cb_h"] = w, h
-                        iblocks.append(ib)
+                    n_parts, pw, ph = 1, w, h
+                res_c = 0
+                for k in range(n_parts):
+                    tu = np.zeros(1, REF_TU_DTYPE)
+                    tx, ty = (x, y + k * ph) if isp != 2 else (x + k * pw, y)
+                    tu["x0"], tu["y0"], tu["w"], tu["h"] = tx, ty, pw, ph
+                    tu["tb"] = -1
+                    c0 = bool(coded[0]) if n_parts == 1 else bool(rng.random() < 0.7)
+                    tu["coded_flag"][0, 0] = int(c0)
+                    if c0:
+                        code = lfnst_code(lfnst_idx, mode_y, w, h, 0) if lfnst_idx else 0
+                        tu["tb"][0, 0] = new_tb(tx, ty, 0, pw, ph, False, trh, trv, qp_y, True, ts=ts_y, bdpcm=bdpcm_y, lfnst=code)
+                    if k == n_parts - 1:
+                        tu["coded_flag"][0, 1], tu["coded_flag"][0, 2] = int(coded[1]), int(coded[2])
+                        # chroma TBs of an ISP unit cover the whole coding block (vvc_ctu.c hls_transform_unit)
+                        res_c = chroma_tbs(tu, x, y, w, h, False, qp_c, coded, True, bdpcm_c)
+                    tus.append(tu)
+                # ---- records for the engine
+                for c in (0, 1, 2):
+                    hs = 1 if c else 0
+                    bw, bh = w >> hs, h >> hs
+                    raw = mode_y if c == 0 else mode_c
+                    if c == 2 and raw >= CCLM_LT:
+                        continue                      # the CCLM record of c_idx 1 covers Cr too
+                    ib = np.zeros(1, abi.IB_DTYPE)
+                    ib["x0"], ib["y0"], ib["w"], ib["h"], ib["c_idx"] = x >> hs, y >> hs, bw, bh, c
+                    ib["mode"] = raw if raw >= CCLM_LT else wide_angle_mode(raw, bw, bh, c)
+                    ib["ref_idx"] = ref_idx if c == 0 else 0
+                    fl = 0
+                    if c == 0 and mip:
+                        fl |= abi.IB_MIP | (abi.IB_MIP_TRANSPOSED if cu["mip_transposed"][0] else 0)
+                        ib["mip_mode"] = cu["mip_mode"][0]
+                    if c == 0 and isp:                # one record per coding block; w x h = the prediction unit
+                        fl |= abi.IB_ISP
+                        ib["w"], ib["h"] = max(pw, 4), ph
+                    if (c == 0 and bdpcm_y) or (c and bdpcm_c):
+                        fl |= abi.IB_BDPCM
+                    if raw >= CCLM_LT:
+                        fl |= abi.IB_RESIDUAL if res_c else 0
+                        ib["res_planes"] = res_c
+                    elif c == 0:
+                        fl |= abi.IB_RESIDUAL if (isp or coded[0]) else 0
+                    elif res_c & (1 << (c - 1)):
+                        fl |= abi.IB_RESIDUAL
+                    ib["flags"] = fl
+                    ib["up_left"] = up_left
+                    ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
+                    ib["cb_w"], ib["cb_h"] = w, h
+                    iblocks.append(ib)
                 done[uy:uy + uh, ux:ux + uw] = True
                 cus.append(cu)
-                tus.append(tu)
             ctu_first.append(len(iblocks))
     tbs = np.concatenate(tbs) if tbs else np.zeros(0, abi.TB_DTYPE)
     levels = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
-    rparams = abi.residual_params(10, 1)
+    if pic_flags & abi.TB_SCALING:
+        rparams = abi.residual_params(10, 1 if rng.random() < 0.5 else -1, rng.integers(4, 65, (28, 64)).astype(np.uint8),
+                                      rng.integers(4, 65, 14).astype(np.uint8))
+    else:
+        rparams = abi.residual_params(10, 1 if rng.random() < 0.5 else -1)
     order_cls = abi.residual_class(tbs)
     area = tbs["log2_w"].astype(np.int32) + tbs["log2_h"]
     order = np.lexsort((-area, order_cls))
@@ -762,7 +893,11 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.arange(n_refs)
     iparams = abi.inter_params(10, ld, None, None, ref_slot)
-    pb = abi.order_blocks_by_width(np.concatenate(pblocks), iparams) if pblocks else np.zeros(0, abi.PB_DTYPE)
+    if pblocks and inter_tools is not None:     # the tool mix of inter_picture() on this picture's inter CUs
+        pb, iparams = _decorate_blocks(np.random.default_rng(seed + 77), np.concatenate(pblocks), set(inter_tools), n_refs,
+                                       keep_mv=True)
+    else:
+        pb = abi.order_blocks_by_width(np.concatenate(pblocks), iparams) if pblocks else np.zeros(0, abi.PB_DTYPE)
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     ip = abi.IntraParams()

@@ -434,6 +434,12 @@ VVCB200_API int vvcb200_pic_inter(VVCB200Ctx *ctx, const VVCB200PredBlock *block
 /* Stage RECON, residual part: upload levels + descriptors, then one fused launch (see vvcb200_residual_batch). */
 VVCB200_API int vvcb200_pic_residual(VVCB200Ctx *ctx, const int16_t *levels, size_t n_levels,
                                      const VVCB200TransformBlock *tbs, int n, const VVCB200ResidualParams *params);
+/* Stage RECON, intra part (after vvcb200_pic_inter and vvcb200_pic_residual of the same picture): blocks holds the
+ * records of CTU i (raster index) at ctu_first[i] .. ctu_first[i + 1] in decoding order, exactly as the parser meets
+ * them; the context schedules them (vvcb200_intra_schedule) and runs vvcb200_intra_picture with the residual planes
+ * vvcb200_pic_residual filled for TBs flagged VVCB200_TB_TO_RESIDUAL. */
+VVCB200_API int vvcb200_pic_intra(VVCB200Ctx *ctx, const VVCB200IntraBlock *blocks, const uint32_t *ctu_first,
+                                  int ctus_w, int ctus_h, const VVCB200IntraParams *params);
 /* Stage LMCS: inverse luma mapping of the whole picture (host LUT of 1 << bit_depth entries). */
 VVCB200_API int vvcb200_pic_lmcs(VVCB200Ctx *ctx, const uint16_t *inv_lut);
 /* Stages DEBLOCK_V + DEBLOCK_H.  All table pointers are HOST memory (stride4 x rows4 bytes each; ctb_offsets 6 bytes

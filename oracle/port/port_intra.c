@@ -454,6 +454,28 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
                         add_residual_plane(pic, residual, k, b->x0, b->y0, b->w, b->h, ip->bit_depth);
             continue;
         }
+        if ((b->flags & VVCB200_IB_ISP) && !c) {
+            /* one record per ISP coding block: the sub-partitions are predicted and reconstructed one after the other,
+             * each from its predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit */
+            const int hor = b->w == b->cb_w, n_parts = hor ? b->cb_h / b->h : b->cb_w / b->w;
+            for (int k = 0; k < n_parts; k++) {
+                VVCB200IntraBlock s = *b;
+                if (hor) {
+                    s.y0 += k * b->h;
+                    s.avail_left = b->avail_left > k * b->h ? b->avail_left - k * b->h : 0;
+                    if (k) { s.avail_top = b->w; s.up_left = b->avail_left > 0; }
+                } else {
+                    s.x0 += k * b->w;
+                    s.avail_top = b->avail_top > k * b->w ? b->avail_top - k * b->w : 0;
+                    if (k) { s.avail_left = b->h; s.up_left = b->avail_top > 0; }
+                }
+                uint16_t *src = (uint16_t *)(pic->plane[0] + (size_t)s.y0 * pic->stride[0]) + s.x0;
+                intra_pred_block(src, pic->stride[0] / 2, &s, ip->bit_depth);
+                if (b->flags & VVCB200_IB_RESIDUAL)
+                    add_residual_plane(pic, residual, 0, s.x0, s.y0, s.w, s.h, ip->bit_depth);
+            }
+            continue;
+        }
         uint16_t *src = (uint16_t *)(pic->plane[c] + (size_t)b->y0 * pic->stride[c]) + b->x0;
         intra_pred_block(src, pic->stride[c] / 2, b, ip->bit_depth);
         if (b->flags & VVCB200_IB_RESIDUAL)

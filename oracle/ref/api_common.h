@@ -41,7 +41,7 @@ typedef struct VVCRefCU {
     int32_t bdpcm_flag[3];
     int32_t ciip_flag, coded_flag;
     int32_t first_tu, n_tu;
-    int32_t mts_idx;
+    int32_t mts_idx, lfnst_idx;
 } VVCRefCU;
 
 typedef struct VVCRefTU {

@@ -275,6 +275,8 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
             cu->num_intra_subpartitions = d->num_intra_subpartitions;
             cu->ciip_flag = d->ciip_flag;
             cu->mts_idx = d->mts_idx;
+            cu->lfnst_idx = d->lfnst_idx;
+            cu->apply_lfnst_flag[0] = d->lfnst_idx > 0;      /* single tree: LFNST on luma only */
             for (int c = 0; c < 3; c++)
                 cu->bdpcm_flag[c] = d->bdpcm_flag[c];
             for (int y = d->y0 >> 2; y < (d->y0 + d->h) >> 2; y++)
@@ -302,6 +304,10 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
                     tb->x0 = t->x0; tb->y0 = t->y0;
                     tb->tb_width = t->w >> (c ? 1 : 0);
                     tb->tb_height = t->h >> (c ? 1 : 0);
+                    if (c && d->isp_split_type) {           /* chroma of an ISP unit: the whole coding block */
+                        tb->x0 = d->x0; tb->y0 = d->y0;
+                        tb->tb_width = d->w >> 1; tb->tb_height = d->h >> 1;
+                    }
                     tb->log2_tb_width = av_log2(tb->tb_width);
                     tb->log2_tb_height = av_log2(tb->tb_height);
                     if (t->tb[c] >= 0) {
@@ -328,6 +334,12 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
     }
     e->rsh.sh_dep_quant_used_flag = 0;
     e->rsh.sh_explicit_scaling_list_used_flag = 0;
+    for (int i = 0; i < n_tu_total; i++)                    /* slice-level switches, carried by every TB of the picture */
+        for (int c = 0; c < 3; c++)
+            if (tus[i].tb[c] >= 0) {
+                e->rsh.sh_dep_quant_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_DEP_QUANT);
+                e->rsh.sh_explicit_scaling_list_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_SCALING);
+            }
     for (int ry = 0; ry < ctb_h; ry++)
         for (int rx = 0; rx < ctb_w; rx++)
             ff_vvc_reconstruct(lc, ry * ctb_w + rx, rx, ry);

@@ -12,17 +12,28 @@ def oracle_picture(pic):
     it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
     fwd, inv = pic["lmcs"] if pic["lmcs"] is not None else (None, None)
     edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+    ia = pic.get("intra")
     if refapi.available():
-        refapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
-        refapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], rs["intra_mode"])
+        if len(it["blocks"]):
+            refapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+        if ia is not None:        # one partition of inter and intra CUs: the reference's own RECON stage does both
+            refapi.recon_picture(planes, pic["ref"], ia["params"])
+        else:
+            refapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], rs["intra_mode"])
         if inv is not None:
             refapi.lmcs_picture(planes, inv, pic["ctb_log2"])
         refapi.deblock_picture(planes, db)
         refapi.sao_picture(planes, lf)
         refapi.alf_picture(planes, lf)
         return planes
-    portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
-    portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"])
+    if len(it["blocks"]):
+        portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+    if ia is not None:
+        res = [np.zeros(p.shape, np.int16) for p in planes]
+        portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
+        portapi.intra_picture(planes, res, ia["blocks"], ia["params"])
+    else:
+        portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"])
     if inv is not None:
         portapi.lmcs_picture(planes, inv)
     portapi.deblock_picture(planes, edge, db["qp"], db["ctb_offsets"], db["stride4"], db["params"])
@@ -50,13 +61,20 @@ class EnginePicture:
         self.sao = ctx.pinned_copy(lf["sao"])
         self.alf = ctx.pinned_copy(lf["alf"])
         self.alf_params = ctx.pinned_copy(lf["alf_params"])
+        ia = pic.get("intra")
+        self.intra = None
+        if ia is not None and len(ia["blocks"]):
+            ctb = pic["ctb_log2"]
+            self.intra = (ctx.pinned_copy(ia["blocks"]), ctx.pinned_copy(ia["ctu_first"]),
+                          (pic["width"] + (1 << ctb) - 1) >> ctb, (pic["height"] + (1 << ctb) - 1) >> ctb, ia["params"])
         self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
         self.out = ctx.pinned_planes()
         # the picture is reconstructed into the slot after the references; ref_slot[][] already maps to 0..n_refs-1
         self.cur_slot = self.n_refs
 
     def h2d_bytes(self):
-        return int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
+        intra = 0 if self.intra is None else self.intra[0].nbytes + self.intra[1].nbytes
+        return intra + int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
                    self.ctb_offsets.nbytes + self.sao.nbytes + self.alf.nbytes + self.alf_params.nbytes)
 
     def d2h_bytes(self):
@@ -71,6 +89,8 @@ class EnginePicture:
         ctx.begin(self.cur_slot)
         ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0])
         ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
+        if self.intra is not None:
+            ctx.intra(*self.intra)
         if self.luts is not None:
             ctx.lmcs(self.luts[1])
         ctx.deblock(self.edge, self.qp, self.ctb_offsets, pic["deblock"]["stride4"], pic["deblock"]["params"])

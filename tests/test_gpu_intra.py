@@ -46,6 +46,7 @@ def run_gpu(pic, schedule=True, repeat=1):
     return out
 
 
+ALL_TOOLS = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp")
 CASES = [
     (1, 208, 120, 6, ("pdpc",), 0.6),
     (2, 208, 120, 5, ("pdpc", "mrl"), 0.6),
@@ -53,6 +54,11 @@ CASES = [
     (4, 208, 120, 6, ("pdpc", "mrl", "mip", "cclm"), 0.6),
     (5, 416, 240, 7, ("pdpc", "mrl", "mip", "cclm", "mts"), 1.0),
     (6, 136, 72, 5, ("pdpc", "mrl", "mip", "cclm"), 0.3),
+    (8, 208, 120, 6, ("isp",), 0.8),
+    (9, 208, 120, 5, ("bdpcm", "ts", "lfnst"), 0.8),
+    (10, 256, 192, 7, ALL_TOOLS, 0.7),
+    (11, 136, 72, 5, ALL_TOOLS, 1.0),
+    (12, 416, 240, 6, ALL_TOOLS, 0.4),
     (7, 832, 480, 7, ("pdpc", "mrl", "mip", "cclm", "mts"), 0.5),
 ]
 

@@ -26,6 +26,25 @@ def test_full_picture_md5(seed, w, h, ctb, lmcs, ns, lfase):
         ctx.close()
 
 
+@pytest.mark.parametrize("seed,w,h,ctb,lmcs,frac", [(21, 416, 240, 7, False, 0.3), (22, 416, 240, 6, True, 0.5),
+                                                    (23, 832, 480, 5, False, 1.0), (24, 1920, 1080, 7, True, 0.15)])
+def test_full_picture_with_intra_cus_md5(seed, w, h, ctb, lmcs, frac):
+    """One CU partition with inter and intra CUs: INTER -> residual (inter TBs in place, intra TBs to the residual
+    planes) -> intra wavefront -> (LMCS) -> deblock -> SAO -> ALF, against the reference's INTER + ff_vvc_reconstruct."""
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=lmcs, intra_fraction=frac)
+    want = pipeline.oracle_picture(pic)
+    ctx = lib.Context(0, w, h, dpb_size=3)
+    try:
+        ep = pipeline.EnginePicture(ctx, pic)
+        ep.upload_refs()
+        for _ in range(2):
+            ep.run()
+            ctx.sync()
+            assert util.plane_md5(ep.out) == util.plane_md5(want)
+    finally:
+        ctx.close()
+
+
 def test_full_picture_1080p_md5():
     """BASELINE config 2 size: 1080p full picture recon + deblock + SAO + ALF."""
     pic = synth.full_picture(11, 1920, 1080)

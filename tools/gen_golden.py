@@ -88,7 +88,8 @@ def golden_loopfilter():
 
 def golden_intra():
     """One small picture through the reference's ff_vvc_reconstruct (inter CUs predicted first), planes kept whole."""
-    seed, w, h, ctb, tools, frac = 20261107, 136, 72, 5, ("pdpc", "mrl", "mip", "cclm", "mts"), 0.7
+    seed, w, h, ctb, frac = 20261107, 136, 72, 5, 0.7
+    tools = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp")
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
     planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
     if len(pic["inter"]["blocks"]):
