@@ -33,7 +33,7 @@ if ROOT not in sys.path:
 METRIC = "4K 10-bit VVC recon+loop-filter frames/s per B200; % HBM roofline; 8-GPU agg"
 WORKLOADS = {"4k": (3840, 2160), "1080p": (1920, 1080)}
 L2_BYTES = 126 * 1024 * 1024
-STAGES = ["inter", "residual", "deblock", "sao", "alf"]
+STAGES = ["inter", "residual", "intra", "deblock", "sao", "alf"]
 
 
 def env_int(name, default):
@@ -54,23 +54,26 @@ def measured_peaks():
 # ----------------------------------------------------------------------------------------------------------
 # workload
 # ----------------------------------------------------------------------------------------------------------
-def make_picture(seed, width, height):
-    """Synthetic parsed inter picture (SURVEY.md §8d config 2/3 shape).  Cached under /tmp for re-runs."""
+def make_picture(seed, width, height, intra_fraction):
+    """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
+    with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v4_%dx%d_%d.pkl" % (width, height, seed)
+    cache = "/tmp/vvcb200_bench_v6_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
+    kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
+             ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):
         try:
             with open(cache, "rb") as f:
                 pic = pickle.load(f)
-            for k, cls in (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams)):
+            for k, cls in kinds:
                 pic[k]["params"] = cls.from_buffer_copy(pic[k]["params"])
             return pic
         except Exception:
             pass
-    pic = synth.full_picture(seed, width, height)
+    pic = synth.full_picture(seed, width, height, intra_fraction=intra_fraction)
     try:
         dump = dict(pic)
-        for k in ("inter", "residual", "deblock"):
+        for k, _ in kinds:
             dump[k] = dict(pic[k], params=bytes(pic[k]["params"]))
         with open(cache + ".tmp", "wb") as f:
             pickle.dump(dump, f, protocol=4)
@@ -89,17 +92,29 @@ def picture_stats(pic):
     coded = int(area.sum() + area[(tbs["flags"] & 64) != 0].sum())            # joint TBs rebuild a second plane
     b = pic["inter"]["blocks"]
     lists = np.where(b["pred_flag"] == 3, 2, 1).astype(np.int64)
-    ref_samples = int((b["w"].astype(np.int64) * b["h"] * lists).sum() * 3 // 2)   # luma + 2 x quarter-size chroma
+    # luma + 2 x quarter-size chroma; affine units come as luma-only 4x4 and chroma-only (8x8 footprint) records
+    planes_x2 = np.where(b["flags"] & 8, 2, np.where(b["flags"] & 16, 1, 3)).astype(np.int64)
+    ref_samples = int((b["w"].astype(np.int64) * b["h"] * lists * planes_x2).sum() // 2)
+    ib = pic["intra"]["blocks"]
+    iw = np.where((ib["flags"] & 4) != 0, ib["cb_w"], ib["w"]).astype(np.int64)      # ISP records stand for the coding block
+    ih = np.where((ib["flags"] & 4) != 0, ib["cb_h"], ib["h"]).astype(np.int64)
+    cclm = ib["mode"] >= 81
+    intra_samples = int((iw * ih * np.where(cclm, 2, 1)).sum())
+    intra_bytes = int((2 * iw * ih * np.where(cclm, 2, 1)                                # samples out
+                       + np.where((ib["flags"] & 16) != 0, 2 * iw * ih * np.where(cclm, 2, 1), 0)   # int16 residual in
+                       + 2 * 2 * (iw + ih) * np.where(cclm, 2, 1)                        # reference edges in
+                       + np.where(cclm, 8 * iw * ih, 0)).sum())                          # co-located luma for CCLM
     stage = {
         "inter": 2 * ref_samples + 2 * S,             # reference samples in, prediction out
         "residual": 2 * int(area.sum()) + 4 * coded,  # int16 levels in, destination read + write
+        "intra": intra_bytes,
         "deblock": 2 * (2 * S + 2 * S),               # two passes, each at most picture in + picture out
         "sao": 2 * S + 2 * S,
         "alf": (2 * S + 2 * S) + 2 * S_y,             # picture in + out, luma once more for CC-ALF
     }
     a_pic = 2 * int(area.sum()) + 2 * ref_samples + 2 * S   # §8d: levels in + reference reads + final picture out
     return dict(S=S, coded_samples=coded, ref_samples=ref_samples, stage_bytes=stage, a_pic=a_pic, rho=coded / S,
-                r=ref_samples / S)
+                r=ref_samples / S, intra_share=intra_samples / S)
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -151,36 +166,44 @@ class ClockSampler:
 # CPU arm: the reference's own C on host threads, same stage chain
 # ----------------------------------------------------------------------------------------------------------
 def cpu_picture(pic, threads):
-    """One whole picture through the reference's stage functions, every stage spread over `threads` host threads
-    (sub-blocks / TBs dealt round-robin; loop filters by CTB rows with a join per pass).  Returns seconds, kind."""
-    from ffmpeg_b200 import lib
+    """One whole picture through the reference's stage functions, every stage spread over `threads` host threads:
+    INTER sub-blocks / coding units dealt round-robin, RECON (every residual + intra prediction,
+    ff_vvc_reconstruct) as a CTU-row wavefront like the reference's own scheduler, loop filters by CTB rows with a
+    join per pass.  Returns seconds, kind."""
+    from ffmpeg_b200 import abi, lib
     from oracle import portapi, refapi
-    it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+    it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
     planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
     use_ref = refapi.available()
 
     def spread(fn, parts):
-        ths = [threading.Thread(target=fn, args=(p,)) for p in parts]
+        ths = [threading.Thread(target=fn, args=(p,)) for p in parts if len(p)]
         for th in ths:
             th.start()
         for th in ths:
             th.join()
 
-    blocks = [np.ascontiguousarray(it["blocks"][t::threads]) for t in range(threads)]
-    tbs = [(np.ascontiguousarray(rs["tbs"][t::threads]), np.ascontiguousarray(rs["intra_mode"][t::threads]))
-           for t in range(threads)]
+    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY
+    regular = it["blocks"][(it["blocks"]["flags"] & special) == 0] if use_ref else it["blocks"]
+    blocks = [np.ascontiguousarray(regular[t::threads]) for t in range(threads)]
+    cus = [np.ascontiguousarray(it["cus"][t::threads]) for t in range(threads)]
     edge = None if use_ref else lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"],
                                                        pic["ctb_log2"])
+    prof = it["prof"] if len(it["prof"]) else None
     t0 = time.perf_counter()
     if use_ref:
         spread(lambda b: refapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
-        spread(lambda tb: refapi.residual_batch(planes, rs["levels"], tb[0], rs["params"], tb[1]), tbs)
+        spread(lambda c: refapi.inter_cus(planes, it["refs"], c, it["sb_mv"], it["params"]), cus)
+        refapi.recon_picture(planes, pic["ref"], ia["params"], threads=threads)
         refapi.deblock_picture(planes, db, threads=threads)
         refapi.sao_picture(planes, lf, threads=threads)
         refapi.alf_picture(planes, lf, threads=threads)
     else:
-        spread(lambda b: portapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
-        spread(lambda tb: portapi.residual_batch(planes, rs["levels"], tb[0], rs["params"]), tbs)
+        spread(lambda b: portapi.inter_batch(planes, it["refs"], b, it["params"], prof=prof), blocks)
+        res = [np.zeros(p.shape, np.int16) for p in planes]
+        tbs = [np.ascontiguousarray(rs["tbs"][t::threads]) for t in range(threads)]
+        spread(lambda tb: portapi.residual_batch(planes, rs["levels"], tb, rs["params"], residual_planes=res), tbs)
+        portapi.intra_picture(planes, res, ia["blocks"], ia["params"])
         portapi.deblock_picture(planes, edge, db["qp"], db["ctb_offsets"], db["stride4"], db["params"])
         tmp = [np.zeros_like(p) for p in planes]
         portapi.sao_picture(tmp, planes, lf)
@@ -197,8 +220,9 @@ def cpu_baseline(pic, budget_s=15.0, max_pics=30):
         t += dt
         n += 1
     return {"value": n / t, "unit": "frames/s", "cores": threads, "kind": kind,
-            "sample": "%d whole pictures through INTER + residual + deblock + SAO + ALF; sub-blocks/TBs dealt "
-                      "round-robin and loop-filter CTB rows split over %d host threads (x86 asm not built: no nasm)" % (n, threads)}
+            "sample": "%d whole pictures through INTER + RECON (residual + intra) + deblock + SAO + ALF; sub-blocks / CUs "
+                      "dealt round-robin, RECON as a CTU-row wavefront, loop-filter CTB rows split over %d host threads "
+                      "(x86 asm not built: no nasm)" % (n, threads)}
 
 
 # ----------------------------------------------------------------------------------------------------------
@@ -210,24 +234,26 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k", choices=sorted(WORKLOADS))
     ap.add_argument("--seed", type=int, default=2026)
+    ap.add_argument("--intra-fraction", type=float, default=0.1, help="share of coding units that are intra")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     width, height = WORKLOADS[args.workload]
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    config = {"workload": "%s 4:2:0 10-bit synthetic inter picture (%dx%d), CTU 128, 2 reference pictures"
-                          % (args.workload, width, height),
-              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW, DMVR, BDOF)",
-                         "residual (dequant, inverse DCT2/DST7/DCT8, TS, joint CbCr, add)",
+    config = {"workload": "%s 4:2:0 10-bit synthetic random-access picture (%dx%d), CTU 128, 2 reference pictures, "
+                          "%.0f%% of the coding units intra" % (args.workload, width, height, 100 * args.intra_fraction),
+              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW, DMVR, BDOF, affine + PROF, GPM)",
+                         "residual (dequant, inverse DCT2/DST7/DCT8, LFNST, TS, BDPCM, joint CbCr, scaling lists, add)",
+                         "intra (planar / DC / angular + PDPC, MRL, ISP, MIP, CCLM; dependency-driven)",
                          "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
-              "not_in_step": "intra prediction, PROF/affine/GPM/CIIP (not built yet, see DESIGN.md)",
+              "not_in_step": "CIIP blend, LMCS (separate kernels exist; chroma residual scaling derivation not built)",
               "streams": "one independent picture stream per GPU (replicas, no collective)"}
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        pic = make_picture(args.seed, width, height)
+        pic = make_picture(args.seed, width, height, args.intra_fraction)
         threads = os.cpu_count() or 1
         for _ in range(args.warmup):
             cpu_picture(pic, threads)
@@ -262,11 +288,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    pic = make_picture(args.seed + rank, width, height)
+    pic = make_picture(args.seed + rank, width, height, args.intra_fraction)
     st = picture_stats(pic)
-    it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+    it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
     frame_bytes = 2 * st["S"]
+    ctb = pic["ctb_log2"]
+    irecs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb)
     config.update({"transform_blocks": int(len(rs["tbs"])), "pred_blocks": int(len(it["blocks"])),
+                   "intra_records": int(len(irecs)), "intra_sample_share": round(st["intra_share"], 3),
                    "coded_fraction": round(st["rho"], 3), "ref_samples_per_sample": round(st["r"], 3)})
 
     # ---- device-resident arm: `rot` complete copies of the picture's working set, visited round-robin -----------
@@ -275,7 +304,7 @@ def main():
     def dev(a):
         return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()
 
-    per_set = (len(it["refs"]) + 2) * frame_bytes + rs["levels"].nbytes + rs["tbs"].nbytes + it["blocks"].nbytes + \
+    per_set = (len(it["refs"]) + 3) * frame_bytes + irecs.nbytes + rs["levels"].nbytes + rs["tbs"].nbytes + it["blocks"].nbytes + \
         edge.nbytes + db["qp"].nbytes
     rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
     config["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
@@ -286,7 +315,11 @@ def main():
         s["refs"] = [util.to_device_planes(r, torch) for r in it["refs"]]
         s["cur"] = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
         s["tmp"] = [torch.zeros_like(t) for t in s["cur"]]
-        s["cur_p"], s["tmp_p"] = lib.device_planes(s["cur"]), lib.device_planes(s["tmp"])
+        s["res"] = [torch.zeros_like(t) for t in s["cur"]]
+        s["cur_p"], s["tmp_p"], s["res_p"] = lib.device_planes(s["cur"]), lib.device_planes(s["tmp"]), lib.device_planes(s["res"])
+        s["irecs"] = dev(irecs)
+        s["prof"] = dev(it["prof"]) if len(it["prof"]) else None
+        s["marks"] = torch.zeros(lib.intra_scratch_bytes(width, height), dtype=torch.uint8, device="cuda")
         s["refs_p"] = [lib.device_planes(r) for r in s["refs"]]
         s["blocks"], s["levels"], s["tbs"] = dev(it["blocks"]), dev(rs["levels"]), dev(rs["tbs"])
         s["edge"] = torch.from_numpy(edge).cuda()
@@ -299,30 +332,31 @@ def main():
 
     def step(i, ev=None):
         s = sets[i % rot]
-        marks = []
-        lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], n_blocks, it["params"])
-        marks.append("inter")
+        lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], n_blocks, it["params"], prof=s["prof"])
         if ev is not None:
             ev[1].record()
-        lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], n_tbs, rs["params"])
+        lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], n_tbs, rs["params"], residual=s["res_p"])
         if ev is not None:
             ev[2].record()
-        lib.deblock_picture(s["cur_p"], s["db"], db["params"])
+        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"])
         if ev is not None:
             ev[3].record()
-        lib.sao_picture(s["tmp_p"], s["cur_p"], s["sao"], pic["ctb_log2"])
+        lib.deblock_picture(s["cur_p"], s["db"], db["params"])
         if ev is not None:
             ev[4].record()
-        lib.alf_picture(s["cur_p"], s["tmp_p"], s["alf"], s["alfp"], pic["ctb_log2"])
+        lib.sao_picture(s["tmp_p"], s["cur_p"], s["sao"], pic["ctb_log2"])
         if ev is not None:
             ev[5].record()
+        lib.alf_picture(s["cur_p"], s["tmp_p"], s["alf"], s["alfp"], pic["ctb_log2"])
+        if ev is not None:
+            ev[6].record()
 
     for i in range(warmup):
         step(i)
     barrier()
     sampler = ClockSampler(local) if rank == 0 else None
     # stage boundaries are marked with events on the launching stream (torch's current stream)
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(6)] for _ in range(args.steps)]
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(args.steps)]
     ev_end = torch.cuda.Event(enable_timing=True)
     l0 = lib.launch_count()
     t_host0 = time.perf_counter()
@@ -375,7 +409,7 @@ def main():
         e2e_s = float(t.item())
     e2e = {"value": world * e2e_steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": ep.h2d_bytes(),
            "d2h_bytes_per_step": ep.d2h_bytes(), "steps": e2e_steps,
-           "api": "vvcb200_pic_begin/inter/residual/deblock/sao_alf/download (include/vvc_b200.h), pinned host buffers; "
+           "api": "vvcb200_pic_begin/inter/residual/intra/deblock/sao_alf/download (include/vvc_b200.h), pinned host buffers; "
                   "reference pictures stay in the context's DPB"}
     e2e_ok = util.plane_md5(ep.out)
     ctx.close()
@@ -387,7 +421,7 @@ def main():
 
     peak, peak_kind = measured_peaks()
     top = max(stage_ms, key=stage_ms.get)
-    launches_per_stage = {"inter": 1, "residual": 1, "deblock": 2, "sao": 1, "alf": 2}
+    launches_per_stage = {"inter": 1, "residual": 1, "intra": 1, "deblock": 2, "sao": 1, "alf": 2}
     kernel_ms = stage_ms[top] / launches_per_stage[top]
     algo = st["stage_bytes"][top] / launches_per_stage[top]
     achieved = algo / (kernel_ms * 1e-3) / 1e9

@@ -476,7 +476,8 @@ def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slic
     rp = recon_picture(seed, width, height, ctb_log2=ctb_log2, intra_fraction=intra_fraction, n_refs=n_refs,
                        tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "mts", "ts", "lfnst", "joint", "dep_quant",
                               "scaling"), mean_log2=mean_log2,
-                       inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"))
+                       inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"),
+                       inter_kinds=(CU_REGULAR,) * 7 + (CU_AFFINE,) * 2 + (CU_GPM,), lmcs=lmcs)
     db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
     lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
     out = dict(inter=rp["inter"], residual=rp["residual"], intra=rp["intra"], ref=rp["ref"], deblock=db, lf=lf,
@@ -484,7 +485,6 @@ def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slic
     out["residual"]["intra_mode"] = np.zeros(len(rp["residual"]["tbs"]), np.int32)
     if lmcs:
         out["lmcs"] = lmcs_luts(seed + 4)
-        out["inter"]["blocks"]["flags"] |= abi.PB_LMCS
     return out
 
 
@@ -501,6 +501,73 @@ CU_REGULAR, CU_AFFINE, CU_GPM = 0, 1, 2
 def _round_mv_half(v):
     """ff_vvc_round_mv(mv, 0, 1): halve, rounding half away from zero (reference vvc_mvs.c:1739-1749)."""
     return (v + 1 - (v >= 0)) >> 1
+
+
+def _emit_inter_cu(rng, c, kind, n_refs, lmcs, sb_mv, blocks, prof):
+    """Fill the CU-level record `c` (geometry already set) for an inter CU of `kind` and append its engine records:
+    sub-blocks to `blocks`, 4x4 sub-block vectors to `sb_mv`, PROF tables to `prof`."""
+    x, y, w, h = int(c["x0"]), int(c["y0"]), int(c["w"]), int(c["h"])
+    c["kind"] = kind
+    pf = int(rng.integers(1, 4))
+    c["pred_flag"] = pf if kind != CU_GPM else 3
+    c["ref_idx"] = rng.integers(0, n_refs, 2)
+    c["mv"] = rng.integers(-48 * 16, 48 * 16 + 1, (2, 2))
+    flags = (abi.PB_WP if rng.random() < 0.3 and kind != CU_GPM else 0) | (abi.PB_LMCS if lmcs else 0)
+    if kind == CU_REGULAR and rng.random() < 0.3:
+        flags |= abi.PB_HPEL_IF
+    c["flags"] = flags
+    if pf == 3 and kind != CU_GPM and rng.random() < 0.3:
+        c["bcw_idx"] = int(rng.integers(1, 5))
+    if kind == CU_REGULAR:
+        if w > 16 or h > 16:        # only reached when no other kind is allowed: keep the reference's one-sub-block view legal
+            c["w"], c["h"] = w, h = min(w, 16), min(h, 16)
+        b = np.zeros(1, abi.PB_DTYPE)
+        b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x, y, w, h, pf, c["bcw_idx"]
+        b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags
+        blocks.append(b)
+    elif kind == CU_GPM:
+        c["gpm_partition_idx"] = int(rng.integers(0, 64))
+        c["gpm_list"] = rng.integers(0, 2, 2)
+        for ty in range(0, h, 16):
+            for tx in range(0, w, 16):
+                b = np.zeros(1, abi.PB_DTYPE)
+                b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), 3
+                b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags | abi.PB_GPM
+                b["aux"] = abi.gpm_aux(int(c["gpm_partition_idx"]), int(np.log2(w)), int(np.log2(h)), tx, ty,
+                                       int(c["gpm_list"][0]), int(c["gpm_list"][1]))
+                blocks.append(b)
+    else:
+        nsx, nsy = w // 4, h // 4
+        c["sb_mv_off"] = len(sb_mv)
+        base = c["mv"].astype(np.int64)
+        gx = rng.integers(-6, 7, (2, 2))
+        gy = rng.integers(-6, 7, (2, 2))
+        prof_idx = len(prof)
+        c["cb_prof_flag"] = rng.integers(0, 2, 2)
+        pt = np.zeros(1, abi.PROF_DTYPE)
+        pt["diff_mv_x"] = c["diff_mv_x"] = rng.integers(-31, 32, (2, 16))
+        pt["diff_mv_y"] = c["diff_mv_y"] = rng.integers(-31, 32, (2, 16))
+        prof.append(pt)
+        mvs = np.zeros((nsy, nsx, 2, 2), np.int64)
+        for sy in range(nsy):
+            for sx in range(nsx):
+                mvs[sy, sx] = np.clip(base + gx * sx + gy * sy, -(1 << 17), (1 << 17) - 1)
+                sb_mv.append(mvs[sy, sx].astype(np.int32))
+        pflags = (abi.PB_PROF0 if c["cb_prof_flag"][0] else 0) | (abi.PB_PROF1 if c["cb_prof_flag"][1] else 0)
+        for sy in range(nsy):
+            for sx in range(nsx):
+                b = np.zeros(1, abi.PB_DTYPE)
+                b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 4, 4, pf, c["bcw_idx"]
+                b["ref_idx"], b["mv"] = c["ref_idx"], mvs[sy, sx]
+                b["flags"] = flags | abi.PB_AFFINE | abi.PB_LUMA_ONLY | pflags
+                b["aux"] = prof_idx
+                blocks.append(b)
+                if not (sx & 1) and not (sy & 1):       # derive_affine_mvc: average with the diagonal neighbour
+                    b = np.zeros(1, abi.PB_DTYPE)
+                    b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 8, 8, pf, c["bcw_idx"]
+                    b["ref_idx"], b["mv"] = c["ref_idx"], _round_mv_half(mvs[sy, sx] + mvs[sy + 1, sx + 1])
+                    b["flags"] = (flags & ~abi.PB_LMCS) | abi.PB_CHROMA_ONLY
+                    blocks.append(b)
 
 
 def inter_cu_picture(seed, width, height, n_refs=2, kinds=(CU_REGULAR, CU_AFFINE, CU_GPM), lmcs=False):
@@ -522,67 +589,7 @@ def inter_cu_picture(seed, width, height, n_refs=2, kinds=(CU_REGULAR, CU_AFFINE
             kind = CU_AFFINE if CU_AFFINE in kinds else CU_GPM
             if kind == CU_GPM and not ratio_ok:
                 kind = CU_REGULAR
-        c["kind"] = kind
-        pf = int(rng.integers(1, 4))
-        c["pred_flag"] = pf if kind != CU_GPM else 3
-        c["ref_idx"] = rng.integers(0, n_refs, 2)
-        c["mv"] = rng.integers(-48 * 16, 48 * 16 + 1, (2, 2))
-        flags = (abi.PB_WP if rng.random() < 0.3 and kind != CU_GPM else 0) | (abi.PB_LMCS if lmcs else 0)
-        if kind == CU_REGULAR and rng.random() < 0.3:
-            flags |= abi.PB_HPEL_IF
-        c["flags"] = flags
-        if pf == 3 and kind != CU_GPM and rng.random() < 0.3:
-            c["bcw_idx"] = int(rng.integers(1, 5))
-        if kind == CU_REGULAR:
-            if w > 16 or h > 16:        # only reached when no other kind is allowed: keep the reference's one-sub-block view legal
-                c["w"], c["h"] = w, h = min(w, 16), min(h, 16)
-            b = np.zeros(1, abi.PB_DTYPE)
-            b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x, y, w, h, pf, c["bcw_idx"]
-            b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags
-            blocks.append(b)
-        elif kind == CU_GPM:
-            c["gpm_partition_idx"] = int(rng.integers(0, 64))
-            c["gpm_list"] = rng.integers(0, 2, 2)
-            for ty in range(0, h, 16):
-                for tx in range(0, w, 16):
-                    b = np.zeros(1, abi.PB_DTYPE)
-                    b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), 3
-                    b["ref_idx"], b["mv"], b["flags"] = c["ref_idx"], c["mv"], flags | abi.PB_GPM
-                    b["aux"] = abi.gpm_aux(int(c["gpm_partition_idx"]), int(np.log2(w)), int(np.log2(h)), tx, ty,
-                                           int(c["gpm_list"][0]), int(c["gpm_list"][1]))
-                    blocks.append(b)
-        else:
-            nsx, nsy = w // 4, h // 4
-            c["sb_mv_off"] = len(sb_mv)
-            base = c["mv"].astype(np.int64)
-            gx = rng.integers(-6, 7, (2, 2))
-            gy = rng.integers(-6, 7, (2, 2))
-            prof_idx = len(prof)
-            c["cb_prof_flag"] = rng.integers(0, 2, 2)
-            pt = np.zeros(1, abi.PROF_DTYPE)
-            pt["diff_mv_x"] = c["diff_mv_x"] = rng.integers(-31, 32, (2, 16))
-            pt["diff_mv_y"] = c["diff_mv_y"] = rng.integers(-31, 32, (2, 16))
-            prof.append(pt)
-            mvs = np.zeros((nsy, nsx, 2, 2), np.int64)
-            for sy in range(nsy):
-                for sx in range(nsx):
-                    mvs[sy, sx] = np.clip(base + gx * sx + gy * sy, -(1 << 17), (1 << 17) - 1)
-                    sb_mv.append(mvs[sy, sx].astype(np.int32))
-            pflags = (abi.PB_PROF0 if c["cb_prof_flag"][0] else 0) | (abi.PB_PROF1 if c["cb_prof_flag"][1] else 0)
-            for sy in range(nsy):
-                for sx in range(nsx):
-                    b = np.zeros(1, abi.PB_DTYPE)
-                    b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 4, 4, pf, c["bcw_idx"]
-                    b["ref_idx"], b["mv"] = c["ref_idx"], mvs[sy, sx]
-                    b["flags"] = flags | abi.PB_AFFINE | abi.PB_LUMA_ONLY | pflags
-                    b["aux"] = prof_idx
-                    blocks.append(b)
-                    if not (sx & 1) and not (sy & 1):       # derive_affine_mvc: average with the diagonal neighbour
-                        b = np.zeros(1, abi.PB_DTYPE)
-                        b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"], b["bcw_idx"] = x + 4 * sx, y + 4 * sy, 8, 8, pf, c["bcw_idx"]
-                        b["ref_idx"], b["mv"] = c["ref_idx"], _round_mv_half(mvs[sy, sx] + mvs[sy + 1, sx + 1])
-                        b["flags"] = (flags & ~abi.PB_LMCS) | abi.PB_CHROMA_ONLY
-                        blocks.append(b)
+        _emit_inter_cu(rng, c, kind, n_refs, lmcs, sb_mv, blocks, prof)
     weight = np.zeros((2, 3, 16), np.int16)
     offset = rng.integers(-64, 64, (2, 3, 16)).astype(np.int16)
     weight[:, 0, :] = (1 << ld[0]) + rng.integers(-128, 128, (2, 16))
@@ -650,14 +657,16 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
          residual: TB batch (TBs of intra CUs flagged TB_TO_RESIDUAL),
          intra: VVCB200IntraBlock records + per-CTU ranges (stage RECON wavefront).
     tools: intra side "mrl", "mip", "cclm", "isp", "bdpcm"; residual side "mts", "ts", "lfnst", "joint", "dep_quant",
-    "scaling" ("pdpc" is always on, it is not signalled).
+    "scaling" ("pdpc" is always on, it is not signalled).  inter_tools: block-level tool mix of inter_picture() on the
+    regular inter CUs; inter_kinds: CU kinds to draw from (CU_REGULAR, CU_AFFINE, CU_GPM) — affine / GPM units come with
+    their CU-level description (`inter.cus`, `inter.sb_mv`) for the reference harness and PROF tables (`inter.prof`).
     Neighbour availability follows the reference's rules (vvc_intra.c:593-648) on a 4x4-unit reconstruction mask."""
     rng = np.random.default_rng(seed)
     tools = set(tools)
@@ -667,6 +676,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     done = np.zeros((u4h, u4w), bool)               # luma and chroma become available together (single tree)
     cus, tus, tbs, lv_chunks = [], [], [], []
     pblocks, iblocks, ctu_first = [], [], [0]
+    cu_blocks, cu_recs, sb_mv, prof = [], [], [], []     # affine / GPM coding units
     lv_off = 0
     pic_flags = (abi.TB_DEP_QUANT if "dep_quant" in tools and rng.random() < 0.5 else 0) | \
                 (abi.TB_SCALING if "scaling" in tools and rng.random() < 0.6 else 0)
@@ -758,15 +768,24 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                         tu["tb"][0, 0] = new_tb(x, y, 0, w, h, True, trh, trv, qp_y, False, ts=ts)
                     chroma_tbs(tu, x, y, w, h, True, qp_c, coded, False, 0)
                     tus.append(tu)
-                    pf = int(rng.integers(1, 4))
-                    mv = rng.integers(-40 * 16, 40 * 16 + 1, (2, 2))
-                    ridx = rng.integers(0, n_refs, 2)
-                    for ty in range(0, h, 16):
-                        for tx in range(0, w, 16):
-                            b = np.zeros(1, abi.PB_DTYPE)
-                            b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
-                            b["ref_idx"], b["mv"] = ridx, mv
-                            pblocks.append(b)
+                    kind = int(rng.choice(inter_kinds)) if inter_kinds else CU_REGULAR
+                    if kind == CU_GPM and max(w, h) // min(w, h) >= 8:
+                        kind = CU_REGULAR
+                    if kind != CU_REGULAR:
+                        c = np.zeros(1, CU_DTYPE)
+                        c["x0"], c["y0"], c["w"], c["h"] = x, y, w, h
+                        _emit_inter_cu(rng, c[0], kind, n_refs, lmcs, sb_mv, cu_blocks, prof)
+                        cu_recs.append(c)
+                    else:
+                        pf = int(rng.integers(1, 4))
+                        mv = rng.integers(-40 * 16, 40 * 16 + 1, (2, 2))
+                        ridx = rng.integers(0, n_refs, 2)
+                        for ty in range(0, h, 16):
+                            for tx in range(0, w, 16):
+                                b = np.zeros(1, abi.PB_DTYPE)
+                                b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
+                                b["ref_idx"], b["mv"] = ridx, mv
+                                pblocks.append(b)
                     done[uy:uy + uh, ux:ux + uw] = True
                     cus.append(cu)
                     continue
@@ -898,13 +917,21 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                                        keep_mv=True)
     else:
         pb = abi.order_blocks_by_width(np.concatenate(pblocks), iparams) if pblocks else np.zeros(0, abi.PB_DTYPE)
+    if lmcs:
+        pb["flags"] |= abi.PB_LMCS
+    n_regular = len(pb)
+    if cu_blocks:                               # one batch for the engine: regular sub-blocks + affine / GPM records
+        pb = abi.order_blocks_by_width(np.concatenate([pb] + cu_blocks), iparams)
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     ip = abi.IntraParams()
     ip.bit_depth, ip.ctb_log2_size, ip.chroma_vertical_collocated = 10, ctb_log2, int(rng.integers(0, 2))
     return dict(
         ref=dict(cus=np.concatenate(cus), tus=np.concatenate(tus), tbs=tbs, levels=levels, params=rparams),
-        inter=dict(blocks=pb, params=iparams, refs=refs),
+        inter=dict(blocks=pb, params=iparams, refs=refs, n_regular=n_regular,
+                   cus=np.concatenate(cu_recs) if cu_recs else np.zeros(0, CU_DTYPE),
+                   sb_mv=np.array(sb_mv, np.int32).reshape(-1, 2, 2),
+                   prof=np.concatenate(prof) if prof else np.zeros(0, abi.PROF_DTYPE)),
         residual=dict(tbs=np.ascontiguousarray(tbs[order]), levels=levels, params=rparams),
         intra=dict(blocks=np.concatenate(iblocks) if iblocks else np.zeros(0, abi.IB_DTYPE),
                    ctu_first=np.array(ctu_first, np.uint32), params=ip),

@@ -11,6 +11,8 @@
 #include "api_common.h"
 
 #include <stdlib.h>
+#include <pthread.h>
+#include <stdatomic.h>
 
 typedef struct ReconEnv {
     VVCFrameContext     fc;
@@ -196,9 +198,39 @@ VVCREF_EXPORT int vvcref_residual_batch(const VVCRefPlanes *pl, const int16_t *l
  * cpm) are filled, and the reference predicts every intra block from its reconstructed neighbours and adds every
  * residual, exactly as the decoder does after parsing.  Inter prediction must already be in the planes (stage INTER).
  */
+/* CTU rows dealt round-robin to `threads` workers; a CTU starts when the row above is two CTUs ahead, the wavefront of
+ * the reference's own scheduler (vvc_thread.c:156-184). */
+typedef struct ReconWorker {
+    ReconEnv *e;
+    int first_row, step, ctb_w, ctb_h;
+    atomic_int *row_done;
+    pthread_t th;
+} ReconWorker;
+
+static void *recon_worker(void *arg)
+{
+    ReconWorker *w = arg;
+    VVCLocalContext *lc = aligned_alloc(64, (sizeof(*lc) + 63) & ~(size_t)63);
+    memset(lc, 0, sizeof(*lc));
+    lc->fc = &w->e->fc;
+    lc->sc = &w->e->sc;
+    for (int ry = w->first_row; ry < w->ctb_h; ry += w->step)
+        for (int rx = 0; rx < w->ctb_w; rx++) {
+            if (ry > 0) {
+                const int need = rx + 2 < w->ctb_w ? rx + 2 : w->ctb_w;
+                while (atomic_load_explicit(&w->row_done[ry - 1], memory_order_acquire) < need)
+                    ;
+            }
+            ff_vvc_reconstruct(lc, ry * w->ctb_w + rx, rx, ry);
+            atomic_store_explicit(&w->row_done[ry], rx + 1, memory_order_release);
+        }
+    free(lc);
+    return NULL;
+}
+
 VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *cus, int n_cus, const VVCRefTU *tus,
                                        const VVCB200TransformBlock *tbs, const int16_t *levels,
-                                       const VVCB200ResidualParams *params, const VVCB200IntraParams *ip)
+                                       const VVCB200ResidualParams *params, const VVCB200IntraParams *ip, int threads)
 {
     ReconEnv *e = env_new(pl, params);
     const int ctb_log2 = ip->ctb_log2_size, ctb = 1 << ctb_log2;
@@ -340,9 +372,24 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
                 e->rsh.sh_dep_quant_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_DEP_QUANT);
                 e->rsh.sh_explicit_scaling_list_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_SCALING);
             }
-    for (int ry = 0; ry < ctb_h; ry++)
-        for (int rx = 0; rx < ctb_w; rx++)
-            ff_vvc_reconstruct(lc, ry * ctb_w + rx, rx, ry);
+    if (threads <= 1) {
+        for (int ry = 0; ry < ctb_h; ry++)
+            for (int rx = 0; rx < ctb_w; rx++)
+                ff_vvc_reconstruct(lc, ry * ctb_w + rx, rx, ry);
+    } else {
+        ReconWorker *ws = calloc(threads, sizeof(*ws));
+        atomic_int *row_done = calloc(ctb_h, sizeof(*row_done));
+        if (threads > ctb_h)
+            threads = ctb_h;
+        for (int t = 0; t < threads; t++) {
+            ws[t] = (ReconWorker){ .e = e, .first_row = t, .step = threads, .ctb_w = ctb_w, .ctb_h = ctb_h, .row_done = row_done };
+            pthread_create(&ws[t].th, NULL, recon_worker, &ws[t]);
+        }
+        for (int t = 0; t < threads; t++)
+            pthread_join(ws[t].th, NULL);
+        free(row_done);
+        free(ws);
+    }
 
     free(coeff_store); free(tu_store); free(lc); free(slice_idx); free(col_bd); free(row_bd); free(tabs);
     free(cu_store); free(ctus); free(e);

@@ -176,12 +176,13 @@ def inter_cus(dst, refs, cus, sb_mv, params, lmcs_fwd_lut=None):
         raise RuntimeError("vvcref_inter_cus failed")
 
 
-def recon_picture(planes, ref, intra_params):
-    """Reference ff_vvc_reconstruct() over the whole picture; `ref` is synth.recon_picture()["ref"]."""
+def recon_picture(planes, ref, intra_params, threads=1):
+    """Reference ff_vvc_reconstruct() over the whole picture; `ref` is synth.recon_picture()["ref"].
+    threads > 1: CTU rows on that many host threads in the reference's wavefront order."""
     pl = abi.host_planes(planes)
     cus, tus = np.ascontiguousarray(ref["cus"]), np.ascontiguousarray(ref["tus"])
     tbs = np.ascontiguousarray(ref["tbs"], abi.TB_DTYPE)
     lv = np.ascontiguousarray(ref["levels"], np.int16)
     lib().vvcref_recon_picture(C.byref(pl), C.c_void_p(cus.ctypes.data), len(cus), C.c_void_p(tus.ctypes.data),
                                C.c_void_p(tbs.ctypes.data), C.c_void_p(lv.ctypes.data), C.byref(ref["params"]),
-                               C.byref(intra_params))
+                               C.byref(intra_params), int(threads))

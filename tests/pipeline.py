@@ -3,6 +3,7 @@ import numpy as np
 
 from ffmpeg_b200 import lib
 from oracle import portapi, refapi
+from tests import util
 
 
 def oracle_picture(pic):
@@ -14,8 +15,7 @@ def oracle_picture(pic):
     edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
     ia = pic.get("intra")
     if refapi.available():
-        if len(it["blocks"]):
-            refapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+        util.oracle_inter(planes, it, fwd, True)
         if ia is not None:        # one partition of inter and intra CUs: the reference's own RECON stage does both
             refapi.recon_picture(planes, pic["ref"], ia["params"])
         else:
@@ -26,8 +26,7 @@ def oracle_picture(pic):
         refapi.sao_picture(planes, lf)
         refapi.alf_picture(planes, lf)
         return planes
-    if len(it["blocks"]):
-        portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], fwd)
+    util.oracle_inter(planes, it, fwd, False)
     if ia is not None:
         res = [np.zeros(p.shape, np.int16) for p in planes]
         portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
@@ -52,6 +51,8 @@ class EnginePicture:
         self.n_refs = len(it["refs"])
         self.refs = [[ctx.pinned_copy(np.ascontiguousarray(p)) for p in r] for r in it["refs"]]
         self.blocks = ctx.pinned_copy(it["blocks"])
+        prof = it.get("prof")
+        self.prof = ctx.pinned_copy(prof) if prof is not None and len(prof) else None
         self.levels = ctx.pinned_copy(rs["levels"])
         self.tbs = ctx.pinned_copy(rs["tbs"])
         edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
@@ -74,6 +75,7 @@ class EnginePicture:
 
     def h2d_bytes(self):
         intra = 0 if self.intra is None else self.intra[0].nbytes + self.intra[1].nbytes
+        intra += 0 if self.prof is None else self.prof.nbytes
         return intra + int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
                    self.ctb_offsets.nbytes + self.sao.nbytes + self.alf.nbytes + self.alf_params.nbytes)
 
@@ -87,7 +89,7 @@ class EnginePicture:
     def run(self, download=True):
         ctx, pic = self.ctx, self.pic
         ctx.begin(self.cur_slot)
-        ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0])
+        ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0], prof=self.prof)
         ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
         if self.intra is not None:
             ctx.intra(*self.intra)

@@ -4,6 +4,7 @@ import os
 
 import numpy as np
 
+from ffmpeg_b200 import abi
 from oracle import portapi, refapi
 
 GOLDEN = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
@@ -46,14 +47,34 @@ def from_device_planes(tensors):
     return [t.cpu().numpy().view(np.uint16) for t in tensors]
 
 
+def oracle_inter(planes, it, fwd=None, use_ref=None, threads=1):
+    """Stage INTER of a picture's `inter` dict on the oracle.  Reference: the block-level harness on the regular
+    sub-blocks, the CU-level harness (predict_inter on whole units) on the affine / GPM units; port: every record."""
+    if use_ref is None:
+        use_ref = refapi.available()
+    blocks = it["blocks"]
+    if not len(blocks):
+        return
+    if not use_ref:
+        prof = it.get("prof")
+        portapi.inter_batch(planes, it["refs"], blocks, it["params"], fwd, prof=prof if prof is not None and len(prof) else None)
+        return
+    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY
+    regular = blocks[(blocks["flags"] & special) == 0]
+    if len(regular):
+        refapi.inter_batch(planes, it["refs"], regular, it["params"], fwd)
+    cus = it.get("cus")
+    if cus is not None and len(cus):
+        refapi.inter_cus(planes, it["refs"], cus, it["sb_mv"], it["params"], fwd)
+
+
 def oracle_recon(planes, pic, order=None):
     """Stage INTER + RECON of a synth.recon_picture(): the compiled reference's ff_vvc_reconstruct when present,
     else the C port's inter -> residual planes -> intra chain.  `order`: intra records to use with the port
     (e.g. the wavefront order) instead of the decoding order."""
     it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
     use_ref = refapi.available() and order is None
-    if len(it["blocks"]):
-        (refapi if use_ref else portapi).inter_batch(planes, it["refs"], it["blocks"], it["params"])
+    oracle_inter(planes, it, None, use_ref)
     if use_ref:
         refapi.recon_picture(planes, pic["ref"], ia["params"])
         return planes
