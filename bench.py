@@ -183,7 +183,7 @@ def cpu_picture(pic, threads):
         for th in ths:
             th.join()
 
-    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY
+    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY | abi.PB_CIIP
     regular = it["blocks"][(it["blocks"]["flags"] & special) == 0] if use_ref else it["blocks"]
     blocks = [np.ascontiguousarray(regular[t::threads]) for t in range(threads)]
     cus = [np.ascontiguousarray(it["cus"][t::threads]) for t in range(threads)]
@@ -194,7 +194,7 @@ def cpu_picture(pic, threads):
     if use_ref:
         spread(lambda b: refapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
         spread(lambda c: refapi.inter_cus(planes, it["refs"], c, it["sb_mv"], it["params"]), cus)
-        refapi.recon_picture(planes, pic["ref"], ia["params"], threads=threads)
+        refapi.recon_picture(planes, pic["ref"], ia["params"], threads=threads, inter=it)
         refapi.deblock_picture(planes, db, threads=threads)
         refapi.sao_picture(planes, lf, threads=threads)
         refapi.alf_picture(planes, lf, threads=threads)

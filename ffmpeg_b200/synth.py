@@ -474,8 +474,8 @@ def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slic
     """full_picture() over ONE coding-unit partition: every CU is inter (prediction sub-blocks, TBs added in place) or
     intra (records for the wavefront, TBs routed through the residual planes), as in a P/B picture with intra CUs."""
     rp = recon_picture(seed, width, height, ctb_log2=ctb_log2, intra_fraction=intra_fraction, n_refs=n_refs,
-                       tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "mts", "ts", "lfnst", "joint", "dep_quant",
-                              "scaling"), mean_log2=mean_log2,
+                       tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "ciip", "mts", "ts", "lfnst", "joint",
+                              "dep_quant", "scaling"), mean_log2=mean_log2,
                        inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"),
                        inter_kinds=(CU_REGULAR,) * 7 + (CU_AFFINE,) * 2 + (CU_GPM,), lmcs=lmcs)
     db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
@@ -611,6 +611,7 @@ REF_CU_DTYPE = np.dtype([
     ("mip_flag", "<i4"), ("mip_transposed", "<i4"), ("mip_mode", "<i4"), ("mip_chroma_direct", "<i4"),
     ("isp_split_type", "<i4"), ("num_intra_subpartitions", "<i4"), ("bdpcm_flag", "<i4", (3,)), ("ciip_flag", "<i4"),
     ("coded_flag", "<i4"), ("first_tu", "<i4"), ("n_tu", "<i4"), ("mts_idx", "<i4"), ("lfnst_idx", "<i4"),
+    ("inter_flags", "<i4"), ("pred_flag", "<i4"), ("ref_idx", "<i4", (2,)), ("mv", "<i4", (2, 2)),
 ])                                  # mirrors VVCRefCU (oracle/ref/api_common.h)
 REF_TU_DTYPE = np.dtype([
     ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("coded_flag", "<i4", (3,)), ("joint", "<i4"),
@@ -663,7 +664,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
          residual: TB batch (TBs of intra CUs flagged TB_TO_RESIDUAL),
          intra: VVCB200IntraBlock records + per-CTU ranges (stage RECON wavefront).
-    tools: intra side "mrl", "mip", "cclm", "isp", "bdpcm"; residual side "mts", "ts", "lfnst", "joint", "dep_quant",
+    tools: intra side "mrl", "mip", "cclm", "isp", "bdpcm", "ciip" (inter units blended with a planar intra prediction);
+    residual side "mts", "ts", "lfnst", "joint", "dep_quant",
     "scaling" ("pdpc" is always on, it is not signalled).  inter_tools: block-level tool mix of inter_picture() on the
     regular inter CUs; inter_kinds: CU kinds to draw from (CU_REGULAR, CU_AFFINE, CU_GPM) — affine / GPM units come with
     their CU-level description (`inter.cus`, `inter.sb_mv`) for the reference harness and PROF tables (`inter.prof`).
@@ -677,6 +679,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     cus, tus, tbs, lv_chunks = [], [], [], []
     pblocks, iblocks, ctu_first = [], [], [0]
     cu_blocks, cu_recs, sb_mv, prof = [], [], [], []     # affine / GPM coding units
+    is_intra = np.zeros((u4h, u4w), bool)
+    ciip_flags = (abi.PB_WP if rng.random() < 0.5 else 0) | (abi.PB_LMCS if lmcs else 0) if "ciip" in tools else 0
     lv_off = 0
     pic_flags = (abi.TB_DEP_QUANT if "dep_quant" in tools and rng.random() < 0.5 else 0) | \
                 (abi.TB_SCALING if "scaling" in tools and rng.random() < 0.6 else 0)
@@ -755,6 +759,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 qp_y, qp_c = int(rng.integers(14, 60)), int(rng.integers(14, 60))
                 ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
                 if not intra:
+                    ciip = "ciip" in tools and rng.random() < 0.3
                     tu = np.zeros(1, REF_TU_DTYPE)
                     tu["x0"], tu["y0"], tu["w"], tu["h"] = x, y, w, h
                     tu["coded_flag"] = coded
@@ -765,13 +770,46 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                         trh, trv = [(1, 1), (2, 1), (1, 2), (2, 2)][int(rng.integers(0, 4))]
                     cu["mts_idx"] = _MTS_OF[(trh, trv)]
                     if coded[0]:
-                        tu["tb"][0, 0] = new_tb(x, y, 0, w, h, True, trh, trv, qp_y, False, ts=ts)
-                    chroma_tbs(tu, x, y, w, h, True, qp_c, coded, False, 0)
+                        tu["tb"][0, 0] = new_tb(x, y, 0, w, h, True, trh, trv, qp_y, ciip, ts=ts)
+                    res_c = chroma_tbs(tu, x, y, w, h, True, qp_c, coded, ciip, 0)
                     tus.append(tu)
                     kind = int(rng.choice(inter_kinds)) if inter_kinds else CU_REGULAR
                     if kind == CU_GPM and max(w, h) // min(w, h) >= 8:
                         kind = CU_REGULAR
-                    if kind != CU_REGULAR:
+                    if ciip:
+                        # merge motion, default weighting unless the slice has explicit weights; the inter prediction is
+                        # made in stage INTER (records flagged PB_CIIP), the planar prediction and the blend in stage RECON
+                        pf = int(rng.integers(1, 4))
+                        mv = rng.integers(-40 * 16, 40 * 16 + 1, (2, 2))
+                        ridx = rng.integers(0, n_refs, 2)
+                        fl = ciip_flags | (abi.PB_HPEL_IF if rng.random() < 0.2 else 0)
+                        cu["ciip_flag"], cu["inter_flags"], cu["pred_flag"], cu["ref_idx"], cu["mv"] = 1, fl, pf, ridx, mv
+                        for ty in range(0, h, 16):
+                            for tx in range(0, w, 16):
+                                b = np.zeros(1, abi.PB_DTYPE)
+                                b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
+                                b["ref_idx"], b["mv"], b["flags"] = ridx, mv, fl | abi.PB_CIIP
+                                cu_blocks.append(b)
+                        x0b, y0b = x & (ctb - 1), y & (ctb - 1)
+                        cand_up, cand_left = ctb_up or y0b > 0, ctb_left or x0b > 0
+                        up_left = (cand_left and cand_up) if (x0b or y0b) else (ctb_left and ctb_up)
+                        end_x4 = min(width, (rx + 1) * ctb) >> 2
+                        end_y4 = min(height, (ry + 1) * ctb) >> 2
+                        top4 = ((u4w - ux) if ctb_up else 0) if y0b == 0 else _avail(done, ux, uy - 1, True, end_x4)
+                        left4 = ((end_y4 - uy) if ctb_left else 0) if x0b == 0 else _avail(done, ux - 1, uy, False, end_y4)
+                        wt = 1 + int(cand_up and is_intra[(y - 1) >> 2, (x - 1 + w) >> 2]) + \
+                            int(cand_left and is_intra[(y - 1 + h) >> 2, (x - 1) >> 2])      # vvc_inter.c:523-543
+                        for c in (0, 1, 2):
+                            hs = 1 if c else 0
+                            ib = np.zeros(1, abi.IB_DTYPE)
+                            ib["x0"], ib["y0"], ib["w"], ib["h"], ib["c_idx"] = x >> hs, y >> hs, w >> hs, h >> hs, c
+                            has_res = bool(coded[0]) if c == 0 else bool(res_c & (1 << (c - 1)))
+                            ib["flags"] = abi.IB_CIIP | (abi.IB_RESIDUAL if has_res else 0)
+                            ib["ciip_weight"], ib["up_left"] = wt, up_left
+                            ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
+                            ib["cb_w"], ib["cb_h"] = w, h
+                            iblocks.append(ib)
+                    elif kind != CU_REGULAR:
                         c = np.zeros(1, CU_DTYPE)
                         c["x0"], c["y0"], c["w"], c["h"] = x, y, w, h
                         _emit_inter_cu(rng, c[0], kind, n_refs, lmcs, sb_mv, cu_blocks, prof)
@@ -894,6 +932,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     ib["cb_w"], ib["cb_h"] = w, h
                     iblocks.append(ib)
                 done[uy:uy + uh, ux:ux + uw] = True
+                is_intra[uy:uy + uh, ux:ux + uw] = True
                 cus.append(cu)
             ctu_first.append(len(iblocks))
     tbs = np.concatenate(tbs) if tbs else np.zeros(0, abi.TB_DTYPE)

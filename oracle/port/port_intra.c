@@ -477,6 +477,18 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
             continue;
         }
         uint16_t *src = (uint16_t *)(pic->plane[c] + (size_t)b->y0 * pic->stride[c]) + b->x0;
+        if (b->flags & VVCB200_IB_CIIP) {
+            /* the inter prediction is in the picture; blend it with the intra prediction (put_ciip, vvc_inter_template.c:60-76) */
+            static uint16_t inter[64 * 64];
+            const int stride = pic->stride[c] / 2, wt = b->ciip_weight;
+            for (int j = 0; j < b->h; j++)
+                for (int i2 = 0; i2 < b->w; i2++)
+                    inter[j * b->w + i2] = src[i2 + (ptrdiff_t)stride * j];
+            intra_pred_block(src, stride, b, ip->bit_depth);
+            for (int j = 0; j < b->h; j++)
+                for (int i2 = 0; i2 < b->w; i2++)
+                    src[i2 + (ptrdiff_t)stride * j] = (src[i2 + (ptrdiff_t)stride * j] * wt + inter[j * b->w + i2] * (4 - wt) + 2) >> 2;
+        } else
         intra_pred_block(src, pic->stride[c] / 2, b, ip->bit_depth);
         if (b->flags & VVCB200_IB_RESIDUAL)
             add_residual_plane(pic, residual, c, b->x0, b->y0, b->w, b->h, ip->bit_depth);

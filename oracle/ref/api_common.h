@@ -42,6 +42,9 @@ typedef struct VVCRefCU {
     int32_t ciip_flag, coded_flag;
     int32_t first_tu, n_tu;
     int32_t mts_idx, lfnst_idx;
+    /* CIIP units (ciip_flag): the merge motion the reference predicts from inside RECON (vvc_intra.c:515-516) */
+    int32_t inter_flags;                /* VVCB200_PB_WP / HPEL_IF / LMCS */
+    int32_t pred_flag, ref_idx[2], mv[2][2];
 } VVCRefCU;
 
 typedef struct VVCRefTU {

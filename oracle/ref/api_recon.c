@@ -28,6 +28,11 @@ typedef struct ReconEnv {
     VVCScalingList      sl;
     CodingUnit          cu;
     TransformUnit       tu;
+    /* CIIP: ff_vvc_predict_ciip() runs the inter path from inside RECON */
+    RefPicList          rpl[2];
+    VVCFrame            cur;
+    VVCFrame            refs[16];
+    AVFrame             ref_frames[16];
 } ReconEnv;
 
 static ReconEnv *env_new(const VVCRefPlanes *pl, const VVCB200ResidualParams *p)
@@ -230,7 +235,9 @@ static void *recon_worker(void *arg)
 
 VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *cus, int n_cus, const VVCRefTU *tus,
                                        const VVCB200TransformBlock *tbs, const int16_t *levels,
-                                       const VVCB200ResidualParams *params, const VVCB200IntraParams *ip, int threads)
+                                       const VVCB200ResidualParams *params, const VVCB200IntraParams *ip, int threads,
+                                       const VVCRefPlanes *refs, int n_refs, const VVCB200InterParams *inter,
+                                       const uint16_t *lmcs_fwd_lut)
 {
     ReconEnv *e = env_new(pl, params);
     const int ctb_log2 = ip->ctb_log2_size, ctb = 1 << ctb_log2;
@@ -279,6 +286,36 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
     e->fc.tab.imm    = tabs + (size_t)mcw * mch * 2;
     e->fc.tab.ipm    = tabs + (size_t)mcw * mch * 3;
     e->fc.tab.cpm[0] = tabs + (size_t)mcw * mch * 4;
+    /* motion field: PF_INTRA on intra units (read by ciip_derive_intra_weight), the merge motion on CIIP units */
+    e->fc.tab.mvf = calloc((size_t)mcw * mch, sizeof(MvField));
+    e->pps.min_pu_height = mch;
+    if (refs && inter && n_refs <= 16) {
+        PredWeightTable *w = &e->sc.sh.pwt;
+        e->fc.ref = &e->cur;
+        e->sc.rpl = e->rpl;
+        e->rsh.sh_slice_type = VVC_SLICE_TYPE_B;
+        ff_videodsp_init(&e->fc.vdsp, params->bit_depth);
+        for (int i = 0; i < n_refs; i++) {
+            for (int c = 0; c < 3; c++) {
+                e->ref_frames[i].data[c]     = refs[i].plane[c];
+                e->ref_frames[i].linesize[c] = refs[i].stride[c];
+            }
+            e->refs[i].frame = &e->ref_frames[i];
+        }
+        for (int l = 0; l < 2; l++)
+            for (int i = 0; i < 15; i++)
+                e->rpl[l].ref[i] = inter->ref_slot[l][i] < n_refs ? &e->refs[inter->ref_slot[l][i]] : NULL;
+        w->log2_denom[0] = inter->log2_denom[0];
+        w->log2_denom[1] = inter->log2_denom[1];
+        for (int l = 0; l < 2; l++)
+            for (int c = 0; c < 3; c++)
+                for (int i = 0; i < MAX_WEIGHTS; i++) {
+                    w->weight[l][c][i] = inter->weight[l][c][i];
+                    w->offset[l][c][i] = inter->offset[l][c][i];
+                }
+        if (lmcs_fwd_lut)
+            memcpy(e->fc.ps.lmcs.fwd_lut, lmcs_fwd_lut, sizeof(uint16_t) << params->bit_depth);
+    }
 
     {
         int *cp = coeff_store;
@@ -311,9 +348,31 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
             cu->apply_lfnst_flag[0] = d->lfnst_idx > 0;      /* single tree: LFNST on luma only */
             for (int c = 0; c < 3; c++)
                 cu->bdpcm_flag[c] = d->bdpcm_flag[c];
+            if (d->ciip_flag) {
+                if (!e->fc.ref)
+                    return -1;                                  /* CIIP units need the reference pictures */
+                cu->intra_pred_mode_y = cu->intra_pred_mode_c = INTRA_PLANAR;
+                cu->pu.mi.num_sb_x = cu->pu.mi.num_sb_y = 1;
+                cu->pu.mi.hpel_if_idx = !!(d->inter_flags & VVCB200_PB_HPEL_IF);
+                cu->pu.mi.pred_flag = d->pred_flag;
+                /* slice-level switches, the same for every CIIP unit of the picture */
+                e->rpps.pps_weighted_pred_flag = e->rpps.pps_weighted_bipred_flag = !!(d->inter_flags & VVCB200_PB_WP);
+                e->rsh.sh_lmcs_used_flag = !!(d->inter_flags & VVCB200_PB_LMCS);
+            }
             for (int y = d->y0 >> 2; y < (d->y0 + d->h) >> 2; y++)
                 for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++) {
                     const size_t o = (size_t)y * mcw + x;
+                    MvField *mvf = &e->fc.tab.mvf[o];
+                    mvf->pred_flag = d->pred_mode ? PF_INTRA : d->ciip_flag ? d->pred_flag : PF_L0;
+                    mvf->ciip_flag = d->ciip_flag;
+                    if (d->ciip_flag) {
+                        for (int l = 0; l < 2; l++) {
+                            mvf->mv[l].x = d->mv[l][0];
+                            mvf->mv[l].y = d->mv[l][1];
+                            mvf->ref_idx[l] = d->ref_idx[l];
+                        }
+                        mvf->hpel_if_idx = cu->pu.mi.hpel_if_idx;
+                    }
                     e->fc.tab.imf[o]    = d->mip_flag;
                     e->fc.tab.imtf[o]   = d->mip_transposed;
                     e->fc.tab.imm[o]    = d->mip_mode;
@@ -391,6 +450,7 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
         free(ws);
     }
 
+    free(e->fc.tab.mvf);
     free(coeff_store); free(tu_store); free(lc); free(slice_idx); free(col_bd); free(row_bd); free(tabs);
     free(cu_store); free(ctus); free(e);
     (void)n_tb_total;

@@ -176,13 +176,22 @@ def inter_cus(dst, refs, cus, sb_mv, params, lmcs_fwd_lut=None):
         raise RuntimeError("vvcref_inter_cus failed")
 
 
-def recon_picture(planes, ref, intra_params, threads=1):
+def recon_picture(planes, ref, intra_params, threads=1, inter=None, lmcs_fwd_lut=None):
     """Reference ff_vvc_reconstruct() over the whole picture; `ref` is synth.recon_picture()["ref"].
-    threads > 1: CTU rows on that many host threads in the reference's wavefront order."""
+    threads > 1: CTU rows on that many host threads in the reference's wavefront order.
+    inter: the picture's `inter` dict (refs, params), needed when the picture has CIIP units."""
     pl = abi.host_planes(planes)
     cus, tus = np.ascontiguousarray(ref["cus"]), np.ascontiguousarray(ref["tus"])
     tbs = np.ascontiguousarray(ref["tbs"], abi.TB_DTYPE)
     lv = np.ascontiguousarray(ref["levels"], np.int16)
-    lib().vvcref_recon_picture(C.byref(pl), C.c_void_p(cus.ctypes.data), len(cus), C.c_void_p(tus.ctypes.data),
+    ra, n_refs = None, 0
+    if inter is not None:
+        ra, n_refs = abi.planes_array([abi.host_planes(r) for r in inter["refs"]]), len(inter["refs"])
+    lut = None if lmcs_fwd_lut is None else np.ascontiguousarray(lmcs_fwd_lut, np.uint16)
+    r = lib().vvcref_recon_picture(C.byref(pl), C.c_void_p(cus.ctypes.data), len(cus), C.c_void_p(tus.ctypes.data),
                                C.c_void_p(tbs.ctypes.data), C.c_void_p(lv.ctypes.data), C.byref(ref["params"]),
-                               C.byref(intra_params), int(threads))
+                               C.byref(intra_params), int(threads), ra, n_refs,
+                               C.byref(inter["params"]) if inter is not None else None,
+                               C.c_void_p(lut.ctypes.data) if lut is not None else None)
+    if r != 0:
+        raise RuntimeError("vvcref_recon_picture failed")

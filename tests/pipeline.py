@@ -17,7 +17,7 @@ def oracle_picture(pic):
     if refapi.available():
         util.oracle_inter(planes, it, fwd, True)
         if ia is not None:        # one partition of inter and intra CUs: the reference's own RECON stage does both
-            refapi.recon_picture(planes, pic["ref"], ia["params"])
+            refapi.recon_picture(planes, pic["ref"], ia["params"], inter=it, lmcs_fwd_lut=fwd)
         else:
             refapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], rs["intra_mode"])
         if inv is not None:

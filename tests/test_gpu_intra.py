@@ -46,7 +46,7 @@ def run_gpu(pic, schedule=True, repeat=1):
     return out
 
 
-ALL_TOOLS = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp")
+ALL_TOOLS = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp", "ciip")
 CASES = [
     (1, 208, 120, 6, ("pdpc",), 0.6),
     (2, 208, 120, 5, ("pdpc", "mrl"), 0.6),

@@ -10,7 +10,7 @@ from ffmpeg_b200 import abi, lib, synth
 from oracle import portapi, refapi
 from tests import util
 
-ALL_TOOLS = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp")
+ALL_TOOLS = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp", "ciip")
 CASES = [
     (1, 208, 120, 6, ("pdpc",), 0.6),
     (2, 208, 120, 5, ("pdpc", "mrl"), 0.6),
@@ -29,8 +29,7 @@ CASES = [
 def _port(pic, order=None):
     planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
     it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
-    if len(it["blocks"]):
-        portapi.inter_batch(planes, it["refs"], it["blocks"], it["params"])
+    util.oracle_inter(planes, it, None, False)
     res = [np.zeros(p.shape, np.int16) for p in planes]
     portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
     portapi.intra_picture(planes, res, ia["blocks"] if order is None else order, ia["params"])
@@ -42,9 +41,8 @@ def _port(pic, order=None):
 def test_port_matches_reference_reconstruct(seed, w, h, ctb, tools, frac):
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
     want = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
-    if len(pic["inter"]["blocks"]):
-        refapi.inter_batch(want, pic["inter"]["refs"], pic["inter"]["blocks"], pic["inter"]["params"])
-    refapi.recon_picture(want, pic["ref"], pic["intra"]["params"])
+    util.oracle_inter(want, pic["inter"], None, True)
+    refapi.recon_picture(want, pic["ref"], pic["intra"]["params"], inter=pic["inter"])
     got = _port(pic)
     for c in range(3):
         assert np.array_equal(got[c], want[c]), "plane %d differs" % c

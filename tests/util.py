@@ -59,7 +59,7 @@ def oracle_inter(planes, it, fwd=None, use_ref=None, threads=1):
         prof = it.get("prof")
         portapi.inter_batch(planes, it["refs"], blocks, it["params"], fwd, prof=prof if prof is not None and len(prof) else None)
         return
-    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY
+    special = abi.PB_GPM | abi.PB_AFFINE | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY | abi.PB_CIIP   # CIIP: predicted in RECON
     regular = blocks[(blocks["flags"] & special) == 0]
     if len(regular):
         refapi.inter_batch(planes, it["refs"], regular, it["params"], fwd)
@@ -76,7 +76,7 @@ def oracle_recon(planes, pic, order=None):
     use_ref = refapi.available() and order is None
     oracle_inter(planes, it, None, use_ref)
     if use_ref:
-        refapi.recon_picture(planes, pic["ref"], ia["params"])
+        refapi.recon_picture(planes, pic["ref"], ia["params"], inter=it)
         return planes
     res = [np.zeros(p.shape, np.int16) for p in planes]
     portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)

@@ -89,12 +89,11 @@ def golden_loopfilter():
 def golden_intra():
     """One small picture through the reference's ff_vvc_reconstruct (inter CUs predicted first), planes kept whole."""
     seed, w, h, ctb, frac = 20261107, 136, 72, 5, 0.7
-    tools = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp")
+    tools = ("pdpc", "mrl", "mip", "cclm", "mts", "ts", "dep_quant", "scaling", "joint", "lfnst", "bdpcm", "isp", "ciip")
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
     planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
-    if len(pic["inter"]["blocks"]):
-        refapi.inter_batch(planes, pic["inter"]["refs"], pic["inter"]["blocks"], pic["inter"]["params"])
-    refapi.recon_picture(planes, pic["ref"], pic["intra"]["params"])
+    util.oracle_inter(planes, pic["inter"], None, True)
+    refapi.recon_picture(planes, pic["ref"], pic["intra"]["params"], inter=pic["inter"])
     return dict(seed=seed, width=w, height=h, ctb_log2=ctb, tools=np.array(tools), intra_fraction=frac,
                 blocks_md5=np.array(util.md5(pic["intra"]["blocks"])),
                 plane0=planes[0], plane1=planes[1], plane2=planes[2])
