@@ -185,17 +185,19 @@ ALF_PARAMS_DTYPE = np.dtype([
 
 
 # ---- intra --------------------------------------------------------------------------------------------------------
-IB_MIP, IB_MIP_TRANSPOSED, IB_ISP, IB_BDPCM, IB_RESIDUAL, IB_CIIP = 1, 2, 4, 8, 16, 32
+IB_MIP, IB_MIP_TRANSPOSED, IB_ISP, IB_BDPCM, IB_RESIDUAL, IB_CIIP, IB_ADD_ONLY, IB_LMCS_SCALE = 1, 2, 4, 8, 16, 32, 64, 128
 TB_TO_RESIDUAL = 512
 
 IB_DTYPE = np.dtype([
     ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("c_idx", "u1"), ("mode", "i1"), ("ref_idx", "u1"),
     ("flags", "u1"), ("mip_mode", "u1"), ("up_left", "u1"), ("avail_top", "<u2"), ("avail_left", "<u2"),
-    ("cb_w", "u1"), ("cb_h", "u1"), ("ciip_weight", "u1"), ("res_planes", "u1"), ("reserved2", "<u4", (2,)),
+    ("cb_w", "u1"), ("cb_h", "u1"), ("ciip_weight", "u1"), ("res_planes", "u1"),
+    ("vpdu_x", "u1"), ("vpdu_y", "u1"), ("vpdu_avail", "u1"), ("reserved3", "u1"), ("reserved2", "<u4"),
 ], align=False)
 assert IB_DTYPE.itemsize == 28
 
 
 class IntraParams(C.Structure):
     _fields_ = [("bit_depth", C.c_int32), ("ctb_log2_size", C.c_int32), ("chroma_vertical_collocated", C.c_int32),
-                ("reserved", C.c_int32)]
+                ("lmcs_chroma_scale", C.c_int32), ("lmcs_pivot", C.c_uint16 * 17), ("lmcs_chroma_scale_coeff", C.c_uint16 * 16),
+                ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("pad", C.c_uint8 * 4)]

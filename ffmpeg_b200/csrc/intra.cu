@@ -42,6 +42,8 @@ struct IntraArgs {
     uint8_t *marks[3];            // pending marks per plane
     int mpitch[3];
     int *ticket;
+    uint16_t lmcs_pivot[17], lmcs_coeff[16];
+    int lmcs_min_bin, lmcs_max_bin;
 };
 
 __device__ __forceinline__ int ilog2(int v) { return 31 - __clz(v); }
@@ -150,18 +152,65 @@ __device__ __forceinline__ int warp_sum(int v)
     return v;
 }
 
+// ---- luma-dependent chroma residual scaling (vvc_intra_template.c:376-449) ------------------------------------------
+// The factor of a VPDU comes from the mean of the reconstructed luma samples left of and above it.
+__device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, int lane)
+{
+    const int size = min(1 << a.ctb_log2, 64), ls = ilog2(size);
+    const int x = b.vpdu_x << ls, y = b.vpdu_y << ls;
+    const bool al = b.vpdu_avail & 1, at = b.vpdu_avail & 2;
+    const int rows = min(size, a.pic.h[0] - y), cols = min(size, a.pic.w[0] - x);
+    for (;;) {
+        bool p = false;
+        if (al) p |= col_pending(a, 0, (x >> 2) - 1, y >> 2, unit_count(y, rows, 2), lane);
+        if (at) p |= row_pending(a, 0, (y >> 2) - 1, x >> 2, unit_count(x, cols, 2), lane);
+        if (!__any_sync(kFull, p))
+            break;
+        __nanosleep(64);
+    }
+    __threadfence();
+    const uint16_t *luma = a.pic.p[0] + (size_t)y * a.pic.stride[0] + x;
+    int sum = 0, cnt = 0;
+    if (al) {                                                             // past the picture edge the last sample repeats
+        for (int i = lane; i < size; i += 32)
+            sum += __ldcg(luma - 1 + (ptrdiff_t)a.pic.stride[0] * min(i, rows - 1));
+        cnt = size;
+    }
+    if (at) {
+        for (int i = lane; i < size; i += 32)
+            sum += __ldcg(luma - a.pic.stride[0] + min(i, cols - 1));
+        cnt += size;
+    }
+    sum = warp_sum(sum);
+    const int mean = cnt ? (sum + (cnt >> 1)) >> ilog2(cnt) : 1 << (a.bd - 1);
+    int i = a.lmcs_min_bin;
+    while (i <= a.lmcs_max_bin && mean >= a.lmcs_pivot[i + 1])
+        i++;
+    return a.lmcs_coeff[min(i, 15)];
+}
+
+__device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
+{
+    const int c = clip_intp2(r, bd);
+    return c > 0 ? (c * scale + (1 << 10)) >> 11 : -((-c * scale + (1 << 10)) >> 11);
+}
+
 // ---- one angular / planar / DC / MIP block --------------------------------------------------------------------------
 struct Store {                    // what happens to a predicted sample on its way to the picture
     uint16_t *dst;
     const int16_t *res;
-    int dstride, rstride, bd, ciip_w;
+    int dstride, rstride, bd, ciip_w, lscale;
     __device__ __forceinline__ void put(int x, int y, int pred) const
     {
         uint16_t *d = dst + (size_t)y * dstride + x;
         if (ciip_w)                                                       // put_ciip, vvc_inter_template.c:60-76
             pred = (pred * ciip_w + (int)__ldcg(d) * (4 - ciip_w) + 2) >> 2;
-        if (res)                                                          // add_residual, vvc_itx_1d / vvcdsp.h:154
-            pred = clip_pixel(pred + res[(size_t)y * rstride + x], bd);
+        if (res) {                                                        // add_residual, vvc_itx_1d / vvcdsp.h:154
+            int r = res[(size_t)y * rstride + x];
+            if (lscale)
+                r = scale_chroma_residual(r, lscale, bd);
+            pred = clip_pixel(pred + r, bd);
+        }
         *d = (uint16_t)pred;
     }
 };
@@ -179,6 +228,22 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
     const int ref_line = ref_idx == 3 ? -4 : -1 - ref_idx;
     const int stride = a.pic.stride[c];
     uint16_t *src = a.pic.p[c] + (size_t)b.y0 * stride + b.x0;
+    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, lane) : 0;
+
+    if (b.flags & VVCB200_IB_ADD_ONLY) {                                  // the prediction is there already
+        if (b.flags & VVCB200_IB_RESIDUAL) {
+            const int16_t *res = a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0;
+            for (int idx = lane; idx < w * h; idx += 32) {
+                const int x = idx & (w - 1), y = idx >> lw;
+                int r = res[(size_t)y * a.res_stride[c] + x];
+                if (lscale)
+                    r = scale_chroma_residual(r, lscale, bd);
+                uint16_t *d = src + (size_t)y * stride + x;
+                *d = (uint16_t)clip_pixel((int)__ldcg(d) + r, bd);
+            }
+        }
+        return;
+    }
 
     // how much of each edge the mode reads (vvc_intra_template.c:470-520)
     int left_size, ul, ut, refw = 0, refh = 0;
@@ -300,6 +365,7 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
     st.ciip_w = (b.flags & VVCB200_IB_CIIP) ? b.ciip_weight : 0;
     st.res = (b.flags & VVCB200_IB_RESIDUAL) ? a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0 : nullptr;
     st.rstride = a.res_stride[c];
+    st.lscale = lscale;
     const int n = w * h;
 
     if (is_mip) {                                                         // vvc_intra_template.c:707-836
@@ -485,6 +551,7 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
         __threadfence();
     }
 
+    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, lane) : 0;
     const int16_t *res[2] = { nullptr, nullptr };
     if (b.flags & VVCB200_IB_RESIDUAL)
         for (int c = 0; c < 2; c++)
@@ -492,8 +559,12 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
                 res[c] = a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x;
     const int n = w * h, lw = ilog2(w);
     auto emit = [&](int c, int i, int j, int v) {
-        if (res[c])
-            v = clip_pixel(v + res[c][(size_t)j * a.res_stride[c + 1] + i], bd);
+        if (res[c]) {
+            int r = res[c][(size_t)j * a.res_stride[c + 1] + i];
+            if (lscale)
+                r = scale_chroma_residual(r, lscale, bd);
+            v = clip_pixel(v + r, bd);
+        }
         dst[c][(size_t)j * cs[c] + i] = (uint16_t)v;
     };
     if (!avail_t && !avail_l) {
@@ -743,6 +814,12 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     a.bd = params->bit_depth;
     a.ctb_log2 = params->ctb_log2_size;
     a.collocated = params->chroma_vertical_collocated;
+    for (int i = 0; i < 17; i++)
+        a.lmcs_pivot[i] = params->lmcs_pivot[i];
+    for (int i = 0; i < 16; i++)
+        a.lmcs_coeff[i] = params->lmcs_chroma_scale_coeff[i];
+    a.lmcs_min_bin = params->lmcs_min_bin_idx;
+    a.lmcs_max_bin = params->lmcs_max_bin_idx < 15 ? params->lmcs_max_bin_idx : 15;
     const ScratchLayout l = scratch_layout(pic->width[0], pic->height[0]);
     a.ticket = (int *)d_scratch;
     for (int c = 0; c < 3; c++) {

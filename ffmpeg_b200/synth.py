@@ -443,6 +443,18 @@ def lmcs_luts(seed, bd=10):
     return fwd, inv
 
 
+def lmcs_model(seed, fwd, bd=10):
+    """Pivots of the 16 bins in the mapped domain (taken from the forward LUT) and per-bin chroma residual scale factors
+    (11 fractional bits), shaped like VVCLMCS (reference vvc_ps.h:192-202)."""
+    rng = np.random.default_rng(seed)
+    org_cw = (1 << bd) // 16
+    pivot = np.array([int(fwd[min(i * org_cw, (1 << bd) - 1)]) for i in range(16)] + [(1 << bd) - 1], np.uint16)
+    coeff = rng.integers(1 << 10, 1 << 12, 16).astype(np.uint16)
+    lo = int(rng.integers(0, 3))
+    hi = int(rng.integers(13, 16))
+    return dict(pivot=pivot, coeff=coeff, min_bin=lo, max_bin=hi)
+
+
 # ---- a whole picture --------------------------------------------------------------------------------------------
 def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, lmcs=False, n_slices=1, lfase=1,
                  residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3, intra_fraction=0.0):
@@ -473,7 +485,9 @@ def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, 
 def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2, intra_fraction):
     """full_picture() over ONE coding-unit partition: every CU is inter (prediction sub-blocks, TBs added in place) or
     intra (records for the wavefront, TBs routed through the residual planes), as in a P/B picture with intra CUs."""
+    luts = lmcs_luts(seed + 4) if lmcs else None
     rp = recon_picture(seed, width, height, ctb_log2=ctb_log2, intra_fraction=intra_fraction, n_refs=n_refs,
+                       lmcs_chroma=lmcs_model(seed + 5, luts[0]) if lmcs else None,
                        tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "ciip", "mts", "ts", "lfnst", "joint",
                               "dep_quant", "scaling"), mean_log2=mean_log2,
                        inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"),
@@ -484,7 +498,7 @@ def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slic
                dims=rp["dims"], ctb_log2=ctb_log2, seed=seed, width=width, height=height, lmcs=None)
     out["residual"]["intra_mode"] = np.zeros(len(rp["residual"]["tbs"]), np.int32)
     if lmcs:
-        out["lmcs"] = lmcs_luts(seed + 4)
+        out["lmcs"] = luts
     return out
 
 
@@ -658,7 +672,7 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
@@ -669,6 +683,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     "scaling" ("pdpc" is always on, it is not signalled).  inter_tools: block-level tool mix of inter_picture() on the
     regular inter CUs; inter_kinds: CU kinds to draw from (CU_REGULAR, CU_AFFINE, CU_GPM) — affine / GPM units come with
     their CU-level description (`inter.cus`, `inter.sb_mv`) for the reference harness and PROF tables (`inter.prof`).
+    lmcs_chroma: an lmcs_model() -> luma-dependent chroma residual scaling: every chroma TB goes through the residual
+    planes and every chroma block with a residual gets a record (intra, or add-only for inter units).
     Neighbour availability follows the reference's rules (vvc_intra.c:593-648) on a 4x4-unit reconstruction mask."""
     rng = np.random.default_rng(seed)
     tools = set(tools)
@@ -724,6 +740,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
 
     def chroma_tbs(tu, x, y, w, h, inter, qp_c, coded, to_res, bdpcm_c):
         """Chroma TBs of a TU (luma geometry in): separate Cb / Cr, or one joint TB standing for both."""
+        to_res = to_res or lmcs_chroma is not None
         jm = 0
         if "joint" in tools and (coded[1] or coded[2]) and not bdpcm_c and rng.random() < 0.3:
             jm = int(rng.integers(1, 4))     # 1: Cb carries, both coded; 2: Cb carries, Cr halved; 3: Cr carries, Cb halved
@@ -741,6 +758,25 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 tu["tb"][0, c] = new_tb(x >> 1, y >> 1, c, w >> 1, h >> 1, inter, 0, 0, qp_c, to_res, ts=ts, bdpcm=bdpcm_c)
                 got |= 1 << (c - 1)
         return got
+
+    vsize = min(ctb, 64)
+
+    def set_vpdu(ib, x, y, ctb_left, ctb_up):
+        vx, vy = x & ~(vsize - 1), y & ~(vsize - 1)
+        ib["vpdu_x"], ib["vpdu_y"] = vx // vsize, vy // vsize
+        ib["vpdu_avail"] = int((vx & (ctb - 1)) > 0 or ctb_left) | (int((vy & (ctb - 1)) > 0 or ctb_up) << 1)
+        ib["flags"] |= abi.IB_LMCS_SCALE
+
+    def add_only_records(x, y, w, h, res_c, ctb_left, ctb_up):
+        """Chroma blocks of an inter unit whose residual waits for the luma-dependent scale."""
+        for c in (1, 2):
+            if res_c & (1 << (c - 1)):
+                ib = np.zeros(1, abi.IB_DTYPE)
+                ib["x0"], ib["y0"], ib["w"], ib["h"], ib["c_idx"] = x >> 1, y >> 1, w >> 1, h >> 1, c
+                ib["flags"] = abi.IB_ADD_ONLY | abi.IB_RESIDUAL
+                ib["cb_w"], ib["cb_h"] = w, h
+                set_vpdu(ib, x, y, ctb_left, ctb_up)
+                iblocks.append(ib)
 
     for ry in range(ch):
         for rx in range(cw):
@@ -808,6 +844,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                             ib["ciip_weight"], ib["up_left"] = wt, up_left
                             ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
                             ib["cb_w"], ib["cb_h"] = w, h
+                            if c and has_res and lmcs_chroma is not None:
+                                set_vpdu(ib, x, y, ctb_left, ctb_up)
                             iblocks.append(ib)
                     elif kind != CU_REGULAR:
                         c = np.zeros(1, CU_DTYPE)
@@ -824,6 +862,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                                 b["x0"], b["y0"], b["w"], b["h"], b["pred_flag"] = x + tx, y + ty, min(16, w), min(16, h), pf
                                 b["ref_idx"], b["mv"] = ridx, mv
                                 pblocks.append(b)
+                    if lmcs_chroma is not None and not ciip:
+                        add_only_records(x, y, w, h, res_c, ctb_left, ctb_up)
                     done[uy:uy + uh, ux:ux + uw] = True
                     cus.append(cu)
                     continue
@@ -930,6 +970,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     ib["up_left"] = up_left
                     ib["avail_top"], ib["avail_left"] = (top4 * 4) >> hs, (left4 * 4) >> hs
                     ib["cb_w"], ib["cb_h"] = w, h
+                    if c and (fl & abi.IB_RESIDUAL) and lmcs_chroma is not None:
+                        set_vpdu(ib, x, y, ctb_left, ctb_up)
                     iblocks.append(ib)
                 done[uy:uy + uh, ux:ux + uw] = True
                 is_intra[uy:uy + uh, ux:ux + uw] = True
@@ -965,6 +1007,11 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
     ip = abi.IntraParams()
     ip.bit_depth, ip.ctb_log2_size, ip.chroma_vertical_collocated = 10, ctb_log2, int(rng.integers(0, 2))
+    if lmcs_chroma is not None:
+        ip.lmcs_chroma_scale = 1
+        ip.lmcs_pivot[:] = [int(v) for v in lmcs_chroma["pivot"]]
+        ip.lmcs_chroma_scale_coeff[:] = [int(v) for v in lmcs_chroma["coeff"]]
+        ip.lmcs_min_bin_idx, ip.lmcs_max_bin_idx = lmcs_chroma["min_bin"], lmcs_chroma["max_bin"]
     return dict(
         ref=dict(cus=np.concatenate(cus), tus=np.concatenate(tus), tbs=tbs, levels=levels, params=rparams),
         inter=dict(blocks=pb, params=iparams, refs=refs, n_regular=n_regular,

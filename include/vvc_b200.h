@@ -334,6 +334,12 @@ enum {
     VVCB200_IB_BDPCM          = 1 << 3,  /* cu->bdpcm_flag[c_idx]: no PDPC (vvc_intra.c:564)                                */
     VVCB200_IB_RESIDUAL       = 1 << 4,  /* add the int16 residual plane to the prediction (the TB was coded)               */
     VVCB200_IB_CIIP           = 1 << 5,  /* CIIP blend of this (planar) prediction with the inter prediction already in dst */
+    VVCB200_IB_ADD_ONLY       = 1 << 6,  /* no prediction: the block already holds its (inter) prediction; only add the
+                                            residual plane.  Used for chroma blocks of inter units when the residual has
+                                            to wait for reconstructed luma (VVCB200_IB_LMCS_SCALE)                         */
+    VVCB200_IB_LMCS_SCALE     = 1 << 7,  /* chroma: scale the residual by the factor of the block's VPDU, derived from the
+                                            reconstructed luma next to it (lmcs_derive_chroma_scale,
+                                            vvc_intra_template.c:390-428)                                                  */
 };
 
 typedef struct VVCB200IntraBlock {
@@ -351,15 +357,25 @@ typedef struct VVCB200IntraBlock {
     uint8_t  cb_w, cb_h;        /* ISP: the coding block's size in luma samples (refw = cb_w + w, vvc_intra_template.c:511-514) */
     uint8_t  ciip_weight;       /* CIIP: intra weight 1..3 (ciip_derive_intra_weight, vvc_inter.c:523-543)                */
     uint8_t  res_planes;        /* CCLM record with VVCB200_IB_RESIDUAL: bit 0 = Cb has a coded residual, bit 1 = Cr     */
-    uint32_t reserved2[2];
+    /* VVCB200_IB_LMCS_SCALE: the VPDU of the coding unit's origin, in units of min(CTB size, 64) luma samples, and whether
+     * the luma column left of it (bit 0) / the luma row above it (bit 1) is available (ff_vvc_get_left/top_available)     */
+    uint8_t  vpdu_x, vpdu_y, vpdu_avail;
+    uint8_t  reserved3;
+    uint32_t reserved2;
 } VVCB200IntraBlock;            /* 28 bytes */
 
 typedef struct VVCB200IntraParams {
     int32_t bit_depth;
     int32_t ctb_log2_size;
     int32_t chroma_vertical_collocated;   /* sps_chroma_vertical_collocated_flag (CCLM down-sampling filter)              */
-    int32_t reserved;
-} VVCB200IntraParams;
+    int32_t lmcs_chroma_scale;            /* sh_lmcs_used_flag && ph_chroma_residual_scale_flag: chroma records carry
+                                             VVCB200_IB_LMCS_SCALE (informative for the device, which goes by the records) */
+    /* LMCS model for records flagged VVCB200_IB_LMCS_SCALE (VVCLMCS, vvc_ps.h:192-202) */
+    uint16_t lmcs_pivot[17];
+    uint16_t lmcs_chroma_scale_coeff[16];
+    uint8_t  lmcs_min_bin_idx, lmcs_max_bin_idx;
+    uint8_t  pad[4];
+} VVCB200IntraParams;           /* 88 bytes */
 
 /*
  * Reconstruction of the intra blocks of one picture, in place on `pic` (which already holds the inter prediction +
@@ -370,6 +386,10 @@ typedef struct VVCB200IntraParams {
  * CTUs of a diagonal interleaved) from per-CTU decoding-order records.
  * d_residual: int16 residual planes written by vvcb200_residual_batch for TBs flagged VVCB200_TB_TO_RESIDUAL (may be
  * NULL if no record has VVCB200_IB_RESIDUAL).
+ * Luma-dependent chroma residual scaling (sh_lmcs_used_flag && ph_chroma_residual_scale_flag): the factor depends on
+ * reconstructed luma, so the host cannot put it into VVCB200TransformBlock.lmcs_scale.  Instead every chroma TB of such
+ * a picture (w * h > 4) is flagged VVCB200_TB_TO_RESIDUAL without VVCB200_TB_LMCS_SCALE, and its block gets a record
+ * here flagged VVCB200_IB_RESIDUAL | VVCB200_IB_LMCS_SCALE — an intra record, or VVCB200_IB_ADD_ONLY for an inter unit.
  * d_scratch: vvcb200_intra_scratch_bytes() bytes of device memory, zeroed once after allocation; a successful call
  * leaves the marks zero again.  Two calls may not share a scratch buffer concurrently.
  */

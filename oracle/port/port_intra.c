@@ -428,13 +428,49 @@ static void cclm_block(const PortPlanes *pic, const VVCB200IntraBlock *b, const 
                 dst[c][i + j * cs[c]] = port_clip_pixel(((dsy[j * w + i] * a[c]) >> k[c]) + bb[c], bd);
 }
 
-static void add_residual_plane(const PortPlanes *pic, const PortPlanes *res, int c, int x, int y, int w, int h, int bd)
+/* lmcs_derive_chroma_scale (vvc_intra_template.c:376-428): the factor of the VPDU from the mean of the reconstructed luma
+ * samples in the column left of it and the row above it; 0 = no scaling */
+static int vpdu_chroma_scale(const PortPlanes *pic, const VVCB200IntraBlock *b, const VVCB200IntraParams *ip)
+{
+    if (!(b->flags & VVCB200_IB_LMCS_SCALE))
+        return 0;
+    const int size = (1 << ip->ctb_log2_size) < 64 ? 1 << ip->ctb_log2_size : 64;
+    const int x = b->vpdu_x * size, y = b->vpdu_y * size;
+    const int rows = size < pic->height[0] - y ? size : pic->height[0] - y;
+    const int cols = size < pic->width[0] - x ? size : pic->width[0] - x;
+    const ptrdiff_t ls = pic->stride[0] / 2;
+    const uint16_t *luma = (const uint16_t *)pic->plane[0] + (ptrdiff_t)y * ls + x;
+    int sum = 0, cnt = 0;
+    if (b->vpdu_avail & 1) {
+        for (int i = 0; i < size; i++)
+            sum += luma[-1 + ls * (i < rows ? i : rows - 1)];
+        cnt = size;
+    }
+    if (b->vpdu_avail & 2) {
+        for (int i = 0; i < size; i++)
+            sum += luma[-ls + (i < cols ? i : cols - 1)];
+        cnt += size;
+    }
+    const int mean = cnt ? (sum + (cnt >> 1)) >> ilog2(cnt) : 1 << (ip->bit_depth - 1);
+    int i = ip->lmcs_min_bin_idx;
+    while (i <= ip->lmcs_max_bin_idx && i < 16 && mean >= ip->lmcs_pivot[i + 1])
+        i++;
+    return ip->lmcs_chroma_scale_coeff[i < 15 ? i : 15];
+}
+
+static void add_residual_plane(const PortPlanes *pic, const PortPlanes *res, int c, int x, int y, int w, int h, int bd, int scale)
 {
     for (int j = 0; j < h; j++) {
         uint16_t *d = (uint16_t *)(pic->plane[c] + (size_t)(y + j) * pic->stride[c]) + x;
         const int16_t *r = (const int16_t *)(res->plane[c] + (size_t)(y + j) * res->stride[c]) + x;
-        for (int i = 0; i < w; i++)
-            d[i] = port_clip_pixel(d[i] + r[i], bd);
+        for (int i = 0; i < w; i++) {
+            int v = r[i];
+            if (scale) {                                        /* lmcs_scale_chroma, vvc_intra_template.c:431-449 */
+                const int cl = v < -(1 << bd) ? -(1 << bd) : v > (1 << bd) - 1 ? (1 << bd) - 1 : v;
+                v = cl > 0 ? (cl * scale + (1 << 10)) >> 11 : -((-cl * scale + (1 << 10)) >> 11);
+            }
+            d[i] = port_clip_pixel(d[i] + v, bd);
+        }
     }
 }
 
@@ -446,12 +482,18 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
     for (int i = 0; i < n; i++) {
         const VVCB200IntraBlock *b = &blocks[i];
         const int c = b->c_idx;
+        const int scale = vpdu_chroma_scale(pic, b, ip);
+        if (b->flags & VVCB200_IB_ADD_ONLY) {
+            if (b->flags & VVCB200_IB_RESIDUAL)
+                add_residual_plane(pic, residual, c, b->x0, b->y0, b->w, b->h, ip->bit_depth, scale);
+            continue;
+        }
         if (b->mode >= 81) {
             cclm_block(pic, b, ip);
             if (b->flags & VVCB200_IB_RESIDUAL)
                 for (int k = 1; k <= 2; k++)
                     if (b->res_planes & k)
-                        add_residual_plane(pic, residual, k, b->x0, b->y0, b->w, b->h, ip->bit_depth);
+                        add_residual_plane(pic, residual, k, b->x0, b->y0, b->w, b->h, ip->bit_depth, scale);
             continue;
         }
         if ((b->flags & VVCB200_IB_ISP) && !c) {
@@ -472,7 +514,7 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
                 uint16_t *src = (uint16_t *)(pic->plane[0] + (size_t)s.y0 * pic->stride[0]) + s.x0;
                 intra_pred_block(src, pic->stride[0] / 2, &s, ip->bit_depth);
                 if (b->flags & VVCB200_IB_RESIDUAL)
-                    add_residual_plane(pic, residual, 0, s.x0, s.y0, s.w, s.h, ip->bit_depth);
+                    add_residual_plane(pic, residual, 0, s.x0, s.y0, s.w, s.h, ip->bit_depth, 0);
             }
             continue;
         }
@@ -491,7 +533,7 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
         } else
         intra_pred_block(src, pic->stride[c] / 2, b, ip->bit_depth);
         if (b->flags & VVCB200_IB_RESIDUAL)
-            add_residual_plane(pic, residual, c, b->x0, b->y0, b->w, b->h, ip->bit_depth);
+            add_residual_plane(pic, residual, c, b->x0, b->y0, b->w, b->h, ip->bit_depth, scale);
     }
     return 0;
 }

@@ -279,6 +279,14 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
     e->pps.ctb_to_col_bd = col_bd;
     e->pps.ctb_to_row_bd = row_bd;
     e->rsps.sps_chroma_vertical_collocated_flag = ip->chroma_vertical_collocated;
+    if (ip->lmcs_chroma_scale) {                            /* luma-dependent chroma residual scaling */
+        e->rsh.sh_lmcs_used_flag = 1;
+        e->rph.ph_chroma_residual_scale_flag = 1;
+        e->fc.ps.lmcs.min_bin_idx = ip->lmcs_min_bin_idx;
+        e->fc.ps.lmcs.max_bin_idx = ip->lmcs_max_bin_idx;
+        memcpy(e->fc.ps.lmcs.pivot, ip->lmcs_pivot, sizeof(e->fc.ps.lmcs.pivot));
+        memcpy(e->fc.ps.lmcs.chroma_scale_coeff, ip->lmcs_chroma_scale_coeff, sizeof(e->fc.ps.lmcs.chroma_scale_coeff));
+    }
     e->fc.tab.slice_idx = slice_idx;
     e->fc.tab.ctus = ctus;
     e->fc.tab.imf    = tabs;
@@ -357,7 +365,7 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
                 cu->pu.mi.pred_flag = d->pred_flag;
                 /* slice-level switches, the same for every CIIP unit of the picture */
                 e->rpps.pps_weighted_pred_flag = e->rpps.pps_weighted_bipred_flag = !!(d->inter_flags & VVCB200_PB_WP);
-                e->rsh.sh_lmcs_used_flag = !!(d->inter_flags & VVCB200_PB_LMCS);
+                e->rsh.sh_lmcs_used_flag |= !!(d->inter_flags & VVCB200_PB_LMCS);
             }
             for (int y = d->y0 >> 2; y < (d->y0 + d->h) >> 2; y++)
                 for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++) {

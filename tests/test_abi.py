@@ -34,7 +34,8 @@ def test_abi_version_and_error_string():
 
 def test_struct_sizes_match_c():
     names = ["VVCB200TransformBlock", "VVCB200ResidualParams", "VVCB200Planes", "VVCB200PredBlock", "VVCB200InterParams",
-             "VVCB200DeblockParams", "VVCB200DeblockTables", "VVCB200SaoCtb", "VVCB200AlfCtb", "VVCB200AlfParams"]
+             "VVCB200DeblockParams", "VVCB200DeblockTables", "VVCB200SaoCtb", "VVCB200AlfCtb", "VVCB200AlfParams",
+             "VVCB200IntraBlock", "VVCB200IntraParams", "VVCB200ProfTable"]
     code = '#include <stdio.h>\n#include "vvc_b200.h"\nint main(void){' + \
         "".join('printf("%%zu\\n", sizeof(%s));' % n for n in names) + "return 0;}\n"
     with tempfile.TemporaryDirectory() as d:
@@ -45,7 +46,8 @@ def test_struct_sizes_match_c():
         sizes = [int(v) for v in subprocess.check_output([exe]).split()]
     assert sizes == [abi.TB_DTYPE.itemsize, C.sizeof(abi.ResidualParams), C.sizeof(abi.Planes), abi.PB_DTYPE.itemsize,
                      C.sizeof(abi.InterParams), C.sizeof(abi.DeblockParams), C.sizeof(abi.DeblockTables),
-                     abi.SAO_DTYPE.itemsize, abi.ALF_CTB_DTYPE.itemsize, abi.ALF_PARAMS_DTYPE.itemsize]
+                     abi.SAO_DTYPE.itemsize, abi.ALF_CTB_DTYPE.itemsize, abi.ALF_PARAMS_DTYPE.itemsize,
+                     abi.IB_DTYPE.itemsize, C.sizeof(abi.IntraParams), abi.PROF_DTYPE.itemsize]
 
 
 def test_bad_arguments_are_rejected_without_a_gpu():
