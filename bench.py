@@ -58,7 +58,7 @@ def make_picture(seed, width, height, intra_fraction):
     """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
     with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v6_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
+    cache = "/tmp/vvcb200_bench_v7_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
     kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
              ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):
@@ -293,7 +293,8 @@ def main():
     it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
     frame_bytes = 2 * st["S"]
     ctb = pic["ctb_log2"]
-    irecs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb)
+    irecs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb, ctb,
+                                width, height)
     config.update({"transform_blocks": int(len(rs["tbs"])), "pred_blocks": int(len(it["blocks"])),
                    "intra_records": int(len(irecs)), "intra_sample_share": round(st["intra_share"], 3),
                    "coded_fraction": round(st["rho"], 3), "ref_samples_per_sample": round(st["r"], 3)})

@@ -19,7 +19,7 @@ FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     "--expt-relaxed-constexpr", "--extended-lambda", "-Xcompiler", "-fPIC,-fvisibility=hidden",
     "-I", os.path.join(ROOT, "include"), "-I", CSRC,
-]
+] + os.environ.get("VVCB200_NVCC_FLAGS", "").split()      # development only, e.g. -DVVC_INTRA_PROFILE
 
 
 def _newer(a, b):

@@ -410,17 +410,14 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
     }
     DeviceGuard g(c->device);
     c->intra_order.resize(n);
-    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, c->intra_order.data()))
+    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, shift, c->width, c->height, c->intra_order.data(), nullptr))
         return r;
     // the copy below is from pageable memory: the driver stages it before returning, so the vector may be reused
     if (int r = upload(c, c->iblocks, c->intra_order.data(), (size_t)n * sizeof(VVCB200IntraBlock)))
         return r;
     const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
-    if (!c->intra_marks.p) {
-        if (int r = c->intra_marks.reserve(marks))
-            return r;
-        VVC_CUDA(cudaMemsetAsync(c->intra_marks.p, 0, c->intra_marks.cap, c->stream));
-    }
+    if (int r = c->intra_marks.reserve(marks))
+        return r;
     return vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr,
                                  (const VVCB200IntraBlock *)c->iblocks.p, n, params, c->intra_marks.p, c->stream);
 }

@@ -6,10 +6,12 @@
 //
 // Intra prediction reads reconstructed neighbours, so the work is a dependency graph, not a batch.  The reference
 // walks it as a CTU wavefront (vvc_thread.c:156-184); here the graph is resolved per block:
-//   * every record marks the 4x4 (chroma: 4x2) units it will write as "pending" (mark kernel);
-//   * warps draw records from a ticket counter in array order — a topological order, see vvcb200_intra_schedule —
-//     and spin until the units holding the neighbour samples they read are no longer pending;
-//   * a warp that finished a record publishes its samples (__threadfence) and clears the record's marks.
+//   * a pre-pass fills the samples every intra record will write with a sentinel (0xffff, not a sample value at any
+//     supported bit depth); warps draw records from a ticket counter in array order — a topological order, see
+//     vvcb200_intra_schedule — and re-read the neighbour samples they need until none of them is the sentinel: the
+//     read that detects readiness is the read that fetches the data, and the writer needs no fence and no flag;
+//   * blocks that are overwritten in place (CIIP blend, add-only chroma of inter units) cannot carry a sentinel: they
+//     mark their 4x4 (chroma: 4x2) units "pending" in the scratch maps instead, publish with a fence and clear the marks.
 // A ticket is only ever held by a resident warp and waits only on lower tickets, so the scheme cannot deadlock
 // whatever the grid size; parallelism is what the picture's block graph offers (blocks of one anti-diagonal of
 // CTUs and independent blocks inside a CTU run concurrently), which is far more than one warp per CTU row.
@@ -25,11 +27,36 @@ constexpr int kWarps   = 4;       // warps per CTA
 constexpr int kEdgeLen = 256;     // samples per edge array: indices -72 .. 183 are addressable
 constexpr int kEdgeOrg = 72;
 constexpr unsigned kFull = 0xffffffffu;
+constexpr unsigned kSentinel = 0xffffu;                                   // "not reconstructed yet"
+#ifdef VVC_INTRA_PROFILE
+__device__ unsigned long long g_prof[8];      // cycles: 0 ticket+record, 1 record total, 2 publish; 3 records; 4 wait (inside 1)
+#define PROF_T() clock64()
+#define PROF_ADD(i, v) do { if (lane == 0) atomicAdd(&g_prof[i], (unsigned long long)(v)); } while (0)
+#else
+#define PROF_T() 0ll
+#define PROF_ADD(i, v) do { } while (0)
+#endif
 
-struct WarpScratch {
+// Staging area of a warp: everything a record reads that does not depend on its neighbours (its residual, the inter
+// prediction of a CIIP block) is fetched with cp.async BEFORE the warp starts waiting, so that the latency of those
+// reads never sits on the picture's dependency chain; CCLM stages the co-located luma window here after the wait.
+constexpr int kStageRes   = 64 * 64 * 2;                                  // residual block, or Cb + Cr residual of a CCLM record
+constexpr int kStageExtra = 65 * 68 * 2 + 16;                             // CIIP: inter prediction; CCLM: luma window
+struct __align__(16) WarpScratch {
+    uint8_t  stage_res[kStageRes];
+    uint8_t  stage_extra[kStageExtra];
     uint16_t edge[4][kEdgeLen];   // left, top, filtered left, filtered top
     int      red[16];             // MIP: reduced boundary
     uint16_t mip[64];             // MIP: reduced prediction, row-major at the reduced size
+};
+
+// Small tables every record consults, copied once per CTA: after each acquire fence the L1 is invalidated, so a table
+// left in global memory would cost an L2 round trip per lookup on the dependency chain.
+struct CtaTables {
+    int16_t angle[95], inv_angle[95];
+    int8_t  luma_filter[256];
+    uint16_t mip_off[4];
+    uint8_t mip_mat[4736];
 };
 
 struct IntraArgs {
@@ -39,15 +66,15 @@ struct IntraArgs {
     const VVCB200IntraBlock *blocks;
     int n;
     int bd, ctb_log2, collocated;
-    uint8_t *marks[3];            // pending marks per plane
+    uint8_t *marks[3];            // pending marks per plane (in-place records only)
     int mpitch[3];
-    int *ticket;
+    int *ticket;                  // ticket[0]: next record; ticket[1]: the picture has in-place records
     uint16_t lmcs_pivot[17], lmcs_coeff[16];
     int lmcs_min_bin, lmcs_max_bin;
 };
 
 __device__ __forceinline__ int ilog2(int v) { return 31 - __clz(v); }
-__device__ __forceinline__ int unit_shift(int c) { return c ? 1 : 2; }     // rows per unit: 4 (luma) / 2 (chroma)
+__host__ __device__ __forceinline__ int unit_shift(int c) { return c ? 1 : 2; }     // rows per unit: 4 (luma) / 2 (chroma)
 
 __device__ __forceinline__ VVCB200IntraBlock load_record(const VVCB200IntraBlock *p)
 {
@@ -60,31 +87,63 @@ __device__ __forceinline__ VVCB200IntraBlock load_record(const VVCB200IntraBlock
 }
 
 // ---- pending marks -------------------------------------------------------------------------------------------
-__device__ __forceinline__ bool row_pending(const IntraArgs &a, int c, int uy, int ux0, int n, int lane)
+// Marks and the samples they guard are exchanged through L2: producers publish with fence.acq_rel.gpu before clearing
+// a mark, consumers poll with gpu-scope relaxed loads, fence, then read samples with ld.cg.  (__threadfence() would be
+// a sequentially consistent fence, MEMBAR.SC.GPU, several times more expensive on the critical path.)
+__device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" ::: "memory"); }
+
+// w samples per row (multiple of 4), h rows, global -> shared (compact rows of w), asynchronously.  8-byte pieces: block
+// origins are only guaranteed to be multiples of 4 samples (ternary splits).
+__device__ __forceinline__ void stage_block_async(void *sdst, const void *g, int gstride /* samples */, int w, int h, int lane)
 {
-    bool p = false;
-    for (int i = lane; i < n; i += 32)
-        p |= *((const volatile uint8_t *)a.marks[c] + (size_t)uy * a.mpitch[c] + ux0 + i) != 0;
-    return p;
+    const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sdst);
+    const uint16_t *gp = static_cast<const uint16_t *>(g);
+    const int per_row = w >> 2, n = per_row * h;
+    for (int i = lane; i < n; i += 32) {
+        const int y = i / per_row, x = (i - y * per_row) << 2;
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + (y * w + x) * 2), "l"(gp + (size_t)y * gstride + x) : "memory");
+    }
+}
+__device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+__device__ __forceinline__ unsigned load_mark(const uint8_t *p)
+{
+    unsigned v;
+    asm volatile("ld.relaxed.gpu.global.u8 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
 }
 
-__device__ __forceinline__ bool col_pending(const IntraArgs &a, int c, int ux, int uy0, int n, int lane)
+__device__ __forceinline__ void store_mark(uint8_t *p, unsigned v)
 {
-    bool p = false;
+    asm volatile("st.relaxed.gpu.global.u8 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// marks: 0 = never marked, 1 = pending, 2 = was pending, now written.  Returns the OR of the marks of the run.
+__device__ __forceinline__ unsigned row_marks(const IntraArgs &a, int c, int uy, int ux0, int n, int lane)
+{
+    unsigned m = 0;
     for (int i = lane; i < n; i += 32)
-        p |= *((const volatile uint8_t *)a.marks[c] + (size_t)(uy0 + i) * a.mpitch[c] + ux) != 0;
-    return p;
+        m |= load_mark(a.marks[c] + (size_t)uy * a.mpitch[c] + ux0 + i);
+    return m;
+}
+
+__device__ __forceinline__ unsigned col_marks(const IntraArgs &a, int c, int ux, int uy0, int n, int lane)
+{
+    unsigned m = 0;
+    for (int i = lane; i < n; i += 32)
+        m |= load_mark(a.marks[c] + (size_t)(uy0 + i) * a.mpitch[c] + ux);
+    return m;
 }
 
 // units touched by samples [p0, p0 + n) along an axis with 1 << s samples per unit
-__device__ __forceinline__ int unit_count(int p0, int n, int s) { return n > 0 ? ((p0 + n - 1) >> s) - (p0 >> s) + 1 : 0; }
+__host__ __device__ __forceinline__ int unit_count(int p0, int n, int s) { return n > 0 ? ((p0 + n - 1) >> s) - (p0 >> s) + 1 : 0; }
 
 __device__ void set_marks(const IntraArgs &a, int c, int x0, int y0, int w, int h, uint8_t v, int lane)
 {
     const int s = unit_shift(c);
     const int ux = x0 >> 2, uy = y0 >> s, nx = unit_count(x0, w, 2), ny = unit_count(y0, h, s);
     for (int i = lane; i < nx * ny; i += 32)
-        *((volatile uint8_t *)a.marks[c] + (size_t)(uy + i / nx) * a.mpitch[c] + ux + i % nx) = v;
+        store_mark(a.marks[c] + (size_t)(uy + i / nx) * a.mpitch[c] + ux + i % nx, v);
 }
 
 // the samples a record writes: an ISP luma record stands for its whole coding block
@@ -95,24 +154,35 @@ __device__ __forceinline__ void record_extent(const VVCB200IntraBlock &b, int &w
     h = isp ? b.cb_h : b.h;
 }
 
+__device__ __forceinline__ bool in_place(const VVCB200IntraBlock &b) { return b.flags & (VVCB200_IB_CIIP | VVCB200_IB_ADD_ONLY); }
+
 __global__ void intra_mark_kernel(IntraArgs a)
 {
     const int lane = threadIdx.x & 31;
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (t == 0 && lane == 0)
-        *a.ticket = 0;
     if (t >= a.n)
         return;
     const VVCB200IntraBlock b = load_record(a.blocks + t);
     int w, h;
     record_extent(b, w, h);
-    set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane);
-    if (b.mode >= 81)
-        set_marks(a, 2, b.x0, b.y0, w, h, 1, lane);
+    if (in_place(b)) {
+        set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane);
+        if (lane == 0)
+            a.ticket[1] = 1;
+        return;
+    }
+    for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {       // sentinel over everything the record will write
+        uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
+        const int per_row = w >> 2;
+        for (int i = lane; i < per_row * h; i += 32) {
+            const int y = i / per_row, x = (i - y * per_row) << 2;
+            *reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x) = make_uint2(0xffffffffu, 0xffffffffu);
+        }
+    }
 }
 
 // ---- mode helpers (vvc_intra.c:538-660) ---------------------------------------------------------------------------
-__device__ __forceinline__ bool ref_filter_mode(int mode)
+__host__ __device__ __forceinline__ bool ref_filter_mode(int mode)
 {
     // modes whose angle hits integer sample positions: the reference smooths the edge instead of interpolating
     switch (mode) {
@@ -124,22 +194,22 @@ __device__ __forceinline__ bool ref_filter_mode(int mode)
 
 __device__ __forceinline__ bool is_plain_mode(int mode) { return mode == 0 || mode == 1 || mode == 18 || mode == 50; }
 
-__device__ __forceinline__ int nscale_of(int lw, int lh, int mode)
+__device__ __forceinline__ int nscale_of(const CtaTables &tb, int lw, int lh, int mode)
 {
     if (is_plain_mode(mode))
         return (lw + lh - 2) >> 2;
-    const int ns = (mode >= 50 ? lh : lw) - ilog2(3 * VVC_INTRA_INV_ANGLE[mode + 14] - 2) + 8;
+    const int ns = (mode >= 50 ? lh : lw) - ilog2(3 * tb.inv_angle[mode + 14] - 2) + 8;
     return min(ns, 2);
 }
 
-__device__ __forceinline__ bool need_pdpc(int w, int h, int lw, int lh, bool bdpcm, int mode, int ref_idx)
+__device__ __forceinline__ bool need_pdpc(const CtaTables &tb, int w, int h, int lw, int lh, bool bdpcm, int mode, int ref_idx)
 {
     if (w >= 4 && h >= 4 && !ref_idx && !bdpcm) {
         if (is_plain_mode(mode))
             return true;
         if (mode > 18 && mode < 50)
             return false;
-        return nscale_of(lw, lh, mode) >= 0;
+        return nscale_of(tb, lw, lh, mode) >= 0;
     }
     return false;
 }
@@ -152,34 +222,196 @@ __device__ __forceinline__ int warp_sum(int v)
     return v;
 }
 
+// ---- what a record reads, as runs of mark units: shared by the device (what to wait for) and by the host scheduler
+// (which records a record depends on) so that the two can never disagree ------------------------------------------
+struct Span {
+    int c, horizontal;            // plane; run goes right (1) or down (0)
+    int ux, uy, n;                // first unit and length
+};
+constexpr int kMaxSpans = 12;
+
+__host__ __device__ __forceinline__ int imin(int a, int b) { return a < b ? a : b; }
+__host__ __device__ __forceinline__ int imax(int a, int b) { return a > b ? a : b; }
+
+struct EdgeExtent {
+    int ul, ut;                   // samples of the left / top edge the mode reads (vvc_intra_template.c:470-520)
+    int left_size, refw, refh;
+    bool smooth;                  // [1 2 1] smoothing of the edges
+};
+
+__host__ __device__ inline EdgeExtent edge_extent(const VVCB200IntraBlock &b)
+{
+    EdgeExtent e;
+    const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode;
+    const bool is_mip = b.flags & VVCB200_IB_MIP, isp = b.flags & VVCB200_IB_ISP;
+    const bool pdpc_plain = w >= 4 && h >= 4 && !b.ref_idx && !(b.flags & VVCB200_IB_BDPCM);
+    e.smooth = !b.ref_idx && w * h > 32 && !c && !isp && !is_mip && ref_filter_mode(mode);
+    e.refw = e.refh = 0;
+    if (is_mip || mode == 0) {
+        e.left_size = h + 1;
+        e.ul = e.left_size + e.smooth;
+        e.ut = w + 1 + e.smooth;
+    } else if (mode == 1) {
+        e.ul = e.left_size = h;
+        e.ut = w;
+    } else if (mode == 50) {
+        e.ul = e.left_size = pdpc_plain ? h : 1;
+        e.ut = w;
+    } else if (mode == 18) {
+        e.ul = e.left_size = h;
+        e.ut = pdpc_plain ? w : 1;
+    } else {
+        if (!isp || c) { e.refw = w * 2; e.refh = h * 2; }
+        else           { e.refw = b.cb_w + w; e.refh = b.cb_h + h; }
+        e.ut = e.refw;
+        e.ul = e.left_size = e.refh;
+    }
+    return e;
+}
+
+// the luma column / row next to the VPDU that a luma-dependent chroma scale is derived from
+__host__ __device__ inline int vpdu_deps(const VVCB200IntraBlock &b, int ctb_log2, int pic_w, int pic_h, Span *out)
+{
+    int n = 0;
+    if (!(b.flags & VVCB200_IB_LMCS_SCALE))
+        return 0;
+    const int size = imin(1 << ctb_log2, 64);
+    const int x = b.vpdu_x * size, y = b.vpdu_y * size;
+    const int rows = imin(size, pic_h - y), cols = imin(size, pic_w - x);
+    if (b.vpdu_avail & 1) out[n++] = Span{ 0, 0, (x >> 2) - 1, y >> 2, unit_count(y, rows, 2) };
+    if (b.vpdu_avail & 2) out[n++] = Span{ 0, 1, x >> 2, (y >> 2) - 1, unit_count(x, cols, 2) };
+    return n;
+}
+
+// skip_wait: bit 0 = the row above (and the corner), bit 1 = the column to the left (and the corner) were written by
+// the same warp (earlier ISP sub-partitions) and carry this record's own marks
+__host__ __device__ inline int predict_deps(const VVCB200IntraBlock &b, int skip_wait, Span *out)
+{
+    if (b.flags & VVCB200_IB_ADD_ONLY)
+        return 0;
+    const EdgeExtent e = edge_extent(b);
+    const int la = imin(e.ul, b.avail_left), ta = imin(e.ut, b.avail_top);
+    const int c = b.c_idx, s = unit_shift(c), ux = b.x0 >> 2, uy = b.y0 >> s;
+    int n = 0;
+    if (la && !(skip_wait & 2)) out[n++] = Span{ c, 0, ux - 1, uy, unit_count(b.y0, la, s) };
+    if (ta && !(skip_wait & 1)) out[n++] = Span{ c, 1, ux, uy - 1, unit_count(b.x0, ta, 2) };
+    if (b.up_left && !skip_wait) out[n++] = Span{ c, 1, ux - 1, uy - 1, 1 };
+    return n;
+}
+
+struct CclmCounts { int num[2]; };
+__host__ __device__ inline CclmCounts cclm_counts(const VVCB200IntraBlock &b)
+{
+    CclmCounts k;
+    const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
+    const int mn = imin(b.w, b.h);
+    if (b.mode == 81) {
+        k.num[0] = avail_t ? b.w : 0;
+        k.num[1] = avail_l ? b.h : 0;
+    } else {
+        k.num[0] = (avail_t && b.mode == 83) ? imin(b.w + mn, b.avail_top) : 0;
+        k.num[1] = (avail_l && b.mode == 82) ? imin(b.h + mn, b.avail_left) : 0;
+    }
+    return k;
+}
+
+// CCLM: own luma block, luma neighbours under the down-sampling footprint, chroma neighbours of both planes
+__host__ __device__ inline int cclm_deps(const VVCB200IntraBlock &b, Span *out)
+{
+    const CclmCounts k = cclm_counts(b);
+    const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
+    const int w = b.w, h = b.h, x = b.x0, y = b.y0, x0 = x * 2, y0 = y * 2;
+    const int lux = x0 >> 2, luy = y0 >> 2, cux = x >> 2, cuy = y >> 1;
+    const int lnx = unit_count(x0, 2 * w, 2), lny = unit_count(y0, 2 * h, 2);
+    int n = 0;
+    out[n++] = Span{ 0, 1, lux, luy, lnx };
+    out[n++] = Span{ 0, 1, lux, luy + lny - 1, lnx };
+    if (avail_t) out[n++] = Span{ 0, 1, lux, luy - 1, unit_count(x0, 2 * imax(w, k.num[0]), 2) };
+    if (avail_l) out[n++] = Span{ 0, 0, lux - 1, luy, unit_count(y0, 2 * imax(h, k.num[1]), 2) };
+    if (avail_t && avail_l) out[n++] = Span{ 0, 1, lux - 1, luy - 1, 1 };
+    for (int c = 1; c <= 2; c++) {
+        if (k.num[0]) out[n++] = Span{ c, 1, cux, cuy - 1, unit_count(x, k.num[0], 2) };
+        if (k.num[1]) out[n++] = Span{ c, 0, cux - 1, cuy, unit_count(y, k.num[1], 1) };
+    }
+    return n;
+}
+
+// sub-partition k of an ISP record (vvc_intra.c:217-226): geometry and the availability that follows from the
+// coding block's; returns the skip_wait bits
+__host__ __device__ inline int isp_part(const VVCB200IntraBlock &b, int k, VVCB200IntraBlock &s)
+{
+    const bool hor = b.w == b.cb_w;
+    s = b;
+    if (hor) {
+        s.y0 += k * b.h;
+        s.avail_left = imax((int)b.avail_left - k * b.h, 0);
+        if (k) { s.avail_top = b.w; s.up_left = b.avail_left > 0; }
+    } else {
+        s.x0 += k * b.w;
+        s.avail_top = imax((int)b.avail_top - k * b.w, 0);
+        if (k) { s.avail_left = b.h; s.up_left = b.avail_top > 0; }
+    }
+    return k ? (hor ? 1 : 2) : 0;
+}
+__host__ __device__ inline int isp_parts(const VVCB200IntraBlock &b) { return b.w == b.cb_w ? b.cb_h / b.h : b.cb_w / b.w; }
+
+// wait until none of the units in the runs is pending any more; the acquire fence is only needed when some unit was
+// written by an in-place record (its samples were published before its mark went from 1 to 2)
+__device__ void wait_spans(const IntraArgs &a, const Span *sp, int n, int lane)
+{
+    if (!n)
+        return;
+    unsigned m;
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+        m = 0;
+        for (int i = 0; i < n; i++)
+            m |= sp[i].horizontal ? row_marks(a, sp[i].c, sp[i].uy, sp[i].ux, sp[i].n, lane)
+                                  : col_marks(a, sp[i].c, sp[i].ux, sp[i].uy, sp[i].n, lane);
+        m = __reduce_or_sync(kFull, m);
+        if (!(m & 1))
+            break;
+        __nanosleep(backoff);
+    }
+    if (m & 2)
+        fence_gpu();
+}
+
 // ---- luma-dependent chroma residual scaling (vvc_intra_template.c:376-449) ------------------------------------------
 // The factor of a VPDU comes from the mean of the reconstructed luma samples left of and above it.
-__device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, int lane)
+__device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane)
 {
     const int size = min(1 << a.ctb_log2, 64), ls = ilog2(size);
     const int x = b.vpdu_x << ls, y = b.vpdu_y << ls;
     const bool al = b.vpdu_avail & 1, at = b.vpdu_avail & 2;
     const int rows = min(size, a.pic.h[0] - y), cols = min(size, a.pic.w[0] - x);
-    for (;;) {
-        bool p = false;
-        if (al) p |= col_pending(a, 0, (x >> 2) - 1, y >> 2, unit_count(y, rows, 2), lane);
-        if (at) p |= row_pending(a, 0, (y >> 2) - 1, x >> 2, unit_count(x, cols, 2), lane);
-        if (!__any_sync(kFull, p))
-            break;
-        __nanosleep(64);
+    if (has_marks) {
+        Span sp[2];
+        wait_spans(a, sp, vpdu_deps(b, a.ctb_log2, a.pic.w[0], a.pic.h[0], sp), lane);
     }
-    __threadfence();
     const uint16_t *luma = a.pic.p[0] + (size_t)y * a.pic.stride[0] + x;
-    int sum = 0, cnt = 0;
-    if (al) {                                                             // past the picture edge the last sample repeats
-        for (int i = lane; i < size; i += 32)
-            sum += __ldcg(luma - 1 + (ptrdiff_t)a.pic.stride[0] * min(i, rows - 1));
-        cnt = size;
-    }
-    if (at) {
-        for (int i = lane; i < size; i += 32)
-            sum += __ldcg(luma - a.pic.stride[0] + min(i, cols - 1));
-        cnt += size;
+    int sum, cnt;
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+        bool bad = false;
+        sum = cnt = 0;
+        if (al) {                                                         // past the picture edge the last sample repeats
+            for (int i = lane; i < size; i += 32) {
+                const unsigned v = __ldcg(luma - 1 + (ptrdiff_t)a.pic.stride[0] * min(i, rows - 1));
+                bad |= v == kSentinel;
+                sum += v;
+            }
+            cnt = size;
+        }
+        if (at) {
+            for (int i = lane; i < size; i += 32) {
+                const unsigned v = __ldcg(luma - a.pic.stride[0] + min(i, cols - 1));
+                bad |= v == kSentinel;
+                sum += v;
+            }
+            cnt += size;
+        }
+        if (!__any_sync(kFull, bad))
+            break;
+        __nanosleep(backoff);
     }
     sum = warp_sum(sum);
     const int mean = cnt ? (sum + (cnt >> 1)) >> ilog2(cnt) : 1 << (a.bd - 1);
@@ -198,15 +430,16 @@ __device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
 // ---- one angular / planar / DC / MIP block --------------------------------------------------------------------------
 struct Store {                    // what happens to a predicted sample on its way to the picture
     uint16_t *dst;
-    const int16_t *res;
-    int dstride, rstride, bd, ciip_w, lscale;
+    const int16_t *res;           // staged residual block (shared memory, rows of w), or null
+    const uint16_t *inter;        // CIIP: staged inter prediction (shared memory, rows of w)
+    int dstride, w, bd, ciip_w, lscale;
     __device__ __forceinline__ void put(int x, int y, int pred) const
     {
         uint16_t *d = dst + (size_t)y * dstride + x;
         if (ciip_w)                                                       // put_ciip, vvc_inter_template.c:60-76
-            pred = (pred * ciip_w + (int)__ldcg(d) * (4 - ciip_w) + 2) >> 2;
+            pred = (pred * ciip_w + (int)inter[y * w + x] * (4 - ciip_w) + 2) >> 2;
         if (res) {                                                        // add_residual, vvc_itx_1d / vvcdsp.h:154
-            int r = res[(size_t)y * rstride + x];
+            int r = res[y * w + x];
             if (lscale)
                 r = scale_chroma_residual(r, lscale, bd);
             pred = clip_pixel(pred + r, bd);
@@ -215,96 +448,135 @@ struct Store {                    // what happens to a predicted sample on its w
     }
 };
 
-// skip_wait: bit 0 = the row above (and the corner), bit 1 = the column to the left (and the corner) were written by
-// this warp itself (earlier ISP sub-partitions) and carry this record's own marks
-__device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, int skip_wait = 0)
+__device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, int lane,
+                               bool has_marks, int skip_wait = 0)
 {
+    const long long p0 = PROF_T();
     const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode, ref_idx = b.ref_idx, bd = a.bd;
     const int lw = ilog2(w), lh = ilog2(h);
     const bool is_mip = b.flags & VVCB200_IB_MIP, isp = b.flags & VVCB200_IB_ISP;
-    const bool pdpc = need_pdpc(w, h, lw, lh, b.flags & VVCB200_IB_BDPCM, mode, ref_idx);
+    const bool pdpc = need_pdpc(tb, w, h, lw, lh, b.flags & VVCB200_IB_BDPCM, mode, ref_idx);
     const bool rff = !is_mip && ref_filter_mode(mode);
-    const bool smooth = !ref_idx && w * h > 32 && !c && !isp && rff;      // [1 2 1] edge smoothing
+    const EdgeExtent ee = edge_extent(b);
+    const bool smooth = ee.smooth;
     const int ref_line = ref_idx == 3 ? -4 : -1 - ref_idx;
     const int stride = a.pic.stride[c];
     uint16_t *src = a.pic.p[c] + (size_t)b.y0 * stride + b.x0;
-    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, lane) : 0;
+    const bool has_res = b.flags & VVCB200_IB_RESIDUAL;
+    const bool ciip = b.flags & VVCB200_IB_CIIP, add_only = b.flags & VVCB200_IB_ADD_ONLY;
+    // reads that do not depend on the neighbours start now and land while the warp waits
+    if (has_res)
+        stage_block_async(ws.stage_res, a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0, a.res_stride[c], w, h, lane);
+    if (ciip || add_only)
+        stage_block_async(ws.stage_extra, src, stride, w, h, lane);
+    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, has_marks, lane) : 0;
 
-    if (b.flags & VVCB200_IB_ADD_ONLY) {                                  // the prediction is there already
-        if (b.flags & VVCB200_IB_RESIDUAL) {
-            const int16_t *res = a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0;
+    if (add_only) {                                                       // the prediction is there already
+        if (has_res) {
+            const int16_t *res = reinterpret_cast<const int16_t *>(ws.stage_res);
+            const uint16_t *cur = reinterpret_cast<const uint16_t *>(ws.stage_extra);
+            stage_wait();
+            __syncwarp();
             for (int idx = lane; idx < w * h; idx += 32) {
                 const int x = idx & (w - 1), y = idx >> lw;
-                int r = res[(size_t)y * a.res_stride[c] + x];
+                int r = res[idx];
                 if (lscale)
                     r = scale_chroma_residual(r, lscale, bd);
-                uint16_t *d = src + (size_t)y * stride + x;
-                *d = (uint16_t)clip_pixel((int)__ldcg(d) + r, bd);
+                src[(size_t)y * stride + x] = (uint16_t)clip_pixel((int)cur[idx] + r, bd);
             }
         }
         return;
     }
 
-    // how much of each edge the mode reads (vvc_intra_template.c:470-520)
-    int left_size, ul, ut, refw = 0, refh = 0;
-    if (is_mip || mode == 0) {
-        left_size = h + 1;
-        ul = left_size + smooth;
-        ut = w + 1 + smooth;
-    } else if (mode == 1) {
-        ul = left_size = h;
-        ut = w;
-    } else if (mode == 50) {
-        ul = left_size = pdpc ? h : 1;
-        ut = w;
-    } else if (mode == 18) {
-        ul = left_size = h;
-        ut = pdpc ? w : 1;
-    } else {
-        if (!isp || c) { refw = w * 2; refh = h * 2; }
-        else           { refw = b.cb_w + w; refh = b.cb_h + h; }
-        ut = refw;
-        ul = left_size = refh;
-    }
+    const int left_size = ee.left_size, ul = ee.ul, ut = ee.ut, refw = ee.refw, refh = ee.refh;
     const int la = min(ul, (int)b.avail_left), ta = min(ut, (int)b.avail_top);
 
-    // ---- wait for the neighbours this block reads
-    {
-        const int s = unit_shift(c), ux = b.x0 >> 2, uy = b.y0 >> s;
-        const int nl = unit_count(b.y0, la, s), nt = unit_count(b.x0, ta, 2);
-        for (;;) {
-            bool p = false;
-            if (nl && !(skip_wait & 2)) p |= col_pending(a, c, ux - 1, uy, nl, lane);
-            if (nt && !(skip_wait & 1)) p |= row_pending(a, c, uy - 1, ux, nt, lane);
-            if (b.up_left && !skip_wait) p |= row_pending(a, c, uy - 1, ux - 1, 1, lane);
-            if (!__any_sync(kFull, p))
-                break;
-            __nanosleep(64);
-        }
-        __threadfence();
+    // ---- neighbours written in place (CIIP, add-only) announce themselves through the marks
+    PROF_ADD(7, PROF_T() - p0);
+    if (has_marks) {
+        Span sp[3];
+        wait_spans(a, sp, predict_deps(b, skip_wait, sp), lane);
     }
 
-    // ---- gather the edges into shared memory
-    uint16_t *left = ws.edge[0] + kEdgeOrg, *top = ws.edge[1] + kEdgeOrg;
-    for (int i = lane; i < la; i += 32)
-        left[i] = __ldcg(src + ref_line + (ptrdiff_t)stride * i);
-    for (int i = lane; i < ta; i += 32)
-        top[i] = __ldcg(src + i + (ptrdiff_t)stride * ref_line);
-    if (lane < -ref_line) {                                               // the corner run, indices -1 .. ref_line
-        const int i = -1 - lane;
-        int vl, vt;
-        if (b.up_left) {
-            vl = __ldcg(src + ref_line + (ptrdiff_t)stride * i);
-            vt = __ldcg(src + i + (ptrdiff_t)stride * ref_line);
-        } else if (la) {
-            vl = vt = __ldcg(src + ref_line);
-        } else if (ta) {
-            vl = vt = __ldcg(src + (ptrdiff_t)stride * ref_line);
+    // ---- which of the edge samples the prediction really consumes.  The reference fetches `ul` / `ut` samples whatever
+    // the mode; samples that never reach the output need not be waited for (their value, sentinel or not, is
+    // irrelevant), which removes the above-right / below-left dependency for most modes and shortens the chains.
+    int need_l = ul, need_t = ut;
+    if (is_mip) {
+        need_l = h; need_t = w;
+    } else if (mode == 1) {
+        if (!pdpc) { need_t = w >= h ? w : 0; need_l = h >= w ? h : 0; }
+    } else if (mode == 50) {
+        need_l = pdpc ? h : 0;
+    } else if (mode == 18) {
+        need_t = pdpc ? w : 0;
+    } else if (mode != 0) {
+        const bool vertical = mode >= 34;
+        const int ang = tb.angle[mode + 14];
+        const int n_main = vertical ? w : h, n_al = vertical ? h : w;
+        int need_main, need_side;
+        if (ang > 0) {
+            need_main = n_main + (((n_al + ref_idx) * ang) >> 5) + 2 + smooth;
+            need_side = 0;
+            if (pdpc) {
+                const int ns = nscale_of(tb, lw, lh, mode);
+                need_side = n_al + ((256 + min(n_main, 3 << ns) * tb.inv_angle[mode + 14]) >> 9) + 1 + smooth;
+            }
         } else {
-            vl = vt = 1 << (bd - 1);
+            need_main = n_main + 2 + smooth;
+            need_side = n_al + 2 + smooth;
         }
-        left[i] = vl;
-        top[i] = vt;
+        need_t = min(ut, vertical ? need_main : need_side);
+        need_l = min(ul, vertical ? need_side : need_main);
+    }
+
+    // ---- gather the edges into shared memory; a sentinel among them means "not reconstructed yet": read again
+    const long long g0 = PROF_T();
+    uint16_t *left = ws.edge[0] + kEdgeOrg, *top = ws.edge[1] + kEdgeOrg;
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+        unsigned lv[4], tv[4], vl = 0, vt = 0;
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = lane + 32 * k;
+            lv[k] = i < la ? __ldcg(src + ref_line + (ptrdiff_t)stride * i) : 0;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = lane + 32 * k;
+            tv[k] = i < ta ? __ldcg(src + i + (ptrdiff_t)stride * ref_line) : 0;
+        }
+        if (lane < -ref_line) {                                           // the corner run, indices -1 .. ref_line
+            const int i = -1 - lane;
+            if (b.up_left) {
+                vl = __ldcg(src + ref_line + (ptrdiff_t)stride * i);
+                vt = __ldcg(src + i + (ptrdiff_t)stride * ref_line);
+            } else if (la) {
+                vl = vt = __ldcg(src + ref_line);
+            } else if (ta) {
+                vl = vt = __ldcg(src + (ptrdiff_t)stride * ref_line);
+            } else {
+                vl = vt = 1 << (bd - 1);
+            }
+        }
+        bool bad = vl == kSentinel || vt == kSentinel;
+#pragma unroll
+        for (int k = 0; k < 4; k++)
+            bad |= (lv[k] == kSentinel && lane + 32 * k < need_l) || (tv[k] == kSentinel && lane + 32 * k < need_t);
+        if (__any_sync(kFull, bad)) {
+            __nanosleep(backoff);
+            continue;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            const int i = lane + 32 * k;
+            if (i < la) left[i] = lv[k];
+            if (i < ta) top[i] = tv[k];
+        }
+        if (lane < -ref_line) {
+            left[-1 - lane] = vl;
+            top[-1 - lane] = vt;
+        }
+        break;
     }
     __syncwarp();
     {                                                                     // substitution of what is not there
@@ -343,8 +615,8 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
             interp = min(d50, d18) > thres;
         }
         if (mode != 50 && mode != 18) {
-            angle = VVC_INTRA_ANGLE[mode + 14];
-            const int inv = VVC_INTRA_INV_ANGLE[mode + 14];
+            angle = tb.angle[mode + 14];
+            const int inv = tb.inv_angle[mode + 14];
             uint16_t *mainr = mode >= 34 ? top : left, *side = mode >= 34 ? left : top;
             const int nm = mode >= 34 ? w : h, ns = mode >= 34 ? h : w, refn = mode >= 34 ? refw : refh;
             if (angle < 0) {                                              // project the side edge onto the main one
@@ -362,10 +634,16 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
 
     Store st;
     st.dst = src; st.dstride = stride; st.bd = bd;
-    st.ciip_w = (b.flags & VVCB200_IB_CIIP) ? b.ciip_weight : 0;
-    st.res = (b.flags & VVCB200_IB_RESIDUAL) ? a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0 : nullptr;
-    st.rstride = a.res_stride[c];
+    st.ciip_w = ciip ? b.ciip_weight : 0;
+    st.res = has_res ? reinterpret_cast<const int16_t *>(ws.stage_res) : nullptr;
+    st.inter = reinterpret_cast<const uint16_t *>(ws.stage_extra);
+    st.w = w;
     st.lscale = lscale;
+    const long long g1 = PROF_T();
+    stage_wait();                                                         // residual / inter prediction are in shared memory
+    __syncwarp();
+    PROF_ADD(5, g1 - g0);
+    PROF_ADD(6, PROF_T() - g1);
     const int n = w * h;
 
     if (is_mip) {                                                         // vvc_intra_template.c:707-836
@@ -374,7 +652,7 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
         const int in_size = 2 * bsz - (size_id == 2);
         const int nout = psz * psz;
         const bool tr = b.flags & VVCB200_IB_MIP_TRANSPOSED;
-        const uint8_t *m = VVC_MIP_MAT + VVC_MIP_OFF[size_id] + b.mip_mode * nout * in_size;
+        const uint8_t *m = tb.mip_mat + tb.mip_off[size_id] + b.mip_mode * nout * in_size;
         if (lane < 2 * bsz) {                                             // boundary down-sampling
             const int pass = lane >= bsz, i = lane - pass * bsz;
             const uint16_t *ref = pass ? left : top;
@@ -482,9 +760,9 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
 
     // angular (vvc_intra_template.c:838-1001): `along` runs with the prediction direction's axis, `cross` across it
     const bool vertical = mode >= 34;
-    const int inv = pdpc ? VVC_INTRA_INV_ANGLE[mode + 14] : 0, nscale = pdpc ? nscale_of(lw, lh, mode) : 0;
+    const int inv = pdpc ? tb.inv_angle[mode + 14] : 0, nscale = pdpc ? nscale_of(tb, lw, lh, mode) : 0;
     const uint16_t *main_ref = (vertical ? top : left) - (1 + ref_idx), *side = vertical ? left : top;
-    const int8_t *ftab = VVC_INTRA_LUMA_FILTER + interp * 128;
+    const int8_t *ftab = tb.luma_filter + interp * 128;
     for (int idx = lane; idx < n; idx += 32) {
         const int x = idx & (w - 1), y = idx >> lw;
         const int along = vertical ? y : x, cross = vertical ? x : y;
@@ -509,8 +787,15 @@ __device__ void predict_record(const IntraArgs &a, const VVCB200IntraBlock &b, W
     }
 }
 
+__device__ __forceinline__ int checked_load(const uint16_t *p, bool &bad)
+{
+    const unsigned v = __ldcg(p);
+    bad |= v == kSentinel;
+    return (int)v;
+}
+
 // ---- CCLM (vvc_intra_template.c:29-375): one record predicts Cb and Cr --------------------------------------------
-__device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int lane)
+__device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, bool has_marks)
 {
     const int bd = a.bd, w = b.w, h = b.h, x = b.x0, y = b.y0, x0 = x * 2, y0 = y * 2, mode = b.mode;
     const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
@@ -518,49 +803,50 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
     const uint16_t *luma = a.pic.p[0] + (size_t)y0 * ls + x0;
     const int cs[2] = { a.pic.stride[1], a.pic.stride[2] };
     uint16_t *dst[2] = { a.pic.p[1] + (size_t)y * cs[0] + x, a.pic.p[2] + (size_t)y * cs[1] + x };
-    const int mn = min(w, h);
-    int num[2];
-    if (mode == 81) {
-        num[0] = avail_t ? w : 0;
-        num[1] = avail_l ? h : 0;
-    } else {
-        num[0] = (avail_t && mode == 83) ? min(w + mn, (int)b.avail_top) : 0;
-        num[1] = (avail_l && mode == 82) ? min(h + mn, (int)b.avail_left) : 0;
-    }
-
-    // ---- wait: own luma block, luma neighbours under the down-sampling footprint, chroma neighbours of both planes
-    {
-        const int lux = x0 >> 2, luy = y0 >> 2, cux = x >> 2, cuy = y >> 1;
-        const int lnt = avail_t ? unit_count(x0, 2 * max(w, num[0]), 2) : 0;
-        const int lnl = avail_l ? unit_count(y0, 2 * max(h, num[1]), 2) : 0;
-        const int cnt_ = unit_count(x, num[0], 2), cnl = unit_count(y, num[1], 1);
-        const int lnx = unit_count(x0, 2 * w, 2), lny = unit_count(y0, 2 * h, 2);
-        for (;;) {
-            bool p = row_pending(a, 0, luy, lux, lnx, lane) | row_pending(a, 0, luy + lny - 1, lux, lnx, lane);
-            if (lnt) p |= row_pending(a, 0, luy - 1, lux, lnt, lane);
-            if (lnl) p |= col_pending(a, 0, lux - 1, luy, lnl, lane);
-            if (avail_t && avail_l) p |= row_pending(a, 0, luy - 1, lux - 1, 1, lane);
-            for (int c = 1; c <= 2; c++) {
-                if (cnt_) p |= row_pending(a, c, cuy - 1, cux, cnt_, lane);
-                if (cnl) p |= col_pending(a, c, cux - 1, cuy, cnl, lane);
-            }
-            if (!__any_sync(kFull, p))
-                break;
-            __nanosleep(64);
-        }
-        __threadfence();
-    }
-
-    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, lane) : 0;
-    const int16_t *res[2] = { nullptr, nullptr };
-    if (b.flags & VVCB200_IB_RESIDUAL)
-        for (int c = 0; c < 2; c++)
-            if (b.res_planes & (1 << c))
-                res[c] = a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x;
+    const CclmCounts kc = cclm_counts(b);
+    const int num[2] = { kc.num[0], kc.num[1] };
     const int n = w * h, lw = ilog2(w);
+    const int16_t *res[2] = { nullptr, nullptr };
+    if (b.flags & VVCB200_IB_RESIDUAL)                                    // residuals travel while the warp waits
+        for (int c = 0; c < 2; c++)
+            if (b.res_planes & (1 << c)) {
+                int16_t *sres = reinterpret_cast<int16_t *>(ws.stage_res) + c * n;
+                stage_block_async(sres, a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x, a.res_stride[c + 1], w, h, lane);
+                res[c] = sres;
+            }
+    if (has_marks) {
+        Span sp[kMaxSpans];
+        wait_spans(a, sp, cclm_deps(b, sp), lane);
+    }
+    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, has_marks, lane) : 0;
+    // the co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte pieces;
+    // the block's own luma is usually the last thing to arrive: poll its last row cheaply, then fetch and verify everything
+    uint16_t *win = reinterpret_cast<uint16_t *>(ws.stage_extra);
+    const int wx0 = avail_l ? -4 : 0, wy0 = avail_t ? -1 : 0, wpitch = 2 * w + 4;
+    if (avail_t || avail_l) {
+        const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+            bool bad = false;
+            for (int i = lane; i < 2 * w; i += 32)
+                bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
+            if (!__any_sync(kFull, bad)) {
+                for (int i = lane; i < per_row * rows; i += 32) {
+                    const int r = i / per_row, q = i - r * per_row;
+                    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
+                    bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
+                    *reinterpret_cast<uint2 *>(win + (r + 1 + wy0) * wpitch + 4 + wx0 + 4 * q) = v;
+                }
+                if (!__any_sync(kFull, bad))
+                    break;
+            }
+            __nanosleep(backoff);
+        }
+    }
+    stage_wait();
+    __syncwarp();
     auto emit = [&](int c, int i, int j, int v) {
         if (res[c]) {
-            int r = res[c][(size_t)j * a.res_stride[c + 1] + i];
+            int r = res[c][j * w + i];
             if (lscale)
                 r = scale_chroma_residual(r, lscale, bd);
             v = clip_pixel(v + r, bd);
@@ -573,7 +859,7 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
                 emit(c, idx & (w - 1), idx >> lw, 1 << (bd - 1));
         return;
     }
-#define L(dx, dy) ((int)__ldcg(luma + (dx) + (ptrdiff_t)ls * (dy)))
+#define L(dx, dy) checked_load(luma + (dx) + (ptrdiff_t)ls * (dy), bad)
     int ka[2] = { 0, 0 }, kb[2] = { 1 << (bd - 1), 1 << (bd - 1) }, kk[2] = { 0, 0 };
     if (num[0] || num[1]) {
         const int is4 = !avail_t || !avail_l || mode != 81;
@@ -584,6 +870,8 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
             cnt[i] = min(num[i], (1 + is4) << 1);
         }
         int v0 = 0, v1 = 0, v2 = 0;                                       // lane i gathers neighbour sample i
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {  // until none of the neighbours is a sentinel
+        bool bad = false;
         if (lane < cnt[0]) {
             const int pos = start[0] + lane * step[0], lx = pos * 2;
             const int xl = (lx || avail_l) ? lx - 1 : lx;
@@ -595,8 +883,8 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
             } else {
                 v0 = (L(xl, -1) + 2 * L(lx, -1) + L(lx + 1, -1) + 2) >> 2; // one luma line above a CTU boundary
             }
-            v1 = __ldcg(dst[0] + pos - cs[0]);
-            v2 = __ldcg(dst[1] + pos - cs[1]);
+            v1 = checked_load(dst[0] + pos - cs[0], bad);
+            v2 = checked_load(dst[1] + pos - cs[1], bad);
         } else if (lane < cnt[0] + cnt[1]) {
             const int pos = start[1] + (lane - cnt[0]) * step[1], ly = pos * 2;
             if (a.collocated) {
@@ -605,8 +893,12 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
             } else {
                 v0 = (L(-3, ly) + L(-3, ly + 1) + 2 * L(-2, ly) + 2 * L(-2, ly + 1) + L(-1, ly) + L(-1, ly + 1) + 4) >> 3;
             }
-            v1 = __ldcg(dst[0] - 1 + (ptrdiff_t)pos * cs[0]);
-            v2 = __ldcg(dst[1] - 1 + (ptrdiff_t)pos * cs[1]);
+            v1 = checked_load(dst[0] - 1 + (ptrdiff_t)pos * cs[0], bad);
+            v2 = checked_load(dst[1] - 1 + (ptrdiff_t)pos * cs[1], bad);
+        }
+        if (!__any_sync(kFull, bad))
+            break;
+        __nanosleep(backoff);
         }
         int sel[3][4];
 #pragma unroll
@@ -661,6 +953,7 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
             }
         }
     }
+#define W(dx, dy) ((int)win[((dy) + 1) * wpitch + 4 + (dx)])
     for (int idx = lane; idx < n; idx += 32) {                            // down-sampled luma -> both chroma planes
         const int i = idx & (w - 1), j = idx >> lw;
         const int lx = 2 * i, ly = 2 * j;
@@ -668,22 +961,37 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, int 
         int ds;
         if (a.collocated) {
             const int yt = (j || avail_t) ? ly - 1 : ly;
-            ds = (L(xl, ly) + L(lx, yt) + 4 * L(lx, ly) + L(lx + 1, ly) + L(lx, ly + 1) + 4) >> 3;
+            ds = (W(xl, ly) + W(lx, yt) + 4 * W(lx, ly) + W(lx + 1, ly) + W(lx, ly + 1) + 4) >> 3;
         } else {
-            ds = (L(xl, ly) + L(xl, ly + 1) + 2 * L(lx, ly) + 2 * L(lx, ly + 1) + L(lx + 1, ly) + L(lx + 1, ly + 1) + 4) >> 3;
+            ds = (W(xl, ly) + W(xl, ly + 1) + 2 * W(lx, ly) + 2 * W(lx, ly + 1) + W(lx + 1, ly) + W(lx + 1, ly + 1) + 4) >> 3;
         }
         for (int c = 0; c < 2; c++)
             emit(c, i, j, clip_pixel(((ds * ka[c]) >> kk[c]) + kb[c], bd));
     }
+#undef W
 #undef L
 }
 
 __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
 {
-    __shared__ WarpScratch s_ws[kWarps];
+    extern __shared__ __align__(16) uint8_t s_dyn[];
+    __shared__ CtaTables tb;
     const int lane = threadIdx.x & 31;
-    WarpScratch &ws = s_ws[threadIdx.x >> 5];
+    WarpScratch &ws = reinterpret_cast<WarpScratch *>(s_dyn)[threadIdx.x >> 5];
+    for (int i = threadIdx.x; i < 95; i += blockDim.x) {
+        tb.angle[i] = VVC_INTRA_ANGLE[i];
+        tb.inv_angle[i] = VVC_INTRA_INV_ANGLE[i];
+    }
+    for (int i = threadIdx.x; i < 256; i += blockDim.x)
+        tb.luma_filter[i] = VVC_INTRA_LUMA_FILTER[i];
+    for (int i = threadIdx.x; i < 4736; i += blockDim.x)
+        tb.mip_mat[i] = VVC_MIP_MAT[i];
+    if (threadIdx.x < 4)
+        tb.mip_off[threadIdx.x] = VVC_MIP_OFF[threadIdx.x];
+    __syncthreads();
+    const bool has_marks = a.ticket[1] != 0;                              // written by the pre-pass
     for (;;) {
+        const long long t0 = PROF_T();
         int t = 0;
         if (lane == 0)
             t = atomicAdd(a.ticket, 1);
@@ -691,39 +999,33 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
         if (t >= a.n)
             break;
         const VVCB200IntraBlock b = load_record(a.blocks + t);
+        const long long t1 = PROF_T();
         if (b.mode >= 81) {
-            cclm_record(a, b, lane);
+            cclm_record(a, b, ws, lane, has_marks);
         } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
             // ISP: the sub-partitions of the coding block one after the other, each predicted from its reconstructed
             // predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit
-            const bool hor = b.w == b.cb_w;
-            const int n_parts = hor ? b.cb_h / b.h : b.cb_w / b.w;
+            const int n_parts = isp_parts(b);
             for (int k = 0; k < n_parts; k++) {
-                VVCB200IntraBlock s = b;
-                if (hor) {
-                    s.y0 += k * b.h;
-                    s.avail_left = max((int)b.avail_left - k * b.h, 0);
-                    if (k) { s.avail_top = b.w; s.up_left = b.avail_left > 0; }
-                } else {
-                    s.x0 += k * b.w;
-                    s.avail_top = max((int)b.avail_top - k * b.w, 0);
-                    if (k) { s.avail_left = b.h; s.up_left = b.avail_top > 0; }
-                }
-                predict_record(a, s, ws, lane, k ? (hor ? 1 : 2) : 0);
-                __threadfence();                                          // the next sub-partition reads these samples
+                VVCB200IntraBlock s;
+                const int skip = isp_part(b, k, s);
+                predict_record(a, tb, s, ws, lane, has_marks, skip);
                 __syncwarp();
             }
         } else {
-            predict_record(a, b, ws, lane);
+            predict_record(a, tb, b, ws, lane, has_marks);
         }
-        __threadfence();                                                  // samples before marks
+        const long long t2 = PROF_T();
+        if (in_place(b)) {                                                // samples before marks
+            fence_gpu();
+            __syncwarp();
+            set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 2, lane);
+        }
         __syncwarp();
-        int ew, eh;
-        record_extent(b, ew, eh);
-        set_marks(a, b.c_idx, b.x0, b.y0, ew, eh, 0, lane);
-        if (b.mode >= 81)
-            set_marks(a, 2, b.x0, b.y0, ew, eh, 0, lane);
-        __syncwarp();
+        PROF_ADD(0, t1 - t0);
+        PROF_ADD(1, t2 - t1);
+        PROF_ADD(2, PROF_T() - t2);
+        PROF_ADD(3, 1);
     }
 }
 
@@ -760,32 +1062,80 @@ extern "C" size_t vvcb200_intra_scratch_bytes(int width, int height)
     return scratch_layout(width, height).total;
 }
 
+#include <stdlib.h>
+#include <vector>
+
 extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
-                                      VVCB200IntraBlock *out)
+                                      int ctb_log2_size, int width, int height, VVCB200IntraBlock *out, int32_t *n_levels)
 {
-    if (!in || !ctu_first || !out || ctus_w <= 0 || ctus_h <= 0) {
+    if (!in || !ctu_first || !out || ctus_w <= 0 || ctus_h <= 0 || ctb_log2_size < 5 || ctb_log2_size > 7 ||
+        width <= 0 || height <= 0 || width > (ctus_w << ctb_log2_size) || height > (ctus_h << ctb_log2_size)) {
         set_error("vvcb200_intra_schedule: bad arguments");
         return VVCB200_ERR_ARG;
     }
-    size_t o = 0;
-    for (int d = 0; d <= ctus_w - 1 + 2 * (ctus_h - 1); d++) {
-        // CTUs of this anti-diagonal: (d - 2y, y); round-robin over them so that a window of consecutive tickets
-        // spans every CTU that can run now
-        const int y_lo = d - (ctus_w - 1) > 0 ? (d - (ctus_w - 1) + 1) / 2 : 0;
-        const int y_hi = d / 2 < ctus_h - 1 ? d / 2 : ctus_h - 1;
-        uint32_t longest = 0;
-        for (int y = y_lo; y <= y_hi; y++) {
-            const int rs = y * ctus_w + d - 2 * y;
-            const uint32_t len = ctu_first[rs + 1] - ctu_first[rs];
-            longest = len > longest ? len : longest;
+    // Depth of every record in the dependency graph: 1 + the largest depth among the records that wrote the units it
+    // waits for (the same runs the kernel polls).  Records come CTU by CTU in decoding order, so every writer a record
+    // depends on has been seen.  Sorting by depth is a topological order in which a window of consecutive tickets holds
+    // the records that are ready now anywhere in the picture.
+    const uint32_t n = ctu_first[ctus_w * ctus_h];
+    const int uw = ((ctus_w << ctb_log2_size) >> 2) + 2;                  // one guard column / row on the low side
+    const int uh[3] = { ((ctus_h << ctb_log2_size) >> 2) + 2, ((ctus_h << ctb_log2_size) >> 2) + 2,
+                        ((ctus_h << ctb_log2_size) >> 2) + 2 };          // chroma: half the samples, 2-row units
+    std::vector<int32_t> map[3];
+    for (int c = 0; c < 3; c++)
+        map[c].assign((size_t)uw * uh[c], 0);
+    std::vector<int32_t> depth(n);
+    auto at = [&](int c, int ux, int uy) -> int32_t & { return map[c][(size_t)(uy + 1) * uw + ux + 1]; };
+    int32_t max_depth = 0;
+    Span sp[kMaxSpans + 3];
+    for (uint32_t i = 0; i < n; i++) {
+        const VVCB200IntraBlock &b = in[i];
+        int32_t d = 0;
+        auto take = [&](int cnt) {
+            for (int k = 0; k < cnt; k++)
+                for (int j = 0; j < sp[k].n; j++) {
+                    const int32_t v = sp[k].horizontal ? at(sp[k].c, sp[k].ux + j, sp[k].uy) : at(sp[k].c, sp[k].ux, sp[k].uy + j);
+                    d = v > d ? v : d;
+                }
+        };
+        if (b.c_idx > 2 || (b.x0 >> 2) >= uw - 2 || (b.y0 >> unit_shift(b.c_idx)) >= uh[b.c_idx] - 2) {
+            set_error("vvcb200_intra_schedule: record %u lies outside the picture", i);
+            return VVCB200_ERR_ARG;
         }
-        for (uint32_t k = 0; k < longest; k++)
-            for (int y = y_lo; y <= y_hi; y++) {
-                const int rs = y * ctus_w + d - 2 * y;
-                if (ctu_first[rs] + k < ctu_first[rs + 1])
-                    out[o++] = in[ctu_first[rs] + k];
+        take(vpdu_deps(b, ctb_log2_size, width, height, sp));
+        if (b.mode >= 81) {
+            take(cclm_deps(b, sp));
+        } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
+            const int parts = isp_parts(b);
+            for (int k = 0; k < parts; k++) {
+                VVCB200IntraBlock s;
+                const int skip = isp_part(b, k, s);
+                take(predict_deps(s, skip, sp));
             }
+        } else {
+            take(predict_deps(b, 0, sp));
+        }
+        depth[i] = ++d;
+        max_depth = d > max_depth ? d : max_depth;
+        const bool isp = (b.flags & VVCB200_IB_ISP) && !b.c_idx;
+        const int w = isp ? b.cb_w : b.w, h = isp ? b.cb_h : b.h;
+        for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {
+            const int s = unit_shift(c);
+            const int ux = b.x0 >> 2, uy = b.y0 >> s, nx = unit_count(b.x0, w, 2), ny = unit_count(b.y0, h, s);
+            for (int y = 0; y < ny; y++)
+                for (int x = 0; x < nx; x++)
+                    at(c, ux + x, uy + y) = d;
+        }
     }
+    std::vector<uint32_t> start(max_depth + 2, 0);                        // counting sort by depth, stable
+    for (uint32_t i = 0; i < n; i++)
+        start[depth[i] + 1]++;
+    for (int32_t d = 1; d <= max_depth + 1; d++)
+        start[d] += start[d - 1];
+    for (uint32_t i = 0; i < n; i++)
+        out[start[depth[i]]++] = in[i];
+    if (n_levels)
+        *n_levels = max_depth;
     return 0;
 }
 
@@ -827,10 +1177,20 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         a.mpitch[c] = l.pitch[c];
     }
     cudaStream_t s = (cudaStream_t)stream;
+    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, l.total, s));                  // ticket counter, in-place flag, marks
     intra_mark_kernel<<<(n + 3) / 4, 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
-    const int ctas = min((n + kWarps - 1) / kWarps, sm_count() * 4);
-    intra_kernel<<<ctas, kWarps * 32, 0, s>>>(a);
+    static const int per_sm = getenv("VVCB200_INTRA_CTAS_PER_SM") ? atoi(getenv("VVCB200_INTRA_CTAS_PER_SM")) : 4;   // TUNING, temporary
+    const int ctas = min((n + kWarps - 1) / kWarps, sm_count() * per_sm);
+    const size_t smem = sizeof(WarpScratch) * kWarps;
+    static bool attr_set[64];                                             // per device: allow > 48 KB of shared memory
+    int dev = 0;
+    VVC_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        VVC_CUDA(cudaFuncSetAttribute(intra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set[dev] = true;
+    }
+    intra_kernel<<<ctas, kWarps * 32, smem, s>>>(a);
     VVC_LAUNCH_CHECK();
     return 0;
 }
@@ -893,3 +1253,15 @@ extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB
     VVC_CUDA(cudaMemsetAsync(ptr, 0, need, (cudaStream_t)stream));
     return vvcb200_intra_picture(pic, d_residual, d_blocks, n, params, ptr, stream);
 }
+
+#ifdef VVC_INTRA_PROFILE
+extern "C" VVCB200_API int vvcb200_intra_profile(unsigned long long *out8, int reset)
+{
+    VVC_CUDA(cudaMemcpyFromSymbol(out8, vvcb200::g_prof, sizeof(unsigned long long) * 8));
+    if (reset) {
+        unsigned long long z[8] = { 0 };
+        VVC_CUDA(cudaMemcpyToSymbol(vvcb200::g_prof, z, sizeof(z)));
+    }
+    return 0;
+}
+#endif

@@ -94,14 +94,16 @@ def intra_scratch_bytes(width, height):
     return int(f(int(width), int(height)))
 
 
-def intra_schedule(blocks, ctu_first, ctus_w, ctus_h):
-    """vvcb200_intra_schedule: per-CTU decoding-order records -> wavefront order (host helper, no GPU involved)."""
+def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, want_levels=False):
+    """vvcb200_intra_schedule: per-CTU decoding-order records -> dependency-depth order (host helper, no GPU involved)."""
     blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
     ctu_first = np.ascontiguousarray(ctu_first, np.uint32)
     assert len(ctu_first) == ctus_w * ctus_h + 1 and ctu_first[-1] == len(blocks)
     out = np.zeros(len(blocks), abi.IB_DTYPE)
-    check(load().vvcb200_intra_schedule(_ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), _ptr(out)))
-    return out
+    levels = C.c_int32(0)
+    check(load().vvcb200_intra_schedule(_ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), int(ctb_log2), int(width),
+                                        int(height), _ptr(out), C.byref(levels)))
+    return (out, int(levels.value)) if want_levels else out
 
 
 def intra_picture(pic, residual, blocks, n, params, scratch, stream=None):

@@ -491,7 +491,7 @@ def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slic
                        tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "ciip", "mts", "ts", "lfnst", "joint",
                               "dep_quant", "scaling"), mean_log2=mean_log2,
                        inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"),
-                       inter_kinds=(CU_REGULAR,) * 7 + (CU_AFFINE,) * 2 + (CU_GPM,), lmcs=lmcs)
+                       inter_kinds=(CU_REGULAR,) * 7 + (CU_AFFINE,) * 2 + (CU_GPM,), lmcs=lmcs, ciip_share=0.1)
     db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
     lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
     out = dict(inter=rp["inter"], residual=rp["residual"], intra=rp["intra"], ref=rp["ref"], deblock=db, lf=lf,
@@ -672,7 +672,7 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
@@ -795,7 +795,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 qp_y, qp_c = int(rng.integers(14, 60)), int(rng.integers(14, 60))
                 ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
                 if not intra:
-                    ciip = "ciip" in tools and rng.random() < 0.3
+                    ciip = "ciip" in tools and rng.random() < ciip_share
                     tu = np.zeros(1, REF_TU_DTYPE)
                     tu["x0"], tu["y0"], tu["w"], tu["h"] = x, y, w, h
                     tu["coded_flag"] = coded
@@ -886,7 +886,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     cu["mip_mode"] = int(rng.integers(0, (16, 8, 6)[size_id]))
                     mode_y = 0
                 elif "mrl" in tools and y0b > 0 and mode_y != 0 and r < 0.2:
-                    ref_idx = int(rng.choice([1, 3]))
+                    ref_idx = int(rng.choice([1, 2]))      # what ff_vvc_intra_luma_ref_idx() can return (vvc_cabac.c:1282-1290)
                 elif "isp" in tools and w * h > 16 and r < 0.4:
                     isp = int(rng.integers(1, 3))            # 1 horizontal, 2 vertical split (vvc_ctu.h:113-117)
                 elif "bdpcm" in tools and w <= 32 and h <= 32 and r < 0.55:

@@ -347,7 +347,7 @@ typedef struct VVCB200IntraBlock {
     uint8_t  w, h;              /* size in samples of that plane (1..64)                                                  */
     uint8_t  c_idx;             /* 0 Y, 1 Cb, 2 Cr; a CCLM record has c_idx 1 and covers both chroma planes               */
     int8_t   mode;              /* intra mode after wide-angle mapping (-14..80, vvc_intra.c:693-714); 81..83 = LT/L/T CCLM */
-    uint8_t  ref_idx;           /* cu->intra_luma_ref_idx as the reference stores it (0, 1 or 3)                          */
+    uint8_t  ref_idx;           /* cu->intra_luma_ref_idx as the reference stores it (0, 1 or 2; vvc_cabac.c:1282-1290)    */
     uint8_t  flags;             /* VVCB200_IB_*                                                                           */
     uint8_t  mip_mode;          /* intra_mip_mode                                                                         */
     uint8_t  up_left;           /* lc->na.cand_up_left                                                                    */
@@ -382,22 +382,27 @@ typedef struct VVCB200IntraParams {
  * residual of every inter block).  One launch; warps draw records from a ticket counter in array order and each
  * record waits, on per-4x4 "pending" marks in `d_scratch`, for exactly the neighbour samples it reads.  The array order
  * must therefore be topological (every record after the records it reads from): the decoding order is one, and
- * vvcb200_intra_schedule() builds the order the engine prefers (CTU anti-diagonals x + 2y of vvc_thread.c:161,
- * CTUs of a diagonal interleaved) from per-CTU decoding-order records.
+ * vvcb200_intra_schedule() builds the order the engine prefers from per-CTU decoding-order records: sorted by depth
+ * in the dependency graph, so that consecutive tickets are the records that can run now anywhere in the picture
+ * (a finer-grained form of the CTU wavefront of vvc_thread.c:156-184).
  * d_residual: int16 residual planes written by vvcb200_residual_batch for TBs flagged VVCB200_TB_TO_RESIDUAL (may be
  * NULL if no record has VVCB200_IB_RESIDUAL).
  * Luma-dependent chroma residual scaling (sh_lmcs_used_flag && ph_chroma_residual_scale_flag): the factor depends on
  * reconstructed luma, so the host cannot put it into VVCB200TransformBlock.lmcs_scale.  Instead every chroma TB of such
  * a picture (w * h > 4) is flagged VVCB200_TB_TO_RESIDUAL without VVCB200_TB_LMCS_SCALE, and its block gets a record
  * here flagged VVCB200_IB_RESIDUAL | VVCB200_IB_LMCS_SCALE — an intra record, or VVCB200_IB_ADD_ONLY for an inter unit.
- * d_scratch: vvcb200_intra_scratch_bytes() bytes of device memory, zeroed once after allocation; a successful call
- * leaves the marks zero again.  Two calls may not share a scratch buffer concurrently.
+ * d_scratch: vvcb200_intra_scratch_bytes() bytes of device memory (ticket counter + marks of the blocks that are
+ * rewritten in place, CIIP and add-only); the call clears it itself.  Two calls may not share a scratch buffer
+ * concurrently.  Samples of pure intra blocks need no marks: the call first fills them with 0xffff ("not yet
+ * reconstructed"), so bit depths above 15 are not supported by this entry point.
  */
 VVCB200_API size_t vvcb200_intra_scratch_bytes(int width, int height /* luma samples */);
 /* Host helper: `in` holds the records of CTU i (raster index) at ctu_first[i] .. ctu_first[i + 1], in decoding order;
- * `out` (same length, must not alias) receives them in wavefront order. */
+ * `out` (same length, must not alias) receives them in dependency-depth order.  width / height: luma samples.
+ * n_levels (may be NULL): the length of the longest dependency chain, i.e. the number of serial steps of the picture. */
 VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
-                                       VVCB200IntraBlock *out);
+                                       int ctb_log2_size, int width, int height, VVCB200IntraBlock *out,
+                                       int32_t *n_levels);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
                                       const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);

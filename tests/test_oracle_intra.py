@@ -63,13 +63,13 @@ def test_schedule_is_a_topological_permutation(seed, w, h, ctb):
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, intra_fraction=0.8)
     ia = pic["intra"]
     cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
-    order = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch)
+    order = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h)
     assert sorted(order.tobytes()[i:i + 28] for i in range(0, order.nbytes, 28)) == \
         sorted(ia["blocks"].tobytes()[i:i + 28] for i in range(0, ia["blocks"].nbytes, 28))
     a, b = _port(pic), _port(pic, order)
     for c in range(3):
         assert np.array_equal(a[c], b[c])
-    if cw > 2 and ch > 1:                                   # really a wavefront: CTU (0, 1) is drawn before the end of row 0
+    if cw > 2 and ch > 1:                                   # not the decoding order: a later CTU row starts before row 0 ends
         first_row1 = next(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 1)
         last_row0 = max(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 0)
         assert first_row1 < last_row0

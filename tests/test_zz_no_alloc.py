@@ -27,7 +27,7 @@ def _stage(pic):
     levels = torch.from_numpy(rs["levels"]).cuda()
     lib.residual_batch(dpl, levels, tbs, len(rs["tbs"]), rs["params"], residual=lib.device_planes(res))
     w, h, ctb = pic["width"], pic["height"], pic["ctb_log2"]
-    recs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb)
+    recs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb, ctb, w, h)
     torch.cuda.synchronize()
     return dev, res, torch.from_numpy(recs.view(np.uint8).reshape(-1)).cuda(), len(recs)
 

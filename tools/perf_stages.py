@@ -1,0 +1,100 @@
+#!/usr/bin/env python
+"""Stage-level timing experiments on the bench picture (GPU only; development tool, not part of the product).
+
+    python tools/perf_stages.py [--workload 4k|1080p] [--intra-fraction F]
+
+Times vvcb200_inter_batch on subsets of the prediction records (by tool), the residual, intra and filter stages,
+each as the mean of `reps` launches bracketed by CUDA events."""
+import argparse
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+from ffmpeg_b200 import abi, lib  # noqa: E402
+from tests import util  # noqa: E402
+
+
+def timed(torch, fn, reps=20):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(reps):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / reps
+
+
+def main():
+    import torch
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--workload", default="4k")
+    ap.add_argument("--intra-fraction", type=float, default=0.1)
+    ap.add_argument("--seed", type=int, default=2026)
+    args = ap.parse_args()
+    width, height = bench.WORKLOADS[args.workload]
+    pic = bench.make_picture(args.seed, width, height, args.intra_fraction)
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+
+    def dev(a):
+        return torch.from_numpy(np.ascontiguousarray(a).view(np.uint8).reshape(-1)).cuda()
+
+    refs = [util.to_device_planes(r, torch) for r in it["refs"]]
+    refs_p = [lib.device_planes(r) for r in refs]
+    cur = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
+    cur_p = lib.device_planes(cur)
+    prof = dev(it["prof"]) if len(it["prof"]) else None
+    b = it["blocks"]
+    f = b["flags"]
+    subsets = {
+        "all": np.ones(len(b), bool),
+        "regular": (f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY)) == 0,
+        "regular_plain": (f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY | abi.PB_DMVR | abi.PB_BDOF)) == 0,
+        "dmvr": (f & abi.PB_DMVR) != 0,
+        "bdof_only": ((f & abi.PB_BDOF) != 0) & ((f & abi.PB_DMVR) == 0),
+        "affine_luma": (f & abi.PB_LUMA_ONLY) != 0,
+        "affine_chroma": (f & abi.PB_CHROMA_ONLY) != 0,
+        "gpm": (f & abi.PB_GPM) != 0,
+    }
+    for name, m in subsets.items():
+        sub = np.ascontiguousarray(b[m])
+        if not len(sub):
+            continue
+        p = abi.InterParams.from_buffer_copy(bytes(it["params"]))
+        p.n_w16, p.n_w8 = int((sub["w"] == 16).sum()), int((sub["w"] == 8).sum())
+        d = dev(sub)
+        ms = timed(torch, lambda: lib.inter_batch(cur_p, refs_p, d, len(sub), p, prof=prof))
+        area = int((sub["w"].astype(np.int64) * sub["h"]).sum())
+        print("inter %-14s %7d records %9d luma-samples  %.4f ms  (%.2f ns/record)" % (name, len(sub), area, ms, 1e6 * ms / len(sub)))
+
+    res = [torch.zeros_like(t) for t in cur]
+    res_p = lib.device_planes(res)
+    tbs, levels = dev(rs["tbs"]), dev(rs["levels"])
+    ms = timed(torch, lambda: lib.residual_batch(cur_p, levels, tbs, len(rs["tbs"]), rs["params"], residual=res_p))
+    print("residual %d TBs  %.4f ms; classes %s" % (len(rs["tbs"]), ms, list(rs["params"].n_class)))
+    ctb = pic["ctb_log2"]
+    cw, ch = (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb
+    marks = torch.zeros(lib.intra_scratch_bytes(width, height), dtype=torch.uint8, device="cuda")
+    for label, recs in (("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height)), ("decoding order", ia["blocks"])):
+        d = dev(recs)
+        ms = timed(torch, lambda: lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks))
+        print("intra %-15s %d records  %.4f ms" % (label, len(recs), ms))
+        if hasattr(lib.load(), "vvcb200_intra_profile"):
+            import ctypes as C
+            buf = (C.c_ulonglong * 8)()
+            lib.load().vvcb200_intra_profile(buf, 1)                      # reset
+            lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks)
+            torch.cuda.synchronize()
+            lib.load().vvcb200_intra_profile(buf, 1)
+            n = max(1, buf[3])
+            print("   per record (cycles): ticket+load %.0f, body %.0f (of which waiting %.0f, edge gather %.0f, stage wait %.0f), "
+                  "publish %.0f; pre-wait %.0f; records %d" % (buf[0] / n, buf[1] / n, buf[4] / n, buf[5] / n, buf[6] / n, buf[2] / n, buf[7] / n, buf[3]))
+
+
+if __name__ == "__main__":
+    main()
