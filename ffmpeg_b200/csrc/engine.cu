@@ -60,17 +60,33 @@ struct DeviceGuard {
 
 }  // namespace
 
+// Device copies of one picture's host descriptor batches.  Two sets alternate from picture to picture so that the
+// uploads of picture n + 1 (copy stream) overlap the kernels of picture n (compute stream).
+struct StageSet {
+    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks;
+    VVCB200IntraBlock *h_order = nullptr;  // pinned: the picture's intra records in scheduled order
+    size_t h_order_cap = 0;
+    cudaEvent_t uploaded = nullptr;    // last upload into this set (recorded on the upload stream)
+    cudaEvent_t consumed = nullptr;    // last kernel that read this set (recorded on the compute stream)
+    bool in_use = false;
+};
+
 struct VVCB200Ctx {
     int device = 0;
     int width = 0, height = 0, bit_depth = 10, hshift = 1, vshift = 1;
-    cudaStream_t stream = nullptr;
+    cudaStream_t stream = nullptr;     // compute
+    cudaStream_t h2d = nullptr;        // descriptor uploads
+    cudaStream_t d2h = nullptr;        // picture downloads
     std::vector<DevPicture> dpb;   // reference pictures + the picture under reconstruction
+    std::vector<cudaEvent_t> downloaded;   // per DPB slot: last download of that slot (d2h stream)
+    std::vector<char> download_pending;
+    cudaEvent_t computed = nullptr;    // scratch event: "compute stream got here"
     DevPicture scratch;            // SAO output / ALF input
     DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
-    std::vector<VVCB200IntraBlock> intra_order;   // host: the picture's intra records in wavefront order
     int cur = 0;
-    // per-stage device copies of the host descriptor batches
-    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks, intra_marks;
+    StageSet sets[2];
+    int set = 0;
+    DevBuffer intra_marks;
 };
 
 namespace {
@@ -102,11 +118,35 @@ DevPicture *slot_of(VVCB200Ctx *c, int slot)
     return slot < (int)c->dpb.size() ? &c->dpb[slot] : nullptr;
 }
 
+// Host -> device copy of a descriptor batch on the upload stream.  A buffer that has to grow is only reallocated after
+// the kernels still reading its set have finished (cudaFree would wait for them anyway, but on the whole device).
 int upload(VVCB200Ctx *c, DevBuffer &b, const void *host, size_t bytes)
 {
+    if (bytes > b.cap) {
+        VVC_CUDA(cudaStreamSynchronize(c->stream));
+        VVC_CUDA(cudaStreamSynchronize(c->h2d));
+    }
     if (int r = b.reserve(bytes))
         return r;
-    VVC_CUDA(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, c->stream));
+    VVC_CUDA(cudaMemcpyAsync(b.p, host, bytes, cudaMemcpyHostToDevice, c->h2d));
+    return 0;
+}
+
+// the compute stream may read the current set once everything uploaded so far has arrived
+int uploads_visible(VVCB200Ctx *c)
+{
+    StageSet &s = c->sets[c->set];
+    VVC_CUDA(cudaEventRecord(s.uploaded, c->h2d));
+    VVC_CUDA(cudaStreamWaitEvent(c->stream, s.uploaded, 0));
+    return 0;
+}
+
+// the current set is being read by what the compute stream holds now
+int set_consumed(VVCB200Ctx *c)
+{
+    StageSet &s = c->sets[c->set];
+    VVC_CUDA(cudaEventRecord(s.consumed, c->stream));
+    s.in_use = true;
     return 0;
 }
 
@@ -152,9 +192,20 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     c->height = height;
     c->bit_depth = bit_depth;
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->computed, cudaEventDisableTiming);
+    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
+        e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].consumed, cudaEventDisableTiming);
+    }
+    c->downloaded.assign(dpb_size, nullptr);
+    c->download_pending.assign(dpb_size, 0);
+    for (int i = 0; i < dpb_size && e == cudaSuccess; i++)
+        e = cudaEventCreateWithFlags(&c->downloaded[i], cudaEventDisableTiming);
     if (e != cudaSuccess) {
-        delete c;
-        return cuda_fail(e, "cudaStreamCreate", __FILE__, __LINE__);
+        vvcb200_ctx_destroy(c);
+        return cuda_fail(e, "stream / event creation", __FILE__, __LINE__);
     }
     c->dpb.resize(dpb_size);
     int r = alloc_picture(c, &c->scratch);
@@ -173,12 +224,24 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     if (!c)
         return;
     DeviceGuard g(c->device);
-    if (c->stream)
-        cudaStreamSynchronize(c->stream);
-    DevBuffer *bufs[] = { &c->levels, &c->tbs, &c->blocks, &c->refined, &c->prof, &c->lut_fwd, &c->lut_inv, &c->db_tables, &c->sao, &c->alf,
-                          &c->alf_params, &c->iblocks, &c->intra_marks };
-    for (DevBuffer *b : bufs)
-        b->release();
+    for (cudaStream_t st : { c->stream, c->h2d, c->d2h })
+        if (st)
+            cudaStreamSynchronize(st);
+    for (StageSet &ss : c->sets) {
+        DevBuffer *bufs[] = { &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
+                              &ss.sao, &ss.alf, &ss.alf_params, &ss.iblocks };
+        for (DevBuffer *b : bufs)
+            b->release();
+        if (ss.h_order) cudaFreeHost(ss.h_order);
+        if (ss.uploaded) cudaEventDestroy(ss.uploaded);
+        if (ss.consumed) cudaEventDestroy(ss.consumed);
+    }
+    c->intra_marks.release();
+    for (cudaEvent_t ev : c->downloaded)
+        if (ev)
+            cudaEventDestroy(ev);
+    if (c->computed)
+        cudaEventDestroy(c->computed);
     for (DevPicture &p : c->dpb)
         if (p.base)
             cudaFree(p.base);
@@ -186,8 +249,9 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
         cudaFree(c->scratch.base);
     if (c->residual.base)
         cudaFree(c->residual.base);
-    if (c->stream)
-        cudaStreamDestroy(c->stream);
+    for (cudaStream_t st : { c->stream, c->h2d, c->d2h })
+        if (st)
+            cudaStreamDestroy(st);
     delete c;
 }
 
@@ -195,7 +259,14 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
 {
     if (!c)
         return VVCB200_ERR_ARG;
+    DeviceGuard g(c->device);
+    VVC_CUDA(cudaStreamSynchronize(c->h2d));
     VVC_CUDA(cudaStreamSynchronize(c->stream));
+    VVC_CUDA(cudaStreamSynchronize(c->d2h));
+    for (char &p : c->download_pending)
+        p = 0;
+    for (StageSet &ss : c->sets)
+        ss.in_use = false;
     return 0;
 }
 
@@ -234,7 +305,16 @@ int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
         set_error("vvcb200_pic_begin: bad context or slot %d", slot);
         return VVCB200_ERR_ARG;
     }
+    DeviceGuard g(c->device);
     c->cur = slot;
+    c->set ^= 1;
+    StageSet &s = c->sets[c->set];
+    if (s.in_use)                         // uploads of this picture must not overtake the kernels of the picture before last
+        VVC_CUDA(cudaStreamWaitEvent(c->h2d, s.consumed, 0));
+    if (c->download_pending[slot]) {      // the slot's previous content is still on its way to the host
+        VVC_CUDA(cudaStreamWaitEvent(c->stream, c->downloaded[slot], 0));
+        c->download_pending[slot] = 0;
+    }
     return 0;
 }
 
@@ -260,9 +340,14 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    const int idx = slot < 0 ? c->cur : slot;
+    VVC_CUDA(cudaEventRecord(c->computed, c->stream));
+    VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->computed, 0));
     for (int i = 0; i < 3; i++)
         VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
-                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->stream));
+                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->d2h));
+    VVC_CUDA(cudaEventRecord(c->downloaded[idx], c->d2h));
+    c->download_pending[idx] = 1;
     return 0;
 }
 
@@ -284,13 +369,14 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
         }
     }
     DeviceGuard g(c->device);
-    if (int r = upload(c, c->blocks, blocks, (size_t)n * sizeof(*blocks)))
+    StageSet &S = c->sets[c->set];
+    if (int r = upload(c, S.blocks, blocks, (size_t)n * sizeof(*blocks)))
         return r;
     const uint16_t *d_lut = nullptr;
     if (lmcs_fwd_lut) {
-        if (int r = upload(c, c->lut_fwd, lmcs_fwd_lut, sizeof(uint16_t) << c->bit_depth))
+        if (int r = upload(c, S.lut_fwd, lmcs_fwd_lut, sizeof(uint16_t) << c->bit_depth))
             return r;
-        d_lut = (const uint16_t *)c->lut_fwd.p;
+        d_lut = (const uint16_t *)S.lut_fwd.p;
     }
     VVCB200Planes refs[16];
     const int n_refs = (int)c->dpb.size() < 16 ? (int)c->dpb.size() : 16;
@@ -304,18 +390,24 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
             }
     int32_t *d_mv = nullptr;
     if (refined_mv) {
-        if (int r = c->refined.reserve((size_t)n * 4 * sizeof(int32_t)))
+        if ((size_t)n * 4 * sizeof(int32_t) > S.refined.cap)
+            VVC_CUDA(cudaStreamSynchronize(c->stream));
+        if (int r = S.refined.reserve((size_t)n * 4 * sizeof(int32_t)))
             return r;
-        d_mv = (int32_t *)c->refined.p;
+        d_mv = (int32_t *)S.refined.p;
     }
     const VVCB200ProfTable *d_prof = nullptr;
     if (prof && n_prof > 0) {
-        if (int r = upload(c, c->prof, prof, (size_t)n_prof * sizeof(*prof)))
+        if (int r = upload(c, S.prof, prof, (size_t)n_prof * sizeof(*prof)))
             return r;
-        d_prof = (const VVCB200ProfTable *)c->prof.p;
+        d_prof = (const VVCB200ProfTable *)S.prof.p;
     }
-    if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)c->blocks.p, n, params,
+    if (int r = uploads_visible(c))
+        return r;
+    if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)S.blocks.p, n, params,
                                     d_lut, nullptr, d_mv, d_prof, c->stream))
+        return r;
+    if (int r = set_consumed(c))
         return r;
     if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
         VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
@@ -354,9 +446,10 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
         }
     }
     DeviceGuard g(c->device);
-    if (int r = upload(c, c->levels, levels, n_levels * sizeof(int16_t)))
+    StageSet &S = c->sets[c->set];
+    if (int r = upload(c, S.levels, levels, n_levels * sizeof(int16_t)))
         return r;
-    if (int r = upload(c, c->tbs, tbs, (size_t)n * sizeof(VVCB200TransformBlock)))
+    if (int r = upload(c, S.tbs, tbs, (size_t)n * sizeof(VVCB200TransformBlock)))
         return r;
     const VVCB200Planes *res = nullptr;
     for (int i = 0; i < n && !res; i++)
@@ -366,8 +459,12 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
                     return r;
             res = &c->residual.planes;
         }
-    return vvcb200_residual_batch(&c->dpb[c->cur].planes, res, (const int16_t *)c->levels.p,
-                                  (const VVCB200TransformBlock *)c->tbs.p, n, params, c->stream);
+    if (int r = uploads_visible(c))
+        return r;
+    if (int r = vvcb200_residual_batch(&c->dpb[c->cur].planes, res, (const int16_t *)S.levels.p,
+                                       (const VVCB200TransformBlock *)S.tbs.p, n, params, c->stream))
+        return r;
+    return set_consumed(c);
 }
 
 int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint32_t *ctu_first, int ctus_w, int ctus_h,
@@ -409,17 +506,32 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
-    c->intra_order.resize(n);
-    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, shift, c->width, c->height, c->intra_order.data(), nullptr))
+    StageSet &S = c->sets[c->set];
+    if (S.in_use)                         // the copy that last read this set's pinned staging must be over
+        VVC_CUDA(cudaEventSynchronize(S.uploaded));
+    if ((size_t)n > S.h_order_cap) {      // pinned staging for the scheduled order (this set's previous upload has long finished)
+        if (S.h_order)
+            cudaFreeHost(S.h_order);
+        S.h_order = nullptr;
+        S.h_order_cap = 0;
+        const size_t want = (size_t)n + n / 4 + 1024;
+        VVC_CUDA(cudaHostAlloc((void **)&S.h_order, want * sizeof(VVCB200IntraBlock), cudaHostAllocDefault));
+        S.h_order_cap = want;
+    }
+    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, shift, c->width, c->height,
+                                       VVCB200_INTRA_ORDER_DIAGONAL, S.h_order, nullptr))
         return r;
-    // the copy below is from pageable memory: the driver stages it before returning, so the vector may be reused
-    if (int r = upload(c, c->iblocks, c->intra_order.data(), (size_t)n * sizeof(VVCB200IntraBlock)))
+    if (int r = upload(c, S.iblocks, S.h_order, (size_t)n * sizeof(VVCB200IntraBlock)))
         return r;
     const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
     if (int r = c->intra_marks.reserve(marks))
         return r;
-    return vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr,
-                                 (const VVCB200IntraBlock *)c->iblocks.p, n, params, c->intra_marks.p, c->stream);
+    if (int r = uploads_visible(c))
+        return r;
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr,
+                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, c->intra_marks.p, c->stream))
+        return r;
+    return set_consumed(c);
 }
 
 int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
@@ -429,9 +541,14 @@ int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
-    if (int r = upload(c, c->lut_inv, inv_lut, sizeof(uint16_t) << c->bit_depth))
+    StageSet &S = c->sets[c->set];
+    if (int r = upload(c, S.lut_inv, inv_lut, sizeof(uint16_t) << c->bit_depth))
         return r;
-    return vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)c->lut_inv.p, c->bit_depth, c->stream);
+    if (int r = uploads_visible(c))
+        return r;
+    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, c->stream))
+        return r;
+    return set_consumed(c);
 }
 
 int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB200DeblockParams *params)
@@ -441,14 +558,19 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    StageSet &S = c->sets[c->set];
     const size_t rows4 = (size_t)(c->height + 3) >> 2;
     const size_t units = (size_t)t->stride4 * rows4;
     const int shift = params->ctb_log2_size;
     const size_t n_ctb = (size_t)((c->width + (1 << shift) - 1) >> shift) * ((c->height + (1 << shift) - 1) >> shift);
     // one device arena: 6 edge tables, 3 qp tables, the per-CTB offsets
-    if (int r = c->db_tables.reserve(units * 9 + n_ctb * 6 + 64))
+    if (units * 9 + n_ctb * 6 + 64 > S.db_tables.cap) {
+        VVC_CUDA(cudaStreamSynchronize(c->stream));
+        VVC_CUDA(cudaStreamSynchronize(c->h2d));
+    }
+    if (int r = S.db_tables.reserve(units * 9 + n_ctb * 6 + 64))
         return r;
-    uint8_t *d = (uint8_t *)c->db_tables.p;
+    uint8_t *d = (uint8_t *)S.db_tables.p;
     VVCB200DeblockTables dt = *t;
     for (int dir = 0; dir < 2; dir++)
         for (int k = 0; k < 3; k++) {
@@ -456,7 +578,7 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
                 set_error("vvcb200_pic_deblock: missing edge table");
                 return VVCB200_ERR_ARG;
             }
-            VVC_CUDA(cudaMemcpyAsync(d, t->d_edge[dir][k], units, cudaMemcpyHostToDevice, c->stream));
+            VVC_CUDA(cudaMemcpyAsync(d, t->d_edge[dir][k], units, cudaMemcpyHostToDevice, c->h2d));
             dt.d_edge[dir][k] = d;
             d += units;
         }
@@ -465,13 +587,17 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
             set_error("vvcb200_pic_deblock: missing qp table");
             return VVCB200_ERR_ARG;
         }
-        VVC_CUDA(cudaMemcpyAsync(d, t->d_qp[k], units, cudaMemcpyHostToDevice, c->stream));
+        VVC_CUDA(cudaMemcpyAsync(d, t->d_qp[k], units, cudaMemcpyHostToDevice, c->h2d));
         dt.d_qp[k] = (const int8_t *)d;
         d += units;
     }
-    VVC_CUDA(cudaMemcpyAsync(d, t->d_ctb_offsets, n_ctb * 6, cudaMemcpyHostToDevice, c->stream));
+    VVC_CUDA(cudaMemcpyAsync(d, t->d_ctb_offsets, n_ctb * 6, cudaMemcpyHostToDevice, c->h2d));
     dt.d_ctb_offsets = (const int8_t *)d;
-    return vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, c->stream);
+    if (int r = uploads_visible(c))
+        return r;
+    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, c->stream))
+        return r;
+    return set_consumed(c);
 }
 
 int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200AlfCtb *alf,
@@ -482,33 +608,41 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    StageSet &S = c->sets[c->set];
     const int sh = ctb_log2_size;
     const size_t n_ctb = (size_t)((c->width + (1 << sh) - 1) >> sh) * ((c->height + (1 << sh) - 1) >> sh);
     VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &c->scratch.planes;
     if (sao) {
-        if (int r = upload(c, c->sao, sao, n_ctb * sizeof(*sao)))
+        if (int r = upload(c, S.sao, sao, n_ctb * sizeof(*sao)))
             return r;
-        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)c->sao.p, ctb_log2_size, c->bit_depth, c->stream))
+        if (int r = uploads_visible(c))
+            return r;
+        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, c->stream))
             return r;
     }
     if (alf) {
-        if (int r = upload(c, c->alf, alf, n_ctb * sizeof(*alf)))
+        if (int r = upload(c, S.alf, alf, n_ctb * sizeof(*alf)))
             return r;
-        if (int r = upload(c, c->alf_params, alf_params, sizeof(*alf_params)))
+        if (int r = upload(c, S.alf_params, alf_params, sizeof(*alf_params)))
             return r;
         if (!sao) {
             // ALF reads `tmp`: without SAO the source is the current picture itself
             const size_t bytes = (size_t)cur->stride[0] * cur->height[0] + 2 * (size_t)cur->stride[1] * cur->height[1];
             VVC_CUDA(cudaMemcpyAsync(c->scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, c->stream));
         }
-        return vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)c->alf.p, (const VVCB200AlfParams *)c->alf_params.p,
-                                   ctb_log2_size, c->bit_depth, c->stream);
+        if (int r = uploads_visible(c))
+            return r;
+        if (int r = vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)S.alf.p, (const VVCB200AlfParams *)S.alf_params.p,
+                                        ctb_log2_size, c->bit_depth, c->stream))
+            return r;
+        return set_consumed(c);
     }
     if (sao) {
         // SAO only: its output becomes the picture (swap the buffers instead of copying back)
         DevPicture t = c->dpb[c->cur];
         c->dpb[c->cur] = c->scratch;
         c->scratch = t;
+        return set_consumed(c);
     }
     return 0;
 }

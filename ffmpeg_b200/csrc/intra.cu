@@ -1065,77 +1065,145 @@ extern "C" size_t vvcb200_intra_scratch_bytes(int width, int height)
 #include <stdlib.h>
 #include <vector>
 
+// Host scheduler.  Depth of every record in the dependency graph: 1 + the largest depth among the records that wrote
+// the units it waits for (the same runs the kernel would poll).  Records come CTU by CTU in decoding order, so every
+// writer a record depends on has been seen.  Sorting by depth is a topological order in which a window of
+// consecutive tickets holds the records that are ready now anywhere in the picture.
+// Map entries are (epoch << 16 | depth): a new picture bumps the epoch instead of clearing the maps; a record only
+// stamps the units other records can read (its top row, bottom row and right column).
+namespace vvcb200 {
+struct IntraScheduler {
+    std::vector<uint32_t> map[3];
+    std::vector<uint16_t> depth;
+    std::vector<uint32_t> start;
+    int uw = 0, uh = 0;
+    uint32_t epoch = 0;
+
+    int run(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h, int ctb_log2, int width,
+            int height, VVCB200IntraBlock *out, int32_t *n_levels)
+    {
+        const uint32_t n = ctu_first[ctus_w * ctus_h];
+        const int w_units = ((ctus_w << ctb_log2) >> 2) + 2, h_units = ((ctus_h << ctb_log2) >> 2) + 2;   // one guard column / row
+        if (w_units != uw || h_units != uh || ++epoch >= 0xffff) {
+            uw = w_units;
+            uh = h_units;
+            epoch = 1;
+            for (int c = 0; c < 3; c++)
+                map[c].assign((size_t)uw * uh, 0);                        // chroma: half the samples, 2-row units: same count
+        }
+        depth.resize(n);
+        const uint32_t tag = epoch << 16;
+        uint32_t max_depth = 0;
+        Span sp[kMaxSpans + 3];
+        for (uint32_t i = 0; i < n; i++) {
+            const VVCB200IntraBlock &b = in[i];
+            if (b.c_idx > 2 || (b.x0 >> 2) >= uw - 2 || (b.y0 >> unit_shift(b.c_idx)) >= uh - 2)
+                return -(int)i - 1;
+            uint32_t d = 0;
+            auto take = [&](int cnt) {
+                for (int k = 0; k < cnt; k++) {
+                    const uint32_t *m = map[sp[k].c].data() + (size_t)(sp[k].uy + 1) * uw + sp[k].ux + 1;
+                    const size_t step = sp[k].horizontal ? 1 : (size_t)uw;
+                    uint32_t best = 0;
+                    for (int j = 0; j < sp[k].n; j++) {
+                        const uint32_t v = m[j * step] ^ tag;                 // < 65536 iff stamped in this picture
+                        best = v < 65536u && v > best ? v : best;
+                    }
+                    d = best > d ? best : d;
+                }
+            };
+            take(vpdu_deps(b, ctb_log2, width, height, sp));
+            const bool isp = (b.flags & VVCB200_IB_ISP) && !b.c_idx;
+            if (b.mode >= 81) {
+                take(cclm_deps(b, sp));
+            } else if (isp) {
+                const int parts = isp_parts(b);
+                for (int k = 0; k < parts; k++) {
+                    VVCB200IntraBlock s;
+                    const int skip = isp_part(b, k, s);
+                    take(predict_deps(s, skip, sp));
+                }
+            } else {
+                take(predict_deps(b, 0, sp));
+            }
+            depth[i] = (uint16_t)++d;
+            max_depth = d > max_depth ? d : max_depth;
+            if (d >= 0xffff)
+                return -(int)i - 1;
+            const int w = isp ? b.cb_w : b.w, h = isp ? b.cb_h : b.h;
+            const uint32_t stamp = tag | d;
+            for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {
+                const int s = unit_shift(c);
+                const int nx = unit_count(b.x0, w, 2), ny = unit_count(b.y0, h, s);
+                uint32_t *m = map[c].data() + (size_t)((b.y0 >> s) + 1) * uw + (b.x0 >> 2) + 1;
+                for (int x = 0; x < nx; x++)
+                    m[x] = m[(size_t)(ny - 1) * uw + x] = stamp;
+                for (int y = 1; y + 1 < ny; y++)
+                    m[(size_t)y * uw + nx - 1] = stamp;
+            }
+        }
+        start.assign(max_depth + 2, 0);                                   // counting sort by depth, stable
+        for (uint32_t i = 0; i < n; i++)
+            start[depth[i] + 1]++;
+        for (uint32_t d = 1; d <= max_depth + 1; d++)
+            start[d] += start[d - 1];
+        for (uint32_t i = 0; i < n; i++)
+            out[start[depth[i]]++] = in[i];
+        if (n_levels)
+            *n_levels = (int32_t)max_depth;
+        return 0;
+    }
+};
+
+IntraScheduler *intra_scheduler_new() { return new IntraScheduler; }
+void intra_scheduler_free(IntraScheduler *s) { delete s; }
+int intra_scheduler_run(IntraScheduler *s, const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
+                        int ctb_log2, int width, int height, VVCB200IntraBlock *out, int32_t *n_levels)
+{
+    return s->run(in, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, out, n_levels);
+}
+}  // namespace vvcb200
+
 extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
-                                      int ctb_log2_size, int width, int height, VVCB200IntraBlock *out, int32_t *n_levels)
+                                      int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
+                                      int32_t *n_levels)
 {
     if (!in || !ctu_first || !out || ctus_w <= 0 || ctus_h <= 0 || ctb_log2_size < 5 || ctb_log2_size > 7 ||
-        width <= 0 || height <= 0 || width > (ctus_w << ctb_log2_size) || height > (ctus_h << ctb_log2_size)) {
+        width <= 0 || height <= 0 || width > (ctus_w << ctb_log2_size) || height > (ctus_h << ctb_log2_size) ||
+        (order != VVCB200_INTRA_ORDER_DIAGONAL && order != VVCB200_INTRA_ORDER_DEPTH)) {
         set_error("vvcb200_intra_schedule: bad arguments");
         return VVCB200_ERR_ARG;
     }
-    // Depth of every record in the dependency graph: 1 + the largest depth among the records that wrote the units it
-    // waits for (the same runs the kernel polls).  Records come CTU by CTU in decoding order, so every writer a record
-    // depends on has been seen.  Sorting by depth is a topological order in which a window of consecutive tickets holds
-    // the records that are ready now anywhere in the picture.
-    const uint32_t n = ctu_first[ctus_w * ctus_h];
-    const int uw = ((ctus_w << ctb_log2_size) >> 2) + 2;                  // one guard column / row on the low side
-    const int uh[3] = { ((ctus_h << ctb_log2_size) >> 2) + 2, ((ctus_h << ctb_log2_size) >> 2) + 2,
-                        ((ctus_h << ctb_log2_size) >> 2) + 2 };          // chroma: half the samples, 2-row units
-    std::vector<int32_t> map[3];
-    for (int c = 0; c < 3; c++)
-        map[c].assign((size_t)uw * uh[c], 0);
-    std::vector<int32_t> depth(n);
-    auto at = [&](int c, int ux, int uy) -> int32_t & { return map[c][(size_t)(uy + 1) * uw + ux + 1]; };
-    int32_t max_depth = 0;
-    Span sp[kMaxSpans + 3];
-    for (uint32_t i = 0; i < n; i++) {
-        const VVCB200IntraBlock &b = in[i];
-        int32_t d = 0;
-        auto take = [&](int cnt) {
-            for (int k = 0; k < cnt; k++)
-                for (int j = 0; j < sp[k].n; j++) {
-                    const int32_t v = sp[k].horizontal ? at(sp[k].c, sp[k].ux + j, sp[k].uy) : at(sp[k].c, sp[k].ux, sp[k].uy + j);
-                    d = v > d ? v : d;
-                }
-        };
-        if (b.c_idx > 2 || (b.x0 >> 2) >= uw - 2 || (b.y0 >> unit_shift(b.c_idx)) >= uh[b.c_idx] - 2) {
-            set_error("vvcb200_intra_schedule: record %u lies outside the picture", i);
-            return VVCB200_ERR_ARG;
-        }
-        take(vpdu_deps(b, ctb_log2_size, width, height, sp));
-        if (b.mode >= 81) {
-            take(cclm_deps(b, sp));
-        } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
-            const int parts = isp_parts(b);
-            for (int k = 0; k < parts; k++) {
-                VVCB200IntraBlock s;
-                const int skip = isp_part(b, k, s);
-                take(predict_deps(s, skip, sp));
+    if (order == VVCB200_INTRA_ORDER_DIAGONAL) {
+        // CTU anti-diagonals x + 2y (the above-right CTU comes first, vvc_thread.c:161), the CTUs of a diagonal dealt
+        // round-robin so that a window of consecutive tickets spans every CTU that can run now.  O(n).
+        size_t o = 0;
+        for (int d = 0; d <= ctus_w - 1 + 2 * (ctus_h - 1); d++) {
+            const int y_lo = d - (ctus_w - 1) > 0 ? (d - (ctus_w - 1) + 1) / 2 : 0;
+            const int y_hi = d / 2 < ctus_h - 1 ? d / 2 : ctus_h - 1;
+            uint32_t longest = 0;
+            for (int y = y_lo; y <= y_hi; y++) {
+                const int rs = y * ctus_w + d - 2 * y;
+                const uint32_t len = ctu_first[rs + 1] - ctu_first[rs];
+                longest = len > longest ? len : longest;
             }
-        } else {
-            take(predict_deps(b, 0, sp));
+            for (uint32_t k = 0; k < longest; k++)
+                for (int y = y_lo; y <= y_hi; y++) {
+                    const int rs = y * ctus_w + d - 2 * y;
+                    if (ctu_first[rs] + k < ctu_first[rs + 1])
+                        out[o++] = in[ctu_first[rs] + k];
+                }
         }
-        depth[i] = ++d;
-        max_depth = d > max_depth ? d : max_depth;
-        const bool isp = (b.flags & VVCB200_IB_ISP) && !b.c_idx;
-        const int w = isp ? b.cb_w : b.w, h = isp ? b.cb_h : b.h;
-        for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {
-            const int s = unit_shift(c);
-            const int ux = b.x0 >> 2, uy = b.y0 >> s, nx = unit_count(b.x0, w, 2), ny = unit_count(b.y0, h, s);
-            for (int y = 0; y < ny; y++)
-                for (int x = 0; x < nx; x++)
-                    at(c, ux + x, uy + y) = d;
-        }
+        if (n_levels)
+            *n_levels = 0;
+        return 0;
     }
-    std::vector<uint32_t> start(max_depth + 2, 0);                        // counting sort by depth, stable
-    for (uint32_t i = 0; i < n; i++)
-        start[depth[i] + 1]++;
-    for (int32_t d = 1; d <= max_depth + 1; d++)
-        start[d] += start[d - 1];
-    for (uint32_t i = 0; i < n; i++)
-        out[start[depth[i]]++] = in[i];
-    if (n_levels)
-        *n_levels = max_depth;
+    static thread_local IntraScheduler sched;                             // keeps its maps from call to call
+    const int r = sched.run(in, ctu_first, ctus_w, ctus_h, ctb_log2_size, width, height, out, n_levels);
+    if (r) {
+        set_error("vvcb200_intra_schedule: record %d lies outside the picture or the dependency chain is too long", -r - 1);
+        return VVCB200_ERR_ARG;
+    }
     return 0;
 }
 
@@ -1180,8 +1248,7 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     VVC_CUDA(cudaMemsetAsync(d_scratch, 0, l.total, s));                  // ticket counter, in-place flag, marks
     intra_mark_kernel<<<(n + 3) / 4, 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
-    static const int per_sm = getenv("VVCB200_INTRA_CTAS_PER_SM") ? atoi(getenv("VVCB200_INTRA_CTAS_PER_SM")) : 4;   // TUNING, temporary
-    const int ctas = min((n + kWarps - 1) / kWarps, sm_count() * per_sm);
+    const int ctas = min((n + kWarps - 1) / kWarps, sm_count() * 3);      // 3 CTAs of 64 KB shared memory fit an SM
     const size_t smem = sizeof(WarpScratch) * kWarps;
     static bool attr_set[64];                                             // per device: allow > 48 KB of shared memory
     int dev = 0;

@@ -94,15 +94,18 @@ def intra_scratch_bytes(width, height):
     return int(f(int(width), int(height)))
 
 
-def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, want_levels=False):
-    """vvcb200_intra_schedule: per-CTU decoding-order records -> dependency-depth order (host helper, no GPU involved)."""
+INTRA_ORDER_DIAGONAL, INTRA_ORDER_DEPTH = 0, 1
+
+
+def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, want_levels=False, order=INTRA_ORDER_DEPTH):
+    """vvcb200_intra_schedule: per-CTU decoding-order records -> wavefront / dependency-depth order (host helper)."""
     blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
     ctu_first = np.ascontiguousarray(ctu_first, np.uint32)
     assert len(ctu_first) == ctus_w * ctus_h + 1 and ctu_first[-1] == len(blocks)
     out = np.zeros(len(blocks), abi.IB_DTYPE)
     levels = C.c_int32(0)
     check(load().vvcb200_intra_schedule(_ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), int(ctb_log2), int(width),
-                                        int(height), _ptr(out), C.byref(levels)))
+                                        int(height), int(order), _ptr(out), C.byref(levels)))
     return (out, int(levels.value)) if want_levels else out
 
 
@@ -127,7 +130,7 @@ class Context:
         self._h = C.c_void_p()
         check(load().vvcb200_ctx_create(C.byref(self._h), int(device), int(width), int(height),
                                         int(chroma_format_idc), int(bit_depth), int(dpb_size)))
-        self.width, self.height, self.bit_depth = width, height, bit_depth
+        self.width, self.height, self.bit_depth, self.dpb_size = width, height, bit_depth, dpb_size
         self._pinned = []
         self._keep = []
 

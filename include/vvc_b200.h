@@ -382,9 +382,7 @@ typedef struct VVCB200IntraParams {
  * residual of every inter block).  One launch; warps draw records from a ticket counter in array order and each
  * record waits, on per-4x4 "pending" marks in `d_scratch`, for exactly the neighbour samples it reads.  The array order
  * must therefore be topological (every record after the records it reads from): the decoding order is one, and
- * vvcb200_intra_schedule() builds the order the engine prefers from per-CTU decoding-order records: sorted by depth
- * in the dependency graph, so that consecutive tickets are the records that can run now anywhere in the picture
- * (a finer-grained form of the CTU wavefront of vvc_thread.c:156-184).
+ * vvcb200_intra_schedule() builds better ones from per-CTU decoding-order records (see VVCB200_INTRA_ORDER_*).
  * d_residual: int16 residual planes written by vvcb200_residual_batch for TBs flagged VVCB200_TB_TO_RESIDUAL (may be
  * NULL if no record has VVCB200_IB_RESIDUAL).
  * Luma-dependent chroma residual scaling (sh_lmcs_used_flag && ph_chroma_residual_scale_flag): the factor depends on
@@ -397,11 +395,21 @@ typedef struct VVCB200IntraParams {
  * reconstructed"), so bit depths above 15 are not supported by this entry point.
  */
 VVCB200_API size_t vvcb200_intra_scratch_bytes(int width, int height /* luma samples */);
+enum {
+    /* CTU anti-diagonals x + 2y (the wavefront of vvc_thread.c:156-184), the CTUs of a diagonal interleaved record by
+     * record.  O(n) on the host; what vvcb200_pic_intra uses. */
+    VVCB200_INTRA_ORDER_DIAGONAL = 0,
+    /* Sorted by depth in the dependency graph, so that consecutive tickets are the records that can run now anywhere
+     * in the picture.  Shortens the kernel by up to a third on pictures with scattered intra units, at ~0.1 us of
+     * host time per record. */
+    VVCB200_INTRA_ORDER_DEPTH    = 1,
+};
 /* Host helper: `in` holds the records of CTU i (raster index) at ctu_first[i] .. ctu_first[i + 1], in decoding order;
- * `out` (same length, must not alias) receives them in dependency-depth order.  width / height: luma samples.
- * n_levels (may be NULL): the length of the longest dependency chain, i.e. the number of serial steps of the picture. */
+ * `out` (same length, must not alias) receives them in the requested order.  width / height: luma samples.
+ * n_levels (may be NULL; VVCB200_INTRA_ORDER_DEPTH only): the length of the longest dependency chain, i.e. the number
+ * of serial steps of the picture. */
 VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
-                                       int ctb_log2_size, int width, int height, VVCB200IntraBlock *out,
+                                       int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
                                        int32_t *n_levels);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
                                       const VVCB200IntraBlock *d_blocks, int n,

@@ -69,9 +69,13 @@ class EnginePicture:
             self.intra = (ctx.pinned_copy(ia["blocks"]), ctx.pinned_copy(ia["ctu_first"]),
                           (pic["width"] + (1 << ctb) - 1) >> ctb, (pic["height"] + (1 << ctb) - 1) >> ctb, ia["params"])
         self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
-        self.out = ctx.pinned_planes()
-        # the picture is reconstructed into the slot after the references; ref_slot[][] already maps to 0..n_refs-1
-        self.cur_slot = self.n_refs
+        # pictures are reconstructed into the slots after the references (ref_slot[][] already maps to 0..n_refs-1),
+        # alternating between two slots / two host frames when the context has them, as consecutive pictures of a
+        # decoder do: the download of one picture then overlaps the reconstruction of the next
+        self.n_slots = max(1, min(2, ctx.dpb_size - self.n_refs))
+        self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
+        self.count = 0
+        self.out = self.outs[0]
 
     def h2d_bytes(self):
         intra = 0 if self.intra is None else self.intra[0].nbytes + self.intra[1].nbytes
@@ -88,7 +92,10 @@ class EnginePicture:
 
     def run(self, download=True):
         ctx, pic = self.ctx, self.pic
-        ctx.begin(self.cur_slot)
+        k = self.count % self.n_slots
+        self.count += 1
+        self.out = self.outs[k]
+        ctx.begin(self.n_refs + k)
         ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0], prof=self.prof)
         ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
         if self.intra is not None:

@@ -45,6 +45,29 @@ def test_full_picture_with_intra_cus_md5(seed, w, h, ctb, lmcs, frac):
         ctx.close()
 
 
+def test_back_to_back_pictures_overlap_safely():
+    """Six pictures submitted without a sync in between, alternating between two DPB slots and two host frames: uploads,
+    kernels and downloads of neighbouring pictures overlap on the context's three streams and every frame is right."""
+    pic = synth.full_picture(31, 832, 480, ctb_log2=7, lmcs=True, intra_fraction=0.2)
+    want = util.plane_md5(pipeline.oracle_picture(pic))
+    ctx = lib.Context(0, 832, 480, dpb_size=4)
+    try:
+        ep = pipeline.EnginePicture(ctx, pic)
+        assert ep.n_slots == 2
+        ep.upload_refs()
+        for rounds in range(3):
+            for o in ep.outs:
+                for p in o:
+                    p[:] = 0
+            for _ in range(6):
+                ep.run()
+            ctx.sync()
+            for o in ep.outs:
+                assert util.plane_md5(o) == want
+    finally:
+        ctx.close()
+
+
 def test_full_picture_1080p_md5():
     """BASELINE config 2 size: 1080p full picture recon + deblock + SAO + ALF."""
     pic = synth.full_picture(11, 1920, 1080)

@@ -59,11 +59,12 @@ def test_port_matches_golden():
 
 
 @pytest.mark.parametrize("seed,w,h,ctb", [(11, 416, 240, 5), (12, 416, 240, 6), (13, 300, 200, 7), (14, 64, 64, 6)])
-def test_schedule_is_a_topological_permutation(seed, w, h, ctb):
+@pytest.mark.parametrize("order", [lib.INTRA_ORDER_DIAGONAL, lib.INTRA_ORDER_DEPTH])
+def test_schedule_is_a_topological_permutation(seed, w, h, ctb, order):
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, intra_fraction=0.8)
     ia = pic["intra"]
     cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
-    order = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h)
+    order = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h, order=order)
     assert sorted(order.tobytes()[i:i + 28] for i in range(0, order.nbytes, 28)) == \
         sorted(ia["blocks"].tobytes()[i:i + 28] for i in range(0, ia["blocks"].nbytes, 28))
     a, b = _port(pic), _port(pic, order)

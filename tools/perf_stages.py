@@ -80,7 +80,13 @@ def main():
     ctb = pic["ctb_log2"]
     cw, ch = (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb
     marks = torch.zeros(lib.intra_scratch_bytes(width, height), dtype=torch.uint8, device="cuda")
-    for label, recs in (("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height)), ("decoding order", ia["blocks"])):
+    cf = ia["ctu_first"].astype(np.int64)
+    ctu_of = np.repeat(np.arange(cw * ch), np.diff(cf))
+    k_in = np.arange(len(ia["blocks"])) - cf[ctu_of]
+    diag = (ctu_of % cw) + 2 * (ctu_of // cw)
+    diag_order = ia["blocks"][np.lexsort((ctu_of // cw, k_in, diag))]
+    for label, recs in (("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height)),
+                        ("ctu diagonals", diag_order), ("decoding order", ia["blocks"])):
         d = dev(recs)
         ms = timed(torch, lambda: lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks))
         print("intra %-15s %d records  %.4f ms" % (label, len(recs), ms))
