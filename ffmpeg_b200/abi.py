@@ -131,8 +131,14 @@ def inter_params(bit_depth=10, log2_denom=(0, 0), weight=None, offset=None, ref_
 
 
 def order_blocks_by_width(blocks, params):
-    """Sort a prediction-block batch into the width order the engine wants and record the class sizes."""
-    order = np.argsort(-blocks["w"].astype(np.int32), kind="stable")
+    """Sort a prediction-block batch into the width order the engine wants and record the class sizes.
+    Inside a width class records are grouped by the tools they use (GPM, affine, DMVR, BDOF, weighted, plain; uni / bi):
+    not required for correctness, but warps that run at the same time then execute the same code path, which is what
+    the instruction cache of an SM needs (the kernel is ~120 KB of code, see profiles/)."""
+    f = blocks["flags"].astype(np.int64)
+    kind = (f & (PB_GPM | PB_AFFINE | PB_LUMA_ONLY | PB_CHROMA_ONLY | PB_DMVR | PB_BDOF | PB_WP | PB_PROF0 | PB_PROF1)) * 4 + \
+        blocks["pred_flag"].astype(np.int64) + 1024 * 1024 * (blocks["bcw_idx"] != 0)
+    order = np.lexsort((kind, -blocks["w"].astype(np.int32)))
     blocks = np.ascontiguousarray(blocks[order])
     params.n_w16 = int(np.sum(blocks["w"] == 16))
     params.n_w8 = int(np.sum(blocks["w"] == 8))

@@ -196,16 +196,65 @@ __device__ __forceinline__ void fast_column_pass(const int16_t *inT, int16_t *mi
 
 // Row pass: the lane computes outputs x0 .. x0 + R - 1 of row y and hands them to the epilogue in
 // groups of two adjacent samples.
-template <int R, typename Emit2>
+template <int R, typename Epi>
 __device__ __forceinline__ void fast_row_pass(const int16_t *mid, const uint32_t *mat, int half_n, int y, int x0,
-                                              int n_kp, int sh1, Emit2 emit2)
+                                              int n_kp, int sh1, const Epi &ep)
 {
+    // The R destination samples of this lane (adjacent, in row y) are fetched BEFORE the arithmetic, in the widest
+    // pieces their address allows, so that the load latency hides behind the row transform instead of stalling the
+    // read-modify-write at its end (the kernel's main stall, see profiles/).
+    constexpr int W = R / 2;                                               // 32-bit words
+    uint32_t old[W];
+    const bool rmw = ep.plain();
+    uint32_t *p = reinterpret_cast<uint32_t *>(ep.dst + y * ep.stride + x0);
+    const unsigned al = (unsigned)(uintptr_t)p;
+    const int vec = (W >= 4 && !(al & 15)) ? 4 : (W >= 2 && !(al & 7)) ? 2 : 1;
+    if (rmw) {
+        if (vec == 4) {
+#pragma unroll
+            for (int i = 0; i < W / 4; i++) {
+                const uint4 v = reinterpret_cast<const uint4 *>(p)[i];
+                old[4 * i] = v.x; old[4 * i + 1] = v.y; old[4 * i + 2] = v.z; old[4 * i + 3] = v.w;
+            }
+        } else if (vec == 2) {
+#pragma unroll
+            for (int i = 0; i < W / 2; i++) {
+                const uint2 v = reinterpret_cast<const uint2 *>(p)[i];
+                old[2 * i] = v.x; old[2 * i + 1] = v.y;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < W; i++)
+                old[i] = p[i];
+        }
+    }
     int acc[R];
     dp2a_pass<R>(acc, reinterpret_cast<const uint32_t *>(mid + y * kPairStride), n_kp, mat, half_n, x0);
     const int add = 1 << (sh1 - 1);
+    if (!rmw) {
 #pragma unroll
-    for (int r = 0; r < R; r += 2)
-        emit2(y, x0 + r, (acc[r] + add) >> sh1, (acc[r + 1] + add) >> sh1);
+        for (int r = 0; r < R; r += 2)
+            ep.two(y, x0 + r, (acc[r] + add) >> sh1, (acc[r + 1] + add) >> sh1);
+        return;
+    }
+#pragma unroll
+    for (int i = 0; i < W; i++) {
+        const int r0 = (acc[2 * i] + add) >> sh1, r1 = (acc[2 * i + 1] + add) >> sh1;
+        old[i] = (uint32_t)clip_pixel((int)(old[i] & 0xffff) + r0, ep.bd) | ((uint32_t)clip_pixel((int)(old[i] >> 16) + r1, ep.bd) << 16);
+    }
+    if (vec == 4) {
+#pragma unroll
+        for (int i = 0; i < W / 4; i++)
+            reinterpret_cast<uint4 *>(p)[i] = make_uint4(old[4 * i], old[4 * i + 1], old[4 * i + 2], old[4 * i + 3]);
+    } else if (vec == 2) {
+#pragma unroll
+        for (int i = 0; i < W / 2; i++)
+            reinterpret_cast<uint2 *>(p)[i] = make_uint2(old[2 * i], old[2 * i + 1]);
+    } else {
+#pragma unroll
+        for (int i = 0; i < W; i++)
+            p[i] = old[i];
+    }
 }
 
 // Table 38 (vvc_intra.c:342-362)
@@ -292,6 +341,8 @@ struct Epilogue {
                 dst2[y * stride2 + x] = (uint16_t)clip_pixel(dst2[y * stride2 + x] + r2, bd);
         }
     }
+    // plain add into the picture (no joint plane, no chroma scaling, not into the residual planes)
+    __device__ __forceinline__ bool plain() const { return !(joint || lmcs || to_residual); }
     // two horizontally adjacent samples: one 32-bit read-modify-write (x even, planes 4-byte aligned)
     __device__ __forceinline__ void two(int y, int x, int r0, int r1) const
     {
@@ -397,16 +448,15 @@ __device__ __forceinline__ void fast_block(const ResidualArgs &a, const ScalingL
         const int yl = li & ((1 << log2rows) - 1), g = li >> log2rows;
         const uint32_t *mat = tx_packed(smat, d.trh, d.log2_w);
         const int n_kp = (nzw + 1) >> 1, half = w >> 1;
-        auto emit2 = [&](int y, int x, int r0, int r1) { ep.two(y, x, r0, r1); };
         if (g < (1 << lg)) {
             for (int y = yl; y < h; y += lpt) {
                 switch (per_lane) {
-                case 2:  fast_row_pass<2>(fmid, mat, half, y, g * 2, n_kp, sh1, emit2); break;
-                case 4:  fast_row_pass<4>(fmid, mat, half, y, g * 4, n_kp, sh1, emit2); break;
-                case 8:  fast_row_pass<8>(fmid, mat, half, y, g * 8, n_kp, sh1, emit2); break;
+                case 2:  fast_row_pass<2>(fmid, mat, half, y, g * 2, n_kp, sh1, ep); break;
+                case 4:  fast_row_pass<4>(fmid, mat, half, y, g * 4, n_kp, sh1, ep); break;
+                case 8:  fast_row_pass<8>(fmid, mat, half, y, g * 8, n_kp, sh1, ep); break;
                 default:
                     for (int x0 = g * per_lane; x0 < (g + 1) * per_lane; x0 += 16)
-                        fast_row_pass<16>(fmid, mat, half, y, x0, n_kp, sh1, emit2);
+                        fast_row_pass<16>(fmid, mat, half, y, x0, n_kp, sh1, ep);
                     break;
                 }
             }
