@@ -24,6 +24,7 @@ namespace vvcb200 {
 namespace {
 
 constexpr int kWarps   = 4;       // warps per CTA
+constexpr int kSlots   = 1;       // records a warp holds at a time (1: it simply waits for its record)
 constexpr int kEdgeLen = 256;     // samples per edge array: indices -72 .. 183 are addressable
 constexpr int kEdgeOrg = 72;
 constexpr unsigned kFull = 0xffffffffu;
@@ -45,6 +46,7 @@ constexpr int kStageExtra = 65 * 68 * 2 + 16;                             // CII
 struct __align__(16) WarpScratch {
     uint8_t  stage_res[kStageRes];
     uint8_t  stage_extra[kStageExtra];
+    VVCB200IntraBlock slot[kSlots]; // records this warp holds and looks at in turn
     uint16_t edge[4][kEdgeLen];   // left, top, filtered left, filtered top
     int      red[16];             // MIP: reduced boundary
     uint16_t mip[64];             // MIP: reduced prediction, row-major at the reduced size
@@ -355,12 +357,12 @@ __host__ __device__ inline int isp_part(const VVCB200IntraBlock &b, int k, VVCB2
 }
 __host__ __device__ inline int isp_parts(const VVCB200IntraBlock &b) { return b.w == b.cb_w ? b.cb_h / b.h : b.cb_w / b.w; }
 
-// wait until none of the units in the runs is pending any more; the acquire fence is only needed when some unit was
-// written by an in-place record (its samples were published before its mark went from 1 to 2)
-__device__ void wait_spans(const IntraArgs &a, const Span *sp, int n, int lane)
+// Are the units in the runs free of pending marks?  blocking: poll until they are.  The acquire fence is only needed
+// when some unit was written by an in-place record (its samples were published before its mark went from 1 to 2).
+__device__ bool spans_ready(const IntraArgs &a, const Span *sp, int n, int lane, bool blocking)
 {
     if (!n)
-        return;
+        return true;
     unsigned m;
     for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
         m = 0;
@@ -370,23 +372,32 @@ __device__ void wait_spans(const IntraArgs &a, const Span *sp, int n, int lane)
         m = __reduce_or_sync(kFull, m);
         if (!(m & 1))
             break;
+        if (!blocking)
+            return false;
         __nanosleep(backoff);
     }
     if (m & 2)
         fence_gpu();
+    return true;
 }
 
 // ---- luma-dependent chroma residual scaling (vvc_intra_template.c:376-449) ------------------------------------------
 // The factor of a VPDU comes from the mean of the reconstructed luma samples left of and above it.
-__device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane)
+// Returns false (try mode only) when the luma it depends on is not there yet; the factor comes back in `scale`.
+__device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane, bool blocking,
+                                  int &scale)
 {
+    scale = 0;
+    if (!(b.flags & VVCB200_IB_LMCS_SCALE))
+        return true;
     const int size = min(1 << a.ctb_log2, 64), ls = ilog2(size);
     const int x = b.vpdu_x << ls, y = b.vpdu_y << ls;
     const bool al = b.vpdu_avail & 1, at = b.vpdu_avail & 2;
     const int rows = min(size, a.pic.h[0] - y), cols = min(size, a.pic.w[0] - x);
     if (has_marks) {
         Span sp[2];
-        wait_spans(a, sp, vpdu_deps(b, a.ctb_log2, a.pic.w[0], a.pic.h[0], sp), lane);
+        if (!spans_ready(a, sp, vpdu_deps(b, a.ctb_log2, a.pic.w[0], a.pic.h[0], sp), lane, blocking))
+            return false;
     }
     const uint16_t *luma = a.pic.p[0] + (size_t)y * a.pic.stride[0] + x;
     int sum, cnt;
@@ -411,6 +422,8 @@ __device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b,
         }
         if (!__any_sync(kFull, bad))
             break;
+        if (!blocking)
+            return false;
         __nanosleep(backoff);
     }
     sum = warp_sum(sum);
@@ -418,7 +431,8 @@ __device__ int vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b,
     int i = a.lmcs_min_bin;
     while (i <= a.lmcs_max_bin && mean >= a.lmcs_pivot[i + 1])
         i++;
-    return a.lmcs_coeff[min(i, 15)];
+    scale = a.lmcs_coeff[min(i, 15)];
+    return true;
 }
 
 __device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
@@ -448,8 +462,9 @@ struct Store {                    // what happens to a predicted sample on its w
     }
 };
 
-__device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, int lane,
-                               bool has_marks, int skip_wait = 0)
+// blocking = false: one look at the neighbours; returns false, having written nothing, when they are not all there.
+__device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, int lane,
+                               bool has_marks, bool blocking, int skip_wait = 0)
 {
     const long long p0 = PROF_T();
     const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode, ref_idx = b.ref_idx, bd = a.bd;
@@ -464,15 +479,25 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     uint16_t *src = a.pic.p[c] + (size_t)b.y0 * stride + b.x0;
     const bool has_res = b.flags & VVCB200_IB_RESIDUAL;
     const bool ciip = b.flags & VVCB200_IB_CIIP, add_only = b.flags & VVCB200_IB_ADD_ONLY;
-    // reads that do not depend on the neighbours start now and land while the warp waits
-    if (has_res)
-        stage_block_async(ws.stage_res, a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0, a.res_stride[c], w, h, lane);
-    if (ciip || add_only)
-        stage_block_async(ws.stage_extra, src, stride, w, h, lane);
-    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, has_marks, lane) : 0;
+    // Reads that do not depend on the neighbours (the residual, the inter prediction of an in-place block): a warp that
+    // is going to wait for this record starts them now so that they land meanwhile; one that only takes a look starts
+    // them once it knows the record will run.
+    auto stage_inputs = [&]() {
+        if (has_res)
+            stage_block_async(ws.stage_res, a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0, a.res_stride[c], w, h, lane);
+        if (ciip || (add_only && has_res))
+            stage_block_async(ws.stage_extra, src, stride, w, h, lane);
+    };
+    if (blocking)
+        stage_inputs();
+    int lscale;
+    if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
+        return false;
 
     if (add_only) {                                                       // the prediction is there already
         if (has_res) {
+            if (!blocking)
+                stage_inputs();
             const int16_t *res = reinterpret_cast<const int16_t *>(ws.stage_res);
             const uint16_t *cur = reinterpret_cast<const uint16_t *>(ws.stage_extra);
             stage_wait();
@@ -485,7 +510,7 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
                 src[(size_t)y * stride + x] = (uint16_t)clip_pixel((int)cur[idx] + r, bd);
             }
         }
-        return;
+        return true;
     }
 
     const int left_size = ee.left_size, ul = ee.ul, ut = ee.ut, refw = ee.refw, refh = ee.refh;
@@ -495,7 +520,8 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     PROF_ADD(7, PROF_T() - p0);
     if (has_marks) {
         Span sp[3];
-        wait_spans(a, sp, predict_deps(b, skip_wait, sp), lane);
+        if (!spans_ready(a, sp, predict_deps(b, skip_wait, sp), lane, blocking))
+            return false;
     }
 
     // ---- which of the edge samples the prediction really consumes.  The reference fetches `ul` / `ut` samples whatever
@@ -563,6 +589,8 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
         for (int k = 0; k < 4; k++)
             bad |= (lv[k] == kSentinel && lane + 32 * k < need_l) || (tv[k] == kSentinel && lane + 32 * k < need_t);
         if (__any_sync(kFull, bad)) {
+            if (!blocking)
+                return false;
             __nanosleep(backoff);
             continue;
         }
@@ -578,6 +606,8 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
         }
         break;
     }
+    if (!blocking)
+        stage_inputs();
     __syncwarp();
     {                                                                     // substitution of what is not there
         const int vt = top[ta - 1], vl = left[la - 1];
@@ -711,7 +741,7 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
             }
             st.put(x, y, v);
         }
-        return;
+        return true;
     }
 
     const int scale = (lw + lh - 2) >> 2;
@@ -755,7 +785,7 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
             }
             st.put(x, y, val);
         }
-        return;
+        return true;
     }
 
     // angular (vvc_intra_template.c:838-1001): `along` runs with the prediction direction's axis, `cross` across it
@@ -785,6 +815,7 @@ __device__ void predict_record(const IntraArgs &a, const CtaTables &tb, const VV
         }
         st.put(x, y, pred);
     }
+    return true;
 }
 
 __device__ __forceinline__ int checked_load(const uint16_t *p, bool &bad)
@@ -795,7 +826,8 @@ __device__ __forceinline__ int checked_load(const uint16_t *p, bool &bad)
 }
 
 // ---- CCLM (vvc_intra_template.c:29-375): one record predicts Cb and Cr --------------------------------------------
-__device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, bool has_marks)
+__device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, bool has_marks,
+                            bool blocking)
 {
     const int bd = a.bd, w = b.w, h = b.h, x = b.x0, y = b.y0, x0 = x * 2, y0 = y * 2, mode = b.mode;
     const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
@@ -807,18 +839,29 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
     const int num[2] = { kc.num[0], kc.num[1] };
     const int n = w * h, lw = ilog2(w);
     const int16_t *res[2] = { nullptr, nullptr };
-    if (b.flags & VVCB200_IB_RESIDUAL)                                    // residuals travel while the warp waits
-        for (int c = 0; c < 2; c++)
-            if (b.res_planes & (1 << c)) {
-                int16_t *sres = reinterpret_cast<int16_t *>(ws.stage_res) + c * n;
-                stage_block_async(sres, a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x, a.res_stride[c + 1], w, h, lane);
-                res[c] = sres;
-            }
+    bool staged = false;
+    auto stage_residuals = [&]() {                                        // before waiting, or once the record is known to run
+        if (staged)
+            return;
+        staged = true;
+        if (b.flags & VVCB200_IB_RESIDUAL)
+            for (int c = 0; c < 2; c++)
+                if (b.res_planes & (1 << c)) {
+                    int16_t *sres = reinterpret_cast<int16_t *>(ws.stage_res) + c * n;
+                    stage_block_async(sres, a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x, a.res_stride[c + 1], w, h, lane);
+                    res[c] = sres;
+                }
+    };
+    if (blocking)
+        stage_residuals();
     if (has_marks) {
         Span sp[kMaxSpans];
-        wait_spans(a, sp, cclm_deps(b, sp), lane);
+        if (!spans_ready(a, sp, cclm_deps(b, sp), lane, blocking))
+            return false;
     }
-    const int lscale = (b.flags & VVCB200_IB_LMCS_SCALE) ? vpdu_chroma_scale(a, b, has_marks, lane) : 0;
+    int lscale;
+    if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
+        return false;
     // the co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte pieces;
     // the block's own luma is usually the last thing to arrive: poll its last row cheaply, then fetch and verify everything
     uint16_t *win = reinterpret_cast<uint16_t *>(ws.stage_extra);
@@ -839,10 +882,11 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
                 if (!__any_sync(kFull, bad))
                     break;
             }
+            if (!blocking)
+                return false;
             __nanosleep(backoff);
         }
     }
-    stage_wait();
     __syncwarp();
     auto emit = [&](int c, int i, int j, int v) {
         if (res[c]) {
@@ -854,10 +898,13 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
         dst[c][(size_t)j * cs[c] + i] = (uint16_t)v;
     };
     if (!avail_t && !avail_l) {
+        stage_residuals();
+        stage_wait();
+        __syncwarp();
         for (int idx = lane; idx < n; idx += 32)
             for (int c = 0; c < 2; c++)
                 emit(c, idx & (w - 1), idx >> lw, 1 << (bd - 1));
-        return;
+        return true;
     }
 #define L(dx, dy) checked_load(luma + (dx) + (ptrdiff_t)ls * (dy), bad)
     int ka[2] = { 0, 0 }, kb[2] = { 1 << (bd - 1), 1 << (bd - 1) }, kk[2] = { 0, 0 };
@@ -898,8 +945,11 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
         }
         if (!__any_sync(kFull, bad))
             break;
+        if (!blocking)
+            return false;
         __nanosleep(backoff);
         }
+        stage_residuals();                                                // travel while the model is derived
         int sel[3][4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -953,6 +1003,10 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
             }
         }
     }
+    if (!(num[0] || num[1]))
+        stage_residuals();
+    stage_wait();
+    __syncwarp();
 #define W(dx, dy) ((int)win[((dy) + 1) * wpitch + 4 + (dx)])
     for (int idx = lane; idx < n; idx += 32) {                            // down-sampled luma -> both chroma planes
         const int i = idx & (w - 1), j = idx >> lw;
@@ -970,6 +1024,34 @@ __device__ void cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
     }
 #undef W
 #undef L
+    return true;
+}
+
+// Everything an ISP coding block reads from outside itself: the column left of it and the row above it as far as any
+// sub-partition reaches (twice the block's size, limited by what the host reported available), and the corner.
+__device__ bool isp_external_ready(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane)
+{
+    if (has_marks) {
+        Span sp[3];
+        const int parts = isp_parts(b);
+        for (int q = 0; q < parts; q++) {
+            VVCB200IntraBlock sub;
+            const int skip = isp_part(b, q, sub);
+            if (!spans_ready(a, sp, predict_deps(sub, skip, sp), lane, false))
+                return false;
+        }
+    }
+    const int stride = a.pic.stride[0];
+    const uint16_t *src = a.pic.p[0] + (size_t)b.y0 * stride + b.x0;
+    const int nl = min((int)b.avail_left, 2 * b.cb_h), nt = min((int)b.avail_top, 2 * b.cb_w);
+    bool bad = false;
+    for (int i = lane; i < nl; i += 32)
+        bad |= __ldcg(src - 1 + (ptrdiff_t)stride * i) == kSentinel;
+    for (int i = lane; i < nt; i += 32)
+        bad |= __ldcg(src - stride + i) == kSentinel;
+    if (lane == 0 && b.up_left)
+        bad |= __ldcg(src - stride - 1) == kSentinel;
+    return !__any_sync(kFull, bad);
 }
 
 __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
@@ -990,42 +1072,79 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
         tb.mip_off[threadIdx.x] = VVC_MIP_OFF[threadIdx.x];
     __syncthreads();
     const bool has_marks = a.ticket[1] != 0;                              // written by the pre-pass
+
+    // Each warp holds up to kSlots records drawn in ticket order.  With one slot it waits for that record's neighbours
+    // (tight polling: the lowest latency along a dependency chain, which is what bounds the kernel).  With more slots it
+    // looks at its records in turn and runs whichever is complete; measured on B200 that widens the window of records
+    // that can start early but roughly doubles the time a finished neighbour goes unnoticed, and loses.
+    // Neither can deadlock: the lowest unfinished ticket depends only on finished records and its holder keeps looking.
+    constexpr bool kWait = kSlots == 1;
+    VVCB200IntraBlock *slot = ws.slot;
+    unsigned held = 0;                                                    // bit k: slot k is occupied (warp-uniform)
+    bool tickets_left = true;
+    unsigned backoff = 32;
     for (;;) {
-        const long long t0 = PROF_T();
-        int t = 0;
-        if (lane == 0)
-            t = atomicAdd(a.ticket, 1);
-        t = __shfl_sync(kFull, t, 0);
-        if (t >= a.n)
-            break;
-        const VVCB200IntraBlock b = load_record(a.blocks + t);
-        const long long t1 = PROF_T();
-        if (b.mode >= 81) {
-            cclm_record(a, b, ws, lane, has_marks);
-        } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
-            // ISP: the sub-partitions of the coding block one after the other, each predicted from its reconstructed
-            // predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit
-            const int n_parts = isp_parts(b);
-            for (int k = 0; k < n_parts; k++) {
-                VVCB200IntraBlock s;
-                const int skip = isp_part(b, k, s);
-                predict_record(a, tb, s, ws, lane, has_marks, skip);
-                __syncwarp();
+        while (tickets_left && held != (1u << kSlots) - 1) {              // refill in ticket order
+            int t = 0;
+            if (lane == 0)
+                t = atomicAdd(a.ticket, 1);
+            t = __shfl_sync(kFull, t, 0);
+            if (t >= a.n) {
+                tickets_left = false;
+                break;
             }
-        } else {
-            predict_record(a, tb, b, ws, lane, has_marks);
-        }
-        const long long t2 = PROF_T();
-        if (in_place(b)) {                                                // samples before marks
-            fence_gpu();
-            __syncwarp();
-            set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 2, lane);
+            const int k = __ffs(~held) - 1;
+            if (lane < 7)
+                reinterpret_cast<uint32_t *>(&slot[k])[lane] = __ldg(reinterpret_cast<const uint32_t *>(a.blocks + t) + lane);
+            held |= 1u << k;
         }
         __syncwarp();
-        PROF_ADD(0, t1 - t0);
-        PROF_ADD(1, t2 - t1);
-        PROF_ADD(2, PROF_T() - t2);
-        PROF_ADD(3, 1);
+        if (!held)
+            break;
+        bool progress = false;
+        for (int k = 0; k < kSlots && !progress; k++) {
+            if (!(held & (1u << k)))
+                continue;
+            const VVCB200IntraBlock b = slot[k];
+            bool done;
+            if (b.mode >= 81) {
+                done = cclm_record(a, b, ws, lane, has_marks, kWait);
+            } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
+                // ISP: the sub-partitions of the coding block one after the other, each predicted from its
+                // reconstructed predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit.  Everything the
+                // partitions read from outside the block must be there before the first one starts; after that the warp
+                // only ever waits for its own stores.
+                done = kWait || isp_external_ready(a, b, has_marks, lane);
+                if (done) {
+                    const int n_parts = isp_parts(b);
+                    for (int q = 0; q < n_parts; q++) {
+                        VVCB200IntraBlock sub;
+                        const int skip = isp_part(b, q, sub);
+                        predict_record(a, tb, sub, ws, lane, has_marks, true, skip);
+                        __syncwarp();
+                    }
+                }
+            } else {
+                done = predict_record(a, tb, b, ws, lane, has_marks, kWait);
+            }
+            __syncwarp();
+            if (!done)
+                continue;
+            if (in_place(b)) {                                            // samples before marks
+                fence_gpu();
+                __syncwarp();
+                set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 2, lane);
+                __syncwarp();
+            }
+            held &= ~(1u << k);
+            progress = true;
+        }
+        if (progress) {
+            backoff = 32;
+        } else {
+            __nanosleep(backoff);
+            backoff = min(backoff * 2, 512u);
+        }
     }
 }
 
