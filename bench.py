@@ -58,7 +58,7 @@ def make_picture(seed, width, height, intra_fraction):
     """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
     with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v8_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
+    cache = "/tmp/vvcb200_bench_v9_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
     kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
              ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):

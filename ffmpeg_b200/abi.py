@@ -59,12 +59,22 @@ def residual_class(tbs):
     return np.where(fast, cls, 4).astype(np.int32)
 
 
-def order_tbs_by_class(tbs, params, extra=()):
-    """Sort a TB batch into class order (ties: larger area first) and record the class sizes in `params`.
-    `extra` arrays (one entry per TB) are permuted alongside.  Returns (tbs, *extra)."""
+def tb_order(tbs):
+    """Permutation into class order; inside a class larger areas first, then grouped by block shape, transform pair
+    and flags, so that warps running side by side execute the same code with the same matrices (not required for
+    correctness: the kernel only needs the class order)."""
     cls = residual_class(tbs)
     area = tbs["log2_w"].astype(np.int32) + tbs["log2_h"]
-    order = np.lexsort((-area, cls))
+    shape = tbs["log2_w"].astype(np.int32) * 8 + tbs["log2_h"]
+    tx = tbs["trh"].astype(np.int32) * 4 + tbs["trv"]
+    flags = tbs["flags"].astype(np.int32) & ~np.int32(TB_INTER)
+    return np.lexsort((flags, tx, shape, -area, cls)), cls
+
+
+def order_tbs_by_class(tbs, params, extra=()):
+    """Sort a TB batch into class order (see tb_order) and record the class sizes in `params`.
+    `extra` arrays (one entry per TB) are permuted alongside.  Returns (tbs, *extra)."""
+    order, cls = tb_order(tbs)
     for c in range(4):
         params.n_class[c] = int(np.sum(cls == c))
     return (np.ascontiguousarray(tbs[order]),) + tuple(np.ascontiguousarray(e[order]) for e in extra)

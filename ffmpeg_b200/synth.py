@@ -984,9 +984,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                                       rng.integers(4, 65, 14).astype(np.uint8))
     else:
         rparams = abi.residual_params(10, 1 if rng.random() < 0.5 else -1)
-    order_cls = abi.residual_class(tbs)
-    area = tbs["log2_w"].astype(np.int32) + tbs["log2_h"]
-    order = np.lexsort((-area, order_cls))
+    order, order_cls = abi.tb_order(tbs)
     for c in range(4):
         rparams.n_class[c] = int(np.sum(order_cls == c))
     ld = (0, 0)
