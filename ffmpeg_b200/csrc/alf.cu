@@ -109,12 +109,25 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
     const int tw = min(kTile, g.x0 + g.w - tx0), th = min(kTile, g.y0 + g.h - ty0);
 
     // ---- stage the tile + halo
-    for (int i = t; i < kPad * kPad; i += 256) {
-        const int r = i / kPad, col = i - r * kPad;
-        const int x = tx0 + col - kHalo, y = ty0 + r - kHalo;
+    {
         // halo positions not clamped by an edge flag are real neighbours inside the picture (picture borders are
-        // always flagged by ctb_geom), so every read is in bounds
-        s_pix[r * kPadStr + col] = (uint16_t)padded_sample(src, sstride, g, x, y);
+        // always flagged by ctb_geom), so every read is in bounds.  All of a thread's loads are issued before the first
+        // store so that they are in flight together (this loop was the kernel's main stall).
+        constexpr int kIter = (kPad * kPad + 255) / 256;
+        uint16_t v[kIter];
+#pragma unroll
+        for (int k = 0; k < kIter; k++) {
+            const int i = t + k * 256;
+            const int r = i / kPad, col = i - r * kPad;
+            v[k] = i < kPad * kPad ? (uint16_t)padded_sample(src, sstride, g, tx0 + col - kHalo, ty0 + r - kHalo) : (uint16_t)0;
+        }
+#pragma unroll
+        for (int k = 0; k < kIter; k++) {
+            const int i = t + k * 256;
+            const int r = i / kPad, col = i - r * kPad;
+            if (i < kPad * kPad)
+                s_pix[r * kPadStr + col] = v[k];
+        }
     }
     __syncthreads();
 
