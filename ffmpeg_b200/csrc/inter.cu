@@ -120,11 +120,21 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
     __syncwarp();
     if (active) {
         // stage the window: a lane owns columns li, li + gs, ... and walks down the rows
+        // (eight loads are issued before the first store so that they are in flight together: the dependent
+        // load -> store walk down the rows was the kernel's main memory stall)
         for (int c = li; c < cols; c += gs) {
             const int sx = clip3(xi - BEFORE + c, fw.x0, fw.x1);
-            for (int r = 0; r < rows; r++) {
-                const int sy = clip3(yi - BEFORE + r, fw.y0, fw.y1);
-                win[r * ws + c] = __ldg(src + (size_t)sy * stride + sx);
+            for (int r0 = 0; r0 < rows; r0 += 8) {
+                uint16_t v[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int sy = clip3(yi - BEFORE + r0 + k, fw.y0, fw.y1);
+                    v[k] = __ldg(src + (size_t)sy * stride + sx);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++)
+                    if (r0 + k < rows)
+                        win[(r0 + k) * ws + c] = v[k];
             }
         }
     }
