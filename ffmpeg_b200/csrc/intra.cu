@@ -1109,23 +1109,21 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
             bool done;
             if (b.mode >= 81) {
                 done = cclm_record(a, b, ws, lane, has_marks, kWait);
-            } else if ((b.flags & VVCB200_IB_ISP) && !b.c_idx) {
+            } else {
                 // ISP: the sub-partitions of the coding block one after the other, each predicted from its
                 // reconstructed predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit.  Everything the
                 // partitions read from outside the block must be there before the first one starts; after that the warp
-                // only ever waits for its own stores.
-                done = kWait || isp_external_ready(a, b, has_marks, lane);
-                if (done) {
-                    const int n_parts = isp_parts(b);
-                    for (int q = 0; q < n_parts; q++) {
-                        VVCB200IntraBlock sub;
-                        const int skip = isp_part(b, q, sub);
-                        predict_record(a, tb, sub, ws, lane, has_marks, true, skip);
-                        __syncwarp();
-                    }
+                // only ever waits for its own stores.  Every other record is a single "partition" (one call site keeps
+                // the kernel's code, and with it the pressure on the instruction cache, small).
+                const bool isp = (b.flags & VVCB200_IB_ISP) && !b.c_idx;
+                const int n_parts = isp ? isp_parts(b) : 1;
+                done = !isp || kWait || isp_external_ready(a, b, has_marks, lane);
+                for (int q = 0; done && q < n_parts; q++) {
+                    VVCB200IntraBlock sub = b;
+                    const int skip = isp ? isp_part(b, q, sub) : 0;
+                    done = predict_record(a, tb, sub, ws, lane, has_marks, kWait || isp, skip);
+                    __syncwarp();
                 }
-            } else {
-                done = predict_record(a, tb, b, ws, lane, has_marks, kWait);
             }
             __syncwarp();
             if (!done)
