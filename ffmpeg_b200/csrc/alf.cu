@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
     __shared__ uint16_t s_grad[kCells * kCells][4];
     __shared__ int16_t  s_coef[64][12];
     __shared__ int16_t  s_clip[64][12];
+    __shared__ uint8_t  s_cls[64];
 
     const int tx0 = blockIdx.x * kTile, ty0 = blockIdx.y * kTile;
     const int W = a.src.w[0], H = a.src.h[0];
@@ -176,8 +177,13 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
             cls += ((dir1 << 1) + 2) * 5;
         else if (hvd1 > 2 * hvd0)
             cls += ((dir1 << 1) + 1) * 5;
-        const int tr = dir_d * 2 + dir_hv;
-
+        s_cls[t] = (uint8_t)(cls | ((dir_d * 2 + dir_hv) << 5));
+    }
+    __syncthreads();
+    // the 64 x 12 coefficient / clip fetches (global tables) spread over the whole CTA instead of 12 in a row on 64 threads
+    for (int i = t; i < 64 * 12; i += 256) {
+        const int blk = i / 12, j = i - blk * 12;
+        const int cls = s_cls[blk] & 31, tr = s_cls[blk] >> 5;
         const int set = cp.filt_set_idx_y;
         const int16_t *coeff;
         const uint8_t *clip_idx = nullptr;
@@ -188,17 +194,12 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
             coeff = a.params->luma_coeff[k][VVC_ALF_APS_CLASS_TO_FILT_MAP[cls]];
             clip_idx = a.params->luma_clip_idx[k][cls];
         }
-#pragma unroll
-        for (int j = 0; j < 12; j++) {
-            // transposition tables of alf_recon_coeff_and_clip (vvc_filter_template.c:386-391)
-            const int i1[12] = { 9, 4, 10, 8, 1, 5, 11, 7, 3, 0, 2, 6 };
-            const int i2[12] = { 0, 3, 2, 1, 8, 7, 6, 5, 4, 9, 10, 11 };
-            const int i3[12] = { 9, 8, 10, 4, 3, 7, 11, 5, 1, 0, 2, 6 };
-            const int idx = tr == 0 ? j : tr == 1 ? i1[j] : tr == 2 ? i2[j] : i3[j];
-            const int ci = clip_idx ? clip_idx[idx] : 0;
-            s_coef[t][j] = coeff[idx];
-            s_clip[t][j] = (int16_t)(1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7)));
-        }
+        // transposition tables of alf_recon_coeff_and_clip (vvc_filter_template.c:386-391), 4 bits per entry
+        const unsigned long long i1 = 0x62037b518a49ull, i2 = 0xba9456781230ull, i3 = 0x62015b734a89ull;
+        const int idx = tr == 0 ? j : (int)(((tr == 1 ? i1 : tr == 2 ? i2 : i3) >> (4 * j)) & 15);
+        const int ci = clip_idx ? clip_idx[idx] : 0;
+        s_coef[blk][j] = coeff[idx];
+        s_clip[blk][j] = (int16_t)(1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7)));
     }
     __syncthreads();
 
