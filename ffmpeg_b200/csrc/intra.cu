@@ -100,9 +100,9 @@ __device__ __forceinline__ void stage_block_async(void *sdst, const void *g, int
 {
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sdst);
     const uint16_t *gp = static_cast<const uint16_t *>(g);
-    const int per_row = w >> 2, n = per_row * h;
+    const int per_row = w >> 2, n = per_row * h, lpr = 31 - __clz(per_row);   // w is a power of two
     for (int i = lane; i < n; i += 32) {
-        const int y = i / per_row, x = (i - y * per_row) << 2;
+        const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
         asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + (y * w + x) * 2), "l"(gp + (size_t)y * gstride + x) : "memory");
     }
 }
@@ -175,9 +175,9 @@ __global__ void intra_mark_kernel(IntraArgs a)
     }
     for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {       // sentinel over everything the record will write
         uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
-        const int per_row = w >> 2;
+        const int per_row = w >> 2, lpr = 31 - __clz(per_row);
         for (int i = lane; i < per_row * h; i += 32) {
-            const int y = i / per_row, x = (i - y * per_row) << 2;
+            const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
             *reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x) = make_uint2(0xffffffffu, 0xffffffffu);
         }
     }

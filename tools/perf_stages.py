@@ -85,8 +85,13 @@ def main():
     k_in = np.arange(len(ia["blocks"])) - cf[ctu_of]
     diag = (ctu_of % cw) + 2 * (ctu_of // cw)
     diag_order = ia["blocks"][np.lexsort((ctu_of // cw, k_in, diag))]
+    nodep = diag_order.copy()                   # same work with every dependency removed: the kernel's throughput floor
+    nodep["avail_top"] = 0
+    nodep["avail_left"] = 0
+    nodep["up_left"] = 0
+    nodep["flags"] &= ~np.uint8(abi.IB_LMCS_SCALE)
     for label, recs in (("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height)),
-                        ("ctu diagonals", diag_order), ("decoding order", ia["blocks"])):
+                        ("ctu diagonals", diag_order), ("decoding order", ia["blocks"]), ("no dependencies", nodep)):
         d = dev(recs)
         ms = timed(torch, lambda: lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks))
         print("intra %-15s %d records  %.4f ms" % (label, len(recs), ms))
