@@ -58,7 +58,7 @@ def make_picture(seed, width, height, intra_fraction):
     """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
     with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v10_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
+    cache = "/tmp/vvcb200_bench_v11_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
     kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
              ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):
@@ -97,7 +97,7 @@ def picture_stats(pic):
     ref_samples = int((b["w"].astype(np.int64) * b["h"] * lists * planes_x2).sum() // 2)
     ib = pic["intra"]["blocks"]
     iw = np.where((ib["flags"] & 4) != 0, ib["cb_w"], ib["w"]).astype(np.int64)      # ISP records stand for the coding block
-    ih = np.where((ib["flags"] & 4) != 0, ib["cb_h"], ib["h"] >> (ib["part"] & 3)).astype(np.int64)   # a part record: its share of the rows
+    ih = np.where((ib["flags"] & 4) != 0, ib["cb_h"], ib["h"]).astype(np.int64)
     cclm = ib["mode"] >= 81
     intra_samples = int((iw * ih * np.where(cclm, 2, 1)).sum())
     intra_bytes = int((2 * iw * ih * np.where(cclm, 2, 1)                                # samples out

@@ -208,7 +208,7 @@ IB_DTYPE = np.dtype([
     ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("c_idx", "u1"), ("mode", "i1"), ("ref_idx", "u1"),
     ("flags", "u1"), ("mip_mode", "u1"), ("up_left", "u1"), ("avail_top", "<u2"), ("avail_left", "<u2"),
     ("cb_w", "u1"), ("cb_h", "u1"), ("ciip_weight", "u1"), ("res_planes", "u1"),
-    ("vpdu_x", "u1"), ("vpdu_y", "u1"), ("vpdu_avail", "u1"), ("part", "u1"), ("reserved2", "<u4"),
+    ("vpdu_x", "u1"), ("vpdu_y", "u1"), ("vpdu_avail", "u1"), ("reserved3", "u1"), ("reserved2", "<u4"),
 ], align=False)
 assert IB_DTYPE.itemsize == 28
 

@@ -672,8 +672,7 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3,
-                  split_large=True):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
@@ -762,18 +761,6 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
 
     vsize = min(ctb, 64)
 
-    def emit_ib(ib):
-        """Append a record; a large block (not ISP) goes out as 2 or 4 records, one per share of its rows, so that
-        several warps of the engine work on it."""
-        n_s = int(ib["w"][0]) * int(ib["h"][0])
-        lg = 0 if (ib["flags"][0] & abi.IB_ISP) or not split_large else 2 if n_s >= 2048 else 1 if n_s >= 1024 else 0
-        while lg and (int(ib["h"][0]) >> lg) < 4:
-            lg -= 1
-        for k in range(1 << lg):
-            r = ib.copy()
-            r["part"] = lg | (k << 2)
-            iblocks.append(r)
-
     def set_vpdu(ib, x, y, ctb_left, ctb_up):
         vx, vy = x & ~(vsize - 1), y & ~(vsize - 1)
         ib["vpdu_x"], ib["vpdu_y"] = vx // vsize, vy // vsize
@@ -789,7 +776,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 ib["flags"] = abi.IB_ADD_ONLY | abi.IB_RESIDUAL
                 ib["cb_w"], ib["cb_h"] = w, h
                 set_vpdu(ib, x, y, ctb_left, ctb_up)
-                emit_ib(ib)
+                iblocks.append(ib)
 
     for ry in range(ch):
         for rx in range(cw):
@@ -859,7 +846,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                             ib["cb_w"], ib["cb_h"] = w, h
                             if c and has_res and lmcs_chroma is not None:
                                 set_vpdu(ib, x, y, ctb_left, ctb_up)
-                            emit_ib(ib)
+                            iblocks.append(ib)
                     elif kind != CU_REGULAR:
                         c = np.zeros(1, CU_DTYPE)
                         c["x0"], c["y0"], c["w"], c["h"] = x, y, w, h
@@ -985,7 +972,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     ib["cb_w"], ib["cb_h"] = w, h
                     if c and (fl & abi.IB_RESIDUAL) and lmcs_chroma is not None:
                         set_vpdu(ib, x, y, ctb_left, ctb_up)
-                    emit_ib(ib)
+                    iblocks.append(ib)
                 done[uy:uy + uh, ux:ux + uw] = True
                 is_intra[uy:uy + uh, ux:ux + uw] = True
                 cus.append(cu)

@@ -360,10 +360,7 @@ typedef struct VVCB200IntraBlock {
     /* VVCB200_IB_LMCS_SCALE: the VPDU of the coding unit's origin, in units of min(CTB size, 64) luma samples, and whether
      * the luma column left of it (bit 0) / the luma row above it (bit 1) is available (ff_vvc_get_left/top_available)     */
     uint8_t  vpdu_x, vpdu_y, vpdu_avail;
-    /* A large block may be emitted as 2 or 4 records that differ only in this field; each reconstructs an equal share of
-     * the block's rows, so that several warps work on it.  Bits 0-1: log2 of the number of shares (h >> that >= 4),
-     * bits 2-3: this record's share.  0 = the whole block.  Not for ISP records. */
-    uint8_t  part;
+    uint8_t  reserved3;
     uint32_t reserved2;
 } VVCB200IntraBlock;            /* 28 bytes */
 

@@ -482,8 +482,6 @@ PORT_EXPORT int port_intra_picture(const PortPlanes *pic, const PortPlanes *resi
     for (int i = 0; i < n; i++) {
         const VVCB200IntraBlock *b = &blocks[i];
         const int c = b->c_idx;
-        if (b->part >> 2)               /* a block emitted as several records (one per share of its rows): the first does it all */
-            continue;
         const int scale = vpdu_chroma_scale(pic, b, ip);
         if (b->flags & VVCB200_IB_ADD_ONLY) {
             if (b->flags & VVCB200_IB_RESIDUAL)
