@@ -126,14 +126,20 @@ __device__ __forceinline__ void sao_edge8(uint32_t (&out)[4], const uint16_t *sr
             b[j] = jb < 0 || jb > 7 ? eb : tb[jb];
         }
     }
-    const int o0 = ov[0], o1 = ov[1], o2 = ov[2], o3 = ov[3], o4 = ov[4];
+    // The five offsets (|offset| < 128 at any bit depth up to 12) packed as bytes in the order of d + 2 = 0..4, so that one
+    // PRMT both selects and sign-extends: selector nibble i picks byte i, bit 3 of a nibble replicates that byte's sign.
+    const uint32_t lo = (uint32_t)(ov[1] & 0xff) | ((uint32_t)(ov[2] & 0xff) << 8) | ((uint32_t)(ov[0] & 0xff) << 16) |
+                        ((uint32_t)(ov[3] & 0xff) << 24);
+    const uint32_t hi = (uint32_t)(ov[4] & 0xff);
     const int pmax = (1 << bd) - 1;
     int r[8];
 #pragma unroll
     for (int j = 0; j < 8; j++) {
         const int s = c[j];
-        const int d = (s > a[j]) - (s < a[j]) + (s > b[j]) - (s < b[j]);
-        const int off = d == 0 ? o0 : d == -2 ? o1 : d == -1 ? o2 : d == 1 ? o3 : o4;
+        // sign(s - a) + sign(s - b) + 2 with clamps instead of four compares
+        const int d2 = min(max(s - (int)a[j], -1), 1) + min(max(s - (int)b[j], -1), 1) + 2;
+        int off;                                                          // (the __byte_perm intrinsic masks the sign-replicate bits)
+        asm("prmt.b32 %0, %1, %2, %3;" : "=r"(off) : "r"(lo), "r"(hi), "r"(d2 * 0x1111 + 0x8880));
         r[j] = min(max(s + off, 0), pmax);
     }
 #pragma unroll
@@ -181,12 +187,15 @@ __global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
         uint16_t s[8];
         *reinterpret_cast<uint4 *>(s) = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
         const int pos = pp->band_position[c], sh = a.bd - 5, pmax = (1 << a.bd) - 1;
-        const int o1 = ov[1], o2 = ov[2], o3 = ov[3], o4 = ov[4];
+        // offsets of the four bands as bytes 0..3, byte 4 = 0 for every other band; one PRMT selects and sign-extends
+        const uint32_t lo = (uint32_t)(ov[1] & 0xff) | ((uint32_t)(ov[2] & 0xff) << 8) | ((uint32_t)(ov[3] & 0xff) << 16) |
+                            ((uint32_t)(ov[4] & 0xff) << 24);
         int r[8];
 #pragma unroll
         for (int j = 0; j < 8; j++) {
-            const int k = ((s[j] >> sh) - pos) & 31;
-            const int off = k == 0 ? o1 : k == 1 ? o2 : k == 2 ? o3 : k == 3 ? o4 : 0;
+            const int k = min(((s[j] >> sh) - pos) & 31, 4);
+            int off;
+            asm("prmt.b32 %0, %1, %2, %3;" : "=r"(off) : "r"(lo), "r"(0u), "r"(k * 0x1111 + 0x8880));
             r[j] = min(max(s[j] + off, 0), pmax);
         }
 #pragma unroll
