@@ -17,6 +17,7 @@ namespace vvcb200 {
 
 constexpr int kTile   = 32;
 constexpr int kHalo   = 3;
+constexpr int kColOrg = 4;                       // staged column of the tile's first sample (even: sample pairs are 32-bit aligned)
 constexpr int kPad    = kTile + 2 * kHalo;       // 38
 constexpr int kPadStr = kPad + 2;                // 40 samples per staged row
 constexpr int kCells  = kTile / 2 + 2;           // 18 gradient cells per tile side
@@ -77,9 +78,10 @@ __device__ __forceinline__ int alf_clip2(int curr, int v0, int v1, int c)
     return clip3(v0 - curr, -c, c) + clip3(v1 - curr, -c, c);
 }
 
-__global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
+__global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
 {
-    __shared__ uint16_t s_pix[kPad * kPadStr];
+    __shared__ __align__(16) uint16_t s_pix[kPad * kPadStr];
+    __shared__ int s_wide;                               // some coefficient of the tile does not fit int8 (never in a conforming stream)
     __shared__ uint16_t s_grad[kCells * kCells][4];
     __shared__ int16_t  s_coef[64][12];
     __shared__ int16_t  s_clip[64][12];
@@ -104,6 +106,8 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
         }
         return;
     }
+    if (t == 0)
+        s_wide = 0;
     const CtbGeom g = ctb_geom(a, 0, tx0, ty0, cp.edges);
     const int vb = (1 << a.ctb_log2) - 4;                // ALF_VB_POS_ABOVE_LUMA, CTB-relative (vvc_filter.c:1304)
     const int ty_ctb = ty0 - g.y0;                       // tile origin inside the CTB
@@ -127,7 +131,7 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
             const int i = t + k * 256;
             const int r = i / kPad, col = i - r * kPad;
             if (i < kPad * kPad)
-                s_pix[r * kPadStr + col] = v[k];
+                s_pix[r * kPadStr + col + kColOrg - kHalo] = v[k];
         }
     }
     __syncthreads();
@@ -135,7 +139,7 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
     // ---- gradients per 2x2 cell (alf_classify first loop); cell (gy, gx) has p0 at tile (2gy-2, 2gx-2)
     for (int i = t; i < kCells * kCells; i += 256) {
         const int gy = i / kCells, gx = i - gy * kCells;
-        const int r0 = 2 * gy - 2 + kHalo, c0 = 2 * gx - 2 + kHalo;     // staged coordinates of p0
+        const int r0 = 2 * gy - 2 + kHalo, c0 = 2 * gx - 2 + kColOrg;   // staged coordinates of p0
         const int ygrad = ty_ctb + 2 * gy;                                // the reference's loop variable y
         int ra = r0 - 1, rb = r0, rc = r0 + 1, rd = r0 + 2;               // s0..s3
         if (ygrad == vb)
@@ -198,7 +202,10 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
         const unsigned long long i1 = 0x62037b518a49ull, i2 = 0xba9456781230ull, i3 = 0x62015b734a89ull;
         const int idx = tr == 0 ? j : (int)(((tr == 1 ? i1 : tr == 2 ? i2 : i3) >> (4 * j)) & 15);
         const int ci = clip_idx ? clip_idx[idx] : 0;
-        s_coef[blk][j] = coeff[idx];
+        const int cf = coeff[idx];
+        if (cf < -128 || cf > 127)
+            s_wide = 1;
+        s_coef[blk][j] = (int16_t)cf;
         s_clip[blk][j] = (int16_t)(1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7)));
     }
     __syncthreads();
@@ -217,11 +224,53 @@ __global__ void __launch_bounds__(256) alf_luma_kernel(const AlfArgs a)
             int o1, o2, o3;
             bool near_vb;
             vb_rows(ty_ctb + row, vb, 3, o1, o2, o3, near_vb);
-            const uint16_t *p0 = s_pix + (row + kHalo) * kPadStr + xg * 4 + kHalo;
+            const uint16_t *p0 = s_pix + (row + kHalo) * kPadStr + xg * 4 + kColOrg;
             const uint16_t *p1 = p0 + o1 * kPadStr, *p2 = p0 - o1 * kPadStr;
             const uint16_t *p3 = p0 + o2 * kPadStr, *p4 = p0 - o2 * kPadStr;
             const uint16_t *p5 = p0 + o3 * kPadStr, *p6 = p0 - o3 * kPadStr;
             uint16_t out[4];
+            if (!s_wide) {
+                // Two samples per 32-bit word through the 16x2 integer pipe (VIADD.16x2 / VIADDMNMX.S16x2 on sm_100a), the
+                // tap products through IDP.2A.  Differences, clips and their sums stay inside int16 for bit depths <= 12.
+                // w(p, k) = staged word k of a row relative to this thread's first sample: samples (2k, 2k + 1).
+                auto w = [](const uint16_t *p, int k) { return reinterpret_cast<const uint32_t *>(p)[k]; };
+                // pair starting at sample s of the row: aligned word for even s, funnel shift of two words for odd s
+                auto pr = [&](const uint16_t *p, int s0) {
+                    return (s0 & 1) ? __funnelshift_r(w(p, (s0 - 1) >> 1), w(p, (s0 + 1) >> 1), 16) : w(p, s0 >> 1);
+                };
+                const uint32_t cA = w(p0, 0), cB = w(p0, 1);               // the four current samples
+                int sum[4] = { 0, 0, 0, 0 };
+                auto tap = [&](int k, const uint16_t *pa, int da, const uint16_t *pb, int db) {
+                    const uint32_t c2 = (uint32_t)cl[k] * 0x10001u, n2 = __vneg2(c2);
+                    const uint32_t tA = __vadd2(__vmaxs2(__vmins2(__vsub2(pr(pa, da), cA), c2), n2),
+                                                __vmaxs2(__vmins2(__vsub2(pr(pb, db), cA), c2), n2));
+                    const uint32_t tB = __vadd2(__vmaxs2(__vmins2(__vsub2(pr(pa, da + 2), cB), c2), n2),
+                                                __vmaxs2(__vmins2(__vsub2(pr(pb, db + 2), cB), c2), n2));
+                    const int flo = f[k] & 0xff, fhi = flo << 8;
+                    sum[0] = __dp2a_lo((int)tA, flo, sum[0]);
+                    sum[1] = __dp2a_lo((int)tA, fhi, sum[1]);
+                    sum[2] = __dp2a_lo((int)tB, flo, sum[2]);
+                    sum[3] = __dp2a_lo((int)tB, fhi, sum[3]);
+                };
+                tap(0, p5, 0, p6, 0);
+                tap(1, p3, 1, p4, -1);
+                tap(2, p3, 0, p4, 0);
+                tap(3, p3, -1, p4, 1);
+                tap(4, p1, 2, p2, -2);
+                tap(5, p1, 1, p2, -1);
+                tap(6, p1, 0, p2, 0);
+                tap(7, p1, -1, p2, 1);
+                tap(8, p1, -2, p2, 2);
+                tap(9, p0, 3, p0, -3);
+                tap(10, p0, 2, p0, -2);
+                tap(11, p0, 1, p0, -1);
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const int curr = p0[j];
+                    const int sv = near_vb ? (sum[j] + 512) >> 10 : (sum[j] + 64) >> 7;
+                    out[j] = (uint16_t)clip_pixel(sv + curr, a.bd);
+                }
+            } else
 #pragma unroll
             for (int j = 0; j < 4; j++) {
                 const int curr = p0[j];
