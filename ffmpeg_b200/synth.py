@@ -75,7 +75,7 @@ _DIAG4 = [(0, 0), (0, 1), (1, 0), (0, 2), (1, 1), (2, 0), (0, 3), (1, 2),
 
 
 def residual_picture(seed, width, height, coded_fraction=1.0, levels="realistic", tools=("mts", "ts", "bdpcm", "lfnst",
-                     "scaling", "joint", "dep_quant"), mean_log2=4.0, max_qp=63, sort=True):
+                     "scaling", "joint", "dep_quant"), mean_log2=4.0, max_qp=63, sort=True, bd=10):
     """One picture's residual batch.
 
     Returns dict(tbs=structured array TB_DTYPE, levels=int16 array, params=abi.ResidualParams,
@@ -166,7 +166,7 @@ def residual_picture(seed, width, height, coded_fraction=1.0, levels="realistic"
     level_buf = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
     sl = rng.integers(4, 65, (28, 64)).astype(np.uint8)
     dc = rng.integers(4, 65, 14).astype(np.uint8)
-    params = abi.residual_params(10, 1 if rng.random() < 0.5 else -1, sl, dc)
+    params = abi.residual_params(bd, 1 if rng.random() < 0.5 else -1, sl, dc)
     tbs, intra_mode = abi.order_tbs_by_class(tbs, params, (intra_mode,))
     return dict(tbs=tbs, levels=level_buf, params=params, intra_mode=intra_mode, seed=seed, dims=dims)
 
@@ -208,7 +208,7 @@ def smooth_planes(seed, dims, bd=10):
     return out
 
 
-def _decorate_blocks(rng, b, tools, n_refs, mv_range=64 * 16, far_mv=0.02, keep_mv=False):
+def _decorate_blocks(rng, b, tools, n_refs, mv_range=64 * 16, far_mv=0.02, keep_mv=False, bd=10):
     """Fill prediction mode, vectors and tool flags of the sub-blocks `b` (geometry already set) and build the
     slice's InterParams.  keep_mv: pred_flag / ref_idx / mv are already there (one vector per coding unit)."""
     n = len(b)
@@ -251,12 +251,12 @@ def _decorate_blocks(rng, b, tools, n_refs, mv_range=64 * 16, far_mv=0.02, keep_
     weight[:, 1:, :] = (1 << ld[1]) + rng.integers(-128, 128, (2, 2, 16))
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
-    params = abi.inter_params(10, ld, weight, offset, ref_slot)
+    params = abi.inter_params(bd, ld, weight, offset, ref_slot)
     return abi.order_blocks_by_width(b, params), params
 
 
 def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel"), mv_range=64 * 16, far_mv=0.02,
-                  inter_fraction=1.0, sizes=(4, 8, 16)):
+                  inter_fraction=1.0, sizes=(4, 8, 16), bd=10):
     """Prediction sub-block batch (<= 16x16) tiling the picture + per-slice InterParams."""
     rng = np.random.default_rng(seed)
     tools = set(tools)
@@ -266,14 +266,14 @@ def inter_picture(seed, width, height, n_refs=2, tools=("bi", "wp", "bcw", "hpel
     n = len(tiles)
     b = np.zeros(n, abi.PB_DTYPE)
     b["x0"], b["y0"], b["w"], b["h"] = tiles[:, 0], tiles[:, 1], tiles[:, 2], tiles[:, 3]
-    b, params = _decorate_blocks(rng, b, tools, n_refs, mv_range, far_mv)
+    b, params = _decorate_blocks(rng, b, tools, n_refs, mv_range, far_mv, bd=bd)
     dims = plane_dims(width, height)
-    refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
+    refs = [smooth_planes(seed * 31 + i, dims, bd) for i in range(n_refs)]
     return dict(blocks=b, params=params, refs=refs, dims=dims, seed=seed)
 
 
 # ---- deblocking --------------------------------------------------------------------------------------------
-def deblock_picture(seed, width, height, ctb_log2=7, ladf=None, bs_prob=(0.25, 0.4, 0.35)):
+def deblock_picture(seed, width, height, ctb_log2=7, ladf=None, bs_prob=(0.25, 0.4, 0.35), bd=10):
     """Per-4x4 deblocking tables in the REFERENCE's format (fc->tab.vertical_bs & co, vvcdec.h:158-163), derived
     from a random TB partition with the reference's own length rules (vvc_filter.c:374-397, 418-427) so that
     neighbouring edges never overlap, plus QP tables, per-CTB offsets and LADF parameters."""
@@ -335,7 +335,7 @@ def deblock_picture(seed, width, height, ctb_log2=7, ladf=None, bs_prob=(0.25, 0
     n_ctb = ((width + (1 << ctb_log2) - 1) >> ctb_log2) * ((height + (1 << ctb_log2) - 1) >> ctb_log2)
     ctb_offsets = rng.integers(-12, 13, (n_ctb, 6)).astype(np.int8)
     p = abi.DeblockParams()
-    p.bit_depth, p.ctb_log2_size = 10, ctb_log2
+    p.bit_depth, p.ctb_log2_size = bd, ctb_log2
     use_ladf = bool(rng.random() < 0.5) if ladf is None else ladf
     if use_ladf:
         p.ladf_enabled, p.num_ladf_intervals = 1, 4
@@ -430,7 +430,7 @@ def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on
     p["cc_coeff"] = rng.integers(-64, 64, (2, 4, 7))
     p["cc_enabled"] = 1
     return dict(sao=sao, alf=alf, alf_params=p, slice_idx=slices, lfase=lfase, ctb_log2=ctb_log2,
-                dims=plane_dims(width, height), seed=seed)
+                dims=plane_dims(width, height), seed=seed, bd=bd)
 
 
 def lmcs_luts(seed, bd=10):
@@ -457,45 +457,45 @@ def lmcs_model(seed, fwd, bd=10):
 
 # ---- a whole picture --------------------------------------------------------------------------------------------
 def full_picture(seed, width, height, ctb_log2=7, n_refs=2, coded_fraction=1.0, lmcs=False, n_slices=1, lfase=1,
-                 residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3, intra_fraction=0.0):
+                 residual_tools=("mts", "ts", "lfnst", "scaling", "joint", "dep_quant"), mean_log2=4.3, intra_fraction=0.0, bd=10):
     """All descriptor batches of one inter picture (BASELINE config 2/3 shape): prediction sub-blocks, residual TBs,
     deblocking tables, SAO/ALF CTB parameters.  Stage inputs are generated independently of each other (the
     arithmetic of every stage takes its tables as given); see DESIGN.md for what a real parser adds."""
     if intra_fraction > 0:
         return _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2,
-                                        intra_fraction)
-    inter = inter_picture(seed, width, height, n_refs=n_refs, tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"))
+                                        intra_fraction, bd)
+    inter = inter_picture(seed, width, height, n_refs=n_refs, tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"), bd=bd)
     res = residual_picture(seed + 1, width, height, coded_fraction=coded_fraction, tools=residual_tools,
-                           mean_log2=mean_log2)
+                           mean_log2=mean_log2, bd=bd)
     # every residual TB of an inter picture belongs to an inter CU
     res["tbs"]["flags"] |= abi.TB_INTER
     res["tbs"]["flags"] &= ~np.uint16(abi.TB_BDPCM | abi.TB_BDPCM_VERT)
     res["tbs"]["lfnst"] = 0          # LFNST is intra-only; its TBs stay as plain DCT2 blocks
     res["tbs"], res["intra_mode"] = abi.order_tbs_by_class(res["tbs"], res["params"], (res["intra_mode"],))
-    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
-    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
+    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2, bd=bd)
+    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase, bd=bd)
     out = dict(inter=inter, residual=res, deblock=db, lf=lf, dims=inter["dims"], ctb_log2=ctb_log2, seed=seed,
-               width=width, height=height, lmcs=None)
+               width=width, height=height, lmcs=None, bd=bd)
     if lmcs:
-        out["lmcs"] = lmcs_luts(seed + 4)
+        out["lmcs"] = lmcs_luts(seed + 4, bd)
         inter["blocks"]["flags"] |= abi.PB_LMCS
     return out
 
 
-def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2, intra_fraction):
+def _full_picture_with_intra(seed, width, height, ctb_log2, n_refs, lmcs, n_slices, lfase, mean_log2, intra_fraction, bd=10):
     """full_picture() over ONE coding-unit partition: every CU is inter (prediction sub-blocks, TBs added in place) or
     intra (records for the wavefront, TBs routed through the residual planes), as in a P/B picture with intra CUs."""
-    luts = lmcs_luts(seed + 4) if lmcs else None
+    luts = lmcs_luts(seed + 4, bd) if lmcs else None
     rp = recon_picture(seed, width, height, ctb_log2=ctb_log2, intra_fraction=intra_fraction, n_refs=n_refs,
-                       lmcs_chroma=lmcs_model(seed + 5, luts[0]) if lmcs else None,
+                       lmcs_chroma=lmcs_model(seed + 5, luts[0], bd) if lmcs else None, bd=bd,
                        tools=("mrl", "mip", "cclm", "pdpc", "isp", "bdpcm", "ciip", "mts", "ts", "lfnst", "joint",
                               "dep_quant", "scaling"), mean_log2=mean_log2,
                        inter_tools=("bi", "wp", "bcw", "hpel", "dmvr", "bdof"),
                        inter_kinds=(CU_REGULAR,) * 7 + (CU_AFFINE,) * 2 + (CU_GPM,), lmcs=lmcs, ciip_share=0.1)
-    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2)
-    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase)
+    db = deblock_picture(seed + 2, width, height, ctb_log2=ctb_log2, bd=bd)
+    lf = loopfilter_ctbs(seed + 3, width, height, ctb_log2=ctb_log2, n_slices=n_slices, lfase=lfase, bd=bd)
     out = dict(inter=rp["inter"], residual=rp["residual"], intra=rp["intra"], ref=rp["ref"], deblock=db, lf=lf,
-               dims=rp["dims"], ctb_log2=ctb_log2, seed=seed, width=width, height=height, lmcs=None)
+               dims=rp["dims"], ctb_log2=ctb_log2, seed=seed, width=width, height=height, lmcs=None, bd=bd)
     out["residual"]["intra_mode"] = np.zeros(len(rp["residual"]["tbs"]), np.int32)
     if lmcs:
         out["lmcs"] = luts
@@ -672,7 +672,7 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3, bd=10):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
@@ -980,20 +980,20 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     tbs = np.concatenate(tbs) if tbs else np.zeros(0, abi.TB_DTYPE)
     levels = np.concatenate(lv_chunks) if lv_chunks else np.zeros(0, np.int16)
     if pic_flags & abi.TB_SCALING:
-        rparams = abi.residual_params(10, 1 if rng.random() < 0.5 else -1, rng.integers(4, 65, (28, 64)).astype(np.uint8),
+        rparams = abi.residual_params(bd, 1 if rng.random() < 0.5 else -1, rng.integers(4, 65, (28, 64)).astype(np.uint8),
                                       rng.integers(4, 65, 14).astype(np.uint8))
     else:
-        rparams = abi.residual_params(10, 1 if rng.random() < 0.5 else -1)
+        rparams = abi.residual_params(bd, 1 if rng.random() < 0.5 else -1)
     order, order_cls = abi.tb_order(tbs)
     for c in range(4):
         rparams.n_class[c] = int(np.sum(order_cls == c))
     ld = (0, 0)
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.arange(n_refs)
-    iparams = abi.inter_params(10, ld, None, None, ref_slot)
+    iparams = abi.inter_params(bd, ld, None, None, ref_slot)
     if pblocks and inter_tools is not None:     # the tool mix of inter_picture() on this picture's inter CUs
         pb, iparams = _decorate_blocks(np.random.default_rng(seed + 77), np.concatenate(pblocks), set(inter_tools), n_refs,
-                                       keep_mv=True)
+                                       keep_mv=True, bd=bd)
     else:
         pb = abi.order_blocks_by_width(np.concatenate(pblocks), iparams) if pblocks else np.zeros(0, abi.PB_DTYPE)
     if lmcs:
@@ -1002,9 +1002,9 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     if cu_blocks:                               # one batch for the engine: regular sub-blocks + affine / GPM records
         pb = abi.order_blocks_by_width(np.concatenate([pb] + cu_blocks), iparams)
     dims = plane_dims(width, height)
-    refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
+    refs = [smooth_planes(seed * 31 + i, dims, bd) for i in range(n_refs)]
     ip = abi.IntraParams()
-    ip.bit_depth, ip.ctb_log2_size, ip.chroma_vertical_collocated = 10, ctb_log2, int(rng.integers(0, 2))
+    ip.bit_depth, ip.ctb_log2_size, ip.chroma_vertical_collocated = bd, ctb_log2, int(rng.integers(0, 2))
     if lmcs_chroma is not None:
         ip.lmcs_chroma_scale = 1
         ip.lmcs_pivot[:] = [int(v) for v in lmcs_chroma["pivot"]]
@@ -1019,4 +1019,4 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
         residual=dict(tbs=np.ascontiguousarray(tbs[order]), levels=levels, params=rparams),
         intra=dict(blocks=np.concatenate(iblocks) if iblocks else np.zeros(0, abi.IB_DTYPE),
                    ctu_first=np.array(ctu_first, np.uint32), params=ip),
-        dims=dims, ctb_log2=ctb_log2, width=width, height=height, seed=seed)
+        dims=dims, ctb_log2=ctb_log2, width=width, height=height, seed=seed, bd=bd)

@@ -73,7 +73,8 @@ def deblock_picture(planes, edge, qp, ctb_offsets, stride4, params):
     lib().port_deblock_picture(C.byref(pl), C.byref(t), C.byref(params))
 
 
-def sao_picture(dst, src, lf, bit_depth=10):
+def sao_picture(dst, src, lf, bit_depth=None):
+    bit_depth = lf.get("bd", 10) if bit_depth is None else bit_depth
     d, s = abi.host_planes(dst), abi.host_planes(src)
     sao = np.ascontiguousarray(lf["sao"])
     lib().port_sao_picture(C.byref(d), C.byref(s), C.c_void_p(sao.ctypes.data), int(lf["ctb_log2"]), bit_depth)

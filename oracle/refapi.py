@@ -123,9 +123,10 @@ def deblock_picture(planes, t, threads=1):
         _parallel(lambda a, b: lib().vvcref_deblock_picture(*args, mask, a, b), chunks)
 
 
-def sao_picture(planes, lf, bit_depth=10, threads=1):
+def sao_picture(planes, lf, bit_depth=None, threads=1):
     """Reference SAO stage in place; `lf` is synth.loopfilter_ctbs().  Phase 1 saves every CTB's pre-SAO borders,
     phase 2 filters; each phase may run CTB rows on several threads."""
+    bit_depth = lf.get("bd", 10) if bit_depth is None else bit_depth
     pl = abi.host_planes(planes)
     sao = np.ascontiguousarray(lf["sao"])
     sl = np.ascontiguousarray(lf["slice_idx"], np.int16)

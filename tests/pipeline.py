@@ -21,7 +21,7 @@ def oracle_picture(pic):
         else:
             refapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], rs["intra_mode"])
         if inv is not None:
-            refapi.lmcs_picture(planes, inv, pic["ctb_log2"])
+            refapi.lmcs_picture(planes, inv, pic["ctb_log2"], pic.get("bd", 10))
         refapi.deblock_picture(planes, db)
         refapi.sao_picture(planes, lf)
         refapi.alf_picture(planes, lf)

@@ -68,6 +68,25 @@ def test_back_to_back_pictures_overlap_safely():
         ctx.close()
 
 
+@pytest.mark.parametrize("seed,w,h,ctb,lmcs,frac", [(41, 256, 128, 6, False, 0.0), (42, 256, 128, 5, True, 0.0),
+                                                    (43, 208, 120, 6, True, 0.4), (44, 416, 240, 7, False, 1.0),
+                                                    (45, 832, 480, 7, True, 0.2)])
+def test_full_picture_12_bit_md5(seed, w, h, ctb, lmcs, frac):
+    """Every stage at bit depth 12 (16-bit containers, as in the reference's BIT_DEPTH 12 templates)."""
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=lmcs, intra_fraction=frac, bd=12)
+    want = pipeline.oracle_picture(pic)
+    ctx = lib.Context(0, w, h, bit_depth=12, dpb_size=4)
+    try:
+        ep = pipeline.EnginePicture(ctx, pic)
+        ep.upload_refs()
+        for _ in range(2):
+            ep.run()
+            ctx.sync()
+            assert util.plane_md5(ep.out) == util.plane_md5(want)
+    finally:
+        ctx.close()
+
+
 def test_full_picture_1080p_md5():
     """BASELINE config 2 size: 1080p full picture recon + deblock + SAO + ALF."""
     pic = synth.full_picture(11, 1920, 1080)
