@@ -625,7 +625,7 @@ REF_CU_DTYPE = np.dtype([
     ("mip_flag", "<i4"), ("mip_transposed", "<i4"), ("mip_mode", "<i4"), ("mip_chroma_direct", "<i4"),
     ("isp_split_type", "<i4"), ("num_intra_subpartitions", "<i4"), ("bdpcm_flag", "<i4", (3,)), ("ciip_flag", "<i4"),
     ("coded_flag", "<i4"), ("first_tu", "<i4"), ("n_tu", "<i4"), ("mts_idx", "<i4"), ("lfnst_idx", "<i4"),
-    ("inter_flags", "<i4"), ("pred_flag", "<i4"), ("ref_idx", "<i4", (2,)), ("mv", "<i4", (2, 2)),
+    ("inter_flags", "<i4"), ("pred_flag", "<i4"), ("ref_idx", "<i4", (2,)), ("mv", "<i4", (2, 2)), ("tree_type", "<i4"),
 ])                                  # mirrors VVCRefCU (oracle/ref/api_common.h)
 REF_TU_DTYPE = np.dtype([
     ("x0", "<i4"), ("y0", "<i4"), ("w", "<i4"), ("h", "<i4"), ("coded_flag", "<i4", (3,)), ("joint", "<i4"),
@@ -672,7 +672,8 @@ def _avail(mask, x, y, horizontal, limit):
 
 
 def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2, tools=("mrl", "mip", "cclm", "pdpc"),
-                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3, bd=10):
+                  mean_log2=4.3, inter_tools=None, inter_kinds=None, lmcs=False, lmcs_chroma=None, ciip_share=0.3, bd=10,
+                  dual_tree=False):
     """A picture with intra and inter coding units.  Returns
          ref:   CU / TU arrays + TBs for the reference harness (vvcref_recon_picture), decoding order per CTU,
          inter: prediction sub-block batch of the inter CUs (stage INTER),
@@ -683,6 +684,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     "scaling" ("pdpc" is always on, it is not signalled).  inter_tools: block-level tool mix of inter_picture() on the
     regular inter CUs; inter_kinds: CU kinds to draw from (CU_REGULAR, CU_AFFINE, CU_GPM) — affine / GPM units come with
     their CU-level description (`inter.cus`, `inter.sb_mv`) for the reference harness and PROF tables (`inter.prof`).
+    dual_tree: an I picture with separate luma and chroma partitions (every unit intra; per 64x64 region the luma
+    units come first, then the chroma units, vvc_ctu.c dual_tree_implicit_qt_split); intra_fraction is ignored.
     lmcs_chroma: an lmcs_model() -> luma-dependent chroma residual scaling: every chroma TB goes through the residual
     planes and every chroma block with a residual gets a record (intra, or add-only for inter units).
     Neighbour availability follows the reference's rules (vvc_intra.c:593-648) on a 4x4-unit reconstruction mask."""
@@ -691,7 +694,9 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     ctb = 1 << ctb_log2
     cw, ch = (width + ctb - 1) >> ctb_log2, (height + ctb - 1) >> ctb_log2
     u4w, u4h = (width + 3) >> 2, (height + 3) >> 2
-    done = np.zeros((u4h, u4w), bool)               # luma and chroma become available together (single tree)
+    done_l = np.zeros((u4h, u4w), bool)             # reconstructed luma / chroma, per 4x4 luma unit (one and the same
+    done_c = done_l if not dual_tree else np.zeros((u4h, u4w), bool)   # map in single-tree pictures)
+    luma_mode = np.zeros((u4h, u4w), np.int16)      # IntraPredModeY per unit (0 for MIP), for the chroma DM mode
     cus, tus, tbs, lv_chunks = [], [], [], []
     pblocks, iblocks, ctu_first = [], [], [0]
     cu_blocks, cu_recs, sb_mv, prof = [], [], [], []     # affine / GPM coding units
@@ -782,16 +787,33 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
         for rx in range(cw):
             rs = ry * cw + rx
             regions = []
-            _split_cu(rng, rx * ctb, ry * ctb, ctb, ctb, width, height, 8, mean_log2, regions)
+            if not dual_tree:
+                tmp = []
+                _split_cu(rng, rx * ctb, ry * ctb, ctb, ctb, width, height, 8, mean_log2, tmp)
+                regions = [r + (0,) for r in tmp]
+            else:                                   # tree 1 = luma units, 2 = chroma units, per region of at most 64x64
+                rsz = min(ctb, 64)
+                for qy in range(0, ctb, rsz):
+                    for qx in range(0, ctb, rsz):
+                        for tree in (1, 2):
+                            tmp = []
+                            _split_cu(rng, rx * ctb + qx, ry * ctb + qy, rsz, rsz, width, height, 8, mean_log2, tmp)
+                            regions += [r + (tree,) for r in tmp]
             ctb_left, ctb_up = rx > 0, ry > 0
-            for (x, y, w, h) in regions:
+            for (x, y, w, h, tree) in regions:
+                done = done_c if tree == 2 else done_l
                 cu = np.zeros(1, REF_CU_DTYPE)
-                intra = rng.random() < intra_fraction
+                cu["tree_type"] = tree
+                intra = dual_tree or rng.random() < intra_fraction
                 cu["x0"], cu["y0"], cu["w"], cu["h"], cu["ctu"] = x, y, w, h, rs
                 cu["pred_mode"] = MODE_INTRA if intra else MODE_INTER
                 cu["first_tu"], cu["n_tu"] = len(tus), 1
                 cu["coded_flag"] = 1                    # the reference only skips reconstruct() for uncoded CUs
                 coded = rng.random(3) < 0.8
+                if tree == 1:
+                    coded[1:] = False               # a luma unit of a dual tree has no chroma
+                elif tree == 2:
+                    coded[0] = False
                 qp_y, qp_c = int(rng.integers(14, 60)), int(rng.integers(14, 60))
                 ux, uy, uw, uh = x >> 2, y >> 2, w >> 2, h >> 2
                 if not intra:
@@ -878,9 +900,11 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 # ---- luma tool: MIP | MRL | ISP | BDPCM | plain
                 mode_y = int(rng.choice([0, 1, 18, 50] + list(range(2, 67))))
                 ref_idx, isp, bdpcm_y, lfnst_idx = 0, 0, 0, 0
-                mip = "mip" in tools and rng.random() < 0.15
+                mip = tree != 2 and "mip" in tools and rng.random() < 0.15
                 r = rng.random()
-                if mip:
+                if tree == 2:       # chroma unit: its DM mode is the luma mode at the centre of the co-located area
+                    mode_y = int(luma_mode[(y + h // 2) >> 2, (x + w // 2) >> 2])
+                elif mip:
                     cu["mip_flag"], cu["mip_transposed"] = 1, int(rng.integers(0, 2))
                     size_id = 0 if (w == 4 and h == 4) else 1 if (w == 4 or h == 4 or (w == 8 and h == 8)) else 2
                     cu["mip_mode"] = int(rng.integers(0, (16, 8, 6)[size_id]))
@@ -898,7 +922,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 choices = [0, 1, 18, 50, mode_y] + ([CCLM_LT, CCLM_L, CCLM_T] if "cclm" in tools else [])
                 mode_c = int(rng.choice(choices))
                 bdpcm_c = 0
-                if "bdpcm" in tools and w <= 64 and h <= 64 and rng.random() < 0.12:
+                if tree != 1 and "bdpcm" in tools and w <= 64 and h <= 64 and rng.random() < 0.12:
                     bdpcm_c = int(rng.integers(1, 3))
                     mode_c = 18 if bdpcm_c == 1 else 50
                 cu["intra_pred_mode_c"] = mode_c
@@ -906,7 +930,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 # ---- luma transform: TS | LFNST | explicit MTS | DCT2 (ISP: implicit MTS per sub-partition)
                 trh = trv = 0
                 ts_y = bool(bdpcm_y) or ("ts" in tools and not isp and w <= 32 and h <= 32 and rng.random() < 0.08)
-                if not ts_y and not isp:
+                if not ts_y and not isp and tree != 2:
                     if "lfnst" in tools and (not mip or min(w, h) >= 16) and rng.random() < 0.3:
                         lfnst_idx = int(rng.integers(1, 3))
                     elif "mts" in tools and w <= 32 and h <= 32 and rng.random() < 0.3:
@@ -934,13 +958,13 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     if c0:
                         code = lfnst_code(lfnst_idx, mode_y, w, h, 0) if lfnst_idx else 0
                         tu["tb"][0, 0] = new_tb(tx, ty, 0, pw, ph, False, trh, trv, qp_y, True, ts=ts_y, bdpcm=bdpcm_y, lfnst=code)
-                    if k == n_parts - 1:
+                    if k == n_parts - 1 and tree != 1:
                         tu["coded_flag"][0, 1], tu["coded_flag"][0, 2] = int(coded[1]), int(coded[2])
                         # chroma TBs of an ISP unit cover the whole coding block (vvc_ctu.c hls_transform_unit)
                         res_c = chroma_tbs(tu, x, y, w, h, False, qp_c, coded, True, bdpcm_c)
                     tus.append(tu)
                 # ---- records for the engine
-                for c in (0, 1, 2):
+                for c in ((0, 1, 2), (0,), (1, 2))[tree]:
                     hs = 1 if c else 0
                     bw, bh = w >> hs, h >> hs
                     raw = mode_y if c == 0 else mode_c
@@ -975,6 +999,8 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     iblocks.append(ib)
                 done[uy:uy + uh, ux:ux + uw] = True
                 is_intra[uy:uy + uh, ux:ux + uw] = True
+                if tree != 2:
+                    luma_mode[uy:uy + uh, ux:ux + uw] = mode_y
                 cus.append(cu)
             ctu_first.append(len(iblocks))
     tbs = np.concatenate(tbs) if tbs else np.zeros(0, abi.TB_DTYPE)

@@ -45,6 +45,7 @@ typedef struct VVCRefCU {
     /* CIIP units (ciip_flag): the merge motion the reference predicts from inside RECON (vvc_intra.c:515-516) */
     int32_t inter_flags;                /* VVCB200_PB_WP / HPEL_IF / LMCS */
     int32_t pred_flag, ref_idx[2], mv[2][2];
+    int32_t tree_type;                  /* 0 SINGLE_TREE, 1 DUAL_TREE_LUMA, 2 DUAL_TREE_CHROMA (vvc_ctu.h) */
 } VVCRefCU;
 
 typedef struct VVCRefTU {

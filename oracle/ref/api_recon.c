@@ -339,7 +339,7 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
             }
             *tail = cu;
             tail = &cu->next;
-            cu->tree_type = SINGLE_TREE;
+            cu->tree_type = d->tree_type == 1 ? DUAL_TREE_LUMA : d->tree_type == 2 ? DUAL_TREE_CHROMA : SINGLE_TREE;
             cu->x0 = d->x0; cu->y0 = d->y0; cu->cb_width = d->w; cu->cb_height = d->h;
             cu->pred_mode = d->pred_mode ? MODE_INTRA : MODE_INTER;
             cu->coded_flag = d->coded_flag;
@@ -371,6 +371,8 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
                 for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++) {
                     const size_t o = (size_t)y * mcw + x;
                     MvField *mvf = &e->fc.tab.mvf[o];
+                    if (d->tree_type == 2)
+                        continue;                               /* the per-unit tables describe the luma tree */
                     mvf->pred_flag = d->pred_mode ? PF_INTRA : d->ciip_flag ? d->pred_flag : PF_L0;
                     mvf->ciip_flag = d->ciip_flag;
                     if (d->ciip_flag) {

@@ -98,3 +98,13 @@ def test_empty_picture_is_a_noop():
     ip.bit_depth, ip.ctb_log2_size = 10, 7
     lib.intra_picture(lib.device_planes(dev), None, None, 0, ip, None)
     assert all(np.array_equal(a, b) for a, b in zip(util.from_device_planes(dev), before))
+
+
+@pytest.mark.parametrize("seed,w,h,ctb", [(61, 208, 120, 6), (62, 136, 72, 5), (63, 256, 192, 7), (64, 832, 480, 7)])
+def test_dual_tree_picture_matches_oracle(seed, w, h, ctb):
+    """I picture with separate luma and chroma partitions, as all-intra streams are coded."""
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=ALL_TOOLS, dual_tree=True)
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    got = run_gpu(pic)[0]
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)

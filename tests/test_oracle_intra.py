@@ -74,3 +74,16 @@ def test_schedule_is_a_topological_permutation(seed, w, h, ctb, order):
         first_row1 = next(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 1)
         last_row0 = max(i for i, r in enumerate(order) if r["y0"] >> (ctb - (1 if r["c_idx"] else 0)) == 0)
         assert first_row1 < last_row0
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("seed,w,h,ctb", [(61, 208, 120, 6), (62, 136, 72, 5), (63, 256, 192, 7)])
+def test_port_matches_reference_on_dual_tree_pictures(seed, w, h, ctb):
+    """I pictures with separate luma and chroma partitions (DUAL_TREE_LUMA / DUAL_TREE_CHROMA units): chroma blocks have
+    their own availability and take their DM mode / CCLM luma from a differently partitioned luma plane."""
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=ALL_TOOLS, dual_tree=True)
+    want = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+    refapi.recon_picture(want, pic["ref"], pic["intra"]["params"], inter=pic["inter"])
+    got = _port(pic)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs" % c
