@@ -391,7 +391,8 @@ def main():
     torch.cuda.empty_cache()
 
     # ---- end-to-end arm: Level-B C ABI, pinned host buffers, H2D + D2H inside the timed region ------------------
-    ctx = lib.Context(local, width, height, dpb_size=len(it["refs"]) + 2)   # two slots: download overlaps the next picture
+    ctx = lib.Context(local, width, height, dpb_size=len(it["refs"]) + 2,   # two slots: download overlaps the next picture
+                      validate=1)                                         # the library's default batch checks
     ep = pipeline.EnginePicture(ctx, pic)
     ep.upload_refs()                       # reference pictures are earlier outputs of the same decoder: resident
     e2e_steps = max(3, min(args.steps, 40))

@@ -86,6 +86,7 @@ struct VVCB200Ctx {
     int cur = 0;
     StageSet sets[2];
     int set = 0;
+    int validate = 1;              // 0: trust the emitter, 1: spot checks (class boundaries + every 64th record), 2: every record
     DevBuffer intra_marks;
 };
 
@@ -270,6 +271,16 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
     return 0;
 }
 
+int vvcb200_ctx_set_validation(VVCB200Ctx *c, int level)
+{
+    if (!c || level < 0 || level > 2) {
+        set_error("vvcb200_ctx_set_validation: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    c->validate = level;
+    return 0;
+}
+
 void *vvcb200_ctx_stream(VVCB200Ctx *c) { return c ? (void *)c->stream : nullptr; }
 
 int vvcb200_ctx_planes(VVCB200Ctx *c, int slot, VVCB200Planes *out)
@@ -360,7 +371,11 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     }
     if (n == 0)
         return 0;
-    for (int i = 0; i < n; i++) {           // the batch must come in width order (cheap to check, fatal to get wrong)
+    // the batch must come in width order (fatal to get wrong); how thoroughly that is checked is the caller's choice
+    const int b16 = params->n_w16, b8 = params->n_w16 + params->n_w8;
+    for (int i = 0; i < n && c->validate; i++) {
+        if (c->validate == 1 && (i & 63) && i != b16 - 1 && i != b16 && i != b8 - 1 && i != b8 && i != n - 1)
+            continue;
         const int want = i < params->n_w16 ? 16 : i < params->n_w16 + params->n_w8 ? 8 : 4;
         if (blocks[i].w != want) {
             set_error("vvcb200_pic_inter: block %d has width %d where the width order (n_w16 %d, n_w8 %d) wants %d",
@@ -434,9 +449,11 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
             bound[k] = acc;
         }
         bound[4] = n;
-        for (int i = 0, k = 0; i < n; i++) {
+        for (int i = 0, k = 0; i < n && c->validate; i++) {
             while (k < 4 && i >= bound[k])
                 k++;
+            if (c->validate == 1 && (i & 63) && i != n - 1 && !(k < 4 && (i == bound[k] - 1)) && !(k > 0 && i == bound[k - 1]))
+                continue;
             if (vvcb200_residual_class(&tbs[i]) != k) {
                 set_error("vvcb200_pic_residual: block %d is of class %d where the class order (n_class %d %d %d %d) wants %d",
                           i, vvcb200_residual_class(&tbs[i]), params->n_class[0], params->n_class[1], params->n_class[2],
@@ -491,6 +508,9 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
     bool needs_res = false;
     for (int i = 0; i < n; i++) {
         const VVCB200IntraBlock &b = blocks[i];
+        needs_res |= (b.flags & VVCB200_IB_RESIDUAL) != 0;
+        if (!c->validate || (c->validate == 1 && (i & 63) && i != n - 1))
+            continue;
         const int pw = b.c_idx ? c->width >> c->hshift : c->width, ph = b.c_idx ? c->height >> c->vshift : c->height;
         if (b.c_idx > 2 || !b.w || !b.h || b.w > 64 || b.h > 64 || (b.w & (b.w - 1)) || (b.h & (b.h - 1)) ||
             b.x0 + b.w > pw || b.y0 + b.h > ph || (b.x0 & 3) || (b.y0 & (b.c_idx ? 1 : 3)) || b.mode > 83 || b.mode < -14 ||
@@ -499,7 +519,6 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
                       i, b.c_idx, b.w, b.h, b.x0, b.y0, b.mode);
             return VVCB200_ERR_ARG;
         }
-        needs_res |= (b.flags & VVCB200_IB_RESIDUAL) != 0;
     }
     if (needs_res && !c->residual.base) {
         set_error("vvcb200_pic_intra: records add a residual but vvcb200_pic_residual stored none for this picture");

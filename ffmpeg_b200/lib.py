@@ -126,10 +126,11 @@ class Context:
     """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use
     pinned() to allocate page-locked ones (needed for asynchronous copies)."""
 
-    def __init__(self, device, width, height, bit_depth=10, chroma_format_idc=1, dpb_size=3):
+    def __init__(self, device, width, height, bit_depth=10, chroma_format_idc=1, dpb_size=3, validate=2):
         self._h = C.c_void_p()
         check(load().vvcb200_ctx_create(C.byref(self._h), int(device), int(width), int(height),
                                         int(chroma_format_idc), int(bit_depth), int(dpb_size)))
+        check(load().vvcb200_ctx_set_validation(self._h, int(validate)))    # tests check every record; see the header
         self.width, self.height, self.bit_depth, self.dpb_size = width, height, bit_depth, dpb_size
         self._pinned = []
         self._keep = []

@@ -444,6 +444,10 @@ VVCB200_API int  vvcb200_ctx_create(VVCB200Ctx **ctx, int device, int width, int
                                     int chroma_format_idc, int bit_depth, int dpb_size);
 VVCB200_API void vvcb200_ctx_destroy(VVCB200Ctx *ctx);
 VVCB200_API int  vvcb200_ctx_sync(VVCB200Ctx *ctx);
+/* How thoroughly vvcb200_pic_* check the order and geometry of the host batches before uploading them:
+ * 0 = not at all (the reference trusts its parser too), 1 = class boundaries and every 64th record (default),
+ * 2 = every record (costs ~0.5 ms of host time per 4K picture; what the tests use). */
+VVCB200_API int  vvcb200_ctx_set_validation(VVCB200Ctx *ctx, int level);
 /* cudaStream_t of the context (for callers that enqueue their own work or record events on it). */
 VVCB200_API void *vvcb200_ctx_stream(VVCB200Ctx *ctx);
 /* Device planes of DPB slot `slot` (slot < 0: the picture under reconstruction, fc->frame, vvcdec.h:96). */
