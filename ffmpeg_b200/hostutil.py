@@ -1,0 +1,97 @@
+"""Host-side helpers around the C ABI that tests, bench.py and smoke() share.  Nothing here touches oracle/."""
+import hashlib
+
+import numpy as np
+
+from . import lib
+
+
+def md5(a):
+    return hashlib.md5(np.ascontiguousarray(a).tobytes()).hexdigest()
+
+
+def plane_md5(planes):
+    """Per-plane MD5 of the visible samples (what the reference's framemd5 hashes)."""
+    return [md5(np.ascontiguousarray(p)) for p in planes]
+
+
+def to_device_planes(planes_np, torch, align=64):
+    """Upload numpy planes into pitch-padded torch CUDA tensors (views of width w)."""
+    out = []
+    for p in planes_np:
+        h, w = p.shape
+        stride = (w + align - 1) // align * align
+        t = torch.zeros((h, stride), dtype=torch.int16, device="cuda")
+        t[:, :w] = torch.from_numpy(p.view(np.int16)).cuda()
+        out.append(t[:, :w])
+    return out
+
+
+def from_device_planes(tensors):
+    return [t.cpu().numpy().view(np.uint16) for t in tensors]
+
+
+class EnginePicture:
+    """Pinned host copies of one picture's batches + the Level-B call sequence (HOST buffers in, HOST planes out)."""
+
+    def __init__(self, ctx, pic):
+        it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
+        self.ctx, self.pic = ctx, pic
+        self.n_refs = len(it["refs"])
+        self.refs = [[ctx.pinned_copy(np.ascontiguousarray(p)) for p in r] for r in it["refs"]]
+        self.blocks = ctx.pinned_copy(it["blocks"])
+        prof = it.get("prof")
+        self.prof = ctx.pinned_copy(prof) if prof is not None and len(prof) else None
+        self.levels = ctx.pinned_copy(rs["levels"])
+        self.tbs = ctx.pinned_copy(rs["tbs"])
+        edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+        self.edge = ctx.pinned_copy(edge)
+        self.qp = ctx.pinned_copy(db["qp"])
+        self.ctb_offsets = ctx.pinned_copy(db["ctb_offsets"])
+        self.sao = ctx.pinned_copy(lf["sao"])
+        self.alf = ctx.pinned_copy(lf["alf"])
+        self.alf_params = ctx.pinned_copy(lf["alf_params"])
+        ia = pic.get("intra")
+        self.intra = None
+        if ia is not None and len(ia["blocks"]):
+            ctb = pic["ctb_log2"]
+            self.intra = (ctx.pinned_copy(ia["blocks"]), ctx.pinned_copy(ia["ctu_first"]),
+                          (pic["width"] + (1 << ctb) - 1) >> ctb, (pic["height"] + (1 << ctb) - 1) >> ctb, ia["params"])
+        self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
+        # pictures are reconstructed into the slots after the references (ref_slot[][] already maps to 0..n_refs-1),
+        # alternating between two slots / two host frames when the context has them, as consecutive pictures of a
+        # decoder do: the download of one picture then overlaps the reconstruction of the next
+        self.n_slots = max(1, min(2, ctx.dpb_size - self.n_refs))
+        self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
+        self.count = 0
+        self.out = self.outs[0]
+
+    def h2d_bytes(self):
+        intra = 0 if self.intra is None else self.intra[0].nbytes + self.intra[1].nbytes
+        intra += 0 if self.prof is None else self.prof.nbytes
+        return intra + int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
+                   self.ctb_offsets.nbytes + self.sao.nbytes + self.alf.nbytes + self.alf_params.nbytes)
+
+    def d2h_bytes(self):
+        return int(sum(p.nbytes for p in self.out))
+
+    def upload_refs(self):
+        for i, r in enumerate(self.refs):
+            self.ctx.upload(r, slot=i)
+
+    def run(self, download=True):
+        ctx, pic = self.ctx, self.pic
+        k = self.count % self.n_slots
+        self.count += 1
+        self.out = self.outs[k]
+        ctx.begin(self.n_refs + k)
+        ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0], prof=self.prof)
+        ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
+        if self.intra is not None:
+            ctx.intra(*self.intra)
+        if self.luts is not None:
+            ctx.lmcs(self.luts[1])
+        ctx.deblock(self.edge, self.qp, self.ctb_offsets, pic["deblock"]["stride4"], pic["deblock"]["params"])
+        ctx.sao_alf(self.sao, self.alf, self.alf_params, pic["ctb_log2"])
+        if download:
+            ctx.download(self.out)

@@ -9,7 +9,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import bench  # noqa: E402
 from ffmpeg_b200 import lib  # noqa: E402
-from tests import util  # noqa: E402
+from ffmpeg_b200 import hostutil as util  # noqa: E402
 
 
 def main():
