@@ -396,7 +396,7 @@ def main():
                       validate=1)                                         # the library's default batch checks
     ep = pipeline.EnginePicture(ctx, pic)
     ep.upload_refs()                       # reference pictures are earlier outputs of the same decoder: resident
-    e2e_steps = max(3, min(args.steps, 40))
+    e2e_steps = max(3, min(args.steps, 100))
     for _ in range(3):
         ep.run()
     ctx.sync()
