@@ -10,6 +10,10 @@ if ROOT not in sys.path:
 
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box with -m gpu)")
+    # A fresh checkout has no product library: build it once (nvcc cross-compiles without a GPU).
+    from ffmpeg_b200 import build as b
+    if not os.path.exists(b.SO) and os.path.exists(b.NVCC):
+        b.build()
 
 
 def pytest_collection_modifyitems(config, items):
