@@ -56,9 +56,10 @@ def measured_peaks():
 # ----------------------------------------------------------------------------------------------------------
 def make_picture(seed, width, height, intra_fraction):
     """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
-    with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp for re-runs."""
+    with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp (or $VVCB200_BENCH_CACHE) for re-runs."""
     from ffmpeg_b200 import abi, synth
-    cache = "/tmp/vvcb200_bench_v11_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000))
+    cache = os.path.join(os.environ.get("VVCB200_BENCH_CACHE", "/tmp"),
+                         "vvcb200_bench_v11_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000)))
     kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
              ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):
@@ -247,7 +248,7 @@ def main():
                          "residual (dequant, inverse DCT2/DST7/DCT8, LFNST, TS, BDPCM, joint CbCr, scaling lists, add)",
                          "intra (planar / DC / angular + PDPC, MRL, ISP, MIP, CCLM; dependency-driven)",
                          "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
-              "not_in_step": "CIIP blend, LMCS (separate kernels exist; chroma residual scaling derivation not built)",
+              "not_in_step": "LMCS (sample mapping and luma-dependent chroma scaling are built and tested, not part of this picture)",
               "streams": "one independent picture stream per GPU (replicas, no collective)"}
 
     if args.impl == "reference":
@@ -340,7 +341,7 @@ def main():
         lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], n_tbs, rs["params"], residual=s["res_p"])
         if ev is not None:
             ev[2].record()
-        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"])
+        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"], shadow=s["tmp_p"])
         if ev is not None:
             ev[3].record()
         lib.deblock_picture(s["cur_p"], s["db"], db["params"])

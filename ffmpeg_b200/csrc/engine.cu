@@ -547,7 +547,8 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return r;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr,
+    // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr, &c->scratch.planes,
                                       (const VVCB200IntraBlock *)S.iblocks.p, n, params, c->intra_marks.p, c->stream))
         return r;
     return set_consumed(c);

@@ -24,6 +24,7 @@ namespace vvcb200 {
 namespace {
 
 constexpr int kWarps   = 4;       // warps per CTA
+constexpr int kCtasPerSm = 4;     // 16 warps per SM: what 128 registers per thread and ~50 KB of shared memory per CTA allow
 constexpr int kSlots   = 1;       // records a warp holds at a time (1: it simply waits for its record)
 constexpr int kEdgeLen = 256;     // samples per edge array: indices -72 .. 183 are addressable
 constexpr int kEdgeOrg = 72;
@@ -41,15 +42,27 @@ __device__ unsigned long long g_prof[8];      // cycles: 0 ticket+record, 1 reco
 // Staging area of a warp: everything a record reads that does not depend on its neighbours (its residual, the inter
 // prediction of a CIIP block) is fetched with cp.async BEFORE the warp starts waiting, so that the latency of those
 // reads never sits on the picture's dependency chain; CCLM stages the co-located luma window here after the wait.
-constexpr int kStageRes   = 64 * 64 * 2;                                  // residual block, or Cb + Cr residual of a CCLM record
-constexpr int kStageExtra = 65 * 68 * 2 + 16;                             // CIIP: inter prediction; CCLM: luma window
+// The per-warp buffers hold records of up to kSmallSamples samples, which is nearly all of them: the kernel lives on
+// the number of resident warps (each spends most of its time in L2 round trips), and buffers sized for the largest
+// block would allow 8 warps per SM instead of 16.  A larger record borrows the CTA's one arena, and only once
+// everything it waits for is there, so that an arena holder never blocks on another record.
+constexpr int kSmallSamples = 1024;
+constexpr int kSmallRes   = kSmallSamples * 2;                            // residual block, or Cb + Cr residual of a CCLM record
+constexpr int kSmallExtra = 2624;                                         // CIIP inter prediction; CCLM luma window (16x16, 8x32 chroma)
+constexpr int kArenaRes   = 64 * 64 * 2;
+constexpr int kArenaExtra = 65 * 68 * 2 + 16;
 struct __align__(16) WarpScratch {
-    uint8_t  stage_res[kStageRes];
-    uint8_t  stage_extra[kStageExtra];
+    uint8_t  stage_res[kSmallRes];
+    uint8_t  stage_extra[kSmallExtra];
     VVCB200IntraBlock slot[kSlots]; // records this warp holds and looks at in turn
     uint16_t edge[4][kEdgeLen];   // left, top, filtered left, filtered top
     int      red[16];             // MIP: reduced boundary
     uint16_t mip[64];             // MIP: reduced prediction, row-major at the reduced size
+};
+struct __align__(16) CtaArena {
+    uint8_t stage_res[kArenaRes];
+    uint8_t stage_extra[kArenaExtra];
+    int     lock;
 };
 
 // Small tables every record consults, copied once per CTA: after each acquire fence the L1 is invalidated, so a table
@@ -65,6 +78,8 @@ struct IntraArgs {
     PlanesView pic;
     const int16_t *res[3];
     int res_stride[3];            // in samples
+    uint16_t *shadow[3];          // where the prediction of in-place blocks is kept while the picture holds the sentinel, or null
+    int shadow_stride[3];         // in samples
     const VVCB200IntraBlock *blocks;
     int n;
     int bd, ctb_log2, collocated;
@@ -107,6 +122,24 @@ __device__ __forceinline__ void stage_block_async(void *sdst, const void *g, int
     }
 }
 __device__ __forceinline__ void stage_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+// The CTA's arena for records too large for a warp's own staging buffers.  Taken only by a warp that has nothing left
+// to wait for, so every holder runs to its release.
+__device__ __forceinline__ void arena_acquire(CtaArena &ar, int lane)
+{
+    if (lane == 0)
+        while (atomicCAS(&ar.lock, 0, 1))
+            __nanosleep(64);
+    __syncwarp();
+}
+__device__ __forceinline__ void arena_release(CtaArena &ar, int lane)
+{
+    __syncwarp();
+    if (lane == 0) {
+        __threadfence_block();
+        atomicExch(&ar.lock, 0);
+    }
+}
 
 __device__ __forceinline__ unsigned load_mark(const uint8_t *p)
 {
@@ -167,7 +200,10 @@ __global__ void intra_mark_kernel(IntraArgs a)
     const VVCB200IntraBlock b = load_record(a.blocks + t);
     int w, h;
     record_extent(b, w, h);
-    if (in_place(b)) {
+    if ((b.flags & VVCB200_IB_ADD_ONLY) && !(b.flags & VVCB200_IB_RESIDUAL))
+        return;                                                           // nothing to add: the samples are final already
+    const bool keep = in_place(b);                                        // the block's current samples are an input
+    if (keep && !a.shadow[b.c_idx]) {
         set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane);
         if (lane == 0)
             a.ticket[1] = 1;
@@ -175,10 +211,14 @@ __global__ void intra_mark_kernel(IntraArgs a)
     }
     for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {       // sentinel over everything the record will write
         uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
+        uint16_t *sh = keep ? a.shadow[c] + (size_t)b.y0 * a.shadow_stride[c] + b.x0 : nullptr;
         const int per_row = w >> 2, lpr = 31 - __clz(per_row);
         for (int i = lane; i < per_row * h; i += 32) {
             const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
-            *reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x) = make_uint2(0xffffffffu, 0xffffffffu);
+            uint2 *d = reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x);
+            if (keep)
+                *reinterpret_cast<uint2 *>(sh + (size_t)y * a.shadow_stride[c] + x) = *d;
+            *d = make_uint2(0xffffffffu, 0xffffffffu);
         }
     }
 }
@@ -463,8 +503,9 @@ struct Store {                    // what happens to a predicted sample on its w
 };
 
 // blocking = false: one look at the neighbours; returns false, having written nothing, when they are not all there.
-__device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, int lane,
-                               bool has_marks, bool blocking, int skip_wait = 0)
+// arena_held: set when the record took the CTA's arena (the caller releases it once the record has been written).
+__device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, CtaArena &ar,
+                               bool &arena_held, int lane, bool has_marks, bool blocking, int skip_wait = 0)
 {
     const long long p0 = PROF_T();
     const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode, ref_idx = b.ref_idx, bd = a.bd;
@@ -482,13 +523,25 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     // Reads that do not depend on the neighbours (the residual, the inter prediction of an in-place block): a warp that
     // is going to wait for this record starts them now so that they land meanwhile; one that only takes a look starts
     // them once it knows the record will run.
+    const bool stages = has_res || ciip;
+    const bool big = stages && w * h > kSmallSamples;                     // staged in the arena, after the wait
+    uint8_t *const res_buf = big ? ar.stage_res : ws.stage_res, *const extra_buf = big ? ar.stage_extra : ws.stage_extra;
     auto stage_inputs = [&]() {
+        if (big) {
+            arena_acquire(ar, lane);
+            arena_held = true;
+        }
         if (has_res)
-            stage_block_async(ws.stage_res, a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0, a.res_stride[c], w, h, lane);
-        if (ciip || (add_only && has_res))
-            stage_block_async(ws.stage_extra, src, stride, w, h, lane);
+            stage_block_async(res_buf, a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0, a.res_stride[c], w, h, lane);
+        if (ciip || (add_only && has_res)) {                              // the block's own samples before this record
+            if (a.shadow[c])
+                stage_block_async(extra_buf, a.shadow[c] + (size_t)b.y0 * a.shadow_stride[c] + b.x0, a.shadow_stride[c], w, h, lane);
+            else
+                stage_block_async(extra_buf, src, stride, w, h, lane);
+        }
     };
-    if (blocking)
+    const bool early = blocking && !big;
+    if (early)
         stage_inputs();
     int lscale;
     if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
@@ -496,10 +549,10 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
 
     if (add_only) {                                                       // the prediction is there already
         if (has_res) {
-            if (!blocking)
+            if (!early)
                 stage_inputs();
-            const int16_t *res = reinterpret_cast<const int16_t *>(ws.stage_res);
-            const uint16_t *cur = reinterpret_cast<const uint16_t *>(ws.stage_extra);
+            const int16_t *res = reinterpret_cast<const int16_t *>(res_buf);
+            const uint16_t *cur = reinterpret_cast<const uint16_t *>(extra_buf);
             stage_wait();
             __syncwarp();
             for (int idx = lane; idx < w * h; idx += 32) {
@@ -517,12 +570,14 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     const int la = min(ul, (int)b.avail_left), ta = min(ut, (int)b.avail_top);
 
     // ---- neighbours written in place (CIIP, add-only) announce themselves through the marks
-    PROF_ADD(7, PROF_T() - p0);
+    const long long p1 = PROF_T();
+    PROF_ADD(7, p1 - p0);
     if (has_marks) {
         Span sp[3];
         if (!spans_ready(a, sp, predict_deps(b, skip_wait, sp), lane, blocking))
             return false;
     }
+    PROF_ADD(4, PROF_T() - p1);
 
     // ---- which of the edge samples the prediction really consumes.  The reference fetches `ul` / `ut` samples whatever
     // the mode; samples that never reach the output need not be waited for (their value, sentinel or not, is
@@ -606,7 +661,7 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
         }
         break;
     }
-    if (!blocking)
+    if (!early)
         stage_inputs();
     __syncwarp();
     {                                                                     // substitution of what is not there
@@ -665,8 +720,8 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     Store st;
     st.dst = src; st.dstride = stride; st.bd = bd;
     st.ciip_w = ciip ? b.ciip_weight : 0;
-    st.res = has_res ? reinterpret_cast<const int16_t *>(ws.stage_res) : nullptr;
-    st.inter = reinterpret_cast<const uint16_t *>(ws.stage_extra);
+    st.res = has_res ? reinterpret_cast<const int16_t *>(res_buf) : nullptr;
+    st.inter = reinterpret_cast<const uint16_t *>(extra_buf);
     st.w = w;
     st.lscale = lscale;
     const long long g1 = PROF_T();
@@ -826,8 +881,8 @@ __device__ __forceinline__ int checked_load(const uint16_t *p, bool &bad)
 }
 
 // ---- CCLM (vvc_intra_template.c:29-375): one record predicts Cb and Cr --------------------------------------------
-__device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, int lane, bool has_marks,
-                            bool blocking)
+__device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, CtaArena &ar, bool &arena_held,
+                            int lane, bool has_marks, bool blocking)
 {
     const int bd = a.bd, w = b.w, h = b.h, x = b.x0, y = b.y0, x0 = x * 2, y0 = y * 2, mode = b.mode;
     const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
@@ -839,20 +894,27 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
     const int num[2] = { kc.num[0], kc.num[1] };
     const int n = w * h, lw = ilog2(w);
     const int16_t *res[2] = { nullptr, nullptr };
+    const int wx0 = avail_l ? -4 : 0, wy0 = avail_t ? -1 : 0, wpitch = 2 * w + 4;
+    // too large for the warp's own buffers: residuals and luma window go to the CTA's arena, taken after the last wait
+    const bool big = 2 * n * 2 > kSmallRes || wpitch * (2 * h + 1) * 2 > kSmallExtra;
     bool staged = false;
     auto stage_residuals = [&]() {                                        // before waiting, or once the record is known to run
         if (staged)
             return;
         staged = true;
+        if (big && !arena_held) {
+            arena_acquire(ar, lane);
+            arena_held = true;
+        }
         if (b.flags & VVCB200_IB_RESIDUAL)
             for (int c = 0; c < 2; c++)
                 if (b.res_planes & (1 << c)) {
-                    int16_t *sres = reinterpret_cast<int16_t *>(ws.stage_res) + c * n;
+                    int16_t *sres = reinterpret_cast<int16_t *>(big ? ar.stage_res : ws.stage_res) + c * n;
                     stage_block_async(sres, a.res[c + 1] + (size_t)y * a.res_stride[c + 1] + x, a.res_stride[c + 1], w, h, lane);
                     res[c] = sres;
                 }
     };
-    if (blocking)
+    if (blocking && !big)
         stage_residuals();
     if (has_marks) {
         Span sp[kMaxSpans];
@@ -862,31 +924,6 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
     int lscale;
     if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
         return false;
-    // the co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte pieces;
-    // the block's own luma is usually the last thing to arrive: poll its last row cheaply, then fetch and verify everything
-    uint16_t *win = reinterpret_cast<uint16_t *>(ws.stage_extra);
-    const int wx0 = avail_l ? -4 : 0, wy0 = avail_t ? -1 : 0, wpitch = 2 * w + 4;
-    if (avail_t || avail_l) {
-        const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
-        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
-            bool bad = false;
-            for (int i = lane; i < 2 * w; i += 32)
-                bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
-            if (!__any_sync(kFull, bad)) {
-                for (int i = lane; i < per_row * rows; i += 32) {
-                    const int r = i / per_row, q = i - r * per_row;
-                    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
-                    bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
-                    *reinterpret_cast<uint2 *>(win + (r + 1 + wy0) * wpitch + 4 + wx0 + 4 * q) = v;
-                }
-                if (!__any_sync(kFull, bad))
-                    break;
-            }
-            if (!blocking)
-                return false;
-            __nanosleep(backoff);
-        }
-    }
     __syncwarp();
     auto emit = [&](int c, int i, int j, int v) {
         if (res[c]) {
@@ -949,7 +986,8 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
             return false;
         __nanosleep(backoff);
         }
-        stage_residuals();                                                // travel while the model is derived
+        if (!big)
+            stage_residuals();                                            // travel while the model is derived
         int sel[3][4];
 #pragma unroll
         for (int i = 0; i < 4; i++) {
@@ -1003,8 +1041,47 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
             }
         }
     }
-    if (!(num[0] || num[1]))
-        stage_residuals();
+    // The co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte
+    // pieces.  It comes after the model: the block's own luma is usually the last thing to arrive, and by then only the
+    // fetch, the down-sampling and the stores are left.  Poll its last row cheaply, then fetch and verify everything.
+    uint16_t *win = reinterpret_cast<uint16_t *>(big ? ar.stage_extra : ws.stage_extra);
+    {
+        const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+            bool bad = false;
+            for (int i = lane; i < 2 * w; i += 32)
+                bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
+            if (!__any_sync(kFull, bad)) {
+                if (big && !arena_held) {                                 // look only: the arena is not ours while we may still wait
+                    for (int i = lane; i < per_row * rows; i += 32) {
+                        const int r = i / per_row, q = i - r * per_row;
+                        const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
+                        bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
+                    }
+                    if (__any_sync(kFull, bad)) {
+                        if (!blocking)
+                            return false;
+                        __nanosleep(backoff);
+                        continue;
+                    }
+                    arena_acquire(ar, lane);
+                    arena_held = true;
+                }
+                for (int i = lane; i < per_row * rows; i += 32) {
+                    const int r = i / per_row, q = i - r * per_row;
+                    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
+                    bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
+                    *reinterpret_cast<uint2 *>(win + (r + 1 + wy0) * wpitch + 4 + wx0 + 4 * q) = v;
+                }
+                if (!__any_sync(kFull, bad))
+                    break;
+            }
+            if (!blocking)
+                return false;
+            __nanosleep(backoff);
+        }
+    }
+    stage_residuals();
     stage_wait();
     __syncwarp();
 #define W(dx, dy) ((int)win[((dy) + 1) * wpitch + 4 + (dx)])
@@ -1054,12 +1131,15 @@ __device__ bool isp_external_ready(const IntraArgs &a, const VVCB200IntraBlock &
     return !__any_sync(kFull, bad);
 }
 
-__global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArgs a)
 {
     extern __shared__ __align__(16) uint8_t s_dyn[];
     __shared__ CtaTables tb;
     const int lane = threadIdx.x & 31;
     WarpScratch &ws = reinterpret_cast<WarpScratch *>(s_dyn)[threadIdx.x >> 5];
+    CtaArena &ar = *reinterpret_cast<CtaArena *>(s_dyn + sizeof(WarpScratch) * kWarps);
+    if (threadIdx.x == 0)
+        ar.lock = 0;
     for (int i = threadIdx.x; i < 95; i += blockDim.x) {
         tb.angle[i] = VVC_INTRA_ANGLE[i];
         tb.inv_angle[i] = VVC_INTRA_INV_ANGLE[i];
@@ -1084,6 +1164,7 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
     bool tickets_left = true;
     unsigned backoff = 32;
     for (;;) {
+        const long long pt0 = PROF_T();
         while (tickets_left && held != (1u << kSlots) - 1) {              // refill in ticket order
             int t = 0;
             if (lane == 0)
@@ -1101,14 +1182,16 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
         __syncwarp();
         if (!held)
             break;
+        PROF_ADD(0, PROF_T() - pt0);
         bool progress = false;
         for (int k = 0; k < kSlots && !progress; k++) {
             if (!(held & (1u << k)))
                 continue;
             const VVCB200IntraBlock b = slot[k];
-            bool done;
+            const long long pt1 = PROF_T();
+            bool done, arena_held = false;
             if (b.mode >= 81) {
-                done = cclm_record(a, b, ws, lane, has_marks, kWait);
+                done = cclm_record(a, b, ws, ar, arena_held, lane, has_marks, kWait);
             } else {
                 // ISP: the sub-partitions of the coding block one after the other, each predicted from its
                 // reconstructed predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit.  Everything the
@@ -1121,19 +1204,29 @@ __global__ void __launch_bounds__(kWarps * 32) intra_kernel(IntraArgs a)
                 for (int q = 0; done && q < n_parts; q++) {
                     VVCB200IntraBlock sub = b;
                     const int skip = isp ? isp_part(b, q, sub) : 0;
-                    done = predict_record(a, tb, sub, ws, lane, has_marks, kWait || isp, skip);
+                    done = predict_record(a, tb, sub, ws, ar, arena_held, lane, has_marks, kWait || isp, skip);
                     __syncwarp();
+                    if (arena_held && q + 1 < n_parts) {                  // the next partition may wait for this one's stores
+                        arena_release(ar, lane);
+                        arena_held = false;
+                    }
                 }
             }
             __syncwarp();
+            if (arena_held)
+                arena_release(ar, lane);
             if (!done)
                 continue;
-            if (in_place(b)) {                                            // samples before marks
+            const long long pt2 = PROF_T();
+            PROF_ADD(1, pt2 - pt1);
+            PROF_ADD(3, 1);
+            if (has_marks && in_place(b)) {                               // samples before marks
                 fence_gpu();
                 __syncwarp();
                 set_marks(a, b.c_idx, b.x0, b.y0, b.w, b.h, 2, lane);
                 __syncwarp();
             }
+            PROF_ADD(2, PROF_T() - pt2);
             held &= ~(1u << k);
             progress = true;
         }
@@ -1324,7 +1417,7 @@ extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_
     return 0;
 }
 
-extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
+extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual, const VVCB200Planes *d_shadow,
                                      const VVCB200IntraBlock *d_blocks, int n, const VVCB200IntraParams *params,
                                      void *d_scratch, void *stream)
 {
@@ -1344,6 +1437,18 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         a.res[c] = d_residual ? (const int16_t *)d_residual->d_plane[c] : nullptr;
         a.res_stride[c] = d_residual ? d_residual->stride[c] / 2 : 0;
     }
+    for (int c = 0; c < 3; c++) {
+        a.shadow[c] = d_shadow ? (uint16_t *)d_shadow->d_plane[c] : nullptr;
+        a.shadow_stride[c] = d_shadow ? d_shadow->stride[c] / 2 : 0;
+    }
+    if (d_shadow)
+        for (int c = 0; c < 3; c++)
+            if (!d_shadow->d_plane[c] || d_shadow->width[c] < pic->width[c] || d_shadow->height[c] < pic->height[c] ||
+                d_shadow->d_plane[c] == pic->d_plane[c] || (d_shadow->stride[c] & 7) || ((uintptr_t)d_shadow->d_plane[c] & 7)) {
+                set_error("vvcb200_intra_picture: d_shadow must be a second picture of at least the size of pic, planes and "
+                          "strides multiples of 8 bytes");
+                return VVCB200_ERR_ARG;
+            }
     a.blocks = d_blocks;
     a.n = n;
     a.bd = params->bit_depth;
@@ -1365,8 +1470,12 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     VVC_CUDA(cudaMemsetAsync(d_scratch, 0, l.total, s));                  // ticket counter, in-place flag, marks
     intra_mark_kernel<<<(n + 3) / 4, 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
-    const int ctas = min((n + kWarps - 1) / kWarps, sm_count() * 3);      // 3 CTAs of 64 KB shared memory fit an SM
-    const size_t smem = sizeof(WarpScratch) * kWarps;
+    int ctas = min((n + kWarps - 1) / kWarps, sm_count() * kCtasPerSm);
+#ifdef VVC_INTRA_PROFILE
+    if (const char *e = getenv("VVC_INTRA_CTAS"))                         // development: occupancy experiments
+        ctas = min(ctas, atoi(e));
+#endif
+    const size_t smem = sizeof(WarpScratch) * kWarps + sizeof(CtaArena);
     static bool attr_set[64];                                             // per device: allow > 48 KB of shared memory
     int dev = 0;
     VVC_CUDA(cudaGetDevice(&dev));
@@ -1435,7 +1544,7 @@ extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB
     }
     // the marks have to read zero when the mark kernel starts; an earlier call that failed half-way may have left some
     VVC_CUDA(cudaMemsetAsync(ptr, 0, need, (cudaStream_t)stream));
-    return vvcb200_intra_picture(pic, d_residual, d_blocks, n, params, ptr, stream);
+    return vvcb200_intra_picture(pic, d_residual, nullptr, d_blocks, n, params, ptr, stream);
 }
 
 #ifdef VVC_INTRA_PROFILE

@@ -109,9 +109,10 @@ def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, w
     return (out, int(levels.value)) if want_levels else out
 
 
-def intra_picture(pic, residual, blocks, n, params, scratch, stream=None):
-    """vvcb200_intra_picture: pic/residual are device_planes() structs, blocks/scratch device tensors."""
+def intra_picture(pic, residual, blocks, n, params, scratch, stream=None, shadow=None):
+    """vvcb200_intra_picture: pic/residual/shadow are device_planes() structs, blocks/scratch device tensors."""
     check(load().vvcb200_intra_picture(C.byref(pic), C.byref(residual) if residual is not None else None,
+                                       C.byref(shadow) if shadow is not None else None,
                                        _ptr(blocks), int(n), C.byref(params), _ptr(scratch), _stream(stream)))
 
 

@@ -393,6 +393,12 @@ typedef struct VVCB200IntraParams {
  * rewritten in place, CIIP and add-only); the call clears it itself.  Two calls may not share a scratch buffer
  * concurrently.  Samples of pure intra blocks need no marks: the call first fills them with 0xffff ("not yet
  * reconstructed"), so bit depths above 15 are not supported by this entry point.
+ * d_shadow (may be NULL): a second picture of device memory, at least as large as `pic`, 8-byte aligned planes and
+ * strides, content irrelevant and undefined afterwards.  With it, the prediction of the blocks rewritten in place is
+ * moved there first and those blocks are filled with 0xffff like every other record's, so that no record needs marks
+ * or memory fences — considerably faster on pictures with many CIIP units or luma-dependent chroma scaling.  Any
+ * picture-sized buffer that is idle between the residual and the deblocking stage will do (the loop filters' scratch
+ * picture, as vvcb200_pic_intra uses).  The results are identical either way.
  */
 VVCB200_API size_t vvcb200_intra_scratch_bytes(int width, int height /* luma samples */);
 enum {
@@ -412,7 +418,7 @@ VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32
                                        int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
                                        int32_t *n_levels);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
-                                      const VVCB200IntraBlock *d_blocks, int n,
+                                      const VVCB200Planes *d_shadow, const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);
 
 /*

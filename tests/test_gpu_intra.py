@@ -9,8 +9,9 @@ from tests import util
 pytestmark = pytest.mark.gpu
 
 
-def run_gpu(pic, schedule=True, repeat=1):
-    """INTER -> RESIDUAL -> INTRA on the device, Level A calls only."""
+def run_gpu(pic, schedule=True, repeat=1, shadow=False):
+    """INTER -> RESIDUAL -> INTRA on the device, Level A calls only.  shadow: hand the call a second picture, so that
+    blocks rewritten in place take the sentinel protocol too (else they go by marks and fences)."""
     import torch
     it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
     dev = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
@@ -30,6 +31,8 @@ def run_gpu(pic, schedule=True, repeat=1):
     if schedule:
         recs = lib.intra_schedule(recs, ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb, ctb, w, h)
     scratch = torch.zeros(lib.intra_scratch_bytes(w, h), dtype=torch.uint8, device="cuda")
+    side = [torch.full_like(t, 0x1234) for t in dev] if shadow else None
+    spl = lib.device_planes(side) if shadow else None
     out = []
     if len(recs):
         d_recs = torch.from_numpy(recs.view(np.uint8).reshape(-1)).cuda()
@@ -37,10 +40,12 @@ def run_gpu(pic, schedule=True, repeat=1):
         for _ in range(repeat):
             for t, b in zip(dev, base):
                 t.copy_(b)
-            lib.intra_picture(dpl, rpl, d_recs, len(recs), ia["params"], scratch)
+            lib.intra_picture(dpl, rpl, d_recs, len(recs), ia["params"], scratch, shadow=spl)
             torch.cuda.synchronize()
             out.append(util.from_device_planes(dev))
         assert int((scratch[256:] == 1).sum()) == 0, "no unit may be left pending after the call"
+        if shadow:
+            assert int((scratch[256:] != 0).sum()) == 0, "with a shadow picture nothing goes by marks"
     else:
         out.append(util.from_device_planes(dev))
     return out
@@ -67,19 +72,35 @@ CASES = [
 def test_intra_picture_matches_oracle(seed, w, h, ctb, tools, frac):
     pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
     want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
-    got = run_gpu(pic)[0]
-    for c in range(3):
-        assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)
-    assert util.plane_md5(got) == util.plane_md5(want)
+    for shadow in (False, True):
+        got = run_gpu(pic, shadow=shadow)[0]
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d, shadow %d)" % (c, seed, shadow)
+        assert util.plane_md5(got) == util.plane_md5(want)
 
 
 def test_decoding_order_and_repeat_give_the_same_picture():
     """Any topological order works (plain decoding order included), and the scratch is reusable call after call."""
     pic = synth.recon_picture(21, 416, 240, ctb_log2=6, intra_fraction=0.7)
     want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
-    for got in run_gpu(pic, schedule=False) + run_gpu(pic, schedule=True, repeat=3):
+    for got in run_gpu(pic, schedule=False) + run_gpu(pic, schedule=True, repeat=3) + run_gpu(pic, repeat=2, shadow=True):
         for c in range(3):
             assert np.array_equal(got[c], want[c])
+
+
+@pytest.mark.parametrize("seed,w,h,ctb,frac", [(71, 416, 240, 6, 0.4), (72, 256, 192, 7, 0.15)])
+def test_chroma_scaling_and_ciip_under_both_protocols(seed, w, h, ctb, frac):
+    """Luma-dependent chroma residual scaling gives every inter unit add-only chroma records; with CIIP units they are
+    the blocks rewritten in place.  Marks + fences (no shadow) and sentinels (shadow) must both match the oracle."""
+    luts = synth.lmcs_luts(seed + 4, 10)
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=ALL_TOOLS, intra_fraction=frac,
+                              lmcs_chroma=synth.lmcs_model(seed + 5, luts[0], 10))
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    assert (pic["intra"]["blocks"]["flags"] & abi.IB_ADD_ONLY).any() and (pic["intra"]["blocks"]["flags"] & abi.IB_CIIP).any()
+    for shadow in (False, True):
+        got = run_gpu(pic, shadow=shadow)[0]
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d, shadow %d)" % (c, seed, shadow)
 
 
 def test_all_intra_1080p_property():
@@ -88,6 +109,7 @@ def test_all_intra_1080p_property():
     a = run_gpu(pic, schedule=False)[0]
     b = run_gpu(pic, schedule=True)[0]
     assert util.plane_md5(a) == util.plane_md5(b)
+    assert util.plane_md5(run_gpu(pic, shadow=True)[0]) == util.plane_md5(a)
 
 
 def test_empty_picture_is_a_noop():

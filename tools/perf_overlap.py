@@ -46,7 +46,7 @@ def main():
         q = st.cuda_stream
         lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], len(it["blocks"]), it["params"], prof=s["prof"], stream=q)
         lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], len(rs["tbs"]), rs["params"], residual=s["res_p"], stream=q)
-        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"], stream=q)
+        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"], stream=q, shadow=s["tmp_p"])
         lib.deblock_picture(s["cur_p"], s["db"], db["params"], stream=q)
         lib.sao_picture(s["tmp_p"], s["cur_p"], s["sao"], ctb, stream=q)
         lib.alf_picture(s["cur_p"], s["tmp_p"], s["alf"], s["alfp"], ctb, stream=q)

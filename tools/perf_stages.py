@@ -36,7 +36,11 @@ def main():
     ap.add_argument("--workload", default="4k")
     ap.add_argument("--intra-fraction", type=float, default=0.1)
     ap.add_argument("--seed", type=int, default=2026)
+    ap.add_argument("--lib", default=None, help="experimental library built by tools/build_variant.py")
+    ap.add_argument("--only", default=None, help="inter | residual | intra")
     args = ap.parse_args()
+    if args.lib:
+        lib.SO = os.path.abspath(args.lib)
     width, height = bench.WORKLOADS[args.workload]
     pic = bench.make_picture(args.seed, width, height, args.intra_fraction)
     it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
@@ -63,7 +67,7 @@ def main():
     }
     for name, m in subsets.items():
         sub = np.ascontiguousarray(b[m])
-        if not len(sub):
+        if not len(sub) or args.only not in (None, "inter"):
             continue
         p = abi.InterParams.from_buffer_copy(bytes(it["params"]))
         p.n_w16, p.n_w8 = int((sub["w"] == 16).sum()), int((sub["w"] == 8).sum())
@@ -76,10 +80,14 @@ def main():
     res_p = lib.device_planes(res)
     tbs, levels = dev(rs["tbs"]), dev(rs["levels"])
     ms = timed(torch, lambda: lib.residual_batch(cur_p, levels, tbs, len(rs["tbs"]), rs["params"], residual=res_p))
+    if args.only not in (None, "residual", "intra"):
+        return
     print("residual %d TBs  %.4f ms; classes %s" % (len(rs["tbs"]), ms, list(rs["params"].n_class)))
     ctb = pic["ctb_log2"]
     cw, ch = (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb
     marks = torch.zeros(lib.intra_scratch_bytes(width, height), dtype=torch.uint8, device="cuda")
+    side = [torch.zeros_like(t) for t in cur]
+    side_p = lib.device_planes(side)
     cf = ia["ctu_first"].astype(np.int64)
     ctu_of = np.repeat(np.arange(cw * ch), np.diff(cf))
     k_in = np.arange(len(ia["blocks"])) - cf[ctu_of]
@@ -90,16 +98,26 @@ def main():
     nodep["avail_left"] = 0
     nodep["up_left"] = 0
     nodep["flags"] &= ~np.uint8(abi.IB_LMCS_SCALE)
-    for label, recs in (("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height)),
-                        ("ctu diagonals", diag_order), ("decoding order", ia["blocks"]), ("no dependencies", nodep)):
+    cases = [("scheduled", lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, width, height), None),
+             ("ctu diagonals", diag_order, None), ("decoding order", ia["blocks"], None), ("no dependencies", nodep, None),
+             ("diagonals, marks", diag_order, -1), ("no deps, marks", nodep, -1)]
+    if args.lib and "prof" in args.lib:         # occupancy experiments (profile builds read VVC_INTRA_CTAS)
+        for ctas in (148, 296, 444):
+            cases += [("diagonals, %d CTAs" % ctas, diag_order, ctas), ("no deps, %d CTAs" % ctas, nodep, ctas)]
+    for label, recs, ctas in cases:
+        shadow = None if ctas == -1 else side_p          # -1: in-place records by marks and fences
+        if ctas and ctas > 0:
+            os.environ["VVC_INTRA_CTAS"] = str(ctas)
+        else:
+            os.environ.pop("VVC_INTRA_CTAS", None)
         d = dev(recs)
-        ms = timed(torch, lambda: lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks))
+        ms = timed(torch, lambda: lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks, shadow=shadow))
         print("intra %-15s %d records  %.4f ms" % (label, len(recs), ms))
         if hasattr(lib.load(), "vvcb200_intra_profile"):
             import ctypes as C
             buf = (C.c_ulonglong * 8)()
             lib.load().vvcb200_intra_profile(buf, 1)                      # reset
-            lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks)
+            lib.intra_picture(cur_p, res_p, d, len(recs), ia["params"], marks, shadow=shadow)
             torch.cuda.synchronize()
             lib.load().vvcb200_intra_profile(buf, 1)
             n = max(1, buf[3])
