@@ -19,7 +19,11 @@ def run_gpu(pic, schedule=True, repeat=1, shadow=False):
     if len(it["blocks"]):
         refs = [util.to_device_planes(r, torch) for r in it["refs"]]
         blocks = torch.from_numpy(it["blocks"].view(np.uint8).reshape(-1)).cuda()
-        lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], blocks, len(it["blocks"]), it["params"])
+        prof = it.get("prof")
+        prof = torch.from_numpy(prof.view(np.uint8).reshape(-1)).cuda() if prof is not None and len(prof) else None
+        fwd = torch.from_numpy(pic["lmcs"][0]).cuda() if pic.get("lmcs") is not None else None
+        lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], blocks, len(it["blocks"]), it["params"],
+                        lmcs_fwd_lut=fwd, prof=prof)
     res = [torch.zeros_like(t) for t in dev]
     rpl = lib.device_planes(res)
     if len(rs["tbs"]):
@@ -88,15 +92,30 @@ def test_decoding_order_and_repeat_give_the_same_picture():
             assert np.array_equal(got[c], want[c])
 
 
+def oracle_to_intra(pic):
+    """INTER + RECON of a synth.full_picture() (forward-mapped inter prediction when LMCS is on)."""
+    from oracle import portapi, refapi
+    planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+    fwd = pic["lmcs"][0] if pic["lmcs"] is not None else None
+    util.oracle_inter(planes, it, fwd, refapi.available())
+    if refapi.available():
+        refapi.recon_picture(planes, pic["ref"], ia["params"], inter=it, lmcs_fwd_lut=fwd)
+    else:
+        res = [np.zeros(p.shape, np.int16) for p in planes]
+        portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
+        portapi.intra_picture(planes, res, ia["blocks"], ia["params"])
+    return planes
+
+
 @pytest.mark.parametrize("seed,w,h,ctb,frac", [(71, 416, 240, 6, 0.4), (72, 256, 192, 7, 0.15)])
 def test_chroma_scaling_and_ciip_under_both_protocols(seed, w, h, ctb, frac):
     """Luma-dependent chroma residual scaling gives every inter unit add-only chroma records; with CIIP units they are
     the blocks rewritten in place.  Marks + fences (no shadow) and sentinels (shadow) must both match the oracle."""
-    luts = synth.lmcs_luts(seed + 4, 10)
-    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=ALL_TOOLS, intra_fraction=frac,
-                              lmcs_chroma=synth.lmcs_model(seed + 5, luts[0], 10))
-    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
-    assert (pic["intra"]["blocks"]["flags"] & abi.IB_ADD_ONLY).any() and (pic["intra"]["blocks"]["flags"] & abi.IB_CIIP).any()
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=True, intra_fraction=frac)
+    want = oracle_to_intra(pic)
+    flags = pic["intra"]["blocks"]["flags"]
+    assert (flags & abi.IB_ADD_ONLY).any() and (flags & abi.IB_CIIP).any()
     for shadow in (False, True):
         got = run_gpu(pic, shadow=shadow)[0]
         for c in range(3):
