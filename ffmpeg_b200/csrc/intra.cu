@@ -24,7 +24,10 @@ namespace vvcb200 {
 namespace {
 
 constexpr int kWarps   = 4;       // warps per CTA
-constexpr int kCtasPerSm = 4;     // 16 warps per SM: what 128 registers per thread and ~50 KB of shared memory per CTA allow
+#ifndef VVC_INTRA_CTAS_PER_SM
+#define VVC_INTRA_CTAS_PER_SM 4   // 16 warps per SM: what 128 registers per thread and ~50 KB of shared memory per CTA allow
+#endif
+constexpr int kCtasPerSm = VVC_INTRA_CTAS_PER_SM;
 constexpr int kSlots   = 1;       // records a warp holds at a time (1: it simply waits for its record)
 constexpr int kEdgeLen = 256;     // samples per edge array: indices -72 .. 183 are addressable
 constexpr int kEdgeOrg = 72;
@@ -173,11 +176,12 @@ __device__ __forceinline__ unsigned col_marks(const IntraArgs &a, int c, int ux,
 // units touched by samples [p0, p0 + n) along an axis with 1 << s samples per unit
 __host__ __device__ __forceinline__ int unit_count(int p0, int n, int s) { return n > 0 ? ((p0 + n - 1) >> s) - (p0 >> s) + 1 : 0; }
 
-__device__ void set_marks(const IntraArgs &a, int c, int x0, int y0, int w, int h, uint8_t v, int lane)
+// lane / lanes: this thread's index in the group of threads that shares the block, and the group's size
+__device__ void set_marks(const IntraArgs &a, int c, int x0, int y0, int w, int h, uint8_t v, int lane, int lanes = 32)
 {
     const int s = unit_shift(c);
     const int ux = x0 >> 2, uy = y0 >> s, nx = unit_count(x0, w, 2), ny = unit_count(y0, h, s);
-    for (int i = lane; i < nx * ny; i += 32)
+    for (int i = lane; i < nx * ny; i += lanes)
         store_mark(a.marks[c] + (size_t)(uy + i / nx) * a.mpitch[c] + ux + i % nx, v);
 }
 
@@ -191,10 +195,12 @@ __device__ __forceinline__ void record_extent(const VVCB200IntraBlock &b, int &w
 
 __device__ __forceinline__ bool in_place(const VVCB200IntraBlock &b) { return b.flags & (VVCB200_IB_CIIP | VVCB200_IB_ADD_ONLY); }
 
+// Eight threads per record: most records are 4x4 .. 8x8 blocks, i.e. 4 .. 16 pieces of 8 bytes.
+constexpr int kMarkLanes = 8;
 __global__ void intra_mark_kernel(IntraArgs a)
 {
-    const int lane = threadIdx.x & 31;
-    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & (kMarkLanes - 1);
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) / kMarkLanes;
     if (t >= a.n)
         return;
     const VVCB200IntraBlock b = load_record(a.blocks + t);
@@ -204,7 +210,7 @@ __global__ void intra_mark_kernel(IntraArgs a)
         return;                                                           // nothing to add: the samples are final already
     const bool keep = in_place(b);                                        // the block's current samples are an input
     if (keep && !a.shadow[b.c_idx]) {
-        set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane);
+        set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane, kMarkLanes);
         if (lane == 0)
             a.ticket[1] = 1;
         return;
@@ -213,7 +219,7 @@ __global__ void intra_mark_kernel(IntraArgs a)
         uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
         uint16_t *sh = keep ? a.shadow[c] + (size_t)b.y0 * a.shadow_stride[c] + b.x0 : nullptr;
         const int per_row = w >> 2, lpr = 31 - __clz(per_row);
-        for (int i = lane; i < per_row * h; i += 32) {
+        for (int i = lane; i < per_row * h; i += kMarkLanes) {
             const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
             uint2 *d = reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x);
             if (keep)
@@ -1467,8 +1473,9 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         a.mpitch[c] = l.pitch[c];
     }
     cudaStream_t s = (cudaStream_t)stream;
-    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, l.total, s));                  // ticket counter, in-place flag, marks
-    intra_mark_kernel<<<(n + 3) / 4, 128, 0, s>>>(a);
+    // ticket counter and in-place flag; the marks too unless a shadow picture makes them unnecessary
+    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.total, s));
+    intra_mark_kernel<<<(n + 128 / kMarkLanes - 1) / (128 / kMarkLanes), 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
     int ctas = min((n + kWarps - 1) / kWarps, sm_count() * kCtasPerSm);
 #ifdef VVC_INTRA_PROFILE

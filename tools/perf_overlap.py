@@ -14,6 +14,8 @@ from ffmpeg_b200 import hostutil as util  # noqa: E402
 
 def main():
     import torch
+    if len(sys.argv) > 1:                       # experimental library built by tools/build_variant.py
+        lib.SO = os.path.abspath(sys.argv[1])
     width, height = 3840, 2160
     pic = bench.make_picture(2026, width, height, 0.1)
     it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
