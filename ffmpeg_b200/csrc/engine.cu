@@ -60,35 +60,43 @@ struct DeviceGuard {
 
 }  // namespace
 
-// Device copies of one picture's host descriptor batches.  Two sets alternate from picture to picture so that the
-// uploads of picture n + 1 (copy stream) overlap the kernels of picture n (compute stream).
+// Everything one picture in flight owns: the device copies of its host descriptor batches, its compute stream and its
+// working pictures.  Two sets alternate from picture to picture, so that the uploads of picture n + 1 (copy stream)
+// overlap the kernels of picture n — and so do its kernels, wherever picture n + 1 does not read picture n: the intra
+// stage is bound by dependency latency and leaves most issue slots of the GPU free for the neighbour's INTER / residual
+// kernels.  Pictures that do depend on each other (through the DPB) are ordered with per-slot events.
 struct StageSet {
+    cudaStream_t stream = nullptr; // this lane's compute stream
+    DevPicture scratch;            // SAO output / ALF input; before that, the intra stage's shadow picture
+    DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
+    DevBuffer intra_marks;
     DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks;
     VVCB200IntraBlock *h_order = nullptr;  // pinned: the picture's intra records in scheduled order
     size_t h_order_cap = 0;
     cudaEvent_t uploaded = nullptr;    // last upload into this set (recorded on the upload stream)
     cudaEvent_t consumed = nullptr;    // last kernel that read this set (recorded on the compute stream)
-    bool in_use = false;
+    cudaEvent_t order_copied = nullptr;    // the upload out of h_order (recorded on the upload stream)
+    bool in_use = false, order_pending = false;
 };
 
 struct VVCB200Ctx {
     int device = 0;
     int width = 0, height = 0, bit_depth = 10, hshift = 1, vshift = 1;
-    cudaStream_t stream = nullptr;     // compute
     cudaStream_t h2d = nullptr;        // descriptor uploads
     cudaStream_t d2h = nullptr;        // picture downloads
     std::vector<DevPicture> dpb;   // reference pictures + the picture under reconstruction
     std::vector<cudaEvent_t> downloaded;   // per DPB slot: last download of that slot (d2h stream)
     std::vector<char> download_pending;
-    cudaEvent_t computed = nullptr;    // scratch event: "compute stream got here"
-    DevPicture scratch;            // SAO output / ALF input
-    DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
+    std::vector<cudaEvent_t> written;      // per DPB slot: last kernel / copy that wrote the slot (its writer's stream)
+    std::vector<signed char> writer;       // per DPB slot: lane of that write, -1 if none yet
+    std::vector<unsigned char> readers;    // per DPB slot: lanes that have used it as a reference since
     int cur = 0;
     StageSet sets[2];
     int set = 0;
     int validate = 1;              // 0: trust the emitter, 1: spot checks (class boundaries + every 64th record), 2: every record
-    DevBuffer intra_marks;
 };
+
+static inline cudaStream_t lane_stream(VVCB200Ctx *c) { return c->sets[c->set].stream; }
 
 namespace {
 
@@ -106,7 +114,7 @@ int alloc_picture(VVCB200Ctx *c, DevPicture *pic)
         total += (size_t)pitch * h;
     }
     VVC_CUDA(cudaMalloc(&pic->base, total));
-    VVC_CUDA(cudaMemsetAsync(pic->base, 0, total, c->stream));
+    VVC_CUDA(cudaMemsetAsync(pic->base, 0, total, lane_stream(c)));
     for (int i = 0; i < 3; i++)
         pic->planes.d_plane[i] = (uint8_t *)pic->base + off[i];
     return 0;
@@ -124,7 +132,7 @@ DevPicture *slot_of(VVCB200Ctx *c, int slot)
 int upload(VVCB200Ctx *c, DevBuffer &b, const void *host, size_t bytes)
 {
     if (bytes > b.cap) {
-        VVC_CUDA(cudaStreamSynchronize(c->stream));
+        VVC_CUDA(cudaStreamSynchronize(lane_stream(c)));
         VVC_CUDA(cudaStreamSynchronize(c->h2d));
     }
     if (int r = b.reserve(bytes))
@@ -138,16 +146,42 @@ int uploads_visible(VVCB200Ctx *c)
 {
     StageSet &s = c->sets[c->set];
     VVC_CUDA(cudaEventRecord(s.uploaded, c->h2d));
-    VVC_CUDA(cudaStreamWaitEvent(c->stream, s.uploaded, 0));
+    VVC_CUDA(cudaStreamWaitEvent(s.stream, s.uploaded, 0));
     return 0;
 }
 
-// the current set is being read by what the compute stream holds now
+// the current set is being read by what its compute stream holds now, and the current picture is written up to here
 int set_consumed(VVCB200Ctx *c)
 {
     StageSet &s = c->sets[c->set];
-    VVC_CUDA(cudaEventRecord(s.consumed, c->stream));
+    VVC_CUDA(cudaEventRecord(s.consumed, s.stream));
+    VVC_CUDA(cudaEventRecord(c->written[c->cur], s.stream));
+    c->writer[c->cur] = (signed char)c->set;
     s.in_use = true;
+    return 0;
+}
+
+// Lane `c->set` is about to overwrite DPB slot `slot`: wait for the other lane's write of it and for the other lane's
+// pictures that use it as a reference (everything that lane has queued so far).
+int order_before_write(VVCB200Ctx *c, int slot)
+{
+    const int other = c->set ^ 1;
+    if (c->writer[slot] == other)
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
+    if ((c->readers[slot] >> other) & 1) {
+        if (c->sets[other].in_use)
+            VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->sets[other].consumed, 0));
+    }
+    c->readers[slot] = 0;
+    return 0;
+}
+
+// Lane `c->set` is about to read DPB slot `slot` as a reference picture.
+int order_before_read(VVCB200Ctx *c, int slot)
+{
+    if (c->writer[slot] == (c->set ^ 1))
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
+    c->readers[slot] |= (unsigned char)(1u << c->set);
     return 0;
 }
 
@@ -192,26 +226,35 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     c->width = width;
     c->height = height;
     c->bit_depth = bit_depth;
-    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking);
+    cudaError_t e = cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->computed, cudaEventDisableTiming);
     for (int i = 0; i < 2 && e == cudaSuccess; i++) {
-        e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
+        e = cudaStreamCreateWithFlags(&c->sets[i].stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].consumed, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].order_copied, cudaEventDisableTiming);
     }
     c->downloaded.assign(dpb_size, nullptr);
+    c->written.assign(dpb_size, nullptr);
     c->download_pending.assign(dpb_size, 0);
-    for (int i = 0; i < dpb_size && e == cudaSuccess; i++)
+    c->writer.assign(dpb_size, -1);
+    c->readers.assign(dpb_size, 0);
+    for (int i = 0; i < dpb_size && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&c->downloaded[i], cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->written[i], cudaEventDisableTiming);
+    }
     if (e != cudaSuccess) {
         vvcb200_ctx_destroy(c);
         return cuda_fail(e, "stream / event creation", __FILE__, __LINE__);
     }
     c->dpb.resize(dpb_size);
-    int r = alloc_picture(c, &c->scratch);
+    int r = alloc_picture(c, &c->sets[0].scratch);
+    if (!r)
+        r = alloc_picture(c, &c->sets[1].scratch);
     for (int i = 0; !r && i < dpb_size; i++)
         r = alloc_picture(c, &c->dpb[i]);
+    if (!r && cudaStreamSynchronize(lane_stream(c)) != cudaSuccess)     // the pictures are cleared before either lane runs
+        r = VVCB200_ERR_CUDA;
     if (r) {
         vvcb200_ctx_destroy(c);
         return r;
@@ -225,32 +268,31 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     if (!c)
         return;
     DeviceGuard g(c->device);
-    for (cudaStream_t st : { c->stream, c->h2d, c->d2h })
+    for (cudaStream_t st : { c->sets[0].stream, c->sets[1].stream, c->h2d, c->d2h })
         if (st)
             cudaStreamSynchronize(st);
     for (StageSet &ss : c->sets) {
-        DevBuffer *bufs[] = { &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
+        DevBuffer *bufs[] = { &ss.intra_marks, &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
                               &ss.sao, &ss.alf, &ss.alf_params, &ss.iblocks };
         for (DevBuffer *b : bufs)
             b->release();
         if (ss.h_order) cudaFreeHost(ss.h_order);
         if (ss.uploaded) cudaEventDestroy(ss.uploaded);
         if (ss.consumed) cudaEventDestroy(ss.consumed);
+        if (ss.order_copied) cudaEventDestroy(ss.order_copied);
+        if (ss.scratch.base) cudaFree(ss.scratch.base);
+        if (ss.residual.base) cudaFree(ss.residual.base);
     }
-    c->intra_marks.release();
     for (cudaEvent_t ev : c->downloaded)
         if (ev)
             cudaEventDestroy(ev);
-    if (c->computed)
-        cudaEventDestroy(c->computed);
+    for (cudaEvent_t ev : c->written)
+        if (ev)
+            cudaEventDestroy(ev);
     for (DevPicture &p : c->dpb)
         if (p.base)
             cudaFree(p.base);
-    if (c->scratch.base)
-        cudaFree(c->scratch.base);
-    if (c->residual.base)
-        cudaFree(c->residual.base);
-    for (cudaStream_t st : { c->stream, c->h2d, c->d2h })
+    for (cudaStream_t st : { c->sets[0].stream, c->sets[1].stream, c->h2d, c->d2h })
         if (st)
             cudaStreamDestroy(st);
     delete c;
@@ -262,12 +304,17 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
         return VVCB200_ERR_ARG;
     DeviceGuard g(c->device);
     VVC_CUDA(cudaStreamSynchronize(c->h2d));
-    VVC_CUDA(cudaStreamSynchronize(c->stream));
+    VVC_CUDA(cudaStreamSynchronize(c->sets[0].stream));
+    VVC_CUDA(cudaStreamSynchronize(c->sets[1].stream));
     VVC_CUDA(cudaStreamSynchronize(c->d2h));
     for (char &p : c->download_pending)
         p = 0;
     for (StageSet &ss : c->sets)
-        ss.in_use = false;
+        ss.in_use = ss.order_pending = false;
+    for (size_t i = 0; i < c->writer.size(); i++) {                       // nothing is in flight: no ordering left to do
+        c->writer[i] = -1;
+        c->readers[i] = 0;
+    }
     return 0;
 }
 
@@ -281,7 +328,7 @@ int vvcb200_ctx_set_validation(VVCB200Ctx *c, int level)
     return 0;
 }
 
-void *vvcb200_ctx_stream(VVCB200Ctx *c) { return c ? (void *)c->stream : nullptr; }
+void *vvcb200_ctx_stream(VVCB200Ctx *c) { return c ? (void *)lane_stream(c) : nullptr; }
 
 int vvcb200_ctx_planes(VVCB200Ctx *c, int slot, VVCB200Planes *out)
 {
@@ -323,10 +370,10 @@ int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
     if (s.in_use)                         // uploads of this picture must not overtake the kernels of the picture before last
         VVC_CUDA(cudaStreamWaitEvent(c->h2d, s.consumed, 0));
     if (c->download_pending[slot]) {      // the slot's previous content is still on its way to the host
-        VVC_CUDA(cudaStreamWaitEvent(c->stream, c->downloaded[slot], 0));
+        VVC_CUDA(cudaStreamWaitEvent(s.stream, c->downloaded[slot], 0));
         c->download_pending[slot] = 0;
     }
-    return 0;
+    return order_before_write(c, slot);
 }
 
 int vvcb200_pic_upload(VVCB200Ctx *c, int slot, const uint16_t *const planes[3], const int32_t strides[3])
@@ -337,9 +384,15 @@ int vvcb200_pic_upload(VVCB200Ctx *c, int slot, const uint16_t *const planes[3],
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    const int idx = slot < 0 ? c->cur : slot;
+    if (idx != c->cur)
+        if (int r = order_before_write(c, idx))
+            return r;
     for (int i = 0; i < 3; i++)
         VVC_CUDA(cudaMemcpy2DAsync(p->planes.d_plane[i], p->planes.stride[i], planes[i], strides[i],
-                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyHostToDevice, c->stream));
+                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyHostToDevice, lane_stream(c)));
+    VVC_CUDA(cudaEventRecord(c->written[idx], lane_stream(c)));
+    c->writer[idx] = (signed char)c->set;
     return 0;
 }
 
@@ -352,8 +405,8 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
     }
     DeviceGuard g(c->device);
     const int idx = slot < 0 ? c->cur : slot;
-    VVC_CUDA(cudaEventRecord(c->computed, c->stream));
-    VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->computed, 0));
+    if (c->writer[idx] >= 0)              // whatever wrote the slot last, in whichever lane
+        VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->written[idx], 0));
     for (int i = 0; i < 3; i++)
         VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
                                    (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->d2h));
@@ -373,15 +426,23 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
         return 0;
     // the batch must come in width order (fatal to get wrong); how thoroughly that is checked is the caller's choice
     const int b16 = params->n_w16, b8 = params->n_w16 + params->n_w8;
-    for (int i = 0; i < n && c->validate; i++) {
-        if (c->validate == 1 && (i & 63) && i != b16 - 1 && i != b16 && i != b8 - 1 && i != b8 && i != n - 1)
-            continue;
-        const int want = i < params->n_w16 ? 16 : i < params->n_w16 + params->n_w8 ? 8 : 4;
-        if (blocks[i].w != want) {
-            set_error("vvcb200_pic_inter: block %d has width %d where the width order (n_w16 %d, n_w8 %d) wants %d",
-                      i, blocks[i].w, params->n_w16, params->n_w8, want);
-            return VVCB200_ERR_ARG;
-        }
+    auto check_block = [&](int i) {
+        if (i < 0 || i >= n)
+            return true;
+        const int want = i < b16 ? 16 : i < b8 ? 8 : 4;
+        if (blocks[i].w == want)
+            return true;
+        set_error("vvcb200_pic_inter: block %d has width %d where the width order (n_w16 %d, n_w8 %d) wants %d",
+                  i, blocks[i].w, params->n_w16, params->n_w8, want);
+        return false;
+    };
+    if (c->validate) {
+        for (int i = 0; i < n; i += c->validate == 1 ? 64 : 1)
+            if (!check_block(i))
+                return VVCB200_ERR_ARG;
+        for (int i : { b16 - 1, b16, b8 - 1, b8, n - 1 })               // both sides of every class boundary
+            if (!check_block(i))
+                return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
     StageSet &S = c->sets[c->set];
@@ -403,10 +464,15 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
                 set_error("vvcb200_pic_inter: ref_slot[%d][%d] = %d is not a DPB slot of this context", l, i, params->ref_slot[l][i]);
                 return VVCB200_ERR_ARG;
             }
+    for (int l = 0; l < 2; l++)                   // reference pictures the other lane is still writing
+        for (int i = 0; i < 16; i++)
+            if (params->ref_slot[l][i] != c->cur)
+                if (int r = order_before_read(c, params->ref_slot[l][i]))
+                    return r;
     int32_t *d_mv = nullptr;
     if (refined_mv) {
         if ((size_t)n * 4 * sizeof(int32_t) > S.refined.cap)
-            VVC_CUDA(cudaStreamSynchronize(c->stream));
+            VVC_CUDA(cudaStreamSynchronize(S.stream));
         if (int r = S.refined.reserve((size_t)n * 4 * sizeof(int32_t)))
             return r;
         d_mv = (int32_t *)S.refined.p;
@@ -420,12 +486,12 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     if (int r = uploads_visible(c))
         return r;
     if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)S.blocks.p, n, params,
-                                    d_lut, nullptr, d_mv, d_prof, c->stream))
+                                    d_lut, nullptr, d_mv, d_prof, S.stream))
         return r;
     if (int r = set_consumed(c))
         return r;
     if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
-        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, S.stream));
     return 0;
 }
 
@@ -449,17 +515,28 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
             bound[k] = acc;
         }
         bound[4] = n;
-        for (int i = 0, k = 0; i < n && c->validate; i++) {
+        auto check_tb = [&](int i) {
+            if (i < 0 || i >= n)
+                return true;
+            int k = 0;
             while (k < 4 && i >= bound[k])
                 k++;
-            if (c->validate == 1 && (i & 63) && i != n - 1 && !(k < 4 && (i == bound[k] - 1)) && !(k > 0 && i == bound[k - 1]))
-                continue;
-            if (vvcb200_residual_class(&tbs[i]) != k) {
-                set_error("vvcb200_pic_residual: block %d is of class %d where the class order (n_class %d %d %d %d) wants %d",
-                          i, vvcb200_residual_class(&tbs[i]), params->n_class[0], params->n_class[1], params->n_class[2],
-                          params->n_class[3], k);
+            if (vvcb200_residual_class(&tbs[i]) == k)
+                return true;
+            set_error("vvcb200_pic_residual: block %d is of class %d where the class order (n_class %d %d %d %d) wants %d",
+                      i, vvcb200_residual_class(&tbs[i]), params->n_class[0], params->n_class[1], params->n_class[2],
+                      params->n_class[3], k);
+            return false;
+        };
+        if (c->validate) {
+            for (int i = 0; i < n; i += c->validate == 1 ? 64 : 1)
+                if (!check_tb(i))
+                    return VVCB200_ERR_ARG;
+            for (int k = 0; k < 4; k++)                                   // both sides of every class boundary
+                if (!check_tb(bound[k] - 1) || !check_tb(bound[k]))
+                    return VVCB200_ERR_ARG;
+            if (!check_tb(n - 1))
                 return VVCB200_ERR_ARG;
-            }
         }
     }
     DeviceGuard g(c->device);
@@ -471,15 +548,15 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
     const VVCB200Planes *res = nullptr;
     for (int i = 0; i < n && !res; i++)
         if (tbs[i].flags & VVCB200_TB_TO_RESIDUAL) {
-            if (!c->residual.base)
-                if (int r = alloc_picture(c, &c->residual))
+            if (!S.residual.base)
+                if (int r = alloc_picture(c, &S.residual))
                     return r;
-            res = &c->residual.planes;
+            res = &S.residual.planes;
         }
     if (int r = uploads_visible(c))
         return r;
     if (int r = vvcb200_residual_batch(&c->dpb[c->cur].planes, res, (const int16_t *)S.levels.p,
-                                       (const VVCB200TransformBlock *)S.tbs.p, n, params, c->stream))
+                                       (const VVCB200TransformBlock *)S.tbs.p, n, params, S.stream))
         return r;
     return set_consumed(c);
 }
@@ -505,12 +582,14 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         set_error("vvcb200_pic_intra: bad record ranges");
         return VVCB200_ERR_ARG;
     }
-    bool needs_res = false;
-    for (int i = 0; i < n; i++) {
+    StageSet &S = c->sets[c->set];
+    const bool have_res = S.residual.base != nullptr;                     // residual planes of this lane exist
+    for (int i = 0; i < n && c->validate; i = (i == n - 1 || c->validate == 2) ? i + 1 : (i + 64 < n ? i + 64 : n - 1)) {
         const VVCB200IntraBlock &b = blocks[i];
-        needs_res |= (b.flags & VVCB200_IB_RESIDUAL) != 0;
-        if (!c->validate || (c->validate == 1 && (i & 63) && i != n - 1))
-            continue;
+        if ((b.flags & VVCB200_IB_RESIDUAL) && !have_res) {
+            set_error("vvcb200_pic_intra: records add a residual but vvcb200_pic_residual stored none for this picture");
+            return VVCB200_ERR_ARG;
+        }
         const int pw = b.c_idx ? c->width >> c->hshift : c->width, ph = b.c_idx ? c->height >> c->vshift : c->height;
         if (b.c_idx > 2 || !b.w || !b.h || b.w > 64 || b.h > 64 || (b.w & (b.w - 1)) || (b.h & (b.h - 1)) ||
             b.x0 + b.w > pw || b.y0 + b.h > ph || (b.x0 & 3) || (b.y0 & (b.c_idx ? 1 : 3)) || b.mode > 83 || b.mode < -14 ||
@@ -520,14 +599,11 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
             return VVCB200_ERR_ARG;
         }
     }
-    if (needs_res && !c->residual.base) {
-        set_error("vvcb200_pic_intra: records add a residual but vvcb200_pic_residual stored none for this picture");
-        return VVCB200_ERR_ARG;
-    }
     DeviceGuard g(c->device);
-    StageSet &S = c->sets[c->set];
-    if (S.in_use)                         // the copy that last read this set's pinned staging must be over
-        VVC_CUDA(cudaEventSynchronize(S.uploaded));
+    if (S.order_pending) {                // the copy that last read this set's pinned staging (two pictures ago) must be over
+        VVC_CUDA(cudaEventSynchronize(S.order_copied));
+        S.order_pending = false;
+    }
     if ((size_t)n > S.h_order_cap) {      // pinned staging for the scheduled order (this set's previous upload has long finished)
         if (S.h_order)
             cudaFreeHost(S.h_order);
@@ -542,14 +618,16 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return r;
     if (int r = upload(c, S.iblocks, S.h_order, (size_t)n * sizeof(VVCB200IntraBlock)))
         return r;
+    VVC_CUDA(cudaEventRecord(S.order_copied, c->h2d));
+    S.order_pending = true;
     const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
-    if (int r = c->intra_marks.reserve(marks))
+    if (int r = S.intra_marks.reserve(marks))
         return r;
     if (int r = uploads_visible(c))
         return r;
     // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
-    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, needs_res ? &c->residual.planes : nullptr, &c->scratch.planes,
-                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, c->intra_marks.p, c->stream))
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, have_res ? &S.residual.planes : nullptr, &S.scratch.planes,
+                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, S.intra_marks.p, S.stream))
         return r;
     return set_consumed(c);
 }
@@ -566,7 +644,7 @@ int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
         return r;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, c->stream))
+    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.stream))
         return r;
     return set_consumed(c);
 }
@@ -585,7 +663,7 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
     const size_t n_ctb = (size_t)((c->width + (1 << shift) - 1) >> shift) * ((c->height + (1 << shift) - 1) >> shift);
     // one device arena: 6 edge tables, 3 qp tables, the per-CTB offsets
     if (units * 9 + n_ctb * 6 + 64 > S.db_tables.cap) {
-        VVC_CUDA(cudaStreamSynchronize(c->stream));
+        VVC_CUDA(cudaStreamSynchronize(S.stream));
         VVC_CUDA(cudaStreamSynchronize(c->h2d));
     }
     if (int r = S.db_tables.reserve(units * 9 + n_ctb * 6 + 64))
@@ -615,7 +693,7 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
     dt.d_ctb_offsets = (const int8_t *)d;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, c->stream))
+    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, S.stream))
         return r;
     return set_consumed(c);
 }
@@ -631,13 +709,13 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
     StageSet &S = c->sets[c->set];
     const int sh = ctb_log2_size;
     const size_t n_ctb = (size_t)((c->width + (1 << sh) - 1) >> sh) * ((c->height + (1 << sh) - 1) >> sh);
-    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &c->scratch.planes;
+    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &S.scratch.planes;
     if (sao) {
         if (int r = upload(c, S.sao, sao, n_ctb * sizeof(*sao)))
             return r;
         if (int r = uploads_visible(c))
             return r;
-        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, c->stream))
+        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, S.stream))
             return r;
     }
     if (alf) {
@@ -648,20 +726,20 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
         if (!sao) {
             // ALF reads `tmp`: without SAO the source is the current picture itself
             const size_t bytes = (size_t)cur->stride[0] * cur->height[0] + 2 * (size_t)cur->stride[1] * cur->height[1];
-            VVC_CUDA(cudaMemcpyAsync(c->scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, c->stream));
+            VVC_CUDA(cudaMemcpyAsync(S.scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, S.stream));
         }
         if (int r = uploads_visible(c))
             return r;
         if (int r = vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)S.alf.p, (const VVCB200AlfParams *)S.alf_params.p,
-                                        ctb_log2_size, c->bit_depth, c->stream))
+                                        ctb_log2_size, c->bit_depth, S.stream))
             return r;
         return set_consumed(c);
     }
     if (sao) {
         // SAO only: its output becomes the picture (swap the buffers instead of copying back)
         DevPicture t = c->dpb[c->cur];
-        c->dpb[c->cur] = c->scratch;
-        c->scratch = t;
+        c->dpb[c->cur] = S.scratch;
+        S.scratch = t;
         return set_consumed(c);
     }
     return 0;

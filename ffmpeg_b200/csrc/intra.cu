@@ -195,8 +195,9 @@ __device__ __forceinline__ void record_extent(const VVCB200IntraBlock &b, int &w
 
 __device__ __forceinline__ bool in_place(const VVCB200IntraBlock &b) { return b.flags & (VVCB200_IB_CIIP | VVCB200_IB_ADD_ONLY); }
 
-// Eight threads per record: most records are 4x4 .. 8x8 blocks, i.e. 4 .. 16 pieces of 8 bytes.
-constexpr int kMarkLanes = 8;
+// Threads per record.  (Most records are 4 .. 16 pieces of 8 bytes, but 8 threads per record measured slower than a
+// warp per record: the records sharing a warp differ in size and their loops serialise.)
+constexpr int kMarkLanes = 32;
 __global__ void intra_mark_kernel(IntraArgs a)
 {
     const int lane = threadIdx.x & (kMarkLanes - 1);

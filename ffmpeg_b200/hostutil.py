@@ -59,9 +59,9 @@ class EnginePicture:
                           (pic["width"] + (1 << ctb) - 1) >> ctb, (pic["height"] + (1 << ctb) - 1) >> ctb, ia["params"])
         self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
         # pictures are reconstructed into the slots after the references (ref_slot[][] already maps to 0..n_refs-1),
-        # alternating between two slots / two host frames when the context has them, as consecutive pictures of a
-        # decoder do: the download of one picture then overlaps the reconstruction of the next
-        self.n_slots = max(1, min(2, ctx.dpb_size - self.n_refs))
+        # rotating over up to four slots / host frames when the context has them, as consecutive pictures of a decoder
+        # do: the download of one picture then overlaps the reconstruction of the next ones (two compute lanes)
+        self.n_slots = max(1, min(4, ctx.dpb_size - self.n_refs))
         self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
         self.count = 0
         self.out = self.outs[0]

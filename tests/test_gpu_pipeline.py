@@ -68,6 +68,40 @@ def test_back_to_back_pictures_overlap_safely():
         ctx.close()
 
 
+def test_picture_that_references_its_predecessor():
+    """Consecutive pictures run in different lanes of the context (separate compute streams).  Here the second picture
+    predicts from the first one's output, so its INTER stage has to wait for the other lane; submitted three times
+    without a sync in between, so the first picture's slot is also rewritten while its reader may still be running."""
+    import copy
+    from ffmpeg_b200 import abi
+    pic = synth.full_picture(33, 416, 240, ctb_log2=6, intra_fraction=0.2)
+    out1 = pipeline.oracle_picture(pic)
+    n_refs = len(pic["inter"]["refs"])
+    pic2 = dict(pic, inter=dict(pic["inter"], refs=[[p.copy() for p in out1]] + list(pic["inter"]["refs"][1:])))
+    want1, want2 = util.plane_md5(out1), util.plane_md5(pipeline.oracle_picture(pic2))
+    assert want1 != want2
+    ctx = lib.Context(0, 416, 240, dpb_size=n_refs + 2)
+    try:
+        ep1 = pipeline.EnginePicture(ctx, pic)
+        ep1.upload_refs()
+        eng2 = copy.copy(pic2)
+        eng2["inter"] = dict(pic2["inter"], params=abi.InterParams.from_buffer_copy(bytes(pic["inter"]["params"])))
+        for l in range(2):
+            for i in range(16):
+                if eng2["inter"]["params"].ref_slot[l][i] == 0:
+                    eng2["inter"]["params"].ref_slot[l][i] = n_refs          # the slot ep1 reconstructs into
+        ep2 = pipeline.EnginePicture(ctx, eng2)
+        for _ in range(3):
+            ep1.count, ep2.count = 0, 1                                       # ep1 -> slot n_refs, ep2 -> slot n_refs + 1
+            ep1.run()
+            ep2.run()
+        ctx.sync()
+        assert util.plane_md5(ep1.outs[0]) == want1
+        assert util.plane_md5(ep2.outs[1]) == want2
+    finally:
+        ctx.close()
+
+
 @pytest.mark.parametrize("seed,w,h,ctb,lmcs,frac", [(41, 256, 128, 6, False, 0.0), (42, 256, 128, 5, True, 0.0),
                                                     (43, 208, 120, 6, True, 0.4), (44, 416, 240, 7, False, 1.0),
                                                     (45, 832, 480, 7, True, 0.2)])

@@ -16,7 +16,7 @@ def main():
     import torch
     width, height = 3840, 2160
     pic = bench.make_picture(2026, width, height, 0.1)
-    ctx = lib.Context(0, width, height, dpb_size=4, validate=1)
+    ctx = lib.Context(0, width, height, dpb_size=6, validate=1)
     ep = pipeline.EnginePicture(ctx, pic)
     ep.upload_refs()
     for _ in range(3):
