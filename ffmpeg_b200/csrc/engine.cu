@@ -60,16 +60,21 @@ struct DeviceGuard {
 
 }  // namespace
 
-// Everything one picture in flight owns: the device copies of its host descriptor batches, its compute stream and its
-// working pictures.  Two sets alternate from picture to picture, so that the uploads of picture n + 1 (copy stream)
-// overlap the kernels of picture n — and so do its kernels, wherever picture n + 1 does not read picture n: the intra
+// Pictures in flight.  A lane is a compute stream with its working pictures; consecutive pictures alternate between the
+// two lanes, so that the kernels of picture n + 1 overlap those of picture n wherever n + 1 does not read n: the intra
 // stage is bound by dependency latency and leaves most issue slots of the GPU free for the neighbour's INTER / residual
-// kernels.  Pictures that do depend on each other (through the DPB) are ordered with per-slot events.
-struct StageSet {
+// kernels.  Pictures that do depend on each other (through the DPB) are ordered with per-slot events.  A stage set is
+// the device copy of one picture's host descriptor batches; four sets rotate (two per lane), so that the uploads of a
+// lane's next picture (copy stream) overlap the kernels of its current one.
+struct Lane {
     cudaStream_t stream = nullptr; // this lane's compute stream
     DevPicture scratch;            // SAO output / ALF input; before that, the intra stage's shadow picture
     DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
     DevBuffer intra_marks;
+};
+constexpr int kLanes = 2, kSets = 4;   // two descriptor sets per lane: the next picture of a lane uploads while this one runs
+struct StageSet {
+    Lane *lane = nullptr;          // sets[i] belongs to lanes[i % kLanes]
     DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks;
     VVCB200IntraBlock *h_order = nullptr;  // pinned: the picture's intra records in scheduled order
     size_t h_order_cap = 0;
@@ -91,12 +96,14 @@ struct VVCB200Ctx {
     std::vector<signed char> writer;       // per DPB slot: lane of that write, -1 if none yet
     std::vector<unsigned char> readers;    // per DPB slot: lanes that have used it as a reference since
     int cur = 0;
-    StageSet sets[2];
+    Lane lanes[kLanes];
+    StageSet sets[kSets];
     int set = 0;
     int validate = 1;              // 0: trust the emitter, 1: spot checks (class boundaries + every 64th record), 2: every record
 };
 
-static inline cudaStream_t lane_stream(VVCB200Ctx *c) { return c->sets[c->set].stream; }
+static inline int lane_of(int set) { return set % kLanes; }
+static inline cudaStream_t lane_stream(VVCB200Ctx *c) { return c->lanes[lane_of(c->set)].stream; }
 
 namespace {
 
@@ -146,7 +153,7 @@ int uploads_visible(VVCB200Ctx *c)
 {
     StageSet &s = c->sets[c->set];
     VVC_CUDA(cudaEventRecord(s.uploaded, c->h2d));
-    VVC_CUDA(cudaStreamWaitEvent(s.stream, s.uploaded, 0));
+    VVC_CUDA(cudaStreamWaitEvent(s.lane->stream, s.uploaded, 0));
     return 0;
 }
 
@@ -154,34 +161,35 @@ int uploads_visible(VVCB200Ctx *c)
 int set_consumed(VVCB200Ctx *c)
 {
     StageSet &s = c->sets[c->set];
-    VVC_CUDA(cudaEventRecord(s.consumed, s.stream));
-    VVC_CUDA(cudaEventRecord(c->written[c->cur], s.stream));
-    c->writer[c->cur] = (signed char)c->set;
+    VVC_CUDA(cudaEventRecord(s.consumed, s.lane->stream));
+    VVC_CUDA(cudaEventRecord(c->written[c->cur], s.lane->stream));
+    c->writer[c->cur] = (signed char)lane_of(c->set);
     s.in_use = true;
     return 0;
 }
 
-// Lane `c->set` is about to overwrite DPB slot `slot`: wait for the other lane's write of it and for the other lane's
+// The current lane is about to overwrite DPB slot `slot`: wait for the other lane's write of it and for the other lane's
 // pictures that use it as a reference (everything that lane has queued so far).
 int order_before_write(VVCB200Ctx *c, int slot)
 {
-    const int other = c->set ^ 1;
+    const int other = lane_of(c->set) ^ 1;
     if (c->writer[slot] == other)
         VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
     if ((c->readers[slot] >> other) & 1) {
-        if (c->sets[other].in_use)
-            VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->sets[other].consumed, 0));
+        const StageSet &prev = c->sets[(c->set + kSets - 1) % kSets];     // the other lane's latest picture
+        if (prev.in_use)
+            VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), prev.consumed, 0));
     }
     c->readers[slot] = 0;
     return 0;
 }
 
-// Lane `c->set` is about to read DPB slot `slot` as a reference picture.
+// The current lane is about to read DPB slot `slot` as a reference picture.
 int order_before_read(VVCB200Ctx *c, int slot)
 {
-    if (c->writer[slot] == (c->set ^ 1))
+    if (c->writer[slot] == (lane_of(c->set) ^ 1))
         VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
-    c->readers[slot] |= (unsigned char)(1u << c->set);
+    c->readers[slot] |= (unsigned char)(1u << lane_of(c->set));
     return 0;
 }
 
@@ -228,9 +236,11 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     c->bit_depth = bit_depth;
     cudaError_t e = cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking);
-    for (int i = 0; i < 2 && e == cudaSuccess; i++) {
-        e = cudaStreamCreateWithFlags(&c->sets[i].stream, cudaStreamNonBlocking);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
+    for (int i = 0; i < kLanes && e == cudaSuccess; i++)
+        e = cudaStreamCreateWithFlags(&c->lanes[i].stream, cudaStreamNonBlocking);
+    for (int i = 0; i < kSets && e == cudaSuccess; i++) {
+        c->sets[i].lane = &c->lanes[lane_of(i)];
+        e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].consumed, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].order_copied, cudaEventDisableTiming);
     }
@@ -248,9 +258,9 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
         return cuda_fail(e, "stream / event creation", __FILE__, __LINE__);
     }
     c->dpb.resize(dpb_size);
-    int r = alloc_picture(c, &c->sets[0].scratch);
+    int r = alloc_picture(c, &c->lanes[0].scratch);
     if (!r)
-        r = alloc_picture(c, &c->sets[1].scratch);
+        r = alloc_picture(c, &c->lanes[1].scratch);
     for (int i = 0; !r && i < dpb_size; i++)
         r = alloc_picture(c, &c->dpb[i]);
     if (!r && cudaStreamSynchronize(lane_stream(c)) != cudaSuccess)     // the pictures are cleared before either lane runs
@@ -268,11 +278,11 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     if (!c)
         return;
     DeviceGuard g(c->device);
-    for (cudaStream_t st : { c->sets[0].stream, c->sets[1].stream, c->h2d, c->d2h })
+    for (cudaStream_t st : { c->lanes[0].stream, c->lanes[1].stream, c->h2d, c->d2h })
         if (st)
             cudaStreamSynchronize(st);
     for (StageSet &ss : c->sets) {
-        DevBuffer *bufs[] = { &ss.intra_marks, &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
+        DevBuffer *bufs[] = { &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
                               &ss.sao, &ss.alf, &ss.alf_params, &ss.iblocks };
         for (DevBuffer *b : bufs)
             b->release();
@@ -280,8 +290,11 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
         if (ss.uploaded) cudaEventDestroy(ss.uploaded);
         if (ss.consumed) cudaEventDestroy(ss.consumed);
         if (ss.order_copied) cudaEventDestroy(ss.order_copied);
-        if (ss.scratch.base) cudaFree(ss.scratch.base);
-        if (ss.residual.base) cudaFree(ss.residual.base);
+    }
+    for (Lane &l : c->lanes) {
+        l.intra_marks.release();
+        if (l.scratch.base) cudaFree(l.scratch.base);
+        if (l.residual.base) cudaFree(l.residual.base);
     }
     for (cudaEvent_t ev : c->downloaded)
         if (ev)
@@ -292,7 +305,7 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     for (DevPicture &p : c->dpb)
         if (p.base)
             cudaFree(p.base);
-    for (cudaStream_t st : { c->sets[0].stream, c->sets[1].stream, c->h2d, c->d2h })
+    for (cudaStream_t st : { c->lanes[0].stream, c->lanes[1].stream, c->h2d, c->d2h })
         if (st)
             cudaStreamDestroy(st);
     delete c;
@@ -304,8 +317,8 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
         return VVCB200_ERR_ARG;
     DeviceGuard g(c->device);
     VVC_CUDA(cudaStreamSynchronize(c->h2d));
-    VVC_CUDA(cudaStreamSynchronize(c->sets[0].stream));
-    VVC_CUDA(cudaStreamSynchronize(c->sets[1].stream));
+    VVC_CUDA(cudaStreamSynchronize(c->lanes[0].stream));
+    VVC_CUDA(cudaStreamSynchronize(c->lanes[1].stream));
     VVC_CUDA(cudaStreamSynchronize(c->d2h));
     for (char &p : c->download_pending)
         p = 0;
@@ -365,12 +378,12 @@ int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
     }
     DeviceGuard g(c->device);
     c->cur = slot;
-    c->set ^= 1;
+    c->set = (c->set + 1) % kSets;
     StageSet &s = c->sets[c->set];
     if (s.in_use)                         // uploads of this picture must not overtake the kernels of the picture before last
         VVC_CUDA(cudaStreamWaitEvent(c->h2d, s.consumed, 0));
     if (c->download_pending[slot]) {      // the slot's previous content is still on its way to the host
-        VVC_CUDA(cudaStreamWaitEvent(s.stream, c->downloaded[slot], 0));
+        VVC_CUDA(cudaStreamWaitEvent(s.lane->stream, c->downloaded[slot], 0));
         c->download_pending[slot] = 0;
     }
     return order_before_write(c, slot);
@@ -392,7 +405,7 @@ int vvcb200_pic_upload(VVCB200Ctx *c, int slot, const uint16_t *const planes[3],
         VVC_CUDA(cudaMemcpy2DAsync(p->planes.d_plane[i], p->planes.stride[i], planes[i], strides[i],
                                    (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyHostToDevice, lane_stream(c)));
     VVC_CUDA(cudaEventRecord(c->written[idx], lane_stream(c)));
-    c->writer[idx] = (signed char)c->set;
+    c->writer[idx] = (signed char)lane_of(c->set);
     return 0;
 }
 
@@ -472,7 +485,7 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     int32_t *d_mv = nullptr;
     if (refined_mv) {
         if ((size_t)n * 4 * sizeof(int32_t) > S.refined.cap)
-            VVC_CUDA(cudaStreamSynchronize(S.stream));
+            VVC_CUDA(cudaStreamSynchronize(S.lane->stream));
         if (int r = S.refined.reserve((size_t)n * 4 * sizeof(int32_t)))
             return r;
         d_mv = (int32_t *)S.refined.p;
@@ -486,12 +499,12 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     if (int r = uploads_visible(c))
         return r;
     if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)S.blocks.p, n, params,
-                                    d_lut, nullptr, d_mv, d_prof, S.stream))
+                                    d_lut, nullptr, d_mv, d_prof, S.lane->stream))
         return r;
     if (int r = set_consumed(c))
         return r;
     if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
-        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, S.stream));
+        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, S.lane->stream));
     return 0;
 }
 
@@ -548,15 +561,15 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
     const VVCB200Planes *res = nullptr;
     for (int i = 0; i < n && !res; i++)
         if (tbs[i].flags & VVCB200_TB_TO_RESIDUAL) {
-            if (!S.residual.base)
-                if (int r = alloc_picture(c, &S.residual))
+            if (!S.lane->residual.base)
+                if (int r = alloc_picture(c, &S.lane->residual))
                     return r;
-            res = &S.residual.planes;
+            res = &S.lane->residual.planes;
         }
     if (int r = uploads_visible(c))
         return r;
     if (int r = vvcb200_residual_batch(&c->dpb[c->cur].planes, res, (const int16_t *)S.levels.p,
-                                       (const VVCB200TransformBlock *)S.tbs.p, n, params, S.stream))
+                                       (const VVCB200TransformBlock *)S.tbs.p, n, params, S.lane->stream))
         return r;
     return set_consumed(c);
 }
@@ -583,7 +596,7 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return VVCB200_ERR_ARG;
     }
     StageSet &S = c->sets[c->set];
-    const bool have_res = S.residual.base != nullptr;                     // residual planes of this lane exist
+    const bool have_res = S.lane->residual.base != nullptr;                     // residual planes of this lane exist
     for (int i = 0; i < n && c->validate; i = (i == n - 1 || c->validate == 2) ? i + 1 : (i + 64 < n ? i + 64 : n - 1)) {
         const VVCB200IntraBlock &b = blocks[i];
         if ((b.flags & VVCB200_IB_RESIDUAL) && !have_res) {
@@ -621,13 +634,13 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
     VVC_CUDA(cudaEventRecord(S.order_copied, c->h2d));
     S.order_pending = true;
     const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
-    if (int r = S.intra_marks.reserve(marks))
+    if (int r = S.lane->intra_marks.reserve(marks))
         return r;
     if (int r = uploads_visible(c))
         return r;
     // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
-    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, have_res ? &S.residual.planes : nullptr, &S.scratch.planes,
-                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, S.intra_marks.p, S.stream))
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, have_res ? &S.lane->residual.planes : nullptr, &S.lane->scratch.planes,
+                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, S.lane->intra_marks.p, S.lane->stream))
         return r;
     return set_consumed(c);
 }
@@ -644,7 +657,7 @@ int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
         return r;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.stream))
+    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.lane->stream))
         return r;
     return set_consumed(c);
 }
@@ -663,7 +676,7 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
     const size_t n_ctb = (size_t)((c->width + (1 << shift) - 1) >> shift) * ((c->height + (1 << shift) - 1) >> shift);
     // one device arena: 6 edge tables, 3 qp tables, the per-CTB offsets
     if (units * 9 + n_ctb * 6 + 64 > S.db_tables.cap) {
-        VVC_CUDA(cudaStreamSynchronize(S.stream));
+        VVC_CUDA(cudaStreamSynchronize(S.lane->stream));
         VVC_CUDA(cudaStreamSynchronize(c->h2d));
     }
     if (int r = S.db_tables.reserve(units * 9 + n_ctb * 6 + 64))
@@ -693,7 +706,7 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
     dt.d_ctb_offsets = (const int8_t *)d;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, S.stream))
+    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, S.lane->stream))
         return r;
     return set_consumed(c);
 }
@@ -709,13 +722,13 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
     StageSet &S = c->sets[c->set];
     const int sh = ctb_log2_size;
     const size_t n_ctb = (size_t)((c->width + (1 << sh) - 1) >> sh) * ((c->height + (1 << sh) - 1) >> sh);
-    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &S.scratch.planes;
+    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &S.lane->scratch.planes;
     if (sao) {
         if (int r = upload(c, S.sao, sao, n_ctb * sizeof(*sao)))
             return r;
         if (int r = uploads_visible(c))
             return r;
-        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, S.stream))
+        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, S.lane->stream))
             return r;
     }
     if (alf) {
@@ -726,20 +739,20 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
         if (!sao) {
             // ALF reads `tmp`: without SAO the source is the current picture itself
             const size_t bytes = (size_t)cur->stride[0] * cur->height[0] + 2 * (size_t)cur->stride[1] * cur->height[1];
-            VVC_CUDA(cudaMemcpyAsync(S.scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, S.stream));
+            VVC_CUDA(cudaMemcpyAsync(S.lane->scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, S.lane->stream));
         }
         if (int r = uploads_visible(c))
             return r;
         if (int r = vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)S.alf.p, (const VVCB200AlfParams *)S.alf_params.p,
-                                        ctb_log2_size, c->bit_depth, S.stream))
+                                        ctb_log2_size, c->bit_depth, S.lane->stream))
             return r;
         return set_consumed(c);
     }
     if (sao) {
         // SAO only: its output becomes the picture (swap the buffers instead of copying back)
         DevPicture t = c->dpb[c->cur];
-        c->dpb[c->cur] = S.scratch;
-        S.scratch = t;
+        c->dpb[c->cur] = S.lane->scratch;
+        S.lane->scratch = t;
         return set_consumed(c);
     }
     return 0;
