@@ -124,7 +124,10 @@ __global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
         for (int k = 0; k < kIter; k++) {
             const int i = t + k * 256;
             const int r = i / kPad, col = i - r * kPad;
-            v[k] = i < kPad * kPad ? (uint16_t)padded_sample(src, sstride, g, tx0 + col - kHalo, ty0 + r - kHalo) : (uint16_t)0;
+            if (g.edges == 0)                            // interior CTB: nothing to clamp
+                v[k] = i < kPad * kPad ? src[(ptrdiff_t)(ty0 + r - kHalo) * sstride + tx0 + col - kHalo] : (uint16_t)0;
+            else
+                v[k] = i < kPad * kPad ? (uint16_t)padded_sample(src, sstride, g, tx0 + col - kHalo, ty0 + r - kHalo) : (uint16_t)0;
         }
 #pragma unroll
         for (int k = 0; k < kIter; k++) {
@@ -320,9 +323,17 @@ __global__ void __launch_bounds__(256) alf_chroma_kernel(const AlfArgs a)
     const int ty_ctb = ty0 - g.y0;
 
     if (do_alf) {
-        for (int i = t; i < S * S; i += 256) {
-            const int r = i / S, col = i - r * S;
-            s_pix[i] = (uint16_t)padded_sample(src, sstride, g, tx0 + col - 2, ty0 + r - 2);
+        if (g.edges == 0) {                              // interior CTB: the halo is simply the neighbours' samples
+            const uint16_t *org = src + (ptrdiff_t)(ty0 - 2) * sstride + tx0 - 2;
+            for (int i = t; i < S * S; i += 256) {
+                const int r = i / S, col = i - r * S;
+                s_pix[i] = org[(ptrdiff_t)r * sstride + col];
+            }
+        } else {
+            for (int i = t; i < S * S; i += 256) {
+                const int r = i / S, col = i - r * S;
+                s_pix[i] = (uint16_t)padded_sample(src, sstride, g, tx0 + col - 2, ty0 + r - 2);
+            }
         }
         __syncthreads();
     }
@@ -380,15 +391,23 @@ __global__ void __launch_bounds__(256) alf_chroma_kernel(const AlfArgs a)
                 r3 = r2;
             else if (pos == vb_luma - 1 || pos == vb_luma)
                 r3 = r2 = r0 = ly;
-            const int cur = padded_sample(lp, ls, gl, lx, ly);
             int sum = 0;
-            sum += fc[0] * (padded_sample(lp, ls, gl, lx, r0) - cur);
-            sum += fc[1] * (padded_sample(lp, ls, gl, lx - 1, ly) - cur);
-            sum += fc[2] * (padded_sample(lp, ls, gl, lx + 1, ly) - cur);
-            sum += fc[3] * (padded_sample(lp, ls, gl, lx - 1, r2) - cur);
-            sum += fc[4] * (padded_sample(lp, ls, gl, lx, r2) - cur);
-            sum += fc[5] * (padded_sample(lp, ls, gl, lx + 1, r2) - cur);
-            sum += fc[6] * (padded_sample(lp, ls, gl, lx, r3) - cur);
+            if (gl.edges == 0) {                         // interior CTB: no coordinate needs clamping
+                const uint16_t *q0 = lp + (size_t)r0 * ls + lx, *q1 = lp + (size_t)ly * ls + lx;
+                const uint16_t *q2 = lp + (size_t)r2 * ls + lx, *q3 = lp + (size_t)r3 * ls + lx;
+                const int cur = q1[0];
+                sum = fc[0] * (q0[0] - cur) + fc[1] * (q1[-1] - cur) + fc[2] * (q1[1] - cur) + fc[3] * (q2[-1] - cur) +
+                      fc[4] * (q2[0] - cur) + fc[5] * (q2[1] - cur) + fc[6] * (q3[0] - cur);
+            } else {
+                const int cur = padded_sample(lp, ls, gl, lx, ly);
+                sum += fc[0] * (padded_sample(lp, ls, gl, lx, r0) - cur);
+                sum += fc[1] * (padded_sample(lp, ls, gl, lx - 1, ly) - cur);
+                sum += fc[2] * (padded_sample(lp, ls, gl, lx + 1, ly) - cur);
+                sum += fc[3] * (padded_sample(lp, ls, gl, lx - 1, r2) - cur);
+                sum += fc[4] * (padded_sample(lp, ls, gl, lx, r2) - cur);
+                sum += fc[5] * (padded_sample(lp, ls, gl, lx + 1, r2) - cur);
+                sum += fc[6] * (padded_sample(lp, ls, gl, lx, r3) - cur);
+            }
             sum = clip3((sum + 64) >> 7, -(1 << (a.bd - 1)), (1 << (a.bd - 1)) - 1);
             v = clip_pixel(v + sum, a.bd);
         }
