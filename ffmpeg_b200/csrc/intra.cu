@@ -32,6 +32,10 @@ constexpr int kSlots   = 1;       // records a warp holds at a time (1: it simpl
 constexpr int kEdgeLen = 256;     // samples per edge array: indices -72 .. 183 are addressable
 constexpr int kEdgeOrg = 72;
 constexpr unsigned kFull = 0xffffffffu;
+#ifndef VVC_INTRA_BACKOFF_MAX
+#define VVC_INTRA_BACKOFF_MAX 256
+#endif
+constexpr unsigned kBackoffMax = VVC_INTRA_BACKOFF_MAX;                   // ns between two looks at neighbours that are not there yet
 constexpr unsigned kSentinel = 0xffffu;                                   // "not reconstructed yet"
 #ifdef VVC_INTRA_PROFILE
 __device__ unsigned long long g_prof[8];      // cycles: 0 ticket+record, 1 record total, 2 publish; 3 records; 4 wait (inside 1)
@@ -411,7 +415,7 @@ __device__ bool spans_ready(const IntraArgs &a, const Span *sp, int n, int lane,
     if (!n)
         return true;
     unsigned m;
-    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
         m = 0;
         for (int i = 0; i < n; i++)
             m |= sp[i].horizontal ? row_marks(a, sp[i].c, sp[i].uy, sp[i].ux, sp[i].n, lane)
@@ -448,7 +452,7 @@ __device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b
     }
     const uint16_t *luma = a.pic.p[0] + (size_t)y * a.pic.stride[0] + x;
     int sum, cnt;
-    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
         bool bad = false;
         sum = cnt = 0;
         if (al) {                                                         // past the picture edge the last sample repeats
@@ -621,7 +625,7 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     // ---- gather the edges into shared memory; a sentinel among them means "not reconstructed yet": read again
     const long long g0 = PROF_T();
     uint16_t *left = ws.edge[0] + kEdgeOrg, *top = ws.edge[1] + kEdgeOrg;
-    for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+    for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
         unsigned lv[4], tv[4], vl = 0, vt = 0;
 #pragma unroll
         for (int k = 0; k < 4; k++) {
@@ -961,7 +965,7 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
             cnt[i] = min(num[i], (1 + is4) << 1);
         }
         int v0 = 0, v1 = 0, v2 = 0;                                       // lane i gathers neighbour sample i
-        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {  // until none of the neighbours is a sentinel
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {  // until none of the neighbours is a sentinel
         bool bad = false;
         if (lane < cnt[0]) {
             const int pos = start[0] + lane * step[0], lx = pos * 2;
@@ -1054,7 +1058,7 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
     uint16_t *win = reinterpret_cast<uint16_t *>(big ? ar.stage_extra : ws.stage_extra);
     {
         const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
-        for (unsigned backoff = 32;; backoff = min(backoff * 2, 256u)) {
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
             bool bad = false;
             for (int i = lane; i < 2 * w; i += 32)
                 bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
