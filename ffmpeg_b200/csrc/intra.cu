@@ -51,11 +51,15 @@ __device__ unsigned long long g_prof[8];      // cycles: 0 ticket+record, 1 reco
 // reads never sits on the picture's dependency chain; CCLM stages the co-located luma window here after the wait.
 // The per-warp buffers hold records of up to kSmallSamples samples, which is nearly all of them: the kernel lives on
 // the number of resident warps (each spends most of its time in L2 round trips), and buffers sized for the largest
-// block would allow 8 warps per SM instead of 16.  A larger record borrows the CTA's one arena, and only once
+// block would allow 8 warps per SM instead of 12 .. 16.  A larger record borrows the CTA's one arena, and only once
 // everything it waits for is there, so that an arena holder never blocks on another record.
-constexpr int kSmallSamples = 1024;
+#ifndef VVC_INTRA_SMALL
+#define VVC_INTRA_SMALL 1024
+#define VVC_INTRA_SMALL_EXTRA 2624
+#endif
+constexpr int kSmallSamples = VVC_INTRA_SMALL;
 constexpr int kSmallRes   = kSmallSamples * 2;                            // residual block, or Cb + Cr residual of a CCLM record
-constexpr int kSmallExtra = 2624;                                         // CIIP inter prediction; CCLM luma window (16x16, 8x32 chroma)
+constexpr int kSmallExtra = VVC_INTRA_SMALL_EXTRA;                        // CIIP inter prediction; CCLM luma window (16x16, 8x32 chroma)
 constexpr int kArenaRes   = 64 * 64 * 2;
 constexpr int kArenaExtra = 65 * 68 * 2 + 16;
 struct __align__(16) WarpScratch {
@@ -954,6 +958,51 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
                 emit(c, idx & (w - 1), idx >> lw, 1 << (bd - 1));
         return true;
     }
+    // The co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte
+    // pieces.  It comes after the model: the block's own luma is usually the last thing to arrive, and by then only the
+    // fetch, the down-sampling and the stores are left.  Poll its last row cheaply, then fetch and verify everything.
+    uint16_t *win = reinterpret_cast<uint16_t *>(big ? ar.stage_extra : ws.stage_extra);
+    auto stage_window = [&]() -> bool {
+        const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
+        for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
+            bool bad = false;
+            for (int i = lane; i < 2 * w; i += 32)
+                bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
+            if (!__any_sync(kFull, bad)) {
+                if (big && !arena_held) {                                 // look only: the arena is not ours while we may still wait
+                    for (int i = lane; i < per_row * rows; i += 32) {
+                        const int r = i / per_row, q = i - r * per_row;
+                        const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
+                        bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
+                    }
+                    if (__any_sync(kFull, bad)) {
+                        if (!blocking)
+                            return false;
+                        __nanosleep(backoff);
+                        continue;
+                    }
+                    arena_acquire(ar, lane);
+                    arena_held = true;
+                }
+                for (int i = lane; i < per_row * rows; i += 32) {
+                    const int r = i / per_row, q = i - r * per_row;
+                    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
+                    bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
+                    *reinterpret_cast<uint2 *>(win + (r + 1 + wy0) * wpitch + 4 + wx0 + 4 * q) = v;
+                }
+                if (!__any_sync(kFull, bad))
+                    return true;
+            }
+            if (!blocking)
+                return false;
+            __nanosleep(backoff);
+        }
+    };
+    // A record with buffers of its own fetches the window first: it then travels while the warp waits for the chroma
+    // neighbours, which is what the chains of an intra picture run through.  A record that borrows the arena may only
+    // take it once nothing is left to wait for, so its window comes after the neighbours.
+    if (!big && !stage_window())
+        return false;
 #define L(dx, dy) checked_load(luma + (dx) + (ptrdiff_t)ls * (dy), bad)
     int ka[2] = { 0, 0 }, kb[2] = { 1 << (bd - 1), 1 << (bd - 1) }, kk[2] = { 0, 0 };
     if (num[0] || num[1]) {
@@ -1052,46 +1101,8 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
             }
         }
     }
-    // The co-located luma window, columns -4 (or 0) .. 2w - 1, rows -1 (or 0) .. 2h - 1, into shared memory in 8-byte
-    // pieces.  It comes after the model: the block's own luma is usually the last thing to arrive, and by then only the
-    // fetch, the down-sampling and the stores are left.  Poll its last row cheaply, then fetch and verify everything.
-    uint16_t *win = reinterpret_cast<uint16_t *>(big ? ar.stage_extra : ws.stage_extra);
-    {
-        const int per_row = (2 * w - wx0) >> 2, rows = 2 * h - wy0;
-        for (unsigned backoff = 32;; backoff = min(backoff * 2, kBackoffMax)) {
-            bool bad = false;
-            for (int i = lane; i < 2 * w; i += 32)
-                bad |= __ldcg(luma + (ptrdiff_t)ls * (2 * h - 1) + i) == kSentinel;
-            if (!__any_sync(kFull, bad)) {
-                if (big && !arena_held) {                                 // look only: the arena is not ours while we may still wait
-                    for (int i = lane; i < per_row * rows; i += 32) {
-                        const int r = i / per_row, q = i - r * per_row;
-                        const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
-                        bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
-                    }
-                    if (__any_sync(kFull, bad)) {
-                        if (!blocking)
-                            return false;
-                        __nanosleep(backoff);
-                        continue;
-                    }
-                    arena_acquire(ar, lane);
-                    arena_held = true;
-                }
-                for (int i = lane; i < per_row * rows; i += 32) {
-                    const int r = i / per_row, q = i - r * per_row;
-                    const uint2 v = __ldcg(reinterpret_cast<const uint2 *>(luma + (ptrdiff_t)ls * (wy0 + r) + wx0 + 4 * q));
-                    bad |= (v.x & 0xffffu) == kSentinel || (v.x >> 16) == kSentinel || (v.y & 0xffffu) == kSentinel || (v.y >> 16) == kSentinel;
-                    *reinterpret_cast<uint2 *>(win + (r + 1 + wy0) * wpitch + 4 + wx0 + 4 * q) = v;
-                }
-                if (!__any_sync(kFull, bad))
-                    break;
-            }
-            if (!blocking)
-                return false;
-            __nanosleep(backoff);
-        }
-    }
+    if (big && !stage_window())
+        return false;
     stage_residuals();
     stage_wait();
     __syncwarp();
@@ -1482,7 +1493,12 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.total, s));
     intra_mark_kernel<<<(n + 128 / kMarkLanes - 1) / (128 / kMarkLanes), 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
-    int ctas = min((n + kWarps - 1) / kWarps, sm_count() * kCtasPerSm);
+    // Pictures with scattered intra units are bound by the number of records in flight and take every warp the SM holds;
+    // pictures that are mostly intra are bound by their dependency chains, where more pollers only lengthen a step
+    // (4K all-intra: 4.4 ms with 12 warps per SM, 4.8 ms with 16; random access: 2 % the other way).
+    const long long areas = ((long long)pic->width[0] * pic->height[0] + 4095) / 4096;       // 64x64 luma areas
+    const int per_sm = n > 30 * areas ? min(kCtasPerSm, 3) : kCtasPerSm;
+    int ctas = min((n + kWarps - 1) / kWarps, sm_count() * per_sm);
 #ifdef VVC_INTRA_PROFILE
     if (const char *e = getenv("VVC_INTRA_CTAS"))                         // development: occupancy experiments
         ctas = min(ctas, atoi(e));
