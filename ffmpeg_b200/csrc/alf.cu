@@ -82,7 +82,7 @@ __global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
 {
     __shared__ __align__(16) uint16_t s_pix[kPad * kPadStr];
     __shared__ int s_wide;                               // some coefficient of the tile does not fit int8 (never in a conforming stream)
-    __shared__ uint16_t s_grad[kCells * kCells][4];
+    __shared__ __align__(8) uint16_t s_grad[kCells * kCells][4];
     __shared__ int16_t  s_coef[64][12];
     __shared__ int16_t  s_clip[64][12];
     __shared__ uint8_t  s_cls[64];
@@ -160,18 +160,23 @@ __global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
     __syncthreads();
 
     // ---- class / transpose per 4x4 block, then its 12 coefficients and clips (alf_get_idx, recon_coeff_and_clip)
-    if (t < 64) {
-        const int bx = t & 7, by = t >> 3;
+    {                                                    // four threads per block, one per column of gradient cells
+        const int blk = t >> 2, j = t & 3;
+        const int bx = blk & 7, by = blk >> 3;
         const int yb = ty_ctb + by * 4;
         int start = 0, end = 4, ac = 2;
         if (yb + 4 == vb) { end = 3; ac = 3; }
         else if (yb == vb) { start = 1; ac = 3; }
         int sum[4] = { 0, 0, 0, 0 };
-        for (int i = start; i < end; i++)
-            for (int j = 0; j < 4; j++) {
-                const uint16_t *c = s_grad[(by * 2 + i) * kCells + bx * 2 + j];
-                sum[0] += c[0]; sum[1] += c[1]; sum[2] += c[2]; sum[3] += c[3];
-            }
+        for (int i = start; i < end; i++) {
+            const uint2 c = *reinterpret_cast<const uint2 *>(s_grad[(by * 2 + i) * kCells + bx * 2 + j]);
+            sum[0] += c.x & 0xffff; sum[1] += c.x >> 16; sum[2] += c.y & 0xffff; sum[3] += c.y >> 16;
+        }
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            sum[k] += __shfl_xor_sync(0xffffffffu, sum[k], 1);
+            sum[k] += __shfl_xor_sync(0xffffffffu, sum[k], 2);
+        }
         const int dir_hv = sum[0] <= sum[1];
         const int hv1 = max(sum[0], sum[1]), hv0 = min(sum[0], sum[1]);
         const int dir_d = sum[2] <= sum[3];
@@ -184,7 +189,8 @@ __global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
             cls += ((dir1 << 1) + 2) * 5;
         else if (hvd1 > 2 * hvd0)
             cls += ((dir1 << 1) + 1) * 5;
-        s_cls[t] = (uint8_t)(cls | ((dir_d * 2 + dir_hv) << 5));
+        if (j == 0)
+            s_cls[blk] = (uint8_t)(cls | ((dir_d * 2 + dir_hv) << 5));
     }
     __syncthreads();
     // the 64 x 12 coefficient / clip fetches (global tables) spread over the whole CTA instead of 12 in a row on 64 threads
