@@ -227,13 +227,31 @@ __global__ void intra_mark_kernel(IntraArgs a)
     for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {       // sentinel over everything the record will write
         uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
         uint16_t *sh = keep ? a.shadow[c] + (size_t)b.y0 * a.shadow_stride[c] + b.x0 : nullptr;
-        const int per_row = w >> 2, lpr = 31 - __clz(per_row);
-        for (int i = lane; i < per_row * h; i += kMarkLanes) {
-            const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
-            uint2 *d = reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x);
-            if (keep)
-                *reinterpret_cast<uint2 *>(sh + (size_t)y * a.shadow_stride[c] + x) = *d;
-            *d = make_uint2(0xffffffffu, 0xffffffffu);
+        const int per_row = w >> 2, lpr = 31 - __clz(per_row), total = per_row * h;
+        // four pieces per thread and round: the loads of a copied block are in flight together (a 64x64 CIIP block walked
+        // piece by piece was the tail of the kernel)
+        for (int i0 = lane; i0 < total; i0 += 4 * kMarkLanes) {
+            uint2 v[4];
+            uint2 *d[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int i = min(i0 + k * kMarkLanes, total - 1);
+                const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
+                d[k] = reinterpret_cast<uint2 *>(dst + (size_t)y * a.pic.stride[c] + x);
+                if (keep)
+                    v[k] = *d[k];
+            }
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                const int i = i0 + k * kMarkLanes;
+                if (i >= total)
+                    break;
+                if (keep) {
+                    const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
+                    *reinterpret_cast<uint2 *>(sh + (size_t)y * a.shadow_stride[c] + x) = v[k];
+                }
+                *d[k] = make_uint2(0xffffffffu, 0xffffffffu);
+            }
         }
     }
 }
