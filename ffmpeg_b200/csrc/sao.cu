@@ -97,26 +97,23 @@ __global__ void __launch_bounds__(256) sao_kernel(const SaoArgs a)
 // straight-line code below.  Needs 16-byte aligned planes and strides.
 template <int EO>
 __device__ __forceinline__ void sao_edge8(uint32_t (&out)[4], const uint16_t *src, int stride, int x, int y,
-                                          const int16_t *ov, int bd)
+                                          const int16_t *ov, int bd, const uint4 &vc, const uint4 &vu, const uint4 &vd)
 {
-    // neighbour a = (x + AX, y + AY), b = (x - AX, y - AY)
+    // neighbour a = (x + AX, y + AY), b = (x - AX, y - AY).  The three rows (vc: y, vu: y - 1, vd: y + 1) were fetched
+    // before the CTB's parameters were known, so that both round trips overlap; only the two samples beside the
+    // vectors are read here, and those sit in lines the neighbouring threads have just asked for.
     constexpr int AX = EO == 1 ? 0 : (EO == 3 ? 1 : -1), AY = EO == 0 ? 0 : -1;
     const uint16_t *rc = src + (size_t)y * stride + x;
     const uint16_t *ra = rc + AY * stride, *rb = rc - AY * stride;
     uint16_t c[8], a[8], b[8];
-    *reinterpret_cast<uint4 *>(c) = *reinterpret_cast<const uint4 *>(rc);
+    *reinterpret_cast<uint4 *>(c) = vc;
     if (AX == 0) {
-        *reinterpret_cast<uint4 *>(a) = *reinterpret_cast<const uint4 *>(ra);
-        *reinterpret_cast<uint4 *>(b) = *reinterpret_cast<const uint4 *>(rb);
+        *reinterpret_cast<uint4 *>(a) = vu;
+        *reinterpret_cast<uint4 *>(b) = vd;
     } else {
         uint16_t ta[8], tb[8];
-        if (AY == 0) {
-#pragma unroll
-            for (int j = 0; j < 8; j++) { ta[j] = c[j]; tb[j] = c[j]; }
-        } else {
-            *reinterpret_cast<uint4 *>(ta) = *reinterpret_cast<const uint4 *>(ra);
-            *reinterpret_cast<uint4 *>(tb) = *reinterpret_cast<const uint4 *>(rb);
-        }
+        *reinterpret_cast<uint4 *>(ta) = AY == 0 ? vc : vu;
+        *reinterpret_cast<uint4 *>(tb) = AY == 0 ? vc : vd;
         // shift by one sample: a[j] = rowA[j + AX], b[j] = rowB[j - AX]
         const uint16_t ea = AX < 0 ? ra[-1] : ra[8], eb = AX < 0 ? rb[8] : rb[-1];
 #pragma unroll
@@ -155,12 +152,20 @@ __global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
     const int y = blockIdx.y;
     if (x >= w || y >= h)
         return;
+    const uint16_t *src = a.src.p[c];
+    const int stride = a.src.stride[c];
+    // the sample rows first: they do not depend on the CTB's parameters, whose fetch then overlaps them (rows y - 1 and
+    // y + 1 are only used by the edge classes; clamped so that the speculative reads stay inside the plane)
+    uint4 vc, vu, vd;
+    if (x + 8 <= w) {
+        vc = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
+        vu = *reinterpret_cast<const uint4 *>(src + (size_t)max(y - 1, 0) * stride + x);
+        vd = *reinterpret_cast<const uint4 *>(src + (size_t)min(y + 1, h - 1) * stride + x);
+    }
     const int l2 = a.ctb_log2 - (c ? 1 : 0);
     const int cx = x >> l2, cy = y >> l2;
     const VVCB200SaoCtb *pp = a.ctbs + cy * a.ctb_width + cx;
     const int type = pp->type_idx[c];
-    const uint16_t *src = a.src.p[c];
-    const int stride = a.src.stride[c];
     uint16_t *d = a.dst.p[c] + (size_t)y * a.dst.stride[c] + x;
     const int cx0 = cx << l2, cy0 = cy << l2;
     const int cw = min(1 << l2, w - cx0), ch = min(1 << l2, h - cy0);
@@ -179,13 +184,13 @@ __global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
     }
     uint32_t out[4];
     if (type == VVCB200_SAO_OFF) {
-        *reinterpret_cast<uint4 *>(d) = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
+        *reinterpret_cast<uint4 *>(d) = vc;
         return;
     }
     const int16_t *ov = pp->offset_val[c];
     if (type == VVCB200_SAO_BAND) {
         uint16_t s[8];
-        *reinterpret_cast<uint4 *>(s) = *reinterpret_cast<const uint4 *>(src + (size_t)y * stride + x);
+        *reinterpret_cast<uint4 *>(s) = vc;
         const int pos = pp->band_position[c], sh = a.bd - 5, pmax = (1 << a.bd) - 1;
         // offsets of the four bands as bytes 0..3, byte 4 = 0 for every other band; one PRMT selects and sign-extends
         const uint32_t lo = (uint32_t)(ov[1] & 0xff) | ((uint32_t)(ov[2] & 0xff) << 8) | ((uint32_t)(ov[3] & 0xff) << 16) |
@@ -203,10 +208,10 @@ __global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
             out[j] = (uint32_t)r[2 * j] | ((uint32_t)r[2 * j + 1] << 16);
     } else {
         switch (pp->eo_class[c]) {
-        case 0:  sao_edge8<0>(out, src, stride, x, y, ov, a.bd); break;
-        case 1:  sao_edge8<1>(out, src, stride, x, y, ov, a.bd); break;
-        case 2:  sao_edge8<2>(out, src, stride, x, y, ov, a.bd); break;
-        default: sao_edge8<3>(out, src, stride, x, y, ov, a.bd); break;
+        case 0:  sao_edge8<0>(out, src, stride, x, y, ov, a.bd, vc, vu, vd); break;
+        case 1:  sao_edge8<1>(out, src, stride, x, y, ov, a.bd, vc, vu, vd); break;
+        case 2:  sao_edge8<2>(out, src, stride, x, y, ov, a.bd, vc, vu, vd); break;
+        default: sao_edge8<3>(out, src, stride, x, y, ov, a.bd, vc, vu, vd); break;
         }
     }
     *reinterpret_cast<uint4 *>(d) = make_uint4(out[0], out[1], out[2], out[3]);
