@@ -78,7 +78,13 @@ __device__ __forceinline__ int alf_clip2(int curr, int v0, int v1, int c)
     return clip3(v0 - curr, -c, c) + clip3(v1 - curr, -c, c);
 }
 
-__global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
+#ifndef VVC_ALF_LUMA_MIN_BLOCKS
+#define VVC_ALF_LUMA_MIN_BLOCKS 4
+#endif
+#ifndef VVC_ALF_CHROMA_MIN_BLOCKS
+#define VVC_ALF_CHROMA_MIN_BLOCKS 1   // (6 or 8 blocks, i.e. 40 / 32 registers, measured 2 % slower on the stage)
+#endif
+__global__ void __launch_bounds__(256, VVC_ALF_LUMA_MIN_BLOCKS) alf_luma_kernel(const AlfArgs a)
 {
     __shared__ __align__(16) uint16_t s_pix[kPad * kPadStr];
     __shared__ int s_wide;                               // some coefficient of the tile does not fit int8 (never in a conforming stream)
@@ -306,7 +312,7 @@ __global__ void __launch_bounds__(256, 4) alf_luma_kernel(const AlfArgs a)
 }
 
 // chroma ALF (5x5) + CC-ALF; grid.z selects Cb / Cr
-__global__ void __launch_bounds__(256) alf_chroma_kernel(const AlfArgs a)
+__global__ void __launch_bounds__(256, VVC_ALF_CHROMA_MIN_BLOCKS) alf_chroma_kernel(const AlfArgs a)
 {
     __shared__ uint16_t s_pix[(kTile + 4) * (kTile + 4)];
     const int T = min(kTile, 1 << (a.ctb_log2 - 1));      // a tile never straddles a chroma CTB

@@ -144,7 +144,10 @@ __device__ __forceinline__ void sao_edge8(uint32_t (&out)[4], const uint16_t *sr
         out[j] = (uint32_t)r[2 * j] | ((uint32_t)r[2 * j + 1] << 16);
 }
 
-__global__ void __launch_bounds__(256) sao_kernel_v8(const SaoArgs a)
+#ifndef VVC_SAO_MIN_BLOCKS
+#define VVC_SAO_MIN_BLOCKS 1
+#endif
+__global__ void __launch_bounds__(128, VVC_SAO_MIN_BLOCKS) sao_kernel_v8(const SaoArgs a)
 {
     const int c = blockIdx.z;
     const int w = a.src.w[c], h = a.src.h[c];
