@@ -82,7 +82,7 @@ __device__ __forceinline__ int alf_clip2(int curr, int v0, int v1, int c)
 #define VVC_ALF_LUMA_MIN_BLOCKS 4
 #endif
 #ifndef VVC_ALF_CHROMA_MIN_BLOCKS
-#define VVC_ALF_CHROMA_MIN_BLOCKS 1   // (6 or 8 blocks, i.e. 40 / 32 registers, measured 2 % slower on the stage)
+#define VVC_ALF_CHROMA_MIN_BLOCKS 5   // 48 registers (6 or 8 blocks, i.e. 40 / 32 registers, measured 2 % slower on the stage; 1 block, 80 registers, 4 %)
 #endif
 __global__ void __launch_bounds__(256, VVC_ALF_LUMA_MIN_BLOCKS) alf_luma_kernel(const AlfArgs a)
 {
