@@ -610,7 +610,10 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
     }
 }
 
-__global__ void __launch_bounds__(kInterWarps * 32)
+#ifndef VVC_INTER_MIN_BLOCKS
+#define VVC_INTER_MIN_BLOCKS 4        // 64 registers.  Measured: 5 / 6 blocks (48 / 40 registers) spill and lose 8 / 12 % of the
+#endif                                // picture; 3 blocks (80 registers) gain under 1 %
+__global__ void __launch_bounds__(kInterWarps * 32, VVC_INTER_MIN_BLOCKS)
 inter_kernel(const InterArgs a, const VVCB200InterParams p)
 {
     __shared__ __align__(16) uint16_t s_buf[kInterWarps][kBufElems];
