@@ -1,0 +1,37 @@
+#!/usr/bin/env python
+"""Development probe: Level-B throughput of the bench picture with and without the picture download (what the copies
+cost on top of the kernels)."""
+import os
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+from ffmpeg_b200 import lib  # noqa: E402
+from ffmpeg_b200 import hostutil as pipeline  # noqa: E402
+
+
+def main():
+    width, height = 3840, 2160
+    pic = bench.make_picture(2026, width, height, 0.1)
+    for slots in (4, 6):
+        ctx = lib.Context(0, width, height, dpb_size=2 + slots, validate=1)
+        ep = pipeline.EnginePicture(ctx, pic)
+        ep.n_slots = min(slots, 4)
+        ep.upload_refs()
+        for download in (True, False):
+            for _ in range(4):
+                ep.run(download=download)
+            ctx.sync()
+            t0 = time.perf_counter()
+            for _ in range(100):
+                ep.run(download=download)
+            ctx.sync()
+            dt = time.perf_counter() - t0
+            print("dpb slots %d, download %s: %.4f ms per picture, %.1f frames/s" % (slots, download, 10 * dt, 100 / dt))
+        ctx.close()
+
+
+if __name__ == "__main__":
+    main()
