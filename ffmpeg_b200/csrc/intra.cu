@@ -538,7 +538,7 @@ struct Store {                    // what happens to a predicted sample on its w
 // blocking = false: one look at the neighbours; returns false, having written nothing, when they are not all there.
 // arena_held: set when the record took the CTA's arena (the caller releases it once the record has been written).
 __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VVCB200IntraBlock &b, WarpScratch &ws, CtaArena &ar,
-                               bool &arena_held, int lane, bool has_marks, bool blocking, int skip_wait = 0)
+                               bool &arena_held, int lane, bool has_marks, bool scaling, bool blocking, int skip_wait = 0)
 {
     const long long p0 = PROF_T();
     const int c = b.c_idx, w = b.w, h = b.h, mode = b.mode, ref_idx = b.ref_idx, bd = a.bd;
@@ -576,8 +576,8 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     const bool early = blocking && !big;
     if (early)
         stage_inputs();
-    int lscale;
-    if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
+    int lscale = 0;
+    if (scaling && !vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
         return false;
 
     if (add_only) {                                                       // the prediction is there already
@@ -915,7 +915,7 @@ __device__ __forceinline__ int checked_load(const uint16_t *p, bool &bad)
 
 // ---- CCLM (vvc_intra_template.c:29-375): one record predicts Cb and Cr --------------------------------------------
 __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, WarpScratch &ws, CtaArena &ar, bool &arena_held,
-                            int lane, bool has_marks, bool blocking)
+                            int lane, bool has_marks, bool scaling, bool blocking)
 {
     const int bd = a.bd, w = b.w, h = b.h, x = b.x0, y = b.y0, x0 = x * 2, y0 = y * 2, mode = b.mode;
     const bool avail_t = b.avail_top > 0, avail_l = b.avail_left > 0;
@@ -954,8 +954,8 @@ __device__ bool cclm_record(const IntraArgs &a, const VVCB200IntraBlock &b, Warp
         if (!spans_ready(a, sp, cclm_deps(b, sp), lane, blocking))
             return false;
     }
-    int lscale;
-    if (!vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
+    int lscale = 0;
+    if (scaling && !vpdu_chroma_scale(a, b, has_marks, lane, blocking, lscale))
         return false;
     __syncwarp();
     auto emit = [&](int c, int i, int j, int v) {
@@ -1171,6 +1171,10 @@ __device__ bool isp_external_ready(const IntraArgs &a, const VVCB200IntraBlock &
     return !__any_sync(kFull, bad);
 }
 
+// kMarks: some blocks are rewritten in place and go by marks (no shadow picture).  The other instantiation carries none
+// of that code, which matters for a kernel whose steps wait on instruction fetch.
+// kScale: the picture uses luma-dependent chroma residual scaling (VVCB200IntraParams.lmcs_chroma_scale).
+template <bool kMarks, bool kScale>
 __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArgs a)
 {
     extern __shared__ __align__(16) uint8_t s_dyn[];
@@ -1191,7 +1195,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
     if (threadIdx.x < 4)
         tb.mip_off[threadIdx.x] = VVC_MIP_OFF[threadIdx.x];
     __syncthreads();
-    const bool has_marks = a.ticket[1] != 0;                              // written by the pre-pass
+    const bool has_marks = kMarks && a.ticket[1] != 0;                    // written by the pre-pass
 
     // Each warp holds up to kSlots records drawn in ticket order.  With one slot it waits for that record's neighbours
     // (tight polling: the lowest latency along a dependency chain, which is what bounds the kernel).  With more slots it
@@ -1231,7 +1235,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
             const long long pt1 = PROF_T();
             bool done, arena_held = false;
             if (b.mode >= 81) {
-                done = cclm_record(a, b, ws, ar, arena_held, lane, has_marks, kWait);
+                done = cclm_record(a, b, ws, ar, arena_held, lane, has_marks, kScale, kWait);
             } else {
                 // ISP: the sub-partitions of the coding block one after the other, each predicted from its
                 // reconstructed predecessor (vvc_intra.c:217-226, 244-252); w x h is the prediction unit.  Everything the
@@ -1244,7 +1248,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
                 for (int q = 0; done && q < n_parts; q++) {
                     VVCB200IntraBlock sub = b;
                     const int skip = isp ? isp_part(b, q, sub) : 0;
-                    done = predict_record(a, tb, sub, ws, ar, arena_held, lane, has_marks, kWait || isp, skip);
+                    done = predict_record(a, tb, sub, ws, ar, arena_held, lane, has_marks, kScale, kWait || isp, skip);
                     __syncwarp();
                     if (arena_held && q + 1 < n_parts) {                  // the next partition may wait for this one's stores
                         arena_release(ar, lane);
@@ -1526,10 +1530,21 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     int dev = 0;
     VVC_CUDA(cudaGetDevice(&dev));
     if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        VVC_CUDA(cudaFuncSetAttribute(intra_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VVC_CUDA(cudaFuncSetAttribute(intra_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VVC_CUDA(cudaFuncSetAttribute(intra_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VVC_CUDA(cudaFuncSetAttribute(intra_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        VVC_CUDA(cudaFuncSetAttribute(intra_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set[dev] = true;
     }
-    intra_kernel<<<ctas, kWarps * 32, smem, s>>>(a);
+    const bool marks = !d_shadow, scale = params->lmcs_chroma_scale != 0;
+    if (marks && scale)
+        intra_kernel<true, true><<<ctas, kWarps * 32, smem, s>>>(a);
+    else if (marks)
+        intra_kernel<true, false><<<ctas, kWarps * 32, smem, s>>>(a);
+    else if (scale)
+        intra_kernel<false, true><<<ctas, kWarps * 32, smem, s>>>(a);
+    else
+        intra_kernel<false, false><<<ctas, kWarps * 32, smem, s>>>(a);
     VVC_LAUNCH_CHECK();
     return 0;
 }

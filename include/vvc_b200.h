@@ -369,7 +369,8 @@ typedef struct VVCB200IntraParams {
     int32_t ctb_log2_size;
     int32_t chroma_vertical_collocated;   /* sps_chroma_vertical_collocated_flag (CCLM down-sampling filter)              */
     int32_t lmcs_chroma_scale;            /* sh_lmcs_used_flag && ph_chroma_residual_scale_flag: chroma records carry
-                                             VVCB200_IB_LMCS_SCALE (informative for the device, which goes by the records) */
+                                             VVCB200_IB_LMCS_SCALE.  Must be set for the flag to be honoured: the launch
+                                             picks a kernel without the scaling code when it is 0 */
     /* LMCS model for records flagged VVCB200_IB_LMCS_SCALE (VVCLMCS, vvc_ps.h:192-202) */
     uint16_t lmcs_pivot[17];
     uint16_t lmcs_chroma_scale_coeff[16];
