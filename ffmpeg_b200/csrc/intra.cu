@@ -122,11 +122,14 @@ __device__ __forceinline__ void fence_gpu() { asm volatile("fence.acq_rel.gpu;" 
 
 // w samples per row (multiple of 4), h rows, global -> shared (compact rows of w), asynchronously.  8-byte pieces: block
 // origins are only guaranteed to be multiples of 4 samples (ternary splits).
-__device__ __forceinline__ void stage_block_async(void *sdst, const void *g, int gstride /* samples */, int w, int h, int lane)
+// One copy of this in the kernel, not one per call site (they made up 30 % of the code, and the kernel is bound by
+// instruction fetch): a call costs a few cycles, and the copies are asynchronous anyway.
+__device__ __noinline__ void stage_block_async(void *sdst, const void *g, int gstride /* samples */, int w, int h, int lane)
 {
     const uint32_t sbase = (uint32_t)__cvta_generic_to_shared(sdst);
     const uint16_t *gp = static_cast<const uint16_t *>(g);
     const int per_row = w >> 2, n = per_row * h, lpr = 31 - __clz(per_row);   // w is a power of two
+#pragma unroll 1
     for (int i = lane; i < n; i += 32) {
         const int y = i >> lpr, x = (i & (per_row - 1)) << 2;
         asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sbase + (y * w + x) * 2), "l"(gp + (size_t)y * gstride + x) : "memory");
