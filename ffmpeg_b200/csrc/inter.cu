@@ -40,6 +40,7 @@ struct InterArgs {
     int32_t *refined_mv;                         // optional: the vectors actually used (DMVR feedback), n x 2 x 2
     const VVCB200ProfTable *prof;                // optional: PROF offset tables of the affine coding units
     int n, n16, n8;                              // blocks of width 16 come first, then width 8, then width 4
+    int first, last;                             // the blocks of this launch's width class
     int bd, to_tmp14;
 };
 
@@ -468,8 +469,9 @@ __device__ __forceinline__ void prof_block(const InterArgs &a, const VVCB200Pred
     __syncwarp();
 }
 
-// One component of one block by one lane group (both lists + weighting + store).
-template <int TAPS>
+// One component of one block by one lane group (both lists + weighting + store).  WC: the block's width in this
+// component, fixed by the width class of the launch.
+template <int TAPS, int WC>
 __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
                                                   bool active, int c, int li, int gs, uint16_t *win, int ws,
                                                   int16_t *tmp, int ts, const int (&mv)[2][2], bool dmvr, bool bdof,
@@ -477,7 +479,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
 {
     const int bd = a.bd;
     const int hs = c ? 1 : 0;
-    const int w = max(b.w >> hs, 1), h = max(b.h >> hs, 1);
+    const int w = WC, h = max(b.h >> hs, 1);
     const int x0 = b.x0 >> hs, y0 = b.y0 >> hs;
     const int log2w = 31 - __clz(w);
     const bool gpm = b.flags & VVCB200_PB_GPM;
@@ -613,6 +615,10 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
 #ifndef VVC_INTER_MIN_BLOCKS
 #define VVC_INTER_MIN_BLOCKS 4        // 64 registers.  Measured: 5 / 6 blocks (48 / 40 registers) spill and lose 8 / 12 % of the
 #endif                                // picture; 3 blocks (80 registers) gain under 1 %
+// One launch per width class (kCls 0 / 1 / 2: blocks of width 16 / 8 / 4, a.first .. a.last): widths, lane groups and
+// staging strides are compile-time constants, the width-4 kernel carries no DMVR / BDOF code (they need 8x8) and the
+// others no PROF code (4x4 sub-blocks only) — the kernel is bound by instruction issue and fetch.
+template <int kCls>
 __global__ void __launch_bounds__(kInterWarps * 32, VVC_INTER_MIN_BLOCKS)
 inter_kernel(const InterArgs a, const VVCB200InterParams p)
 {
@@ -622,19 +628,11 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x * kInterWarps + warp;
 
-    // which width class and which blocks does this warp own?
-    const int n4 = a.n - a.n16 - a.n8;
-    const int warps8 = (a.n8 + 1) >> 1, warps4 = (n4 + 3) >> 2;
-    int cls, first, last;                               // class: 0 -> w 16, 1 -> w 8, 2 -> w 4
-    if (wi < a.n16) {
-        cls = 0; first = wi; last = a.n16;
-    } else if (wi < a.n16 + warps8) {
-        cls = 1; first = a.n16 + (wi - a.n16) * 2; last = a.n16 + a.n8;
-    } else if (wi < a.n16 + warps8 + warps4) {
-        cls = 2; first = a.n16 + a.n8 + (wi - a.n16 - warps8) * 4; last = a.n;
-    } else {
+    // the blocks this warp owns: one of width 16, two of width 8 or four of width 4
+    constexpr int cls = kCls;
+    const int first = a.first + (wi << kCls), last = a.last;
+    if (first >= last)
         return;
-    }
     uint16_t *win = s_buf[warp];
     int16_t *tmp = reinterpret_cast<int16_t *>(s_buf[warp]) + kWinElems;
 
@@ -645,9 +643,9 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const VVCB200PredBlock b = a.blocks[active ? bi : first];
         const bool luma = active && !(b.flags & VVCB200_PB_CHROMA_ONLY);
         int mv[2][2] = { { b.mv[0][0], b.mv[0][1] }, { b.mv[1][0], b.mv[1][1] } };
-        const bool dmvr = (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
-        bool bdof = luma && (b.flags & VVCB200_PB_BDOF) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
-        if (__any_sync(0xffffffffu, active && dmvr)) {
+        const bool dmvr = kCls < 2 && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
+        bool bdof = kCls < 2 && luma && (b.flags & VVCB200_PB_BDOF) && b.pred_flag == 3 && b.h >= 8;
+        if (kCls < 2 && __any_sync(0xffffffffu, active && dmvr)) {
             // each group's scratch: 2 predictions of (w+4) x 20 samples + 25 SADs
             const int region = cls == 0 ? kBufElems : kBufElems / 2;
             if (!dmvr_refine(a, p, b, active && dmvr, li, gs, reinterpret_cast<int16_t *>(s_buf[warp]) + g * region, mv))
@@ -665,7 +663,7 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const int ws = (16 >> cls) + 10;                // 26 / 18 / 14 samples: an odd number of words
         const int win_sz = 23 * ws, tmp_sz = (16 >> cls) * 26;
         const int bdof_region = cls == 0 ? 0 : kBufElems / 2;
-        predict_component<8>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
+        predict_component<8, (16 >> kCls)>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
                              reinterpret_cast<int16_t *>(s_buf[warp]) + g * bdof_region, s_vxy[warp][g & 1]);
     }
     __syncwarp();
@@ -678,11 +676,11 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
 #pragma unroll
         for (int k = 0; k < 4; k++)
             mv[k >> 1][k & 1] = s_mv[warp][(g >> 1) & 3][k];
-        const bool dmvr = active && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.w >= 8 && b.h >= 8;
+        const bool dmvr = kCls < 2 && active && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
         const int wc = 8 >> cls;
         const int ws = wc + 6;                          // 14 / 10 / 8 samples
         const int win_sz = 11 * ws + 8, tmp_sz = wc * 14;
-        predict_component<4>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
+        predict_component<4, (8 >> kCls)>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
                              win + g * win_sz, ws, tmp + g * tmp_sz, 14, mv, dmvr, false, nullptr, nullptr);
     }
 }
@@ -733,9 +731,22 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     a.n16 = params->n_w16;
     a.n8 = params->n_w8;
     a.bd = params->bit_depth;
-    const int n4 = n - a.n16 - a.n8;
-    const int warps = a.n16 + ((a.n8 + 1) >> 1) + ((n4 + 3) >> 2);
-    inter_kernel<<<(warps + kInterWarps - 1) / kInterWarps, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
-    VVC_LAUNCH_CHECK();
+    const int bound[4] = { 0, a.n16, a.n16 + a.n8, n };
+    for (int cls = 0; cls < 3; cls++) {
+        a.first = bound[cls];
+        a.last = bound[cls + 1];
+        const int count = a.last - a.first;
+        if (!count)
+            continue;
+        const int warps = (count + (1 << cls) - 1) >> cls;
+        const int grid = (warps + kInterWarps - 1) / kInterWarps;
+        if (cls == 0)
+            inter_kernel<0><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+        else if (cls == 1)
+            inter_kernel<1><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+        else
+            inter_kernel<2><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+        VVC_LAUNCH_CHECK();
+    }
     return 0;
 }
