@@ -685,6 +685,34 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
     }
 }
 
+// The three width classes are independent grids; on one stream each would wait for the tail of the one before.  Two
+// helper streams per host thread and device run them side by side: forked from and joined back into the caller's stream
+// with events, so the call keeps its stream semantics.
+struct ForkStreams {
+    cudaStream_t side[2] = { nullptr, nullptr };
+    cudaEvent_t fork = nullptr, join[2] = { nullptr, nullptr };
+    bool ok = false;
+};
+
+ForkStreams *fork_streams()
+{
+    static thread_local ForkStreams pool[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return nullptr;
+    ForkStreams &f = pool[dev];
+    if (!f.ok) {
+        bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < 2 && good; i++)
+            good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
+                   cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!good)
+            return nullptr;                                               // the caller falls back to one stream
+        f.ok = true;
+    }
+    return &f;
+}
+
 }  // namespace vvcb200
 
 using namespace vvcb200;
@@ -732,21 +760,39 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     a.n8 = params->n_w8;
     a.bd = params->bit_depth;
     const int bound[4] = { 0, a.n16, a.n16 + a.n8, n };
+    const cudaStream_t main_stream = (cudaStream_t)stream;
+    int classes = 0;
+    for (int cls = 0; cls < 3; cls++)
+        classes += bound[cls + 1] > bound[cls];
+    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;
+    if (f)
+        VVC_CUDA(cudaEventRecord(f->fork, main_stream));
+    int used = 0;                                                         // side streams in use
     for (int cls = 0; cls < 3; cls++) {
         a.first = bound[cls];
         a.last = bound[cls + 1];
         const int count = a.last - a.first;
         if (!count)
             continue;
+        cudaStream_t st = main_stream;                                    // the first class present stays on the caller's stream
+        if (f && classes > 1 && used < 2 && cls > 0 && bound[cls] > 0) {
+            st = f->side[used];
+            VVC_CUDA(cudaStreamWaitEvent(st, f->fork, 0));
+        }
         const int warps = (count + (1 << cls) - 1) >> cls;
         const int grid = (warps + kInterWarps - 1) / kInterWarps;
         if (cls == 0)
-            inter_kernel<0><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+            inter_kernel<0><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         else if (cls == 1)
-            inter_kernel<1><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+            inter_kernel<1><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         else
-            inter_kernel<2><<<grid, kInterWarps * 32, 0, (cudaStream_t)stream>>>(a, *params);
+            inter_kernel<2><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         VVC_LAUNCH_CHECK();
+        if (st != main_stream) {
+            VVC_CUDA(cudaEventRecord(f->join[used], st));
+            VVC_CUDA(cudaStreamWaitEvent(main_stream, f->join[used], 0));
+            used++;
+        }
     }
     return 0;
 }
