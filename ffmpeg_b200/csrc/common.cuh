@@ -30,6 +30,17 @@ void count_launch(int n = 1);
 
 int sm_count();   // SMs of the current device (cached per device)
 
+// Helper streams for entry points that launch several independent grids: on one stream each grid would wait for the
+// tail of the one before.  The grids are forked from the caller's stream and joined back into it with events, so the
+// call keeps its stream semantics.  One set per host thread and device; nullptr when the streams cannot be created
+// (the caller then stays on its one stream).
+struct ForkStreams {
+    cudaStream_t side[4] = { nullptr, nullptr, nullptr, nullptr };
+    cudaEvent_t fork = nullptr, join[4] = { nullptr, nullptr, nullptr, nullptr };
+    bool ok = false;
+};
+ForkStreams *fork_streams();
+
 // ---- device side -------------------------------------------------------------------------------
 __device__ __forceinline__ int clip3(int v, int lo, int hi) { return min(max(v, lo), hi); }
 __device__ __forceinline__ int clip_intp2(int v, int p) { return min(max(v, -(1 << p)), (1 << p) - 1); }

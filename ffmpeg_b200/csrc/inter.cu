@@ -685,34 +685,6 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
     }
 }
 
-// The three width classes are independent grids; on one stream each would wait for the tail of the one before.  Two
-// helper streams per host thread and device run them side by side: forked from and joined back into the caller's stream
-// with events, so the call keeps its stream semantics.
-struct ForkStreams {
-    cudaStream_t side[2] = { nullptr, nullptr };
-    cudaEvent_t fork = nullptr, join[2] = { nullptr, nullptr };
-    bool ok = false;
-};
-
-ForkStreams *fork_streams()
-{
-    static thread_local ForkStreams pool[64];
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
-        return nullptr;
-    ForkStreams &f = pool[dev];
-    if (!f.ok) {
-        bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
-        for (int i = 0; i < 2 && good; i++)
-            good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
-                   cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
-        if (!good)
-            return nullptr;                                               // the caller falls back to one stream
-        f.ok = true;
-    }
-    return &f;
-}
-
 }  // namespace vvcb200
 
 using namespace vvcb200;
@@ -764,7 +736,7 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     int classes = 0;
     for (int cls = 0; cls < 3; cls++)
         classes += bound[cls + 1] > bound[cls];
-    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;
+    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;         // the classes are independent grids: side by side
     if (f)
         VVC_CUDA(cudaEventRecord(f->fork, main_stream));
     int used = 0;                                                         // side streams in use

@@ -40,6 +40,25 @@ int sm_count()
     return cached[dev];
 }
 
+ForkStreams *fork_streams()
+{
+    static thread_local ForkStreams pool[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+        return nullptr;
+    ForkStreams &f = pool[dev];
+    if (!f.ok) {
+        bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
+        for (int i = 0; i < 4 && good; i++)
+            good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
+                   cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
+        if (!good)
+            return nullptr;
+        f.ok = true;
+    }
+    return &f;
+}
+
 }  // namespace vvcb200
 
 extern "C" {
