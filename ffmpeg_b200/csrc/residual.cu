@@ -40,6 +40,7 @@ struct ResidualArgs {
     const VVCB200TransformBlock *tbs;
     int n;
     int n_class[4];                          // blocks per lane-group class (32/16/8/4 lanes per block); the rest is generic
+    int first, last;                         // the blocks of this launch's class
     int bd, range, c_sign;
     int to_residual;
 };
@@ -577,6 +578,11 @@ __host__ __device__ inline int residual_class(const VVCB200TransformBlock &d)
     return m >= 5 ? 0 : m == 4 ? 1 : m == 3 ? 2 : 3;
 }
 
+// One launch per class (kCls 0 .. 3: fast blocks of 32 / 16 / 8 / 4 lanes, 4: the generic ones), blocks a.first .. a.last,
+// side by side on forked streams: each kernel carries only its own path — the fast kernels no transform-skip / BDPCM /
+// LFNST code and no passes of sizes their class never meets, the generic one no packed fast passes — which matters for
+// a kernel that spends a quarter of its stall samples on instruction fetch.
+template <int kCls>
 __global__ void __launch_bounds__(kWarpsPerCta * 32, 7)      // 7 CTAs/SM is also the shared-memory limit (32 KB each)
 residual_kernel(const ResidualArgs a, const ScalingLists sl)
 {
@@ -588,38 +594,28 @@ residual_kernel(const ResidualArgs a, const ScalingLists sl)
     load_matrices(smat);
     __syncthreads();
 
-    // Warp -> (class, first block).  Classes come in batch order: 32-, 16-, 8-, 4-lane blocks, then the generic ones;
-    // the heavy 32-lane blocks are scheduled first, the light ones fill the tail.
     const int wi = blockIdx.x * kWarpsPerCta + warp;
-    int cls = 0, first = 0, base_w = 0, base_b = 0;
-    bool found = false;
-#pragma unroll
-    for (int c = 0; c < 4; c++) {
-        const int per_warp = 1 << c, warps = (a.n_class[c] + per_warp - 1) >> c;
-        if (!found && wi < base_w + warps) {
-            found = true;
-            cls = c;
-            first = base_b + ((wi - base_w) << c);
-        }
-        if (!found) {
-            base_w += warps;
-            base_b += a.n_class[c];
-        }
-    }
-    if (found) {
-        const int last = base_b + a.n_class[cls];
-        const int log2lpt = 5 - cls, lpt = 32 >> cls;
+    if (kCls < 4) {
+        constexpr int cls = kCls < 4 ? kCls : 0;
+        const int first = a.first + (wi << cls), last = a.last;
+        if (first >= last)
+            return;
+        constexpr int log2lpt = 5 - cls, lpt = 32 >> cls;
         const int g = lane >> log2lpt, li = lane & (lpt - 1);
         const bool active = first + g < last;
-        const VVCB200TransformBlock d = a.tbs[active ? first + g : first];
+        VVCB200TransformBlock d = a.tbs[active ? first + g : first];
+        // the class bounds the block's larger side (vvcb200_residual_class): say so, and the passes of larger sizes go
+        constexpr int max_log2 = cls == 0 ? 6 : 5 - cls;
+        d.log2_w = min((int)d.log2_w, max_log2);
+        d.log2_h = min((int)d.log2_h, max_log2);
         // per-block staging: transposed input (lpt columns) + middle block (lpt rows; 64 for the 32-lane class)
-        const int in_sz = lpt * kPairStride, region = cls == 0 ? kWarpElems : 2 * in_sz;
+        constexpr int in_sz = lpt * kPairStride, region = cls == 0 ? kWarpElems : 2 * in_sz;
         fast_block(a, sl, d, active, li, lpt, log2lpt, buf + g * region, buf + g * region + in_sz, smat);
-        return;
+    } else {
+        const int t = a.first + wi;
+        if (t < a.last)
+            generic_block(a, sl, a.tbs[t], lane, buf, buf + kInElems, smat);
     }
-    const int t = base_b + (wi - base_w);
-    if (t < a.n)
-        generic_block(a, sl, a.tbs[t], lane, buf, buf + kInElems, smat);
 }
 
 // ---- Level A: itx.itx[...] on int32 blocks in place, add_residual on int32 blocks --------------------
@@ -742,14 +738,50 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
         rest -= a.n_class[c];
         warps += (a.n_class[c] + (1 << c) - 1) >> c;
     }
-    warps += rest;                              // generic blocks: one warp each
     const size_t smem = kMatPad + kWarpsPerCta * kWarpElems * sizeof(int16_t);
-    static bool ready[64];
-    if (int r = opt_in_smem(residual_kernel, smem, ready))
-        return r;
-    const int grid = (warps + kWarpsPerCta - 1) / kWarpsPerCta;
-    residual_kernel<<<grid, kWarpsPerCta * 32, smem, (cudaStream_t)stream>>>(a, sl);
-    VVC_LAUNCH_CHECK();
+    static bool ready[5][64];
+    if (int r = opt_in_smem(residual_kernel<0>, smem, ready[0])) return r;
+    if (int r = opt_in_smem(residual_kernel<1>, smem, ready[1])) return r;
+    if (int r = opt_in_smem(residual_kernel<2>, smem, ready[2])) return r;
+    if (int r = opt_in_smem(residual_kernel<3>, smem, ready[3])) return r;
+    if (int r = opt_in_smem(residual_kernel<4>, smem, ready[4])) return r;
+    const cudaStream_t main_stream = (cudaStream_t)stream;
+    int classes = 0;
+    for (int c = 0; c < 5; c++)
+        classes += (c < 4 ? a.n_class[c] : rest) > 0;
+    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;        // the classes are independent grids: side by side
+    if (f)
+        VVC_CUDA(cudaEventRecord(f->fork, main_stream));
+    int base = 0, used = 0, launched = 0;
+    for (int c = 0; c < 5; c++) {
+        const int count = c < 4 ? a.n_class[c] : rest;
+        a.first = base;
+        a.last = base + count;
+        base += count;
+        if (!count)
+            continue;
+        cudaStream_t st = main_stream;                                    // the first class present stays on the caller's stream
+        if (f && launched > 0 && used < 4) {
+            st = f->side[used];
+            VVC_CUDA(cudaStreamWaitEvent(st, f->fork, 0));
+        }
+        const int cw = c < 4 ? (count + (1 << c) - 1) >> c : count;     // generic blocks: one warp each
+        const int grid = (cw + kWarpsPerCta - 1) / kWarpsPerCta;
+        switch (c) {
+        case 0:  residual_kernel<0><<<grid, kWarpsPerCta * 32, smem, st>>>(a, sl); break;
+        case 1:  residual_kernel<1><<<grid, kWarpsPerCta * 32, smem, st>>>(a, sl); break;
+        case 2:  residual_kernel<2><<<grid, kWarpsPerCta * 32, smem, st>>>(a, sl); break;
+        case 3:  residual_kernel<3><<<grid, kWarpsPerCta * 32, smem, st>>>(a, sl); break;
+        default: residual_kernel<4><<<grid, kWarpsPerCta * 32, smem, st>>>(a, sl); break;
+        }
+        VVC_LAUNCH_CHECK();
+        launched++;
+        if (st != main_stream) {
+            VVC_CUDA(cudaEventRecord(f->join[used], st));
+            VVC_CUDA(cudaStreamWaitEvent(main_stream, f->join[used], 0));
+            used++;
+        }
+    }
     return 0;
 }
 
