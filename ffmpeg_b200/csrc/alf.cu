@@ -451,12 +451,25 @@ extern "C" int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes
         set_error("vvcb200_alf_picture: luma planes must be 8-byte aligned with strides that are multiples of 8 bytes");
         return VVCB200_ERR_ARG;
     }
+    // luma and chroma write different planes of dst and only read src: two independent grids, side by side
+    const cudaStream_t main_stream = (cudaStream_t)stream;
+    ForkStreams *f = fork_streams(main_stream);
+    cudaStream_t side = main_stream;
+    if (f) {
+        VVC_CUDA(cudaEventRecord(f->fork, main_stream));
+        side = f->side[0];
+        VVC_CUDA(cudaStreamWaitEvent(side, f->fork, 0));
+    }
     dim3 gl((src->width[0] + kTile - 1) / kTile, (src->height[0] + kTile - 1) / kTile, 1);
-    alf_luma_kernel<<<gl, 256, 0, (cudaStream_t)stream>>>(a);
+    alf_luma_kernel<<<gl, 256, 0, main_stream>>>(a);
     VVC_LAUNCH_CHECK();
     const int ct = kTile < (1 << (ctb_log2_size - 1)) ? kTile : (1 << (ctb_log2_size - 1));
     dim3 gc((src->width[1] + ct - 1) / ct, (src->height[1] + ct - 1) / ct, 2);
-    alf_chroma_kernel<<<gc, 256, 0, (cudaStream_t)stream>>>(a);
+    alf_chroma_kernel<<<gc, 256, 0, side>>>(a);
     VVC_LAUNCH_CHECK();
+    if (f) {
+        VVC_CUDA(cudaEventRecord(f->join[0], side));
+        VVC_CUDA(cudaStreamWaitEvent(main_stream, f->join[0], 0));
+    }
     return 0;
 }

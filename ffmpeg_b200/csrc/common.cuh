@@ -32,14 +32,14 @@ int sm_count();   // SMs of the current device (cached per device)
 
 // Helper streams for entry points that launch several independent grids: on one stream each grid would wait for the
 // tail of the one before.  The grids are forked from the caller's stream and joined back into it with events, so the
-// call keeps its stream semantics.  One set per host thread and device; nullptr when the streams cannot be created
-// (the caller then stays on its one stream).
+// call keeps its stream semantics.  One set per host thread, device and calling stream (up to 16; streams are never
+// destroyed behind the library's back in the engine); nullptr when none can be had (the caller stays on its one stream).
 struct ForkStreams {
     cudaStream_t side[4] = { nullptr, nullptr, nullptr, nullptr };
     cudaEvent_t fork = nullptr, join[4] = { nullptr, nullptr, nullptr, nullptr };
     bool ok = false;
 };
-ForkStreams *fork_streams();
+ForkStreams *fork_streams(cudaStream_t main_stream);
 
 // ---- device side -------------------------------------------------------------------------------
 __device__ __forceinline__ int clip3(int v, int lo, int hi) { return min(max(v, lo), hi); }

@@ -736,7 +736,7 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     int classes = 0;
     for (int cls = 0; cls < 3; cls++)
         classes += bound[cls + 1] > bound[cls];
-    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;         // the classes are independent grids: side by side
+    ForkStreams *f = classes > 1 ? fork_streams(main_stream) : nullptr;         // the classes are independent grids: side by side
     if (f)
         VVC_CUDA(cudaEventRecord(f->fork, main_stream));
     int used = 0;                                                         // side streams in use

@@ -749,7 +749,7 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
     int classes = 0;
     for (int c = 0; c < 5; c++)
         classes += (c < 4 ? a.n_class[c] : rest) > 0;
-    ForkStreams *f = classes > 1 ? fork_streams() : nullptr;        // the classes are independent grids: side by side
+    ForkStreams *f = classes > 1 ? fork_streams(main_stream) : nullptr;        // the classes are independent grids: side by side
     if (f)
         VVC_CUDA(cudaEventRecord(f->fork, main_stream));
     int base = 0, used = 0, launched = 0;

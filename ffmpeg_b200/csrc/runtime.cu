@@ -40,23 +40,39 @@ int sm_count()
     return cached[dev];
 }
 
-ForkStreams *fork_streams()
+ForkStreams *fork_streams(cudaStream_t main_stream)
 {
-    static thread_local ForkStreams pool[64];
+    // one set per calling stream: helper streams shared between two pictures' streams would order them behind each other
+    struct Entry { int dev; cudaStream_t main; ForkStreams f; };
+    static thread_local Entry pool[16];
+    static thread_local int used = 0;
     int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64)
+    if (cudaGetDevice(&dev) != cudaSuccess)
         return nullptr;
-    ForkStreams &f = pool[dev];
-    if (!f.ok) {
-        bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
-        for (int i = 0; i < 4 && good; i++)
-            good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
-                   cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
-        if (!good)
-            return nullptr;
-        f.ok = true;
+    for (int i = 0; i < used; i++)
+        if (pool[i].dev == dev && pool[i].main == main_stream)
+            return &pool[i].f;
+    if (used == 16) {                               // all sets taken: hand an old one over (its streams serve any caller)
+        static thread_local int next = 0;
+        Entry &e = pool[next++ & 15];
+        e.dev = dev;
+        e.main = main_stream;
+        return &e.f;
     }
-    return &f;
+    Entry &e = pool[used];
+    ForkStreams f;
+    bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int i = 0; i < 4 && good; i++)
+        good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
+               cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
+    if (!good)
+        return nullptr;
+    f.ok = true;
+    e.dev = dev;
+    e.main = main_stream;
+    e.f = f;
+    used++;
+    return &e.f;
 }
 
 }  // namespace vvcb200
