@@ -272,6 +272,12 @@ def deblock_picture(pic, tables, params, stream=None):
     check(load().vvcb200_deblock_picture(C.byref(pic), C.byref(tables), C.byref(params), _stream(stream)))
 
 
+def deblock_lmcs_picture(dst, src, tables, params, inv_lut=None, stream=None):
+    """vvcb200_deblock_lmcs_picture: both deblocking passes (and the inverse LMCS mapping of luma) in one out-of-place pass."""
+    check(load().vvcb200_deblock_lmcs_picture(C.byref(dst), C.byref(src), C.byref(tables), C.byref(params), _ptr(inv_lut),
+                                              _stream(stream)))
+
+
 def sao_picture(dst, src, ctbs, ctb_log2, bit_depth=10, stream=None):
     """vvcb200_sao_picture: dst/src device_planes(); ctbs device tensor of VVCB200SaoCtb records."""
     check(load().vvcb200_sao_picture(C.byref(dst), C.byref(src), _ptr(ctbs), int(ctb_log2), int(bit_depth), _stream(stream)))

@@ -266,6 +266,21 @@ VVCB200_API int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const 
 VVCB200_API int vvcb200_deblock_picture(const VVCB200Planes *pic, const VVCB200DeblockTables *tables /* host struct */,
                                         const VVCB200DeblockParams *params /* host */, void *stream);
 
+/*
+ * The same two stages (ff_vvc_deblock_vertical + ff_vvc_deblock_horizontal, vvc_filter.c:861-1003) as ONE out-of-place
+ * pass, optionally preceded by stage LMCS (ff_vvc_lmcs_filter, vvc_filter.c:1322-1332): dst = deblock(lut(src)).
+ * Every 64x64 tile of a plane is staged once (128-bit loads, luma mapped through `d_inv_lut` on the way in when it is
+ * non-NULL), filtered across its vertical and then its horizontal edges in shared memory, and written once.
+ * What Level B runs.  `dst` and `src` must be distinct pictures of the same geometry, planes 16-byte aligned with strides
+ * that are multiples of 16 bytes.  Requires what the standard guarantees: no transform block crosses a multiple of 64
+ * luma samples (sps_log2_max_luma_transform_size <= 6).  Results are identical to vvcb200_lmcs_picture +
+ * vvcb200_deblock_picture.
+ */
+VVCB200_API int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVCB200Planes *src,
+                                             const VVCB200DeblockTables *tables /* host struct */,
+                                             const VVCB200DeblockParams *params /* host */,
+                                             const uint16_t *d_inv_lut /* 1 << bit_depth entries, or NULL */, void *stream);
+
 /* ------------------------------------------------------------------------------------------------
  * SAO and ALF (stages SAO / ALF, ff_vvc_sao_filter vvc_filter.c:154-298, ff_vvc_alf_filter 1254-1319;
  * sao.band_filter / edge_filter / edge_restore vvcdsp.h:138-145, alf.classify / recon_coeff_and_clip /
