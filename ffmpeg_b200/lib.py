@@ -289,5 +289,11 @@ def alf_picture(dst, src, ctbs, params, ctb_log2, bit_depth=10, stream=None):
                                      _stream(stream)))
 
 
+def sao_alf_picture(dst, src, sao, alf, params, ctb_log2, bit_depth=10, stream=None):
+    """vvcb200_sao_alf_picture: SAO + ALF (+ CC-ALF) in one pass; sao / alf / params device tensors or None."""
+    check(load().vvcb200_sao_alf_picture(C.byref(dst), C.byref(src), _ptr(sao), _ptr(alf), _ptr(params), int(ctb_log2),
+                                         int(bit_depth), _stream(stream)))
+
+
 def lmcs_picture(pic, lut, bit_depth=10, stream=None):
     check(load().vvcb200_lmcs_picture(C.byref(pic), _ptr(lut), int(bit_depth), _stream(stream)))

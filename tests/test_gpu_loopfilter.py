@@ -51,6 +51,48 @@ def gpu_alf(base, lf):
     return util.from_device_planes(dst)
 
 
+def gpu_sao_alf(base, lf, sao=True, alf=True):
+    """The fused pass: vvcb200_sao_alf_picture."""
+    import torch
+    src = util.to_device_planes(base, torch)
+    dst = util.to_device_planes([np.full_like(p, 0x5555) for p in base], torch)
+    sao_d = torch.from_numpy(lf["sao"].view(np.uint8).reshape(-1)).cuda() if sao else None
+    alf_d = torch.from_numpy(lf["alf"].view(np.uint8).reshape(-1)).cuda() if alf else None
+    params = torch.from_numpy(lf["alf_params"].view(np.uint8).reshape(-1)).cuda() if alf else None
+    lib.sao_alf_picture(lib.device_planes(dst), lib.device_planes(src), sao_d, alf_d, params, lf["ctb_log2"], lf.get("bd", 10))
+    torch.cuda.synchronize()
+    return util.from_device_planes(dst)
+
+
+@pytest.mark.parametrize("w,h", [(416, 240), (136, 72)])
+@pytest.mark.parametrize("i,case", list(enumerate(CASES)))
+def test_fused_sao_alf_matches_oracle_chain(i, case, w, h):
+    ctb, ns, lfase = case
+    lf = synth.loopfilter_ctbs(40 + i, w, h, ctb_log2=ctb, n_slices=ns, lfase=lfase)
+    base = synth.smooth_planes(40 + i, lf["dims"])
+    sao = oracle_sao(base, lf)
+    want = oracle_alf(sao, lf)
+    got = gpu_sao_alf(base, lf)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "plane %d differs" % c
+    # either stage alone
+    got = gpu_sao_alf(base, lf, alf=False)
+    for c in range(3):
+        assert np.array_equal(got[c], sao[c]), "SAO only: plane %d differs" % c
+    want = oracle_alf(base, lf)
+    got = gpu_sao_alf(base, lf, sao=False)
+    for c in range(3):
+        assert np.array_equal(got[c], want[c]), "ALF only: plane %d differs" % c
+
+
+def test_fused_sao_alf_1080p_and_12_bit():
+    for (w, h, ctb, bd, ns, lfase) in ((1920, 1080, 7, 10, 3, 0), (832, 480, 6, 12, 2, 0)):
+        lf = synth.loopfilter_ctbs(51, w, h, ctb_log2=ctb, n_slices=ns, lfase=lfase, alf_on=0.9, bd=bd)
+        base = synth.smooth_planes(51, lf["dims"], bd=bd)
+        want = oracle_alf(oracle_sao(base, lf), lf)
+        assert util.plane_md5(gpu_sao_alf(base, lf)) == util.plane_md5(want)
+
+
 @pytest.mark.parametrize("i,case", list(enumerate(CASES)))
 def test_sao_matches_oracle(i, case):
     ctb, ns, lfase = case
@@ -87,6 +129,7 @@ def test_filters_off_are_identity_4k():
     base = synth.smooth_planes(5, lf["dims"])
     assert util.plane_md5(gpu_sao(base, lf)) == util.plane_md5(base)
     assert util.plane_md5(gpu_alf(base, lf)) == util.plane_md5(base)
+    assert util.plane_md5(gpu_sao_alf(base, lf)) == util.plane_md5(base)
 
 
 def test_lmcs_lut_pass():
