@@ -1,11 +1,13 @@
 #!/usr/bin/env python
 """bench.py — VVC reconstruction + in-loop-filter throughput on B200 (BASELINE.json metric).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload 4k|1080p|8k|tx1080p]
 
-One "step" = one synthetic inter picture through every stage the engine implements (see `config.stages`):
-INTER (luma 8-tap / chroma 4-tap MC, uni/bi/weighted/BCW) -> residual (dequant + inverse DCT2/DST7/DCT8 + add)
--> DEBLOCK_V -> DEBLOCK_H -> SAO -> ALF (+CC-ALF).
+One "step" = one synthetic picture through every stage the engine implements (see `config.stages`):
+INTER (luma 8-tap / chroma 4-tap MC, uni/bi/weighted/BCW, DMVR, BDOF, affine + PROF, GPM) -> residual (dequant +
+inverse DCT2/DST7/DCT8 + add) -> INTRA -> inverse LMCS + DEBLOCK_V + DEBLOCK_H (one pass) -> SAO + ALF + CC-ALF (one pass).
+Workloads (BASELINE.json configs): 4k = config 3 (random-access picture, the one the metric is quoted on), 1080p = config 2,
+8k = config 4 (all-intra 7680x4320), tx1080p = config 1 (dequant + inverse transform batch only).
 `value`   : pictures/s with all descriptor batches and reference pictures resident in HBM, CUDA-event timed,
             max over ranks (N independent streams, one per GPU).
 `e2e`     : the same picture through the Level-B C ABI with HOST (pinned) buffers: every step uploads all
@@ -31,9 +33,9 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 METRIC = "4K 10-bit VVC recon+loop-filter frames/s per B200; % HBM roofline; 8-GPU agg"
-WORKLOADS = {"4k": (3840, 2160), "1080p": (1920, 1080)}
+WORKLOADS = {"4k": (3840, 2160), "1080p": (1920, 1080), "8k": (7680, 4320), "tx1080p": (1920, 1080)}
 L2_BYTES = 126 * 1024 * 1024
-STAGES = ["inter", "residual", "intra", "deblock", "sao", "alf"]
+STAGES = ["inter", "residual", "intra", "deblock", "sao_alf"]
 
 
 def env_int(name, default):
@@ -54,12 +56,12 @@ def measured_peaks():
 # ----------------------------------------------------------------------------------------------------------
 # workload
 # ----------------------------------------------------------------------------------------------------------
-def make_picture(seed, width, height, intra_fraction):
+def make_picture(seed, width, height, intra_fraction, lmcs=True):
     """Synthetic parsed random-access picture (SURVEY.md §8d config 2/3 shape): one CU partition of inter units (regular
     with DMVR/BDOF/BCW/WP, affine + PROF, GPM) and intra units.  Cached under /tmp (or $VVCB200_BENCH_CACHE) for re-runs."""
     from ffmpeg_b200 import abi, synth
     cache = os.path.join(os.environ.get("VVCB200_BENCH_CACHE", "/tmp"),
-                         "vvcb200_bench_v11_%dx%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000)))
+                         "vvcb200_bench_v12_%dx%d_%d_%d_%d.pkl" % (width, height, seed, round(intra_fraction * 1000), int(lmcs)))
     kinds = (("inter", abi.InterParams), ("residual", abi.ResidualParams), ("deblock", abi.DeblockParams),
              ("intra", abi.IntraParams), ("ref", abi.ResidualParams))
     if os.path.exists(cache):
@@ -71,7 +73,7 @@ def make_picture(seed, width, height, intra_fraction):
             return pic
         except Exception:
             pass
-    pic = synth.full_picture(seed, width, height, intra_fraction=intra_fraction)
+    pic = synth.full_picture(seed, width, height, intra_fraction=intra_fraction, lmcs=lmcs)
     try:
         dump = dict(pic)
         for k, _ in kinds:
@@ -109,9 +111,8 @@ def picture_stats(pic):
         "inter": 2 * ref_samples + 2 * S,             # reference samples in, prediction out
         "residual": 2 * int(area.sum()) + 4 * coded,  # int16 levels in, destination read + write
         "intra": intra_bytes,
-        "deblock": 2 * (2 * S + 2 * S),               # two passes, each at most picture in + picture out
-        "sao": 2 * S + 2 * S,
-        "alf": (2 * S + 2 * S) + 2 * S_y,             # picture in + out, luma once more for CC-ALF
+        "deblock": 2 * S + 2 * S,                     # one pass (inverse LMCS + both edge directions): picture in + picture out
+        "sao_alf": 2 * S + 2 * S,                     # one pass (SAO + ALF + CC-ALF): picture in + picture out
     }
     a_pic = 2 * int(area.sum()) + 2 * ref_samples + 2 * S   # §8d: levels in + reference reads + final picture out
     return dict(S=S, coded_samples=coded, ref_samples=ref_samples, stage_bytes=stage, a_pic=a_pic, rho=coded / S,
@@ -169,11 +170,12 @@ class ClockSampler:
 def cpu_picture(pic, threads):
     """One whole picture through the reference's stage functions, every stage spread over `threads` host threads:
     INTER sub-blocks / coding units dealt round-robin, RECON (every residual + intra prediction,
-    ff_vvc_reconstruct) as a CTU-row wavefront like the reference's own scheduler, loop filters by CTB rows with a
-    join per pass.  Returns seconds, kind."""
+    ff_vvc_reconstruct) as a CTU-row wavefront like the reference's own scheduler, LMCS / loop filters by CTB rows with a
+    join per pass.  Returns seconds, kind, planes."""
     from ffmpeg_b200 import abi, lib
     from oracle import portapi, refapi
     it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
+    fwd, inv = pic["lmcs"] if pic["lmcs"] is not None else (None, None)
     planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
     use_ref = refapi.available()
 
@@ -193,40 +195,186 @@ def cpu_picture(pic, threads):
     prof = it["prof"] if len(it["prof"]) else None
     t0 = time.perf_counter()
     if use_ref:
-        spread(lambda b: refapi.inter_batch(planes, it["refs"], b, it["params"]), blocks)
-        spread(lambda c: refapi.inter_cus(planes, it["refs"], c, it["sb_mv"], it["params"]), cus)
-        refapi.recon_picture(planes, pic["ref"], ia["params"], threads=threads, inter=it)
+        spread(lambda b: refapi.inter_batch(planes, it["refs"], b, it["params"], fwd), blocks)
+        spread(lambda c: refapi.inter_cus(planes, it["refs"], c, it["sb_mv"], it["params"], fwd), cus)
+        refapi.recon_picture(planes, pic["ref"], ia["params"], threads=threads, inter=it, lmcs_fwd_lut=fwd)
+        if inv is not None:
+            refapi.lmcs_picture(planes, inv, pic["ctb_log2"], pic.get("bd", 10), threads=threads)
         refapi.deblock_picture(planes, db, threads=threads)
         refapi.sao_picture(planes, lf, threads=threads)
         refapi.alf_picture(planes, lf, threads=threads)
     else:
-        spread(lambda b: portapi.inter_batch(planes, it["refs"], b, it["params"], prof=prof), blocks)
+        spread(lambda b: portapi.inter_batch(planes, it["refs"], b, it["params"], fwd, prof=prof), blocks)
         res = [np.zeros(p.shape, np.int16) for p in planes]
         tbs = [np.ascontiguousarray(rs["tbs"][t::threads]) for t in range(threads)]
         spread(lambda tb: portapi.residual_batch(planes, rs["levels"], tb, rs["params"], residual_planes=res), tbs)
         portapi.intra_picture(planes, res, ia["blocks"], ia["params"])
+        if inv is not None:
+            portapi.lmcs_picture(planes, inv)
         portapi.deblock_picture(planes, edge, db["qp"], db["ctb_offsets"], db["stride4"], db["params"])
         tmp = [np.zeros_like(p) for p in planes]
         portapi.sao_picture(tmp, planes, lf)
         portapi.alf_picture(planes, tmp, lf)
-    return time.perf_counter() - t0, ("reference" if use_ref else "port")
+    return time.perf_counter() - t0, ("reference" if use_ref else "port"), planes
 
 
 def cpu_baseline(pic, budget_s=15.0, max_pics=30):
     threads = os.cpu_count() or 1
-    cpu_picture(pic, threads)                      # warm-up (page-in, first touch)
+    _, _, planes = cpu_picture(pic, threads)       # warm-up (page-in, first touch); its picture is the parity reference
     n, t, kind = 0, 0.0, "port"
     while t < budget_s and n < max_pics:
-        dt, kind = cpu_picture(pic, threads)
+        dt, kind, _ = cpu_picture(pic, threads)
         t += dt
         n += 1
     return {"value": n / t, "unit": "frames/s", "cores": threads, "kind": kind,
-            "sample": "%d whole pictures through INTER + RECON (residual + intra) + deblock + SAO + ALF; sub-blocks / CUs "
+            "sample": "%d whole pictures through INTER + RECON (residual + intra) + LMCS + deblock + SAO + ALF; sub-blocks / CUs "
                       "dealt round-robin, RECON as a CTU-row wavefront, loop-filter CTB rows split over %d host threads "
-                      "(x86 asm not built: no nasm)" % (n, threads)}
+                      "(x86 asm not built: no nasm)" % (n, threads)}, planes
 
 
 # ----------------------------------------------------------------------------------------------------------
+# workload tx1080p (BASELINE config 1): dequant + inverse transform batch only
+# ----------------------------------------------------------------------------------------------------------
+def tx_cpu(pic, threads):
+    """The reference's itransform() over the whole TB batch, TBs dealt round-robin to `threads` host threads."""
+    from oracle import portapi, refapi
+    planes = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
+    parts = [(np.ascontiguousarray(pic["tbs"][t::threads]), np.ascontiguousarray(pic["intra_mode"][t::threads]))
+             for t in range(threads)]
+    use_ref = refapi.available()
+
+    def run(part):
+        tbs, im = part
+        if use_ref:
+            refapi.residual_batch(planes, pic["levels"], tbs, pic["params"], im)
+        else:
+            portapi.residual_batch(planes, pic["levels"], tbs, pic["params"])
+    ths = [threading.Thread(target=run, args=(p,)) for p in parts if len(p[0])]
+    t0 = time.perf_counter()
+    for th in ths:
+        th.start()
+    for th in ths:
+        th.join()
+    return time.perf_counter() - t0, ("reference" if use_ref else "port"), planes
+
+
+def tx_config(args, width, height):
+    return {"workload": "tx1080p: dequant + inverse DCT2/DST7/DCT8 (+ LFNST, TS, BDPCM, scaling lists, joint CbCr) + add over one "
+                        "dense %dx%d 4:2:0 10-bit TB tiling (BASELINE config 1), seed %d" % (width, height, args.seed),
+            "streams": "one independent batch stream per GPU (replicas, no collective)"}
+
+
+def bench_tx(args, rank, world, local):
+    from ffmpeg_b200 import synth
+    width, height = WORKLOADS["tx1080p"]
+    pic = synth.residual_picture(args.seed + rank, width, height)
+    config = tx_config(args, width, height)
+    metric = "1080p dequant + inverse transform batches/s (BASELINE config 1)"
+    threads = os.cpu_count() or 1
+    if args.impl == "reference":
+        for _ in range(args.warmup):
+            tx_cpu(pic, threads)
+        t = 0.0
+        for _ in range(args.steps):
+            dt, kind, _ = tx_cpu(pic, threads)
+            t += dt
+        v = args.steps / t
+        print(json.dumps({"metric": metric, "value": v, "unit": "batches/s", "n_gpus": args.gpus, "steps": args.steps,
+                          "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
+                          "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config, "impl": "reference",
+                          "cpu_baseline": {"value": v, "unit": "batches/s", "cores": threads, "kind": kind,
+                                           "sample": "each step = the whole TB batch"},
+                          "e2e": {"value": v, "unit": "batches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+                          "gpu_launches": 0}))
+        return 0
+    import torch
+    from ffmpeg_b200 import lib
+    from ffmpeg_b200 import hostutil as util
+    torch.cuda.set_device(local)
+    base = [np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]]
+    tbs_np, levels_np = pic["tbs"], pic["levels"]
+    per_set = levels_np.nbytes + tbs_np.nbytes + 2 * sum(p.nbytes for p in base)
+    rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
+    sets = []
+    for _ in range(rot):
+        d = util.to_device_planes(base, torch)
+        sets.append((d, lib.device_planes(d), torch.from_numpy(levels_np).cuda(),
+                     torch.from_numpy(tbs_np.view(np.uint8).reshape(-1)).cuda()))
+    n = len(tbs_np)
+
+    def step(i):
+        d, dp, lv, tb = sets[i % rot]
+        lib.residual_batch(dp, lv, tb, n, pic["params"])
+    warmup = max(args.warmup, 3)
+    for i in range(warmup):
+        step(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    l0 = lib.launch_count()
+    sampler = ClockSampler(local) if rank == 0 else None
+    t_host0 = time.perf_counter()
+    e0.record()
+    for i in range(args.steps):
+        step(warmup + i)
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1)
+    launches = lib.launch_count() - l0
+    t_end, i = time.perf_counter() + 0.6, 0
+    while time.perf_counter() < t_end:          # keep the load up for nvidia-smi's sampling period (not timed)
+        step(i)
+        i += 1
+        if i % 50 == 0:
+            torch.cuda.synchronize()
+    torch.cuda.synchronize()
+    clocks = sampler.stop(t_host0, time.perf_counter()) if sampler is not None else None
+    # parity: the picture after `steps` adds differs per set; compare one fresh add on a zeroed picture
+    d = util.to_device_planes(base, torch)
+    lib.residual_batch(lib.device_planes(d), sets[0][2], sets[0][3], n, pic["params"])
+    torch.cuda.synchronize()
+    got = util.plane_md5(util.from_device_planes(d))
+    area = (1 << (tbs_np["log2_w"].astype(np.int64) + tbs_np["log2_h"]))
+    coded = int(area.sum() + area[(tbs_np["flags"] & 64) != 0].sum())
+    algo = 2 * int(area.sum()) + 4 * coded
+    peak, peak_kind = measured_peaks()
+    kms = ms / args.steps
+    out = {"metric": metric, "value": world * args.steps / (ms / 1e3), "unit": "batches/s", "n_gpus": world, "steps": args.steps,
+           "warmup": warmup, "ms_per_step": kms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+           "dtype": "int32", "data": "synthetic", "config": config, "clocks": clocks, "gpu_launches": int(launches),
+           "transform_blocks": n,
+           "roofline": {"bound": "hbm", "kernel": "residual", "achieved": algo / (kms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                        "frac": algo / (kms * 1e-3) / 1e9 / peak, "traffic": None, "peak_kind": peak_kind,
+                        "algorithmic_bytes_per_launch": algo, "kernel_ms": kms},
+           "l2": "rotating %d working sets (%.0f MB) > 126 MB L2" % (rot, rot * per_set / 1e6)}
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        tx_cpu(pic, threads)
+        n_cpu, t_cpu, kind, planes = 0, 0.0, "port", None
+        while t_cpu < 10.0 and n_cpu < 40:
+            dt, kind, planes = tx_cpu(pic, threads)
+            t_cpu += dt
+            n_cpu += 1
+        ref = util.plane_md5(planes)
+        out["cpu_baseline"] = {"value": n_cpu / t_cpu, "unit": "batches/s", "cores": threads, "kind": kind,
+                               "sample": "%d whole batches, TBs dealt round-robin to %d threads" % (n_cpu, threads)}
+        out["parity"] = {"md5_match": got == ref, "ref_md5": ref, "gpu_md5": got}
+    if rank == 0:
+        print(json.dumps(out))
+    return 0
+
+
+# ----------------------------------------------------------------------------------------------------------
+def picture_config(args, width, height, intra_fraction, lmcs):
+    """What both arms print as `config`: the workload and nothing arm-specific, so that the two lines compare equal."""
+    return {"workload": "%s 4:2:0 10-bit synthetic %s picture (%dx%d), CTU 128, 2 reference pictures, %.0f%% of the coding "
+                        "units intra, LMCS %s, seed %d" % (args.workload, "all-intra" if intra_fraction >= 1 else "random-access",
+                                                          width, height, 100 * intra_fraction, "on" if lmcs else "off", args.seed),
+            "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW, DMVR, BDOF, affine + PROF, GPM, forward LMCS)",
+                       "residual (dequant, inverse DCT2/DST7/DCT8, LFNST, TS, BDPCM, joint CbCr, scaling lists, add)",
+                       "intra (planar / DC / angular + PDPC, MRL, ISP, MIP, CCLM, CIIP, luma-dependent chroma residual scaling; dependency-driven)",
+                       "inverse LMCS", "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
+            "streams": "one independent picture stream per GPU (replicas, no collective)"}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -235,38 +383,38 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="4k", choices=sorted(WORKLOADS))
     ap.add_argument("--seed", type=int, default=2026)
-    ap.add_argument("--intra-fraction", type=float, default=0.1, help="share of coding units that are intra")
+    ap.add_argument("--intra-fraction", type=float, default=None, help="share of coding units that are intra (default 0.1; 8k: 1.0)")
+    ap.add_argument("--lmcs", type=int, default=1, help="0: leave LMCS out of the picture (development only)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
 
     rank, world, local = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
+    if args.workload == "tx1080p":
+        if args.impl == "reference" and rank != 0:
+            return 0
+        return bench_tx(args, rank, world, local)
     width, height = WORKLOADS[args.workload]
+    intra_fraction = args.intra_fraction if args.intra_fraction is not None else (1.0 if args.workload == "8k" else 0.1)
+    lmcs = bool(args.lmcs)
     warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
-    config = {"workload": "%s 4:2:0 10-bit synthetic random-access picture (%dx%d), CTU 128, 2 reference pictures, "
-                          "%.0f%% of the coding units intra" % (args.workload, width, height, 100 * args.intra_fraction),
-              "stages": ["INTER (8-tap luma / 4-tap chroma MC, uni / bi / weighted / BCW, DMVR, BDOF, affine + PROF, GPM)",
-                         "residual (dequant, inverse DCT2/DST7/DCT8, LFNST, TS, BDPCM, joint CbCr, scaling lists, add)",
-                         "intra (planar / DC / angular + PDPC, MRL, ISP, MIP, CCLM; dependency-driven)",
-                         "DEBLOCK_V", "DEBLOCK_H", "SAO", "ALF luma + chroma + CC-ALF"],
-              "not_in_step": "LMCS (sample mapping and luma-dependent chroma scaling are built and tested, not part of this picture)",
-              "streams": "one independent picture stream per GPU (replicas, no collective)"}
+    config = picture_config(args, width, height, intra_fraction, lmcs)
 
     if args.impl == "reference":
         if rank != 0:
             return 0
-        pic = make_picture(args.seed, width, height, args.intra_fraction)
+        pic = make_picture(args.seed, width, height, intra_fraction, lmcs)
         threads = os.cpu_count() or 1
         for _ in range(args.warmup):
             cpu_picture(pic, threads)
         t, kind = 0.0, "port"
         for _ in range(args.steps):
-            dt, kind = cpu_picture(pic, threads)
+            dt, kind, _ = cpu_picture(pic, threads)
             t += dt
         v = args.steps / t
-        config["cpu"] = "reference C built from its own sources (no x86 asm: no nasm on this image), %d host threads" % threads
         out = {"metric": METRIC, "value": v, "unit": "frames/s", "n_gpus": args.gpus, "steps": args.steps,
                "warmup": args.warmup, "ms_per_step": 1e3 * t / args.steps, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "int32", "data": "synthetic", "config": config, "impl": "reference",
+               "cpu": "reference C built from its own sources (no x86 asm: no nasm on this image), %d host threads" % threads,
                "cpu_baseline": {"value": v, "unit": "frames/s", "cores": threads, "kind": kind,
                                 "sample": "each step = one whole picture through the full stage chain"},
                "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -290,16 +438,20 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    pic = make_picture(args.seed + rank, width, height, args.intra_fraction)
+    pic = make_picture(args.seed + rank, width, height, intra_fraction, lmcs)
     st = picture_stats(pic)
     it, rs, ia, db, lf = pic["inter"], pic["residual"], pic["intra"], pic["deblock"], pic["lf"]
+    fwd, inv = pic["lmcs"] if pic["lmcs"] is not None else (None, None)
     frame_bytes = 2 * st["S"]
     ctb = pic["ctb_log2"]
-    irecs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb, ctb,
-                                width, height, order=lib.INTRA_ORDER_DIAGONAL)      # the order vvcb200_pic_intra uses
-    config.update({"transform_blocks": int(len(rs["tbs"])), "pred_blocks": int(len(it["blocks"])),
-                   "intra_records": int(len(irecs)), "intra_sample_share": round(st["intra_share"], 3),
-                   "coded_fraction": round(st["rho"], 3), "ref_samples_per_sample": round(st["r"], 3)})
+    irecs, phases = lib.intra_schedule(ia["blocks"], ia["ctu_first"], (width + (1 << ctb) - 1) >> ctb, (height + (1 << ctb) - 1) >> ctb,
+                                        ctb, width, height, order=lib.INTRA_ORDER_DIAGONAL, phases=True)   # as vvcb200_pic_intra does
+    iparams = lib.phased_params(ia["params"], phases)
+    detail = {"transform_blocks": int(len(rs["tbs"])), "pred_blocks": int(len(it["blocks"])),
+              "intra_records": int(len(irecs)), "intra_phases": {"luma": phases[0], "chroma_add_only": phases[1],
+                                                                  "chroma": int(len(irecs)) - phases[0] - phases[1]},
+              "intra_sample_share": round(st["intra_share"], 3),
+              "coded_fraction": round(st["rho"], 3), "ref_samples_per_sample": round(st["r"], 3)}
 
     # ---- device-resident arm: `rot` complete copies of the picture's working set, visited round-robin -----------
     edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
@@ -311,11 +463,12 @@ def main():
         edge.nbytes + db["qp"].nbytes
     rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
     rot += rot & 1                                   # even: a working set always meets the same lane (stream)
-    config["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
+    detail["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
         rot, rot * per_set / 1e6)
-    config["lanes"] = ("consecutive pictures alternate between two CUDA streams (independent pictures, as the B pictures of "
+    detail["lanes"] = ("consecutive pictures alternate between two CUDA streams (independent pictures, as the B pictures of "
                        "one temporal layer): the latency-bound intra stage of one overlaps the kernels of the other; "
                        "stage_ms come from a separate single-stream pass")
+    n_blocks, n_tbs = len(it["blocks"]), len(rs["tbs"])
     sets = []
     for k in range(rot):
         s = {}
@@ -324,18 +477,20 @@ def main():
         s["tmp"] = [torch.zeros_like(t) for t in s["cur"]]
         s["res"] = [torch.zeros_like(t) for t in s["cur"]]
         s["cur_p"], s["tmp_p"], s["res_p"] = lib.device_planes(s["cur"]), lib.device_planes(s["tmp"]), lib.device_planes(s["res"])
-        s["irecs"] = dev(irecs)
+        s["irecs"] = dev(irecs) if len(irecs) else None
         s["prof"] = dev(it["prof"]) if len(it["prof"]) else None
         s["marks"] = torch.zeros(lib.intra_scratch_bytes(width, height), dtype=torch.uint8, device="cuda")
         s["refs_p"] = [lib.device_planes(r) for r in s["refs"]]
-        s["blocks"], s["levels"], s["tbs"] = dev(it["blocks"]), dev(rs["levels"]), dev(rs["tbs"])
+        s["blocks"] = dev(it["blocks"]) if n_blocks else None
+        s["levels"], s["tbs"] = dev(rs["levels"]), dev(rs["tbs"])
         s["edge"] = torch.from_numpy(edge).cuda()
         s["qp"] = torch.from_numpy(db["qp"]).cuda()
         s["off"] = torch.from_numpy(db["ctb_offsets"]).cuda()
         s["db"] = lib.deblock_tables(s["edge"], s["qp"], s["off"], db["stride4"])
         s["sao"], s["alf"], s["alfp"] = dev(lf["sao"]), dev(lf["alf"]), dev(lf["alf_params"])
+        s["fwd"] = dev(fwd) if fwd is not None else None
+        s["inv"] = dev(inv) if inv is not None else None
         sets.append(s)
-    n_blocks, n_tbs = len(it["blocks"]), len(rs["tbs"])
 
     lanes = [torch.cuda.Stream(), torch.cuda.Stream()]
 
@@ -343,24 +498,23 @@ def main():
         """One picture.  lane: the stream it is queued on (None: torch's current stream, with stage events)."""
         s = sets[i % rot]
         q = lane.cuda_stream if lane is not None else None
-        lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], n_blocks, it["params"], prof=s["prof"], stream=q)
+        if n_blocks:
+            lib.inter_batch(s["cur_p"], s["refs_p"], s["blocks"], n_blocks, it["params"], lmcs_fwd_lut=s["fwd"], prof=s["prof"], stream=q)
         if ev is not None:
             ev[1].record()
         lib.residual_batch(s["cur_p"], s["levels"], s["tbs"], n_tbs, rs["params"], residual=s["res_p"], stream=q)
         if ev is not None:
             ev[2].record()
-        lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), ia["params"], s["marks"], shadow=s["tmp_p"], stream=q)
+        if len(irecs):
+            lib.intra_picture(s["cur_p"], s["res_p"], s["irecs"], len(irecs), iparams, s["marks"], shadow=s["tmp_p"], stream=q)
         if ev is not None:
             ev[3].record()
-        lib.deblock_picture(s["cur_p"], s["db"], db["params"], stream=q)
+        lib.deblock_lmcs_picture(s["tmp_p"], s["cur_p"], s["db"], db["params"], s["inv"], stream=q)
         if ev is not None:
             ev[4].record()
-        lib.sao_picture(s["tmp_p"], s["cur_p"], s["sao"], pic["ctb_log2"], stream=q)
+        lib.sao_alf_picture(s["cur_p"], s["tmp_p"], s["sao"], s["alf"], s["alfp"], pic["ctb_log2"], stream=q)
         if ev is not None:
             ev[5].record()
-        lib.alf_picture(s["cur_p"], s["tmp_p"], s["alf"], s["alfp"], pic["ctb_log2"], stream=q)
-        if ev is not None:
-            ev[6].record()
 
     for i in range(warmup):
         step(i, lane=lanes[i & 1])
@@ -375,7 +529,7 @@ def main():
     stage_ms = {name: float(np.mean([evs[i][k].elapsed_time(evs[i][k + 1]) for i in range(n_serial)]))
                 for k, name in enumerate(STAGES)}
     serial_ms = float(np.mean([evs[i][0].elapsed_time(evs[i][len(STAGES)]) for i in range(n_serial)]))
-    config["serial_ms_per_picture"] = round(serial_ms, 4)
+    detail["serial_ms_per_picture"] = round(serial_ms, 4)
     sampler = ClockSampler(local) if rank == 0 else None
     ev_start, ev_end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     l0 = lib.launch_count()
@@ -408,6 +562,9 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         ms = float(t.item())
     value = world * args.steps / (ms / 1e3)
+    step(0)                                          # one more picture on the current stream: its samples for the parity check
+    torch.cuda.synchronize()
+    dev_md5 = util.plane_md5(util.from_device_planes(sets[0]["cur"]))
     del sets
     torch.cuda.empty_cache()
 
@@ -417,27 +574,44 @@ def main():
     ep = pipeline.EnginePicture(ctx, pic)
     ep.upload_refs()                       # reference pictures are earlier outputs of the same decoder: resident
     e2e_steps = max(3, min(args.steps, 100))
-    for _ in range(3):
-        ep.run()
-    ctx.sync()
-    barrier()
-    t0 = time.perf_counter()
-    for _ in range(e2e_steps):
-        ep.run()
-    ctx.sync()
-    e2e_s = time.perf_counter() - t0
-    if world > 1:
-        t = torch.tensor([e2e_s], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
-    e2e = {"value": world * e2e_steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": ep.h2d_bytes(),
-           "d2h_bytes_per_step": ep.d2h_bytes(), "steps": e2e_steps,
-           "api": "vvcb200_pic_begin/inter/residual/intra/deblock/sao_alf/download (include/vvc_b200.h), pinned host buffers; "
-                  "reference pictures stay in the context's DPB; consecutive pictures rotate over four DPB slots and four "
-                  "host frames and alternate between the context's two compute lanes, so uploads / downloads (copy streams) and the kernels "
-                  "of neighbouring pictures overlap"}
+
+    def e2e_run(n, **kw):
+        for _ in range(3):
+            ep.run(**kw)
+        ctx.sync()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(n):
+            ep.run(**kw)
+        ctx.sync()
+        dt = time.perf_counter() - t0
+        if world > 1:
+            t = torch.tensor([dt], dtype=torch.float64, device="cuda")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            dt = float(t.item())
+        return dt
+
+    e2e_s = e2e_run(e2e_steps)
     e2e_ok = util.plane_md5(ep.out)
     e2e_same = all(util.plane_md5(o) == e2e_ok for o in ep.outs)
+    # what bounds it: the same loop without the picture download, and the download alone
+    no_dl_s = e2e_run(e2e_steps, download=False)
+    dl_s = e2e_run(e2e_steps, only_download=True)
+    h2d, d2h = ep.h2d_bytes(), ep.d2h_bytes()
+    ms_full, ms_nodl, ms_dl = 1e3 * e2e_s / e2e_steps, 1e3 * no_dl_s / e2e_steps, 1e3 * dl_s / e2e_steps
+    bound = max((("picture download (D2H)", ms_dl), ("uploads + kernels + host calls", ms_nodl)), key=lambda kv: kv[1])[0]
+    e2e = {"value": world * e2e_steps / e2e_s, "unit": "frames/s", "h2d_bytes_per_step": h2d,
+           "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+           "ms_per_picture": round(ms_full, 4),
+           "ms_per_picture_without_download": round(ms_nodl, 4),
+           "ms_per_picture_download_alone": round(ms_dl, 4),
+           "d2h_gbs_alone": round(ep.picture_bytes() / (ms_dl * 1e-3) / 1e9, 2),
+           "achieved_h2d_gbs": round(h2d / (ms_full * 1e-3) / 1e9, 2), "achieved_d2h_gbs": round(d2h / (ms_full * 1e-3) / 1e9, 2),
+           "bound": bound,
+           "api": "vvcb200_pic_begin/inter/residual/intra/lmcs/deblock/sao_alf/download (include/vvc_b200.h), pinned host buffers, "
+                  "refined motion vectors read back every picture; reference pictures stay in the context's DPB; consecutive "
+                  "pictures rotate over four DPB slots and four host frames and alternate between the context's two compute "
+                  "lanes, so uploads / downloads (copy streams) and the kernels of neighbouring pictures overlap"}
     ctx.close()
 
     if rank != 0:
@@ -447,11 +621,10 @@ def main():
 
     peak, peak_kind = measured_peaks()
     top = max(stage_ms, key=stage_ms.get)
-    # INTER (3 width classes), residual (5 block classes) and ALF (luma, chroma) launch their grids side by side on forked
-    # streams: each of those stages is timed, and its bytes counted, as one unit; deblocking is two dependent passes
-    launches_per_stage = {"inter": 1, "residual": 1, "intra": 1, "deblock": 2, "sao": 1, "alf": 1}
-    kernel_ms = stage_ms[top] / launches_per_stage[top]
-    algo = st["stage_bytes"][top] / launches_per_stage[top]
+    # INTER (3 width classes), residual (5 block classes) and deblocking (luma, chroma) launch their grids side by side on
+    # forked streams: each stage is timed, and its bytes counted, as one unit
+    kernel_ms = stage_ms[top]
+    algo = st["stage_bytes"][top]
     achieved = algo / (kernel_ms * 1e-3) / 1e9
     traffic = None
     try:
@@ -469,11 +642,16 @@ def main():
                             "frac": st["a_pic"] / (step_ms * 1e-3) / 1e9 / peak}}
     out = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
            "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
-           "dtype": "int32", "data": "synthetic", "config": config, "clocks": clocks, "e2e": e2e,
+           "dtype": "int32", "data": "synthetic", "config": config, "detail": detail, "clocks": clocks, "e2e": e2e,
            "gpu_launches": int(launches), "roofline": roofline, "e2e_plane_md5": e2e_ok,
            "e2e_frames_identical": bool(e2e_same)}
     if world == 1 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline(pic)
+        out["cpu_baseline"], ref_planes = cpu_baseline(pic, budget_s=10.0 if args.workload != "8k" else 1.0)
+        ref_md5 = util.plane_md5(ref_planes)
+        out["parity"] = {"md5_match": bool(ref_md5 == dev_md5 and ref_md5 == e2e_ok and e2e_same), "ref_md5": ref_md5,
+                         "gpu_md5": dev_md5, "e2e_md5": e2e_ok,
+                         "checker": "per-plane MD5 of the reference C's picture (the cpu_baseline leg) against the device-resident "
+                                    "arm's and the end-to-end arm's"}
     print(json.dumps(out))
     if world > 1:
         dist.destroy_process_group()

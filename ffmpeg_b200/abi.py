@@ -118,7 +118,7 @@ assert PB_DTYPE.itemsize == 32
 class InterParams(C.Structure):
     _fields_ = [
         ("bit_depth", C.c_int32), ("log2_denom", C.c_int32 * 2), ("n_w16", C.c_int32), ("n_w8", C.c_int32),
-        ("reserved", C.c_int32 * 3),
+        ("num_ref_idx_active", C.c_int32 * 2), ("reserved", C.c_int32),
         ("weight", ((C.c_int16 * 16) * 3) * 2), ("offset", ((C.c_int16 * 16) * 3) * 2),
         ("ref_slot", (C.c_uint8 * 16) * 2),
     ]
@@ -148,7 +148,10 @@ def order_blocks_by_width(blocks, params):
     f = blocks["flags"].astype(np.int64)
     kind = (f & (PB_GPM | PB_AFFINE | PB_LUMA_ONLY | PB_CHROMA_ONLY | PB_DMVR | PB_BDOF | PB_WP | PB_PROF0 | PB_PROF1)) * 4 + \
         blocks["pred_flag"].astype(np.int64) + 1024 * 1024 * (blocks["bcw_idx"] != 0)
-    order = np.lexsort((kind, -blocks["w"].astype(np.int32)))
+    # the records with the longest latency first (DMVR search + BDOF, BDOF, GPM): a warp spends ten times as long on one of
+    # those as on a plain block, and at the end of the grid they would be its tail
+    slow = np.where(f & PB_DMVR, 0, np.where(f & PB_BDOF, 1, np.where(f & PB_GPM, 2, 3)))
+    order = np.lexsort((kind, slow, -blocks["w"].astype(np.int32)))
     blocks = np.ascontiguousarray(blocks[order])
     params.n_w16 = int(np.sum(blocks["w"] == 16))
     params.n_w8 = int(np.sum(blocks["w"] == 8))
@@ -216,4 +219,5 @@ assert IB_DTYPE.itemsize == 28
 class IntraParams(C.Structure):
     _fields_ = [("bit_depth", C.c_int32), ("ctb_log2_size", C.c_int32), ("chroma_vertical_collocated", C.c_int32),
                 ("lmcs_chroma_scale", C.c_int32), ("lmcs_pivot", C.c_uint16 * 17), ("lmcs_chroma_scale_coeff", C.c_uint16 * 16),
-                ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("pad", C.c_uint8 * 4)]
+                ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("pad", C.c_uint8 * 4),
+                ("n_luma", C.c_int32), ("n_add_only", C.c_int32)]

@@ -40,6 +40,7 @@ struct ForkStreams {
     bool ok = false;
 };
 ForkStreams *fork_streams(cudaStream_t main_stream);
+void fork_streams_release(cudaStream_t main_stream);   // the owner of `main_stream` is about to destroy it (current device)
 
 // ---- device side -------------------------------------------------------------------------------
 __device__ __forceinline__ int clip3(int v, int lo, int hi) { return min(max(v, lo), hi); }

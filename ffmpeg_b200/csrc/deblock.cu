@@ -52,7 +52,8 @@ __device__ __forceinline__ int scale_tc(int tc, int bd)
 }
 
 // loop_filter_luma_large (vvc_filter_template.c:466-552), one line
-__device__ __forceinline__ void luma_large_line(const SegRef &s, int l, int tc, int max_len_p, int max_len_q)
+template <class Seg>
+__device__ __forceinline__ void luma_large_line(const Seg &s, int l, int tc, int max_len_p, int max_len_q)
 {
     // how far the mean `m` below reaches on each side (the reference reads 7 either way; only these matter)
     int np, nq;
@@ -107,7 +108,8 @@ __device__ __forceinline__ void luma_large_line(const SegRef &s, int l, int tc, 
 }
 
 // vvc_loop_filter_luma (vvc_filter_template.c:554-652) for one 4-line segment
-__device__ void deblock_luma_segment(const SegRef &s, int beta_in, int tc_in, int max_len_p, int max_len_q,
+template <class Seg>
+__device__ __forceinline__ void deblock_luma_segment(const Seg &s, int beta_in, int tc_in, int max_len_p, int max_len_q,
                                      int hor_ctu_edge, int bd)
 {
     const int tc = scale_tc(tc_in, bd);
@@ -196,7 +198,8 @@ __device__ void deblock_luma_segment(const SegRef &s, int beta_in, int tc_in, in
 }
 
 // vvc_loop_filter_chroma (vvc_filter_template.c:700-771) for one segment of `size` lines
-__device__ void deblock_chroma_segment(const SegRef &s, int beta_in, int tc_in, int max_len_p, int max_len_q,
+template <class Seg>
+__device__ __forceinline__ void deblock_chroma_segment(const Seg &s, int beta_in, int tc_in, int max_len_p, int max_len_q,
                                        int shift, int bd)
 {
     const int tc = scale_tc(tc_in, bd);
@@ -330,11 +333,13 @@ __global__ void __launch_bounds__(128, VVC_DEBLOCK_MIN_BLOCKS) deblock_kernel(co
 // other edge of that direction reads or modifies (vvc_filter.c:374-397, 418-427), so the edges of a pass are
 // independent threads here exactly as they are in deblock_kernel.
 //
-// Thread mapping: one thread per LINE of an edge (a row for vertical edges, a column for horizontal ones); the 4 (luma)
-// or 2 (chroma) lines of a decision segment are adjacent lanes and share their line-0 / line-3 measures by shuffles.
-// A line keeps its 8 + 8 (4 + 4) samples in registers: two/four 64-bit shared loads for a row, scalar loads for a column.
+// Thread mapping: one thread per decision segment (4 luma / 2 chroma lines), as in deblock_kernel — the same segment
+// routines run on the staged window.  (One thread per line with the segment's decisions shared by shuffles was measured
+// first: 8 segments per warp instead of 32 make every warp walk almost the same union of filter paths, 3x the warp
+// instructions.)
 constexpr int kDT = 64;            // tile side, samples of the plane
 constexpr int kDCA = 8;            // column apron: one 128-bit chunk
+constexpr int kDThreads = 352;      // one round per pass for a luma tile: 17 edges x 20 segments = 340 threads
 constexpr int kDStride = 88;       // staged row stride in samples: 176 B = 11 x 16 B, so that the 128-bit rows of 8
                                    // consecutive lines fall into different bank groups
 
@@ -348,232 +353,89 @@ struct DeblockTileArgs {
     VVCB200DeblockParams p;
 };
 
-__device__ __forceinline__ int seg_sum4(int v)
-{
-    v += __shfl_xor_sync(0xffffffffu, v, 1);
-    v += __shfl_xor_sync(0xffffffffu, v, 2);
-    return v;
-}
+// Accessor of one segment in the staged window: compile-time steps across the edge (XS) and along it (YS).
+template <int XS, int YS>
+struct SegWin {
+    uint16_t *pix;
+    __device__ __forceinline__ int P(int l, int i) const { return pix[-(i + 1) * XS + l * YS]; }
+    __device__ __forceinline__ int Q(int l, int i) const { return pix[i * XS + l * YS]; }
+    __device__ __forceinline__ void setP(int l, int i, int v) const { pix[-(i + 1) * XS + l * YS] = (uint16_t)v; }
+    __device__ __forceinline__ void setQ(int l, int i, int v) const { pix[i * XS + l * YS] = (uint16_t)v; }
+};
 
+// One pass over the staged window: one thread per decision segment (4 luma / 2 chroma lines), exactly the routines of the
+// picture-level kernel on shared memory.  Consecutive lanes take consecutive edges of one segment row (V) or
+// consecutive segments of one edge (H), which spreads a warp's 16-bit accesses over the banks.
 template <bool CHROMA, bool HOR>
-__device__ __forceinline__ void tile_edge_pass(uint16_t *win, const uint16_t *s_tc, const uint8_t *s_beta,
-                                               const DeblockTileArgs &a, int c, int x0, int y0)
+__device__ __forceinline__ void tile_edge_pass(uint16_t *win, const DeblockTileArgs &a, int c, int x0, int y0)
 {
-    constexpr int NS = CHROMA ? 4 : 8;          // samples a line can touch on each side of the edge
     constexpr int ES = CHROMA ? 8 : 4;          // edge spacing in samples of this plane
+    constexpr int SEG = CHROMA ? 2 : 4;         // lines per segment
     constexpr int AR = CHROMA ? 4 : 8;          // row apron
     constexpr int NE = kDT / ES + 1;            // edges per pass, both tile sides included
-    constexpr int LINES = HOR ? kDT : kDT + 2 * AR;
-    constexpr int N = NE * LINES;
-    constexpr int ST = HOR ? kDStride : 1;      // step across the edge
+    constexpr int NSEG = (HOR ? kDT : kDT + 2 * AR) / SEG;
+    constexpr int N = NE * NSEG;
     const int W = a.src.w[c], H = a.src.h[c];
     const int hs = CHROMA ? 1 : 0;
-    const int bd = a.bd;
-    const int lane = threadIdx.x & 31;
-    for (int base = threadIdx.x & ~31; base < N; base += blockDim.x) {
-        const int item = min(base + lane, N - 1);
-        const int e = item / LINES, l = item - e * LINES;
-        const int wx = HOR ? kDCA + l : kDCA + e * ES;          // window coordinates of q0
-        const int wy = HOR ? AR + e * ES : l;
-        const int gx = x0 - kDCA + wx, gy = y0 - AR + wy;       // plane coordinates of q0
-        const bool valid = base + lane < N && gx < W && gy < H && gy >= 0 && (HOR ? gy > 0 : gx > 0);
-        const int ux = (gx << hs) >> 2, uy = (gy << hs) >> 2;
-        const int eb = valid ? a.edge[HOR][c][uy * a.stride4 + ux] : 0;
-        const int bs = eb & 3;
-        if (!__any_sync(0xffffffffu, bs != 0))
+    for (int item = threadIdx.x; item < N; item += blockDim.x) {
+        int e, sg;
+        if (HOR) { e = item / NSEG; sg = item - e * NSEG; }
+        else     { sg = item / NE; e = item - sg * NE; }
+        const int wx = HOR ? kDCA + sg * SEG : kDCA + e * ES;   // window coordinates of line 0's q0
+        const int wy = HOR ? AR + e * ES : sg * SEG;
+        const int gx = x0 - kDCA + wx, gy = y0 - AR + wy;       // plane coordinates
+        if (gx >= W || gy >= H || gy < 0 || (HOR ? gy == 0 : gx == 0))
             continue;
-        uint16_t *q0 = win + wy * kDStride + wx;
-        int p[NS], q[NS];
-        if (HOR) {
-#pragma unroll
-            for (int i = 0; i < NS; i++) {
-                p[i] = q0[-(i + 1) * kDStride];
-                q[i] = q0[i * kDStride];
-            }
-        } else {
-            if constexpr (!CHROMA) {
-                const uint2 a0 = *reinterpret_cast<const uint2 *>(q0 - 8), b1 = *reinterpret_cast<const uint2 *>(q0 + 4);
-                p[NS - 1] = a0.x & 0xffff; p[NS - 2] = a0.x >> 16; p[NS - 3] = a0.y & 0xffff; p[NS - 4] = a0.y >> 16;
-                q[NS - 4] = b1.x & 0xffff; q[NS - 3] = b1.x >> 16; q[NS - 2] = b1.y & 0xffff; q[NS - 1] = b1.y >> 16;
-            }
-            const uint2 a1 = *reinterpret_cast<const uint2 *>(q0 - 4), b0 = *reinterpret_cast<const uint2 *>(q0);
-            p[3] = a1.x & 0xffff; p[2] = a1.x >> 16; p[1] = a1.y & 0xffff; p[0] = a1.y >> 16;
-            q[0] = b0.x & 0xffff; q[1] = b0.x >> 16; q[2] = b0.y & 0xffff; q[3] = b0.y >> 16;
-        }
-        auto setP = [&](int i, int v) { q0[-(i + 1) * ST] = (uint16_t)v; };
-        auto setQ = [&](int i, int v) { q0[i * ST] = (uint16_t)v; };
-        const int pixel_max = (1 << bd) - 1;
+        const int ux = (gx << hs) >> 2, uy = (gy << hs) >> 2;
+        const int eb = a.edge[HOR][c][uy * a.stride4 + ux];
+        const int bs = eb & 3;
+        if (!bs)
+            continue;
+        const int max_len_p = (eb >> 2) & 7, max_len_q = (eb >> 5) & 7;
+        SegWin<HOR ? kDStride : 1, HOR ? 1 : kDStride> s;
+        s.pix = win + wy * kDStride + wx;
         const int qu = uy * a.stride4 + ux;
         const int pu = HOR ? qu - a.stride4 : qu - 1;
         const int ctb = ((gy << hs) >> a.ctb_log2) * a.ctb_width + ((gx << hs) >> a.ctb_log2);
-        int lp = (eb >> 2) & 7, lq = (eb >> 5) & 7;
-
-        if constexpr (!CHROMA) {
-            // ---- luma: vvc_loop_filter_luma (vvc_filter_template.c:554-652), this thread is line l & 3 of its segment
-            const bool dec = (l & 3) == 0 || (l & 3) == 3;               // the decision lines
-            const int level = seg_sum4(dec ? p[0] + q[0] : 0) >> 2;       // ladf_level (vvc_filter_template.c:654-657)
-            int tc = 0, beta = 0;
-            if (bs) {
-                int qp = (a.qp[0][pu] + a.qp[0][qu] + 1) >> 1;
-                if (a.p.ladf_enabled) {
-                    int off = a.p.ladf_lowest_interval_qp_offset;
-                    for (int i = 0; i < a.p.num_ladf_intervals - 1 && level > a.p.ladf_interval_lower_bound[i + 1]; i++)
-                        off = a.p.ladf_qp_offset[i];
-                    qp += off;
-                }
-                const int beta_offset = a.ctb_offsets[ctb * 6], tc_offset = a.ctb_offsets[ctb * 6 + 3];
-                beta = s_beta[clip3(qp + beta_offset, 0, 63)] << (bd - 8);
-                tc = scale_tc(s_tc[clip3(qp + 2 * (bs - 1) + (tc_offset & -2), 0, 65)], bd);
-            }
-            const bool hor_ctu_edge = HOR && !(gy & ((1 << a.ctb_log2) - 1));
-            const bool large_p = lp > 3 && !hor_ctu_edge, large_q = lq > 3;
-            const bool large = large_p || large_q;
-            if (large) {                                                  // kept for the fall-through, as in the reference
-                lp = large_p ? lp : 3;
-                lq = large_q ? lq : 3;
-            }
-            const int tc25 = (tc * 5 + 1) >> 1;
-            const int dp = abs(p[2] - 2 * p[1] + p[0]), dq = abs(q[2] - 2 * q[1] + q[0]);
-            const int dpl = large_p ? (dp + abs(p[5] - 2 * p[4] + p[3]) + 1) >> 1 : dp;
-            const int dql = large_q ? (dq + abs(q[5] - 2 * q[4] + q[3]) + 1) >> 1 : dq;
-            const int d = dp + dq, dl = dpl + dql;
-            const int p_far = lp == 7 ? p[7] : lp == 5 ? p[5] : p[3], q_far = lq == 7 ? q[7] : lq == 5 ? q[5] : q[3];
-            const int spl = abs(p[3] - p[0]) + (lp == 7 ? abs(p[7] - p[6] - p[5] + p[4]) : 0);
-            const int sql = abs(q[0] - q[3]) + (lq == 7 ? abs(q[4] - q[5] - q[6] + q[7]) : 0);
-            const int sp = large_p ? (spl + abs(p[3] - p_far) + 1) >> 1 : spl;
-            const int sq = large_q ? (sql + abs(q[3] - q_far) + 1) >> 1 : sql;
-            const bool near = abs(p[0] - q[0]) < tc25;
-            const bool line_large = sp + sq < (beta * 3 >> 5) && near && (dl << 1) < (beta >> 4);
-            const bool line_strong = abs(p[3] - p[0]) + abs(q[3] - q[0]) < (beta >> 3) && near && (d << 1) < (beta >> 2);
-            const int sa = seg_sum4(dec ? dl | (d << 16) : 0);
-            const int sb = seg_sum4(dec ? dp | (dq << 16) : 0);
-            const int sc = seg_sum4(dec ? (int)line_large | ((int)line_strong << 4) : 0);
-            if (!bs || !tc)
-                continue;
-            if (large && (sa & 0xffff) < beta && (sc & 15) == 2) {
-                // loop_filter_luma_large (vvc_filter_template.c:466-552), this line
-                int m;
-                if (lp == 5 && lq == 5)
-                    m = (p[4] + p[3] + 2 * (p[2] + p[1] + p[0] + q[0] + q[1] + q[2]) + q[3] + q[4] + 8) >> 4;
-                else if (lp == lq)
-                    m = (p[6] + p[5] + p[4] + p[3] + p[2] + p[1] + 2 * (p[0] + q[0]) + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + 8) >> 4;
-                else if (lp + lq == 12)
-                    m = (p[5] + p[4] + p[3] + p[2] + 2 * (p[1] + p[0] + q[0] + q[1]) + q[2] + q[3] + q[4] + q[5] + 8) >> 4;
-                else if (lp + lq == 8)
-                    m = (p[3] + p[2] + p[1] + p[0] + q[0] + q[1] + q[2] + q[3] + 4) >> 3;
-                else if (lq == 7)
-                    m = (2 * (p[2] + p[1] + p[0] + q[0]) + p[0] + p[1] + q[1] + q[2] + q[3] + q[4] + q[5] + q[6] + 8) >> 4;
-                else
-                    m = (p[6] + p[5] + p[4] + p[3] + p[2] + p[1] + 2 * (q[2] + q[1] + q[0] + p[0]) + q[0] + q[1] + 8) >> 4;
-                const int w3[3] = { 53, 32, 11 },               c3[3] = { 6, 4, 2 };
-                const int w5[5] = { 58, 45, 32, 19, 6 },         c5[5] = { 6, 5, 4, 3, 2 };
-                const int w7[7] = { 59, 50, 41, 32, 23, 14, 5 }, c7[7] = { 6, 5, 4, 3, 2, 1, 1 };
-                const int refp = (p_far + (lp == 7 ? p[6] : lp == 5 ? p[4] : p[2]) + 1) >> 1;
-                const int refq = (q_far + (lq == 7 ? q[6] : lq == 5 ? q[4] : q[2]) + 1) >> 1;
-#pragma unroll
-                for (int i = 0; i < 7; i++) {
-                    if (i < lp) {
-                        const int w = lp == 3 ? w3[i % 3] : lp == 5 ? w5[i % 5] : w7[i];
-                        const int cf = lp == 3 ? c3[i % 3] : lp == 5 ? c5[i % 5] : c7[i];
-                        const int lim = (tc * cf) >> 1;
-                        setP(i, p[i] + clip3(((m * w + refp * (64 - w) + 32) >> 6) - p[i], -lim, lim));
-                    }
-                    if (i < lq) {
-                        const int w = lq == 3 ? w3[i % 3] : lq == 5 ? w5[i % 5] : w7[i];
-                        const int cf = lq == 3 ? c3[i % 3] : lq == 5 ? c5[i % 5] : c7[i];
-                        const int lim = (tc * cf) >> 1;
-                        setQ(i, q[i] + clip3(((m * w + refq * (64 - w) + 32) >> 6) - q[i], -lim, lim));
-                    }
-                }
-                continue;
-            }
-            if ((sa >> 16) >= beta)
-                continue;
-            if (lp > 2 && lq > 2 && (sc >> 4) == 2) {
-                // loop_filter_luma_strong (h2656_deblock_template.c:25-51)
-                const int tc2 = tc << 1, tc3 = tc * 3;
-                setP(0, p[0] + clip3(((p[2] + 2 * p[1] + 2 * p[0] + 2 * q[0] + q[1] + 4) >> 3) - p[0], -tc3, tc3));
-                setP(1, p[1] + clip3(((p[2] + p[1] + p[0] + q[0] + 2) >> 2) - p[1], -tc2, tc2));
-                setP(2, p[2] + clip3(((2 * p[3] + 3 * p[2] + p[1] + p[0] + q[0] + 4) >> 3) - p[2], -tc, tc));
-                setQ(0, q[0] + clip3(((p[1] + 2 * p[0] + 2 * q[0] + 2 * q[1] + q[2] + 4) >> 3) - q[0], -tc3, tc3));
-                setQ(1, q[1] + clip3(((p[0] + q[0] + q[1] + q[2] + 2) >> 2) - q[1], -tc2, tc2));
-                setQ(2, q[2] + clip3(((2 * q[3] + 3 * q[2] + q[1] + q[0] + p[0] + 4) >> 3) - q[2], -tc, tc));
-            } else {
-                // loop_filter_luma_weak (h2656_deblock_template.c:53-83)
-                const int side = (beta + (beta >> 1)) >> 3;
-                const bool two_p = lp > 1 && lq > 1 && (sb & 0xffff) < side;
-                const bool two_q = lp > 1 && lq > 1 && (sb >> 16) < side;
-                const int tc_2 = tc >> 1;
-                int delta0 = (9 * (q[0] - p[0]) - 3 * (q[1] - p[1]) + 8) >> 4;
-                if (abs(delta0) < 10 * tc) {
-                    delta0 = clip3(delta0, -tc, tc);
-                    setP(0, clip3(p[0] + delta0, 0, pixel_max));
-                    setQ(0, clip3(q[0] - delta0, 0, pixel_max));
-                    if (two_p)
-                        setP(1, clip3(p[1] + clip3((((p[2] + p[0] + 1) >> 1) - p[1] + delta0) >> 1, -tc_2, tc_2), 0, pixel_max));
-                    if (two_q)
-                        setQ(1, clip3(q[1] + clip3((((q[2] + q[0] + 1) >> 1) - q[1] - delta0) >> 1, -tc_2, tc_2), 0, pixel_max));
-                }
+        int qp;
+        if (!CHROMA) {
+            qp = (a.qp[0][pu] + a.qp[0][qu] + 1) >> 1;
+            if (a.p.ladf_enabled) {
+                const int level = (s.P(0, 0) + s.P(3, 0) + s.Q(0, 0) + s.Q(3, 0)) >> 2;
+                int off = a.p.ladf_lowest_interval_qp_offset;
+                for (int i = 0; i < a.p.num_ladf_intervals - 1 && level > a.p.ladf_interval_lower_bound[i + 1]; i++)
+                    off = a.p.ladf_qp_offset[i];
+                qp += off;
             }
         } else {
-            // ---- chroma: vvc_loop_filter_chroma (vvc_filter_template.c:700-771), 4:2:0: two lines per segment, both decide
-            int tc = 0, beta = 0;
-            if (bs) {
-                const int qp = (a.qp[c][pu] + a.qp[c][qu] - 2 * 6 * (bd - 8) + 1) >> 1;
-                const int beta_offset = a.ctb_offsets[ctb * 6 + c], tc_offset = a.ctb_offsets[ctb * 6 + 3 + c];
-                beta = s_beta[clip3(qp + beta_offset, 0, 63)] << (bd - 8);
-                tc = scale_tc(s_tc[clip3(qp + 2 * (bs - 1) + (tc_offset & -2), 0, 65)], bd);
-            }
-            const int tc25 = (tc * 5 + 1) >> 1;
-            const int p2 = lp == 1 ? p[1] : p[2], p3 = lp == 1 ? p[1] : p[3];
-            const int d = abs(p2 - 2 * p[1] + p[0]) + abs(q[2] - 2 * q[1] + q[0]);
-            const bool dsam = (d << 1) < (beta >> 2) && abs(p3 - p[0]) + abs(q[0] - q[3]) < (beta >> 3) && abs(p[0] - q[0]) < tc25;
-            int sa = d | ((int)dsam << 16);
-            sa += __shfl_xor_sync(0xffffffffu, sa, 1);
-            if (!bs || !tc || !lp || !lq)
-                continue;
-            if (lq == 3 && !((sa & 0xffff) < beta && (sa >> 16) == 2))
-                lp = lq = 1;
-            if (lp == 3 && lq == 3) {
-                setP(0, clip3((p[3] + p[2] + p[1] + 2 * p[0] + q[0] + q[1] + q[2] + 4) >> 3, p[0] - tc, p[0] + tc));
-                setP(1, clip3((2 * p[3] + p[2] + 2 * p[1] + p[0] + q[0] + q[1] + 4) >> 3, p[1] - tc, p[1] + tc));
-                setP(2, clip3((3 * p[3] + 2 * p[2] + p[1] + p[0] + q[0] + 4) >> 3, p[2] - tc, p[2] + tc));
-                setQ(0, clip3((p[2] + p[1] + p[0] + 2 * q[0] + q[1] + q[2] + q[3] + 4) >> 3, q[0] - tc, q[0] + tc));
-                setQ(1, clip3((p[1] + p[0] + q[0] + 2 * q[1] + q[2] + 2 * q[3] + 4) >> 3, q[1] - tc, q[1] + tc));
-                setQ(2, clip3((p[0] + q[0] + q[1] + 2 * q[2] + 3 * q[3] + 4) >> 3, q[2] - tc, q[2] + tc));
-            } else if (lq == 3) {
-                setP(0, clip3((3 * p[1] + 2 * p[0] + q[0] + q[1] + q[2] + 4) >> 3, p[0] - tc, p[0] + tc));
-                setQ(0, clip3((2 * p[1] + p[0] + 2 * q[0] + q[1] + q[2] + q[3] + 4) >> 3, q[0] - tc, q[0] + tc));
-                setQ(1, clip3((p[1] + p[0] + q[0] + 2 * q[1] + q[2] + 2 * q[3] + 4) >> 3, q[1] - tc, q[1] + tc));
-                setQ(2, clip3((p[0] + q[0] + q[1] + 2 * q[2] + 3 * q[3] + 4) >> 3, q[2] - tc, q[2] + tc));
-            } else {
-                const int delta0 = clip3((((q[0] - p[0]) * 4) + p[1] - q[1] + 4) >> 3, -tc, tc);
-                setP(0, clip3(p[0] + delta0, 0, pixel_max));
-                setQ(0, clip3(q[0] - delta0, 0, pixel_max));
-            }
+            qp = (a.qp[c][pu] + a.qp[c][qu] - 2 * 6 * (a.bd - 8) + 1) >> 1;
+        }
+        const int beta_offset = a.ctb_offsets[ctb * 6 + c];
+        const int tc_offset = a.ctb_offsets[ctb * 6 + 3 + c];
+        const int beta = c_betatable[clip3(qp + beta_offset, 0, 63)];
+        const int tc = c_tctable[clip3(qp + 2 * (bs - 1) + (tc_offset & -2), 0, 65)];
+        if (!CHROMA) {
+            const int hor_ctu_edge = HOR && !(gy & ((1 << a.ctb_log2) - 1));
+            deblock_luma_segment(s, beta, tc, max_len_p, max_len_q, hor_ctu_edge, a.bd);
+        } else {
+            deblock_chroma_segment(s, beta, tc, max_len_p, max_len_q, 1, a.bd);
         }
     }
 }
 
 template <bool CHROMA, bool LUT>
-__global__ void __launch_bounds__(256) deblock_tile_kernel(const DeblockTileArgs a)
+__global__ void __launch_bounds__(kDThreads, 3) deblock_tile_kernel(const DeblockTileArgs a)
 {
     constexpr int AR = CHROMA ? 4 : 8;
     constexpr int WR = kDT + 2 * AR;
     __shared__ __align__(16) uint16_t win[WR * kDStride];
-    __shared__ uint16_t s_tc[66];
-    __shared__ uint8_t s_beta[64];
     __shared__ uint16_t s_lut[LUT ? 4096 : 1];
     const int c = CHROMA ? 1 + blockIdx.z : 0;
     const int x0 = blockIdx.x * kDT, y0 = blockIdx.y * kDT;
     const int W = a.src.w[c], H = a.src.h[c];
     const int t = threadIdx.x;
-    if (t < 66)
-        s_tc[t] = c_tctable[t];
-    if (t < 64)
-        s_beta[t] = c_betatable[t];
     if (LUT) {
-        for (int i = t; i < (1 << a.bd); i += 256)
+        for (int i = t; i < (1 << a.bd); i += kDThreads)
             s_lut[i] = a.lut[i];
         __syncthreads();
     }
@@ -582,7 +444,7 @@ __global__ void __launch_bounds__(256) deblock_tile_kernel(const DeblockTileArgs
         const uint16_t *src = a.src.p[c];
         const int stride = a.src.stride[c];
         constexpr int CH = (kDT + 2 * kDCA) / 8;                 // 10 chunks per row
-        for (int i = t; i < WR * CH; i += 256) {
+        for (int i = t; i < WR * CH; i += kDThreads) {
             const int r = i / CH, k = i - r * CH;
             const int gx = x0 - kDCA + 8 * k, gy = y0 - AR + r;
             uint4 v = make_uint4(0, 0, 0, 0);
@@ -599,14 +461,14 @@ __global__ void __launch_bounds__(256) deblock_tile_kernel(const DeblockTileArgs
         }
     }
     __syncthreads();
-    tile_edge_pass<CHROMA, false>(win, s_tc, s_beta, a, c, x0, y0);
+    tile_edge_pass<CHROMA, false>(win, a, c, x0, y0);
     __syncthreads();
-    tile_edge_pass<CHROMA, true>(win, s_tc, s_beta, a, c, x0, y0);
+    tile_edge_pass<CHROMA, true>(win, a, c, x0, y0);
     __syncthreads();
     {
         uint16_t *dst = a.dst.p[c];
         const int stride = a.dst.stride[c];
-        for (int i = t; i < kDT * (kDT / 8); i += 256) {
+        for (int i = t; i < kDT * (kDT / 8); i += kDThreads) {
             const int r = i >> 3, k = i & 7;
             const int gx = x0 + 8 * k, gy = y0 + r;
             if (gy >= H || gx >= W)
@@ -715,12 +577,12 @@ extern "C" int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVCB
     }
     dim3 gl((src->width[0] + kDT - 1) / kDT, (src->height[0] + kDT - 1) / kDT, 1);
     if (d_inv_lut)
-        deblock_tile_kernel<false, true><<<gl, 256, 0, main_stream>>>(a);
+        deblock_tile_kernel<false, true><<<gl, kDThreads, 0, main_stream>>>(a);
     else
-        deblock_tile_kernel<false, false><<<gl, 256, 0, main_stream>>>(a);
+        deblock_tile_kernel<false, false><<<gl, kDThreads, 0, main_stream>>>(a);
     VVC_LAUNCH_CHECK();
     dim3 gc((src->width[1] + kDT - 1) / kDT, (src->height[1] + kDT - 1) / kDT, 2);
-    deblock_tile_kernel<true, false><<<gc, 256, 0, side>>>(a);
+    deblock_tile_kernel<true, false><<<gc, kDThreads, 0, side>>>(a);
     VVC_LAUNCH_CHECK();
     if (f) {
         VVC_CUDA(cudaEventRecord(f->join[0], side));

@@ -71,6 +71,7 @@ struct Lane {
     DevPicture scratch;            // SAO output / ALF input; before that, the intra stage's shadow picture
     DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
     DevBuffer intra_marks;
+    cudaEvent_t tail = nullptr;    // "everything this lane has queued so far", recorded when the other lane must get behind it
 };
 constexpr int kLanes = 2, kSets = 4;   // two descriptor sets per lane: the next picture of a lane uploads while this one runs
 struct StageSet {
@@ -81,7 +82,9 @@ struct StageSet {
     cudaEvent_t uploaded = nullptr;    // last upload into this set (recorded on the upload stream)
     cudaEvent_t consumed = nullptr;    // last kernel that read this set (recorded on the compute stream)
     cudaEvent_t order_copied = nullptr;    // the upload out of h_order (recorded on the upload stream)
-    bool in_use = false, order_pending = false;
+    cudaEvent_t mv_ready = nullptr;        // INTER has written `refined` (compute stream)
+    cudaEvent_t mv_copied = nullptr;       // `refined` has reached the host (download stream)
+    bool in_use = false, order_pending = false, mv_pending = false;
 };
 
 struct VVCB200Ctx {
@@ -100,6 +103,9 @@ struct VVCB200Ctx {
     StageSet sets[kSets];
     int set = 0;
     int validate = 1;              // 0: trust the emitter, 1: spot checks (class boundaries + every 64th record), 2: every record
+    // The loop-filter passes are out of place and ping-pong between the DPB buffer and the lane's scratch picture:
+    bool in_scratch = false;       // the current picture's newest samples are in its lane's scratch picture, not in dpb[cur]
+    bool lmcs_pending = false;     // vvcb200_pic_lmcs was called; the mapping rides on the deblocking pass's load if one follows
 };
 
 static inline int lane_of(int set) { return set % kLanes; }
@@ -169,16 +175,19 @@ int set_consumed(VVCB200Ctx *c)
 }
 
 // The current lane is about to overwrite DPB slot `slot`: wait for the other lane's write of it and for the other lane's
-// pictures that use it as a reference (everything that lane has queued so far).
+// pictures that use it as a reference — everything that lane has queued so far, marked with an event recorded now.
 int order_before_write(VVCB200Ctx *c, int slot)
 {
     const int other = lane_of(c->set) ^ 1;
-    if (c->writer[slot] == other)
-        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
     if ((c->readers[slot] >> other) & 1) {
-        const StageSet &prev = c->sets[(c->set + kSets - 1) % kSets];     // the other lane's latest picture
-        if (prev.in_use)
-            VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), prev.consumed, 0));
+        VVC_CUDA(cudaEventRecord(c->lanes[other].tail, c->lanes[other].stream));
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->lanes[other].tail, 0));
+    } else if (c->writer[slot] == other) {
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
+    }
+    if (c->download_pending[slot]) {      // the slot's previous content is still on its way to the host
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->downloaded[slot], 0));
+        c->download_pending[slot] = 0;
     }
     c->readers[slot] = 0;
     return 0;
@@ -190,6 +199,28 @@ int order_before_read(VVCB200Ctx *c, int slot)
     if (c->writer[slot] == (lane_of(c->set) ^ 1))
         VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->written[slot], 0));
     c->readers[slot] |= (unsigned char)(1u << lane_of(c->set));
+    return 0;
+}
+
+// Bring the current picture to rest in its DPB slot: run a mapping that no deblocking pass picked up, and if the newest
+// samples sit in the lane's scratch picture, exchange the two buffers (both belong to this lane's stream order).
+int settle_picture(VVCB200Ctx *c)
+{
+    StageSet &S = c->sets[c->set];
+    if (c->lmcs_pending) {
+        c->lmcs_pending = false;
+        VVCB200Planes *pl = c->in_scratch ? &S.lane->scratch.planes : &c->dpb[c->cur].planes;
+        if (int r = vvcb200_lmcs_picture(pl, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.lane->stream))
+            return r;
+        if (int r = set_consumed(c))
+            return r;
+    }
+    if (c->in_scratch) {
+        c->in_scratch = false;
+        DevPicture t = c->dpb[c->cur];
+        c->dpb[c->cur] = S.lane->scratch;
+        S.lane->scratch = t;
+    }
     return 0;
 }
 
@@ -236,13 +267,17 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     c->bit_depth = bit_depth;
     cudaError_t e = cudaStreamCreateWithFlags(&c->h2d, cudaStreamNonBlocking);
     if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->d2h, cudaStreamNonBlocking);
-    for (int i = 0; i < kLanes && e == cudaSuccess; i++)
+    for (int i = 0; i < kLanes && e == cudaSuccess; i++) {
         e = cudaStreamCreateWithFlags(&c->lanes[i].stream, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->lanes[i].tail, cudaEventDisableTiming);
+    }
     for (int i = 0; i < kSets && e == cudaSuccess; i++) {
         c->sets[i].lane = &c->lanes[lane_of(i)];
         e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].consumed, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].order_copied, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].mv_ready, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].mv_copied, cudaEventDisableTiming);
     }
     c->downloaded.assign(dpb_size, nullptr);
     c->written.assign(dpb_size, nullptr);
@@ -290,8 +325,12 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
         if (ss.uploaded) cudaEventDestroy(ss.uploaded);
         if (ss.consumed) cudaEventDestroy(ss.consumed);
         if (ss.order_copied) cudaEventDestroy(ss.order_copied);
+        if (ss.mv_ready) cudaEventDestroy(ss.mv_ready);
+        if (ss.mv_copied) cudaEventDestroy(ss.mv_copied);
     }
     for (Lane &l : c->lanes) {
+        if (l.stream) fork_streams_release(l.stream);
+        if (l.tail) cudaEventDestroy(l.tail);
         l.intra_marks.release();
         if (l.scratch.base) cudaFree(l.scratch.base);
         if (l.residual.base) cudaFree(l.residual.base);
@@ -316,6 +355,8 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
     if (!c)
         return VVCB200_ERR_ARG;
     DeviceGuard g(c->device);
+    if (int r = settle_picture(c))
+        return r;
     VVC_CUDA(cudaStreamSynchronize(c->h2d));
     VVC_CUDA(cudaStreamSynchronize(c->lanes[0].stream));
     VVC_CUDA(cudaStreamSynchronize(c->lanes[1].stream));
@@ -323,7 +364,7 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
     for (char &p : c->download_pending)
         p = 0;
     for (StageSet &ss : c->sets)
-        ss.in_use = ss.order_pending = false;
+        ss.in_use = ss.order_pending = ss.mv_pending = false;
     for (size_t i = 0; i < c->writer.size(); i++) {                       // nothing is in flight: no ordering left to do
         c->writer[i] = -1;
         c->readers[i] = 0;
@@ -345,6 +386,11 @@ void *vvcb200_ctx_stream(VVCB200Ctx *c) { return c ? (void *)lane_stream(c) : nu
 
 int vvcb200_ctx_planes(VVCB200Ctx *c, int slot, VVCB200Planes *out)
 {
+    if (c) {
+        DeviceGuard g(c->device);
+        if (int r = settle_picture(c))
+            return r;
+    }
     DevPicture *p = c ? slot_of(c, slot) : nullptr;
     if (!p || !out) {
         set_error("vvcb200_ctx_planes: bad context or slot %d", slot);
@@ -377,15 +423,13 @@ int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
         return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    if (int r = settle_picture(c))        // the picture before this one
+        return r;
     c->cur = slot;
     c->set = (c->set + 1) % kSets;
     StageSet &s = c->sets[c->set];
     if (s.in_use)                         // uploads of this picture must not overtake the kernels of the picture before last
         VVC_CUDA(cudaStreamWaitEvent(c->h2d, s.consumed, 0));
-    if (c->download_pending[slot]) {      // the slot's previous content is still on its way to the host
-        VVC_CUDA(cudaStreamWaitEvent(s.lane->stream, c->downloaded[slot], 0));
-        c->download_pending[slot] = 0;
-    }
     return order_before_write(c, slot);
 }
 
@@ -398,9 +442,13 @@ int vvcb200_pic_upload(VVCB200Ctx *c, int slot, const uint16_t *const planes[3],
     }
     DeviceGuard g(c->device);
     const int idx = slot < 0 ? c->cur : slot;
-    if (idx != c->cur)
-        if (int r = order_before_write(c, idx))
+    if (idx == c->cur) {
+        if (int r = settle_picture(c))
             return r;
+        p = &c->dpb[idx];
+    } else if (int r = order_before_write(c, idx)) {
+        return r;
+    }
     for (int i = 0; i < 3; i++)
         VVC_CUDA(cudaMemcpy2DAsync(p->planes.d_plane[i], p->planes.stride[i], planes[i], strides[i],
                                    (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyHostToDevice, lane_stream(c)));
@@ -418,6 +466,11 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
     }
     DeviceGuard g(c->device);
     const int idx = slot < 0 ? c->cur : slot;
+    if (idx == c->cur) {
+        if (int r = settle_picture(c))
+            return r;
+        p = &c->dpb[idx];
+    }
     if (c->writer[idx] >= 0)              // whatever wrote the slot last, in whichever lane
         VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->written[idx], 0));
     for (int i = 0; i < 3; i++)
@@ -458,6 +511,8 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
                 return VVCB200_ERR_ARG;
     }
     DeviceGuard g(c->device);
+    if (int r = settle_picture(c))
+        return r;
     StageSet &S = c->sets[c->set];
     if (int r = upload(c, S.blocks, blocks, (size_t)n * sizeof(*blocks)))
         return r;
@@ -477,11 +532,13 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
                 set_error("vvcb200_pic_inter: ref_slot[%d][%d] = %d is not a DPB slot of this context", l, i, params->ref_slot[l][i]);
                 return VVCB200_ERR_ARG;
             }
-    for (int l = 0; l < 2; l++)                   // reference pictures the other lane is still writing
-        for (int i = 0; i < 16; i++)
+    for (int l = 0; l < 2; l++) {                 // reference pictures the other lane is still writing
+        const int active = params->num_ref_idx_active[l] > 0 && params->num_ref_idx_active[l] <= 16 ? params->num_ref_idx_active[l] : 16;
+        for (int i = 0; i < active; i++)
             if (params->ref_slot[l][i] != c->cur)
                 if (int r = order_before_read(c, params->ref_slot[l][i]))
                     return r;
+    }
     int32_t *d_mv = nullptr;
     if (refined_mv) {
         if ((size_t)n * 4 * sizeof(int32_t) > S.refined.cap)
@@ -489,6 +546,10 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
         if (int r = S.refined.reserve((size_t)n * 4 * sizeof(int32_t)))
             return r;
         d_mv = (int32_t *)S.refined.p;
+        if (S.mv_pending) {               // this set's previous vectors must have left before the kernels overwrite them
+            VVC_CUDA(cudaStreamWaitEvent(S.lane->stream, S.mv_copied, 0));
+            S.mv_pending = false;
+        }
     }
     const VVCB200ProfTable *d_prof = nullptr;
     if (prof && n_prof > 0) {
@@ -503,8 +564,14 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
         return r;
     if (int r = set_consumed(c))
         return r;
-    if (refined_mv)     // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762)
-        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, S.lane->stream));
+    if (refined_mv) {   // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762), on the
+                        // download stream so that the lane goes straight on with the residual stage
+        VVC_CUDA(cudaEventRecord(S.mv_ready, S.lane->stream));
+        VVC_CUDA(cudaStreamWaitEvent(c->d2h, S.mv_ready, 0));
+        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->d2h));
+        VVC_CUDA(cudaEventRecord(S.mv_copied, c->d2h));
+        S.mv_pending = true;
+    }
     return 0;
 }
 
@@ -553,6 +620,8 @@ int vvcb200_pic_residual(VVCB200Ctx *c, const int16_t *levels, size_t n_levels,
         }
     }
     DeviceGuard g(c->device);
+    if (int r = settle_picture(c))
+        return r;
     StageSet &S = c->sets[c->set];
     if (int r = upload(c, S.levels, levels, n_levels * sizeof(int16_t)))
         return r;
@@ -613,6 +682,8 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         }
     }
     DeviceGuard g(c->device);
+    if (int r = settle_picture(c))
+        return r;
     if (S.order_pending) {                // the copy that last read this set's pinned staging (two pictures ago) must be over
         VVC_CUDA(cudaEventSynchronize(S.order_copied));
         S.order_pending = false;
@@ -626,9 +697,13 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         VVC_CUDA(cudaHostAlloc((void **)&S.h_order, want * sizeof(VVCB200IntraBlock), cudaHostAllocDefault));
         S.h_order_cap = want;
     }
+    int32_t phases[2] = { 0, 0 };
     if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, shift, c->width, c->height,
-                                       VVCB200_INTRA_ORDER_DIAGONAL, S.h_order, nullptr))
+                                       VVCB200_INTRA_ORDER_DIAGONAL, S.h_order, nullptr, phases))
         return r;
+    VVCB200IntraParams phased = *params;
+    phased.n_luma = phases[0];
+    phased.n_add_only = phases[1];
     if (int r = upload(c, S.iblocks, S.h_order, (size_t)n * sizeof(VVCB200IntraBlock)))
         return r;
     VVC_CUDA(cudaEventRecord(S.order_copied, c->h2d));
@@ -640,7 +715,7 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return r;
     // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
     if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, have_res ? &S.lane->residual.planes : nullptr, &S.lane->scratch.planes,
-                                      (const VVCB200IntraBlock *)S.iblocks.p, n, params, S.lane->intra_marks.p, S.lane->stream))
+                                      (const VVCB200IntraBlock *)S.iblocks.p, n, &phased, S.lane->intra_marks.p, S.lane->stream))
         return r;
     return set_consumed(c);
 }
@@ -653,13 +728,15 @@ int vvcb200_pic_lmcs(VVCB200Ctx *c, const uint16_t *inv_lut)
     }
     DeviceGuard g(c->device);
     StageSet &S = c->sets[c->set];
+    if (c->lmcs_pending)                  // a second mapping of the same picture: run the first one now
+        if (int r = settle_picture(c))
+            return r;
     if (int r = upload(c, S.lut_inv, inv_lut, sizeof(uint16_t) << c->bit_depth))
         return r;
-    if (int r = uploads_visible(c))
-        return r;
-    if (int r = vvcb200_lmcs_picture(&c->dpb[c->cur].planes, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.lane->stream))
-        return r;
-    return set_consumed(c);
+    // The mapping is pointwise on luma: it is applied by the deblocking pass while it loads its tiles
+    // (vvcb200_deblock_lmcs_picture), or by settle_picture() if no deblocking call follows for this picture.
+    c->lmcs_pending = true;
+    return 0;
 }
 
 int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB200DeblockParams *params)
@@ -683,6 +760,8 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
         return r;
     uint8_t *d = (uint8_t *)S.db_tables.p;
     VVCB200DeblockTables dt = *t;
+    // ten copies: the host tables are separate allocations (a copy may not span two pinned allocations even when they
+    // happen to be adjacent)
     for (int dir = 0; dir < 2; dir++)
         for (int k = 0; k < 3; k++) {
             if (!t->d_edge[dir][k]) {
@@ -706,8 +785,14 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
     dt.d_ctb_offsets = (const int8_t *)d;
     if (int r = uploads_visible(c))
         return r;
-    if (int r = vvcb200_deblock_picture(&c->dpb[c->cur].planes, &dt, params, S.lane->stream))
+    if (c->in_scratch)                    // a second deblocking call for this picture: start from its DPB buffer again
+        if (int r = settle_picture(c))
+            return r;
+    const uint16_t *lut = c->lmcs_pending ? (const uint16_t *)S.lut_inv.p : nullptr;
+    if (int r = vvcb200_deblock_lmcs_picture(&S.lane->scratch.planes, &c->dpb[c->cur].planes, &dt, params, lut, S.lane->stream))
         return r;
+    c->lmcs_pending = false;
+    c->in_scratch = true;
     return set_consumed(c);
 }
 
@@ -718,44 +803,42 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
         set_error("vvcb200_pic_sao_alf: bad argument");
         return VVCB200_ERR_ARG;
     }
+    if (!sao && !alf)
+        return 0;
     DeviceGuard g(c->device);
     StageSet &S = c->sets[c->set];
     const int sh = ctb_log2_size;
     const size_t n_ctb = (size_t)((c->width + (1 << sh) - 1) >> sh) * ((c->height + (1 << sh) - 1) >> sh);
-    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &S.lane->scratch.planes;
-    if (sao) {
+    if (sao)
         if (int r = upload(c, S.sao, sao, n_ctb * sizeof(*sao)))
             return r;
-        if (int r = uploads_visible(c))
-            return r;
-        if (int r = vvcb200_sao_picture(tmp, cur, (const VVCB200SaoCtb *)S.sao.p, ctb_log2_size, c->bit_depth, S.lane->stream))
-            return r;
-    }
     if (alf) {
         if (int r = upload(c, S.alf, alf, n_ctb * sizeof(*alf)))
             return r;
         if (int r = upload(c, S.alf_params, alf_params, sizeof(*alf_params)))
             return r;
-        if (!sao) {
-            // ALF reads `tmp`: without SAO the source is the current picture itself
-            const size_t bytes = (size_t)cur->stride[0] * cur->height[0] + 2 * (size_t)cur->stride[1] * cur->height[1];
-            VVC_CUDA(cudaMemcpyAsync(S.lane->scratch.base, c->dpb[c->cur].base, bytes, cudaMemcpyDeviceToDevice, S.lane->stream));
-        }
-        if (int r = uploads_visible(c))
-            return r;
-        if (int r = vvcb200_alf_picture(cur, tmp, (const VVCB200AlfCtb *)S.alf.p, (const VVCB200AlfParams *)S.alf_params.p,
-                                        ctb_log2_size, c->bit_depth, S.lane->stream))
-            return r;
-        return set_consumed(c);
     }
-    if (sao) {
-        // SAO only: its output becomes the picture (swap the buffers instead of copying back)
-        DevPicture t = c->dpb[c->cur];
-        c->dpb[c->cur] = S.lane->scratch;
-        S.lane->scratch = t;
-        return set_consumed(c);
+    if (int r = uploads_visible(c))
+        return r;
+    if (c->lmcs_pending) {                // no deblocking pass took the mapping along: run it where the picture is now
+        const bool keep = c->in_scratch;
+        c->in_scratch = false;            // (settle_picture must not move the picture)
+        VVCB200Planes *pl = keep ? &S.lane->scratch.planes : &c->dpb[c->cur].planes;
+        c->lmcs_pending = false;
+        if (int r = vvcb200_lmcs_picture(pl, (const uint16_t *)S.lut_inv.p, c->bit_depth, S.lane->stream))
+            return r;
+        c->in_scratch = keep;
     }
-    return 0;
+    // one fused pass from wherever the picture is into the other buffer
+    VVCB200Planes *cur = &c->dpb[c->cur].planes, *tmp = &S.lane->scratch.planes;
+    VVCB200Planes *src = c->in_scratch ? tmp : cur, *dst = c->in_scratch ? cur : tmp;
+    if (int r = vvcb200_sao_alf_picture(dst, src, sao ? (const VVCB200SaoCtb *)S.sao.p : nullptr,
+                                        alf ? (const VVCB200AlfCtb *)S.alf.p : nullptr,
+                                        alf ? (const VVCB200AlfParams *)S.alf_params.p : nullptr, ctb_log2_size, c->bit_depth,
+                                        S.lane->stream))
+        return r;
+    c->in_scratch = !c->in_scratch;
+    return set_consumed(c);
 }
 
 }  // extern "C"

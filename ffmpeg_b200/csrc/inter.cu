@@ -253,23 +253,41 @@ __device__ __forceinline__ bool dmvr_refine(const InterArgs &a, const VVCB200Int
             const int fy0 = VVC_DMVR_FILTERS[my * 2], fy1 = VVC_DMVR_FILTERS[my * 2 + 1];
             const int sh1 = bd - 6, of1 = 1 << (sh1 - 1);
             if (li < pw4) {
+                // a lane owns one column of the (w + 4) x (h + 4) bilinear block; its two source columns are read four
+                // rows at a time so that eight loads are in flight together (row by row, each row waited for the one
+                // before: 40 L2 round trips in a row made this search the longest thing a warp of the grid does)
                 const int sx0 = clip3(xi + li, 0, pw - 1), sx1 = clip3(xi + li + 1, 0, pw - 1);
-                for (int r = 0; r < ph4; r++) {
-                    const uint16_t *r0 = src + (size_t)clip3(yi + r, 0, ph - 1) * stride;
-                    const uint16_t *r1 = src + (size_t)clip3(yi + r + 1, 0, ph - 1) * stride;
-                    int v;
-                    if (!mx && !my)
-                        v = bd > 10 ? (r0[sx0] + (1 << (bd - 11))) >> (bd - 10) : r0[sx0] << (10 - bd);
-                    else if (!my)
-                        v = (fx0 * r0[sx0] + fx1 * r0[sx1] + of1) >> sh1;
-                    else if (!mx)
-                        v = (fy0 * r0[sx0] + fy1 * r1[sx0] + of1) >> sh1;
-                    else {
-                        const int t0 = (fx0 * r0[sx0] + fx1 * r0[sx1] + of1) >> sh1;
-                        const int t1 = (fx0 * r1[sx0] + fx1 * r1[sx1] + of1) >> sh1;
-                        v = (fy0 * t0 + fy1 * t1 + 8) >> 4;
+                const uint16_t *first = src + (size_t)clip3(yi, 0, ph - 1) * stride;
+                int top0 = __ldg(first + sx0), top1 = __ldg(first + sx1);
+                for (int rb = 0; rb < ph4; rb += 4) {
+                    int c0[4], c1[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        const uint16_t *rr = src + (size_t)clip3(yi + rb + k + 1, 0, ph - 1) * stride;
+                        c0[k] = __ldg(rr + sx0);
+                        c1[k] = __ldg(rr + sx1);
                     }
-                    pred[l][r * pw4 + li] = (int16_t)v;
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (rb + k < ph4) {
+                            const int a0 = k ? c0[k - 1] : top0, a1 = k ? c1[k - 1] : top1;     // row r: (sx0, sx1); row r + 1: c0, c1
+                            int v;
+                            if (!mx && !my)
+                                v = bd > 10 ? (a0 + (1 << (bd - 11))) >> (bd - 10) : a0 << (10 - bd);
+                            else if (!my)
+                                v = (fx0 * a0 + fx1 * a1 + of1) >> sh1;
+                            else if (!mx)
+                                v = (fy0 * a0 + fy1 * c0[k] + of1) >> sh1;
+                            else {
+                                const int t0 = (fx0 * a0 + fx1 * a1 + of1) >> sh1;
+                                const int t1 = (fx0 * c0[k] + fx1 * c1[k] + of1) >> sh1;
+                                v = (fy0 * t0 + fy1 * t1 + 8) >> 4;
+                            }
+                            pred[l][(rb + k) * pw4 + li] = (int16_t)v;
+                        }
+                    }
+                    top0 = c0[3];
+                    top1 = c1[3];
                 }
             }
         }

@@ -96,7 +96,11 @@ struct IntraArgs {
     int bd, ctb_log2, collocated;
     uint8_t *marks[3];            // pending marks per plane (in-place records only)
     int mpitch[3];
-    int *ticket;                  // ticket[0]: next record; ticket[1]: the picture has in-place records
+    int *ticket;                  // next record of this launch
+    int *inplace_flag;            // set by the pre-pass when the picture has in-place records that go by marks
+    int skip_first, skip_n;       // pre-pass: records left alone (the add-only phase of a phased picture)
+    unsigned *vpdu_scale;         // phased pictures: chroma residual scale per VPDU, 0 = not derived yet, else 0x10000 | scale
+    int vpdu_pitch;               // VPDUs per row of that table
     uint16_t lmcs_pivot[17], lmcs_coeff[16];
     int lmcs_min_bin, lmcs_max_bin;
 };
@@ -213,7 +217,7 @@ __global__ void intra_mark_kernel(IntraArgs a)
 {
     const int lane = threadIdx.x & (kMarkLanes - 1);
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) / kMarkLanes;
-    if (t >= a.n)
+    if (t >= a.n || (t >= a.skip_first && t < a.skip_first + a.skip_n))
         return;
     const VVCB200IntraBlock b = load_record(a.blocks + t);
     int w, h;
@@ -224,7 +228,7 @@ __global__ void intra_mark_kernel(IntraArgs a)
     if (keep && !a.shadow[b.c_idx]) {
         set_marks(a, b.c_idx, b.x0, b.y0, w, h, 1, lane, kMarkLanes);
         if (lane == 0)
-            a.ticket[1] = 1;
+            *a.inplace_flag = 1;
         return;
     }
     for (int c = b.c_idx; c <= (b.mode >= 81 ? 2 : b.c_idx); c++) {       // sentinel over everything the record will write
@@ -470,6 +474,16 @@ __device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b
     const int x = b.vpdu_x << ls, y = b.vpdu_y << ls;
     const bool al = b.vpdu_avail & 1, at = b.vpdu_avail & 2;
     const int rows = min(size, a.pic.h[0] - y), cols = min(size, a.pic.w[0] - x);
+    // Phased pictures (every luma sample is final by now): the factor of a VPDU is derived once and kept in a table; a
+    // second warp deriving it at the same time stores the same value.
+    unsigned *cached = a.vpdu_scale ? a.vpdu_scale + b.vpdu_y * a.vpdu_pitch + b.vpdu_x : nullptr;
+    if (cached) {
+        const unsigned v = __ldcg(cached);
+        if (v) {
+            scale = (int)(v & 0xffff);
+            return true;
+        }
+    }
     if (has_marks) {
         Span sp[2];
         if (!spans_ready(a, sp, vpdu_deps(b, a.ctb_log2, a.pic.w[0], a.pic.h[0], sp), lane, blocking))
@@ -508,6 +522,8 @@ __device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b
     while (i <= a.lmcs_max_bin && mean >= a.lmcs_pivot[i + 1])
         i++;
     scale = a.lmcs_coeff[min(i, 15)];
+    if (cached && lane == 0)
+        *cached = 0x10000u | (unsigned)scale;
     return true;
 }
 
@@ -515,6 +531,34 @@ __device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
 {
     const int c = clip_intp2(r, bd);
     return c > 0 ? (c * scale + (1 << 10)) >> 11 : -((-c * scale + (1 << 10)) >> 11);
+}
+
+// ---- the add-only phase of a phased picture ---------------------------------------------------------------------------
+// Chroma blocks of inter units whose residual waits for the luma-dependent scale (VVCB200_IB_ADD_ONLY): once every luma
+// sample of the picture is final they depend on nothing else, so they run as a plain batch — one warp per record —
+// between the luma wavefront and the chroma wavefront instead of as tickets of the latter.
+__global__ void __launch_bounds__(256) intra_add_only_kernel(IntraArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= a.n)
+        return;
+    const VVCB200IntraBlock b = load_record(a.blocks + t);
+    if (!(b.flags & VVCB200_IB_RESIDUAL))
+        return;
+    int lscale = 0;
+    vpdu_chroma_scale(a, b, false, lane, true, lscale);
+    const int c = b.c_idx, w = b.w, h = b.h, lw = ilog2(w);
+    uint16_t *dst = a.pic.p[c] + (size_t)b.y0 * a.pic.stride[c] + b.x0;
+    const int16_t *res = a.res[c] + (size_t)b.y0 * a.res_stride[c] + b.x0;
+    for (int idx = lane; idx < w * h; idx += 32) {
+        const int x = idx & (w - 1), y = idx >> lw;
+        int r = res[(size_t)y * a.res_stride[c] + x];
+        if (lscale)
+            r = scale_chroma_residual(r, lscale, a.bd);
+        uint16_t *d = dst + (size_t)y * a.pic.stride[c] + x;
+        *d = (uint16_t)clip_pixel((int)*d + r, a.bd);
+    }
 }
 
 // ---- one angular / planar / DC / MIP block --------------------------------------------------------------------------
@@ -1198,7 +1242,7 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
     if (threadIdx.x < 4)
         tb.mip_off[threadIdx.x] = VVC_MIP_OFF[threadIdx.x];
     __syncthreads();
-    const bool has_marks = kMarks && a.ticket[1] != 0;                    // written by the pre-pass
+    const bool has_marks = kMarks && *a.inplace_flag != 0;                 // written by the pre-pass
 
     // Each warp holds up to kSlots records drawn in ticket order.  With one slot it waits for that record's neighbours
     // (tight polling: the lowest latency along a dependency chain, which is what bounds the kernel).  With more slots it
@@ -1287,8 +1331,9 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
 }
 
 struct ScratchLayout {
-    size_t off[3], total;
-    int pitch[3];
+    size_t off[3], marks_total;   // ticket sector + marks
+    size_t vpdu_off, total;       // + the per-VPDU scale table of phased pictures
+    int pitch[3], vpdu_pitch;
 };
 
 ScratchLayout scratch_layout(int width, int height)
@@ -1303,7 +1348,11 @@ ScratchLayout scratch_layout(int width, int height)
         o += (size_t)l.pitch[c] * rows;
         o = (o + 255) & ~(size_t)255;
     }
-    l.total = o;
+    l.marks_total = o;
+    l.vpdu_off = o;
+    l.vpdu_pitch = (width + 31) >> 5;                                     // VPDUs are 64x64, or the CTB when that is 32x32
+    o += (size_t)l.vpdu_pitch * ((height + 31) >> 5) * sizeof(unsigned);
+    l.total = (o + 255) & ~(size_t)255;
     return l;
 }
 
@@ -1421,9 +1470,17 @@ int intra_scheduler_run(IntraScheduler *s, const VVCB200IntraBlock *in, const ui
 }
 }  // namespace vvcb200
 
+namespace vvcb200 {
+// phase of a record: 0 luma (and anything that is not a chroma add-only record), 1 chroma add-only, 2 other chroma
+static inline int intra_phase(const VVCB200IntraBlock &b)
+{
+    return !b.c_idx ? 0 : (b.flags & VVCB200_IB_ADD_ONLY) ? 1 : 2;
+}
+}  // namespace vvcb200
+
 extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
                                       int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
-                                      int32_t *n_levels)
+                                      int32_t *n_levels, int32_t *phase_counts)
 {
     if (!in || !ctu_first || !out || ctus_w <= 0 || ctus_h <= 0 || ctb_log2_size < 5 || ctb_log2_size > 7 ||
         width <= 0 || height <= 0 || width > (ctus_w << ctb_log2_size) || height > (ctus_h << ctb_log2_size) ||
@@ -1434,7 +1491,17 @@ extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_
     if (order == VVCB200_INTRA_ORDER_DIAGONAL) {
         // CTU anti-diagonals x + 2y (the above-right CTU comes first, vvc_thread.c:161), the CTUs of a diagonal dealt
         // round-robin so that a window of consecutive tickets spans every CTU that can run now.  O(n).
-        size_t o = 0;
+        size_t cursor[3] = { 0, 0, 0 };                                   // where the next record of each phase goes
+        if (phase_counts) {
+            const uint32_t n = ctu_first[ctus_w * ctus_h];
+            size_t cnt[3] = { 0, 0, 0 };
+            for (uint32_t i = 0; i < n; i++)
+                cnt[intra_phase(in[i])]++;
+            cursor[1] = cnt[0];
+            cursor[2] = cnt[0] + cnt[1];
+            phase_counts[0] = (int32_t)cnt[0];
+            phase_counts[1] = (int32_t)cnt[1];
+        }
         for (int d = 0; d <= ctus_w - 1 + 2 * (ctus_h - 1); d++) {
             const int y_lo = d - (ctus_w - 1) > 0 ? (d - (ctus_w - 1) + 1) / 2 : 0;
             const int y_hi = d / 2 < ctus_h - 1 ? d / 2 : ctus_h - 1;
@@ -1447,8 +1514,10 @@ extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_
             for (uint32_t k = 0; k < longest; k++)
                 for (int y = y_lo; y <= y_hi; y++) {
                     const int rs = y * ctus_w + d - 2 * y;
-                    if (ctu_first[rs] + k < ctu_first[rs + 1])
-                        out[o++] = in[ctu_first[rs] + k];
+                    if (ctu_first[rs] + k < ctu_first[rs + 1]) {
+                        const VVCB200IntraBlock &b = in[ctu_first[rs] + k];
+                        out[cursor[phase_counts ? intra_phase(b) : 0]++] = b;
+                    }
                 }
         }
         if (n_levels)
@@ -1460,6 +1529,19 @@ extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_
     if (r) {
         set_error("vvcb200_intra_schedule: record %d lies outside the picture or the dependency chain is too long", -r - 1);
         return VVCB200_ERR_ARG;
+    }
+    if (phase_counts) {                                                   // stable partition of the depth order
+        static thread_local std::vector<VVCB200IntraBlock> tmp;
+        const uint32_t n = ctu_first[ctus_w * ctus_h];
+        tmp.assign(out, out + n);
+        size_t cnt[3] = { 0, 0, 0 };
+        for (uint32_t i = 0; i < n; i++)
+            cnt[intra_phase(tmp[i])]++;
+        size_t cursor[3] = { 0, cnt[0], cnt[0] + cnt[1] };
+        for (uint32_t i = 0; i < n; i++)
+            out[cursor[intra_phase(tmp[i])]++] = tmp[i];
+        phase_counts[0] = (int32_t)cnt[0];
+        phase_counts[1] = (int32_t)cnt[1];
     }
     return 0;
 }
@@ -1509,13 +1591,33 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     a.lmcs_max_bin = params->lmcs_max_bin_idx < 15 ? params->lmcs_max_bin_idx : 15;
     const ScratchLayout l = scratch_layout(pic->width[0], pic->height[0]);
     a.ticket = (int *)d_scratch;
+    a.inplace_flag = (int *)d_scratch + 1;
     for (int c = 0; c < 3; c++) {
         a.marks[c] = (uint8_t *)d_scratch + l.off[c];
         a.mpitch[c] = l.pitch[c];
     }
+    // phases: luma wavefront, chroma add-only batch, chroma wavefront (see VVCB200IntraParams)
+    const int n_luma = params->n_luma, n_add = params->n_add_only;
+    const bool phased = n_luma > 0 || n_add > 0;
+    if (n_luma < 0 || n_add < 0 || (long long)n_luma + n_add > n) {
+        set_error("vvcb200_intra_picture: n_luma %d + n_add_only %d exceed the %d records", n_luma, n_add, n);
+        return VVCB200_ERR_ARG;
+    }
+    if (phased && n_add && !d_residual) {
+        set_error("vvcb200_intra_picture: add-only records need the residual planes");
+        return VVCB200_ERR_ARG;
+    }
+    a.skip_first = n_luma;
+    a.skip_n = phased ? n_add : 0;
+    a.vpdu_scale = nullptr;
+    a.vpdu_pitch = l.vpdu_pitch;
     cudaStream_t s = (cudaStream_t)stream;
-    // ticket counter and in-place flag; the marks too unless a shadow picture makes them unnecessary
-    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.total, s));
+    // ticket counters and in-place flag; the marks too unless a shadow picture makes them unnecessary
+    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.marks_total, s));
+    if (phased && params->lmcs_chroma_scale) {
+        a.vpdu_scale = (unsigned *)((uint8_t *)d_scratch + l.vpdu_off);
+        VVC_CUDA(cudaMemsetAsync(a.vpdu_scale, 0, l.total - l.vpdu_off, s));
+    }
     intra_mark_kernel<<<(n + 128 / kMarkLanes - 1) / (128 / kMarkLanes), 128, 0, s>>>(a);
     VVC_LAUNCH_CHECK();
     // Pictures with scattered intra units are bound by the number of records in flight and take every warp the SM holds;
@@ -1539,17 +1641,41 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         VVC_CUDA(cudaFuncSetAttribute(intra_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set[dev] = true;
     }
-    const bool marks = !d_shadow, scale = params->lmcs_chroma_scale != 0;
-    if (marks && scale)
-        intra_kernel<true, true><<<ctas, kWarps * 32, smem, s>>>(a);
-    else if (marks)
-        intra_kernel<true, false><<<ctas, kWarps * 32, smem, s>>>(a);
-    else if (scale)
-        intra_kernel<false, true><<<ctas, kWarps * 32, smem, s>>>(a);
-    else
-        intra_kernel<false, false><<<ctas, kWarps * 32, smem, s>>>(a);
-    VVC_LAUNCH_CHECK();
-    return 0;
+    const bool marks = !d_shadow;
+    const VVCB200IntraBlock *all = d_blocks;
+    // one wavefront launch over records [first, first + count) with its own ticket counter
+    auto wavefront = [&](int first, int count, int ticket_idx, bool scale) -> int {
+        if (count <= 0)
+            return 0;
+        IntraArgs w = a;
+        w.blocks = all + first;
+        w.n = count;
+        w.ticket = (int *)d_scratch + ticket_idx;
+        const int grid = min(ctas, (count + kWarps - 1) / kWarps);
+        if (marks && scale)
+            intra_kernel<true, true><<<grid, kWarps * 32, smem, s>>>(w);
+        else if (marks)
+            intra_kernel<true, false><<<grid, kWarps * 32, smem, s>>>(w);
+        else if (scale)
+            intra_kernel<false, true><<<grid, kWarps * 32, smem, s>>>(w);
+        else
+            intra_kernel<false, false><<<grid, kWarps * 32, smem, s>>>(w);
+        VVC_LAUNCH_CHECK();
+        return 0;
+    };
+    const bool scale = params->lmcs_chroma_scale != 0;
+    if (!phased)
+        return wavefront(0, n, 0, scale);
+    if (int r = wavefront(0, n_luma, 0, false))                           // luma records never carry the chroma scale
+        return r;
+    if (n_add) {
+        IntraArgs w = a;
+        w.blocks = all + n_luma;
+        w.n = n_add;
+        intra_add_only_kernel<<<(n_add + 7) / 8, 256, 0, s>>>(w);
+        VVC_LAUNCH_CHECK();
+    }
+    return wavefront(n_luma + n_add, n - n_luma - n_add, 2, scale);
 }
 
 // ---- the same reconstruction with the scratch living in the module image instead of caller memory ---------------
@@ -1583,7 +1709,7 @@ extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB
     }
     if (!n)
         return 0;
-    const size_t need = vvcb200_intra_scratch_bytes(pic->width[0], pic->height[0]);
+    const size_t need = pic->width[0] > 0 && pic->height[0] > 0 ? scratch_layout(pic->width[0], pic->height[0]).marks_total : 0;
     if (!need || need > kStaticScratchBytes) {
         set_error("vvcb200_intra_picture_static: a %dx%d picture needs %zu bytes of marks, the built-in scratch holds %zu "
                   "(pictures up to 1920x1088); use vvcb200_intra_picture with caller memory",
@@ -1606,9 +1732,11 @@ extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB
         }
         ptr = g_intra_scratch_ptr[dev];
     }
-    // the marks have to read zero when the mark kernel starts; an earlier call that failed half-way may have left some
-    VVC_CUDA(cudaMemsetAsync(ptr, 0, need, (cudaStream_t)stream));
-    return vvcb200_intra_picture(pic, d_residual, nullptr, d_blocks, n, params, ptr, stream);
+    // One wavefront over all records (the per-VPDU table of the phased form would not fit the array); the callee clears the
+    // ticket sector and the marks, which an earlier call may have left set.
+    VVCB200IntraParams one = *params;
+    one.n_luma = one.n_add_only = 0;
+    return vvcb200_intra_picture(pic, d_residual, nullptr, d_blocks, n, &one, ptr, stream);
 }
 
 #ifdef VVC_INTRA_PROFILE

@@ -1,5 +1,7 @@
 // runtime.cu — error reporting, launch accounting and device queries behind the C ABI.
 #include <atomic>
+#include <mutex>
+#include <new>
 #include <stdarg.h>
 #include <string.h>
 #include "common.cuh"
@@ -40,39 +42,69 @@ int sm_count()
     return cached[dev];
 }
 
+namespace {
+struct ForkEntry { int dev; cudaStream_t main; ForkStreams f; };
+std::mutex g_fork_mutex;
+ForkEntry *g_fork_pool[64];
+int g_fork_used = 0;
+
+void destroy_fork(ForkStreams &f)
+{
+    for (int i = 0; i < 4; i++) {
+        if (f.side[i]) cudaStreamDestroy(f.side[i]);
+        if (f.join[i]) cudaEventDestroy(f.join[i]);
+    }
+    if (f.fork) cudaEventDestroy(f.fork);
+    f = ForkStreams();
+}
+}  // namespace
+
 ForkStreams *fork_streams(cudaStream_t main_stream)
 {
-    // one set per calling stream: helper streams shared between two pictures' streams would order them behind each other
-    struct Entry { int dev; cudaStream_t main; ForkStreams f; };
-    static thread_local Entry pool[16];
-    static thread_local int used = 0;
+    // one set per device and calling stream: helper streams shared between two pictures' streams would order them behind
+    // each other, and a stream or event of one device cannot serve a launch on another
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess)
         return nullptr;
-    for (int i = 0; i < used; i++)
-        if (pool[i].dev == dev && pool[i].main == main_stream)
-            return &pool[i].f;
-    if (used == 16) {                               // all sets taken: hand an old one over (its streams serve any caller)
-        static thread_local int next = 0;
-        Entry &e = pool[next++ & 15];
-        e.dev = dev;
-        e.main = main_stream;
-        return &e.f;
-    }
-    Entry &e = pool[used];
-    ForkStreams f;
+    std::lock_guard<std::mutex> lock(g_fork_mutex);
+    for (int i = 0; i < g_fork_used; i++)
+        if (g_fork_pool[i]->dev == dev && g_fork_pool[i]->main == main_stream)
+            return &g_fork_pool[i]->f;
+    if (g_fork_used == 64)
+        return nullptr;
+    ForkEntry *e = new (std::nothrow) ForkEntry;
+    if (!e)
+        return nullptr;
+    ForkStreams &f = e->f;
     bool good = cudaEventCreateWithFlags(&f.fork, cudaEventDisableTiming) == cudaSuccess;
     for (int i = 0; i < 4 && good; i++)
         good = cudaStreamCreateWithFlags(&f.side[i], cudaStreamNonBlocking) == cudaSuccess &&
                cudaEventCreateWithFlags(&f.join[i], cudaEventDisableTiming) == cudaSuccess;
-    if (!good)
+    if (!good) {
+        destroy_fork(f);
+        delete e;
         return nullptr;
+    }
     f.ok = true;
-    e.dev = dev;
-    e.main = main_stream;
-    e.f = f;
-    used++;
-    return &e.f;
+    e->dev = dev;
+    e->main = main_stream;
+    g_fork_pool[g_fork_used++] = e;
+    return &e->f;
+}
+
+void fork_streams_release(cudaStream_t main_stream)
+{
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess)
+        return;
+    std::lock_guard<std::mutex> lock(g_fork_mutex);
+    for (int i = 0; i < g_fork_used; i++)
+        if (g_fork_pool[i]->dev == dev && g_fork_pool[i]->main == main_stream) {
+            destroy_fork(g_fork_pool[i]->f);
+            delete g_fork_pool[i];
+            g_fork_pool[i] = g_fork_pool[--g_fork_used];
+            return;
+        }
 }
 
 }  // namespace vvcb200

@@ -202,7 +202,7 @@ __device__ __forceinline__ uint4 sao_chunk(const SaoAlfArgs &a, const PlaneWin &
     return make_uint4(out[0], out[1], out[2], out[3]);
 }
 
-__global__ void __launch_bounds__(256) sao_alf_kernel(const SaoAlfArgs A)
+__global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
 {
     __shared__ __align__(16) uint16_t s_sao_y[kFYSR * kFYS];              // SAO'd luma, rows Y0-3 .., columns X0-8 ..
     __shared__ __align__(16) uint16_t s_sao_c[2][kFCSR * kFCS];           // SAO'd chroma, rows y0c-2 .., columns x0c-8 ..

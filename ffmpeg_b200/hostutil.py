@@ -61,6 +61,8 @@ class EnginePicture:
         # pictures are reconstructed into the slots after the references (ref_slot[][] already maps to 0..n_refs-1),
         # rotating over up to four slots / host frames when the context has them, as consecutive pictures of a decoder
         # do: the download of one picture then overlaps the reconstruction of the next ones (two compute lanes)
+        # DMVR feedback: the vectors actually used come back every picture (the host needs them for later MV prediction)
+        self.refined = [ctx.pinned((max(len(it["blocks"]), 1), 2, 2), np.int32) for _ in range(4)]
         self.n_slots = max(1, min(4, ctx.dpb_size - self.n_refs))
         self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
         self.count = 0
@@ -72,20 +74,28 @@ class EnginePicture:
         return intra + int(self.blocks.nbytes + self.levels.nbytes + self.tbs.nbytes + self.edge.nbytes + self.qp.nbytes +
                    self.ctb_offsets.nbytes + self.sao.nbytes + self.alf.nbytes + self.alf_params.nbytes)
 
-    def d2h_bytes(self):
+    def picture_bytes(self):
         return int(sum(p.nbytes for p in self.out))
+
+    def d2h_bytes(self):
+        return self.picture_bytes() + (int(self.refined[0].nbytes) if len(self.blocks) else 0)
 
     def upload_refs(self):
         for i, r in enumerate(self.refs):
             self.ctx.upload(r, slot=i)
 
-    def run(self, download=True):
+    def run(self, download=True, only_download=False):
         ctx, pic = self.ctx, self.pic
         k = self.count % self.n_slots
         self.count += 1
         self.out = self.outs[k]
+        if only_download:                  # the copy of a finished picture alone (what bench.py times as the D2H leg)
+            ctx.download(self.out, slot=self.n_refs + k)
+            return
         ctx.begin(self.n_refs + k)
-        ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0], prof=self.prof)
+        if len(self.blocks):
+            ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0],
+                      refined_mv=self.refined[self.count % 4], prof=self.prof)
         ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
         if self.intra is not None:
             ctx.intra(*self.intra)

@@ -97,16 +97,30 @@ def intra_scratch_bytes(width, height):
 INTRA_ORDER_DIAGONAL, INTRA_ORDER_DEPTH = 0, 1
 
 
-def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, want_levels=False, order=INTRA_ORDER_DEPTH):
-    """vvcb200_intra_schedule: per-CTU decoding-order records -> wavefront / dependency-depth order (host helper)."""
+def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, want_levels=False, order=INTRA_ORDER_DEPTH,
+                   phases=False):
+    """vvcb200_intra_schedule: per-CTU decoding-order records -> wavefront / dependency-depth order (host helper).
+    phases=True: the records come back grouped luma / chroma add-only / other chroma, with (n_luma, n_add_only) as the
+    last element of the result (what VVCB200IntraParams.n_luma / n_add_only want)."""
     blocks = np.ascontiguousarray(blocks, abi.IB_DTYPE)
     ctu_first = np.ascontiguousarray(ctu_first, np.uint32)
     assert len(ctu_first) == ctus_w * ctus_h + 1 and ctu_first[-1] == len(blocks)
     out = np.zeros(len(blocks), abi.IB_DTYPE)
     levels = C.c_int32(0)
+    counts = (C.c_int32 * 2)(0, 0)
     check(load().vvcb200_intra_schedule(_ptr(blocks), _ptr(ctu_first), int(ctus_w), int(ctus_h), int(ctb_log2), int(width),
-                                        int(height), int(order), _ptr(out), C.byref(levels)))
-    return (out, int(levels.value)) if want_levels else out
+                                        int(height), int(order), _ptr(out), C.byref(levels), counts if phases else None))
+    res = (out, int(levels.value)) if want_levels else (out,)
+    if phases:
+        res = res + ((int(counts[0]), int(counts[1])),)
+    return res if len(res) > 1 else res[0]
+
+
+def phased_params(params, counts):
+    """Copy of an IntraParams with the phase counts of intra_schedule(..., phases=True)."""
+    p = abi.IntraParams.from_buffer_copy(bytes(params))
+    p.n_luma, p.n_add_only = counts
+    return p
 
 
 def intra_picture(pic, residual, blocks, n, params, scratch, stream=None, shadow=None):

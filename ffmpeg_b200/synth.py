@@ -252,6 +252,7 @@ def _decorate_blocks(rng, b, tools, n_refs, mv_range=64 * 16, far_mv=0.02, keep_
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
     params = abi.inter_params(bd, ld, weight, offset, ref_slot)
+    params.num_ref_idx_active[0] = params.num_ref_idx_active[1] = n_refs
     return abi.order_blocks_by_width(b, params), params
 
 
@@ -611,6 +612,7 @@ def inter_cu_picture(seed, width, height, n_refs=2, kinds=(CU_REGULAR, CU_AFFINE
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.stack([rng.permutation(n_refs), rng.permutation(n_refs)])
     params = abi.inter_params(10, ld, weight, offset, ref_slot)
+    params.num_ref_idx_active[0] = params.num_ref_idx_active[1] = n_refs
     blocks = abi.order_blocks_by_width(np.concatenate(blocks), params)
     dims = plane_dims(width, height)
     refs = [smooth_planes(seed * 31 + i, dims) for i in range(n_refs)]
@@ -1017,6 +1019,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
     ref_slot = np.zeros((2, 16), np.uint8)
     ref_slot[:, :n_refs] = np.arange(n_refs)
     iparams = abi.inter_params(bd, ld, None, None, ref_slot)
+    iparams.num_ref_idx_active[0] = iparams.num_ref_idx_active[1] = n_refs
     if pblocks and inter_tools is not None:     # the tool mix of inter_picture() on this picture's inter CUs
         pb, iparams = _decorate_blocks(np.random.default_rng(seed + 77), np.concatenate(pblocks), set(inter_tools), n_refs,
                                        keep_mv=True, bd=bd)

@@ -195,7 +195,9 @@ typedef struct VVCB200InterParams {
     int32_t  log2_denom[2];         /* luma, chroma                                            */
     int32_t  n_w16, n_w8;           /* the batch is ordered by block width: n_w16 blocks of width 16, then n_w8 of
                                        width 8, then the width-4 ones (lets a warp own equal-width blocks)      */
-    int32_t  reserved[3];
+    int32_t  num_ref_idx_active[2]; /* entries of ref_slot[list][] in use (RefPicList.nb_refs, vvcdec.h:45-50); 0 = not
+                                       stated: Level B then treats all 16 as pictures this one reads                 */
+    int32_t  reserved;
     int16_t  weight[2][3][16];      /* [list][c_idx][ref_idx]                                  */
     int16_t  offset[2][3][16];
     uint8_t  ref_slot[2][16];       /* index into the `refs` array of (list, ref_idx)          */
@@ -403,7 +405,13 @@ typedef struct VVCB200IntraParams {
     uint16_t lmcs_chroma_scale_coeff[16];
     uint8_t  lmcs_min_bin_idx, lmcs_max_bin_idx;
     uint8_t  pad[4];
-} VVCB200IntraParams;           /* 88 bytes */
+    /* Phases (vvcb200_intra_schedule with `phase_counts`): records [0, n_luma) are the luma records, the next n_add_only
+     * the chroma VVCB200_IB_ADD_ONLY records, the rest the other chroma records.  Chroma never feeds luma, and an add-only
+     * record depends on luma alone, so the three groups run as luma wavefront -> plain batch -> chroma wavefront: the
+     * add-only records (most records of a random-access picture with chroma residual scaling) stop being tickets of a
+     * latency-bound wavefront.  Both 0: one wavefront over all records in array order. */
+    int32_t  n_luma, n_add_only;
+} VVCB200IntraParams;           /* 96 bytes */
 
 /*
  * Reconstruction of the intra blocks of one picture, in place on `pic` (which already holds the inter prediction +
@@ -441,10 +449,12 @@ enum {
 /* Host helper: `in` holds the records of CTU i (raster index) at ctu_first[i] .. ctu_first[i + 1], in decoding order;
  * `out` (same length, must not alias) receives them in the requested order.  width / height: luma samples.
  * n_levels (may be NULL; VVCB200_INTRA_ORDER_DEPTH only): the length of the longest dependency chain, i.e. the number
- * of serial steps of the picture. */
+ * of serial steps of the picture.
+ * phase_counts (may be NULL): when given, `out` is additionally grouped into the three phases of
+ * VVCB200IntraParams.n_luma / n_add_only (each group keeps the requested order) and receives those two counts. */
 VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
                                        int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
-                                       int32_t *n_levels);
+                                       int32_t *n_levels, int32_t *phase_counts);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
                                       const VVCB200Planes *d_shadow, const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);

@@ -9,7 +9,7 @@ from tests import util
 pytestmark = pytest.mark.gpu
 
 
-def run_gpu(pic, schedule=True, repeat=1, shadow=False):
+def run_gpu(pic, schedule=True, repeat=1, shadow=False, phased=False):
     """INTER -> RESIDUAL -> INTRA on the device, Level A calls only.  shadow: hand the call a second picture, so that
     blocks rewritten in place take the sentinel protocol too (else they go by marks and fences)."""
     import torch
@@ -32,7 +32,13 @@ def run_gpu(pic, schedule=True, repeat=1, shadow=False):
         lib.residual_batch(dpl, levels, tbs, len(rs["tbs"]), rs["params"], residual=rpl)
     w, h, ctb = pic["width"], pic["height"], pic["ctb_log2"]
     recs = ia["blocks"]
-    if schedule:
+    iparams = ia["params"]
+    if phased:          # luma wavefront -> add-only batch -> chroma wavefront (what Level B runs)
+        recs, counts = lib.intra_schedule(recs, ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb, ctb, w, h,
+                                          order=lib.INTRA_ORDER_DIAGONAL if phased == "diagonal" else lib.INTRA_ORDER_DEPTH,
+                                          phases=True)
+        iparams = lib.phased_params(ia["params"], counts)
+    elif schedule:
         recs = lib.intra_schedule(recs, ia["ctu_first"], (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb, ctb, w, h)
     scratch = torch.zeros(lib.intra_scratch_bytes(w, h), dtype=torch.uint8, device="cuda")
     side = [torch.full_like(t, 0x1234) for t in dev] if shadow else None
@@ -44,12 +50,15 @@ def run_gpu(pic, schedule=True, repeat=1, shadow=False):
         for _ in range(repeat):
             for t, b in zip(dev, base):
                 t.copy_(b)
-            lib.intra_picture(dpl, rpl, d_recs, len(recs), ia["params"], scratch, shadow=spl)
+            lib.intra_picture(dpl, rpl, d_recs, len(recs), iparams, scratch, shadow=spl)
             torch.cuda.synchronize()
             out.append(util.from_device_planes(dev))
-        assert int((scratch[256:] == 1).sum()) == 0, "no unit may be left pending after the call"
+        # the per-VPDU table of phased pictures follows the marks (each area a multiple of 256 bytes)
+        marks_end = (lib.intra_scratch_bytes(w, h) - 4 * ((w + 31) // 32) * ((h + 31) // 32)) // 256 * 256
+        marks = scratch[256:marks_end]
+        assert int((marks == 1).sum()) == 0, "no unit may be left pending after the call"
         if shadow:
-            assert int((scratch[256:] != 0).sum()) == 0, "with a shadow picture nothing goes by marks"
+            assert int((marks != 0).sum()) == 0, "with a shadow picture nothing goes by marks"
     else:
         out.append(util.from_device_planes(dev))
     return out
@@ -120,6 +129,21 @@ def test_chroma_scaling_and_ciip_under_both_protocols(seed, w, h, ctb, frac):
         got = run_gpu(pic, shadow=shadow)[0]
         for c in range(3):
             assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d, shadow %d)" % (c, seed, shadow)
+    for shadow, phased in ((False, "diagonal"), (True, "diagonal"), (True, "depth")):
+        got = run_gpu(pic, shadow=shadow, phased=phased, repeat=2)
+        for g in got:
+            for c in range(3):
+                assert np.array_equal(g[c], want[c]), "phased: plane %d differs (seed %d, shadow %d)" % (c, seed, shadow)
+
+
+@pytest.mark.parametrize("seed,w,h,ctb,tools,frac", [CASES[8], CASES[9], CASES[10]])
+def test_phased_intra_matches_oracle(seed, w, h, ctb, tools, frac):
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=tools, intra_fraction=frac)
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    for shadow in (False, True):
+        got = run_gpu(pic, shadow=shadow, phased="diagonal")[0]
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d, shadow %d)" % (c, seed, shadow)
 
 
 def test_all_intra_1080p_property():
@@ -129,6 +153,7 @@ def test_all_intra_1080p_property():
     b = run_gpu(pic, schedule=True)[0]
     assert util.plane_md5(a) == util.plane_md5(b)
     assert util.plane_md5(run_gpu(pic, shadow=True)[0]) == util.plane_md5(a)
+    assert util.plane_md5(run_gpu(pic, shadow=True, phased="diagonal")[0]) == util.plane_md5(a)
 
 
 def test_empty_picture_is_a_noop():

@@ -76,6 +76,34 @@ def test_schedule_is_a_topological_permutation(seed, w, h, ctb, order):
         assert first_row1 < last_row0
 
 
+@pytest.mark.parametrize("order", [lib.INTRA_ORDER_DIAGONAL, lib.INTRA_ORDER_DEPTH])
+def test_phased_schedule_groups_the_records_and_stays_topological(order):
+    """phase_counts: luma records, then chroma add-only records, then the other chroma records, each group in the
+    requested order; read front to back the array is still an order the port reconstructs identically from."""
+    pic = synth.full_picture(5, 256, 192, ctb_log2=6, lmcs=True, intra_fraction=0.3)
+    ia = pic["intra"]
+    w, h, ctb = 256, 192, 6
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    plain = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h, order=order)
+    recs, (n_luma, n_add) = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h, order=order, phases=True)
+    add_only = (recs["flags"] & abi.IB_ADD_ONLY) != 0
+    assert n_add > 0 and (recs["c_idx"][:n_luma] == 0).all()
+    assert add_only[n_luma:n_luma + n_add].all() and (recs["c_idx"][n_luma:] > 0).all() and not add_only[n_luma + n_add:].any()
+    phase = np.where(plain["c_idx"] == 0, 0, np.where((plain["flags"] & abi.IB_ADD_ONLY) != 0, 1, 2))
+    assert recs.tobytes() == np.concatenate([plain[phase == k] for k in range(3)]).tobytes()      # a stable partition
+    from oracle import portapi
+    def port(order_recs):
+        planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+        util.oracle_inter(planes, pic["inter"], pic["lmcs"][0], False)
+        res = [np.zeros(p.shape, np.int16) for p in planes]
+        portapi.residual_batch(planes, pic["residual"]["levels"], pic["residual"]["tbs"], pic["residual"]["params"], residual_planes=res)
+        portapi.intra_picture(planes, res, order_recs, ia["params"])
+        return planes
+    a, b = port(ia["blocks"]), port(recs)
+    for c in range(3):
+        assert np.array_equal(a[c], b[c])
+
+
 @pytest.mark.skipif(not refapi.available(), reason="oracle/_ref not built")
 @pytest.mark.parametrize("seed,w,h,ctb", [(61, 208, 120, 6), (62, 136, 72, 5), (63, 256, 192, 7)])
 def test_port_matches_reference_on_dual_tree_pictures(seed, w, h, ctb):
