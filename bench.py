@@ -488,6 +488,7 @@ def main():
         s["off"] = torch.from_numpy(db["ctb_offsets"]).cuda()
         s["db"] = lib.deblock_tables(s["edge"], s["qp"], s["off"], db["stride4"])
         s["sao"], s["alf"], s["alfp"] = dev(lf["sao"]), dev(lf["alf"]), dev(lf["alf_params"])
+        s["alf_table"] = torch.zeros(lib.sao_alf_scratch_bytes(), dtype=torch.uint8, device="cuda")
         s["fwd"] = dev(fwd) if fwd is not None else None
         s["inv"] = dev(inv) if inv is not None else None
         sets.append(s)
@@ -512,7 +513,7 @@ def main():
         lib.deblock_lmcs_picture(s["tmp_p"], s["cur_p"], s["db"], db["params"], s["inv"], stream=q)
         if ev is not None:
             ev[4].record()
-        lib.sao_alf_picture(s["cur_p"], s["tmp_p"], s["sao"], s["alf"], s["alfp"], pic["ctb_log2"], stream=q)
+        lib.sao_alf_picture(s["cur_p"], s["tmp_p"], s["sao"], s["alf"], s["alfp"], pic["ctb_log2"], scratch=s["alf_table"], stream=q)
         if ev is not None:
             ev[5].record()
 

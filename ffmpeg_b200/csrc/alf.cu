@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256, VVC_ALF_LUMA_MIN_BLOCKS) alf_luma_kernel(
         }
     }
     __syncthreads();
-    alf_luma_filter_tile(a, cp, g, tx0, ty0, S);
+    alf_luma_filter_tile<false>(a, cp, g, tx0, ty0, S);
 }
 
 // chroma ALF (5x5) + CC-ALF; grid.z selects Cb / Cr
@@ -131,6 +131,7 @@ extern "C" int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes
     a.ctb_log2 = ctb_log2_size;
     a.ctb_width = (src->width[0] + (1 << ctb_log2_size) - 1) >> ctb_log2_size;
     a.bd = bit_depth;
+    a.table = nullptr;
     if ((a.dst.stride[0] & 3) || ((uintptr_t)a.dst.p[0] & 7) || (a.src.stride[0] & 1) || ((uintptr_t)a.src.p[0] & 3)) {
         set_error("vvcb200_alf_picture: luma planes must be 8-byte aligned with strides that are multiples of 8 bytes");
         return VVCB200_ERR_ARG;

@@ -23,7 +23,47 @@ struct AlfArgs {
     const VVCB200AlfCtb *ctbs;
     const VVCB200AlfParams *params;
     int ctb_log2, ctb_width, bd;
+    const uint32_t *table;       // alf_coef_table_kernel's output (kTable instantiations), or nullptr
 };
+
+// Luma coefficients and clip values for every (filter set, class, transposition), derived once per picture instead of once
+// per 4x4 block (alf_recon_coeff_and_clip, vvc_filter_template.c:365-408): word [32 + ((set * 25 + cls) * 4 + tr) * 12 + j] =
+// coefficient (int16, low half) | clip value (high half); word [set] != 0: some coefficient of the set does not fit int8.
+constexpr int kAlfSets = 23;                              // 16 fixed sets + up to 7 APS
+constexpr int kAlfTableHead = 32;
+constexpr int kAlfTableWords = kAlfTableHead + kAlfSets * 25 * 4 * 12;
+
+__device__ __forceinline__ void alf_coef_entry(const VVCB200AlfParams *params, int bd, int set, int cls, int tr, int j, int &cf, int &clip)
+{
+    const int16_t *coeff;
+    const uint8_t *clip_idx = nullptr;
+    if (set < 16) {
+        coeff = VVC_ALF_FIX_FILT_COEFF + VVC_ALF_CLASS_TO_FILT_MAP[set * 25 + cls] * 12;
+    } else {
+        const int k = min(set - 16, 6);
+        coeff = params->luma_coeff[k][VVC_ALF_APS_CLASS_TO_FILT_MAP[cls]];
+        clip_idx = params->luma_clip_idx[k][cls];
+    }
+    // transposition tables of alf_recon_coeff_and_clip (vvc_filter_template.c:386-391), 4 bits per entry
+    const unsigned long long i1 = 0x62037b518a49ull, i2 = 0xba9456781230ull, i3 = 0x62015b734a89ull;
+    const int idx = tr == 0 ? j : (int)(((tr == 1 ? i1 : tr == 2 ? i2 : i3) >> (4 * j)) & 15);
+    const int ci = clip_idx ? clip_idx[idx] : 0;
+    cf = coeff[idx];
+    clip = 1 << (bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7));
+}
+
+static __global__ void alf_coef_table_kernel(const VVCB200AlfParams *params, int bd, uint32_t *table)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= kAlfSets * 25 * 4 * 12)
+        return;
+    const int j = i % 12, tr = (i / 12) & 3, cls = (i / 48) % 25, set = i / (48 * 25);
+    int cf, clip;
+    alf_coef_entry(params, bd, set, cls, tr, j, cf, clip);
+    if (cf < -128 || cf > 127)
+        table[set] = 1;                                   // (the head was cleared by the caller)
+    table[kAlfTableHead + i] = (uint32_t)(cf & 0xffff) | ((uint32_t)clip << 16);
+}
 
 struct CtbGeom {
     int x0, y0, w, h;      // CTB rectangle in the component's plane
@@ -90,6 +130,7 @@ struct AlfLumaShared {
 
 // Everything after staging for one 32x32 luma tile at (tx0, ty0) of CTB `g` (record `cp`): S.pix holds the padded window,
 // S.wide was cleared, and a __syncthreads() lies between those writes and this call.  256 threads.
+template <bool kTable>
 __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVCB200AlfCtb &cp, const CtbGeom &g, int tx0,
                                                      int ty0, AlfLumaShared &S)
 {
@@ -160,31 +201,19 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
             s_cls[blk] = (uint8_t)(cls | ((dir_d * 2 + dir_hv) << 5));
     }
     __syncthreads();
-    // the 64 x 12 coefficient / clip fetches (global tables) spread over the whole CTA instead of 12 in a row on 64 threads
-    for (int i = t; i < 64 * 12; i += 256) {
-        const int blk = i / 12, j = i - blk * 12;
-        const int cls = s_cls[blk] & 31, tr = s_cls[blk] >> 5;
-        const int set = cp.filt_set_idx_y;
-        const int16_t *coeff;
-        const uint8_t *clip_idx = nullptr;
-        if (set < 16) {
-            coeff = VVC_ALF_FIX_FILT_COEFF + VVC_ALF_CLASS_TO_FILT_MAP[set * 25 + cls] * 12;
-        } else {
-            const int k = min(set - 16, 6);
-            coeff = a.params->luma_coeff[k][VVC_ALF_APS_CLASS_TO_FILT_MAP[cls]];
-            clip_idx = a.params->luma_clip_idx[k][cls];
+    if (!kTable) {
+        // the 64 x 12 coefficient / clip fetches (global tables) spread over the whole CTA instead of 12 in a row on 64 threads
+        for (int i = t; i < 64 * 12; i += 256) {
+            const int blk = i / 12, j = i - blk * 12;
+            int cf, clip;
+            alf_coef_entry(a.params, a.bd, cp.filt_set_idx_y, s_cls[blk] & 31, s_cls[blk] >> 5, j, cf, clip);
+            if (cf < -128 || cf > 127)
+                s_wide = 1;
+            s_coef[blk][j] = (int16_t)cf;
+            s_clip[blk][j] = (int16_t)clip;
         }
-        // transposition tables of alf_recon_coeff_and_clip (vvc_filter_template.c:386-391), 4 bits per entry
-        const unsigned long long i1 = 0x62037b518a49ull, i2 = 0xba9456781230ull, i3 = 0x62015b734a89ull;
-        const int idx = tr == 0 ? j : (int)(((tr == 1 ? i1 : tr == 2 ? i2 : i3) >> (4 * j)) & 15);
-        const int ci = clip_idx ? clip_idx[idx] : 0;
-        const int cf = coeff[idx];
-        if (cf < -128 || cf > 127)
-            s_wide = 1;
-        s_coef[blk][j] = (int16_t)cf;
-        s_clip[blk][j] = (int16_t)(1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7)));
+        __syncthreads();
     }
-    __syncthreads();
 
     // ---- filter: each thread owns 4 horizontally adjacent samples of one 4x4 block
     {
@@ -192,10 +221,26 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
         if (row < th && xg * 4 < tw) {
             const int blk = (row >> 2) * 8 + xg;
             int f[12], cl[12];
+            bool wide;
+            if (kTable) {                                 // the block's row of the per-picture table: three 128-bit loads
+                const int set = min((int)cp.filt_set_idx_y, kAlfSets - 1);
+                const uint4 *e = reinterpret_cast<const uint4 *>(a.table + kAlfTableHead +
+                                                                ((set * 25 + (s_cls[blk] & 31)) * 4 + (s_cls[blk] >> 5)) * 12);
+                const uint4 e0 = __ldg(e), e1 = __ldg(e + 1), e2 = __ldg(e + 2);
+                const uint32_t ew[12] = { e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w, e2.x, e2.y, e2.z, e2.w };
 #pragma unroll
-            for (int j = 0; j < 12; j++) {
-                f[j] = s_coef[blk][j];
-                cl[j] = s_clip[blk][j];
+                for (int j = 0; j < 12; j++) {
+                    f[j] = (int16_t)(ew[j] & 0xffff);
+                    cl[j] = (int)(ew[j] >> 16);
+                }
+                wide = __ldg(a.table + set) != 0;
+            } else {
+#pragma unroll
+                for (int j = 0; j < 12; j++) {
+                    f[j] = s_coef[blk][j];
+                    cl[j] = s_clip[blk][j];
+                }
+                wide = s_wide != 0;
             }
             int o1, o2, o3;
             bool near_vb;
@@ -205,7 +250,7 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
             const uint16_t *p3 = p0 + o2 * kPadStr, *p4 = p0 - o2 * kPadStr;
             const uint16_t *p5 = p0 + o3 * kPadStr, *p6 = p0 - o3 * kPadStr;
             uint16_t out[4];
-            if (!s_wide) {
+            if (!wide) {
                 // Two samples per 32-bit word through the 16x2 integer pipe (VIADD.16x2 / VIADDMNMX.S16x2 on sm_100a), the
                 // tap products through IDP.2A.  Differences, clips and their sums stay inside int16 for bit depths <= 12.
                 // w(p, k) = staged word k of a row relative to this thread's first sample: samples (2k, 2k + 1).
@@ -310,8 +355,9 @@ __device__ __forceinline__ void alf_chroma_filter_tile(const AlfArgs &a, const V
     }
     const int vb = (1 << l2) - 2;                        // ALF_VB_POS_ABOVE_CHROMA
     const int vb_luma = (1 << a.ctb_log2) - 4;
+    const int lt = 31 - __clz(T);                        // T is 16 or 32
     for (int i = t; i < T * T; i += 256) {
-        const int row = i / T, col = i - row * T;
+        const int row = i >> lt, col = i & (T - 1);
         const int x = tx0 + col, y = ty0 + row;
         if (x >= W || y >= H)
             continue;

@@ -76,7 +76,7 @@ struct Lane {
 constexpr int kLanes = 2, kSets = 4;   // two descriptor sets per lane: the next picture of a lane uploads while this one runs
 struct StageSet {
     Lane *lane = nullptr;          // sets[i] belongs to lanes[i % kLanes]
-    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, iblocks;
+    DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, alf_table, iblocks;
     VVCB200IntraBlock *h_order = nullptr;  // pinned: the picture's intra records in scheduled order
     size_t h_order_cap = 0;
     cudaEvent_t uploaded = nullptr;    // last upload into this set (recorded on the upload stream)
@@ -318,7 +318,7 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
             cudaStreamSynchronize(st);
     for (StageSet &ss : c->sets) {
         DevBuffer *bufs[] = { &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
-                              &ss.sao, &ss.alf, &ss.alf_params, &ss.iblocks };
+                              &ss.sao, &ss.alf, &ss.alf_params, &ss.alf_table, &ss.iblocks };
         for (DevBuffer *b : bufs)
             b->release();
         if (ss.h_order) cudaFreeHost(ss.h_order);
@@ -817,6 +817,8 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
             return r;
         if (int r = upload(c, S.alf_params, alf_params, sizeof(*alf_params)))
             return r;
+        if (int r = S.alf_table.reserve(vvcb200_sao_alf_scratch_bytes()))
+            return r;
     }
     if (int r = uploads_visible(c))
         return r;
@@ -835,7 +837,7 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
     if (int r = vvcb200_sao_alf_picture(dst, src, sao ? (const VVCB200SaoCtb *)S.sao.p : nullptr,
                                         alf ? (const VVCB200AlfCtb *)S.alf.p : nullptr,
                                         alf ? (const VVCB200AlfParams *)S.alf_params.p : nullptr, ctb_log2_size, c->bit_depth,
-                                        S.lane->stream))
+                                        alf ? S.alf_table.p : nullptr, S.lane->stream))
         return r;
     c->in_scratch = !c->in_scratch;
     return set_consumed(c);

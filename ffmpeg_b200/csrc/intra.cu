@@ -464,26 +464,14 @@ __device__ bool spans_ready(const IntraArgs &a, const Span *sp, int n, int lane,
 // ---- luma-dependent chroma residual scaling (vvc_intra_template.c:376-449) ------------------------------------------
 // The factor of a VPDU comes from the mean of the reconstructed luma samples left of and above it.
 // Returns false (try mode only) when the luma it depends on is not there yet; the factor comes back in `scale`.
-__device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane, bool blocking,
+// Phased pictures never get here with luma outstanding: vpdu_scale_kernel has filled the per-VPDU table.
+__device__ bool derive_vpdu_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane, bool blocking,
                                   int &scale)
 {
-    scale = 0;
-    if (!(b.flags & VVCB200_IB_LMCS_SCALE))
-        return true;
     const int size = min(1 << a.ctb_log2, 64), ls = ilog2(size);
     const int x = b.vpdu_x << ls, y = b.vpdu_y << ls;
     const bool al = b.vpdu_avail & 1, at = b.vpdu_avail & 2;
     const int rows = min(size, a.pic.h[0] - y), cols = min(size, a.pic.w[0] - x);
-    // Phased pictures (every luma sample is final by now): the factor of a VPDU is derived once and kept in a table; a
-    // second warp deriving it at the same time stores the same value.
-    unsigned *cached = a.vpdu_scale ? a.vpdu_scale + b.vpdu_y * a.vpdu_pitch + b.vpdu_x : nullptr;
-    if (cached) {
-        const unsigned v = __ldcg(cached);
-        if (v) {
-            scale = (int)(v & 0xffff);
-            return true;
-        }
-    }
     if (has_marks) {
         Span sp[2];
         if (!spans_ready(a, sp, vpdu_deps(b, a.ctb_log2, a.pic.w[0], a.pic.h[0], sp), lane, blocking))
@@ -522,9 +510,45 @@ __device__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b
     while (i <= a.lmcs_max_bin && mean >= a.lmcs_pivot[i + 1])
         i++;
     scale = a.lmcs_coeff[min(i, 15)];
-    if (cached && lane == 0)
-        *cached = 0x10000u | (unsigned)scale;
     return true;
+}
+
+__device__ __forceinline__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB200IntraBlock &b, bool has_marks, int lane,
+                                                  bool blocking, int &scale)
+{
+    scale = 0;
+    if (!(b.flags & VVCB200_IB_LMCS_SCALE))
+        return true;
+    if (a.vpdu_scale) {
+        scale = (int)(__ldcg(a.vpdu_scale + b.vpdu_y * a.vpdu_pitch + b.vpdu_x) & 0xffff);
+        return true;
+    }
+    return derive_vpdu_scale(a, b, has_marks, lane, blocking, scale);
+}
+
+// Phased pictures, between the luma wavefront and the chroma phases: the factor of every VPDU some record asks for,
+// derived once.  One warp per chroma record; the first to claim its VPDU's table entry (0 -> 1) derives the factor and
+// stores it as 0x10000 | factor, the others leave.  (Deriving on demand in the add-only batch does not work: the
+// thirty-odd records of a VPDU are neighbours in the array, in flight together, and all miss together.)
+__global__ void __launch_bounds__(256) vpdu_scale_kernel(IntraArgs a)
+{
+    const int lane = threadIdx.x & 31;
+    const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (t >= a.n)
+        return;
+    const VVCB200IntraBlock b = load_record(a.blocks + t);
+    if (!(b.flags & VVCB200_IB_LMCS_SCALE))
+        return;
+    unsigned *entry = a.vpdu_scale + b.vpdu_y * a.vpdu_pitch + b.vpdu_x;
+    unsigned old = 1;
+    if (lane == 0)
+        old = atomicCAS(entry, 0u, 1u);
+    if (__shfl_sync(kFull, old, 0) != 0)
+        return;
+    int scale = 0;
+    derive_vpdu_scale(a, b, false, lane, true, scale);
+    if (lane == 0)
+        *entry = 0x10000u | (unsigned)scale;
 }
 
 __device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
@@ -1668,6 +1692,13 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         return wavefront(0, n, 0, scale);
     if (int r = wavefront(0, n_luma, 0, false))                           // luma records never carry the chroma scale
         return r;
+    if (a.vpdu_scale && n > n_luma) {                                     // every chroma record's VPDU factor, once
+        IntraArgs w = a;
+        w.blocks = all + n_luma;
+        w.n = n - n_luma;
+        vpdu_scale_kernel<<<(w.n + 7) / 8, 256, 0, s>>>(w);
+        VVC_LAUNCH_CHECK();
+    }
     if (n_add) {
         IntraArgs w = a;
         w.blocks = all + n_luma;

@@ -202,6 +202,7 @@ __device__ __forceinline__ uint4 sao_chunk(const SaoAlfArgs &a, const PlaneWin &
     return make_uint4(out[0], out[1], out[2], out[3]);
 }
 
+template <bool kTable>
 __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
 {
     __shared__ __align__(16) uint16_t s_sao_y[kFYSR * kFYS];              // SAO'd luma, rows Y0-3 .., columns X0-8 ..
@@ -290,15 +291,15 @@ __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
         const CtbGeom g = ctb_geom(a, 0, tx0, ty0, cp.edges);
         if (t == 0)
             S.wide = 0;
-        for (int i = t; i < kPad * kPad; i += 256) {
-            const int r = i / kPad, col = i - r * kPad;
-            int x = tx0 + col - kHalo, y = ty0 + r - kHalo;
-            if (g.edges)
-                pad_coords(g, x, y);
-            S.pix[r * kPadStr + col + kColOrg - kHalo] = luma_at(x, y);
-        }
+        for (int r = t >> 5; r < kPad; r += 8)            // a warp per staged row, lanes along it
+            for (int col = t & 31; col < kPad; col += 32) {
+                int x = tx0 + col - kHalo, y = ty0 + r - kHalo;
+                if (g.edges)
+                    pad_coords(g, x, y);
+                S.pix[r * kPadStr + col + kColOrg - kHalo] = luma_at(x, y);
+            }
         __syncthreads();
-        alf_luma_filter_tile(a, cp, g, tx0, ty0, S);
+        alf_luma_filter_tile<kTable>(a, cp, g, tx0, ty0, S);
         __syncthreads();
     }
 
@@ -317,13 +318,13 @@ __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
             const CtbGeom g = ctb_geom(a, c, tx0, ty0, cp.edges);
             const int Sd = T + 4;
             if (cp.ctb_flag[c]) {
-                for (int i = t; i < Sd * Sd; i += 256) {
-                    const int r = i / Sd, col = i - r * Sd;
-                    int x = tx0 + col - 2, y = ty0 + r - 2;
-                    if (g.edges)
-                        pad_coords(g, x, y);
-                    S.pix[i] = cur_at(x, y);
-                }
+                for (int r = t >> 5; r < Sd; r += 8)
+                    for (int col = t & 31; col < Sd; col += 32) {
+                        int x = tx0 + col - 2, y = ty0 + r - 2;
+                        if (g.edges)
+                            pad_coords(g, x, y);
+                        S.pix[r * Sd + col] = cur_at(x, y);
+                    }
             }
             __syncthreads();
             alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, S.pix, cur_at, luma_at);
@@ -336,9 +337,11 @@ __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
 
 using namespace vvcb200;
 
+extern "C" size_t vvcb200_sao_alf_scratch_bytes(void) { return (size_t)kAlfTableWords * sizeof(uint32_t); }
+
 extern "C" int vvcb200_sao_alf_picture(const VVCB200Planes *dst, const VVCB200Planes *src, const VVCB200SaoCtb *d_sao,
                                        const VVCB200AlfCtb *d_alf, const VVCB200AlfParams *d_params, int ctb_log2_size,
-                                       int bit_depth, void *stream)
+                                       int bit_depth, void *d_scratch, void *stream)
 {
     if (!dst || !src || (d_alf && !d_params) || ctb_log2_size < 5 || ctb_log2_size > 7 || (bit_depth != 10 && bit_depth != 12)) {
         set_error("vvcb200_sao_alf_picture: bad argument");
@@ -367,7 +370,21 @@ extern "C" int vvcb200_sao_alf_picture(const VVCB200Planes *dst, const VVCB200Pl
         return VVCB200_ERR_UNSUP;
     }
     dim3 grid((src->width[0] + kFT - 1) / kFT, (src->height[0] + kFT - 1) / kFT, 1);
-    sao_alf_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+    A.alf.table = nullptr;
+    if (d_alf && d_scratch) {
+        if ((uintptr_t)d_scratch & 15) {
+            set_error("vvcb200_sao_alf_picture: d_scratch must be 16-byte aligned");
+            return VVCB200_ERR_ARG;
+        }
+        // the picture's coefficient / clip table first: a few microseconds that every 4x4 block then does not spend
+        VVC_CUDA(cudaMemsetAsync(d_scratch, 0, kAlfTableHead * sizeof(uint32_t), (cudaStream_t)stream));
+        alf_coef_table_kernel<<<(kAlfSets * 25 * 4 * 12 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(d_params, bit_depth, (uint32_t *)d_scratch);
+        VVC_LAUNCH_CHECK();
+        A.alf.table = (const uint32_t *)d_scratch;
+        sao_alf_kernel<true><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+    } else {
+        sao_alf_kernel<false><<<grid, 256, 0, (cudaStream_t)stream>>>(A);
+    }
     VVC_LAUNCH_CHECK();
     return 0;
 }

@@ -303,10 +303,17 @@ def alf_picture(dst, src, ctbs, params, ctb_log2, bit_depth=10, stream=None):
                                      _stream(stream)))
 
 
-def sao_alf_picture(dst, src, sao, alf, params, ctb_log2, bit_depth=10, stream=None):
-    """vvcb200_sao_alf_picture: SAO + ALF (+ CC-ALF) in one pass; sao / alf / params device tensors or None."""
+def sao_alf_scratch_bytes():
+    f = load().vvcb200_sao_alf_scratch_bytes
+    f.restype = C.c_size_t
+    return int(f())
+
+
+def sao_alf_picture(dst, src, sao, alf, params, ctb_log2, bit_depth=10, scratch=None, stream=None):
+    """vvcb200_sao_alf_picture: SAO + ALF (+ CC-ALF) in one pass; sao / alf / params device tensors or None; scratch: a
+    device tensor of sao_alf_scratch_bytes() bytes (the picture's coefficient table) or None."""
     check(load().vvcb200_sao_alf_picture(C.byref(dst), C.byref(src), _ptr(sao), _ptr(alf), _ptr(params), int(ctb_log2),
-                                         int(bit_depth), _stream(stream)))
+                                         int(bit_depth), _ptr(scratch), _stream(stream)))
 
 
 def lmcs_picture(pic, lut, bit_depth=10, stream=None):

@@ -336,13 +336,17 @@ VVCB200_API int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Plane
  * Stages SAO and ALF (ff_vvc_sao_filter vvc_filter.c:154-298 + ff_vvc_alf_filter 1254-1319) as ONE out-of-place pass:
  * dst = ALF(SAO(src)).  A CTA stages the deblocked samples of a 64x64 luma region (and its chroma) plus a ring of 4,
  * applies SAO in shared memory and runs ALF / CC-ALF on that — the SAO picture never exists in memory.  What Level B runs.
- * d_sao == NULL: SAO off; d_alf == NULL: ALF off (d_params may then be NULL too).  `src` planes 16-byte aligned with
+ * d_sao == NULL: SAO off; d_alf == NULL: ALF off (d_params may then be NULL too).  d_scratch: vvcb200_sao_alf_scratch_bytes()
+ * bytes of device memory, 16-byte aligned, for the picture's luma coefficient / clip table (alf.recon_coeff_and_clip
+ * evaluated once per (set, class, transposition) instead of once per 4x4 block); NULL: every block derives its own.
+ * `src` planes 16-byte aligned with
  * 16-byte multiple strides, `dst` planes 8-byte aligned with 8-byte multiple strides, dst != src, 4:2:0.
  * Results are identical to vvcb200_sao_picture followed by vvcb200_alf_picture.
  */
+VVCB200_API size_t vvcb200_sao_alf_scratch_bytes(void);
 VVCB200_API int vvcb200_sao_alf_picture(const VVCB200Planes *dst, const VVCB200Planes *src, const VVCB200SaoCtb *d_sao,
                                         const VVCB200AlfCtb *d_alf, const VVCB200AlfParams *d_params, int ctb_log2_size,
-                                        int bit_depth, void *stream);
+                                        int bit_depth, void *d_scratch, void *stream);
 
 /* lmcs.filter (vvcdsp.h:124) over whole luma plane in place: pix = lut[pix] (ff_vvc_lmcs_filter, vvc_filter.c:1322-1332). */
 VVCB200_API int vvcb200_lmcs_picture(const VVCB200Planes *pic, const uint16_t *d_lut, int bit_depth, void *stream);

@@ -51,15 +51,17 @@ def gpu_alf(base, lf):
     return util.from_device_planes(dst)
 
 
-def gpu_sao_alf(base, lf, sao=True, alf=True):
-    """The fused pass: vvcb200_sao_alf_picture."""
+def gpu_sao_alf(base, lf, sao=True, alf=True, table=True):
+    """The fused pass: vvcb200_sao_alf_picture (table: with the per-picture coefficient table in caller scratch)."""
     import torch
+    scratch = torch.full((lib.sao_alf_scratch_bytes(),), 0x5a, dtype=torch.uint8, device="cuda") if table else None
     src = util.to_device_planes(base, torch)
     dst = util.to_device_planes([np.full_like(p, 0x5555) for p in base], torch)
     sao_d = torch.from_numpy(lf["sao"].view(np.uint8).reshape(-1)).cuda() if sao else None
     alf_d = torch.from_numpy(lf["alf"].view(np.uint8).reshape(-1)).cuda() if alf else None
     params = torch.from_numpy(lf["alf_params"].view(np.uint8).reshape(-1)).cuda() if alf else None
-    lib.sao_alf_picture(lib.device_planes(dst), lib.device_planes(src), sao_d, alf_d, params, lf["ctb_log2"], lf.get("bd", 10))
+    lib.sao_alf_picture(lib.device_planes(dst), lib.device_planes(src), sao_d, alf_d, params, lf["ctb_log2"], lf.get("bd", 10),
+                        scratch=scratch)
     torch.cuda.synchronize()
     return util.from_device_planes(dst)
 
@@ -72,9 +74,10 @@ def test_fused_sao_alf_matches_oracle_chain(i, case, w, h):
     base = synth.smooth_planes(40 + i, lf["dims"])
     sao = oracle_sao(base, lf)
     want = oracle_alf(sao, lf)
-    got = gpu_sao_alf(base, lf)
-    for c in range(3):
-        assert np.array_equal(got[c], want[c]), "plane %d differs" % c
+    for table in (True, False):
+        got = gpu_sao_alf(base, lf, table=table)
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs (table %d)" % (c, table)
     # either stage alone
     got = gpu_sao_alf(base, lf, alf=False)
     for c in range(3):
