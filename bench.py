@@ -577,7 +577,7 @@ def main():
     e2e_steps = max(3, min(args.steps, 100))
 
     def e2e_run(n, **kw):
-        for _ in range(3):
+        for _ in range(8):                   # twice round the context's four descriptor sets and four picture slots
             ep.run(**kw)
         ctx.sync()
         barrier()

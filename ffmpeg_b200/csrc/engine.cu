@@ -77,14 +77,12 @@ constexpr int kLanes = 2, kSets = 4;   // two descriptor sets per lane: the next
 struct StageSet {
     Lane *lane = nullptr;          // sets[i] belongs to lanes[i % kLanes]
     DevBuffer levels, tbs, blocks, refined, prof, lut_fwd, lut_inv, db_tables, sao, alf, alf_params, alf_table, iblocks;
-    VVCB200IntraBlock *h_order = nullptr;  // pinned: the picture's intra records in scheduled order
-    size_t h_order_cap = 0;
+    DevBuffer iblocks_in, ctu_first, sched_scratch, phase_counts;   // intra records as emitted, their CTU ranges, the device scheduler's state
     cudaEvent_t uploaded = nullptr;    // last upload into this set (recorded on the upload stream)
     cudaEvent_t consumed = nullptr;    // last kernel that read this set (recorded on the compute stream)
-    cudaEvent_t order_copied = nullptr;    // the upload out of h_order (recorded on the upload stream)
     cudaEvent_t mv_ready = nullptr;        // INTER has written `refined` (compute stream)
     cudaEvent_t mv_copied = nullptr;       // `refined` has reached the host (download stream)
-    bool in_use = false, order_pending = false, mv_pending = false;
+    bool in_use = false, mv_pending = false;
 };
 
 struct VVCB200Ctx {
@@ -202,6 +200,13 @@ int order_before_read(VVCB200Ctx *c, int slot)
     return 0;
 }
 
+int ensure_residual(VVCB200Ctx *c, Lane *lane)
+{
+    if (lane->residual.base)
+        return 0;
+    return alloc_picture(c, &lane->residual);
+}
+
 // Bring the current picture to rest in its DPB slot: run a mapping that no deblocking pass picked up, and if the newest
 // samples sit in the lane's scratch picture, exchange the two buffers (both belong to this lane's stream order).
 int settle_picture(VVCB200Ctx *c)
@@ -275,7 +280,6 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
         c->sets[i].lane = &c->lanes[lane_of(i)];
         e = cudaEventCreateWithFlags(&c->sets[i].uploaded, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].consumed, cudaEventDisableTiming);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].order_copied, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].mv_ready, cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->sets[i].mv_copied, cudaEventDisableTiming);
     }
@@ -298,7 +302,35 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
         r = alloc_picture(c, &c->lanes[1].scratch);
     for (int i = 0; !r && i < dpb_size; i++)
         r = alloc_picture(c, &c->dpb[i]);
-    if (!r && cudaStreamSynchronize(lane_stream(c)) != cudaSuccess)     // the pictures are cleared before either lane runs
+    // Working memory for the descriptor batches of a typical picture of this size, so that the steady state never meets the
+    // allocator (an allocation serialises against everything in flight on the device): dense levels, TBs of 32 samples,
+    // prediction and intra records of 32 luma samples on average; a picture that needs more grows its buffer once.
+    const size_t wh = (size_t)width * height;
+    const int ctb32 = ((width + 31) >> 5) * ((height + 31) >> 5);
+    for (int i = 0; !r && i < kSets; i++) {
+        StageSet &ss = c->sets[i];
+        struct { DevBuffer *b; size_t bytes; } want[] = {
+            { &ss.levels, 3 * wh }, { &ss.tbs, wh * 3 / 64 * sizeof(VVCB200TransformBlock) },
+            { &ss.blocks, wh / 32 * sizeof(VVCB200PredBlock) }, { &ss.refined, wh / 32 * 16 },
+            { &ss.prof, wh / 256 * sizeof(VVCB200ProfTable) / 4 }, { &ss.lut_fwd, sizeof(uint16_t) << bit_depth },
+            { &ss.lut_inv, sizeof(uint16_t) << bit_depth }, { &ss.db_tables, (wh / 16 + 64) * 9 + (size_t)ctb32 * 6 + 64 },
+            { &ss.sao, (size_t)ctb32 * sizeof(VVCB200SaoCtb) }, { &ss.alf, (size_t)ctb32 * sizeof(VVCB200AlfCtb) },
+            { &ss.alf_params, sizeof(VVCB200AlfParams) }, { &ss.alf_table, vvcb200_sao_alf_scratch_bytes() },
+            { &ss.iblocks, wh / 48 * sizeof(VVCB200IntraBlock) }, { &ss.iblocks_in, wh / 48 * sizeof(VVCB200IntraBlock) },
+            { &ss.ctu_first, ((size_t)ctb32 + 1) * 4 },
+            { &ss.sched_scratch, vvcb200_intra_schedule_scratch_bytes((int)(wh / 48), (width + 31) >> 5, (height + 31) >> 5) },
+            { &ss.phase_counts, 256 },
+        };
+        for (auto &w : want)
+            if (!r)
+                r = w.b->reserve(w.bytes);
+    }
+    for (int i = 0; !r && i < kLanes; i++) {
+        r = c->lanes[i].intra_marks.reserve(vvcb200_intra_scratch_bytes(width, height));
+        if (!r)
+            r = alloc_picture(c, &c->lanes[i].residual);
+    }
+    if (!r && cudaDeviceSynchronize() != cudaSuccess)                   // the pictures are cleared before either lane runs
         r = VVCB200_ERR_CUDA;
     if (r) {
         vvcb200_ctx_destroy(c);
@@ -318,13 +350,12 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
             cudaStreamSynchronize(st);
     for (StageSet &ss : c->sets) {
         DevBuffer *bufs[] = { &ss.levels, &ss.tbs, &ss.blocks, &ss.refined, &ss.prof, &ss.lut_fwd, &ss.lut_inv, &ss.db_tables,
-                              &ss.sao, &ss.alf, &ss.alf_params, &ss.alf_table, &ss.iblocks };
+                              &ss.sao, &ss.alf, &ss.alf_params, &ss.alf_table, &ss.iblocks, &ss.iblocks_in, &ss.ctu_first,
+                              &ss.sched_scratch, &ss.phase_counts };
         for (DevBuffer *b : bufs)
             b->release();
-        if (ss.h_order) cudaFreeHost(ss.h_order);
         if (ss.uploaded) cudaEventDestroy(ss.uploaded);
         if (ss.consumed) cudaEventDestroy(ss.consumed);
-        if (ss.order_copied) cudaEventDestroy(ss.order_copied);
         if (ss.mv_ready) cudaEventDestroy(ss.mv_ready);
         if (ss.mv_copied) cudaEventDestroy(ss.mv_copied);
     }
@@ -364,7 +395,7 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
     for (char &p : c->download_pending)
         p = 0;
     for (StageSet &ss : c->sets)
-        ss.in_use = ss.order_pending = ss.mv_pending = false;
+        ss.in_use = ss.mv_pending = false;
     for (size_t i = 0; i < c->writer.size(); i++) {                       // nothing is in flight: no ordering left to do
         c->writer[i] = -1;
         c->readers[i] = 0;
@@ -684,37 +715,37 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
     DeviceGuard g(c->device);
     if (int r = settle_picture(c))
         return r;
-    if (S.order_pending) {                // the copy that last read this set's pinned staging (two pictures ago) must be over
-        VVC_CUDA(cudaEventSynchronize(S.order_copied));
-        S.order_pending = false;
-    }
-    if ((size_t)n > S.h_order_cap) {      // pinned staging for the scheduled order (this set's previous upload has long finished)
-        if (S.h_order)
-            cudaFreeHost(S.h_order);
-        S.h_order = nullptr;
-        S.h_order_cap = 0;
-        const size_t want = (size_t)n + n / 4 + 1024;
-        VVC_CUDA(cudaHostAlloc((void **)&S.h_order, want * sizeof(VVCB200IntraBlock), cudaHostAllocDefault));
-        S.h_order_cap = want;
-    }
-    int32_t phases[2] = { 0, 0 };
-    if (int r = vvcb200_intra_schedule(blocks, ctu_first, ctus_w, ctus_h, shift, c->width, c->height,
-                                       VVCB200_INTRA_ORDER_DIAGONAL, S.h_order, nullptr, phases))
+    // The records go up as the parser emitted them; the wavefront order is made on the device (three small kernels), so the
+    // calling thread spends no time per record.
+    const int nctu = ctus_w * ctus_h;
+    if (int r = upload(c, S.iblocks_in, blocks, (size_t)n * sizeof(VVCB200IntraBlock)))
         return r;
-    VVCB200IntraParams phased = *params;
-    phased.n_luma = phases[0];
-    phased.n_add_only = phases[1];
-    if (int r = upload(c, S.iblocks, S.h_order, (size_t)n * sizeof(VVCB200IntraBlock)))
+    if (int r = upload(c, S.ctu_first, ctu_first, (size_t)(nctu + 1) * sizeof(uint32_t)))
         return r;
-    VVC_CUDA(cudaEventRecord(S.order_copied, c->h2d));
-    S.order_pending = true;
-    const size_t marks = vvcb200_intra_scratch_bytes(c->width, c->height);
-    if (int r = S.lane->intra_marks.reserve(marks))
+    const size_t need[3] = { (size_t)n * sizeof(VVCB200IntraBlock), vvcb200_intra_schedule_scratch_bytes(n, ctus_w, ctus_h),
+                             vvcb200_intra_scratch_bytes(c->width, c->height) };
+    DevBuffer *bufs[3] = { &S.iblocks, &S.sched_scratch, &S.lane->intra_marks };
+    for (int i = 0; i < 3; i++)
+        if (need[i] > bufs[i]->cap) {                 // (only before the buffers have reached their working size)
+            VVC_CUDA(cudaStreamSynchronize(S.lane->stream));
+            if (int r = bufs[i]->reserve(need[i]))
+                return r;
+        }
+    if (int r = S.phase_counts.reserve(256))
         return r;
     if (int r = uploads_visible(c))
         return r;
+    if (int r = vvcb200_intra_schedule_device((const VVCB200IntraBlock *)S.iblocks_in.p, (const uint32_t *)S.ctu_first.p, n, ctus_w,
+                                              ctus_h, (VVCB200IntraBlock *)S.iblocks.p, (int32_t *)S.phase_counts.p,
+                                              S.sched_scratch.p, S.lane->stream))
+        return r;
+    VVCB200IntraParams phased = *params;
+    phased.n_luma = phased.n_add_only = 0;
+    phased.d_phase_counts = (const int32_t *)S.phase_counts.p;
+    if (int r = ensure_residual(c, S.lane))           // (a picture without stored residuals still hands the planes over)
+        return r;
     // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
-    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, have_res ? &S.lane->residual.planes : nullptr, &S.lane->scratch.planes,
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, &S.lane->residual.planes, &S.lane->scratch.planes,
                                       (const VVCB200IntraBlock *)S.iblocks.p, n, &phased, S.lane->intra_marks.p, S.lane->stream))
         return r;
     return set_consumed(c);

@@ -99,11 +99,37 @@ struct IntraArgs {
     int *ticket;                  // next record of this launch
     int *inplace_flag;            // set by the pre-pass when the picture has in-place records that go by marks
     int skip_first, skip_n;       // pre-pass: records left alone (the add-only phase of a phased picture)
+    const int *phase_info;        // device: n_luma, n_add_only, n_chroma as vvcb200_intra_schedule_device left them, or null
+    int phase;                    // with phase_info: which records this launch is for (kPhase*)
     unsigned *vpdu_scale;         // phased pictures: chroma residual scale per VPDU, 0 = not derived yet, else 0x10000 | scale
     int vpdu_pitch;               // VPDUs per row of that table
     uint16_t lmcs_pivot[17], lmcs_coeff[16];
     int lmcs_min_bin, lmcs_max_bin;
 };
+
+// Launches whose record range is only known on the device (the schedule was made there) read it here.
+enum { kPhaseLuma = 0, kPhaseAddOnly = 1, kPhaseChroma = 2, kPhaseAllChroma = 3, kPhaseMark = 4 };
+struct RecordRange {
+    const VVCB200IntraBlock *blocks;
+    int n, skip_first, skip_n;
+};
+// (returns a copy of the few fields instead of patching the argument struct: a kernel that writes to its parameter makes
+// the compiler move all of it into local memory)
+__device__ __forceinline__ RecordRange resolve_phase(const IntraArgs &a)
+{
+    RecordRange r = { a.blocks, a.n, a.skip_first, a.skip_n };
+    if (!a.phase_info)
+        return r;
+    const int n0 = a.phase_info[0], n1 = a.phase_info[1], n2 = a.phase_info[2];
+    switch (a.phase) {
+    case kPhaseLuma:      r.n = n0; break;
+    case kPhaseAddOnly:   r.blocks += n0; r.n = n1; break;
+    case kPhaseChroma:    r.blocks += n0 + n1; r.n = n2; break;
+    case kPhaseAllChroma: r.blocks += n0; r.n = n1 + n2; break;
+    default:              r.n = n0 + n1 + n2; r.skip_first = n0; r.skip_n = n1; break;
+    }
+    return r;
+}
 
 __device__ __forceinline__ int ilog2(int v) { return 31 - __clz(v); }
 __host__ __device__ __forceinline__ int unit_shift(int c) { return c ? 1 : 2; }     // rows per unit: 4 (luma) / 2 (chroma)
@@ -213,13 +239,14 @@ __device__ __forceinline__ bool in_place(const VVCB200IntraBlock &b) { return b.
 // Threads per record.  (Most records are 4 .. 16 pieces of 8 bytes, but 8 threads per record measured slower than a
 // warp per record: the records sharing a warp differ in size and their loops serialise.)
 constexpr int kMarkLanes = 32;
-__global__ void intra_mark_kernel(IntraArgs a)
+__global__ void intra_mark_kernel(const IntraArgs a)
 {
+    const RecordRange rr = resolve_phase(a);
     const int lane = threadIdx.x & (kMarkLanes - 1);
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) / kMarkLanes;
-    if (t >= a.n || (t >= a.skip_first && t < a.skip_first + a.skip_n))
+    if (t >= rr.n || (t >= rr.skip_first && t < rr.skip_first + rr.skip_n))
         return;
-    const VVCB200IntraBlock b = load_record(a.blocks + t);
+    const VVCB200IntraBlock b = load_record(rr.blocks + t);
     int w, h;
     record_extent(b, w, h);
     if ((b.flags & VVCB200_IB_ADD_ONLY) && !(b.flags & VVCB200_IB_RESIDUAL))
@@ -530,13 +557,14 @@ __device__ __forceinline__ bool vpdu_chroma_scale(const IntraArgs &a, const VVCB
 // derived once.  One warp per chroma record; the first to claim its VPDU's table entry (0 -> 1) derives the factor and
 // stores it as 0x10000 | factor, the others leave.  (Deriving on demand in the add-only batch does not work: the
 // thirty-odd records of a VPDU are neighbours in the array, in flight together, and all miss together.)
-__global__ void __launch_bounds__(256) vpdu_scale_kernel(IntraArgs a)
+__global__ void __launch_bounds__(256) vpdu_scale_kernel(const IntraArgs a)
 {
+    const RecordRange rr = resolve_phase(a);
     const int lane = threadIdx.x & 31;
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (t >= a.n)
+    if (t >= rr.n)
         return;
-    const VVCB200IntraBlock b = load_record(a.blocks + t);
+    const VVCB200IntraBlock b = load_record(rr.blocks + t);
     if (!(b.flags & VVCB200_IB_LMCS_SCALE))
         return;
     unsigned *entry = a.vpdu_scale + b.vpdu_y * a.vpdu_pitch + b.vpdu_x;
@@ -561,13 +589,14 @@ __device__ __forceinline__ int scale_chroma_residual(int r, int scale, int bd)
 // Chroma blocks of inter units whose residual waits for the luma-dependent scale (VVCB200_IB_ADD_ONLY): once every luma
 // sample of the picture is final they depend on nothing else, so they run as a plain batch — one warp per record —
 // between the luma wavefront and the chroma wavefront instead of as tickets of the latter.
-__global__ void __launch_bounds__(256) intra_add_only_kernel(IntraArgs a)
+__global__ void __launch_bounds__(256) intra_add_only_kernel(const IntraArgs a)
 {
+    const RecordRange rr = resolve_phase(a);
     const int lane = threadIdx.x & 31;
     const int t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-    if (t >= a.n)
+    if (t >= rr.n)
         return;
-    const VVCB200IntraBlock b = load_record(a.blocks + t);
+    const VVCB200IntraBlock b = load_record(rr.blocks + t);
     if (!(b.flags & VVCB200_IB_RESIDUAL))
         return;
     int lscale = 0;
@@ -1246,10 +1275,11 @@ __device__ bool isp_external_ready(const IntraArgs &a, const VVCB200IntraBlock &
 // of that code, which matters for a kernel whose steps wait on instruction fetch.
 // kScale: the picture uses luma-dependent chroma residual scaling (VVCB200IntraParams.lmcs_chroma_scale).
 template <bool kMarks, bool kScale>
-__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArgs a)
+__global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(const IntraArgs a)
 {
     extern __shared__ __align__(16) uint8_t s_dyn[];
     __shared__ CtaTables tb;
+    const RecordRange rr = resolve_phase(a);
     const int lane = threadIdx.x & 31;
     WarpScratch &ws = reinterpret_cast<WarpScratch *>(s_dyn)[threadIdx.x >> 5];
     CtaArena &ar = *reinterpret_cast<CtaArena *>(s_dyn + sizeof(WarpScratch) * kWarps);
@@ -1285,13 +1315,13 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
             if (lane == 0)
                 t = atomicAdd(a.ticket, 1);
             t = __shfl_sync(kFull, t, 0);
-            if (t >= a.n) {
+            if (t >= rr.n) {
                 tickets_left = false;
                 break;
             }
             const int k = __ffs(~held) - 1;
             if (lane < 7)
-                reinterpret_cast<uint32_t *>(&slot[k])[lane] = __ldg(reinterpret_cast<const uint32_t *>(a.blocks + t) + lane);
+                reinterpret_cast<uint32_t *>(&slot[k])[lane] = __ldg(reinterpret_cast<const uint32_t *>(rr.blocks + t) + lane);
             held |= 1u << k;
         }
         __syncwarp();
@@ -1352,6 +1382,121 @@ __global__ void __launch_bounds__(kWarps * 32, kCtasPerSm) intra_kernel(IntraArg
             backoff = min(backoff * 2, 512u);
         }
     }
+}
+
+// ---- the record order made on the device (vvcb200_intra_schedule_device) ---------------------------------------------
+// Same order as the host helper's diagonal form, per phase: CTU anti-diagonals x + 2y, the CTUs of a diagonal dealt
+// record by record, each CTU's records of a phase in decoding order.
+// 1. one warp per CTU: every record's phase and its index k among the CTU's records of that phase; the CTU's three counts
+__global__ void __launch_bounds__(256) intra_rank_kernel(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int nctu,
+                                                         uint32_t *rank, uint16_t *ctu_of, int *len)
+{
+    const int lane = threadIdx.x & 31;
+    const int c = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (c >= nctu)
+        return;
+    const uint32_t first = ctu_first[c], last = ctu_first[c + 1];
+    int cnt[3] = { 0, 0, 0 };
+    for (uint32_t i0 = first; i0 < last; i0 += 32) {
+        const uint32_t i = i0 + lane;
+        const bool valid = i < last;
+        int p = -1;
+        if (valid) {
+            const uint32_t *w = reinterpret_cast<const uint32_t *>(in + i);
+            const uint32_t w1 = __ldg(w + 1), w2 = __ldg(w + 2);                  // (w, h, c_idx, mode), (ref_idx, flags, ...)
+            const int c_idx = (w1 >> 16) & 0xff, flags = (w2 >> 8) & 0xff;
+            p = !c_idx ? 0 : (flags & VVCB200_IB_ADD_ONLY) ? 1 : 2;
+        }
+        int k = 0;
+#pragma unroll
+        for (int q = 0; q < 3; q++) {
+            const unsigned m = __ballot_sync(kFull, p == q);
+            if (p == q)
+                k = cnt[q] + __popc(m & ((1u << lane) - 1));
+            cnt[q] += __popc(m);
+        }
+        if (valid) {
+            rank[i] = ((uint32_t)p << 30) | (uint32_t)k;
+            ctu_of[i] = (uint16_t)c;
+        }
+    }
+    if (lane < 3)
+        len[c * 3 + lane] = lane == 0 ? cnt[0] : lane == 1 ? cnt[1] : cnt[2];
+}
+
+__device__ __forceinline__ void diagonal_rows(int d, int ctus_w, int ctus_h, int &y_lo, int &y_hi)
+{
+    y_lo = d - (ctus_w - 1) > 0 ? (d - (ctus_w - 1) + 1) / 2 : 0;
+    y_hi = d / 2 < ctus_h - 1 ? d / 2 : ctus_h - 1;
+}
+
+// 2. one CTA: records per (phase, diagonal), their exclusive prefix, the three phase totals
+__global__ void __launch_bounds__(256) intra_base_kernel(const int *len, int ctus_w, int ctus_h, int *diag_base, int *info)
+{
+    const int nd = ctus_w + 2 * (ctus_h - 1);
+    for (int d = threadIdx.x; d < nd; d += blockDim.x) {
+        int y_lo, y_hi, tot[3] = { 0, 0, 0 };
+        diagonal_rows(d, ctus_w, ctus_h, y_lo, y_hi);
+        for (int y = y_lo; y <= y_hi; y++) {
+            const int *l = len + (y * ctus_w + d - 2 * y) * 3;
+            tot[0] += l[0]; tot[1] += l[1]; tot[2] += l[2];
+        }
+        for (int p = 0; p < 3; p++)
+            diag_base[p * nd + d] = tot[p];
+    }
+    __syncthreads();
+    if (threadIdx.x < 3) {
+        const int p = threadIdx.x;
+        int run = 0;
+        for (int d = 0; d < nd; d++) {
+            const int v = diag_base[p * nd + d];
+            diag_base[p * nd + d] = run;
+            run += v;
+        }
+        info[p] = run;
+    }
+}
+
+// 3. one thread per record: its place, then the copy
+__global__ void __launch_bounds__(256) intra_scatter_kernel(const VVCB200IntraBlock *in, int n, const uint32_t *rank,
+                                                            const uint16_t *ctu_of, const int *len, const int *diag_base,
+                                                            const int *info, int ctus_w, int ctus_h, VVCB200IntraBlock *out)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n)
+        return;
+    const uint32_t r = rank[i];
+    const int p = r >> 30, k = r & 0x3fffffff, c = ctu_of[i];
+    const int cy = c / ctus_w, cx = c - cy * ctus_w, d = cx + 2 * cy, nd = ctus_w + 2 * (ctus_h - 1);
+    int y_lo, y_hi;
+    diagonal_rows(d, ctus_w, ctus_h, y_lo, y_hi);
+    int pos = diag_base[p * nd + d] + (p > 0 ? info[0] : 0) + (p > 1 ? info[1] : 0);
+    for (int y = y_lo; y <= y_hi; y++) {
+        const int L = len[(y * ctus_w + d - 2 * y) * 3 + p];
+        pos += min(L, k) + (y < cy && L > k ? 1 : 0);
+    }
+    const uint32_t *src = reinterpret_cast<const uint32_t *>(in + i);
+    uint32_t *dst = reinterpret_cast<uint32_t *>(out + pos);
+#pragma unroll
+    for (int j = 0; j < 7; j++)
+        dst[j] = __ldg(src + j);
+}
+
+struct SchedLayout {
+    size_t rank, ctu_of, len, diag, total;
+};
+
+SchedLayout sched_layout(int n, int ctus_w, int ctus_h)
+{
+    SchedLayout l;
+    size_t o = 0;
+    auto take = [&](size_t bytes) { const size_t at = o; o = (o + bytes + 255) & ~(size_t)255; return at; };
+    l.rank = take((size_t)n * 4);
+    l.ctu_of = take((size_t)n * 2);
+    l.len = take((size_t)ctus_w * ctus_h * 3 * 4);
+    l.diag = take((size_t)(ctus_w + 2 * (ctus_h - 1)) * 3 * 4);
+    l.total = o;
+    return l;
 }
 
 struct ScratchLayout {
@@ -1621,18 +1766,21 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         a.mpitch[c] = l.pitch[c];
     }
     // phases: luma wavefront, chroma add-only batch, chroma wavefront (see VVCB200IntraParams)
-    const int n_luma = params->n_luma, n_add = params->n_add_only;
-    const bool phased = n_luma > 0 || n_add > 0;
+    const int *d_counts = params->d_phase_counts;                          // the order was made on the device
+    const int n_luma = d_counts ? 0 : params->n_luma, n_add = d_counts ? 0 : params->n_add_only;
+    const bool phased = d_counts || n_luma > 0 || n_add > 0;
     if (n_luma < 0 || n_add < 0 || (long long)n_luma + n_add > n) {
         set_error("vvcb200_intra_picture: n_luma %d + n_add_only %d exceed the %d records", n_luma, n_add, n);
         return VVCB200_ERR_ARG;
     }
-    if (phased && n_add && !d_residual) {
+    if ((d_counts || (phased && n_add)) && !d_residual) {
         set_error("vvcb200_intra_picture: add-only records need the residual planes");
         return VVCB200_ERR_ARG;
     }
     a.skip_first = n_luma;
     a.skip_n = phased ? n_add : 0;
+    a.phase_info = d_counts;
+    a.phase = kPhaseMark;
     a.vpdu_scale = nullptr;
     a.vpdu_pitch = l.vpdu_pitch;
     cudaStream_t s = (cudaStream_t)stream;
@@ -1668,12 +1816,13 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     const bool marks = !d_shadow;
     const VVCB200IntraBlock *all = d_blocks;
     // one wavefront launch over records [first, first + count) with its own ticket counter
-    auto wavefront = [&](int first, int count, int ticket_idx, bool scale) -> int {
+    auto wavefront = [&](int first, int count, int ticket_idx, bool scale, int phase) -> int {
         if (count <= 0)
             return 0;
         IntraArgs w = a;
         w.blocks = all + first;
         w.n = count;
+        w.phase = phase;                                                  // (with d_counts the kernel finds its own range)
         w.ticket = (int *)d_scratch + ticket_idx;
         const int grid = min(ctas, (count + kWarps - 1) / kWarps);
         if (marks && scale)
@@ -1689,8 +1838,24 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     };
     const bool scale = params->lmcs_chroma_scale != 0;
     if (!phased)
-        return wavefront(0, n, 0, scale);
-    if (int r = wavefront(0, n_luma, 0, false))                           // luma records never carry the chroma scale
+        return wavefront(0, n, 0, scale, 0);
+    if (d_counts) {
+        // the ranges live on the device: every launch is sized for all n records and takes its own share
+        if (int r = wavefront(0, n, 0, false, kPhaseLuma))
+            return r;
+        IntraArgs w = a;
+        w.n = n;
+        if (a.vpdu_scale) {
+            w.phase = kPhaseAllChroma;
+            vpdu_scale_kernel<<<(n + 7) / 8, 256, 0, s>>>(w);
+            VVC_LAUNCH_CHECK();
+        }
+        w.phase = kPhaseAddOnly;
+        intra_add_only_kernel<<<(n + 7) / 8, 256, 0, s>>>(w);
+        VVC_LAUNCH_CHECK();
+        return wavefront(0, n, 2, scale, kPhaseChroma);
+    }
+    if (int r = wavefront(0, n_luma, 0, false, 0))                        // luma records never carry the chroma scale
         return r;
     if (a.vpdu_scale && n > n_luma) {                                     // every chroma record's VPDU factor, once
         IntraArgs w = a;
@@ -1706,7 +1871,43 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         intra_add_only_kernel<<<(n_add + 7) / 8, 256, 0, s>>>(w);
         VVC_LAUNCH_CHECK();
     }
-    return wavefront(n_luma + n_add, n - n_luma - n_add, 2, scale);
+    return wavefront(n_luma + n_add, n - n_luma - n_add, 2, scale, 0);
+}
+
+extern "C" size_t vvcb200_intra_schedule_scratch_bytes(int n, int ctus_w, int ctus_h)
+{
+    if (n < 0 || ctus_w <= 0 || ctus_h <= 0)
+        return 0;
+    return sched_layout(n, ctus_w, ctus_h).total;
+}
+
+extern "C" int vvcb200_intra_schedule_device(const VVCB200IntraBlock *d_in, const uint32_t *d_ctu_first, int n, int ctus_w,
+                                             int ctus_h, VVCB200IntraBlock *d_out, int32_t *d_phase_counts, void *d_scratch,
+                                             void *stream)
+{
+    if (n < 0 || ctus_w <= 0 || ctus_h <= 0 || ctus_w * ctus_h > 65535 || !d_phase_counts ||
+        (n && (!d_in || !d_ctu_first || !d_out || !d_scratch || d_in == d_out))) {
+        set_error("vvcb200_intra_schedule_device: bad arguments");
+        return VVCB200_ERR_ARG;
+    }
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!n) {
+        VVC_CUDA(cudaMemsetAsync(d_phase_counts, 0, 3 * sizeof(int32_t), s));
+        return 0;
+    }
+    const SchedLayout l = sched_layout(n, ctus_w, ctus_h);
+    uint8_t *base = (uint8_t *)d_scratch;
+    uint32_t *rank = (uint32_t *)(base + l.rank);
+    uint16_t *ctu_of = (uint16_t *)(base + l.ctu_of);
+    int *len = (int *)(base + l.len), *diag = (int *)(base + l.diag);
+    const int nctu = ctus_w * ctus_h;
+    intra_rank_kernel<<<(nctu + 7) / 8, 256, 0, s>>>(d_in, d_ctu_first, nctu, rank, ctu_of, len);
+    VVC_LAUNCH_CHECK();
+    intra_base_kernel<<<1, 256, 0, s>>>(len, ctus_w, ctus_h, diag, d_phase_counts);
+    VVC_LAUNCH_CHECK();
+    intra_scatter_kernel<<<(n + 255) / 256, 256, 0, s>>>(d_in, n, rank, ctu_of, len, diag, d_phase_counts, ctus_w, ctus_h, d_out);
+    VVC_LAUNCH_CHECK();
+    return 0;
 }
 
 // ---- the same reconstruction with the scratch living in the module image instead of caller memory ---------------
@@ -1767,6 +1968,7 @@ extern "C" int vvcb200_intra_picture_static(const VVCB200Planes *pic, const VVCB
     // ticket sector and the marks, which an earlier call may have left set.
     VVCB200IntraParams one = *params;
     one.n_luma = one.n_add_only = 0;
+    one.d_phase_counts = nullptr;
     return vvcb200_intra_picture(pic, d_residual, nullptr, d_blocks, n, &one, ptr, stream);
 }
 

@@ -34,7 +34,7 @@ def from_device_planes(tensors):
 class EnginePicture:
     """Pinned host copies of one picture's batches + the Level-B call sequence (HOST buffers in, HOST planes out)."""
 
-    def __init__(self, ctx, pic):
+    def __init__(self, ctx, pic, max_slots=4, want_mv=True):
         it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
         self.ctx, self.pic = ctx, pic
         self.n_refs = len(it["refs"])
@@ -63,7 +63,8 @@ class EnginePicture:
         # do: the download of one picture then overlaps the reconstruction of the next ones (two compute lanes)
         # DMVR feedback: the vectors actually used come back every picture (the host needs them for later MV prediction)
         self.refined = [ctx.pinned((max(len(it["blocks"]), 1), 2, 2), np.int32) for _ in range(4)]
-        self.n_slots = max(1, min(4, ctx.dpb_size - self.n_refs))
+        self.want_mv = want_mv
+        self.n_slots = max(1, min(max_slots, ctx.dpb_size - self.n_refs))
         self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
         self.count = 0
         self.out = self.outs[0]
@@ -78,7 +79,7 @@ class EnginePicture:
         return int(sum(p.nbytes for p in self.out))
 
     def d2h_bytes(self):
-        return self.picture_bytes() + (int(self.refined[0].nbytes) if len(self.blocks) else 0)
+        return self.picture_bytes() + (int(self.refined[0].nbytes) if len(self.blocks) and self.want_mv else 0)
 
     def upload_refs(self):
         for i, r in enumerate(self.refs):
@@ -95,7 +96,7 @@ class EnginePicture:
         ctx.begin(self.n_refs + k)
         if len(self.blocks):
             ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0],
-                      refined_mv=self.refined[self.count % 4], prof=self.prof)
+                      refined_mv=self.refined[self.count % 4] if self.want_mv else None, prof=self.prof)
         ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
         if self.intra is not None:
             ctx.intra(*self.intra)

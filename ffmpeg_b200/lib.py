@@ -116,6 +116,19 @@ def intra_schedule(blocks, ctu_first, ctus_w, ctus_h, ctb_log2, width, height, w
     return res if len(res) > 1 else res[0]
 
 
+def intra_schedule_device(d_in, d_ctu_first, n, ctus_w, ctus_h, d_out, d_counts, d_scratch, stream=None):
+    """vvcb200_intra_schedule_device: all arguments device tensors (records as emitted + CTU ranges in, phased diagonal
+    order + the three phase counts out)."""
+    check(load().vvcb200_intra_schedule_device(_ptr(d_in), _ptr(d_ctu_first), int(n), int(ctus_w), int(ctus_h), _ptr(d_out),
+                                               _ptr(d_counts), _ptr(d_scratch), _stream(stream)))
+
+
+def intra_schedule_scratch_bytes(n, ctus_w, ctus_h):
+    f = load().vvcb200_intra_schedule_scratch_bytes
+    f.restype = C.c_size_t
+    return int(f(int(n), int(ctus_w), int(ctus_h)))
+
+
 def phased_params(params, counts):
     """Copy of an IntraParams with the phase counts of intra_schedule(..., phases=True)."""
     p = abi.IntraParams.from_buffer_copy(bytes(params))

@@ -415,7 +415,10 @@ typedef struct VVCB200IntraParams {
      * add-only records (most records of a random-access picture with chroma residual scaling) stop being tickets of a
      * latency-bound wavefront.  Both 0: one wavefront over all records in array order. */
     int32_t  n_luma, n_add_only;
-} VVCB200IntraParams;           /* 96 bytes */
+    /* Alternatively the counts in DEVICE memory, as vvcb200_intra_schedule_device leaves them (three int32: luma, add-only,
+     * other chroma); non-NULL: n_luma / n_add_only are ignored and every launch reads its range there. */
+    const int32_t *d_phase_counts;
+} VVCB200IntraParams;           /* 104 bytes */
 
 /*
  * Reconstruction of the intra blocks of one picture, in place on `pic` (which already holds the inter prediction +
@@ -459,6 +462,18 @@ enum {
 VVCB200_API int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_t *ctu_first, int ctus_w, int ctus_h,
                                        int ctb_log2_size, int width, int height, int order, VVCB200IntraBlock *out,
                                        int32_t *n_levels, int32_t *phase_counts);
+/*
+ * The same schedule made on the device, so that the host only copies the records up as the parser emitted them:
+ * d_in holds the records of CTU i (raster index) at d_ctu_first[i] .. d_ctu_first[i + 1] in decoding order; d_out (n records,
+ * must not alias) receives them grouped into the three phases, each phase in the diagonal order (CTU anti-diagonals x + 2y,
+ * the CTUs of a diagonal dealt record by record); d_phase_counts receives the three group sizes (pass it on in
+ * VVCB200IntraParams.d_phase_counts).  d_scratch: vvcb200_intra_schedule_scratch_bytes(n, ctus_w, ctus_h) bytes.
+ * What vvcb200_pic_intra uses (the host form costs ~8 ns per record on the calling thread).
+ */
+VVCB200_API size_t vvcb200_intra_schedule_scratch_bytes(int n, int ctus_w, int ctus_h);
+VVCB200_API int vvcb200_intra_schedule_device(const VVCB200IntraBlock *d_in, const uint32_t *d_ctu_first, int n, int ctus_w,
+                                              int ctus_h, VVCB200IntraBlock *d_out, int32_t *d_phase_counts, void *d_scratch,
+                                              void *stream);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
                                       const VVCB200Planes *d_shadow, const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);

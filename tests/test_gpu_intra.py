@@ -174,3 +174,56 @@ def test_dual_tree_picture_matches_oracle(seed, w, h, ctb):
     got = run_gpu(pic)[0]
     for c in range(3):
         assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)
+
+
+@pytest.mark.parametrize("seed,w,h,ctb", [(81, 416, 240, 6), (82, 832, 480, 7), (83, 136, 72, 5)])
+def test_device_schedule_is_the_phased_diagonal_order_and_reconstructs_the_oracle_picture(seed, w, h, ctb):
+    """vvcb200_intra_schedule_device: per phase, CTU anti-diagonals with the CTUs of a diagonal dealt record by record."""
+    import torch
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=True, intra_fraction=0.35)
+    ia = pic["intra"]
+    recs, cf = ia["blocks"], ia["ctu_first"].astype(np.uint32)
+    n, cw, ch = len(recs), (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    d_in = torch.from_numpy(recs.view(np.uint8).reshape(-1)).cuda()
+    d_cf = torch.from_numpy(cf.view(np.int32)).cuda()
+    d_out = torch.zeros_like(d_in)
+    d_counts = torch.zeros(4, dtype=torch.int32, device="cuda")
+    scratch = torch.zeros(lib.intra_schedule_scratch_bytes(n, cw, ch), dtype=torch.uint8, device="cuda")
+    lib.intra_schedule_device(d_in, d_cf, n, cw, ch, d_out, d_counts, scratch)
+    torch.cuda.synchronize()
+    got = d_out.cpu().numpy().view(abi.IB_DTYPE)
+    counts = d_counts.cpu().numpy()
+    ctu = np.repeat(np.arange(cw * ch), np.diff(cf.astype(np.int64)))
+    phase = np.where(recs["c_idx"] == 0, 0, np.where((recs["flags"] & abi.IB_ADD_ONLY) != 0, 1, 2))
+    k = np.zeros(n, np.int64)
+    for c in range(cw * ch):
+        for p in range(3):
+            m = np.nonzero((ctu == c) & (phase == p))[0]
+            k[m] = np.arange(len(m))
+    cy, cx = ctu // cw, ctu % cw
+    order = np.lexsort((cy, k, cx + 2 * cy, phase))
+    assert list(counts[:3]) == [int((phase == p).sum()) for p in range(3)]
+    assert got.tobytes() == recs[order].tobytes()
+    # and the picture reconstructed from that order, the counts staying on the device
+    want = oracle_to_intra(pic)
+    dev = util.to_device_planes([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], torch)
+    dpl = lib.device_planes(dev)
+    it, rs = pic["inter"], pic["residual"]
+    refs = [util.to_device_planes(r, torch) for r in it["refs"]]
+    prof = it.get("prof")
+    lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], torch.from_numpy(it["blocks"].view(np.uint8).reshape(-1)).cuda(),
+                    len(it["blocks"]), it["params"], lmcs_fwd_lut=torch.from_numpy(pic["lmcs"][0]).cuda(),
+                    prof=torch.from_numpy(prof.view(np.uint8).reshape(-1)).cuda() if prof is not None and len(prof) else None)
+    res = [torch.zeros_like(t) for t in dev]
+    rpl = lib.device_planes(res)
+    lib.residual_batch(dpl, torch.from_numpy(rs["levels"]).cuda(), torch.from_numpy(rs["tbs"].view(np.uint8).reshape(-1)).cuda(),
+                       len(rs["tbs"]), rs["params"], residual=rpl)
+    ip = abi.IntraParams.from_buffer_copy(bytes(ia["params"]))
+    ip.d_phase_counts = d_counts.data_ptr()
+    marks = torch.zeros(lib.intra_scratch_bytes(w, h), dtype=torch.uint8, device="cuda")
+    side = [torch.zeros_like(t) for t in dev]
+    lib.intra_picture(dpl, rpl, d_out, n, ip, marks, shadow=lib.device_planes(side))
+    torch.cuda.synchronize()
+    got_pic = util.from_device_planes(dev)
+    for c in range(3):
+        assert np.array_equal(got_pic[c], want[c]), "plane %d differs" % c
