@@ -26,7 +26,7 @@ assert TB_DTYPE.itemsize == 24
 class ResidualParams(C.Structure):
     _fields_ = [
         ("bit_depth", C.c_int32), ("log2_transform_range", C.c_int32),
-        ("joint_c_sign", C.c_int32), ("reserved", C.c_int32), ("n_class", C.c_int32 * 4),
+        ("joint_c_sign", C.c_int32), ("levels_sparse", C.c_int32), ("n_class", C.c_int32 * 4),
         ("scaling_matrix_rec", (C.c_uint8 * 64) * 28),
         ("scaling_matrix_dc_rec", C.c_uint8 * 14),
         ("pad", C.c_uint8 * 2),
@@ -211,7 +211,7 @@ IB_DTYPE = np.dtype([
     ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("c_idx", "u1"), ("mode", "i1"), ("ref_idx", "u1"),
     ("flags", "u1"), ("mip_mode", "u1"), ("up_left", "u1"), ("avail_top", "<u2"), ("avail_left", "<u2"),
     ("cb_w", "u1"), ("cb_h", "u1"), ("ciip_weight", "u1"), ("res_planes", "u1"),
-    ("vpdu_x", "u1"), ("vpdu_y", "u1"), ("vpdu_avail", "u1"), ("reserved3", "u1"), ("reserved2", "<u4"),
+    ("vpdu_x", "u1"), ("vpdu_y", "u1"), ("vpdu_avail", "u1"), ("isp_coded", "u1"), ("reserved2", "<u4"),
 ], align=False)
 assert IB_DTYPE.itemsize == 28
 
@@ -221,3 +221,11 @@ class IntraParams(C.Structure):
                 ("lmcs_chroma_scale", C.c_int32), ("lmcs_pivot", C.c_uint16 * 17), ("lmcs_chroma_scale_coeff", C.c_uint16 * 16),
                 ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("pad", C.c_uint8 * 4),
                 ("n_luma", C.c_int32), ("n_add_only", C.c_int32), ("d_phase_counts", C.c_void_p)]
+
+
+class Window(C.Structure):
+    _fields_ = [("crop_left", C.c_int32), ("crop_right", C.c_int32), ("crop_top", C.c_int32), ("crop_bottom", C.c_int32)]
+
+
+class Export(C.Structure):
+    _fields_ = [("planes", Planes), ("ready", C.c_void_p)]

@@ -119,7 +119,7 @@ extern "C" int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes
                                    const VVCB200AlfParams *d_params, int ctb_log2_size, int bit_depth, void *stream)
 {
     if (!dst || !src || !d_ctbs || !d_params || ctb_log2_size < 5 || ctb_log2_size > 7 ||
-        (bit_depth != 8 && bit_depth != 10 && bit_depth != 12)) {
+        (bit_depth != 10 && bit_depth != 12)) {
         set_error("vvcb200_alf_picture: bad argument");
         return VVCB200_ERR_ARG;
     }

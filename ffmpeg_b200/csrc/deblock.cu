@@ -494,8 +494,8 @@ extern "C" int vvcb200_deblock_picture(const VVCB200Planes *pic, const VVCB200De
         set_error("vvcb200_deblock_picture: bad argument");
         return VVCB200_ERR_ARG;
     }
-    if (p->bit_depth != 8 && p->bit_depth != 10 && p->bit_depth != 12) {
-        set_error("unsupported bit depth %d (8, 10 or 12)", p->bit_depth);
+    if (p->bit_depth != 10 && p->bit_depth != 12) {
+        set_error("unsupported bit depth %d (10 or 12: 8-bit pictures are uint8 planes in the reference, which are not built)", p->bit_depth);
         return VVCB200_ERR_ARG;
     }
     if (p->ctb_log2_size < 5 || p->ctb_log2_size > 7 || p->num_ladf_intervals > 5) {

@@ -96,6 +96,7 @@ struct VVCB200Ctx {
     std::vector<cudaEvent_t> written;      // per DPB slot: last kernel / copy that wrote the slot (its writer's stream)
     std::vector<signed char> writer;       // per DPB slot: lane of that write, -1 if none yet
     std::vector<unsigned char> readers;    // per DPB slot: lanes that have used it as a reference since
+    std::vector<cudaEvent_t> released;     // per DPB slot: a consumer's "done reading" event (vvcb200_pic_release), or null
     int cur = 0;
     Lane lanes[kLanes];
     StageSet sets[kSets];
@@ -187,6 +188,10 @@ int order_before_write(VVCB200Ctx *c, int slot)
         VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->downloaded[slot], 0));
         c->download_pending[slot] = 0;
     }
+    if (c->released[slot]) {              // an exported picture whose consumer may still be reading
+        VVC_CUDA(cudaStreamWaitEvent(lane_stream(c), c->released[slot], 0));
+        c->released[slot] = nullptr;
+    }
     c->readers[slot] = 0;
     return 0;
 }
@@ -240,8 +245,8 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
         set_error("vvcb200_ctx_create: bad dimensions %dx%d (multiples of 8 up to 16384)", width, height);
         return VVCB200_ERR_ARG;
     }
-    if (bit_depth != 8 && bit_depth != 10 && bit_depth != 12) {
-        set_error("vvcb200_ctx_create: unsupported bit depth %d", bit_depth);
+    if (bit_depth != 10 && bit_depth != 12) {
+        set_error("vvcb200_ctx_create: unsupported bit depth %d (10 or 12; 8-bit pictures are uint8 planes in the reference, not built)", bit_depth);
         return VVCB200_ERR_ARG;
     }
     if (dpb_size < 1 || dpb_size > 17) {
@@ -288,6 +293,7 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     c->download_pending.assign(dpb_size, 0);
     c->writer.assign(dpb_size, -1);
     c->readers.assign(dpb_size, 0);
+    c->released.assign(dpb_size, nullptr);
     for (int i = 0; i < dpb_size && e == cudaSuccess; i++) {
         e = cudaEventCreateWithFlags(&c->downloaded[i], cudaEventDisableTiming);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->written[i], cudaEventDisableTiming);
@@ -400,6 +406,7 @@ int vvcb200_ctx_sync(VVCB200Ctx *c)
         c->writer[i] = -1;
         c->readers[i] = 0;
     }
+    // (c->released stays: the consumer's event belongs to another stream)
     return 0;
 }
 
@@ -507,6 +514,88 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
     for (int i = 0; i < 3; i++)
         VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
                                    (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->d2h));
+    VVC_CUDA(cudaEventRecord(c->downloaded[idx], c->d2h));
+    c->download_pending[idx] = 1;
+    return 0;
+}
+
+static int window_of(VVCB200Ctx *c, const VVCB200Window *w, VVCB200Window &out, const char *who)
+{
+    out = w ? *w : VVCB200Window{ 0, 0, 0, 0 };
+    if (out.crop_left < 0 || out.crop_right < 0 || out.crop_top < 0 || out.crop_bottom < 0 ||
+        ((out.crop_left | out.crop_right | out.crop_top | out.crop_bottom) & 1) ||
+        out.crop_left + out.crop_right >= c->width || out.crop_top + out.crop_bottom >= c->height) {
+        set_error("%s: bad window (crop %d %d %d %d of %dx%d; even luma values)", who, out.crop_left, out.crop_right,
+                  out.crop_top, out.crop_bottom, c->width, c->height);
+        return VVCB200_ERR_ARG;
+    }
+    return 0;
+}
+
+static void window_planes(VVCB200Ctx *c, const VVCB200Planes &pl, const VVCB200Window &w, VVCB200Planes &out)
+{
+    for (int i = 0; i < 3; i++) {
+        const int hs = i ? c->hshift : 0, vs = i ? c->vshift : 0;
+        out.d_plane[i] = (uint8_t *)pl.d_plane[i] + (size_t)(w.crop_top >> vs) * pl.stride[i] + (size_t)(w.crop_left >> hs) * 2;
+        out.stride[i] = pl.stride[i];
+        out.width[i] = pl.width[i] - ((w.crop_left + w.crop_right) >> hs);
+        out.height[i] = pl.height[i] - ((w.crop_top + w.crop_bottom) >> vs);
+    }
+}
+
+int vvcb200_pic_export(VVCB200Ctx *c, int slot, const VVCB200Window *window, VVCB200Export *out)
+{
+    if (!c || !out || slot >= (int)c->dpb.size()) {
+        set_error("vvcb200_pic_export: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    VVCB200Window w;
+    if (int r = window_of(c, window, w, "vvcb200_pic_export"))
+        return r;
+    DeviceGuard g(c->device);
+    const int idx = slot < 0 ? c->cur : slot;
+    if (idx == c->cur)
+        if (int r = settle_picture(c))
+            return r;
+    window_planes(c, c->dpb[idx].planes, w, out->planes);
+    if (c->writer[idx] < 0)               // nothing in flight wrote it: an event that is complete already
+        VVC_CUDA(cudaEventRecord(c->written[idx], c->lanes[0].stream));
+    out->ready = (void *)c->written[idx];
+    return 0;
+}
+
+int vvcb200_pic_release(VVCB200Ctx *c, int slot, void *consumer_done)
+{
+    if (!c || slot >= (int)c->dpb.size()) {
+        set_error("vvcb200_pic_release: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    c->released[slot < 0 ? c->cur : slot] = (cudaEvent_t)consumer_done;
+    return 0;
+}
+
+int vvcb200_pic_download_window(VVCB200Ctx *c, int slot, const VVCB200Window *window, uint16_t *const planes[3],
+                                const int32_t strides[3])
+{
+    if (!c || !planes || !strides || slot >= (int)c->dpb.size()) {
+        set_error("vvcb200_pic_download_window: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    VVCB200Window w;
+    if (int r = window_of(c, window, w, "vvcb200_pic_download_window"))
+        return r;
+    DeviceGuard g(c->device);
+    const int idx = slot < 0 ? c->cur : slot;
+    if (idx == c->cur)
+        if (int r = settle_picture(c))
+            return r;
+    VVCB200Planes pl;
+    window_planes(c, c->dpb[idx].planes, w, pl);
+    if (c->writer[idx] >= 0)
+        VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->written[idx], 0));
+    for (int i = 0; i < 3; i++)
+        VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], pl.d_plane[i], pl.stride[i], (size_t)pl.width[i] * 2, pl.height[i],
+                                   cudaMemcpyDeviceToHost, c->d2h));
     VVC_CUDA(cudaEventRecord(c->downloaded[idx], c->d2h));
     c->download_pending[idx] = 1;
     return 0;
@@ -877,6 +966,43 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
 }  // extern "C"
 
 // ---- host-side descriptor producers ----------------------------------------------------------------------
+extern "C" int vvcb200_pack_levels_sparse(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int16_t *out, size_t out_cap,
+                                          size_t *out_len)
+{
+    if (!dense || !tbs || !out || !out_len || n < 0) {
+        set_error("vvcb200_pack_levels_sparse: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    size_t o = 0;
+    for (int t = 0; t < n; t++) {
+        const int box = tbs[t].nzw * tbs[t].nzh, words = (box + 31) >> 5;
+        const int16_t *lv = dense + tbs[t].coeff_off;
+        if (o + 2 * (size_t)words + box > out_cap) {
+            set_error("vvcb200_pack_levels_sparse: output buffer too small");
+            return VVCB200_ERR_TOO_BIG;
+        }
+        uint32_t *bitmap = reinterpret_cast<uint32_t *>(out + o);     // o stays even: 2 * words + an even number of levels
+        int16_t *nz = out + o + 2 * words;
+        int count = 0;
+        for (int w = 0; w < words; w++) {
+            uint32_t bits = 0;
+            const int lim = box - 32 * w < 32 ? box - 32 * w : 32;
+            for (int b = 0; b < lim; b++)
+                if (lv[32 * w + b]) {
+                    bits |= 1u << b;
+                    nz[count++] = lv[32 * w + b];
+                }
+            bitmap[w] = bits;
+        }
+        if (count & 1)
+            nz[count++] = 0;                                          // keep the next block's bitmap 4-byte aligned
+        tbs[t].coeff_off = (uint32_t)o;
+        o += 2 * (size_t)words + count;
+    }
+    *out_len = o;
+    return 0;
+}
+
 extern "C" int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const uint8_t *const bs[2][3],
                                           const uint8_t *const len_p[2], const uint8_t *const len_q[2],
                                           const uint8_t *tb_w_c, const uint8_t *tb_h_c,

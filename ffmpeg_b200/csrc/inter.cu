@@ -716,8 +716,8 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
         set_error("vvcb200_inter_batch: bad argument (n_refs must be 1..%d)", kMaxRefs);
         return VVCB200_ERR_ARG;
     }
-    if (params->bit_depth != 8 && params->bit_depth != 10 && params->bit_depth != 12) {
-        set_error("unsupported bit depth %d (8, 10 or 12)", params->bit_depth);
+    if (params->bit_depth != 10 && params->bit_depth != 12) {
+        set_error("unsupported bit depth %d (10 or 12: 8-bit pictures are uint8 planes in the reference, which are not built)", params->bit_depth);
         return VVCB200_ERR_ARG;
     }
     if (params->n_w16 < 0 || params->n_w8 < 0 || params->n_w16 + params->n_w8 > n) {

@@ -447,10 +447,30 @@ __host__ __device__ inline int cclm_deps(const VVCB200IntraBlock &b, Span *out)
 
 // sub-partition k of an ISP record (vvc_intra.c:217-226): geometry and the availability that follows from the
 // coding block's; returns the skip_wait bits
+// Transform partitions of an ISP coding block (vvc_ctu.c: 4x8 / 8x4 blocks split in two, all others in four) and the
+// width of one when the split is vertical (a horizontal split always has h < cb_h, a vertical one h == cb_h; with
+// partitions narrower than 4 the prediction unit is 4 wide and spans several of them, vvc_intra.c:217-226).
+__host__ __device__ inline int isp_tb_count(const VVCB200IntraBlock &b) { return b.cb_w * b.cb_h == 32 ? 2 : 4; }
+__host__ __device__ inline bool isp_vertical(const VVCB200IntraBlock &b) { return b.h == b.cb_h; }
+
 __host__ __device__ inline int isp_part(const VVCB200IntraBlock &b, int k, VVCB200IntraBlock &s)
 {
     const bool hor = b.w == b.cb_w;
     s = b;
+    // which of the transform partitions inside prediction unit k carry a residual (isp_coded): the others add nothing,
+    // whatever the residual planes hold there
+    if (b.flags & VVCB200_IB_RESIDUAL) {
+        int bits;
+        if (isp_vertical(b)) {
+            const int ratio = b.w / (b.cb_w / isp_tb_count(b));
+            bits = (b.isp_coded >> (k * ratio)) & ((1 << ratio) - 1);
+        } else {
+            bits = (b.isp_coded >> k) & 1;
+        }
+        s.isp_coded = (uint8_t)bits;
+        if (!bits)
+            s.flags &= ~VVCB200_IB_RESIDUAL;
+    }
     if (hor) {
         s.y0 += k * b.h;
         s.avail_left = imax((int)b.avail_left - k * b.h, 0);
@@ -620,12 +640,13 @@ struct Store {                    // what happens to a predicted sample on its w
     const int16_t *res;           // staged residual block (shared memory, rows of w), or null
     const uint16_t *inter;        // CIIP: staged inter prediction (shared memory, rows of w)
     int dstride, w, bd, ciip_w, lscale;
+    int res_cols, res_shift;      // ISP: bit (x >> res_shift) of res_cols says whether column x lies in a coded partition
     __device__ __forceinline__ void put(int x, int y, int pred) const
     {
         uint16_t *d = dst + (size_t)y * dstride + x;
         if (ciip_w)                                                       // put_ciip, vvc_inter_template.c:60-76
             pred = (pred * ciip_w + (int)inter[y * w + x] * (4 - ciip_w) + 2) >> 2;
-        if (res) {                                                        // add_residual, vvc_itx_1d / vvcdsp.h:154
+        if (res && ((res_cols >> (x >> res_shift)) & 1)) {                // add_residual, vvc_itx_1d / vvcdsp.h:154
             int r = res[y * w + x];
             if (lscale)
                 r = scale_chroma_residual(r, lscale, bd);
@@ -857,6 +878,13 @@ __device__ bool predict_record(const IntraArgs &a, const CtaTables &tb, const VV
     st.inter = reinterpret_cast<const uint16_t *>(extra_buf);
     st.w = w;
     st.lscale = lscale;
+    st.res_cols = 1;
+    st.res_shift = 8;                                                     // every column maps to bit 0
+    if (isp && !c && has_res) {
+        st.res_cols = b.isp_coded;
+        if (isp_vertical(b))
+            st.res_shift = ilog2(b.cb_w / isp_tb_count(b));
+    }
     const long long g1 = PROF_T();
     stage_wait();                                                         // residual / inter prediction are in shared memory
     __syncwarp();
@@ -1729,6 +1757,15 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     }
     if (!n)
         return 0;
+    // the pre-pass and the staging copies move 8 bytes at a time
+    for (int c = 0; c < 3; c++) {
+        if (((uintptr_t)pic->d_plane[c] & 7) || (pic->stride[c] & 7) ||
+            (d_residual && (((uintptr_t)d_residual->d_plane[c] & 7) || (d_residual->stride[c] & 7)))) {
+            set_error("vvcb200_intra_picture: planes of pic and d_residual must be 8-byte aligned with strides that are multiples "
+                      "of 8 bytes (plane %d)", c);
+            return VVCB200_ERR_ARG;
+        }
+    }
     IntraArgs a;
     a.pic = make_view(pic);
     for (int c = 0; c < 3; c++) {

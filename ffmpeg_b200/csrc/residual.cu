@@ -43,7 +43,36 @@ struct ResidualArgs {
     int first, last;                         // the blocks of this launch's class
     int bd, range, c_sign;
     int to_residual;
+    int sparse;                              // levels come as bitmap + non-zero values (VVCB200ResidualParams.levels_sparse)
 };
+
+// The levels of one TB's scan box (nzw x nzh, row-major) into `dst`, by the `lpt` lanes of a group (lane li).
+// Dense: the box as it is.  Sparse: ceil(n / 32) bitmap words (bit i % 32 of word i / 32 set = level i is non-zero) followed
+// by the non-zero levels in box order; a lane walks its positions i = li, li + lpt, ... with a running count of the bits
+// before the word it is in, so a level's place is that count plus the bits below its own in the word.
+__device__ __forceinline__ void fetch_levels(const ResidualArgs &a, const VVCB200TransformBlock &d, int16_t *dst, int li, int lpt)
+{
+    const int n = d.nzw * d.nzh;
+    const int16_t *lv = a.levels + d.coeff_off;
+    if (!a.sparse) {
+        for (int i = li; i < n; i += lpt)
+            dst[i] = lv[i];
+        return;
+    }
+    const uint32_t *bitmap = reinterpret_cast<const uint32_t *>(lv);
+    const int16_t *nz = lv + 2 * ((n + 31) >> 5);
+    int cur = -1, before = 0;
+    uint32_t word = 0;
+    for (int i = li; i < n; i += lpt) {
+        const int wi = i >> 5;
+        while (cur < wi) {                               // (at most once per word: lpt <= 32)
+            before += __popc(word);
+            word = __ldg(bitmap + ++cur);
+        }
+        const uint32_t bit = 1u << (i & 31);
+        dst[i] = (word & bit) ? nz[before + __popc(word & (bit - 1))] : (int16_t)0;
+    }
+}
 
 // Packed matrix of (type, log2N) in shared memory: word [kp * (N/2) + jp], see tools/gen_tables.py
 __device__ __forceinline__ const uint32_t *tx_packed(const uint32_t *smat, int type, int log2n)
@@ -386,7 +415,6 @@ __device__ __forceinline__ void fast_block(const ResidualArgs &a, const ScalingL
 {
     const int w = 1 << d.log2_w, h = 1 << d.log2_h;
     const int nzw = d.nzw, nzh = d.nzh;
-    const int16_t *lv = a.levels + d.coeff_off;
     const Epilogue ep = make_epilogue(a, d);
     const int sh1 = 5 + a.range - a.bd;
     const bool dconly = d.trh == VVCB200_DCT2 && d.trv == VVCB200_DCT2 && nzw == 1 && nzh == 1 && w == h;
@@ -395,8 +423,7 @@ __device__ __forceinline__ void fast_block(const ResidualArgs &a, const ScalingL
         asm volatile("prefetch.global.L1 [%0];" ::"l"(ep.dst + li * ep.stride));
     // levels: coalesced fetch into the (still free) middle buffer
     if (active)
-        for (int i = li; i < nzw * nzh; i += lpt)
-            fmid[i] = lv[i];
+        fetch_levels(a, d, fmid, li, lpt);
     __syncwarp();
     if (active && dconly) {
         // DC-only square DCT-II block (vvcdsp.c:101-108): one value for the whole block
@@ -471,7 +498,6 @@ __device__ __forceinline__ void generic_block(const ResidualArgs &a, const Scali
 {
     const int w = 1 << d.log2_w, h = 1 << d.log2_h;
     const bool ts = d.flags & VVCB200_TB_TS;
-    const int16_t *lv = a.levels + d.coeff_off;
     int nzw = d.nzw, nzh = d.nzh, in_stride = d.nzw;
     const Dequant q = make_dequant(d, ts, a.bd, a.range);
     const Epilogue ep = make_epilogue(a, d);
@@ -480,9 +506,11 @@ __device__ __forceinline__ void generic_block(const ResidualArgs &a, const Scali
     // ---- levels into shared memory (+ BDPCM prefix sums on the raw levels)
     if (d.flags & VVCB200_TB_BDPCM) {
         in_stride = w;
+        fetch_levels(a, d, mid, lane, 32);                // the scan box first (mid is free until the column pass)
+        __syncwarp();
         for (int i = lane; i < w * h; i += 32) {
             const int y = i >> d.log2_w, x = i & (w - 1);
-            in[i] = (x < nzw && y < nzh) ? lv[y * nzw + x] : (int16_t)0;
+            in[i] = (x < nzw && y < nzh) ? mid[y * nzw + x] : (int16_t)0;
         }
         __syncwarp();
         if (d.flags & VVCB200_TB_BDPCM_VERT) {
@@ -506,8 +534,7 @@ __device__ __forceinline__ void generic_block(const ResidualArgs &a, const Scali
         }
         __syncwarp();
     } else {
-        for (int i = lane; i < nzw * nzh; i += 32)
-            in[i] = lv[i];
+        fetch_levels(a, d, in, lane, 32);
         __syncwarp();
     }
     // ---- dequant (vvc_intra.c:277-417)
@@ -723,6 +750,11 @@ extern "C" int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Pla
     a.bd = params->bit_depth;
     a.range = params->log2_transform_range;
     a.c_sign = params->joint_c_sign;
+    a.sparse = params->levels_sparse != 0;
+    if (a.sparse && ((uintptr_t)d_levels & 3)) {
+        set_error("vvcb200_residual_batch: a sparse level buffer must be 4-byte aligned");
+        return VVCB200_ERR_ARG;
+    }
     ScalingLists sl;
     memcpy(sl.rec, params->scaling_matrix_rec, sizeof(sl.rec));
     memset(sl.dc, 16, sizeof(sl.dc));

@@ -253,7 +253,7 @@ extern "C" int vvcb200_sao_picture(const VVCB200Planes *dst, const VVCB200Planes
                                    int ctb_log2_size, int bit_depth, void *stream)
 {
     if (!dst || !src || !d_ctbs || ctb_log2_size < 5 || ctb_log2_size > 7 ||
-        (bit_depth != 8 && bit_depth != 10 && bit_depth != 12)) {
+        (bit_depth != 10 && bit_depth != 12)) {
         set_error("vvcb200_sao_picture: bad argument");
         return VVCB200_ERR_ARG;
     }
@@ -281,7 +281,7 @@ extern "C" int vvcb200_sao_picture(const VVCB200Planes *dst, const VVCB200Planes
 
 extern "C" int vvcb200_lmcs_picture(const VVCB200Planes *pic, const uint16_t *d_lut, int bit_depth, void *stream)
 {
-    if (!pic || !d_lut || (bit_depth != 8 && bit_depth != 10 && bit_depth != 12)) {
+    if (!pic || !d_lut || (bit_depth != 10 && bit_depth != 12)) {
         set_error("vvcb200_lmcs_picture: bad argument");
         return VVCB200_ERR_ARG;
     }

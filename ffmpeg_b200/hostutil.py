@@ -34,7 +34,7 @@ def from_device_planes(tensors):
 class EnginePicture:
     """Pinned host copies of one picture's batches + the Level-B call sequence (HOST buffers in, HOST planes out)."""
 
-    def __init__(self, ctx, pic, max_slots=4, want_mv=True):
+    def __init__(self, ctx, pic, max_slots=4, want_mv=True, sparse_levels="auto"):
         it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
         self.ctx, self.pic = ctx, pic
         self.n_refs = len(it["refs"])
@@ -42,8 +42,17 @@ class EnginePicture:
         self.blocks = ctx.pinned_copy(it["blocks"])
         prof = it.get("prof")
         self.prof = ctx.pinned_copy(prof) if prof is not None and len(prof) else None
-        self.levels = ctx.pinned_copy(rs["levels"])
-        self.tbs = ctx.pinned_copy(rs["tbs"])
+        # levels travel as dense scan boxes or in the sparse form (bitmap + non-zero values), whichever is smaller for the
+        # picture (the synthetic pictures fill their scan boxes to 95 %, real residuals to a third or less)
+        self.res_params = rs["params"]
+        levels, tbs = rs["levels"], rs["tbs"]
+        if sparse_levels and len(tbs):
+            sp_levels, sp_tbs = lib.pack_levels_sparse(levels, tbs)
+            if sparse_levels is True or sp_levels.nbytes < levels.nbytes:     # "auto": whichever form is smaller, as an emitter would
+                levels, tbs = sp_levels, sp_tbs
+                self.res_params = lib.sparse_params(rs["params"])
+        self.levels = ctx.pinned_copy(levels)
+        self.tbs = ctx.pinned_copy(tbs)
         edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
         self.edge = ctx.pinned_copy(edge)
         self.qp = ctx.pinned_copy(db["qp"])
@@ -97,7 +106,7 @@ class EnginePicture:
         if len(self.blocks):
             ctx.inter(self.blocks, pic["inter"]["params"], None if self.luts is None else self.luts[0],
                       refined_mv=self.refined[self.count % 4] if self.want_mv else None, prof=self.prof)
-        ctx.residual(self.levels, self.tbs, pic["residual"]["params"])
+        ctx.residual(self.levels, self.tbs, self.res_params)
         if self.intra is not None:
             ctx.intra(*self.intra)
         if self.luts is not None:

@@ -71,6 +71,24 @@ def device_planes(tensors):
     return p
 
 
+def pack_levels_sparse(levels, tbs):
+    """vvcb200_pack_levels_sparse (host, no CUDA): dense int16 level buffer + TB records -> (sparse buffer, TB records with
+    coeff_off into it).  Pair with a ResidualParams whose levels_sparse is 1 (sparse_params)."""
+    levels = np.ascontiguousarray(levels, np.int16)
+    out_tbs = np.ascontiguousarray(tbs, abi.TB_DTYPE).copy()
+    cap = levels.size + 2 * len(out_tbs) + 2 * (levels.size // 32) + 64
+    out = np.zeros(cap, np.int16)
+    n = C.c_size_t(0)
+    check(load().vvcb200_pack_levels_sparse(_ptr(levels), _ptr(out_tbs), len(out_tbs), _ptr(out), C.c_size_t(cap), C.byref(n)))
+    return out[:n.value].copy(), out_tbs
+
+
+def sparse_params(params):
+    p = abi.ResidualParams.from_buffer_copy(bytes(params))
+    p.levels_sparse = 1
+    return p
+
+
 def residual_batch(dst, levels, tbs, n, params, residual=None, stream=None):
     """vvcb200_residual_batch: dst/residual are device_planes() structs (or None), levels/tbs device tensors."""
     check(load().vvcb200_residual_batch(
@@ -228,6 +246,21 @@ class Context:
     def download(self, planes, slot=-1):
         ptrs, strides = self._plane_args(planes)
         check(load().vvcb200_pic_download(self._h, int(slot), ptrs, strides))
+
+    def export(self, slot=-1, window=None):
+        """vvcb200_pic_export: (Planes of the window in device memory, cudaEvent_t handle)."""
+        w = abi.Window(*window) if window is not None else None
+        out = abi.Export()
+        check(load().vvcb200_pic_export(self._h, int(slot), C.byref(w) if w is not None else None, C.byref(out)))
+        return out.planes, out.ready
+
+    def release(self, slot=-1, done_event=None):
+        check(load().vvcb200_pic_release(self._h, int(slot), C.c_void_p(done_event) if done_event else None))
+
+    def download_window(self, planes, window, slot=-1):
+        ptrs, strides = self._plane_args(planes)
+        w = abi.Window(*window)
+        check(load().vvcb200_pic_download_window(self._h, int(slot), C.byref(w), ptrs, strides))
 
     def inter(self, blocks, params, lmcs_fwd_lut=None, refined_mv=None, prof=None):
         assert blocks.dtype == abi.PB_DTYPE

@@ -360,47 +360,79 @@ def slice_map(rng, ctb_w, ctb_h, n_slices):
     return np.searchsorted(cuts, np.arange(n), side="right").astype(np.int16)
 
 
-def sao_no_filter_flags(slice_idx, ctb_w, ctb_h, lfase):
+def tile_grid(ctb_w, ctb_h, tile_cols, tile_rows, lfate):
+    """ctb_to_col_bd / ctb_to_row_bd (VVCPPS, first CTB column / row of the tile a CTB column / row belongs to, one entry
+    past the end included) for tile boundaries given as CTB indices, e.g. tile_cols=(0, 2): two tile columns."""
+    def bd(n, starts):
+        starts = sorted(set(int(v) for v in starts) | {0})
+        out = np.zeros(n + 1, np.uint16)
+        for i in range(n + 1):
+            out[i] = n if i == n else max(v for v in starts if v <= i)
+        return out
+    col, row = bd(ctb_w, tile_cols), bd(ctb_h, tile_rows)
+    return dict(col_bd=col, row_bd=row, num_tiles=len(set(col[:-1])) * len(set(row[:-1])), lfate=int(lfate))
+
+
+def sao_no_filter_flags(slice_idx, ctb_w, ctb_h, lfase, tiles=None):
     """Host-side derivation of VVCB200SaoCtb.no_filter (vert/horiz/diag_edge of ff_vvc_sao_filter,
-    reference vvc_filter.c:175-212) for one tile and pps_loop_filter_across_slices_enabled_flag = lfase."""
+    reference vvc_filter.c:163-212) from the slice map (pps_loop_filter_across_slices_enabled_flag = lfase) and the tile
+    grid (tile_grid(); its sides count when pps_loop_filter_across_tiles_enabled_flag is 0 and there is more than one tile)."""
     out = np.zeros(ctb_w * ctb_h, np.uint8)
-    if lfase:
+    no_tile = tiles is not None and tiles["num_tiles"] > 1 and not tiles["lfate"]
+    if lfase and not no_tile:
         return out
     s = slice_idx.reshape(ctb_h, ctb_w)
+    col = tiles["col_bd"] if tiles is not None else None
+    row = tiles["row_bd"] if tiles is not None else None
     for y in range(ctb_h):
         for x in range(ctb_w):
             L, T, R, B = x == 0, y == 0, x == ctb_w - 1, y == ctb_h - 1
+            lt = no_tile and not L and col[x] == x
+            rt = no_tile and not R and col[x] != col[x + 1]
+            ut = no_tile and not T and row[y] == y
+            bt = no_tile and not B and row[y] != row[y + 1]
+            sl = (lambda yy, xx: not lfase and s[y, x] != s[yy, xx])
             f = 0
-            if not L and s[y, x] != s[y, x - 1]: f |= 1
-            if not R and s[y, x] != s[y, x + 1]: f |= 2
-            if not T and s[y, x] != s[y - 1, x]: f |= 4
-            if not B and s[y, x] != s[y + 1, x]: f |= 8
-            if not L and not T and s[y, x] != s[y - 1, x - 1]: f |= 16
-            if not T and not R and s[y, x] != s[y - 1, x + 1]: f |= 32
-            if not R and not B and s[y, x] != s[y + 1, x + 1]: f |= 64
-            if not L and not B and s[y, x] != s[y + 1, x - 1]: f |= 128
+            if not L and (sl(y, x - 1) or lt): f |= 1
+            if not R and (sl(y, x + 1) or rt): f |= 2
+            if not T and (sl(y - 1, x) or ut): f |= 4
+            if not B and (sl(y + 1, x) or bt): f |= 8
+            if not L and not T and (sl(y - 1, x - 1) or lt or ut): f |= 16
+            if not T and not R and (sl(y - 1, x + 1) or rt or ut): f |= 32
+            if not R and not B and (sl(y + 1, x + 1) or rt or bt): f |= 64
+            if not L and not B and (sl(y + 1, x - 1) or lt or bt): f |= 128
             out[y * ctb_w + x] = f
     return out
 
 
-def alf_edge_flags(slice_idx, ctb_w, ctb_h, lfase):
-    """Host-side derivation of VVCB200AlfCtb.edges beyond the picture borders (reference vvc_filter.c:1273-1280)."""
+def alf_edge_flags(slice_idx, ctb_w, ctb_h, lfase, tiles=None):
+    """Host-side derivation of VVCB200AlfCtb.edges beyond the picture borders (reference vvc_filter.c:1264-1280)."""
     out = np.zeros(ctb_w * ctb_h, np.uint8)
-    if lfase:
+    no_tile = tiles is not None and not tiles["lfate"]
+    if lfase and not no_tile:
         return out
     s = slice_idx.reshape(ctb_h, ctb_w)
+    col = tiles["col_bd"] if tiles is not None else None
+    row = tiles["row_bd"] if tiles is not None else None
     for y in range(ctb_h):
         for x in range(ctb_w):
             f = 0
-            if x > 0 and s[y, x] != s[y, x - 1]: f |= 1
-            if y > 0 and s[y, x] != s[y - 1, x]: f |= 2
-            if x < ctb_w - 1 and s[y, x] != s[y, x + 1]: f |= 4
-            if y < ctb_h - 1 and s[y, x] != s[y + 1, x]: f |= 8
+            if not lfase:
+                if x > 0 and s[y, x] != s[y, x - 1]: f |= 1
+                if y > 0 and s[y, x] != s[y - 1, x]: f |= 2
+                if x < ctb_w - 1 and s[y, x] != s[y, x + 1]: f |= 4
+                if y < ctb_h - 1 and s[y, x] != s[y + 1, x]: f |= 8
+            if no_tile:
+                if x > 0 and col[x] != col[x - 1]: f |= 1
+                if y > 0 and row[y] != row[y - 1]: f |= 2
+                if x < ctb_w - 1 and col[x] != col[x + 1]: f |= 4
+                if y < ctb_h - 1 and row[y] != row[y + 1]: f |= 8
             out[y * ctb_w + x] = f
     return out
 
 
-def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on=0.85, cc_on=0.5, bd=10):
+def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on=0.85, cc_on=0.5, bd=10,
+                    tile_cols=None, tile_rows=None, lfate=1):
     """Per-CTB SAO and ALF parameters + the slice's ALF APS content (random, int8-range coefficients like
     tests/checkasm/vvc_alf.c:52-66; SAO offsets < 1 << (bd - 5) like tests/checkasm/vvc_sao.c:37)."""
     rng = np.random.default_rng(seed)
@@ -408,6 +440,7 @@ def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on
     ctb_h = (height + (1 << ctb_log2) - 1) >> ctb_log2
     n = ctb_w * ctb_h
     slices = slice_map(rng, ctb_w, ctb_h, n_slices)
+    tiles = tile_grid(ctb_w, ctb_h, tile_cols or (0,), tile_rows or (0,), lfate) if (tile_cols or tile_rows) else None
     sao = np.zeros(n, abi.SAO_DTYPE)
     sao["type_idx"] = rng.integers(0, 3, (n, 3))
     sao["band_position"] = rng.integers(0, 32, (n, 3))
@@ -415,13 +448,13 @@ def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on
     off = rng.integers(-(1 << (bd - 5)) + 1, 1 << (bd - 5), (n, 3, 5)).astype(np.int16)
     off[:, :, 0] = 0
     sao["offset_val"] = off
-    sao["no_filter"] = sao_no_filter_flags(slices, ctb_w, ctb_h, lfase)
+    sao["no_filter"] = sao_no_filter_flags(slices, ctb_w, ctb_h, lfase, tiles)
     alf = np.zeros(n, abi.ALF_CTB_DTYPE)
     alf["ctb_flag"] = rng.random((n, 3)) < alf_on
     alf["filt_set_idx_y"] = np.where(rng.random(n) < 0.4, rng.integers(0, 16, n), 16 + rng.integers(0, 6, n))
     alf["alt_idx"] = rng.integers(0, 8, (n, 2))
     alf["cc_idc"] = np.where(rng.random((n, 2)) < cc_on, rng.integers(1, 5, (n, 2)), 0)
-    alf["edges"] = alf_edge_flags(slices, ctb_w, ctb_h, lfase)
+    alf["edges"] = alf_edge_flags(slices, ctb_w, ctb_h, lfase, tiles)
     p = np.zeros(1, abi.ALF_PARAMS_DTYPE)
     p["bit_depth"], p["ctb_log2_size"] = bd, ctb_log2
     p["luma_coeff"] = rng.integers(-128, 128, (7, 25, 12))
@@ -431,7 +464,7 @@ def loopfilter_ctbs(seed, width, height, ctb_log2=7, n_slices=1, lfase=1, alf_on
     p["cc_coeff"] = rng.integers(-64, 64, (2, 4, 7))
     p["cc_enabled"] = 1
     return dict(sao=sao, alf=alf, alf_params=p, slice_idx=slices, lfase=lfase, ctb_log2=ctb_log2,
-                dims=plane_dims(width, height), seed=seed, bd=bd)
+                dims=plane_dims(width, height), seed=seed, bd=bd, tiles=tiles)
 
 
 def lmcs_luts(seed, bd=10):
@@ -950,6 +983,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                 else:
                     n_parts, pw, ph = 1, w, h
                 res_c = 0
+                isp_coded = 0
                 for k in range(n_parts):
                     tu = np.zeros(1, REF_TU_DTYPE)
                     tx, ty = (x, y + k * ph) if isp != 2 else (x + k * pw, y)
@@ -957,6 +991,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     tu["tb"] = -1
                     c0 = bool(coded[0]) if n_parts == 1 else bool(rng.random() < 0.7)
                     tu["coded_flag"][0, 0] = int(c0)
+                    isp_coded |= int(c0) << k
                     if c0:
                         code = lfnst_code(lfnst_idx, mode_y, w, h, 0) if lfnst_idx else 0
                         tu["tb"][0, 0] = new_tb(tx, ty, 0, pw, ph, False, trh, trv, qp_y, True, ts=ts_y, bdpcm=bdpcm_y, lfnst=code)
@@ -983,6 +1018,7 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
                     if c == 0 and isp:                # one record per coding block; w x h = the prediction unit
                         fl |= abi.IB_ISP
                         ib["w"], ib["h"] = max(pw, 4), ph
+                        ib["isp_coded"] = isp_coded
                     if (c == 0 and bdpcm_y) or (c and bdpcm_c):
                         fl |= abi.IB_BDPCM
                     if raw >= CCLM_LT:

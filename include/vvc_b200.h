@@ -94,7 +94,11 @@ typedef struct VVCB200ResidualParams {
     int32_t  bit_depth;             /* 8, 10 or 12 (sps->bit_depth)                                     */
     int32_t  log2_transform_range;  /* 15 (sps->log2_transform_range; extended precision is not built)  */
     int32_t  joint_c_sign;          /* 1 - 2 * ph_joint_cbcr_sign_flag (vvc_intra.c:171)                */
-    int32_t  reserved;
+    int32_t  levels_sparse;         /* 0: coeff_off points at the dense nzw x nzh box; 1: at the sparse form of it —
+                                       (nzw * nzh + 31) / 32 bitmap words of 32 bits (bit i % 32 of word i / 32: level i
+                                       of the box is non-zero), then the non-zero levels in box order; coeff_off even.
+                                       What hls_residual_coding knows anyway (its significance map, vvc_cabac.c:2141-2392);
+                                       vvcb200_pack_levels_sparse converts a dense buffer.                             */
     int32_t  n_class[4];            /* The batch is ordered by vvcb200_residual_class(): n_class[0] blocks of class 0, then
                                        class 1, 2, 3; the rest (class 4) follows.  Equal-class blocks share a warp.       */
     uint8_t  scaling_matrix_rec[28][64];   /* VVCScalingList.scaling_matrix_rec, vvc_ps.h:187-190      */
@@ -102,7 +106,10 @@ typedef struct VVCB200ResidualParams {
     uint8_t  pad[2];
 } VVCB200ResidualParams;
 
-/* A picture (or any sample array triple) resident in device memory. */
+/* A picture (or any sample array triple) resident in device memory.  Alignment: the stand-alone stage entries accept any
+ * 2-byte aligned planes unless they say otherwise; vvcb200_intra_picture wants planes and strides that are multiples of 8
+ * bytes, the fused passes (vvcb200_deblock_lmcs_picture, vvcb200_sao_alf_picture) multiples of 16 — what
+ * vvcb200_ctx_create allocates (256-byte rows). */
 typedef struct VVCB200Planes {
     void     *d_plane[3];      /* device pointers, 16-bit samples */
     int32_t   stride[3];       /* bytes                           */
@@ -137,6 +144,13 @@ VVCB200_API int vvcb200_dsp_add_residual_batch(const VVCB200Planes *dst, const i
 /* Lane-group class of a transform block (host helper, no CUDA): 0..3 = 2-D transform done with 32 / 16 / 8 / 4 lanes
  * (largest side >= 32 / 16 / 8 / <= 4), 4 = generic (transform skip, BDPCM, LFNST, 1-D).  Emitters keep one list per class. */
 VVCB200_API int vvcb200_residual_class(const VVCB200TransformBlock *tb);
+
+/* Host helper (pure CPU): rewrite a dense level buffer in the sparse form.  `tbs` (n records) are
+ * updated in place: coeff_off then indexes `out`.  `out` needs room for the worst case, n_dense + 2 * n + 2 * (n_dense / 32)
+ * int16; returns the number of int16 written through out_len.  Typical residuals (a fifth of the scan box non-zero)
+ * shrink 3-4x, which is most of what a picture uploads. */
+VVCB200_API int vvcb200_pack_levels_sparse(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int16_t *out,
+                                           size_t out_cap, size_t *out_len);
 
 VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
                            const int16_t *d_levels, const VVCB200TransformBlock *d_tbs, int n,
@@ -393,7 +407,10 @@ typedef struct VVCB200IntraBlock {
     /* VVCB200_IB_LMCS_SCALE: the VPDU of the coding unit's origin, in units of min(CTB size, 64) luma samples, and whether
      * the luma column left of it (bit 0) / the luma row above it (bit 1) is available (ff_vvc_get_left/top_available)     */
     uint8_t  vpdu_x, vpdu_y, vpdu_avail;
-    uint8_t  reserved3;
+    /* ISP records with VVCB200_IB_RESIDUAL: bit k set = transform partition k of the coding block (in coding order) has a
+     * coded residual (tu.coded_flag[0] of that partition's TransformUnit); the other partitions add nothing, whatever
+     * the residual planes hold there — vvcb200_residual_batch only writes the TBs it is given. */
+    uint8_t  isp_coded;
     uint32_t reserved2;
 } VVCB200IntraBlock;            /* 28 bytes */
 
@@ -427,7 +444,9 @@ typedef struct VVCB200IntraParams {
  * must therefore be topological (every record after the records it reads from): the decoding order is one, and
  * vvcb200_intra_schedule() builds better ones from per-CTU decoding-order records (see VVCB200_INTRA_ORDER_*).
  * d_residual: int16 residual planes written by vvcb200_residual_batch for TBs flagged VVCB200_TB_TO_RESIDUAL (may be
- * NULL if no record has VVCB200_IB_RESIDUAL).
+ * NULL if no record has VVCB200_IB_RESIDUAL).  Contract: a record flagged VVCB200_IB_RESIDUAL reads the planes over its
+ * whole block — except ISP records, which read only the partitions named in isp_coded — so every sample it reads must
+ * have been written by a TB of THIS picture; the planes are never cleared between pictures.
  * Luma-dependent chroma residual scaling (sh_lmcs_used_flag && ph_chroma_residual_scale_flag): the factor depends on
  * reconstructed luma, so the host cannot put it into VVCB200TransformBlock.lmcs_scale.  Instead every chroma TB of such
  * a picture (w * h > 4) is flagged VVCB200_TB_TO_RESIDUAL without VVCB200_TB_LMCS_SCALE, and its block gets a record
@@ -552,6 +571,36 @@ VVCB200_API int vvcb200_pic_sao_alf(VVCB200Ctx *ctx, const VVCB200SaoCtb *sao, c
                                     const VVCB200AlfParams *alf_params, int ctb_log2_size);
 /* Copy DPB slot `slot` (slot < 0: current picture) back to host memory (the AVFrame the decoder outputs). */
 VVCB200_API int vvcb200_pic_download(VVCB200Ctx *ctx, int slot, uint16_t *const planes[3], const int32_t strides[3]);
+
+/* ------------------------------------------------------------------------------------------------
+ * Output path: what the decoder does with a finished picture — crop to the conformance window
+ * (vvc_refs.c:188-191 sets AVFrame.crop_*, export_frame_params vvcdec.c:666-677 the visible size) and hand the
+ * frame on.  Two ways out:
+ *   vvcb200_pic_export          no copy: device planes of the window + an event, for a consumer on the same GPU (what an
+ *                               AV_PIX_FMT_CUDA frame carries: data[] = device pointers, linesize[] = pitch, plus the
+ *                               stream / event discipline of libavutil/hwcontext_cuda.c);
+ *   vvcb200_pic_download_window the download of vvcb200_pic_download restricted to the window.
+ * Crop values are in luma samples and must be even (4:2:0).
+ * ---------------------------------------------------------------------------------------------- */
+typedef struct VVCB200Window {
+    int32_t crop_left, crop_right, crop_top, crop_bottom;
+} VVCB200Window;
+
+typedef struct VVCB200Export {
+    VVCB200Planes planes;       /* device pointers to the window's first sample, width / height of the window, the
+                                   picture's own strides                                                               */
+    void         *ready;        /* cudaEvent_t owned by the context: recorded after the last operation that wrote the
+                                   picture; make the consuming stream wait for it (cudaStreamWaitEvent)                */
+} VVCB200Export;
+
+/* The planes stay valid and unchanged until the slot is handed to vvcb200_pic_begin / vvcb200_pic_upload again.  A consumer
+ * that may still be reading by then passes the cudaEvent_t it records after its last read to vvcb200_pic_release: the
+ * next writer of the slot waits for it (the event must stay alive until that writer has been enqueued). */
+VVCB200_API int vvcb200_pic_export(VVCB200Ctx *ctx, int slot, const VVCB200Window *window /* NULL: whole picture */,
+                                   VVCB200Export *out);
+VVCB200_API int vvcb200_pic_release(VVCB200Ctx *ctx, int slot, void *consumer_done /* cudaEvent_t or NULL */);
+VVCB200_API int vvcb200_pic_download_window(VVCB200Ctx *ctx, int slot, const VVCB200Window *window,
+                                            uint16_t *const planes[3], const int32_t strides[3]);
 
 #ifdef __cplusplus
 }

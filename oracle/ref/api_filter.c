@@ -24,6 +24,26 @@ typedef struct FilterEnv {
     uint16_t            *col_bd, *row_bd;
 } FilterEnv;
 
+/* Tile grid planted for the next SAO / ALF calls (test harness state, not thread-safe against concurrent re-planting):
+ * col_bd[x] / row_bd[y] = first CTB column / row of the tile that holds CTB column x / row y, one entry past the end
+ * included (VVCPPS.ctb_to_col_bd / ctb_to_row_bd, vvc_ps.c); n_cols == 0: one tile. */
+static uint16_t g_col_bd[520], g_row_bd[520];
+static int g_tile_cols, g_tile_rows, g_num_tiles = 1, g_lfate = 1;
+
+VVCREF_EXPORT int vvcref_set_tiles(const uint16_t *col_bd, int n_cols, const uint16_t *row_bd, int n_rows, int num_tiles,
+                                   int loop_filter_across_tiles)
+{
+    if (n_cols < 0 || n_rows < 0 || n_cols > 519 || n_rows > 519)
+        return -1;
+    g_tile_cols = n_cols;
+    g_tile_rows = n_rows;
+    for (int i = 0; i < n_cols; i++) g_col_bd[i] = col_bd[i];
+    for (int i = 0; i < n_rows; i++) g_row_bd[i] = row_bd[i];
+    g_num_tiles = n_cols ? num_tiles : 1;
+    g_lfate = n_cols ? loop_filter_across_tiles : 1;
+    return 0;
+}
+
 static FilterEnv *filter_env_new(const VVCRefPlanes *pl, int bit_depth, int ctb_log2)
 {
     FilterEnv *e = calloc(1, sizeof(*e));
@@ -64,6 +84,10 @@ static FilterEnv *filter_env_new(const VVCRefPlanes *pl, int bit_depth, int ctb_
     /* one tile, one slice: all CTBs map to tile column/row 0 */
     e->col_bd = calloc(e->pps.ctb_width + 2, sizeof(uint16_t));
     e->row_bd = calloc(e->pps.ctb_height + 2, sizeof(uint16_t));
+    if (g_tile_cols == (int)e->pps.ctb_width + 1 && g_tile_rows == (int)e->pps.ctb_height + 1) {
+        memcpy(e->col_bd, g_col_bd, g_tile_cols * sizeof(uint16_t));
+        memcpy(e->row_bd, g_row_bd, g_tile_rows * sizeof(uint16_t));
+    }
     e->pps.ctb_to_col_bd = e->col_bd;
     e->pps.ctb_to_row_bd = e->row_bd;
     e->fc.tab.slice_idx  = calloc(e->pps.ctb_count, sizeof(int16_t));
@@ -168,7 +192,8 @@ static void plant_slices(FilterEnv *e, const int16_t *slice_idx, int lfase)
     if (slice_idx)
         memcpy(e->fc.tab.slice_idx, slice_idx, e->pps.ctb_count * sizeof(int16_t));
     e->rpps.pps_loop_filter_across_slices_enabled_flag = lfase;
-    e->rpps.num_tiles_in_pic = 1;
+    e->rpps.num_tiles_in_pic = g_num_tiles;
+    e->rpps.pps_loop_filter_across_tiles_enabled_flag = g_lfate;
 }
 
 /*

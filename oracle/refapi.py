@@ -123,10 +123,22 @@ def deblock_picture(planes, t, threads=1):
         _parallel(lambda a, b: lib().vvcref_deblock_picture(*args, mask, a, b), chunks)
 
 
+def _plant_tiles(lf):
+    """Tile grid of synth.loopfilter_ctbs(tile_cols=..., tile_rows=...) for the next SAO / ALF calls (or one tile)."""
+    t = lf.get("tiles")
+    if t is None:
+        lib().vvcref_set_tiles(None, 0, None, 0, 1, 1)
+        return
+    col, row = np.ascontiguousarray(t["col_bd"], np.uint16), np.ascontiguousarray(t["row_bd"], np.uint16)
+    lib().vvcref_set_tiles(C.c_void_p(col.ctypes.data), len(col), C.c_void_p(row.ctypes.data), len(row), int(t["num_tiles"]),
+                           int(t["lfate"]))
+
+
 def sao_picture(planes, lf, bit_depth=None, threads=1):
     """Reference SAO stage in place; `lf` is synth.loopfilter_ctbs().  Phase 1 saves every CTB's pre-SAO borders,
     phase 2 filters; each phase may run CTB rows on several threads."""
     bit_depth = lf.get("bd", 10) if bit_depth is None else bit_depth
+    _plant_tiles(lf)
     pl = abi.host_planes(planes)
     sao = np.ascontiguousarray(lf["sao"])
     sl = np.ascontiguousarray(lf["slice_idx"], np.int16)
@@ -141,6 +153,7 @@ def sao_picture(planes, lf, bit_depth=None, threads=1):
 
 
 def alf_picture(planes, lf, threads=1):
+    _plant_tiles(lf)
     pl = abi.host_planes(planes)
     alf = np.ascontiguousarray(lf["alf"])
     sl = np.ascontiguousarray(lf["slice_idx"], np.int16)

@@ -58,3 +58,23 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     pl = abi.Planes()
     rc = l.vvcb200_residual_batch(C.byref(pl), None, None, None, 0, C.byref(p), None)
     assert rc == -1 and b"bit depth" in l.vvcb200_last_error()
+
+
+def test_sparse_level_packer_round_trips():
+    """vvcb200_pack_levels_sparse: bitmap + non-zero values per TB decode back to the dense scan boxes."""
+    import numpy as np
+    from ffmpeg_b200 import synth
+    pic = synth.residual_picture(3, 416, 240)
+    pic["levels"][::3] = 0
+    lv, tbs = lib.pack_levels_sparse(pic["levels"], pic["tbs"])
+    assert (tbs["coeff_off"] % 2 == 0).all()
+    for t_old, t_new in list(zip(pic["tbs"], tbs))[::37]:
+        n = int(t_old["nzw"]) * int(t_old["nzh"])
+        dense = pic["levels"][t_old["coeff_off"]:t_old["coeff_off"] + n]
+        words = (n + 31) // 32
+        off = int(t_new["coeff_off"])
+        bitmap = lv[off:off + 2 * words].view(np.uint32)
+        bits = np.unpackbits(bitmap.view(np.uint8), bitorder="little")[:n].astype(bool)
+        assert np.array_equal(bits, dense != 0)
+        nz = lv[off + 2 * words:off + 2 * words + int(bits.sum())]
+        assert np.array_equal(nz, dense[bits])

@@ -9,7 +9,7 @@ from tests import util
 pytestmark = pytest.mark.gpu
 
 
-def run_gpu(pic, schedule=True, repeat=1, shadow=False, phased=False):
+def run_gpu(pic, schedule=True, repeat=1, shadow=False, phased=False, stale_residual=False):
     """INTER -> RESIDUAL -> INTRA on the device, Level A calls only.  shadow: hand the call a second picture, so that
     blocks rewritten in place take the sentinel protocol too (else they go by marks and fences)."""
     import torch
@@ -24,7 +24,8 @@ def run_gpu(pic, schedule=True, repeat=1, shadow=False, phased=False):
         fwd = torch.from_numpy(pic["lmcs"][0]).cuda() if pic.get("lmcs") is not None else None
         lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], blocks, len(it["blocks"]), it["params"],
                         lmcs_fwd_lut=fwd, prof=prof)
-    res = [torch.zeros_like(t) for t in dev]
+    # stale_residual: the planes arrive full of another picture's leftovers; only what this picture's TBs write may be read
+    res = [torch.full_like(t, 0x2b67) if stale_residual else torch.zeros_like(t) for t in dev]
     rpl = lib.device_planes(res)
     if len(rs["tbs"]):
         tbs = torch.from_numpy(rs["tbs"].view(np.uint8).reshape(-1)).cuda()
@@ -227,3 +228,17 @@ def test_device_schedule_is_the_phased_diagonal_order_and_reconstructs_the_oracl
     got_pic = util.from_device_planes(dev)
     for c in range(3):
         assert np.array_equal(got_pic[c], want[c]), "plane %d differs" % c
+
+
+@pytest.mark.parametrize("seed,w,h,ctb", [(8, 208, 120, 6), (91, 416, 240, 7), (92, 136, 72, 5)])
+def test_uncoded_isp_partitions_add_nothing_whatever_the_residual_planes_hold(seed, w, h, ctb):
+    """ISP records carry one residual flag for the coding block; partitions without a coded TB (isp_coded) must not pick up
+    what an earlier picture left in the residual planes."""
+    pic = synth.recon_picture(seed, w, h, ctb_log2=ctb, tools=("isp", "pdpc", "mts", "cclm"), intra_fraction=0.9)
+    isp = pic["intra"]["blocks"][(pic["intra"]["blocks"]["flags"] & abi.IB_ISP) != 0]
+    assert len(isp) and (isp["isp_coded"] != 15).any(), "the picture needs partially coded ISP blocks"
+    want = util.oracle_recon([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], pic)
+    for shadow, phased in ((False, False), (True, "diagonal")):
+        got = run_gpu(pic, shadow=shadow, phased=phased, stale_residual=True)[0]
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs (shadow %s)" % (c, shadow)

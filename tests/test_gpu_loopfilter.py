@@ -145,3 +145,20 @@ def test_lmcs_lut_pass():
     got = util.from_device_planes(dev)
     assert np.array_equal(got[0], inv[base[0]])
     assert np.array_equal(got[1], base[1])
+
+
+@pytest.mark.parametrize("lfate", [0, 1])
+@pytest.mark.parametrize("ctb,w,h", [(5, 416, 240), (6, 416, 240), (7, 832, 480)])
+def test_two_by_two_tiles_match_reference(ctb, w, h, lfate):
+    """pps_loop_filter_across_tiles_enabled_flag 0 and 1 on a 2x2 tile grid with two slices (vvc_filter.c:163-212,
+    1264-1280): the host derives the per-CTB flags, the reference derives its own from ctb_to_col_bd / ctb_to_row_bd."""
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    lf = synth.loopfilter_ctbs(60 + ctb, w, h, ctb_log2=ctb, n_slices=2, lfase=0, tile_cols=(0, cw // 2), tile_rows=(0, ch // 2),
+                               lfate=lfate)
+    assert lf["tiles"]["num_tiles"] == 4
+    base = synth.smooth_planes(60, lf["dims"])
+    sao = oracle_sao(base, lf)
+    want = oracle_alf(sao, lf)
+    assert util.plane_md5(gpu_sao(base, lf)) == util.plane_md5(sao)
+    assert util.plane_md5(gpu_alf(sao, lf)) == util.plane_md5(want)
+    assert util.plane_md5(gpu_sao_alf(base, lf)) == util.plane_md5(want)

@@ -134,3 +134,59 @@ def test_full_picture_1080p_md5():
         assert util.plane_md5(ep.out) == util.plane_md5(want)
     finally:
         ctx.close()
+
+
+def test_different_pictures_on_one_lane_do_not_see_each_others_residuals():
+    """Two pictures with different CU / TB / ISP layouts alternate on the context: each lane's int16 residual picture is
+    allocated once and never cleared, so a picture must read only what its own TBs wrote."""
+    a = synth.full_picture(51, 416, 240, ctb_log2=6, lmcs=True, intra_fraction=0.6)
+    b = synth.full_picture(52, 416, 240, ctb_log2=6, lmcs=True, intra_fraction=0.6)
+    want = {id(a): util.plane_md5(pipeline.oracle_picture(a)), id(b): util.plane_md5(pipeline.oracle_picture(b))}
+    ctx = lib.Context(0, 416, 240, dpb_size=6)
+    try:
+        ea, eb = pipeline.EnginePicture(ctx, a), pipeline.EnginePicture(ctx, b)
+        ea.upload_refs()                                     # (both pictures' reference slots: a's and b's differ)
+        for seq in ((ea, ea, eb, eb, ea, ea), (eb, ea, ea, eb, eb, ea)):
+            for i, ep in enumerate(seq):
+                ep.upload_refs()
+                ep.count = i
+                ep.run()
+                ctx.sync()
+                assert util.plane_md5(ep.out) == want[id(ep.pic)], "picture %d of the sequence" % i
+    finally:
+        ctx.close()
+
+
+def test_export_and_windowed_download_crop_to_the_conformance_window():
+    """the picture leaves either as device planes of the conformance window plus a ready event (no copy), or as
+    a download of the window only; both must hold the oracle picture cropped the way AVFrame.crop_* says."""
+    import torch
+    pic = synth.full_picture(61, 416, 240, ctb_log2=6, intra_fraction=0.2)
+    want = pipeline.oracle_picture(pic)
+    win = (8, 16, 4, 12)                                    # left, right, top, bottom in luma samples
+    crop = [want[0][4:240 - 12, 8:416 - 16], want[1][2:120 - 6, 4:208 - 8], want[2][2:120 - 6, 4:208 - 8]]
+    ctx = lib.Context(0, 416, 240, dpb_size=4)
+    try:
+        ep = pipeline.EnginePicture(ctx, pic)
+        ep.upload_refs()
+        ep.run(download=False)
+        planes, ready = ctx.export(window=win)
+        assert ready and [planes.width[c] for c in range(3)] == [392, 196, 196] and [planes.height[c] for c in range(3)] == [224, 112, 112]
+        ev = torch.cuda.ExternalStream(ctx.stream())       # (the lane stream: later work on it is ordered behind the picture)
+        ev.synchronize()
+        got = util.read_device_planes(planes)
+        for c in range(3):
+            assert np.array_equal(got[c], crop[c]), "exported plane %d differs" % c
+        host = [ctx.pinned(p.shape, np.uint16) for p in crop]
+        ctx.download_window(host, win)
+        ctx.release()                                       # nothing else is reading: the slot may be rewritten
+        ctx.sync()
+        for c in range(3):
+            assert np.array_equal(host[c], crop[c]), "downloaded window plane %d differs" % c
+        # bad windows are refused
+        with pytest.raises(lib.VVCB200Error):
+            ctx.export(window=(3, 0, 0, 0))
+        with pytest.raises(lib.VVCB200Error):
+            ctx.export(window=(208, 208, 0, 0))
+    finally:
+        ctx.close()

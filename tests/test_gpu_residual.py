@@ -19,9 +19,12 @@ def _params_for(pic):
     return p
 
 
-def _run_gpu(pic, planes_np, to_residual=False):
+def _run_gpu(pic, planes_np, to_residual=False, sparse=False):
     import torch
     pic = dict(pic, params=_params_for(pic))
+    if sparse:
+        lv, tb = lib.pack_levels_sparse(pic["levels"], pic["tbs"])
+        pic = dict(pic, levels=lv, tbs=tb, params=lib.sparse_params(pic["params"]))
     dev = util.to_device_planes(planes_np, torch)
     tbs = torch.from_numpy(pic["tbs"].view(np.uint8).reshape(-1)).cuda()
     levels = torch.from_numpy(pic["levels"]).cuda()
@@ -46,6 +49,7 @@ def test_residual_batch_matches_oracle(seed, w, h, levels):
     for c in range(3):
         assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)
     assert util.plane_md5(got) == util.plane_md5(want)
+    assert util.plane_md5(_run_gpu(pic, base, sparse=True)) == util.plane_md5(want), "sparse level format"
 
 
 def test_residual_plane_mode_matches_oracle():
@@ -167,3 +171,18 @@ def test_level_b_context_host_buffers():
             assert util.plane_md5(out) == util.plane_md5(want)
     finally:
         ctx.close()
+
+
+def test_sparse_levels_with_mostly_empty_scan_boxes():
+    """A scan box filled to a quarter, as real residuals are: the sparse form is less than half the dense bytes and
+    reconstructs the same picture; Level B takes the smaller form by itself."""
+    pic = synth.residual_picture(12, 416, 240)
+    rng = np.random.default_rng(12)
+    pic = dict(pic, levels=np.where(rng.random(pic["levels"].shape) < 0.25, pic["levels"], 0).astype(np.int16))
+    lv, _ = lib.pack_levels_sparse(pic["levels"], pic["tbs"])
+    assert lv.nbytes < 0.5 * pic["levels"].nbytes
+    base = util.noise_planes(12, pic["dims"])
+    want = [p.copy() for p in base]
+    util.oracle_residual(want, pic)
+    assert util.plane_md5(_run_gpu(pic, base, sparse=True)) == util.plane_md5(want)
+    assert util.plane_md5(_run_gpu(pic, base, sparse=False)) == util.plane_md5(want)

@@ -81,3 +81,22 @@ def test_port_loopfilter_matches_golden():
         o = [np.zeros_like(p) for p in base]
         portapi.alf_picture(o, s, lf)
         assert util.plane_md5(o) == list(g[name + "_alf_md5"])
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("lfate", [0, 1])
+def test_port_matches_reference_on_a_tile_grid(lfate):
+    """2x2 tiles, two slices: the flags synth derives on the host (what a real emitter hands the engine) against the
+    reference's own derivation from ctb_to_col_bd / ctb_to_row_bd (vvc_filter.c:163-212, 1264-1280)."""
+    lf = synth.loopfilter_ctbs(77, 416, 240, ctb_log2=5, n_slices=2, lfase=0, tile_cols=(0, 6), tile_rows=(0, 4), lfate=lfate)
+    base = synth.smooth_planes(7, lf["dims"])
+    a = [p.copy() for p in base]
+    refapi.sao_picture(a, lf)
+    b = [np.zeros_like(p) for p in base]
+    portapi.sao_picture(b, base, lf)
+    assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    c = [p.copy() for p in a]
+    refapi.alf_picture(c, lf)
+    d = [np.zeros_like(p) for p in a]
+    portapi.alf_picture(d, a, lf)
+    assert all(np.array_equal(x, y) for x, y in zip(c, d))

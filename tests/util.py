@@ -58,3 +58,21 @@ def oracle_recon(planes, pic, order=None):
     portapi.residual_batch(planes, rs["levels"], rs["tbs"], rs["params"], residual_planes=res)
     portapi.intra_picture(planes, res, ia["blocks"] if order is None else order, ia["params"])
     return planes
+
+
+def read_device_planes(planes):
+    """Host copies of the planes an abi.Planes struct points at in DEVICE memory (cudaMemcpy2D through the CUDA runtime,
+    which shares the primary context with the engine); used to look at exported windows."""
+    import ctypes as C
+    import glob
+    paths = glob.glob("/usr/local/cuda/lib64/libcudart.so*") + ["libcudart.so"]
+    rt = C.CDLL(sorted(paths)[0])
+    out = []
+    for c in range(3):
+        w, h = planes.width[c], planes.height[c]
+        a = np.zeros((h, w), np.uint16)
+        rc = rt.cudaMemcpy2D(C.c_void_p(a.ctypes.data), C.c_size_t(w * 2), C.c_void_p(planes.plane[c]), C.c_size_t(planes.stride[c]),
+                             C.c_size_t(w * 2), C.c_size_t(h), C.c_int(2))
+        assert rc == 0, "cudaMemcpy2D failed: %d" % rc
+        out.append(a)
+    return out
