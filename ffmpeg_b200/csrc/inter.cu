@@ -350,7 +350,8 @@ __device__ __forceinline__ bool dmvr_refine(const InterArgs &a, const VVCB200Int
 // here that is an index clamp on read.  v0 / v1: the lane's own prediction samples (x = li % w, rows chunk * outs + k).
 __device__ __forceinline__ void bdof_block(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
                                            bool go, int li, int gs, int16_t *buf, int8_t *vxy, const int (&v0)[8],
-                                           const int (&v1)[8], const int (&mv)[2][2], const Window (&fw)[2])
+                                           const int (&v1)[8], const int (&mv)[2][2], const Window (&fw)[2],
+                                           const uint16_t *lut)
 {
     const int w = b.w, h = b.h, bd = a.bd;
     const int log2w = 31 - __clz(w);
@@ -441,8 +442,8 @@ __device__ __forceinline__ void bdof_block(const InterArgs &a, const VVCB200Inte
             const int vx = vxy[2 * sb], vy = vxy[2 * sb + 1];
             const int off = vx * (gh[0][i] - gh[1][i]) + vy * (gv[0][i] - gv[1][i]);
             int r = clip_pixel((pa[0][(y + 1) * ps + x + 1] + of4 + pa[1][(y + 1) * ps + x + 1] + off) >> sh4, bd);
-            if ((b.flags & VVCB200_PB_LMCS) && a.lmcs_fwd)
-                r = __ldg(a.lmcs_fwd + r);
+            if ((b.flags & VVCB200_PB_LMCS) && lut)
+                r = lut[r];
             a.dst.p[0][(size_t)(b.y0 + y) * a.dst.stride[0] + b.x0 + x] = (uint16_t)r;
         }
     }
@@ -493,7 +494,7 @@ template <int TAPS, int WC>
 __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
                                                   bool active, int c, int li, int gs, uint16_t *win, int ws,
                                                   int16_t *tmp, int ts, const int (&mv)[2][2], bool dmvr, bool bdof,
-                                                  int16_t *bdof_buf, int8_t *bdof_vxy)
+                                                  int16_t *bdof_buf, int8_t *bdof_vxy, const uint16_t *lut)
 {
     const int bd = a.bd;
     const int hs = c ? 1 : 0;
@@ -536,7 +537,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
         }
     }
     if (TAPS == 8 && !a.to_tmp14 && __any_sync(0xffffffffu, active && bdof))
-        bdof_block(a, p, b, active && bdof, li, gs, bdof_buf, bdof_vxy, v0, v1, mv, fw);
+        bdof_block(a, p, b, active && bdof, li, gs, bdof_buf, bdof_vxy, v0, v1, mv, fw, lut);
     if (!active || (TAPS == 8 && bdof && !a.to_tmp14))
         return;
 
@@ -595,7 +596,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
             off = (((o0 + o1) << (bd - 8)) + 1) << (sh - 1);
         }
     }
-    const bool lmcs = c == 0 && (b.flags & VVCB200_PB_LMCS) && a.lmcs_fwd;
+    const bool lmcs = c == 0 && (b.flags & VVCB200_PB_LMCS) && lut;
     const int nchunk = h >= 4 ? 2 : 1, outs = h / nchunk;
     const int x = li & (w - 1), chunk = li >> log2w;
     if (chunk >= nchunk)
@@ -624,7 +625,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
             }
             r = clip_pixel(r, bd);
             if (lmcs)
-                r = __ldg(a.lmcs_fwd + r);
+                r = lut[r];
             a.dst.p[c][(size_t)(y0 + y) * a.dst.stride[c] + x0 + x] = (uint16_t)r;
         }
     }
@@ -643,6 +644,15 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
     __shared__ __align__(16) uint16_t s_buf[kInterWarps][kBufElems];
     __shared__ int s_mv[kInterWarps][4][4];             // refined vectors of the warp's blocks, luma phase -> chroma phase
     __shared__ int8_t s_vxy[kInterWarps][2][32];        // BDOF (vx, vy) per 4x4 of the warp's (up to two) blocks
+    // the forward LMCS LUT of the slice in shared memory: every luma sample of a mapped block goes through it
+    __shared__ uint16_t s_lut[4096];
+    const uint16_t *lut = nullptr;
+    if (a.lmcs_fwd) {
+        for (int i = threadIdx.x; i < (1 << a.bd); i += kInterWarps * 32)
+            s_lut[i] = __ldg(a.lmcs_fwd + i);
+        __syncthreads();
+        lut = s_lut;
+    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x * kInterWarps + warp;
 
@@ -682,7 +692,7 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const int win_sz = 23 * ws, tmp_sz = (16 >> cls) * 26;
         const int bdof_region = cls == 0 ? 0 : kBufElems / 2;
         predict_component<8, (16 >> kCls)>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
-                             reinterpret_cast<int16_t *>(s_buf[warp]) + g * bdof_region, s_vxy[warp][g & 1]);
+                             reinterpret_cast<int16_t *>(s_buf[warp]) + g * bdof_region, s_vxy[warp][g & 1], lut);
     }
     __syncwarp();
     {   // chroma: each luma group splits into a Cb half and a Cr half
@@ -699,7 +709,7 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const int ws = wc + 6;                          // 14 / 10 / 8 samples
         const int win_sz = 11 * ws + 8, tmp_sz = wc * 14;
         predict_component<4, (8 >> kCls)>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
-                             win + g * win_sz, ws, tmp + g * tmp_sz, 14, mv, dmvr, false, nullptr, nullptr);
+                             win + g * win_sz, ws, tmp + g * tmp_sz, 14, mv, dmvr, false, nullptr, nullptr, nullptr);
     }
 }
 

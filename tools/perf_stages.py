@@ -53,6 +53,7 @@ def main():
     cur = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
     cur_p = lib.device_planes(cur)
     prof = dev(it["prof"]) if len(it["prof"]) else None
+    fwd = dev(pic["lmcs"][0]) if pic.get("lmcs") is not None else None
     b = it["blocks"]
     f = b["flags"]
     subsets = {
@@ -72,7 +73,7 @@ def main():
         p = abi.InterParams.from_buffer_copy(bytes(it["params"]))
         p.n_w16, p.n_w8 = int((sub["w"] == 16).sum()), int((sub["w"] == 8).sum())
         d = dev(sub)
-        ms = timed(torch, lambda: lib.inter_batch(cur_p, refs_p, d, len(sub), p, prof=prof))
+        ms = timed(torch, lambda: lib.inter_batch(cur_p, refs_p, d, len(sub), p, lmcs_fwd_lut=fwd, prof=prof))
         area = int((sub["w"].astype(np.int64) * sub["h"]).sum())
         print("inter %-14s %7d records %9d luma-samples  %.4f ms  (%.2f ns/record)" % (name, len(sub), area, ms, 1e6 * ms / len(sub)))
 
