@@ -229,3 +229,11 @@ class Window(C.Structure):
 
 class Export(C.Structure):
     _fields_ = [("planes", Planes), ("ready", C.c_void_p)]
+
+
+# ---- boundary-strength derivation on the device (vvcb200_deblock_derive_edges) --------------------------------------
+MOTION_DTYPE = np.dtype([("mv", "<i4", (2, 2)), ("ref_id", "i1", (2,)), ("pred_flag", "u1"), ("ciip_flag", "u1")])   # 20 bytes
+PARTITION_DTYPE = np.dtype([("tb_off", "u1"), ("tb_size", "u1"), ("cu_off_x", "u1"), ("cu_off_y", "u1"),
+                            ("ctb_off", "u1"), ("ctb_size", "u1"), ("cflags", "u1"), ("reserved", "u1")])          # 8 bytes
+REF_MVF_DTYPE = np.dtype([("mv", "<i4", (2, 2)), ("ref_idx", "i1", (2,)), ("hpel_if_idx", "u1"), ("bcw_idx", "u1"),
+                          ("pred_flag", "u1"), ("ciip_flag", "u1"), ("pad", "u1", (2,))])   # MvField, vvc_ctu.h:195-202 (24 bytes)

@@ -483,6 +483,125 @@ __global__ void __launch_bounds__(kDThreads, 3) deblock_tile_kernel(const Debloc
     }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------------
+// Boundary strengths / filter lengths on the device (vvcb200_deblock_derive_edges): one thread per luma 4x4 unit derives
+// the unit's vertical-edge and horizontal-edge bytes of all three planes.  Every rule cites the reference it restates.
+struct BsArgs {
+    uint8_t *out[2][3];
+    const VVCB200MotionUnit *motion;
+    const VVCB200PartitionUnit *part;
+    const uint8_t *ctb_edges;
+    int width, height, stride4, rows4, ctb_log2, ctb_width;
+};
+
+// boundary_strength(), vvc_filter.c:308-372; reference pictures compared through ref_id
+__device__ __forceinline__ int motion_bs(const VVCB200MotionUnit &c, const VVCB200MotionUnit &n)
+{
+    auto far = [](const int32_t (&a)[2], const int32_t (&b)[2]) { return abs(a[0] - b[0]) >= 8 || abs(a[1] - b[1]) >= 8; };
+    if (c.pred_flag == 3 && n.pred_flag == 3) {
+        if (c.ref_id[0] == n.ref_id[0] && c.ref_id[0] == c.ref_id[1] && n.ref_id[0] == n.ref_id[1])
+            return (far(n.mv[0], c.mv[0]) || far(n.mv[1], c.mv[1])) && (far(n.mv[1], c.mv[0]) || far(n.mv[0], c.mv[1]));
+        if (n.ref_id[0] == c.ref_id[0] && n.ref_id[1] == c.ref_id[1])
+            return far(n.mv[0], c.mv[0]) || far(n.mv[1], c.mv[1]);
+        if (n.ref_id[1] == c.ref_id[0] && n.ref_id[0] == c.ref_id[1])
+            return far(n.mv[1], c.mv[0]) || far(n.mv[0], c.mv[1]);
+        return 1;
+    }
+    if (c.pred_flag != 3 && n.pred_flag != 3) {
+        const int lc = (c.pred_flag & 1) ? 0 : 1, ln = (n.pred_flag & 1) ? 0 : 1;
+        if (c.ref_id[lc] != n.ref_id[ln])
+            return 1;
+        return far(c.mv[lc], n.mv[ln]);
+    }
+    return 1;
+}
+
+__global__ void __launch_bounds__(256) deblock_bs_kernel(const BsArgs a)
+{
+    const int ux = blockIdx.x * blockDim.x + threadIdx.x, uy = blockIdx.y;
+    if (ux >= a.stride4 || uy >= a.rows4)
+        return;
+    const int x = ux << 2, y = uy << 2, u = uy * a.stride4 + ux;
+    uint8_t res[2][3] = { { 0, 0, 0 }, { 0, 0, 0 } };
+    if (x < a.width && y < a.height) {
+        const VVCB200PartitionUnit q = a.part[u];
+        const VVCB200MotionUnit mq = a.motion[u];
+        const int ctb_mask = (1 << a.ctb_log2) - 1;
+        const int ce = a.ctb_edges ? a.ctb_edges[(y >> a.ctb_log2) * a.ctb_width + (x >> a.ctb_log2)] : 0;
+        const bool sb_cu = mq.pred_flag != 0 && (q.cu_off_x & 32);            // !is_intra && (msf || iaf), vvc_filter.c:497-500
+#pragma unroll
+        for (int dir = 0; dir < 2; dir++) {                                   // 0: vertical edge at x, 1: horizontal edge at y
+            const int pos = dir ? y : x;
+            if (pos == 0)
+                continue;
+            const int pu = dir ? u - a.stride4 : u - 1;
+            const VVCB200PartitionUnit p = a.part[pu];
+            const VVCB200MotionUnit mp = a.motion[pu];
+            // a slice / tile limit on this CTB side that must not be filtered across (vvc_filter.c:505-512, 566-573)
+            const bool barred = !(pos & ctb_mask) && (ce & (dir ? 2 : 1));
+            const bool intra_side = mq.pred_flag == 0 || mp.pred_flag == 0 || mq.ciip_flag || mp.ciip_flag;
+            // ---- luma
+            const int tb_off = dir ? q.tb_off >> 4 : q.tb_off & 15;           // offset of this unit in its TB, units of 4
+            const int cu_off = dir ? q.cu_off_y : q.cu_off_x & 31;            // offset in its coding unit
+            const int log2_q = dir ? (q.tb_size >> 3) & 7 : q.tb_size & 7, log2_p = dir ? (p.tb_size >> 3) & 7 : p.tb_size & 7;
+            const bool has_sb = sb_cu && (q.cu_off_x & (dir ? 128 : 64));     // cb_width / cb_height > 8
+            if (tb_off == 0) {
+                if (!barred) {                                                // transform edge, vvc_filter.c:514-556
+                    int bs;
+                    if ((q.tb_size & 128) && (p.tb_size & 128))
+                        bs = 0;
+                    else if (intra_side)
+                        bs = 2;
+                    else if ((q.tb_size & 64) || (p.tb_size & 64))
+                        bs = 1;
+                    else if (cu_off && ((cu_off & 1) || !has_sb))             // inside a CU, not on the 8-sample grid or no sub-blocks
+                        bs = 0;
+                    else
+                        bs = motion_bs(mq, mp);
+                    // derive_max_filter_length_luma, vvc_filter.c:374-397
+                    int lp, lq;
+                    if (log2_p <= 2 || log2_q <= 2) {
+                        lp = lq = 1;
+                    } else {
+                        lp = log2_p >= 5 ? 7 : 3;
+                        lq = log2_q >= 5 ? 7 : 3;
+                    }
+                    if (has_sb)
+                        lq = min(5, lq);
+                    if (p.cu_off_x & 32)
+                        lp = min(5, lp);
+                    res[dir][0] = (uint8_t)(bs | (lp << 2) | (lq << 5));
+                }
+            } else if (sb_cu && !(cu_off & 1)) {
+                // edge of the 8x8 sub-block grid inside a TB (vvc_deblock_subblock_bs_*, vvc_filter.c:399-475)
+                const int i = tb_off << 2, size = 1 << log2_q;
+                const int len = (i == 4 || i == size - 4) ? 1 : (i == 8 || i == size - 8) ? 2 : 3;
+                res[dir][0] = (uint8_t)(motion_bs(mq, mp) | (len << 2) | (len << 5));
+            }
+            // ---- chroma: edges of the chroma transform blocks on the 8-chroma-sample grid (vvc_filter.c:646-749)
+            const int ctb_off = dir ? q.ctb_off >> 4 : q.ctb_off & 15;
+            if (ctb_off == 0 && !(pos & 15) && !barred) {
+                const bool pcm = (q.cflags & 2) && (p.cflags & 2);
+                const bool joint = (q.cflags & 1) || (p.cflags & 1);
+                const int sz_q = dir ? (q.ctb_size >> 3) & 7 : q.ctb_size & 7, sz_p = dir ? (p.ctb_size >> 3) & 7 : p.ctb_size & 7;
+                const bool big = sz_p >= 3 && sz_q >= 3;                      // max_filter_length_chroma, vvc_filter.c:796-817
+                const bool ctu_edge = dir && !(y & ctb_mask);
+#pragma unroll
+                for (int c = 1; c < 3; c++) {
+                    const bool cbf = ((q.ctb_size | p.ctb_size) & (c == 1 ? 64 : 128)) || joint;
+                    const int bs = pcm ? 0 : intra_side ? 2 : cbf ? 1 : 0;
+                    const int lq = big ? 3 : bs == 2, lp = big ? (ctu_edge ? 1 : 3) : bs == 2;
+                    res[dir][c] = (uint8_t)(bs | (lp << 2) | (lq << 5));
+                }
+            }
+        }
+    }
+    for (int dir = 0; dir < 2; dir++)
+        for (int c = 0; c < 3; c++)
+            a.out[dir][c][u] = res[dir][c];
+}
+
 }  // namespace vvcb200
 
 using namespace vvcb200;
@@ -588,5 +707,39 @@ extern "C" int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVCB
         VVC_CUDA(cudaEventRecord(f->join[0], side));
         VVC_CUDA(cudaStreamWaitEvent(main_stream, f->join[0], 0));
     }
+    return 0;
+}
+
+
+extern "C" int vvcb200_deblock_derive_edges(uint8_t *const d_edge_out[2][3], const VVCB200MotionUnit *d_motion,
+                                            const VVCB200PartitionUnit *d_part, const uint8_t *d_ctb_edges, int width,
+                                            int height, int stride4, int ctb_log2_size, void *stream)
+{
+    if (!d_edge_out || !d_motion || !d_part || width <= 0 || height <= 0 || stride4 < (width + 3) / 4 || ctb_log2_size < 5 ||
+        ctb_log2_size > 7) {
+        set_error("vvcb200_deblock_derive_edges: bad argument");
+        return VVCB200_ERR_ARG;
+    }
+    BsArgs a;
+    for (int d = 0; d < 2; d++)
+        for (int c = 0; c < 3; c++) {
+            if (!d_edge_out[d][c]) {
+                set_error("vvcb200_deblock_derive_edges: missing output table");
+                return VVCB200_ERR_ARG;
+            }
+            a.out[d][c] = d_edge_out[d][c];
+        }
+    a.motion = d_motion;
+    a.part = d_part;
+    a.ctb_edges = d_ctb_edges;
+    a.width = width;
+    a.height = height;
+    a.stride4 = stride4;
+    a.rows4 = (height + 3) >> 2;
+    a.ctb_log2 = ctb_log2_size;
+    a.ctb_width = (width + (1 << ctb_log2_size) - 1) >> ctb_log2_size;
+    dim3 grid((stride4 + 255) / 256, a.rows4);
+    deblock_bs_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(a);
+    VVC_LAUNCH_CHECK();
     return 0;
 }

@@ -328,6 +328,15 @@ def deblock_tables(edge, qp, ctb_offsets, stride4):
     return t
 
 
+def deblock_derive_edges(edge_out, motion, part, ctb_edges, width, height, stride4, ctb_log2, stream=None):
+    """vvcb200_deblock_derive_edges: edge_out a device tensor [2][3][r4][s4] uint8; motion / part device tensors of
+    VVCB200MotionUnit / VVCB200PartitionUnit records; ctb_edges a device tensor (one byte per CTB) or None."""
+    inner = C.c_void_p * 3
+    ptrs = (inner * 2)(*[inner(*[edge_out[d][c].data_ptr() for c in range(3)]) for d in range(2)])
+    check(load().vvcb200_deblock_derive_edges(ptrs, _ptr(motion), _ptr(part), _ptr(ctb_edges), int(width), int(height),
+                                              int(stride4), int(ctb_log2), _stream(stream)))
+
+
 def deblock_picture(pic, tables, params, stream=None):
     check(load().vvcb200_deblock_picture(C.byref(pic), C.byref(tables), C.byref(params), _stream(stream)))
 

@@ -1085,3 +1085,91 @@ def recon_picture(seed, width, height, ctb_log2=7, intra_fraction=0.5, n_refs=2,
         intra=dict(blocks=np.concatenate(iblocks) if iblocks else np.zeros(0, abi.IB_DTYPE),
                    ctu_first=np.array(ctu_first, np.uint32), params=ip),
         dims=dims, ctb_log2=ctb_log2, width=width, height=height, seed=seed, bd=bd)
+
+
+# ---- the per-4x4 state boundary strengths are derived from ------------------------------------------------------------
+def deblock_state(pic):
+    """Per-4x4 tables of a full_picture(intra_fraction > 0) / recon_picture(): the reference's own set (fc->tab.mvf, tb_pos_*,
+    tb_width / tb_height, cb_pos_*, cb_width / cb_height, tu_coded_flag, tu_joint_cbcr_residual_flag, pcmf, msf, iaf — written
+    the way set_tb_pos / set_tb_tab / set_cb_pos do, vvc_ctu.c:40-74, 1145-1166) from the picture's CU / TU lists and
+    prediction records, and the engine's compact form of the same (VVCB200MotionUnit, VVCB200PartitionUnit).
+    Motion stored for a GPM unit is its first partition's (what the BS rules see is whatever the table holds)."""
+    w, h = pic["width"], pic["height"]
+    s4, r4 = (w + 3) // 4, (h + 3) // 4
+    cus, tus = pic["ref"]["cus"], pic["ref"]["tus"]
+    it = pic["inter"]
+    mvf = np.zeros((r4, s4), abi.REF_MVF_DTYPE)                  # pred_flag 0 = PF_INTRA
+    blocks = it["blocks"]
+    for b in blocks[(blocks["flags"] & abi.PB_CHROMA_ONLY) == 0]:
+        ux, uy, uw, uh = b["x0"] >> 2, b["y0"] >> 2, max(b["w"] >> 2, 1), max(b["h"] >> 2, 1)
+        m = mvf[uy:uy + uh, ux:ux + uw]
+        if b["flags"] & abi.PB_GPM:
+            lst = (int(b["aux"]) >> 18) & 1
+            m["pred_flag"] = 1 + lst
+            m["mv"][..., lst, :] = b["mv"][0]
+            m["ref_idx"][..., lst] = b["ref_idx"][0]
+        else:
+            m["pred_flag"], m["mv"], m["ref_idx"] = b["pred_flag"], b["mv"], b["ref_idx"]
+        m["ciip_flag"] = 1 if b["flags"] & abi.PB_CIIP else 0
+    tb_x0 = np.zeros((2, r4, s4), np.int32)
+    tb_y0 = np.zeros((2, r4, s4), np.int32)
+    tb_w = np.zeros((2, r4, s4), np.uint8)
+    tb_h = np.zeros((2, r4, s4), np.uint8)
+    cb_x, cb_y = np.zeros((r4, s4), np.int32), np.zeros((r4, s4), np.int32)
+    cb_w, cb_h = np.zeros((r4, s4), np.uint8), np.zeros((r4, s4), np.uint8)
+    cbf = np.zeros((3, r4, s4), np.uint8)
+    joint = np.zeros((r4, s4), np.uint8)
+    pcmf = np.zeros((2, r4, s4), np.uint8)
+    msf, iaf = np.zeros((r4, s4), np.uint8), np.zeros((r4, s4), np.uint8)
+    for c in it.get("cus", ()):
+        if c["kind"] == CU_AFFINE:
+            iaf[c["y0"] >> 2:(c["y0"] + c["h"]) >> 2, c["x0"] >> 2:(c["x0"] + c["w"]) >> 2] = 1
+
+    def put_tb(tree, x, y, tw, th):                                # set_tb_pos: geometry in luma samples, tw / th in the tree's samples
+        sh = 1 if tree else 0
+        ux, uy = x >> 2, y >> 2
+        uw, uh = max(1, tw >> (2 - sh)), max(1, th >> (2 - sh))
+        tb_x0[tree, uy:uy + uh, ux:ux + uw], tb_y0[tree, uy:uy + uh, ux:ux + uw] = x, y
+        tb_w[tree, uy:uy + uh, ux:ux + uw], tb_h[tree, uy:uy + uh, ux:ux + uw] = tw, th
+
+    for cu in cus:
+        x, y, cw_, ch_ = int(cu["x0"]), int(cu["y0"]), int(cu["w"]), int(cu["h"])
+        tree = int(cu["tree_type"])
+        ux, uy, uw, uh = x >> 2, y >> 2, cw_ >> 2, ch_ >> 2
+        if tree != 2:
+            cb_x[uy:uy + uh, ux:ux + uw], cb_y[uy:uy + uh, ux:ux + uw] = x, y
+            cb_w[uy:uy + uh, ux:ux + uw], cb_h[uy:uy + uh, ux:ux + uw] = cw_, ch_
+        isp = int(cu["isp_split_type"]) != 0
+        for k in range(int(cu["n_tu"])):
+            tu = tus[int(cu["first_tu"]) + k]
+            tx, ty, tw, th = int(tu["x0"]), int(tu["y0"]), int(tu["w"]), int(tu["h"])
+            if tree != 2:
+                put_tb(0, tx, ty, tw, th)
+                cbf[0, ty >> 2:(ty + max(th, 4)) >> 2, tx >> 2:(tx + max(tw, 4)) >> 2] = tu["coded_flag"][0]
+            if tree != 1 and (not isp or k == int(cu["n_tu"]) - 1):
+                gx, gy, gw, gh = (x, y, cw_, ch_) if isp else (tx, ty, tw, th)   # chroma TBs of an ISP unit cover the coding block
+                put_tb(1, gx, gy, gw >> 1, gh >> 1)
+                sl = (slice(gy >> 2, (gy + gh) >> 2), slice(gx >> 2, (gx + gw) >> 2))
+                cbf[1][sl], cbf[2][sl], joint[sl] = tu["coded_flag"][1], tu["coded_flag"][2], tu["joint"]
+    ref_poc = np.zeros((2, 16), np.int32)
+    for l in range(2):
+        for i in range(16):
+            ref_poc[l, i] = 100 + int(it["params"].ref_slot[l][i])
+    # ---- the engine's compact form
+    uxs, uys = np.meshgrid(np.arange(s4), np.arange(r4))
+    log2 = lambda a: np.where(a > 0, np.log2(np.maximum(a, 1)).astype(np.int64), 0)
+    motion = np.zeros((r4, s4), abi.MOTION_DTYPE)
+    motion["mv"], motion["pred_flag"], motion["ciip_flag"] = mvf["mv"], mvf["pred_flag"], mvf["ciip_flag"]
+    for l in range(2):
+        motion["ref_id"][..., l] = ref_poc[l][np.clip(mvf["ref_idx"][..., l], 0, 15)] - 100
+    part = np.zeros((r4, s4), abi.PARTITION_DTYPE)
+    part["tb_off"] = ((uxs - (tb_x0[0] >> 2)) & 15) | (((uys - (tb_y0[0] >> 2)) & 15) << 4)
+    part["tb_size"] = log2(tb_w[0]) | (log2(tb_h[0]) << 3) | ((cbf[0] != 0) << 6) | ((pcmf[0] != 0) << 7)
+    part["cu_off_x"] = ((uxs - (cb_x >> 2)) & 31) | (((msf | iaf) != 0) << 5) | ((cb_w > 8) << 6) | ((cb_h > 8) << 7)
+    part["cu_off_y"] = (uys - (cb_y >> 2)) & 31
+    part["ctb_off"] = ((uxs - (tb_x0[1] >> 2)) & 15) | (((uys - (tb_y0[1] >> 2)) & 15) << 4)
+    part["ctb_size"] = log2(tb_w[1]) | (log2(tb_h[1]) << 3) | ((cbf[1] != 0) << 6) | ((cbf[2] != 0) << 7)
+    part["cflags"] = (joint != 0) | ((pcmf[1] != 0) << 1)
+    return dict(mvf=mvf, tb_pos_x0=tb_x0, tb_pos_y0=tb_y0, tb_width=tb_w, tb_height=tb_h, cb_pos_x=cb_x, cb_pos_y=cb_y,
+                cb_width=cb_w, cb_height=cb_h, tu_coded_flag=cbf, tu_joint=joint, pcmf=pcmf, msf=msf, iaf=iaf, ref_poc=ref_poc,
+                motion=motion, part=part, stride4=s4, rows4=r4)

@@ -278,6 +278,43 @@ VVCB200_API int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const 
                                            const uint8_t *tb_w_c, const uint8_t *tb_h_c,
                                            int stride4, int rows4, int ctb_log2_size);
 
+/*
+ * Boundary strengths and filter lengths derived ON THE DEVICE: vvc_deblock_bs and its helpers
+ * (vvc_filter.c:308-782: boundary_strength, derive_max_filter_length_luma, the sub-block edge rules, the chroma cbf
+ * rules) plus max_filter_length_chroma (796-817), evaluated per luma 4x4 unit from two compact per-unit tables instead of
+ * the reference's fc->tab.* set.  Output: the packed edge bytes vvcb200_deblock_picture / vvcb200_deblock_lmcs_picture read
+ * (exactly what vvcb200_pack_deblock_edges makes of the reference's tables).
+ */
+typedef struct VVCB200MotionUnit {  /* MvField (vvc_ctu.h:195-202) of one 4x4 luma unit, fc->tab.mvf                    */
+    int32_t mv[2][2];               /* mv[list] = {x, y}, 1/16 sample                                                    */
+    int8_t  ref_id[2];              /* a number that identifies the reference PICTURE of (list, ref_idx): the host
+                                       resolves RefPicList.list[ref_idx] (a POC, possibly of another slice's lists,
+                                       ff_vvc_get_ref_list) to an index into the picture's distinct references          */
+    uint8_t pred_flag;              /* 0 PF_INTRA, 1 PF_L0, 2 PF_L1, 3 PF_BI (vvc_ctu.h:222-227)                          */
+    uint8_t ciip_flag;
+} VVCB200MotionUnit;                /* 20 bytes */
+
+typedef struct VVCB200PartitionUnit {   /* where a 4x4 luma unit sits in its transform blocks and coding unit            */
+    uint8_t tb_off;                 /* luma TB: (x - tb_pos_x0) / 4 | (y - tb_pos_y0) / 4 << 4   (fc->tab.tb_pos_x0/y0[0]) */
+    uint8_t tb_size;                /* log2 tb_width | log2 tb_height << 3 | tu_coded_flag[0] << 6 | pcmf[0] << 7          */
+    uint8_t cu_off_x;               /* (x - cb_pos_x) / 4 | sub-block CU (msf || iaf) << 5 | cb_width > 8 << 6 |
+                                       cb_height > 8 << 7                                                                 */
+    uint8_t cu_off_y;               /* (y - cb_pos_y) / 4                                                                 */
+    uint8_t ctb_off;                /* chroma TB (luma coordinates): (x - tb_pos_x0[1]) / 4 | (y - tb_pos_y0[1]) / 4 << 4  */
+    uint8_t ctb_size;               /* log2 chroma tb_width | log2 tb_height << 3 (chroma samples) | tu_coded_flag[1] << 6 |
+                                       tu_coded_flag[2] << 7                                                              */
+    uint8_t cflags;                 /* bit0 tu_joint_cbcr_residual_flag, bit1 pcmf[1]                                     */
+    uint8_t reserved;
+} VVCB200PartitionUnit;             /* 8 bytes */
+
+/* d_motion, d_part: stride4 x rows4 units.  d_ctb_edges: per CTB (raster), bit0 / bit1 = the left / upper CTB side is a
+ * slice or tile limit that must not be filtered across (vvc_filter.c:505-512: BOUNDARY_*_SLICE with
+ * pps_loop_filter_across_slices_enabled_flag 0, BOUNDARY_*_TILE with ..._across_tiles... 0); NULL: none.
+ * d_edge_out[dir][c]: stride4 x rows4 bytes each. */
+VVCB200_API int vvcb200_deblock_derive_edges(uint8_t *const d_edge_out[2][3], const VVCB200MotionUnit *d_motion,
+                                             const VVCB200PartitionUnit *d_part, const uint8_t *d_ctb_edges, int width,
+                                             int height /* luma samples */, int stride4, int ctb_log2_size, void *stream);
+
 /* Both deblocking passes over the whole picture, in place: all vertical edges, then all horizontal edges. */
 VVCB200_API int vvcb200_deblock_picture(const VVCB200Planes *pic, const VVCB200DeblockTables *tables /* host struct */,
                                         const VVCB200DeblockParams *params /* host */, void *stream);

@@ -345,3 +345,81 @@ VVCREF_EXPORT int vvcref_lmcs_picture(const VVCRefPlanes *pl, const uint16_t *in
     filter_env_free(e);
     return 0;
 }
+
+
+/*
+ * The reference's own boundary-strength / filter-length derivation (vvc_deblock_bs and its helpers, vvc_filter.c:308-782)
+ * over a picture whose per-4x4 tables the caller plants in the reference's format (fc->tab.*, vvcdec.h:122-187):
+ *   mvf:        MvField per 4x4 (24 bytes each, vvc_ctu.h:195-202)
+ *   tb_pos_x0 / tb_pos_y0 [2], tb_width / tb_height [2]: per 4x4, luma and chroma trees (set_tb_pos, vvc_ctu.c:40-60)
+ *   cb_pos_x / cb_pos_y, cb_width / cb_height: luma tree (set_cb_pos, vvc_ctu.c:1145-1166)
+ *   tu_coded_flag[3], tu_joint, pcmf[2], msf, iaf: per 4x4
+ *   ref_poc[2][16]: RefPicList.list of the (single) slice
+ * Output: bs[dir][c], len_p[dir], len_q[dir] (stride4 x rows4 bytes, zero where the reference writes nothing).
+ */
+VVCREF_EXPORT int vvcref_deblock_bs(int width, int height, int ctb_log2, const void *mvf,
+                                    const int32_t *const tb_pos_x0[2], const int32_t *const tb_pos_y0[2],
+                                    const uint8_t *const tb_width[2], const uint8_t *const tb_height[2],
+                                    const int32_t *cb_pos_x, const int32_t *cb_pos_y, const uint8_t *cb_width,
+                                    const uint8_t *cb_height, const uint8_t *const tu_coded_flag[3], const uint8_t *tu_joint,
+                                    const uint8_t *const pcmf[2], const uint8_t *msf, const uint8_t *iaf,
+                                    const int32_t *ref_poc /* [2][16] */, const int16_t *slice_idx, int lfase,
+                                    uint8_t *const bs[2][3], uint8_t *const len_p[2], uint8_t *const len_q[2])
+{
+    VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
+    FilterEnv *e = filter_env_new(&pl, 10, ctb_log2);
+    const size_t units = (size_t)e->pps.min_tu_width * e->pps.min_tu_height;
+    plant_slices(e, slice_idx, lfase);
+    e->fc.tab.mvf = (MvField *)mvf;
+    for (int i = 0; i < 2; i++) {
+        e->fc.tab.tb_pos_x0[i] = (int *)tb_pos_x0[i];
+        e->fc.tab.tb_pos_y0[i] = (int *)tb_pos_y0[i];
+        e->fc.tab.tb_width[i]  = (uint8_t *)tb_width[i];
+        e->fc.tab.tb_height[i] = (uint8_t *)tb_height[i];
+        e->fc.tab.pcmf[i]      = (uint8_t *)pcmf[i];
+    }
+    e->fc.tab.cb_pos_x[0]  = (int *)cb_pos_x;
+    e->fc.tab.cb_pos_y[0]  = (int *)cb_pos_y;
+    e->fc.tab.cb_width[0]  = (uint8_t *)cb_width;
+    e->fc.tab.cb_height[0] = (uint8_t *)cb_height;
+    for (int c = 0; c < 3; c++)
+        e->fc.tab.tu_coded_flag[c] = (uint8_t *)tu_coded_flag[c];
+    e->fc.tab.tu_joint_cbcr_residual_flag = (uint8_t *)tu_joint;
+    e->fc.tab.msf = (uint8_t *)msf;
+    e->fc.tab.iaf = (uint8_t *)iaf;
+    for (int l = 0; l < 2; l++)
+        for (int i = 0; i < 16; i++)
+            e->rpl[l].list[i] = ref_poc[l * 16 + i];
+    for (int c = 0; c < 3; c++) {
+        memset(bs[0][c], 0, units);
+        memset(bs[1][c], 0, units);
+        e->fc.tab.vertical_bs[c]   = bs[0][c];
+        e->fc.tab.horizontal_bs[c] = bs[1][c];
+    }
+    for (int d = 0; d < 2; d++) {
+        memset(len_p[d], 0, units);
+        memset(len_q[d], 0, units);
+    }
+    e->fc.tab.vertical_p   = len_p[0];
+    e->fc.tab.vertical_q   = len_q[0];
+    e->fc.tab.horizontal_p = len_p[1];
+    e->fc.tab.horizontal_q = len_q[1];
+    /* every slice uses the same reference picture lists here: across a slice limit the reference looks the neighbour's
+     * lists up through fc->ref->rpl_tab (ff_vvc_get_ref_list, vvc_refs.c:66-74) */
+    VVCFrame cur = { 0 };
+    RefPicListTab **rpl_tab = calloc(e->pps.ctb_count, sizeof(*rpl_tab));
+    for (unsigned i = 0; i < e->pps.ctb_count; i++)
+        rpl_tab[i] = (RefPicListTab *)e->rpl;
+    cur.rpl_tab = rpl_tab;
+    e->fc.ref = &cur;
+    for (int ry = 0; ry < (int)e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < (int)e->pps.ctb_width; rx++) {
+            const int x0 = rx << ctb_log2, y0 = ry << ctb_log2;
+            ff_vvc_decode_neighbour(e->lc, x0, y0, rx, ry, ry * e->pps.ctb_width + rx);
+            vvc_deblock_bs(e->lc, x0, y0, 1);
+            vvc_deblock_bs(e->lc, x0, y0, 0);
+        }
+    free(rpl_tab);
+    filter_env_free(e);
+    return 0;
+}

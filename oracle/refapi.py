@@ -209,3 +209,26 @@ def recon_picture(planes, ref, intra_params, threads=1, inter=None, lmcs_fwd_lut
                                C.c_void_p(lut.ctypes.data) if lut is not None else None)
     if r != 0:
         raise RuntimeError("vvcref_recon_picture failed")
+
+
+def deblock_bs(st, width, height, ctb_log2, slice_idx=None, lfase=1):
+    """Reference vvc_deblock_bs (vvc_filter.c:756-782 and everything it calls) over synth.deblock_state() tables.
+    Returns bs [2][3][r4][s4], len_p [2][r4][s4], len_q [2][r4][s4] as the reference leaves fc->tab.*_bs / *_p / *_q."""
+    r4, s4 = st["rows4"], st["stride4"]
+    bs = np.zeros((2, 3, r4, s4), np.uint8)
+    len_p, len_q = np.zeros((2, r4, s4), np.uint8), np.zeros((2, r4, s4), np.uint8)
+    keep = {k: np.ascontiguousarray(st[k]) for k in ("mvf", "tb_pos_x0", "tb_pos_y0", "tb_width", "tb_height", "cb_pos_x", "cb_pos_y",
+                                                      "cb_width", "cb_height", "tu_coded_flag", "tu_joint", "pcmf", "msf", "iaf", "ref_poc")}
+    sl = None if slice_idx is None else np.ascontiguousarray(slice_idx, np.int16)
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    _plant_tiles({})
+    r = lib().vvcref_deblock_bs(int(width), int(height), int(ctb_log2), p(keep["mvf"]),
+                                _ptr_grid(keep["tb_pos_x0"], (2,)), _ptr_grid(keep["tb_pos_y0"], (2,)),
+                                _ptr_grid(keep["tb_width"], (2,)), _ptr_grid(keep["tb_height"], (2,)),
+                                p(keep["cb_pos_x"]), p(keep["cb_pos_y"]), p(keep["cb_width"]), p(keep["cb_height"]),
+                                _ptr_grid(keep["tu_coded_flag"], (3,)), p(keep["tu_joint"]), _ptr_grid(keep["pcmf"], (2,)),
+                                p(keep["msf"]), p(keep["iaf"]), p(keep["ref_poc"]), p(sl) if sl is not None else None, int(lfase),
+                                _ptr_grid(bs, (2, 3)), _ptr_grid(len_p, (2,)), _ptr_grid(len_q, (2,)))
+    if r != 0:
+        raise RuntimeError("vvcref_deblock_bs failed")
+    return bs, len_p, len_q

@@ -76,3 +76,43 @@ def test_tile_pass_matches_two_pass_4k():
     base = synth.smooth_planes(11, t["dims"])
     edge = lib.pack_deblock_edges(t["bs"], t["len_p"], t["len_q"], t["tb_w_c"], t["tb_h_c"], 7)
     assert util.plane_md5(gpu_deblock(base, t, edge, True)) == util.plane_md5(gpu_deblock(base, t, edge, False))
+
+
+def _norm(e):
+    return np.where((e & 3) == 0, 0, e)
+
+
+@pytest.mark.parametrize("seed,w,h,ctb,frac,ns", [(40, 416, 240, 6, 0.3, 1), (43, 416, 240, 5, 0.3, 3), (44, 832, 480, 7, 0.2, 2),
+                                                 (45, 1920, 1080, 7, 0.1, 1)])
+def test_device_derived_edges_match_the_reference_and_filter_the_same_picture(seed, w, h, ctb, frac, ns):
+    """vvcb200_deblock_derive_edges over a consistent picture state against the reference's vvc_deblock_bs
+    (oracle/_ref), every 4x4 unit; then the picture deblocked from the device-derived edges against the reference's
+    deblocking driven by ITS tables."""
+    import torch
+    from oracle import port_bs
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, intra_fraction=frac)
+    st = synth.deblock_state(pic)
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    slices = synth.slice_map(np.random.default_rng(seed), cw, ch, ns)
+    lfase = 1 if ns == 1 else 0
+    edges = (synth.alf_edge_flags(slices, cw, ch, lfase) & 3).astype(np.uint8)
+    d_motion = torch.from_numpy(st["motion"].view(np.uint8).reshape(-1)).cuda()
+    d_part = torch.from_numpy(st["part"].view(np.uint8).reshape(-1)).cuda()
+    d_edges = torch.from_numpy(edges).cuda()
+    out = torch.full((2, 3, st["rows4"], st["stride4"]), 0x77, dtype=torch.uint8, device="cuda")
+    lib.deblock_derive_edges(out, d_motion, d_part, d_edges, w, h, st["stride4"], ctb)
+    torch.cuda.synchronize()
+    got = out.cpu().numpy()
+    if w * h <= 416 * 240:
+        assert np.array_equal(got, port_bs.derive_edges(st["motion"], st["part"], w, h, ctb, edges))
+    t = synth.deblock_picture(seed, w, h, ctb_log2=ctb)          # qp tables, per-CTB offsets, LADF parameters
+    if refapi.available():
+        bs, lp, lq = refapi.deblock_bs(st, w, h, ctb, slices, lfase)
+        want = lib.pack_deblock_edges(bs, lp, lq, np.ascontiguousarray(st["tb_width"][1]), np.ascontiguousarray(st["tb_height"][1]), ctb)
+        assert np.array_equal(_norm(got), _norm(want))
+        t = dict(t, bs=bs, len_p=lp, len_q=lq, tb_w_c=np.ascontiguousarray(st["tb_width"][1]), tb_h_c=np.ascontiguousarray(st["tb_height"][1]))
+        base = synth.smooth_planes(seed, t["dims"])
+        ref_pic = [p.copy() for p in base]
+        refapi.deblock_picture(ref_pic, t)
+        for fused in (False, True):
+            assert util.plane_md5(gpu_deblock(base, t, got, fused)) == util.plane_md5(ref_pic)

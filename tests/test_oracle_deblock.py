@@ -54,3 +54,29 @@ def test_port_deblock_matches_golden():
         planes = synth.smooth_planes(seed, t["dims"])
         port_deblock(planes, t)
         assert util.plane_md5(planes) == list(g[name + "_plane_md5"])
+
+
+def _norm(e):
+    """Edge bytes with bs == 0 carry no information (the filter skips them)."""
+    return np.where((e & 3) == 0, 0, e)
+
+
+@pytest.mark.skipif(not refapi.available(), reason="oracle/_ref not built")
+@pytest.mark.parametrize("seed,w,h,ctb,frac,ns", [(40, 416, 240, 6, 0.3, 1), (41, 256, 192, 7, 0.5, 1), (42, 208, 120, 5, 0.1, 1),
+                                                 (43, 416, 240, 5, 0.3, 3)])
+def test_bs_port_matches_the_references_vvc_deblock_bs(seed, w, h, ctb, frac, ns):
+    """boundary strengths and filter lengths from a CONSISTENT picture state (the CU / TU / MV tables of a
+    synthetic picture with affine, GPM, CIIP, ISP and intra units) — the reference's own vvc_deblock_bs over fc->tab.*
+    against the restatement over the engine's compact per-4x4 tables."""
+    from oracle import port_bs
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, intra_fraction=frac)
+    st = synth.deblock_state(pic)
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    slices = synth.slice_map(np.random.default_rng(seed), cw, ch, ns)
+    lfase = 1 if ns == 1 else 0
+    bs, lp, lq = refapi.deblock_bs(st, w, h, ctb, slices, lfase)
+    assert (bs == 2).any() and (bs == 1).any() and (lp == 7).any() and (lp == 2).any()
+    want = lib.pack_deblock_edges(bs, lp, lq, np.ascontiguousarray(st["tb_width"][1]), np.ascontiguousarray(st["tb_height"][1]), ctb)
+    edges = (synth.alf_edge_flags(slices, cw, ch, lfase) & 3).astype(np.uint8)
+    got = port_bs.derive_edges(st["motion"], st["part"], w, h, ctb, edges)
+    assert np.array_equal(_norm(got), _norm(want))
