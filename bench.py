@@ -462,7 +462,8 @@ def main():
     per_set = (len(it["refs"]) + 3) * frame_bytes + irecs.nbytes + rs["levels"].nbytes + rs["tbs"].nbytes + it["blocks"].nbytes + \
         edge.nbytes + db["qp"].nbytes
     rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
-    rot += rot & 1                                   # even: a working set always meets the same lane (stream)
+    n_lanes = env_int("VVCB200_BENCH_LANES", 2)
+    rot = -(-rot // n_lanes) * n_lanes               # a multiple of the lanes: a working set always meets the same lane (stream)
     detail["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
         rot, rot * per_set / 1e6)
     detail["lanes"] = ("consecutive pictures alternate between two CUDA streams (independent pictures, as the B pictures of "
@@ -493,7 +494,8 @@ def main():
         s["inv"] = dev(inv) if inv is not None else None
         sets.append(s)
 
-    lanes = [torch.cuda.Stream(), torch.cuda.Stream()]
+    n_lanes = env_int("VVCB200_BENCH_LANES", 2)      # development: pictures in flight in the device-resident arm
+    lanes = [torch.cuda.Stream() for _ in range(n_lanes)]
 
     def step(i, ev=None, lane=None):
         """One picture.  lane: the stream it is queued on (None: torch's current stream, with stage events)."""
@@ -518,7 +520,7 @@ def main():
             ev[5].record()
 
     for i in range(warmup):
-        step(i, lane=lanes[i & 1])
+        step(i, lane=lanes[i % n_lanes])
     barrier()
     # stage boundaries are marked with events on the launching stream (torch's current stream), one picture at a time
     n_serial = max(1, min(args.steps, 10))
@@ -539,7 +541,7 @@ def main():
     for q in lanes:
         q.wait_event(ev_start)
     for i in range(args.steps):
-        step(warmup + i, lane=lanes[i & 1])
+        step(warmup + i, lane=lanes[(warmup + i) % n_lanes])
     for q in lanes:
         torch.cuda.current_stream().wait_stream(q)   # ... until both lanes have drained
     ev_end.record()
@@ -551,7 +553,7 @@ def main():
         # too short for nvidia-smi's sampling period: keep the same load running a little longer (not timed)
         t_end, i = time.perf_counter() + 0.6, 0
         while time.perf_counter() < t_end:
-            step(i, lane=lanes[i & 1])
+            step(i, lane=lanes[i % n_lanes])
             i += 1
             if i % 20 == 0:
                 torch.cuda.synchronize()
@@ -638,7 +640,8 @@ def main():
                 "frac": achieved / peak, "traffic": traffic, "peak_kind": peak_kind,
                 "algorithmic_bytes_per_launch": algo, "kernel_ms": kernel_ms,
                 "stage_ms": {k: round(v, 4) for k, v in stage_ms.items()},
-                "stage_frac_of_peak": {k: round(st["stage_bytes"][k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) for k in STAGES},
+                "stage_frac_of_peak": {k: round(st["stage_bytes"][k] / (stage_ms[k] * 1e-3) / 1e9 / peak, 4) for k in STAGES
+                                       if stage_ms[k] > 0.01},          # (a stage without work has no rate)
                 "picture": {"algorithmic_bytes": st["a_pic"], "achieved": st["a_pic"] / (step_ms * 1e-3) / 1e9,
                             "frac": st["a_pic"] / (step_ms * 1e-3) / 1e9 / peak}}
     out = {"metric": METRIC, "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": warmup,
