@@ -1,0 +1,276 @@
+/*
+ * vvcb200_emit.c — descriptor producer inside the reference decoder (see vvcb200_emit.h).
+ * Every function cites the reference code whose traversal it follows; the pixel work of that code is what the
+ * engine does from the records written here.
+ */
+#include <stdlib.h>
+#include <string.h>
+
+#include "libavcodec/vvc/vvc_ctu.h"
+#include "libavcodec/vvc/vvc_mvs.h"
+#include "libavcodec/vvc/vvcdec.h"
+
+#include "vvcb200_emit.h"
+
+/* ---- growable arrays ------------------------------------------------------------------------------------- */
+static void *grow(VVCB200EmitBatch *b, void *p, int *cap, int need, size_t elem)
+{
+    if (need <= *cap)
+        return p;
+    int want = *cap ? *cap * 2 : 1024;
+    while (want < need)
+        want *= 2;
+    void *q = realloc(p, (size_t)want * elem);
+    if (!q) {
+        b->error = VVCB200_ERR_NOMEM;
+        return p;
+    }
+    *cap = want;
+    return q;
+}
+
+void vvcb200_emit_reset(VVCB200EmitBatch *b)
+{
+    b->n_blocks = b->n_prof = b->n_tbs = b->n_iblocks = b->n_ctus = 0;
+    b->n_levels = 0;
+    b->error = 0;
+}
+
+void vvcb200_emit_free(VVCB200EmitBatch *b)
+{
+    free(b->blocks);
+    free(b->prof);
+    free(b->tbs);
+    free(b->levels);
+    free(b->iblocks);
+    free(b->ctu_first);
+    memset(b, 0, sizeof(*b));
+}
+
+static VVCB200PredBlock *new_block(VVCB200EmitBatch *b)
+{
+    b->blocks = grow(b, b->blocks, &b->cap_blocks, b->n_blocks + 1, sizeof(*b->blocks));
+    if (b->error)
+        return NULL;
+    VVCB200PredBlock *r = &b->blocks[b->n_blocks++];
+    memset(r, 0, sizeof(*r));
+    return r;
+}
+
+/* ---- stage INTER -------------------------------------------------------------------------------------------- */
+/* flags every record of the unit carries: the slice-level switches derive_weight_uni / derive_weight look at
+ * (vvc_inter.c:125-150) and the forward mapping predict_inter applies to non-CIIP units (vvc_inter.c:888-891) */
+static int unit_flags(const VVCLocalContext *lc, const CodingUnit *cu)
+{
+    const VVCSH *sh   = &lc->sc->sh;
+    const VVCPPS *pps = lc->fc->ps.pps;
+    int f = 0;
+    if ((IS_P(sh->r) && pps->r->pps_weighted_pred_flag) || (IS_B(sh->r) && pps->r->pps_weighted_bipred_flag))
+        f |= VVCB200_PB_WP;
+    if (sh->r->sh_lmcs_used_flag)
+        f |= VVCB200_PB_LMCS;
+    if (cu->ciip_flag)
+        f |= VVCB200_PB_CIIP;
+    return f;
+}
+
+static void fill_motion(VVCB200PredBlock *r, const MvField *mvf)
+{
+    r->pred_flag = mvf->pred_flag;
+    r->bcw_idx   = mvf->bcw_idx;
+    for (int l = 0; l < 2; l++) {
+        r->ref_idx[l] = mvf->ref_idx[l];
+        r->mv[l][0]   = mvf->mv[l].x;
+        r->mv[l][1]   = mvf->mv[l].y;
+    }
+}
+
+/* pred_regular_blk (vvc_inter.c:787-815): one sub-block per (sbx, sby); a sub-block larger than 16x16 (a unit without
+ * DMVR has one sub-block, num_sb_x == num_sb_y == 1) is cut into 16x16 records — translational MC is separable per
+ * sample, and 16x16 is the reference's own DMVR / BDOF unit */
+static void emit_regular(VVCB200EmitBatch *b, const VVCLocalContext *lc, const CodingUnit *cu)
+{
+    const PredictionUnit *pu = &cu->pu;
+    const MotionInfo *mi     = &pu->mi;
+    const int sbw = cu->cb_width / mi->num_sb_x, sbh = cu->cb_height / mi->num_sb_y;
+    int flags = unit_flags(lc, cu);
+
+    if (mi->hpel_if_idx)
+        flags |= VVCB200_PB_HPEL_IF;
+    if (pu->bdof_flag)
+        flags |= VVCB200_PB_BDOF;
+    if (pu->dmvr_flag)
+        flags |= VVCB200_PB_DMVR;
+    for (int sby = 0; sby < mi->num_sb_y; sby++)
+        for (int sbx = 0; sbx < mi->num_sb_x; sbx++) {
+            const int x0 = cu->x0 + sbx * sbw, y0 = cu->y0 + sby * sbh;
+            const MvField *mvf = ff_vvc_get_mvf(lc->fc, x0, y0);
+            for (int ty = 0; ty < sbh; ty += 16)
+                for (int tx = 0; tx < sbw; tx += 16) {
+                    VVCB200PredBlock *r = new_block(b);
+                    if (!r)
+                        return;
+                    r->x0 = x0 + tx;
+                    r->y0 = y0 + ty;
+                    r->w  = FFMIN(16, sbw);
+                    r->h  = FFMIN(16, sbh);
+                    fill_motion(r, mvf);
+                    r->flags = flags;
+                }
+        }
+}
+
+/* pred_affine_blk (vvc_inter.c:828-873): a luma-only record per 4x4 sub-block (filter set 2, PROF per list where
+ * cb_prof_flag says so) and, on every second sub-block in x and y, a chroma-only record with derive_affine_mvc's
+ * vector (the mean of this sub-block's and its lower-right neighbour's, rounded by ff_vvc_round_mv(.., 0, 1)) */
+static void emit_affine(VVCB200EmitBatch *b, const VVCLocalContext *lc, const CodingUnit *cu)
+{
+    const VVCFrameContext *fc = lc->fc;
+    const PredictionUnit *pu  = &cu->pu;
+    const MotionInfo *mi      = &pu->mi;
+    const int sbw = cu->cb_width / mi->num_sb_x, sbh = cu->cb_height / mi->num_sb_y;
+    const int hs = fc->ps.sps->hshift[1], vs = fc->ps.sps->vshift[1];
+    const int flags = unit_flags(lc, cu);
+    int prof_idx;
+
+    if (sbw != 4 || sbh != 4 || hs != 1 || vs != 1) {
+        b->error = VVCB200_ERR_UNSUP;
+        return;
+    }
+    b->prof = grow(b, b->prof, &b->cap_prof, b->n_prof + 1, sizeof(*b->prof));
+    if (b->error)
+        return;
+    prof_idx = b->n_prof++;
+    for (int l = 0; l < 2; l++)
+        for (int k = 0; k < 16; k++) {
+            b->prof[prof_idx].diff_mv_x[l][k] = pu->diff_mv_x[l][k];
+            b->prof[prof_idx].diff_mv_y[l][k] = pu->diff_mv_y[l][k];
+        }
+    for (int sby = 0; sby < mi->num_sb_y; sby++)
+        for (int sbx = 0; sbx < mi->num_sb_x; sbx++) {
+            const int x = cu->x0 + sbx * sbw, y = cu->y0 + sby * sbh;
+            const MvField *mv = ff_vvc_get_mvf(fc, x, y);
+            VVCB200PredBlock *r = new_block(b);
+            if (!r)
+                return;
+            r->x0 = x; r->y0 = y; r->w = sbw; r->h = sbh;
+            fill_motion(r, mv);
+            r->pred_flag = mi->pred_flag;
+            r->flags = flags | VVCB200_PB_AFFINE | VVCB200_PB_LUMA_ONLY |
+                       (pu->cb_prof_flag[0] ? VVCB200_PB_PROF0 : 0) | (pu->cb_prof_flag[1] ? VVCB200_PB_PROF1 : 0);
+            r->aux = prof_idx;
+            if (!(sby & 1) && !(sbx & 1)) {
+                const MvField *mv2 = ff_vvc_get_mvf(fc, x + hs * sbw, y + vs * sbh);
+                MvField mvc = *mv;
+                mvc.mv[0].x += mv2->mv[0].x; mvc.mv[0].y += mv2->mv[0].y;
+                mvc.mv[1].x += mv2->mv[1].x; mvc.mv[1].y += mv2->mv[1].y;
+                ff_vvc_round_mv(mvc.mv + 0, 0, 1);
+                ff_vvc_round_mv(mvc.mv + 1, 0, 1);
+                r = new_block(b);
+                if (!r)
+                    return;
+                r->x0 = x; r->y0 = y; r->w = sbw << hs; r->h = sbh << vs;
+                fill_motion(r, &mvc);
+                r->pred_flag = mi->pred_flag;
+                r->flags = (flags & ~VVCB200_PB_LMCS) | VVCB200_PB_CHROMA_ONLY;
+            }
+        }
+}
+
+/* pred_gpm_blk (vvc_inter.c:466-521): both partitions' predictions over the whole unit, blended by position; records
+ * of at most 16x16 that carry the unit's partition, size and their own offset (VVCB200_GPM_AUX) */
+static void emit_gpm(VVCB200EmitBatch *b, const VVCLocalContext *lc, const CodingUnit *cu)
+{
+    const PredictionUnit *pu = &cu->pu;
+    const int flags = (unit_flags(lc, cu) & ~VVCB200_PB_WP) | VVCB200_PB_GPM;    /* GPM is never explicitly weighted */
+    const int lw = av_log2(cu->cb_width), lh = av_log2(cu->cb_height);
+    int list[2];
+
+    for (int k = 0; k < 2; k++)
+        list[k] = pu->gpm_mv[k].pred_flag - PF_L0;
+    for (int ty = 0; ty < cu->cb_height; ty += 16)
+        for (int tx = 0; tx < cu->cb_width; tx += 16) {
+            VVCB200PredBlock *r = new_block(b);
+            if (!r)
+                return;
+            r->x0 = cu->x0 + tx; r->y0 = cu->y0 + ty;
+            r->w = FFMIN(16, cu->cb_width); r->h = FFMIN(16, cu->cb_height);
+            r->pred_flag = PF_BI;
+            for (int k = 0; k < 2; k++) {
+                r->ref_idx[k] = pu->gpm_mv[k].ref_idx[list[k]];
+                r->mv[k][0]   = pu->gpm_mv[k].mv[list[k]].x;
+                r->mv[k][1]   = pu->gpm_mv[k].mv[list[k]].y;
+            }
+            r->flags = flags;
+            r->aux = VVCB200_GPM_AUX(pu->gpm_partition_idx, lw, lh, tx, ty, list[0], list[1]);
+        }
+}
+
+int vvcb200_emit_inter_cu(VVCB200EmitBatch *b, const VVCLocalContext *lc)
+{
+    const CodingUnit *cu     = lc->cu;
+    const PredictionUnit *pu = &cu->pu;
+
+    if (b->error)
+        return b->error;
+    if (pu->merge_gpm_flag)
+        emit_gpm(b, lc, cu);
+    else if (pu->inter_affine_flag)
+        emit_affine(b, lc, cu);
+    else
+        emit_regular(b, lc, cu);
+    return b->error;
+}
+
+/* ---- batch order --------------------------------------------------------------------------------------------
+ * Width classes 16 / 8 / 4 (required by the kernels); inside a class the records with the longest latency first (DMVR,
+ * BDOF, GPM), then grouped by the tools they use so that warps running side by side share a code path.  Stable. */
+static long long block_key(const VVCB200PredBlock *r)
+{
+    const int f = r->flags;
+    const long long kind = (long long)(f & (VVCB200_PB_GPM | VVCB200_PB_AFFINE | VVCB200_PB_LUMA_ONLY | VVCB200_PB_CHROMA_ONLY |
+                                            VVCB200_PB_DMVR | VVCB200_PB_BDOF | VVCB200_PB_WP | VVCB200_PB_PROF0 | VVCB200_PB_PROF1)) * 4 +
+                           r->pred_flag + 1024 * 1024 * (r->bcw_idx != 0);
+    const int slow = (f & VVCB200_PB_DMVR) ? 0 : (f & VVCB200_PB_BDOF) ? 1 : (f & VVCB200_PB_GPM) ? 2 : 3;
+    const int wcls = r->w == 16 ? 0 : r->w == 8 ? 1 : 2;
+    return ((long long)wcls << 40) | ((long long)slow << 36) | kind;
+}
+
+void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params)
+{
+    const int n = b->n_blocks;
+    VVCB200PredBlock *tmp = malloc((size_t)(n ? n : 1) * sizeof(*tmp));
+    long long *key = malloc((size_t)(n ? n : 1) * sizeof(*key)), *ktmp = malloc((size_t)(n ? n : 1) * sizeof(*ktmp));
+    if (!tmp || !key || !ktmp) {
+        b->error = VVCB200_ERR_NOMEM;
+        free(tmp); free(key); free(ktmp);
+        return;
+    }
+    for (int i = 0; i < n; i++)
+        key[i] = block_key(&b->blocks[i]);
+    /* bottom-up merge sort: stable, O(n log n), no recursion */
+    VVCB200PredBlock *src = b->blocks, *dst = tmp;
+    long long *ks = key, *kd = ktmp;
+    for (int width = 1; width < n; width *= 2) {
+        for (int lo = 0; lo < n; lo += 2 * width) {
+            const int mid = FFMIN(lo + width, n), hi = FFMIN(lo + 2 * width, n);
+            int i = lo, j = mid, o = lo;
+            while (i < mid || j < hi) {
+                const int take_left = j >= hi || (i < mid && ks[i] <= ks[j]);
+                const int s = take_left ? i++ : j++;
+                dst[o] = src[s];
+                kd[o++] = ks[s];
+            }
+        }
+        VVCB200PredBlock *t = src; src = dst; dst = t;
+        long long *kt = ks; ks = kd; kd = kt;
+    }
+    if (src != b->blocks)
+        memcpy(b->blocks, src, (size_t)n * sizeof(*src));
+    params->n_w16 = params->n_w8 = 0;
+    for (int i = 0; i < n; i++) {
+        params->n_w16 += b->blocks[i].w == 16;
+        params->n_w8  += b->blocks[i].w == 8;
+    }
+    free(tmp); free(key); free(ktmp);
+}

@@ -1,0 +1,58 @@
+/*
+ * vvcb200_emit.h — the descriptor producer that sits in the reference decoder.
+ *
+ * These functions take the reference's OWN structures (VVCFrameContext, VVCLocalContext, CodingUnit, PredictionUnit,
+ * TransformUnit, TransformBlock, MvField, SAOParams, ALFParams: libavcodec/vvc/vvc_ctu.h:136-460, vvcdec.h:86-200) and
+ * write the batches libvvcb200.so consumes (include/vvc_b200.h).  They are the bodies the stage runners of
+ * libavcodec/vvc/vvc_thread.c:432-566 get in place of their pixel work:
+ *
+ *   run_inter   ff_vvc_predict_inter()  ->  vvcb200_emit_inter_cu() per coding unit       (vvc_inter.c:875-913)
+ *   run_recon   ff_vvc_reconstruct()    ->  vvcb200_emit_recon_ctu() per CTU              (vvc_intra.c:498-527)
+ *   run_sao / run_alf                   ->  vvcb200_emit_filters() once per picture       (vvc_filter.c:154-298, 1254-1319)
+ *
+ * The file is compiled against the reference's headers, where they lie (the reference tree is not part of this
+ * repository): oracle/Makefile builds it into oracle/_ref/libvvcref.so next to the harness that drives it in the tests.
+ * Pure host C, no CUDA.  A batch grows by realloc; the caller hands the arrays to vvcb200_pic_* and frees them with
+ * vvcb200_emit_free().
+ */
+#ifndef VVCB200_EMIT_H
+#define VVCB200_EMIT_H
+
+#include <stddef.h>
+#include <stdint.h>
+#include "vvc_b200.h"
+
+struct VVCLocalContext;
+struct VVCFrameContext;
+
+typedef struct VVCB200EmitBatch {
+    /* stage INTER */
+    VVCB200PredBlock *blocks;          /* in emission order; sort with vvcb200_emit_order_blocks() before submitting */
+    int n_blocks, cap_blocks;
+    VVCB200ProfTable *prof;
+    int n_prof, cap_prof;
+    /* stage RECON */
+    VVCB200TransformBlock *tbs;
+    int n_tbs, cap_tbs;
+    int16_t *levels;
+    size_t n_levels, cap_levels;
+    VVCB200IntraBlock *iblocks;        /* decoding order per CTU */
+    int n_iblocks, cap_iblocks;
+    uint32_t *ctu_first;               /* ctb_count + 1 entries once every CTU has been emitted (raster order) */
+    int n_ctus, cap_ctus;
+    int error;                         /* sticky: out of memory, or a unit the engine does not take */
+} VVCB200EmitBatch;
+
+void vvcb200_emit_reset(VVCB200EmitBatch *b);     /* keep the arrays, forget their content */
+void vvcb200_emit_free(VVCB200EmitBatch *b);
+
+/* The body of predict_inter() (vvc_inter.c:875-892) for lc->cu as records: regular units in sub-blocks of at most 16x16
+ * with their DMVR / BDOF / BCW / weighted-prediction / half-pel flags, affine units as 4x4 luma-only records + chroma-only
+ * records with derive_affine_mvc's vector + one PROF table, GPM units with VVCB200_GPM_AUX; VVCB200_PB_LMCS where the
+ * reference maps the prediction forward; CIIP units flagged VVCB200_PB_CIIP (their blend happens in RECON). */
+int vvcb200_emit_inter_cu(VVCB200EmitBatch *b, const struct VVCLocalContext *lc);
+
+/* Width order + tool groups (VVCB200InterParams.n_w16 / n_w8), stable; what vvcb200_pic_inter wants. */
+void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params);
+
+#endif /* VVCB200_EMIT_H */

@@ -6,6 +6,7 @@
  */
 #include "libavcodec/vvc/vvc_inter.c"
 #include "api_common.h"
+#include "vvcb200_emit.h"
 
 #include <stdlib.h>
 
@@ -166,6 +167,10 @@ VVCREF_EXPORT void vvcref_put(int bd, int is_chroma, int16_t *dst, const uint8_t
  * the reference splits affine units into 4x4 sub-blocks, averages vectors for chroma (derive_affine_mvc) and blends
  * GPM partitions itself.  sb_mv: affine sub-block vectors, see VVCRefInterCU.sb_mv_off.
  */
+/* When set, vvcref_inter_cus runs the product's emitter (ffmpeg_b200/emit/vvcb200_emit.c) on every coding unit it has
+ * built, in place of the reference's predict_inter(): the same reference structs in, engine records out. */
+static VVCB200EmitBatch *g_emit;
+
 VVCREF_EXPORT int vvcref_inter_cus(const VVCRefPlanes *dst, const VVCRefPlanes *refs, int n_refs,
                                    const VVCRefInterCU *cus, int n, const int32_t *sb_mv,
                                    const VVCB200InterParams *p, const uint16_t *lmcs_fwd_lut)
@@ -295,13 +300,47 @@ VVCREF_EXPORT int vvcref_inter_cus(const VVCRefPlanes *dst, const VVCRefPlanes *
                 for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++)
                     e->fc.tab.mvf[y * min_pu_width + x] = mvf;
         }
-        predict_inter(lc);
+        if (g_emit)
+            vvcb200_emit_inter_cu(g_emit, lc);              /* the emitter in predict_inter's place */
+        else
+            predict_inter(lc);
     }
-    ret = 0;
+    ret = g_emit ? g_emit->error : 0;
 end:
     free(e->fc.tab.mvf);
     free(e->cur.tab_dmvr_mvf);
     free(lc);
     free(e);
+    return ret;
+}
+
+
+/*
+ * f1 test entry: the CU-level descriptions are turned into the reference's CodingUnit / PredictionUnit / MvField state
+ * exactly as vvcref_inter_cus does, and the emitter writes the engine's records from THAT.  blocks / prof: caller
+ * arrays of cap_blocks / cap_prof records; returns the counts through n_blocks / n_prof.  order != 0: also apply the
+ * batch order and return n_w16 / n_w8 in `p`.
+ */
+VVCREF_EXPORT int vvcref_emit_inter_cus(int width, int height, const VVCRefInterCU *cus, int n, const int32_t *sb_mv,
+                                        VVCB200InterParams *p, VVCB200PredBlock *blocks, int cap_blocks, int *n_blocks,
+                                        VVCB200ProfTable *prof, int cap_prof, int *n_prof, int order)
+{
+    VVCB200EmitBatch batch = { 0 };
+    VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
+    int ret;
+    g_emit = &batch;
+    ret = vvcref_inter_cus(&pl, &pl, 0, cus, n, sb_mv, p, NULL);
+    g_emit = NULL;
+    if (!ret && order)
+        vvcb200_emit_order_blocks(&batch, p);
+    if (!ret && (batch.n_blocks > cap_blocks || batch.n_prof > cap_prof))
+        ret = -2;
+    if (!ret) {
+        memcpy(blocks, batch.blocks, (size_t)batch.n_blocks * sizeof(*blocks));
+        memcpy(prof, batch.prof, (size_t)batch.n_prof * sizeof(*prof));
+        *n_blocks = batch.n_blocks;
+        *n_prof = batch.n_prof;
+    }
+    vvcb200_emit_free(&batch);
     return ret;
 }

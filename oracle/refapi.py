@@ -232,3 +232,22 @@ def deblock_bs(st, width, height, ctb_log2, slice_idx=None, lfase=1):
     if r != 0:
         raise RuntimeError("vvcref_deblock_bs failed")
     return bs, len_p, len_q
+
+
+def emit_inter_cus(width, height, cus, sb_mv, params, order=False):
+    """synth's CU-level descriptions -> the reference's CodingUnit / PredictionUnit / MvField state (as
+    inter_cus builds it) -> the product's emitter (ffmpeg_b200/emit/vvcb200_emit.c) -> (blocks, prof, params copy)."""
+    cus = np.ascontiguousarray(cus)
+    sb = np.ascontiguousarray(sb_mv, np.int32)
+    cap = int(sum((int(c["w"]) // 4) * (int(c["h"]) // 4) * 2 for c in cus)) + 16
+    blocks = np.zeros(cap, abi.PB_DTYPE)
+    prof = np.zeros(len(cus) + 1, abi.PROF_DTYPE)
+    nb, npf = C.c_int(0), C.c_int(0)
+    p = abi.InterParams.from_buffer_copy(bytes(params))
+    r = lib().vvcref_emit_inter_cus(int(width), int(height), C.c_void_p(cus.ctypes.data), len(cus),
+                                    C.c_void_p(sb.ctypes.data) if sb.size else None, C.byref(p),
+                                    C.c_void_p(blocks.ctypes.data), cap, C.byref(nb), C.c_void_p(prof.ctypes.data), len(prof),
+                                    C.byref(npf), int(order))
+    if r != 0:
+        raise RuntimeError("vvcref_emit_inter_cus failed: %d" % r)
+    return blocks[:nb.value].copy(), prof[:npf.value].copy(), p
