@@ -274,3 +274,55 @@ void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params)
     }
     free(tmp); free(key); free(ktmp);
 }
+
+/* ---- array helpers shared with vvcb200_emit_recon.h ------------------------------------------------------------- */
+VVCB200TransformBlock *vvcb200_emit_new_tb(VVCB200EmitBatch *b)
+{
+    b->tbs = grow(b, b->tbs, &b->cap_tbs, b->n_tbs + 1, sizeof(*b->tbs));
+    if (b->error)
+        return NULL;
+    VVCB200TransformBlock *t = &b->tbs[b->n_tbs++];
+    memset(t, 0, sizeof(*t));
+    return t;
+}
+
+VVCB200IntraBlock *vvcb200_emit_new_iblock(VVCB200EmitBatch *b)
+{
+    b->iblocks = grow(b, b->iblocks, &b->cap_iblocks, b->n_iblocks + 1, sizeof(*b->iblocks));
+    if (b->error)
+        return NULL;
+    VVCB200IntraBlock *r = &b->iblocks[b->n_iblocks++];
+    memset(r, 0, sizeof(*r));
+    return r;
+}
+
+/* room for n more levels; returns their place and the offset they start at */
+int16_t *vvcb200_emit_levels(VVCB200EmitBatch *b, int n, uint32_t *off)
+{
+    if (b->n_levels + (size_t)n > b->cap_levels) {
+        size_t want = b->cap_levels ? b->cap_levels * 2 : 1 << 16;
+        while (want < b->n_levels + (size_t)n)
+            want *= 2;
+        int16_t *q = realloc(b->levels, want * sizeof(int16_t));
+        if (!q) {
+            b->error = VVCB200_ERR_NOMEM;
+            return NULL;
+        }
+        b->levels = q;
+        b->cap_levels = want;
+    }
+    *off = (uint32_t)b->n_levels;
+    b->n_levels += n;
+    return b->levels + *off;
+}
+
+/* CTUs are emitted in raster order: ctu_first[rs] = records so far, ctu_first[rs + 1] is set when the CTU is done */
+void vvcb200_emit_ctu_mark(VVCB200EmitBatch *b, int rs, int end)
+{
+    b->ctu_first = grow(b, b->ctu_first, &b->cap_ctus, rs + 2, sizeof(*b->ctu_first));
+    if (b->error)
+        return;
+    b->ctu_first[rs + end] = (uint32_t)b->n_iblocks;
+    if (rs + 1 > b->n_ctus)
+        b->n_ctus = rs + 1;
+}

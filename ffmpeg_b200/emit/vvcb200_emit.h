@@ -55,4 +55,19 @@ int vvcb200_emit_inter_cu(VVCB200EmitBatch *b, const struct VVCLocalContext *lc)
 /* Width order + tool groups (VVCB200InterParams.n_w16 / n_w8), stable; what vvcb200_pic_inter wants. */
 void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params);
 
+/* The body of ff_vvc_reconstruct() (vvc_intra.c:498-527) for CTU `rs` as records: a VVCB200TransformBlock + its scan-box
+ * levels per coded transform block (qp from derive_qp, transform pair from derive_transform_type, LFNST set / transposition
+ * from derive_ilfnst_pred_mode_intra — the reference's own functions), and a VVCB200IntraBlock per intra prediction unit
+ * and plane with the availability ff_vvc_get_top_available / ff_vvc_get_left_available report at that point of the
+ * traversal, CIIP records with ciip_derive_intra_weight's weight, add-only chroma records where the residual waits for
+ * the luma-dependent scale.  CTUs must come in raster order.  Defined in vvcb200_emit_recon.h, which is included at the
+ * end of libavcodec/vvc/vvc_intra.c (it calls that file's static helpers). */
+int vvcb200_emit_recon_ctu(VVCB200EmitBatch *b, struct VVCLocalContext *lc, int rs, int rx, int ry);
+
+/* internal: array helpers (vvcb200_emit.c) used by vvcb200_emit_recon.h */
+VVCB200TransformBlock *vvcb200_emit_new_tb(VVCB200EmitBatch *b);
+VVCB200IntraBlock *vvcb200_emit_new_iblock(VVCB200EmitBatch *b);
+int16_t *vvcb200_emit_levels(VVCB200EmitBatch *b, int n, uint32_t *off);
+void vvcb200_emit_ctu_mark(VVCB200EmitBatch *b, int rs, int end);
+
 #endif /* VVCB200_EMIT_H */

@@ -8,6 +8,7 @@
  * from the same flat descriptors the CUDA engine consumes, and calls them.
  */
 #include "libavcodec/vvc/vvc_intra.c"
+#include "vvcb200_emit_recon.h"     /* the product's RECON emitter: it belongs at the end of vvc_intra.c */
 #include "api_common.h"
 
 #include <stdlib.h>
@@ -205,6 +206,10 @@ VVCREF_EXPORT int vvcref_residual_batch(const VVCRefPlanes *pl, const int16_t *l
  */
 /* CTU rows dealt round-robin to `threads` workers; a CTU starts when the row above is two CTUs ahead, the wavefront of
  * the reference's own scheduler (vvc_thread.c:156-184). */
+/* When set, vvcref_recon_picture runs the product's emitter (ffmpeg_b200/emit/vvcb200_emit_recon.h) on every CTU in place
+ * of ff_vvc_reconstruct(): the same reference structs in, engine records out, no pixel touched. */
+static VVCB200EmitBatch *g_emit_recon;
+
 typedef struct ReconWorker {
     ReconEnv *e;
     int first_row, step, ctb_w, ctb_h;
@@ -441,7 +446,11 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
                 e->rsh.sh_dep_quant_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_DEP_QUANT);
                 e->rsh.sh_explicit_scaling_list_used_flag |= !!(tbs[tus[i].tb[c]].flags & VVCB200_TB_SCALING);
             }
-    if (threads <= 1) {
+    if (g_emit_recon) {
+        for (int ry = 0; ry < ctb_h; ry++)
+            for (int rx = 0; rx < ctb_w; rx++)
+                vvcb200_emit_recon_ctu(g_emit_recon, lc, ry * ctb_w + rx, rx, ry);
+    } else if (threads <= 1) {
         for (int ry = 0; ry < ctb_h; ry++)
             for (int rx = 0; rx < ctb_w; rx++)
                 ff_vvc_reconstruct(lc, ry * ctb_w + rx, rx, ry);
@@ -465,4 +474,47 @@ VVCREF_EXPORT int vvcref_recon_picture(const VVCRefPlanes *pl, const VVCRefCU *c
     free(cu_store); free(ctus); free(e);
     (void)n_tb_total;
     return 0;
+}
+
+/*
+ * f1 test entry: the CU / TU arrays are turned into the reference's CTU -> CodingUnit -> TransformUnit -> TransformBlock
+ * lists and per-min-CB tables exactly as vvcref_recon_picture does, and the emitter writes the engine's RECON records
+ * from THAT.  `in_tbs` / `in_levels` only feed the TransformBlock fields residual parsing would have left (scan box,
+ * levels, ts, qp); everything else in the emitted records is derived from the reference structs.  Caller-allocated
+ * outputs; returns 0, -1 (emitter error) or -2 (an output array is too small).
+ */
+VVCREF_EXPORT int vvcref_emit_recon_picture(int width, int height, const VVCRefCU *cus, int n_cus, const VVCRefTU *tus,
+                                            const VVCB200TransformBlock *in_tbs, const int16_t *in_levels,
+                                            const VVCB200ResidualParams *params, const VVCB200IntraParams *ip,
+                                            int with_refs, const VVCB200InterParams *inter,
+                                            VVCB200TransformBlock *tbs, int cap_tbs, int *n_tbs,
+                                            int16_t *levels, int cap_levels, int *n_levels,
+                                            VVCB200IntraBlock *iblocks, int cap_iblocks, int *n_iblocks,
+                                            uint32_t *ctu_first, int cap_ctus, int *n_ctus)
+{
+    VVCB200EmitBatch batch = { 0 };
+    VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
+    int ret;
+
+    g_emit_recon = &batch;
+    /* CIIP units want a reference picture list to exist; the emitter never follows it */
+    ret = vvcref_recon_picture(&pl, cus, n_cus, tus, in_tbs, in_levels, params, ip, 1, with_refs ? &pl : NULL, 0, inter, NULL);
+    g_emit_recon = NULL;
+    if (!ret && batch.error)
+        ret = -1;
+    if (!ret && (batch.n_tbs > cap_tbs || batch.n_levels > (size_t)cap_levels || batch.n_iblocks > cap_iblocks ||
+                 batch.n_ctus + 1 > cap_ctus))
+        ret = -2;
+    if (!ret) {
+        memcpy(tbs, batch.tbs, (size_t)batch.n_tbs * sizeof(*tbs));
+        memcpy(levels, batch.levels, batch.n_levels * sizeof(*levels));
+        memcpy(iblocks, batch.iblocks, (size_t)batch.n_iblocks * sizeof(*iblocks));
+        memcpy(ctu_first, batch.ctu_first, (size_t)(batch.n_ctus + 1) * sizeof(*ctu_first));
+        *n_tbs = batch.n_tbs;
+        *n_levels = (int)batch.n_levels;
+        *n_iblocks = batch.n_iblocks;
+        *n_ctus = batch.n_ctus;
+    }
+    vvcb200_emit_free(&batch);
+    return ret;
 }
