@@ -326,3 +326,215 @@ void vvcb200_emit_ctu_mark(VVCB200EmitBatch *b, int rs, int end)
     if (rs + 1 > b->n_ctus)
         b->n_ctus = rs + 1;
 }
+
+/* ---- loop filters --------------------------------------------------------------------------------------------- */
+#define EMIT_CTB(tab, x, y) ((tab)[(y) * pps->ctb_width + (x)])
+
+/* The unfilterable sides / corners ff_vvc_sao_filter works out before it touches a sample (vvc_filter.c:163-211). */
+static uint8_t sao_no_filter(const VVCFrameContext *fc, const int x_ctb, const int y_ctb)
+{
+    const VVCPPS *pps        = fc->ps.pps;
+    const int16_t *slice_idx = fc->tab.slice_idx;
+    const int lfase          = pps->r->pps_loop_filter_across_slices_enabled_flag;
+    const int no_tile_filter = pps->r->num_tiles_in_pic > 1 && !pps->r->pps_loop_filter_across_tiles_enabled_flag;
+    const int left = x_ctb == 0, top = y_ctb == 0, right = x_ctb == pps->ctb_width - 1, bottom = y_ctb == pps->ctb_height - 1;
+    const int here = EMIT_CTB(slice_idx, x_ctb, y_ctb);
+    int lt = 0, rt = 0, ut = 0, bt = 0, flags = 0;
+#define OTHER_SLICE(dx, dy) (!lfase && here != EMIT_CTB(slice_idx, x_ctb + (dx), y_ctb + (dy)))
+
+    if (!no_tile_filter && lfase)
+        return 0;
+    if (!left) {
+        lt = no_tile_filter && pps->ctb_to_col_bd[x_ctb] == x_ctb;
+        flags |= (OTHER_SLICE(-1, 0) || lt) << 0;
+    }
+    if (!right) {
+        rt = no_tile_filter && pps->ctb_to_col_bd[x_ctb] != pps->ctb_to_col_bd[x_ctb + 1];
+        flags |= (OTHER_SLICE(1, 0) || rt) << 1;
+    }
+    if (!top) {
+        ut = no_tile_filter && pps->ctb_to_row_bd[y_ctb] == y_ctb;
+        flags |= (OTHER_SLICE(0, -1) || ut) << 2;
+    }
+    if (!bottom) {
+        bt = no_tile_filter && pps->ctb_to_row_bd[y_ctb] != pps->ctb_to_row_bd[y_ctb + 1];
+        flags |= (OTHER_SLICE(0, 1) || bt) << 3;
+    }
+    if (!left && !top)
+        flags |= (OTHER_SLICE(-1, -1) || lt || ut) << 4;
+    if (!top && !right)
+        flags |= (OTHER_SLICE(1, -1) || rt || ut) << 5;
+    if (!right && !bottom)
+        flags |= (OTHER_SLICE(1, 1) || rt || bt) << 6;
+    if (!left && !bottom)
+        flags |= (OTHER_SLICE(-1, 1) || lt || bt) << 7;
+#undef OTHER_SLICE
+    return flags;
+}
+
+/* fc->tab.mvf / tb_pos / cb_pos / flags of one 4x4 unit -> the two compact records vvcb200_deblock_derive_edges reads.
+ * What vvc_deblock_bs looks at: vvc_filter.c:308-371 (motion), 399-475 (TB sizes), 477-782 (TB / CU / sub-block edges). */
+static void emit_unit(const VVCB200EmitFilters *out, const VVCFrameContext *fc, const RefPicList *rpl, const int ux, const int uy)
+{
+    const int o = uy * fc->ps.pps->min_pu_width + ux;
+    const MvField *m = &fc->tab.mvf[o];
+    VVCB200MotionUnit *mu = &out->motion[o];
+    VVCB200PartitionUnit *pu = &out->part[o];
+
+    memset(mu, 0, sizeof(*mu));
+    memset(pu, 0, sizeof(*pu));
+    mu->pred_flag = m->pred_flag;
+    mu->ciip_flag = m->ciip_flag;
+    for (int l = 0; l < 2; l++) {
+        mu->mv[l][0] = m->mv[l].x;
+        mu->mv[l][1] = m->mv[l].y;
+        /* the reference compares the POCs rpl->list[ref_idx] (vvc_filter.c:320-352); the picture behind one is the same
+         * question, and the DPB slot answers it without a search */
+        if (rpl && m->ref_idx[l] >= 0 && rpl[l].ref[m->ref_idx[l]])
+            mu->ref_id[l] = (int8_t)(rpl[l].ref[m->ref_idx[l]] - fc->DPB);
+    }
+    pu->tb_off   = ((ux - (fc->tab.tb_pos_x0[LUMA][o] >> 2)) & 15) | (((uy - (fc->tab.tb_pos_y0[LUMA][o] >> 2)) & 15) << 4);
+    pu->tb_size  = av_log2(FFMAX(fc->tab.tb_width[LUMA][o], 1)) | (av_log2(FFMAX(fc->tab.tb_height[LUMA][o], 1)) << 3) |
+                   (!!fc->tab.tu_coded_flag[LUMA][o] << 6) | (!!fc->tab.pcmf[LUMA][o] << 7);
+    pu->cu_off_x = ((ux - (fc->tab.cb_pos_x[LUMA][o] >> 2)) & 31) | ((fc->tab.msf[o] || fc->tab.iaf[o]) << 5) |
+                   ((fc->tab.cb_width[LUMA][o] > 8) << 6) | ((fc->tab.cb_height[LUMA][o] > 8) << 7);
+    pu->cu_off_y = (uy - (fc->tab.cb_pos_y[LUMA][o] >> 2)) & 31;
+    pu->ctb_off  = ((ux - (fc->tab.tb_pos_x0[CHROMA][o] >> 2)) & 15) | (((uy - (fc->tab.tb_pos_y0[CHROMA][o] >> 2)) & 15) << 4);
+    pu->ctb_size = av_log2(FFMAX(fc->tab.tb_width[CHROMA][o], 1)) | (av_log2(FFMAX(fc->tab.tb_height[CHROMA][o], 1)) << 3) |
+                   (!!fc->tab.tu_coded_flag[CB][o] << 6) | (!!fc->tab.tu_coded_flag[CR][o] << 7);
+    pu->cflags   = (fc->tab.tu_joint_cbcr_residual_flag[o] != 0) | (!!fc->tab.pcmf[CHROMA][o] << 1);
+}
+
+void vvcb200_emit_filters_ctu(const VVCB200EmitFilters *out, const VVCLocalContext *lc, const int rx, const int ry)
+{
+    const VVCFrameContext *fc = lc->fc;
+    const VVCSPS *sps         = fc->ps.sps;
+    const VVCPPS *pps         = fc->ps.pps;
+    const int rs              = ry * pps->ctb_width + rx;
+    const int lfase           = pps->r->pps_loop_filter_across_slices_enabled_flag;
+    const int lfate           = pps->r->pps_loop_filter_across_tiles_enabled_flag;
+
+    if (out->sao) {
+        const SAOParams *s = &fc->tab.sao[rs];
+        VVCB200SaoCtb *d = &out->sao[rs];
+        memset(d, 0, sizeof(*d));
+        for (int c = 0; c < 3; c++) {
+            d->type_idx[c]      = s->type_idx[c];
+            d->band_position[c] = s->band_position[c];
+            d->eo_class[c]      = s->eo_class[c];
+            for (int k = 0; k < 5; k++)
+                d->offset_val[c][k] = s->offset_val[c][k];
+        }
+        d->no_filter = sao_no_filter(fc, rx, ry);
+    }
+    if (out->alf) {
+        const ALFParams *a = &fc->tab.alf[rs];
+        VVCB200AlfCtb *d = &out->alf[rs];
+        /* ff_vvc_alf_filter's edges[] (vvc_filter.c:1266-1280) without the picture borders, which the device knows */
+        const int last_x = rx == pps->ctb_width - 1, last_y = ry == pps->ctb_height - 1;
+        int left = 0, top = 0, right = 0, bottom = 0;
+        if (!lfate) {
+            left   |= !!(lc->boundary_flags & BOUNDARY_LEFT_TILE);
+            top    |= !!(lc->boundary_flags & BOUNDARY_UPPER_TILE);
+            right  |= !last_x && pps->ctb_to_col_bd[rx] != pps->ctb_to_col_bd[rx + 1];
+            bottom |= !last_y && pps->ctb_to_row_bd[ry] != pps->ctb_to_row_bd[ry + 1];
+        }
+        if (!lfase) {
+            left   |= !!(lc->boundary_flags & BOUNDARY_LEFT_SLICE);
+            top    |= !!(lc->boundary_flags & BOUNDARY_UPPER_SLICE);
+            right  |= !last_x && EMIT_CTB(fc->tab.slice_idx, rx, ry) != EMIT_CTB(fc->tab.slice_idx, rx + 1, ry);
+            bottom |= !last_y && EMIT_CTB(fc->tab.slice_idx, rx, ry) != EMIT_CTB(fc->tab.slice_idx, rx, ry + 1);
+        }
+        memset(d, 0, sizeof(*d));
+        for (int c = 0; c < 3; c++)
+            d->ctb_flag[c] = a->ctb_flag[c];
+        d->filt_set_idx_y = a->ctb_filt_set_idx_y;
+        for (int c = 0; c < 2; c++) {
+            d->alt_idx[c] = a->alf_ctb_filter_alt_idx[c];
+            d->cc_idc[c]  = a->ctb_cc_idc[c];
+        }
+        d->edges = left | (top << 1) | (right << 2) | (bottom << 3);
+    }
+    if (out->ctb_offsets) {
+        const DBParams *p = &fc->tab.deblock[rs];
+        for (int c = 0; c < 3; c++) {
+            out->ctb_offsets[rs * 6 + c]     = p->beta_offset[c];
+            out->ctb_offsets[rs * 6 + 3 + c] = p->tc_offset[c];
+        }
+    }
+    if (out->ctb_edges)             /* vvc_filter.c:505-512, 572-579: CTB sides the deblocking filter must not cross */
+        out->ctb_edges[rs] = ((!lfase && (lc->boundary_flags & BOUNDARY_LEFT_SLICE)) || (!lfate && (lc->boundary_flags & BOUNDARY_LEFT_TILE))) |
+                             (((!lfase && (lc->boundary_flags & BOUNDARY_UPPER_SLICE)) || (!lfate && (lc->boundary_flags & BOUNDARY_UPPER_TILE))) << 1);
+    if (out->motion && out->part) {
+        const int x0 = rx << sps->ctb_log2_size_y, y0 = ry << sps->ctb_log2_size_y;
+        const int ux1 = FFMIN(x0 + sps->ctb_size_y, pps->width) >> 2, uy1 = FFMIN(y0 + sps->ctb_size_y, pps->height) >> 2;
+        const RefPicList *rpl = lc->sc->rpl;                    /* the lists of the slice this CTB belongs to */
+        for (int uy = y0 >> 2; uy < uy1; uy++)
+            for (int ux = x0 >> 2; ux < ux1; ux++)
+                emit_unit(out, fc, rpl, ux, uy);
+    }
+}
+
+void vvcb200_emit_alf_params(VVCB200AlfParams *p, const VVCFrameContext *fc, const SliceContext *sc)
+{
+    const H266RawSliceHeader *rsh = sc->sh.r;
+    const VVCALF *chroma = fc->ps.alf_list[rsh->sh_alf_aps_id_chroma];
+
+    memset(p, 0, sizeof(*p));
+    p->bit_depth     = fc->ps.sps->bit_depth;
+    p->ctb_log2_size = fc->ps.sps->ctb_log2_size_y;
+    for (int k = 0; k < rsh->sh_num_alf_aps_ids_luma && k < 7; k++) {          /* alf_get_coeff_and_clip, vvc_filter.c:1155-1160 */
+        const VVCALF *aps = fc->ps.alf_list[rsh->sh_alf_aps_id_luma[k]];
+        if (!aps)
+            continue;
+        memcpy(p->luma_coeff[k], aps->luma_coeff, sizeof(p->luma_coeff[k]));
+        memcpy(p->luma_clip_idx[k], aps->luma_clip_idx, sizeof(p->luma_clip_idx[k]));
+    }
+    if (chroma) {                                                                 /* alf_filter_chroma, 1196-1211 */
+        memcpy(p->chroma_coeff, chroma->chroma_coeff, sizeof(p->chroma_coeff));
+        memcpy(p->chroma_clip_idx, chroma->chroma_clip_idx, sizeof(p->chroma_clip_idx));
+    }
+    for (int i = 0; i < 2; i++) {                                                 /* alf_filter_cc, 1213-1228 */
+        const VVCALF *cc = fc->ps.alf_list[i ? rsh->sh_alf_cc_cr_aps_id : rsh->sh_alf_cc_cb_aps_id];   /* NULL: no such APS */
+        p->cc_enabled[i] = cc != NULL;
+        if (cc)
+            for (int f = 0; f < 4; f++)
+                for (int k = 0; k < 7; k++)
+                    p->cc_coeff[i][f][k] = cc->cc_coeff[i][f][k];
+    }
+}
+
+void vvcb200_emit_deblock_params(VVCB200DeblockParams *p, const VVCFrameContext *fc)
+{
+    const VVCSPS *sps = fc->ps.sps;
+
+    memset(p, 0, sizeof(*p));
+    p->bit_depth     = sps->bit_depth;
+    p->ctb_log2_size = sps->ctb_log2_size_y;
+    p->ladf_enabled  = sps->r->sps_ladf_enabled_flag;                            /* get_qp_y / ladf, vvc_filter.c:829-859 */
+    p->ladf_lowest_interval_qp_offset = sps->r->sps_ladf_lowest_interval_qp_offset;
+    p->num_ladf_intervals = sps->num_ladf_intervals;
+    for (int i = 0; i < 4; i++)
+        p->ladf_qp_offset[i] = sps->r->sps_ladf_qp_offset[i];
+    for (int i = 0; i < 5; i++)
+        p->ladf_interval_lower_bound[i] = sps->ladf_interval_lower_bound[i];
+}
+
+void vvcb200_emit_store_refined_mv(const VVCFrameContext *fc, const VVCB200PredBlock *blocks, const int n, const int32_t *refined_mv)
+{
+    const int min_pu_width = fc->ps.pps->min_pu_width;
+
+    for (int i = 0; i < n; i++) {
+        const VVCB200PredBlock *b = &blocks[i];
+        if (!(b->flags & VVCB200_PB_DMVR))
+            continue;
+        MvField m = fc->tab.mvf[(b->y0 >> MIN_PU_LOG2) * min_pu_width + (b->x0 >> MIN_PU_LOG2)];
+        for (int l = 0; l < 2; l++) {
+            m.mv[l].x = refined_mv[i * 4 + l * 2];
+            m.mv[l].y = refined_mv[i * 4 + l * 2 + 1];
+        }
+        for (int y = b->y0; y < b->y0 + b->h; y += MIN_PU_SIZE)              /* set_dmvr_info, vvc_inter.c:749-761 */
+            for (int x = b->x0; x < b->x0 + b->w; x += MIN_PU_SIZE)
+                fc->ref->tab_dmvr_mvf[(y >> MIN_PU_LOG2) * min_pu_width + (x >> MIN_PU_LOG2)] = m;
+    }
+}

@@ -64,6 +64,30 @@ void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params);
  * end of libavcodec/vvc/vvc_intra.c (it calls that file's static helpers). */
 int vvcb200_emit_recon_ctu(VVCB200EmitBatch *b, struct VVCLocalContext *lc, int rs, int rx, int ry);
 
+/* ---- loop filters: per-CTB parameters and the per-4x4 state the device derives boundary strengths from ---------------
+ * Caller-owned arrays (pinned host memory in a decoder: they are what vvcb200_pic_deblock / vvcb200_pic_sao_alf upload). */
+struct SliceContext;
+typedef struct VVCB200EmitFilters {
+    VVCB200SaoCtb *sao;                /* ctb_count, raster */
+    VVCB200AlfCtb *alf;                /* ctb_count */
+    int8_t        *ctb_offsets;        /* ctb_count x 6: beta_offset[3], tc_offset[3] (fc->tab.deblock, DBParams) */
+    uint8_t       *ctb_edges;          /* ctb_count: bit0 / bit1 = left / upper CTB side not to be deblocked across */
+    VVCB200MotionUnit    *motion;      /* min_pu_width x min_pu_height */
+    VVCB200PartitionUnit *part;
+} VVCB200EmitFilters;
+
+/* One CTB: what ff_vvc_sao_filter (vvc_filter.c:154-212), ff_vvc_alf_filter (1254-1280) and vvc_deblock_bs (308-782) read
+ * about it, flattened.  lc must have been through ff_vvc_decode_neighbour() for this CTB (boundary_flags, sc). The QP tables
+ * need no conversion: VVCB200DeblockTables.d_qp[c] is a copy of fc->tab.qp[c] as it is. */
+void vvcb200_emit_filters_ctu(const VVCB200EmitFilters *out, const struct VVCLocalContext *lc, int rx, int ry);
+/* The APS content a slice header selects (alf_filter_luma / _chroma / _cc, vvc_filter.c:1161-1228). */
+void vvcb200_emit_alf_params(VVCB200AlfParams *p, const struct VVCFrameContext *fc, const struct SliceContext *sc);
+void vvcb200_emit_deblock_params(VVCB200DeblockParams *p, const struct VVCFrameContext *fc);
+/* run_inter's other half (vvc_inter.c:750-762): the vectors DMVR settled on, as vvcb200_pic_inter returned them for the
+ * sorted batch, written into fc->ref->tab_dmvr_mvf for the units of the flagged records. */
+void vvcb200_emit_store_refined_mv(const struct VVCFrameContext *fc, const VVCB200PredBlock *blocks, int n,
+                                   const int32_t *refined_mv /* n x 2 x 2 */);
+
 /* internal: array helpers (vvcb200_emit.c) used by vvcb200_emit_recon.h */
 VVCB200TransformBlock *vvcb200_emit_new_tb(VVCB200EmitBatch *b);
 VVCB200IntraBlock *vvcb200_emit_new_iblock(VVCB200EmitBatch *b);

@@ -285,7 +285,7 @@ static void emit_ciip(VVCB200EmitBatch *b, VVCLocalContext *lc)
     const int planes = coded ? emit_chroma_residual_planes(tu) : 0;
 
     if (coded && tu->next) {            /* one record adds the residual over the whole block: it must be one TU */
-        b->error = 1;
+        b->error = VVCB200_ERR_UNSUP;
         return;
     }
     ff_vvc_set_neighbour_available(lc, cu->x0, cu->y0, cu->cb_width, cu->cb_height);

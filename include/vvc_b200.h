@@ -363,7 +363,8 @@ typedef struct VVCB200AlfCtb {      /* ALFParams, vvc_ctu.h:453-460, plus the CT
     uint8_t filt_set_idx_y;         /* AlfCtbFiltSetIdxY: < 16 fixed filter set, else 16 + index into luma sets   */
     uint8_t alt_idx[2];             /* alf_ctb_filter_alt_idx[]                                                   */
     uint8_t cc_idc[2];              /* alf_ctb_cc_cb_idc, alf_ctb_cc_cr_idc                                       */
-    uint8_t edges;                  /* bit0 LEFT, bit1 TOP, bit2 RIGHT, bit3 BOTTOM: picture / slice / tile limit */
+    uint8_t edges;                  /* bit0 LEFT, bit1 TOP, bit2 RIGHT, bit3 BOTTOM: slice / tile limit (picture
+                                       borders are implied; setting them too is harmless)                       */
     uint8_t reserved[3];
 } VVCB200AlfCtb;                    /* 12 bytes */
 

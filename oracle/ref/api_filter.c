@@ -6,6 +6,7 @@
  */
 #include "libavcodec/vvc/vvc_filter.c"
 #include "api_common.h"
+#include "vvcb200_emit.h"
 
 #include <stdlib.h>
 
@@ -357,6 +358,10 @@ VVCREF_EXPORT int vvcref_lmcs_picture(const VVCRefPlanes *pl, const uint16_t *in
  *   ref_poc[2][16]: RefPicList.list of the (single) slice
  * Output: bs[dir][c], len_p[dir], len_q[dir] (stride4 x rows4 bytes, zero where the reference writes nothing).
  */
+/* When set, vvcref_deblock_bs runs the product's emitter (vvcb200_emit_filters_ctu) on every CTB in place of the
+ * reference's vvc_deblock_bs: the same fc->tab.* state in, the engine's compact per-4x4 records out. */
+static const VVCB200EmitFilters *g_emit_filters;
+
 VVCREF_EXPORT int vvcref_deblock_bs(int width, int height, int ctb_log2, const void *mvf,
                                     const int32_t *const tb_pos_x0[2], const int32_t *const tb_pos_y0[2],
                                     const uint8_t *const tb_width[2], const uint8_t *const tb_height[2],
@@ -390,6 +395,10 @@ VVCREF_EXPORT int vvcref_deblock_bs(int width, int height, int ctb_log2, const v
     for (int l = 0; l < 2; l++)
         for (int i = 0; i < 16; i++)
             e->rpl[l].list[i] = ref_poc[l * 16 + i];
+    if (g_emit_filters)                                     /* the picture behind each POC: DPB slot POC - 100 */
+        for (int l = 0; l < 2; l++)
+            for (int i = 0; i < 16; i++)
+                e->rpl[l].ref[i] = &e->fc.DPB[(ref_poc[l * 16 + i] - 100) & 15];
     for (int c = 0; c < 3; c++) {
         memset(bs[0][c], 0, units);
         memset(bs[1][c], 0, units);
@@ -416,10 +425,122 @@ VVCREF_EXPORT int vvcref_deblock_bs(int width, int height, int ctb_log2, const v
         for (int rx = 0; rx < (int)e->pps.ctb_width; rx++) {
             const int x0 = rx << ctb_log2, y0 = ry << ctb_log2;
             ff_vvc_decode_neighbour(e->lc, x0, y0, rx, ry, ry * e->pps.ctb_width + rx);
+            if (g_emit_filters) {
+                vvcb200_emit_filters_ctu(g_emit_filters, e->lc, rx, ry);
+                continue;
+            }
             vvc_deblock_bs(e->lc, x0, y0, 1);
             vvc_deblock_bs(e->lc, x0, y0, 0);
         }
     free(rpl_tab);
+    filter_env_free(e);
+    return 0;
+}
+
+
+/* f1 test entry: the per-4x4 state in the reference's format -> vvcb200_emit_filters_ctu -> VVCB200MotionUnit /
+ * VVCB200PartitionUnit tables + the per-CTB "do not deblock across" flags.  Same inputs as vvcref_deblock_bs. */
+VVCREF_EXPORT int vvcref_emit_deblock_units(int width, int height, int ctb_log2, const void *mvf,
+                                            const int32_t *const tb_pos_x0[2], const int32_t *const tb_pos_y0[2],
+                                            const uint8_t *const tb_width[2], const uint8_t *const tb_height[2],
+                                            const int32_t *cb_pos_x, const int32_t *cb_pos_y, const uint8_t *cb_width,
+                                            const uint8_t *cb_height, const uint8_t *const tu_coded_flag[3], const uint8_t *tu_joint,
+                                            const uint8_t *const pcmf[2], const uint8_t *msf, const uint8_t *iaf,
+                                            const int32_t *ref_poc, const int16_t *slice_idx, int lfase,
+                                            VVCB200MotionUnit *motion, VVCB200PartitionUnit *part, uint8_t *ctb_edges)
+{
+    const size_t units = (size_t)((width + 3) >> 2) * ((height + 3) >> 2);
+    uint8_t *dummy = malloc(units);
+    uint8_t *const bs[2][3] = { { dummy, dummy, dummy }, { dummy, dummy, dummy } };
+    uint8_t *const len[2] = { dummy, dummy };
+    const VVCB200EmitFilters out = { .motion = motion, .part = part, .ctb_edges = ctb_edges };
+    int ret;
+
+    g_emit_filters = &out;
+    ret = vvcref_deblock_bs(width, height, ctb_log2, mvf, tb_pos_x0, tb_pos_y0, tb_width, tb_height, cb_pos_x, cb_pos_y, cb_width,
+                            cb_height, tu_coded_flag, tu_joint, pcmf, msf, iaf, ref_poc, slice_idx, lfase, bs, len, len);
+    g_emit_filters = NULL;
+    free(dummy);
+    return ret;
+}
+
+/* f1 test entry: per-CTB SAO / ALF / deblocking parameters planted in the reference's format (SAOParams, ALFParams, the
+ * VVCALF APS list behind the slice header, DBParams, the LADF fields of the SPS) exactly as vvcref_sao_picture /
+ * vvcref_alf_picture / vvcref_deblock_picture plant them -> the emitter -> the engine's records, restore / edge flags
+ * included (the inputs' no_filter / edges are NOT read). */
+VVCREF_EXPORT int vvcref_emit_loopfilter_ctbs(int width, int height, int ctb_log2, int bit_depth,
+                                              const VVCB200SaoCtb *in_sao, const VVCB200AlfCtb *in_alf,
+                                              const VVCB200AlfParams *in_ap, const int16_t *slice_idx, int lfase,
+                                              const int8_t *in_offsets, const VVCB200DeblockParams *in_dp,
+                                              VVCB200SaoCtb *sao_out, VVCB200AlfCtb *alf_out, VVCB200AlfParams *ap_out,
+                                              int8_t *offsets_out, uint8_t *ctb_edges_out, VVCB200DeblockParams *dp_out)
+{
+    VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
+    FilterEnv *e = filter_env_new(&pl, bit_depth, ctb_log2);
+    const unsigned n = e->pps.ctb_count;
+    SAOParams *sao = calloc(n, sizeof(*sao));
+    ALFParams *alf = calloc(n, sizeof(*alf));
+    DBParams *db   = calloc(n, sizeof(*db));
+    VVCALF *aps    = calloc(8, sizeof(*aps));
+    const VVCB200EmitFilters out = { .sao = sao_out, .alf = alf_out, .ctb_offsets = offsets_out, .ctb_edges = ctb_edges_out };
+
+    plant_slices(e, slice_idx, lfase);
+    for (unsigned i = 0; i < n; i++) {
+        for (int c = 0; c < 3; c++) {
+            sao[i].type_idx[c]      = in_sao[i].type_idx[c];
+            sao[i].band_position[c] = in_sao[i].band_position[c];
+            sao[i].eo_class[c]      = in_sao[i].eo_class[c];
+            for (int k = 0; k < 5; k++)
+                sao[i].offset_val[c][k] = in_sao[i].offset_val[c][k];
+            alf[i].ctb_flag[c]      = in_alf[i].ctb_flag[c];
+            db[i].beta_offset[c]    = in_offsets[i * 6 + c];
+            db[i].tc_offset[c]      = in_offsets[i * 6 + 3 + c];
+        }
+        alf[i].ctb_filt_set_idx_y = in_alf[i].filt_set_idx_y;
+        for (int c = 0; c < 2; c++) {
+            alf[i].alf_ctb_filter_alt_idx[c] = in_alf[i].alt_idx[c];
+            alf[i].ctb_cc_idc[c]             = in_alf[i].cc_idc[c];
+        }
+    }
+    e->fc.tab.sao = sao;
+    e->fc.tab.alf = alf;
+    e->fc.tab.deblock = db;
+    /* the APS list as vvcref_alf_picture lays it out: luma set k -> APS k, chroma + cross-component -> APS 7 */
+    for (int k = 0; k < 7; k++) {
+        memcpy(aps[k].luma_coeff, in_ap->luma_coeff[k], sizeof(aps[k].luma_coeff));
+        memcpy(aps[k].luma_clip_idx, in_ap->luma_clip_idx[k], sizeof(aps[k].luma_clip_idx));
+        e->rsh.sh_alf_aps_id_luma[k] = k;
+    }
+    e->rsh.sh_num_alf_aps_ids_luma = 7;
+    memcpy(aps[7].chroma_coeff, in_ap->chroma_coeff, sizeof(aps[7].chroma_coeff));
+    memcpy(aps[7].chroma_clip_idx, in_ap->chroma_clip_idx, sizeof(aps[7].chroma_clip_idx));
+    for (int i = 0; i < 2; i++)
+        for (int f = 0; f < 4; f++)
+            for (int k = 0; k < 7; k++)
+                aps[7].cc_coeff[i][f][k] = in_ap->cc_coeff[i][f][k];
+    e->rsh.sh_alf_aps_id_chroma = 7;
+    e->rsh.sh_alf_cc_cb_aps_id  = in_ap->cc_enabled[0] ? 7 : 6;
+    e->rsh.sh_alf_cc_cr_aps_id  = in_ap->cc_enabled[1] ? 7 : 6;
+    for (int k = 0; k < 8; k++)
+        e->fc.ps.alf_list[k] = &aps[k];
+    if (!in_ap->cc_enabled[0] || !in_ap->cc_enabled[1])
+        e->fc.ps.alf_list[6] = NULL;
+    e->rsps.sps_ladf_enabled_flag = in_dp->ladf_enabled;
+    e->rsps.sps_ladf_lowest_interval_qp_offset = in_dp->ladf_lowest_interval_qp_offset;
+    e->sps.num_ladf_intervals = in_dp->num_ladf_intervals;
+    for (int i = 0; i < 4; i++)
+        e->rsps.sps_ladf_qp_offset[i] = in_dp->ladf_qp_offset[i];
+    for (int i = 0; i < 5; i++)
+        e->sps.ladf_interval_lower_bound[i] = in_dp->ladf_interval_lower_bound[i];
+
+    for (int ry = 0; ry < (int)e->pps.ctb_height; ry++)
+        for (int rx = 0; rx < (int)e->pps.ctb_width; rx++) {
+            ff_vvc_decode_neighbour(e->lc, rx << ctb_log2, ry << ctb_log2, rx, ry, ry * e->pps.ctb_width + rx);
+            vvcb200_emit_filters_ctu(&out, e->lc, rx, ry);
+        }
+    vvcb200_emit_alf_params(ap_out, &e->fc, &e->sc);
+    vvcb200_emit_deblock_params(dp_out, &e->fc);
+    free(aps); free(db); free(alf); free(sao);
     filter_env_free(e);
     return 0;
 }

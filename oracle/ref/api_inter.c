@@ -34,6 +34,8 @@ typedef struct InterEnv {
  * derivation, DMVR search and BDOF all run unmodified.  Arguments mirror vvcb200_inter_batch().
  * refined_mv (optional, n x 2 x 2 ints): MvField.mv after DMVR as stored in tab_dmvr_mvf.
  */
+static int g_store_check;
+
 VVCREF_EXPORT int vvcref_inter_batch(const VVCRefPlanes *dst, const VVCRefPlanes *refs, int n_refs,
                                      const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *p,
                                      const uint16_t *lmcs_fwd_lut, int32_t *refined_mv)
@@ -142,11 +144,38 @@ VVCREF_EXPORT int vvcref_inter_batch(const VVCRefPlanes *dst, const VVCRefPlanes
         }
     }
     ret = 0;
+    if (g_store_check && refined_mv) {
+        /* f1: the emitter's write-back of the refined vectors (vvcb200_emit_store_refined_mv) into a fresh table must
+         * leave what the reference's own set_dmvr_info calls left in tab_dmvr_mvf */
+        const size_t units = (size_t)min_pu_width * min_pu_height;
+        MvField *want = e->cur.tab_dmvr_mvf;
+        e->cur.tab_dmvr_mvf = calloc(units, sizeof(MvField));
+        vvcb200_emit_store_refined_mv(&e->fc, blocks, n, refined_mv);
+        for (size_t u = 0; u < units; u++) {
+            const MvField *a = &want[u], *b = &e->cur.tab_dmvr_mvf[u];
+            ret += a->mv[0].x != b->mv[0].x || a->mv[0].y != b->mv[0].y || a->mv[1].x != b->mv[1].x || a->mv[1].y != b->mv[1].y ||
+                   a->ref_idx[0] != b->ref_idx[0] || a->ref_idx[1] != b->ref_idx[1] || a->pred_flag != b->pred_flag ||
+                   a->bcw_idx != b->bcw_idx || a->hpel_if_idx != b->hpel_if_idx || a->ciip_flag != b->ciip_flag;
+        }
+        free(want);
+    }
 end:
     free(e->fc.tab.mvf);
     free(e->cur.tab_dmvr_mvf);
     free(lc);
     free(e);
+    return ret;
+}
+
+/* Number of 4x4 units whose tab_dmvr_mvf entry differs between the reference's run and the emitter's write-back. */
+VVCREF_EXPORT int vvcref_emit_store_refined_check(const VVCRefPlanes *dst, const VVCRefPlanes *refs, int n_refs,
+                                                  const VVCB200PredBlock *blocks, int n, const VVCB200InterParams *p,
+                                                  int32_t *refined_mv)
+{
+    int ret;
+    g_store_check = 1;
+    ret = vvcref_inter_batch(dst, refs, n_refs, blocks, n, p, NULL, refined_mv);
+    g_store_check = 0;
     return ret;
 }
 

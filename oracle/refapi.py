@@ -276,3 +276,62 @@ def emit_recon_picture(width, height, ref, intra_params, inter=None):
     if r != 0:
         raise RuntimeError("vvcref_emit_recon_picture failed: %d" % r)
     return tbs[:nt.value].copy(), lv[:nl.value].copy(), ibs[:ni.value].copy(), first[:nc.value + 1].copy()
+
+
+def emit_deblock_units(st, width, height, ctb_log2, slice_idx=None, lfase=1):
+    """synth.deblock_state()'s tables in the reference's format (fc->tab.mvf, tb_pos_*, cb_pos_*, ...) ->
+    vvcb200_emit_filters_ctu -> (motion units, partition units, per-CTB no-deblock flags)."""
+    r4, s4 = st["rows4"], st["stride4"]
+    cw, ch = (width + (1 << ctb_log2) - 1) >> ctb_log2, (height + (1 << ctb_log2) - 1) >> ctb_log2
+    motion = np.zeros((r4, s4), abi.MOTION_DTYPE)
+    part = np.zeros((r4, s4), abi.PARTITION_DTYPE)
+    edges = np.zeros(cw * ch, np.uint8)
+    keep = {k: np.ascontiguousarray(st[k]) for k in ("mvf", "tb_pos_x0", "tb_pos_y0", "tb_width", "tb_height", "cb_pos_x", "cb_pos_y",
+                                                      "cb_width", "cb_height", "tu_coded_flag", "tu_joint", "pcmf", "msf", "iaf", "ref_poc")}
+    sl = None if slice_idx is None else np.ascontiguousarray(slice_idx, np.int16)
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    _plant_tiles({})
+    r = lib().vvcref_emit_deblock_units(int(width), int(height), int(ctb_log2), p(keep["mvf"]),
+                                        _ptr_grid(keep["tb_pos_x0"], (2,)), _ptr_grid(keep["tb_pos_y0"], (2,)),
+                                        _ptr_grid(keep["tb_width"], (2,)), _ptr_grid(keep["tb_height"], (2,)),
+                                        p(keep["cb_pos_x"]), p(keep["cb_pos_y"]), p(keep["cb_width"]), p(keep["cb_height"]),
+                                        _ptr_grid(keep["tu_coded_flag"], (3,)), p(keep["tu_joint"]), _ptr_grid(keep["pcmf"], (2,)),
+                                        p(keep["msf"]), p(keep["iaf"]), p(keep["ref_poc"]), p(sl) if sl is not None else None,
+                                        int(lfase), p(motion), p(part), p(edges))
+    if r != 0:
+        raise RuntimeError("vvcref_emit_deblock_units failed")
+    return motion, part, edges
+
+
+def emit_loopfilter_ctbs(t, width, height, ctb_offsets, deblock_params):
+    """synth.loopfilter_ctbs() parameters planted as SAOParams / ALFParams / VVCALF APS list / DBParams ->
+    vvcb200_emit_filters_ctu + vvcb200_emit_alf_params + vvcb200_emit_deblock_params -> the engine's records."""
+    n = len(t["sao"])
+    sao_in, alf_in = np.ascontiguousarray(t["sao"]), np.ascontiguousarray(t["alf"])
+    ap_in = np.ascontiguousarray(t["alf_params"])
+    off_in = np.ascontiguousarray(ctb_offsets, np.int8)
+    sl = np.ascontiguousarray(t["slice_idx"], np.int16)
+    sao, alf = np.zeros(n, abi.SAO_DTYPE), np.zeros(n, abi.ALF_CTB_DTYPE)
+    ap = np.zeros(1, abi.ALF_PARAMS_DTYPE)
+    off, edges = np.zeros((n, 6), np.int8), np.zeros(n, np.uint8)
+    dp = abi.DeblockParams()
+    p = lambda a: C.c_void_p(a.ctypes.data)
+    _plant_tiles(t)
+    r = lib().vvcref_emit_loopfilter_ctbs(int(width), int(height), int(t["ctb_log2"]), int(t["bd"]), p(sao_in), p(alf_in), p(ap_in),
+                                          p(sl), int(t["lfase"]), p(off_in), C.byref(deblock_params),
+                                          p(sao), p(alf), p(ap), p(off), p(edges), C.byref(dp))
+    _plant_tiles({})
+    if r != 0:
+        raise RuntimeError("vvcref_emit_loopfilter_ctbs failed")
+    return sao, alf, ap, off, edges, dp
+
+
+def emit_store_refined_check(dst, refs, blocks, params):
+    """the reference predicts the batch (filling fc->ref->tab_dmvr_mvf through set_dmvr_info), then
+    vvcb200_emit_store_refined_mv writes the same refined vectors into a fresh table; returns the number of differing units."""
+    pl = abi.host_planes(dst)
+    ra = abi.planes_array([abi.host_planes(r) for r in refs])
+    blocks = np.ascontiguousarray(blocks, abi.PB_DTYPE)
+    mv = np.zeros((len(blocks), 2, 2), np.int32)
+    return lib().vvcref_emit_store_refined_check(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks),
+                                                 C.byref(params), C.c_void_p(mv.ctypes.data)), mv

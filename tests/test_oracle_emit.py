@@ -77,3 +77,49 @@ def test_recon_emitter_writes_the_transform_blocks_and_intra_records(name):
     assert np.array_equal(lv, pic["ref"]["levels"])
     assert not _diff(ibs, pic["intra"]["blocks"], abi.IB_DTYPE.names)
     assert np.array_equal(first, pic["intra"]["ctu_first"])
+
+
+@pytest.mark.parametrize("seed,ctb,frac,ns", [(40, 6, 0.3, 1), (43, 5, 0.3, 3), (44, 7, 0.2, 2)])
+def test_filters_emitter_writes_the_per_unit_deblocking_state(seed, ctb, frac, ns):
+    """vvcb200_emit_filters_ctu over fc->tab.mvf / tb_pos / cb_pos / coded flags: the compact motion + partition records the
+    device derives boundary strengths from, and the CTB sides deblocking must not cross (slice limits, lfase 0)."""
+    w, h = 416, 240
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, intra_fraction=frac)
+    st = synth.deblock_state(pic)
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    slices = synth.slice_map(np.random.default_rng(seed), cw, ch, ns)
+    lfase = 1 if ns == 1 else 0
+    motion, part, edges = refapi.emit_deblock_units(st, w, h, ctb, slices, lfase)
+    assert not _diff(motion.reshape(-1), st["motion"].reshape(-1), abi.MOTION_DTYPE.names)
+    assert not _diff(part.reshape(-1), st["part"].reshape(-1), abi.PARTITION_DTYPE.names)
+    assert np.array_equal(edges, (synth.alf_edge_flags(slices, cw, ch, lfase) & 3).astype(np.uint8))
+
+
+@pytest.mark.parametrize("ns,lfase,tiles,lfate", [(1, 1, None, 1), (4, 0, None, 1), (3, 1, ((0, 2), (0, 1)), 0), (3, 0, ((0, 1, 3), (0, 2)), 0),
+                                                   (1, 1, ((0, 2), (0, 1)), 1)])
+def test_filters_emitter_writes_sao_alf_and_deblocking_parameters(ns, lfase, tiles, lfate):
+    """SAOParams / ALFParams / APS list / DBParams / LADF fields -> VVCB200SaoCtb / AlfCtb / AlfParams / offsets / DeblockParams,
+    with the SAO restore flags (vvc_filter.c:163-211) and the ALF edge flags (1266-1280) worked out from slice_idx, the tile
+    grid and the two loop-filter-across flags."""
+    w, h, ctb = 832, 480, 7
+    kw = dict(tile_cols=tiles[0], tile_rows=tiles[1], lfate=lfate) if tiles else {}
+    t = synth.loopfilter_ctbs(50 + ns, w, h, ctb_log2=ctb, n_slices=ns, lfase=lfase, **kw)
+    d = synth.deblock_picture(60, w, h, ctb_log2=ctb, ladf=True)
+    sao, alf, ap, off, edges, dp = refapi.emit_loopfilter_ctbs(t, w, h, d["ctb_offsets"], d["params"])
+    assert not _diff(sao, t["sao"], abi.SAO_DTYPE.names)
+    assert not _diff(alf, t["alf"], abi.ALF_CTB_DTYPE.names)
+    assert ap.tobytes() == t["alf_params"].tobytes()
+    assert np.array_equal(off, d["ctb_offsets"])
+    assert np.array_equal(edges, t["alf"]["edges"] & 3)
+    assert bytes(dp) == bytes(d["params"])
+
+
+def test_refined_vectors_go_back_into_the_dmvr_table():
+    """run_inter's other half: the vectors DMVR settled on (vvcb200_pic_inter's refined_mv) written into
+    fc->ref->tab_dmvr_mvf as set_dmvr_info (vvc_inter.c:749-761) does — same units, same MvField."""
+    pic = synth.inter_picture(9, 416, 240, tools=("bi", "dmvr", "bdof", "hpel"))
+    dst = [np.zeros_like(p) for p in pic["refs"][0]]
+    bad, mv = refapi.emit_store_refined_check(dst, pic["refs"], pic["blocks"], pic["params"])
+    dm = (pic["blocks"]["flags"] & abi.PB_DMVR) != 0
+    assert dm.sum() > 20 and np.any(mv[dm] != pic["blocks"]["mv"][dm])       # DMVR moved something
+    assert bad == 0
