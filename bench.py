@@ -232,6 +232,36 @@ def cpu_baseline(pic, budget_s=15.0, max_pics=30):
                       "(x86 asm not built: no nasm)" % (n, threads)}, planes
 
 
+def emit_host_ms(pic):
+    """host time of the descriptor emitter (ffmpeg_b200/emit, compiled against the reference's headers into
+    oracle/_ref/libvvcref.so) for this picture: the reference-side state the harness builds from `pic` in, the engine's
+    batches out.  One host thread, fresh arrays; the reference runs these stage bodies on all its threads, CTU by CTU."""
+    from ffmpeg_b200 import abi, synth
+    from oracle import refapi
+    if not refapi.available() or pic.get("ref") is None:
+        return None
+    w, h, it = pic["width"], pic["height"], pic["inter"]
+    b = it["blocks"]
+    plain = b[(b["flags"] & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_LUMA_ONLY | abi.PB_CHROMA_ONLY)) == 0]
+    cus = np.zeros(len(plain), synth.CU_DTYPE)
+    for k in ("x0", "y0", "w", "h", "pred_flag", "bcw_idx", "ref_idx", "mv"):
+        cus[k] = plain[k]
+    cus["flags"] = plain["flags"]
+    all_cus = np.concatenate([cus, it["cus"]]) if len(it["cus"]) else cus
+    out = {}
+    if len(all_cus):
+        refapi.emit_inter_cus(w, h, all_cus, it["sb_mv"], it["params"], order=True)
+        out["inter"] = round(refapi.emit_last_ms(), 3)
+    has_ciip = bool(pic["ref"]["cus"]["ciip_flag"].any())
+    refapi.emit_recon_picture(w, h, pic["ref"], pic["intra"]["params"], inter=it if has_ciip else None)
+    out["recon"] = round(refapi.emit_last_ms(), 3)
+    refapi.emit_loopfilter_ctbs(pic["lf"], w, h, pic["deblock"]["ctb_offsets"], pic["deblock"]["params"])
+    out["filters"] = round(refapi.emit_last_ms(), 3)
+    out["total"] = round(sum(out.values()), 3)
+    out["threads"] = 1
+    return out
+
+
 # ----------------------------------------------------------------------------------------------------------
 # workload tx1080p (BASELINE config 1): dequant + inverse transform batch only
 # ----------------------------------------------------------------------------------------------------------
@@ -651,6 +681,8 @@ def main():
            "e2e_frames_identical": bool(e2e_same)}
     if world == 1 and not args.no_cpu_baseline:
         out["cpu_baseline"], ref_planes = cpu_baseline(pic, budget_s=10.0 if args.workload != "8k" else 1.0)
+        if args.workload != "8k":
+            out["cpu_baseline"]["emit_host_ms"] = emit_host_ms(pic)
         ref_md5 = util.plane_md5(ref_planes)
         out["parity"] = {"md5_match": bool(ref_md5 == dev_md5 and ref_md5 == e2e_ok and e2e_same), "ref_md5": ref_md5,
                          "gpu_md5": dev_md5, "e2e_md5": e2e_ok,

@@ -54,4 +54,15 @@ typedef struct VVCRefTU {
     int32_t joint;
     int32_t tb[3];                      /* index into the VVCB200TransformBlock array, or -1 */
 } VVCRefTU;
+
+/* Host time spent inside the product's emitter (ffmpeg_b200/emit) during the last vvcref_emit_* call of this thread's
+ * process, in nanoseconds — the harness's own work of building the reference-side state is not counted (glue.c). */
+#include <time.h>
+extern int64_t vvcref_emit_ns;
+static inline int64_t vvcref_now_ns(void)
+{
+    struct timespec ts;
+    timespec_get(&ts, TIME_UTC);             /* C11; the build is -std=c11 */
+    return (int64_t)ts.tv_sec * 1000000000 + ts.tv_nsec;
+}
 #endif

@@ -426,7 +426,9 @@ VVCREF_EXPORT int vvcref_deblock_bs(int width, int height, int ctb_log2, const v
             const int x0 = rx << ctb_log2, y0 = ry << ctb_log2;
             ff_vvc_decode_neighbour(e->lc, x0, y0, rx, ry, ry * e->pps.ctb_width + rx);
             if (g_emit_filters) {
+                const int64_t t0 = vvcref_now_ns();
                 vvcb200_emit_filters_ctu(g_emit_filters, e->lc, rx, ry);
+                vvcref_emit_ns += vvcref_now_ns() - t0;
                 continue;
             }
             vvc_deblock_bs(e->lc, x0, y0, 1);
@@ -457,6 +459,7 @@ VVCREF_EXPORT int vvcref_emit_deblock_units(int width, int height, int ctb_log2,
     int ret;
 
     g_emit_filters = &out;
+    vvcref_emit_ns = 0;
     ret = vvcref_deblock_bs(width, height, ctb_log2, mvf, tb_pos_x0, tb_pos_y0, tb_width, tb_height, cb_pos_x, cb_pos_y, cb_width,
                             cb_height, tu_coded_flag, tu_joint, pcmf, msf, iaf, ref_poc, slice_idx, lfase, bs, len, len);
     g_emit_filters = NULL;
@@ -533,13 +536,21 @@ VVCREF_EXPORT int vvcref_emit_loopfilter_ctbs(int width, int height, int ctb_log
     for (int i = 0; i < 5; i++)
         e->sps.ladf_interval_lower_bound[i] = in_dp->ladf_interval_lower_bound[i];
 
+    vvcref_emit_ns = 0;
     for (int ry = 0; ry < (int)e->pps.ctb_height; ry++)
         for (int rx = 0; rx < (int)e->pps.ctb_width; rx++) {
+            int64_t t0;
             ff_vvc_decode_neighbour(e->lc, rx << ctb_log2, ry << ctb_log2, rx, ry, ry * e->pps.ctb_width + rx);
+            t0 = vvcref_now_ns();
             vvcb200_emit_filters_ctu(&out, e->lc, rx, ry);
+            vvcref_emit_ns += vvcref_now_ns() - t0;
         }
-    vvcb200_emit_alf_params(ap_out, &e->fc, &e->sc);
-    vvcb200_emit_deblock_params(dp_out, &e->fc);
+    {
+        const int64_t t0 = vvcref_now_ns();
+        vvcb200_emit_alf_params(ap_out, &e->fc, &e->sc);
+        vvcb200_emit_deblock_params(dp_out, &e->fc);
+        vvcref_emit_ns += vvcref_now_ns() - t0;
+    }
     free(aps); free(db); free(alf); free(sao);
     filter_env_free(e);
     return 0;

@@ -283,9 +283,11 @@ VVCREF_EXPORT int vvcref_inter_cus(const VVCRefPlanes *dst, const VVCRefPlanes *
         pu->mi.pred_flag   = d->pred_flag;
         pu->bdof_flag      = !!(d->flags & VVCB200_PB_BDOF);
         pu->dmvr_flag      = !!(d->flags & VVCB200_PB_DMVR);
+        cu->ciip_flag      = !!(d->flags & VVCB200_PB_CIIP);   /* predict_inter leaves such a unit to RECON; the emitter flags it */
         e->rpps.pps_weighted_bipred_flag = !!(d->flags & VVCB200_PB_WP);
         e->rsh.sh_lmcs_used_flag         = !!(d->flags & VVCB200_PB_LMCS);
         mvf.pred_flag   = d->pred_flag;
+        mvf.ciip_flag   = cu->ciip_flag;
         mvf.bcw_idx     = d->bcw_idx;
         mvf.hpel_if_idx = pu->mi.hpel_if_idx;
         for (int l = 0; l < 2; l++) {
@@ -329,9 +331,11 @@ VVCREF_EXPORT int vvcref_inter_cus(const VVCRefPlanes *dst, const VVCRefPlanes *
                 for (int x = d->x0 >> 2; x < (d->x0 + d->w) >> 2; x++)
                     e->fc.tab.mvf[y * min_pu_width + x] = mvf;
         }
-        if (g_emit)
+        if (g_emit) {
+            const int64_t t0 = vvcref_now_ns();
             vvcb200_emit_inter_cu(g_emit, lc);              /* the emitter in predict_inter's place */
-        else
+            vvcref_emit_ns += vvcref_now_ns() - t0;
+        } else
             predict_inter(lc);
     }
     ret = g_emit ? g_emit->error : 0;
@@ -358,10 +362,22 @@ VVCREF_EXPORT int vvcref_emit_inter_cus(int width, int height, const VVCRefInter
     VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
     int ret;
     g_emit = &batch;
+    vvcref_emit_ns = 0;
     ret = vvcref_inter_cus(&pl, &pl, 0, cus, n, sb_mv, p, NULL);
     g_emit = NULL;
-    if (!ret && order)
+    {   /* the per-unit timer calls are not the emitter's: take their own cost (measured here) off again */
+        int64_t t0 = vvcref_now_ns(), t1 = t0;
+        for (int i = 0; i < 2000; i++)
+            t1 = vvcref_now_ns();
+        vvcref_emit_ns -= (t1 - t0) * n / 2000;
+        if (vvcref_emit_ns < 0)
+            vvcref_emit_ns = 0;
+    }
+    if (!ret && order) {
+        const int64_t t0 = vvcref_now_ns();
         vvcb200_emit_order_blocks(&batch, p);
+        vvcref_emit_ns += vvcref_now_ns() - t0;
+    }
     if (!ret && (batch.n_blocks > cap_blocks || batch.n_prof > cap_prof))
         ret = -2;
     if (!ret) {

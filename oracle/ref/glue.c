@@ -131,3 +131,10 @@ __attribute__((constructor)) static void oracle_static_init(void)
 {
     memset(ff_vvc_default_scale_m, 16, sizeof(ff_vvc_default_scale_m));
 }
+
+#include "api_common.h"
+int64_t vvcref_emit_ns;
+VVCREF_EXPORT int64_t vvcref_emit_last_ns(void)
+{
+    return vvcref_emit_ns;
+}

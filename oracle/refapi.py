@@ -335,3 +335,10 @@ def emit_store_refined_check(dst, refs, blocks, params):
     mv = np.zeros((len(blocks), 2, 2), np.int32)
     return lib().vvcref_emit_store_refined_check(C.byref(pl), ra, len(refs), C.c_void_p(blocks.ctypes.data), len(blocks),
                                                  C.byref(params), C.c_void_p(mv.ctypes.data)), mv
+
+
+def emit_last_ms():
+    """Host milliseconds the last emit_* call spent inside the product's emitter (not in the harness around it)."""
+    f = lib().vvcref_emit_last_ns
+    f.restype = C.c_int64
+    return f() / 1e6

@@ -45,6 +45,27 @@ def test_full_picture_with_intra_cus_md5(seed, w, h, ctb, lmcs, frac):
         ctx.close()
 
 
+@pytest.mark.parametrize("seed,w,h,ctb,lmcs,ns,lfase", [(31, 416, 240, 7, False, 1, 1), (32, 832, 480, 6, True, 3, 0)])
+def test_picture_from_emitted_descriptors_md5(seed, w, h, ctb, lmcs, ns, lfase):
+    """the emitter (ffmpeg_b200/emit) turns the reference-side state of the picture — CTU / CodingUnit /
+    TransformUnit lists, MvField table, SAOParams / ALFParams / APS list — into the engine's batches; the engine run on THOSE
+    must produce what ff_vvc_predict_inter + ff_vvc_reconstruct + the loop filters produce on the same state."""
+    from oracle import refapi
+    if not refapi.available():
+        pytest.skip("oracle/_ref not built")
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=lmcs, n_slices=ns, lfase=lfase, intra_fraction=0.3)
+    want = pipeline.oracle_picture(pic)
+    ctx = lib.Context(0, w, h, dpb_size=3)
+    try:
+        ep = pipeline.EnginePicture(ctx, pipeline.emitted_picture(pic))
+        ep.upload_refs()
+        ep.run()
+        ctx.sync()
+        assert util.plane_md5(ep.out) == util.plane_md5(want)
+    finally:
+        ctx.close()
+
+
 def test_back_to_back_pictures_overlap_safely():
     """Six pictures submitted without a sync in between, alternating between two DPB slots and two host frames: uploads,
     kernels and downloads of neighbouring pictures overlap on the context's three streams and every frame is right."""
