@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256, VVC_ALF_LUMA_MIN_BLOCKS) alf_luma_kernel(
         }
     }
     __syncthreads();
-    alf_luma_filter_tile<false>(a, cp, g, tx0, ty0, S);
+    alf_luma_filter_tile<false>(a, cp, g, tx0, ty0, S, S.pix);
 }
 
 // chroma ALF (5x5) + CC-ALF; grid.z selects Cb / Cr
@@ -106,7 +106,7 @@ __global__ void __launch_bounds__(256, VVC_ALF_CHROMA_MIN_BLOCKS) alf_chroma_ker
     }
     const uint16_t *lp = a.src.p[0];
     const int ls = a.src.stride[0];
-    alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, s_pix,
+    alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, s_pix, S,
                            [&](int x, int y) { return src[(size_t)y * sstride + x]; },
                            [&](int x, int y) { return lp[(size_t)y * ls + x]; });
 }

@@ -128,13 +128,14 @@ struct AlfLumaShared {
     int wide;                                            // some coefficient of the tile does not fit int8 (never in a conforming stream)
 };
 
-// Everything after staging for one 32x32 luma tile at (tx0, ty0) of CTB `g` (record `cp`): S.pix holds the padded window,
+// Everything after staging for one 32x32 luma tile at (tx0, ty0) of CTB `g` (record `cp`): s_pix (row stride kStr, 32-bit
+// aligned) holds the padded window — sample (tx0 + c - kColOrg, ty0 + r - kHalo) at s_pix[r * kStr + c] — which is S.pix
+// after alf_prepare_buffer's clamping, or any window of the pre-ALF samples when the CTB has no edge to clamp at;
 // S.wide was cleared, and a __syncthreads() lies between those writes and this call.  256 threads.
-template <bool kTable>
+template <bool kTable, int kStr = kPadStr>
 __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVCB200AlfCtb &cp, const CtbGeom &g, int tx0,
-                                                     int ty0, AlfLumaShared &S)
+                                                     int ty0, AlfLumaShared &S, const uint16_t *s_pix)
 {
-    uint16_t *const s_pix = S.pix;
     uint16_t (*const s_grad)[4] = S.grad;
     int16_t (*const s_coef)[12] = S.coef;
     int16_t (*const s_clip)[12] = S.clip;
@@ -157,8 +158,8 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
             rd = rc;
         else if (ygrad == vb + 2)
             ra = rb;
-        const uint16_t *s0 = s_pix + ra * kPadStr, *s1 = s_pix + rb * kPadStr;
-        const uint16_t *s2 = s_pix + rc * kPadStr, *s3 = s_pix + rd * kPadStr;
+        const uint16_t *s0 = s_pix + ra * kStr, *s1 = s_pix + rb * kStr;
+        const uint16_t *s2 = s_pix + rc * kStr, *s3 = s_pix + rd * kStr;
         const int val0 = s1[c0] << 1, val1 = s2[c0 + 1] << 1;
         s_grad[i][0] = (uint16_t)(abs(val0 - s0[c0] - s2[c0]) + abs(val1 - s1[c0 + 1] - s3[c0 + 1]));
         s_grad[i][1] = (uint16_t)(abs(val0 - s1[c0 - 1] - s1[c0 + 1]) + abs(val1 - s2[c0] - s2[c0 + 2]));
@@ -245,10 +246,10 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
             int o1, o2, o3;
             bool near_vb;
             vb_rows(ty_ctb + row, vb, 3, o1, o2, o3, near_vb);
-            const uint16_t *p0 = s_pix + (row + kHalo) * kPadStr + xg * 4 + kColOrg;
-            const uint16_t *p1 = p0 + o1 * kPadStr, *p2 = p0 - o1 * kPadStr;
-            const uint16_t *p3 = p0 + o2 * kPadStr, *p4 = p0 - o2 * kPadStr;
-            const uint16_t *p5 = p0 + o3 * kPadStr, *p6 = p0 - o3 * kPadStr;
+            const uint16_t *p0 = s_pix + (row + kHalo) * kStr + xg * 4 + kColOrg;
+            const uint16_t *p1 = p0 + o1 * kStr, *p2 = p0 - o1 * kStr;
+            const uint16_t *p3 = p0 + o2 * kStr, *p4 = p0 - o2 * kStr;
+            const uint16_t *p5 = p0 + o3 * kStr, *p6 = p0 - o3 * kStr;
             uint16_t out[4];
             if (!wide) {
                 // Two samples per 32-bit word through the 16x2 integer pipe (VIADD.16x2 / VIADDMNMX.S16x2 on sm_100a), the
@@ -318,14 +319,15 @@ __device__ __forceinline__ void alf_luma_filter_tile(const AlfArgs &a, const VVC
 }
 
 // One chroma tile of side T (<= 32, never straddling a chroma CTB) at (tx0, ty0) of component c: 5x5 ALF from the padded
-// (T + 4)^2 window in s_pix (staged by the caller when cp.ctb_flag[c] is set, __syncthreads() in between) and CC-ALF
+// (T + 4)^2 window in s_pix, row stride S (staged by the caller when cp.ctb_flag[c] is set, __syncthreads() in between;
+// or a window of the pre-ALF samples when the CTB has no edge to clamp at) and CC-ALF
 // (alf_filter_cc, vvc_filter_template.c:223-263).  cur(x, y): the pre-ALF sample of this plane; luma(x, y): the pre-ALF
 // luma sample at a plane position (already padded for the luma CTB by this function).  256 threads.
 template <class CurAt, class LumaAt>
 __device__ __forceinline__ void alf_chroma_filter_tile(const AlfArgs &a, const VVCB200AlfCtb &cp, const CtbGeom &g, int c,
-                                                       int T, int tx0, int ty0, const uint16_t *s_pix, CurAt cur, LumaAt luma)
+                                                       int T, int tx0, int ty0, const uint16_t *s_pix, int S, CurAt cur,
+                                                       LumaAt luma)
 {
-    const int S = T + 4;
     const int W = a.src.w[c], H = a.src.h[c];
     const int l2 = a.ctb_log2 - 1;
     uint16_t *dst = a.dst.p[c];

@@ -90,6 +90,27 @@ __device__ __forceinline__ int sao_sample_win(const PlaneWin &src, const VVCB200
     return clip_pixel(s + ov[idx], bd);
 }
 
+// The 8 samples of a chunk one by one, for the few chunks that touch a picture border or a no-filter side.  Deliberately a
+// real call with a rolled loop: inlined eight-fold into both call sites this rule set was two thirds of the kernel's code,
+// and the instruction cache paid for it on every other chunk.
+__device__ __noinline__ uint4 sao_chunk_slow(const uint16_t *wp, int wstride, int wx0, int wy0, int ww, int wh,
+                                             const VVCB200SaoCtb *pp, int c, int x, int y, int cx0, int cy0, int cw, int ch,
+                                             int W, int H, int bd)
+{
+    const PlaneWin src = { wp, wstride, wx0, wy0, ww, wh };
+    const VVCB200SaoCtb p = *pp;
+    unsigned long long lo = 0, hi = 0;
+#pragma unroll 1
+    for (int j = 0; j < 8; j++) {
+        const unsigned long long v = x + j < W ? (unsigned long long)sao_sample_win(src, p, c, x + j, y, cx0, cy0, cw, ch, W, H, bd) : 0;
+        if (j < 4)
+            lo |= v << (16 * j);
+        else
+            hi |= v << (16 * (j - 4));
+    }
+    return make_uint4((uint32_t)lo, (uint32_t)(lo >> 32), (uint32_t)hi, (uint32_t)(hi >> 32));
+}
+
 // Offsets looked up for both halves of a packed index word (each half 0..4) with two PRMTs: byte i of (lo, hi) holds entry
 // i, selector nibbles (k, k | 8) pick the byte and replicate its sign, which sign-extends it into the 16-bit half.
 __device__ __forceinline__ uint32_t lut5_s16x2(uint32_t idx2, uint32_t lo, uint32_t hi)
@@ -125,16 +146,8 @@ __device__ __forceinline__ uint4 sao_chunk(const SaoAlfArgs &a, const PlaneWin &
     }
     const uint32_t cw4[4] = { vc.x, vc.y, vc.z, vc.w };
     uint32_t out[4];
-    if (slow) {
-        const VVCB200SaoCtb p = *pp;
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            const int v0 = x + 2 * j < W ? sao_sample_win(src, p, c, x + 2 * j, y, cx0, cy0, cw, ch, W, H, bd) : 0;
-            const int v1 = x + 2 * j + 1 < W ? sao_sample_win(src, p, c, x + 2 * j + 1, y, cx0, cy0, cw, ch, W, H, bd) : 0;
-            out[j] = (uint32_t)v0 | ((uint32_t)v1 << 16);
-        }
-        return make_uint4(out[0], out[1], out[2], out[3]);
-    }
+    if (slow)
+        return sao_chunk_slow(src.p, src.stride, src.x0, src.y0, src.w, src.h, pp, c, x, y, cx0, cy0, cw, ch, W, H, bd);
     const int16_t *ov = pp->offset_val[c];
     const uint32_t pmax2 = (uint32_t)((1 << bd) - 1) * 0x10001u;
     if (type == VVCB200_SAO_BAND) {
@@ -202,8 +215,11 @@ __device__ __forceinline__ uint4 sao_chunk(const SaoAlfArgs &a, const PlaneWin &
     return make_uint4(out[0], out[1], out[2], out[3]);
 }
 
+#ifndef VVC_SAOALF_MINB
+#define VVC_SAOALF_MINB 4
+#endif
 template <bool kTable>
-__global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
+__global__ void __launch_bounds__(256, VVC_SAOALF_MINB) sao_alf_kernel(const SaoAlfArgs A)
 {
     __shared__ __align__(16) uint16_t s_sao_y[kFYSR * kFYS];              // SAO'd luma, rows Y0-3 .., columns X0-8 ..
     __shared__ __align__(16) uint16_t s_sao_c[2][kFCSR * kFCS];           // SAO'd chroma, rows y0c-2 .., columns x0c-8 ..
@@ -291,15 +307,22 @@ __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
         const CtbGeom g = ctb_geom(a, 0, tx0, ty0, cp.edges);
         if (t == 0)
             S.wide = 0;
+        if (!g.edges) {
+            // a CTB with no side to clamp at (four in five of a 4K picture's): alf_prepare_buffer's window IS the SAO
+            // window, the filter reads it where it lies
+            alf_luma_filter_tile<kTable, kFYS>(a, cp, g, tx0, ty0, S,
+                                               s_sao_y + (ty0 - kHalo - (Y0 - 3)) * kFYS + (tx0 - kColOrg - (X0 - 8)));
+            __syncthreads();
+            continue;
+        }
         for (int r = t >> 5; r < kPad; r += 8)            // a warp per staged row, lanes along it
             for (int col = t & 31; col < kPad; col += 32) {
                 int x = tx0 + col - kHalo, y = ty0 + r - kHalo;
-                if (g.edges)
-                    pad_coords(g, x, y);
+                pad_coords(g, x, y);
                 S.pix[r * kPadStr + col + kColOrg - kHalo] = luma_at(x, y);
             }
         __syncthreads();
-        alf_luma_filter_tile<kTable>(a, cp, g, tx0, ty0, S);
+        alf_luma_filter_tile<kTable>(a, cp, g, tx0, ty0, S, S.pix);
         __syncthreads();
     }
 
@@ -317,17 +340,21 @@ __global__ void __launch_bounds__(256, 4) sao_alf_kernel(const SaoAlfArgs A)
             const VVCB200AlfCtb cp = a.ctbs ? a.ctbs[(ty0 >> l2) * a.ctb_width + (tx0 >> l2)] : off;
             const CtbGeom g = ctb_geom(a, c, tx0, ty0, cp.edges);
             const int Sd = T + 4;
+            if (!g.edges) {                               // as for luma: nothing to clamp, the SAO window is the padded window
+                alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, sc + (ty0 - 2 - (yc0 - 2)) * kFCS + (tx0 - 2 - (xc0 - 8)), kFCS,
+                                       cur_at, luma_at);
+                continue;
+            }
             if (cp.ctb_flag[c]) {
                 for (int r = t >> 5; r < Sd; r += 8)
                     for (int col = t & 31; col < Sd; col += 32) {
                         int x = tx0 + col - 2, y = ty0 + r - 2;
-                        if (g.edges)
-                            pad_coords(g, x, y);
+                        pad_coords(g, x, y);
                         S.pix[r * Sd + col] = cur_at(x, y);
                     }
             }
             __syncthreads();
-            alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, S.pix, cur_at, luma_at);
+            alf_chroma_filter_tile(a, cp, g, c, T, tx0, ty0, S.pix, Sd, cur_at, luma_at);
             __syncthreads();
         }
     }

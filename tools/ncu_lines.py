@@ -1,54 +1,72 @@
 #!/usr/bin/env python
-"""Development tool: executed warp instructions and stall samples of one kernel per source line, by joining the SASS
-page of an .ncu-rep with the line table of the kernel's cubin (for reports captured without source import).
-usage: python tools/ncu_lines.py rep.ncu-rep kernel_regex file.cubin [n_lines]"""
+"""Warp instructions executed per CUDA source line of one kernel: the SASS page of an .ncu-rep (first captured launch)
+joined, instruction by instruction, with the line table of the same kernel in the built library (nvdisasm -g).
+usage: python tools/ncu_lines.py rep.ncu-rep kernel_regex cubin mangled_substring [n]
+  e.g. cuobjdump -xelf all ffmpeg_b200/libvvcb200.so  ->  saoalf.sm_100a.cubin"""
 import collections
 import csv
-import io
 import re
 import subprocess
 import sys
 
 
-def main():
-    rep, kernel, cubin = sys.argv[1:4]
-    top = int(sys.argv[4]) if len(sys.argv) > 4 else 40
-    dis = subprocess.run(["nvdisasm", "-g", "-c", cubin], capture_output=True, text=True).stdout
-    line_of, cur, fn, want = {}, None, None, None
-    for l in dis.splitlines():
-        m = re.search(r'\.text\.(\S+)', l) if l.startswith("//---") or ".section" in l else None
-        if m:
-            fn = m.group(1)
+def sass_rows(rep, kernel):
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel,
+                          "--print-source", "sass"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    first = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
+    hdr = rows[first]
+    col = {h: k for k, h in enumerate(hdr)}
+    data = []
+    for r in rows[first + 1:]:
+        if r and r[0] == "Address":
+            break
+        if len(r) == len(hdr):
+            data.append((r[col["Source"]].strip(), float(r[col["Instructions Executed"]] or 0), float(r[col["# Samples"]] or 0)))
+    return data
+
+
+def line_table(cubin, mangled):
+    out = subprocess.run(["nvdisasm", "-g", cubin], capture_output=True, text=True).stdout.splitlines()
+    lines, cur, on = [], None, False
+    for l in out:
+        if l.startswith(".text."):
+            on = mangled in l
+            continue
+        if not on:
+            continue
         m = re.search(r'//## File "([^"]+)", line (\d+)', l)
         if m:
             cur = (m.group(1).split("/")[-1], int(m.group(2)))
-        m = re.match(r'\s+/\*([0-9a-f]{4,6})\*/', l)
-        if m and fn and re.search(kernel, fn):
-            line_of[int(m.group(1), 16)] = cur
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel, "--print-source", "sass"],
-                         capture_output=True, text=True).stdout
-    rows = list(csv.reader(io.StringIO(out)))
-    hdr = next(r for r in rows if r and r[0] == "Address")
-    data = rows[rows.index(hdr) + 1:]
-    col = {h: i for i, h in enumerate(hdr)}
+            continue
+        if re.match(r"\s+/\*[0-9a-f]{4,}\*/\s+\S", l) and ".byte" not in l and ".dword" not in l:
+            lines.append(cur)
+    return lines
 
-    def f(r, n):
-        try:
-            return float(r[col[n]])
-        except (ValueError, KeyError, IndexError):
-            return 0.0
-    base = int(data[0][col["Address"]], 16)
-    acc = collections.defaultdict(lambda: [0.0, 0.0, 0])
-    for r in data:
-        k = line_of.get(int(r[col["Address"]], 16) - base)
-        acc[k][0] += f(r, "Instructions Executed")
-        acc[k][1] += f(r, "# Samples")
-        acc[k][2] += 1
-    tot = sum(v[0] for v in acc.values()) or 1
-    tots = sum(v[1] for v in acc.values()) or 1
-    print("line, executed warp instructions (share), stall samples (share), SASS instructions")
-    for k, v in sorted(acc.items(), key=lambda kv: -kv[1][0])[:top]:
-        print("%-22s %12.0f (%4.1f%%) %7.0f (%4.1f%%) %5d" % (k, v[0], 100 * v[0] / tot, v[1], 100 * v[1] / tots, v[2]))
+
+def main():
+    rep, kernel, cubin, mangled = sys.argv[1:5]
+    n = int(sys.argv[5]) if len(sys.argv) > 5 else 40
+    data, lt = sass_rows(rep, kernel), line_table(cubin, mangled)
+    print("%d SASS rows in the report, %d in the library" % (len(data), len(lt)))
+    if len(data) != len(lt):
+        print("instruction counts differ: the library is not the profiled build")
+        return
+    ex, smp = collections.Counter(), collections.Counter()
+    for (src, e, s), ln in zip(data, lt):
+        ex[ln] += e
+        smp[ln] += s
+    tot = sum(ex.values())
+    src_cache = {}
+    for ln, e in ex.most_common(n):
+        f = ln[0] if ln else "?"
+        if f not in src_cache:
+            try:
+                src_cache[f] = open("ffmpeg_b200/csrc/" + f).read().splitlines()
+            except OSError:
+                src_cache[f] = []
+        text = src_cache[f][ln[1] - 1].strip() if ln and ln[1] - 1 < len(src_cache[f]) else ""
+        print("%5.1f%% %10.0f  smp %5.0f  %s:%d  %s" % (100 * e / tot, e, smp[ln], f, ln[1] if ln else 0, text[:100]))
 
 
 if __name__ == "__main__":

@@ -37,7 +37,7 @@ def main():
     ap.add_argument("--intra-fraction", type=float, default=0.1)
     ap.add_argument("--seed", type=int, default=2026)
     ap.add_argument("--lib", default=None, help="experimental library built by tools/build_variant.py")
-    ap.add_argument("--only", default=None, help="inter | residual | intra")
+    ap.add_argument("--only", default=None, help="inter | residual | intra | filters")
     args = ap.parse_args()
     if args.lib:
         lib.SO = os.path.abspath(args.lib)
@@ -76,6 +76,27 @@ def main():
         ms = timed(torch, lambda: lib.inter_batch(cur_p, refs_p, d, len(sub), p, lmcs_fwd_lut=fwd, prof=prof))
         area = int((sub["w"].astype(np.int64) * sub["h"]).sum())
         print("inter %-14s %7d records %9d luma-samples  %.4f ms  (%.2f ns/record)" % (name, len(sub), area, ms, 1e6 * ms / len(sub)))
+
+    if args.only in (None, "filters"):
+        db, lf = pic["deblock"], pic["lf"]
+        src = util.to_device_planes(bench.smooth_source(pic) if hasattr(bench, "smooth_source") else it["refs"][0], torch)
+        src_p = lib.device_planes(src)
+        edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+        d_edge, d_qp, d_off = torch.from_numpy(edge).cuda(), torch.from_numpy(db["qp"]).cuda(), torch.from_numpy(db["ctb_offsets"]).cuda()
+        tabs = lib.deblock_tables(d_edge, d_qp, d_off, db["stride4"])
+        inv = dev(pic["lmcs"][1]) if pic.get("lmcs") is not None else None
+        ms = timed(torch, lambda: lib.deblock_lmcs_picture(cur_p, src_p, tabs, db["params"], inv))
+        print("deblock + inverse LMCS (tile pass)  %.4f ms" % ms)
+        sao, alf, alfp = dev(lf["sao"]), dev(lf["alf"]), dev(lf["alf_params"])
+        table = torch.zeros(lib.sao_alf_scratch_bytes(), dtype=torch.uint8, device="cuda")
+        ms = timed(torch, lambda: lib.sao_alf_picture(cur_p, src_p, sao, alf, alfp, pic["ctb_log2"], scratch=table))
+        print("SAO + ALF (one pass, table)         %.4f ms" % ms)
+        ms = timed(torch, lambda: lib.sao_alf_picture(cur_p, src_p, sao, alf, alfp, pic["ctb_log2"], scratch=None))
+        print("SAO + ALF (one pass, no table)      %.4f ms" % ms)
+        ms = timed(torch, lambda: lib.sao_alf_picture(cur_p, src_p, sao, None, None, pic["ctb_log2"]))
+        print("SAO alone (one pass)                %.4f ms" % ms)
+        if args.only == "filters":
+            return
 
     res = [torch.zeros_like(t) for t in cur]
     res_p = lib.device_planes(res)
