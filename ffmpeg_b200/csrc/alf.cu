@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(256, VVC_ALF_LUMA_MIN_BLOCKS) alf_luma_kernel(
 // chroma ALF (5x5) + CC-ALF; grid.z selects Cb / Cr
 __global__ void __launch_bounds__(256, VVC_ALF_CHROMA_MIN_BLOCKS) alf_chroma_kernel(const AlfArgs a)
 {
-    __shared__ uint16_t s_pix[(kTile + 4) * (kTile + 4)];
+    __shared__ __align__(16) uint16_t s_pix[(kTile + 4) * (kTile + 4)];
     const int T = min(kTile, 1 << (a.ctb_log2 - 1));      // a tile never straddles a chroma CTB
     const int S = T + 4;
     const int c = 1 + blockIdx.z;
@@ -136,6 +136,11 @@ extern "C" int vvcb200_alf_picture(const VVCB200Planes *dst, const VVCB200Planes
         set_error("vvcb200_alf_picture: luma planes must be 8-byte aligned with strides that are multiples of 8 bytes");
         return VVCB200_ERR_ARG;
     }
+    for (int c = 1; c < 3; c++)
+        if ((a.dst.stride[c] & 1) || ((uintptr_t)a.dst.p[c] & 3) || (a.dst.w[c] & 1)) {
+            set_error("vvcb200_alf_picture: chroma planes must be 4-byte aligned with even strides and widths (sample pairs)");
+            return VVCB200_ERR_ARG;
+        }
     // luma and chroma write different planes of dst and only read src: two independent grids, side by side
     const cudaStream_t main_stream = (cudaStream_t)stream;
     ForkStreams *f = fork_streams(main_stream);

@@ -338,6 +338,7 @@ __device__ __forceinline__ void alf_chroma_filter_tile(const AlfArgs &a, const V
     const bool do_cc = cc && a.params->cc_enabled[c - 1];
     const int ty_ctb = ty0 - g.y0;
     int f[6], cl[6];
+    bool wide = false;                                   // a coefficient outside int8: never in a conforming stream
     if (do_alf) {
         const int alt = min((int)cp.alt_idx[c - 1], 7);
 #pragma unroll
@@ -345,6 +346,7 @@ __device__ __forceinline__ void alf_chroma_filter_tile(const AlfArgs &a, const V
             const int ci = a.params->chroma_clip_idx[alt][j];
             f[j] = a.params->chroma_coeff[alt][j];
             cl[j] = 1 << (a.bd - (ci == 0 ? 0 : ci == 1 ? 3 : ci == 2 ? 5 : 7));
+            wide = wide || f[j] < -128 || f[j] > 127;
         }
     }
     int fc[7];
@@ -357,54 +359,92 @@ __device__ __forceinline__ void alf_chroma_filter_tile(const AlfArgs &a, const V
     }
     const int vb = (1 << l2) - 2;                        // ALF_VB_POS_ABOVE_CHROMA
     const int vb_luma = (1 << a.ctb_log2) - 4;
-    const int lt = 31 - __clz(T);                        // T is 16 or 32
-    for (int i = t; i < T * T; i += 256) {
-        const int row = i >> lt, col = i & (T - 1);
+    const int half = T >> 1, lh = 31 - __clz(half);      // T is 16 or 32; a thread owns two horizontally adjacent samples
+    const int pmax = (1 << a.bd) - 1;
+    for (int i = t; i < T * half; i += 256) {
+        const int row = i >> lh, col = (i & (half - 1)) * 2;
         const int x = tx0 + col, y = ty0 + row;
-        if (x >= W || y >= H)
+        if (x >= W || y >= H)                            // (plane widths are even: a pair is inside or outside as one)
             continue;
-        int v;
+        int v0, v1;
         if (do_alf) {
             int o1, o2, o3;
             bool near_vb;
             vb_rows(ty_ctb + row, vb, 1, o1, o2, o3, near_vb);
             const uint16_t *p0 = s_pix + (row + 2) * S + col + 2;
             const uint16_t *p1 = p0 + o1 * S, *p2 = p0 - o1 * S, *p3 = p0 + o2 * S, *p4 = p0 - o2 * S;
-            const int curr = p0[0];
-            int sum = 0;
-            sum += f[0] * alf_clip2(curr, p3[0],  p4[0],  cl[0]);
-            sum += f[1] * alf_clip2(curr, p1[1],  p2[-1], cl[1]);
-            sum += f[2] * alf_clip2(curr, p1[0],  p2[0],  cl[2]);
-            sum += f[3] * alf_clip2(curr, p1[-1], p2[1],  cl[3]);
-            sum += f[4] * alf_clip2(curr, p0[2],  p0[-2], cl[4]);
-            sum += f[5] * alf_clip2(curr, p0[1],  p0[-1], cl[5]);
-            sum = near_vb ? (sum + 512) >> 10 : (sum + 64) >> 7;
-            v = clip_pixel(sum + curr, a.bd);
+            int sum0 = 0, sum1 = 0;
+            const int c0 = p0[0], c1 = p0[1];
+            if (!wide) {
+                // the pair through the 16x2 integer pipe, as in the luma filter: differences, clips and their sums stay in int16
+                auto w = [](const uint16_t *p, int k) { return reinterpret_cast<const uint32_t *>(p)[k]; };
+                auto pr = [&](const uint16_t *p, int s0) {
+                    return (s0 & 1) ? __funnelshift_r(w(p, (s0 - 1) >> 1), w(p, (s0 + 1) >> 1), 16) : w(p, s0 >> 1);
+                };
+                const uint32_t cw = w(p0, 0);
+                auto tap = [&](int k, const uint16_t *pa, int da, const uint16_t *pb, int db) {
+                    const uint32_t c2 = (uint32_t)cl[k] * 0x10001u, n2 = __vneg2(c2);
+                    const uint32_t tA = __vadd2(__vmaxs2(__vmins2(__vsub2(pr(pa, da), cw), c2), n2),
+                                                __vmaxs2(__vmins2(__vsub2(pr(pb, db), cw), c2), n2));
+                    const int flo = f[k] & 0xff;
+                    sum0 = __dp2a_lo((int)tA, flo, sum0);
+                    sum1 = __dp2a_lo((int)tA, flo << 8, sum1);
+                };
+                tap(0, p3, 0, p4, 0);
+                tap(1, p1, 1, p2, -1);
+                tap(2, p1, 0, p2, 0);
+                tap(3, p1, -1, p2, 1);
+                tap(4, p0, 2, p0, -2);
+                tap(5, p0, 1, p0, -1);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 2; j++) {
+                    const int curr = p0[j];
+                    int sum = 0;
+                    sum += f[0] * alf_clip2(curr, p3[j],     p4[j],     cl[0]);
+                    sum += f[1] * alf_clip2(curr, p1[j + 1], p2[j - 1], cl[1]);
+                    sum += f[2] * alf_clip2(curr, p1[j],     p2[j],     cl[2]);
+                    sum += f[3] * alf_clip2(curr, p1[j - 1], p2[j + 1], cl[3]);
+                    sum += f[4] * alf_clip2(curr, p0[j + 2], p0[j - 2], cl[4]);
+                    sum += f[5] * alf_clip2(curr, p0[j + 1], p0[j - 1], cl[5]);
+                    if (j == 0) sum0 = sum; else sum1 = sum;
+                }
+            }
+            v0 = min(max((near_vb ? (sum0 + 512) >> 10 : (sum0 + 64) >> 7) + c0, 0), pmax);
+            v1 = min(max((near_vb ? (sum1 + 512) >> 10 : (sum1 + 64) >> 7) + c1, 0), pmax);
         } else {
-            v = cur(x, y);
+            v0 = cur(x, y);
+            v1 = cur(x + 1, y);
         }
         if (do_cc) {
-            // 4:2:0: luma position (2x, 2y)
-            const int lx = x * 2, ly = y * 2;
+            // 4:2:0: chroma (x, y) sits at luma (2x, 2y); rows by the virtual-boundary rule, then alf_prepare_buffer's clamp —
+            // separable, and the centre column / row is always inside the CTB
+            const int ly = y * 2;
             const int pos = (ty_ctb + row) * 2;
             int r0 = ly - 1, r2 = ly + 1, r3 = ly + 2;
             if (pos == vb_luma - 2 || pos == vb_luma + 1)
                 r3 = r2;
             else if (pos == vb_luma - 1 || pos == vb_luma)
                 r3 = r2 = r0 = ly;
-            auto at = [&](int px, int py) {
-                if (gl.edges)                             // interior CTB: no coordinate needs clamping
-                    pad_coords(gl, px, py);
-                return (int)luma(px, py);
-            };
-            const int cu = at(lx, ly);
-            int sum = fc[0] * (at(lx, r0) - cu) + fc[1] * (at(lx - 1, ly) - cu) + fc[2] * (at(lx + 1, ly) - cu) +
-                      fc[3] * (at(lx - 1, r2) - cu) + fc[4] * (at(lx, r2) - cu) + fc[5] * (at(lx + 1, r2) - cu) +
-                      fc[6] * (at(lx, r3) - cu);
-            sum = clip3((sum + 64) >> 7, -(1 << (a.bd - 1)), (1 << (a.bd - 1)) - 1);
-            v = clip_pixel(v + sum, a.bd);
+            int xs[5] = { 2 * x - 1, 2 * x, 2 * x + 1, 2 * x + 2, 2 * x + 3 };
+            if (gl.edges) {
+                pad_coords(gl, xs[0], r0);                // (xs[1..3] lie between two samples of the CTB: never clamped)
+                pad_coords(gl, xs[2], r2);
+                pad_coords(gl, xs[4], r3);
+            }
+            const int half_range = 1 << (a.bd - 1);
+#pragma unroll
+            for (int j = 0; j < 2; j++) {
+                const int xm = xs[2 * j], xc = xs[2 * j + 1], xp = xs[2 * j + 2];
+                const int cu = luma(xc, ly);
+                int sum = fc[0] * (luma(xc, r0) - cu) + fc[1] * (luma(xm, ly) - cu) + fc[2] * (luma(xp, ly) - cu) +
+                          fc[3] * (luma(xm, r2) - cu) + fc[4] * (luma(xc, r2) - cu) + fc[5] * (luma(xp, r2) - cu) +
+                          fc[6] * (luma(xc, r3) - cu);
+                sum = clip3((sum + 64) >> 7, -half_range, half_range - 1);
+                if (j == 0) v0 = min(max(v0 + sum, 0), pmax); else v1 = min(max(v1 + sum, 0), pmax);
+            }
         }
-        dst[(size_t)y * dstride + x] = (uint16_t)v;
+        *reinterpret_cast<uint32_t *>(dst + (size_t)y * dstride + x) = (uint32_t)v0 | ((uint32_t)v1 << 16);
     }
 }
 

@@ -5,14 +5,17 @@ usage: python tools/ncu_lines.py rep.ncu-rep kernel_regex cubin mangled_substrin
   e.g. cuobjdump -xelf all ffmpeg_b200/libvvcb200.so  ->  saoalf.sm_100a.cubin"""
 import collections
 import csv
+import os
 import re
 import subprocess
 import sys
 
 
 def sass_rows(rep, kernel):
+    skip = os.environ.get("NCU_SKIP")              # n-th matching launch instead of the first
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--kernel-name", "regex:" + kernel,
-                          "--print-source", "sass"], capture_output=True, text=True).stdout
+                          "--print-source", "sass"] + (["--launch-skip", skip, "--launch-count", "1"] if skip else []),
+                         capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     first = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[first]

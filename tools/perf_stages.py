@@ -37,8 +37,12 @@ def main():
     ap.add_argument("--intra-fraction", type=float, default=0.1)
     ap.add_argument("--seed", type=int, default=2026)
     ap.add_argument("--lib", default=None, help="experimental library built by tools/build_variant.py")
+    ap.add_argument("--reps", type=int, default=20)
     ap.add_argument("--only", default=None, help="inter | residual | intra | filters")
     args = ap.parse_args()
+    global timed
+    _timed = timed
+    timed = lambda torch, fn, reps=None: _timed(torch, fn, args.reps)
     if args.lib:
         lib.SO = os.path.abspath(args.lib)
     width, height = bench.WORKLOADS[args.workload]
