@@ -490,7 +490,9 @@ __device__ __forceinline__ void prof_block(const InterArgs &a, const VVCB200Pred
 
 // One component of one block by one lane group (both lists + weighting + store).  WC: the block's width in this
 // component, fixed by the width class of the launch.
-template <int TAPS, int WC>
+// kFancyX false: the instantiation for records that use none of DMVR / BDOF / PROF / GPM — two thirds of the kernel's code
+// is those tools, and the plain records (most of a picture) run a quarter faster without it in the instruction cache.
+template <int TAPS, int WC, bool kFancyX>
 __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB200InterParams &p, const VVCB200PredBlock &b,
                                                   bool active, int c, int li, int gs, uint16_t *win, int ws,
                                                   int16_t *tmp, int ts, const int (&mv)[2][2], bool dmvr, bool bdof,
@@ -501,7 +503,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
     const int w = WC, h = max(b.h >> hs, 1);
     const int x0 = b.x0 >> hs, y0 = b.y0 >> hs;
     const int log2w = 31 - __clz(w);
-    const bool gpm = b.flags & VVCB200_PB_GPM;
+    const bool gpm = kFancyX && (b.flags & VVCB200_PB_GPM);
     const int set = (c || gpm) ? 0 : (b.flags & VVCB200_PB_AFFINE) ? 2 : (b.flags & VVCB200_PB_HPEL_IF) ? 1 : 0;
     int v0[8], v1[8];
     Window fw[2];
@@ -526,7 +528,7 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
         else
             interpolate<TAPS>(v1, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
                               win, ws, tmp, ts);
-        if (TAPS == 8 && a.prof) {
+        if (TAPS == 8 && kFancyX && a.prof) {
             const bool go = use && w == 4 && h == 4 && (b.flags & (l ? VVCB200_PB_PROF1 : VVCB200_PB_PROF0));
             if (__any_sync(0xffffffffu, go)) {
                 if (l == 0)
@@ -536,9 +538,9 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
             }
         }
     }
-    if (TAPS == 8 && !a.to_tmp14 && __any_sync(0xffffffffu, active && bdof))
+    if (TAPS == 8 && kFancyX && !a.to_tmp14 && __any_sync(0xffffffffu, active && bdof))
         bdof_block(a, p, b, active && bdof, li, gs, bdof_buf, bdof_vxy, v0, v1, mv, fw, lut);
-    if (!active || (TAPS == 8 && bdof && !a.to_tmp14))
+    if (!active || (TAPS == 8 && kFancyX && bdof && !a.to_tmp14))
         return;
 
     // ---- combine (weights are uniform inside a lane group)
@@ -637,29 +639,42 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
 // One launch per width class (kCls 0 / 1 / 2: blocks of width 16 / 8 / 4, a.first .. a.last): widths, lane groups and
 // staging strides are compile-time constants, the width-4 kernel carries no DMVR / BDOF code (they need 8x8) and the
 // others no PROF code (4x4 sub-blocks only) — the kernel is bound by instruction issue and fetch.
-template <int kCls>
+// kPart: 0 every record; 1 only the warps none of whose records uses DMVR / BDOF / PROF / GPM (the instantiation carries
+// no code for them); 2 only the other warps.  Parts 1 and 2 are launched over the same range and between them do what
+// part 0 does: no contract on the record order is needed, a sorted batch just makes whole CTAs leave at once.
+constexpr int kFancyFlags = VVCB200_PB_DMVR | VVCB200_PB_BDOF | VVCB200_PB_GPM | VVCB200_PB_PROF0 | VVCB200_PB_PROF1;
+template <int kCls, int kPart>
 __global__ void __launch_bounds__(kInterWarps * 32, VVC_INTER_MIN_BLOCKS)
 inter_kernel(const InterArgs a, const VVCB200InterParams p)
 {
+    constexpr bool kFancyX = kPart != 1;
     __shared__ __align__(16) uint16_t s_buf[kInterWarps][kBufElems];
     __shared__ int s_mv[kInterWarps][4][4];             // refined vectors of the warp's blocks, luma phase -> chroma phase
     __shared__ int8_t s_vxy[kInterWarps][2][32];        // BDOF (vx, vy) per 4x4 of the warp's (up to two) blocks
     // the forward LMCS LUT of the slice in shared memory: every luma sample of a mapped block goes through it
     __shared__ uint16_t s_lut[4096];
     const uint16_t *lut = nullptr;
-    if (a.lmcs_fwd) {
-        for (int i = threadIdx.x; i < (1 << a.bd); i += kInterWarps * 32)
-            s_lut[i] = __ldg(a.lmcs_fwd + i);
-        __syncthreads();
-        lut = s_lut;
-    }
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int wi = blockIdx.x * kInterWarps + warp;
 
     // the blocks this warp owns: one of width 16, two of width 8 or four of width 4
     constexpr int cls = kCls;
     const int first = a.first + (wi << kCls), last = a.last;
-    if (first >= last)
+    bool mine = first < last;
+    if (kPart != 0) {
+        const int bi = first + (lane >> (5 - cls));
+        const bool fancy = bi < last && (a.blocks[bi].flags & kFancyFlags);
+        mine = mine && (__any_sync(0xffffffffu, fancy) == (kPart == 2));
+        if (!__syncthreads_or(mine))
+            return;
+    }
+    if (a.lmcs_fwd) {
+        for (int i = threadIdx.x; i < (1 << a.bd); i += kInterWarps * 32)
+            s_lut[i] = __ldg(a.lmcs_fwd + i);
+        __syncthreads();
+        lut = s_lut;
+    }
+    if (!mine)
         return;
     uint16_t *win = s_buf[warp];
     int16_t *tmp = reinterpret_cast<int16_t *>(s_buf[warp]) + kWinElems;
@@ -671,9 +686,9 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const VVCB200PredBlock b = a.blocks[active ? bi : first];
         const bool luma = active && !(b.flags & VVCB200_PB_CHROMA_ONLY);
         int mv[2][2] = { { b.mv[0][0], b.mv[0][1] }, { b.mv[1][0], b.mv[1][1] } };
-        const bool dmvr = kCls < 2 && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
-        bool bdof = kCls < 2 && luma && (b.flags & VVCB200_PB_BDOF) && b.pred_flag == 3 && b.h >= 8;
-        if (kCls < 2 && __any_sync(0xffffffffu, active && dmvr)) {
+        const bool dmvr = kFancyX && kCls < 2 && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
+        bool bdof = kFancyX && kCls < 2 && luma && (b.flags & VVCB200_PB_BDOF) && b.pred_flag == 3 && b.h >= 8;
+        if (kFancyX && kCls < 2 && __any_sync(0xffffffffu, active && dmvr)) {
             // each group's scratch: 2 predictions of (w+4) x 20 samples + 25 SADs
             const int region = cls == 0 ? kBufElems : kBufElems / 2;
             if (!dmvr_refine(a, p, b, active && dmvr, li, gs, reinterpret_cast<int16_t *>(s_buf[warp]) + g * region, mv))
@@ -691,7 +706,7 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
         const int ws = (16 >> cls) + 10;                // 26 / 18 / 14 samples: an odd number of words
         const int win_sz = 23 * ws, tmp_sz = (16 >> cls) * 26;
         const int bdof_region = cls == 0 ? 0 : kBufElems / 2;
-        predict_component<8, (16 >> kCls)>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
+        predict_component<8, (16 >> kCls), kFancyX>(a, p, b, luma, 0, li, gs, win + g * win_sz, ws, tmp + g * tmp_sz, 26, mv, active && dmvr, bdof,
                              reinterpret_cast<int16_t *>(s_buf[warp]) + g * bdof_region, s_vxy[warp][g & 1], lut);
     }
     __syncwarp();
@@ -704,11 +719,11 @@ inter_kernel(const InterArgs a, const VVCB200InterParams p)
 #pragma unroll
         for (int k = 0; k < 4; k++)
             mv[k >> 1][k & 1] = s_mv[warp][(g >> 1) & 3][k];
-        const bool dmvr = kCls < 2 && active && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
+        const bool dmvr = kFancyX && kCls < 2 && active && (b.flags & VVCB200_PB_DMVR) && b.pred_flag == 3 && b.h >= 8;
         const int wc = 8 >> cls;
         const int ws = wc + 6;                          // 14 / 10 / 8 samples
         const int win_sz = 11 * ws + 8, tmp_sz = wc * 14;
-        predict_component<4, (8 >> kCls)>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
+        predict_component<4, (8 >> kCls), kFancyX>(a, p, b, active && !(b.flags & VVCB200_PB_LUMA_ONLY), 1 + (g & 1), li, gs,
                              win + g * win_sz, ws, tmp + g * tmp_sz, 14, mv, dmvr, false, nullptr, nullptr, nullptr);
     }
 }
@@ -761,32 +776,46 @@ extern "C" int vvcb200_inter_batch(const VVCB200Planes *dst, const VVCB200Planes
     a.bd = params->bit_depth;
     const int bound[4] = { 0, a.n16, a.n16 + a.n8, n };
     const cudaStream_t main_stream = (cudaStream_t)stream;
-    int classes = 0;
-    for (int cls = 0; cls < 3; cls++)
-        classes += bound[cls + 1] > bound[cls];
-    ForkStreams *f = classes > 1 ? fork_streams(main_stream) : nullptr;         // the classes are independent grids: side by side
+    // The launches: classes 0 / 1 as two grids over the same records (warps with a DMVR / BDOF / GPM record, the slow ones,
+    // first; then the warps without, on a kernel a third the size), class 2 as one.  They write disjoint blocks: side by side.
+    struct Launch { int cls, part; } launches[5];
+    int n_launch = 0;
+    for (int cls = 0; cls < 3; cls++) {
+        if (bound[cls + 1] == bound[cls])
+            continue;
+        if (cls < 2) {
+            launches[n_launch++] = { cls, 2 };
+            launches[n_launch++] = { cls, 1 };
+        } else {
+            launches[n_launch++] = { cls, 0 };
+        }
+    }
+    ForkStreams *f = n_launch > 1 ? fork_streams(main_stream) : nullptr;
     if (f)
         VVC_CUDA(cudaEventRecord(f->fork, main_stream));
     int used = 0;                                                         // side streams in use
-    for (int cls = 0; cls < 3; cls++) {
+    for (int i = 0; i < n_launch; i++) {
+        const int cls = launches[i].cls, part = launches[i].part;
         a.first = bound[cls];
         a.last = bound[cls + 1];
         const int count = a.last - a.first;
-        if (!count)
-            continue;
-        cudaStream_t st = main_stream;                                    // the first class present stays on the caller's stream
-        if (f && classes > 1 && used < 2 && cls > 0 && bound[cls] > 0) {
+        cudaStream_t st = main_stream;                                    // the first launch stays on the caller's stream
+        if (f && i > 0 && used < 4) {
             st = f->side[used];
             VVC_CUDA(cudaStreamWaitEvent(st, f->fork, 0));
         }
         const int warps = (count + (1 << cls) - 1) >> cls;
         const int grid = (warps + kInterWarps - 1) / kInterWarps;
-        if (cls == 0)
-            inter_kernel<0><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
+        if (cls == 0 && part == 2)
+            inter_kernel<0, 2><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
+        else if (cls == 0)
+            inter_kernel<0, 1><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
+        else if (cls == 1 && part == 2)
+            inter_kernel<1, 2><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         else if (cls == 1)
-            inter_kernel<1><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
+            inter_kernel<1, 1><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         else
-            inter_kernel<2><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
+            inter_kernel<2, 0><<<grid, kInterWarps * 32, 0, st>>>(a, *params);
         VVC_LAUNCH_CHECK();
         if (st != main_stream) {
             VVC_CUDA(cudaEventRecord(f->join[used], st));
