@@ -113,8 +113,10 @@ template <int TAPS>
 __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, int gs, int w, int h, int log2w,
                                             const uint16_t *src, int stride, const Window &fw, int xi, int yi,
                                             const int8_t *hf, const int8_t *vf, int bd,
-                                            uint16_t *win, int ws, int16_t *tmp, int ts)
+                                            uint16_t *win, int ws, int16_t *tmp, int ts, int trim)
 {
+    // trim = 1: the filter set's outer taps are zero (the 6-tap affine luma set): the window's outer ring and the first /
+    // last intermediate row are multiplied by zero whatever they hold, so they are neither fetched nor computed
     constexpr int BEFORE = TAPS / 2 - 1;
     const int rows = h + TAPS - 1, cols = w + TAPS - 1;
 
@@ -123,9 +125,9 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
         // stage the window: a lane owns columns li, li + gs, ... and walks down the rows
         // (eight loads are issued before the first store so that they are in flight together: the dependent
         // load -> store walk down the rows was the kernel's main memory stall)
-        for (int c = li; c < cols; c += gs) {
+        for (int c = li + trim; c < cols - trim; c += gs) {
             const int sx = clip3(xi - BEFORE + c, fw.x0, fw.x1);
-            for (int r0 = 0; r0 < rows; r0 += 8) {
+            for (int r0 = trim; r0 < rows - trim; r0 += 8) {
                 uint16_t v[8];
 #pragma unroll
                 for (int k = 0; k < 8; k++) {
@@ -134,7 +136,7 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
                 }
 #pragma unroll
                 for (int k = 0; k < 8; k++)
-                    if (r0 + k < rows)
+                    if (r0 + k < rows - trim)
                         win[(r0 + k) * ws + c] = v[k];
             }
         }
@@ -145,8 +147,8 @@ __device__ __forceinline__ void interpolate(int (&val)[8], bool active, int li, 
         TapWords<TAPS> t;
         t.load(hf);
         const int strips = w > 8 ? 2 : 1, sw = min(w, 8);
-        for (int i = li; i < rows * strips; i += gs) {
-            const int r = strips == 2 ? i >> 1 : i, s = strips == 2 ? i & 1 : 0;
+        for (int i = li; i < (rows - 2 * trim) * strips; i += gs) {
+            const int r = trim + (strips == 2 ? i >> 1 : i), s = strips == 2 ? i & 1 : 0;
             const uint32_t *p = reinterpret_cast<const uint32_t *>(win + r * ws + s * 8);
             int wd[8], out[8];
 #pragma unroll
@@ -524,10 +526,10 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
                              TAPS / 2 - 1, TAPS / 2);
         if (l == 0)
             interpolate<TAPS>(v0, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
-                              win, ws, tmp, ts);
+                              win, ws, tmp, ts, TAPS == 8 && set == 2);
         else
             interpolate<TAPS>(v1, use, li, gs, w, h, log2w, ref.p[c], ref.stride[c], fw[l], xi, yi, hf, vf, bd,
-                              win, ws, tmp, ts);
+                              win, ws, tmp, ts, TAPS == 8 && set == 2);
         if (TAPS == 8 && kFancyX && a.prof) {
             const bool go = use && w == 4 && h == 4 && (b.flags & (l ? VVCB200_PB_PROF1 : VVCB200_PB_PROF0));
             if (__any_sync(0xffffffffu, go)) {
@@ -603,34 +605,55 @@ __device__ __forceinline__ void predict_component(const InterArgs &a, const VVCB
     const int x = li & (w - 1), chunk = li >> log2w;
     if (chunk >= nchunk)
         return;
+    if (a.to_tmp14) {
+        int16_t *o = reinterpret_cast<int16_t *>(a.tmp14.p[c]) + (size_t)(y0 + chunk * outs) * a.tmp14.stride[c] + x0 + x;
 #pragma unroll
-    for (int k = 0; k < 8; k++) {
-        if (k < outs) {
-            const int y = chunk * outs + k;
-            if (a.to_tmp14) {
-                int16_t *o = reinterpret_cast<int16_t *>(a.tmp14.p[c]) + (size_t)(y0 + y) * a.tmp14.stride[c] + x0 + x;
-                *o = (int16_t)(l_uni == 0 ? v0[k] : v1[k]);
-                continue;
-            }
-            int r;
-            if (mode == 0)
-                r = ((l_uni == 0 ? v0[k] : v1[k]) + off) >> sh;
-            else if (mode == 1)
-                r = (((l_uni == 0 ? v0[k] : v1[k]) * wgt0 + off) >> sh) + ox;
-            else if (mode == 2)
-                r = (v0[k] + v1[k] + off) >> sh;
-            else if (mode == 3)
-                r = (v0[k] * wgt0 + v1[k] * wgt1 + off) >> sh;
-            else {
+        for (int k = 0; k < 8; k++)
+            if (k < outs)
+                o[(size_t)k * a.tmp14.stride[c]] = (int16_t)(l_uni == 0 ? v0[k] : v1[k]);
+        return;
+    }
+    // every mode as one multiply-add form r = (v0 * wgt0 + v1 * wgt1 + off) >> sh (+ ox): the mode is decided once per block,
+    // not once per sample, and the row pointer walks down the block
+    const int pmax = (1 << bd) - 1;
+    const int dstride = a.dst.stride[c];
+    uint16_t *o = a.dst.p[c] + (size_t)(y0 + chunk * outs) * dstride + x0 + x;
+    if (mode == 4) {
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (k < outs) {
+                const int y = chunk * outs + k;
                 const int wg = gpm_w[(gpm_y + gpm_sy * (y << hs)) * 112 + gpm_x + gpm_sx * (x << hs)];
-                r = (v0[k] * wg + v1[k] * (8 - wg) + off) >> sh;
+                int r = min(max((v0[k] * wg + v1[k] * (8 - wg) + off) >> sh, 0), pmax);
+                if (lmcs)
+                    r = lut[r];
+                o[(size_t)k * dstride] = (uint16_t)r;
             }
-            r = clip_pixel(r, bd);
+        return;
+    }
+    if (mode < 2) {                                      // one list: ((v * w + off) >> sh) + ox, w = 1 without weights
+        if (mode == 0)
+            wgt0 = 1;
+#pragma unroll
+        for (int k = 0; k < 8; k++)
+            if (k < outs) {
+                int r = min(max((((l_uni == 0 ? v0[k] : v1[k]) * wgt0 + off) >> sh) + ox, 0), pmax);
+                if (lmcs)
+                    r = lut[r];
+                o[(size_t)k * dstride] = (uint16_t)r;
+            }
+        return;
+    }
+    if (mode == 2)
+        wgt0 = wgt1 = 1;
+#pragma unroll
+    for (int k = 0; k < 8; k++)
+        if (k < outs) {
+            int r = min(max((v0[k] * wgt0 + v1[k] * wgt1 + off) >> sh, 0), pmax);
             if (lmcs)
                 r = lut[r];
-            a.dst.p[c][(size_t)(y0 + y) * a.dst.stride[c] + x0 + x] = (uint16_t)r;
+            o[(size_t)k * dstride] = (uint16_t)r;
         }
-    }
 }
 
 #ifndef VVC_INTER_MIN_BLOCKS
