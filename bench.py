@@ -553,12 +553,15 @@ def main():
         step(i, lane=lanes[i % n_lanes])
     barrier()
     # stage boundaries are marked with events on the launching stream (torch's current stream), one picture at a time
+    # (the first pictures after the barrier find the GPU idle and measure how fast the host submits, not how long the
+    # kernels run: three extra pictures are queued first and left out)
     n_serial = max(1, min(args.steps, 10))
-    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(n_serial)]
-    for i in range(n_serial):
+    evs = [[torch.cuda.Event(enable_timing=True) for _ in range(len(STAGES) + 1)] for _ in range(n_serial + 3)]
+    for i in range(n_serial + 3):
         evs[i][0].record()
         step(i, evs[i])
     barrier()
+    evs = evs[3:]
     stage_ms = {name: float(np.mean([evs[i][k].elapsed_time(evs[i][k + 1]) for i in range(n_serial)]))
                 for k, name in enumerate(STAGES)}
     serial_ms = float(np.mean([evs[i][0].elapsed_time(evs[i][len(STAGES)]) for i in range(n_serial)]))

@@ -102,6 +102,70 @@ def main():
         if args.only == "filters":
             return
 
+    if args.only == "inter_after":
+        # the INTER stage timed by events on the launching stream, alone and right after another stage's kernels
+        sub = np.ascontiguousarray(b)
+        p = abi.InterParams.from_buffer_copy(bytes(it["params"]))
+        d = dev(sub)
+        lf = pic["lf"]
+        src = util.to_device_planes(it["refs"][0], torch)
+        src_p = lib.device_planes(src)
+        out2 = util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch)
+        out2_p = lib.device_planes(out2)
+        sao, alf, alfp = dev(lf["sao"]), dev(lf["alf"]), dev(lf["alf_params"])
+        table = torch.zeros(lib.sao_alf_scratch_bytes(), dtype=torch.uint8, device="cuda")
+
+        def inter():
+            lib.inter_batch(cur_p, refs_p, d, len(sub), p, lmcs_fwd_lut=fwd, prof=prof)
+
+        def saoalf():
+            lib.sao_alf_picture(out2_p, src_p, sao, alf, alfp, pic["ctb_log2"], scratch=table)
+        for label, before in (("alone", None), ("after SAO + ALF", saoalf), ("after another INTER", inter)):
+            tot, n = 0.0, 20
+            evs = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(n)]
+            inter(); torch.cuda.synchronize()
+            for e0, e1 in evs:
+                if before:
+                    before()
+                e0.record(); inter(); e1.record()
+            torch.cuda.synchronize()
+            print("inter %-22s %.4f ms" % (label, sum(e0.elapsed_time(e1) for e0, e1 in evs) / n))
+        return
+
+    if args.only == "inter_rot":
+        # which operand being cold (not in L2) costs the INTER stage what: rotate four copies of one operand at a time
+        sub = np.ascontiguousarray(b)
+        p = abi.InterParams.from_buffer_copy(bytes(it["params"]))
+        R = 4
+        refs_sets = [[util.to_device_planes(r, torch) for r in it["refs"]] for _ in range(R)]
+        refs_ps = [[lib.device_planes(r) for r in rs_] for rs_ in refs_sets]
+        curs = [util.to_device_planes([np.zeros((h, w), np.uint16) for (w, h) in pic["dims"]], torch) for _ in range(R)]
+        cur_ps = [lib.device_planes(c) for c in curs]
+        blks = [dev(sub) for _ in range(R)]
+        profs = [dev(it["prof"]) for _ in range(R)]
+        junk = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+        for label, rr, rc, rb, flush in (("nothing rotates", 0, 0, 0, 0), ("refs rotate", 1, 0, 0, 0), ("dst rotates", 0, 1, 0, 0),
+                                         ("records rotate", 0, 0, 1, 0), ("all rotate", 1, 1, 1, 0), ("L2 flushed before each", 0, 0, 0, 1)):
+            k = [0]
+
+            def fn():
+                i = k[0] % R
+                k[0] += 1
+                lib.inter_batch(cur_ps[i if rc else 0], refs_ps[i if rr else 0], blks[i if rb else 0], len(sub), p, lmcs_fwd_lut=fwd,
+                                prof=profs[i if rb else 0])
+            if not flush:
+                print("inter, %-24s %.4f ms" % (label, timed(torch, fn)))
+            else:
+                tot = 0.0
+                for _ in range(10):
+                    junk.add_(1)
+                    torch.cuda.synchronize()
+                    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                    e0.record(); fn(); e1.record(); torch.cuda.synchronize()
+                    tot += e0.elapsed_time(e1)
+                print("inter, %-24s %.4f ms" % (label, tot / 10))
+        return
+
     res = [torch.zeros_like(t) for t in cur]
     res_p = lib.device_planes(res)
     tbs, levels = dev(rs["tbs"]), dev(rs["levels"])
