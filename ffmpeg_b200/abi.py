@@ -118,7 +118,7 @@ assert PB_DTYPE.itemsize == 32
 class InterParams(C.Structure):
     _fields_ = [
         ("bit_depth", C.c_int32), ("log2_denom", C.c_int32 * 2), ("n_w16", C.c_int32), ("n_w8", C.c_int32),
-        ("num_ref_idx_active", C.c_int32 * 2), ("reserved", C.c_int32),
+        ("num_ref_idx_active", C.c_int32 * 2), ("dmvr_first", C.c_int32),
         ("weight", ((C.c_int16 * 16) * 3) * 2), ("offset", ((C.c_int16 * 16) * 3) * 2),
         ("ref_slot", (C.c_uint8 * 16) * 2),
     ]
@@ -155,6 +155,7 @@ def order_blocks_by_width(blocks, params):
     blocks = np.ascontiguousarray(blocks[order])
     params.n_w16 = int(np.sum(blocks["w"] == 16))
     params.n_w8 = int(np.sum(blocks["w"] == 8))
+    params.dmvr_first = 1                           # slow rank 0 = DMVR: a prefix of each width class
     return blocks
 
 
@@ -206,6 +207,7 @@ ALF_PARAMS_DTYPE = np.dtype([
 # ---- intra --------------------------------------------------------------------------------------------------------
 IB_MIP, IB_MIP_TRANSPOSED, IB_ISP, IB_BDPCM, IB_RESIDUAL, IB_CIIP, IB_ADD_ONLY, IB_LMCS_SCALE = 1, 2, 4, 8, 16, 32, 64, 128
 TB_TO_RESIDUAL = 512
+TB_LEVELS8 = 1024
 
 IB_DTYPE = np.dtype([
     ("x0", "<u2"), ("y0", "<u2"), ("w", "u1"), ("h", "u1"), ("c_idx", "u1"), ("mode", "i1"), ("ref_idx", "u1"),

@@ -688,7 +688,21 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
                         // download stream so that the lane goes straight on with the residual stage
         VVC_CUDA(cudaEventRecord(S.mv_ready, S.lane->stream));
         VVC_CUDA(cudaStreamWaitEvent(c->d2h, S.mv_ready, 0));
-        VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->d2h));
+        if (params->dmvr_first) {
+            // the batch is in the recommended order: the records DMVR may move are a prefix of the width-16 and of the width-8
+            // class; every other entry would only tell the host the vectors it sent
+            const int start[2] = { 0, b16 }, end[2] = { b16, b8 };
+            for (int k = 0; k < 2; k++) {
+                int m = start[k];
+                while (m < end[k] && (blocks[m].flags & VVCB200_PB_DMVR))
+                    m++;
+                if (m > start[k])
+                    VVC_CUDA(cudaMemcpyAsync(refined_mv + (size_t)start[k] * 4, d_mv + (size_t)start[k] * 4,
+                                             (size_t)(m - start[k]) * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->d2h));
+            }
+        } else {
+            VVC_CUDA(cudaMemcpyAsync(refined_mv, d_mv, (size_t)n * 4 * sizeof(int32_t), cudaMemcpyDeviceToHost, c->d2h));
+        }
         VVC_CUDA(cudaEventRecord(S.mv_copied, c->d2h));
         S.mv_pending = true;
     }
@@ -966,41 +980,68 @@ int vvcb200_pic_sao_alf(VVCB200Ctx *c, const VVCB200SaoCtb *sao, const VVCB200Al
 }  // extern "C"
 
 // ---- host-side descriptor producers ----------------------------------------------------------------------
-extern "C" int vvcb200_pack_levels_sparse(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int16_t *out, size_t out_cap,
-                                          size_t *out_len)
+extern "C" int vvcb200_pack_levels(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int sparse, int narrow, int16_t *out,
+                                   size_t out_cap, size_t *out_len)
 {
     if (!dense || !tbs || !out || !out_len || n < 0) {
-        set_error("vvcb200_pack_levels_sparse: bad argument");
+        set_error("vvcb200_pack_levels: bad argument");
         return VVCB200_ERR_ARG;
     }
     size_t o = 0;
     for (int t = 0; t < n; t++) {
-        const int box = tbs[t].nzw * tbs[t].nzh, words = (box + 31) >> 5;
+        const int box = tbs[t].nzw * tbs[t].nzh, words = sparse ? (box + 31) >> 5 : 0;
         const int16_t *lv = dense + tbs[t].coeff_off;
-        if (o + 2 * (size_t)words + box > out_cap) {
-            set_error("vvcb200_pack_levels_sparse: output buffer too small");
+        if (o + 2 * (size_t)words + box + 2 > out_cap) {
+            set_error("vvcb200_pack_levels: output buffer too small");
             return VVCB200_ERR_TOO_BIG;
         }
-        uint32_t *bitmap = reinterpret_cast<uint32_t *>(out + o);     // o stays even: 2 * words + an even number of levels
-        int16_t *nz = out + o + 2 * words;
+        bool fits8 = narrow != 0;
+        for (int i = 0; fits8 && i < box; i++)
+            fits8 = lv[i] >= -128 && lv[i] <= 127;
+        uint32_t *bitmap = reinterpret_cast<uint32_t *>(out + o);     // sparse: o stays even
+        int16_t *body = out + o + 2 * words;
+        int8_t *body8 = reinterpret_cast<int8_t *>(body);
         int count = 0;
-        for (int w = 0; w < words; w++) {
-            uint32_t bits = 0;
-            const int lim = box - 32 * w < 32 ? box - 32 * w : 32;
-            for (int b = 0; b < lim; b++)
-                if (lv[32 * w + b]) {
-                    bits |= 1u << b;
-                    nz[count++] = lv[32 * w + b];
-                }
-            bitmap[w] = bits;
+        if (sparse) {
+            for (int w = 0; w < words; w++) {
+                uint32_t bits = 0;
+                const int lim = box - 32 * w < 32 ? box - 32 * w : 32;
+                for (int b = 0; b < lim; b++)
+                    if (lv[32 * w + b]) {
+                        bits |= 1u << b;
+                        if (fits8)
+                            body8[count++] = (int8_t)lv[32 * w + b];
+                        else
+                            body[count++] = lv[32 * w + b];
+                    }
+                bitmap[w] = bits;
+            }
+        } else {
+            for (int i = 0; i < box; i++)
+                if (fits8)
+                    body8[count++] = (int8_t)lv[i];
+                else
+                    body[count++] = lv[i];
         }
-        if (count & 1)
-            nz[count++] = 0;                                          // keep the next block's bitmap 4-byte aligned
+        if (fits8) {
+            while (count & (sparse ? 3 : 1))                          // whole int16 slots; sparse: the next bitmap stays 4-byte aligned
+                body8[count++] = 0;
+            count >>= 1;
+        } else if (sparse && (count & 1)) {
+            body[count++] = 0;
+        }
+        tbs[t].flags = (uint16_t)((tbs[t].flags & ~VVCB200_TB_LEVELS8) | (fits8 ? VVCB200_TB_LEVELS8 : 0));
         tbs[t].coeff_off = (uint32_t)o;
         o += 2 * (size_t)words + count;
     }
     *out_len = o;
     return 0;
+}
+
+extern "C" int vvcb200_pack_levels_sparse(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int16_t *out, size_t out_cap,
+                                          size_t *out_len)
+{
+    return vvcb200_pack_levels(dense, tbs, n, 1, 0, out, out_cap, out_len);
 }
 
 extern "C" int vvcb200_pack_deblock_edges(uint8_t *const edge_out[2][3], const uint8_t *const bs[2][3],

@@ -54,13 +54,21 @@ __device__ __forceinline__ void fetch_levels(const ResidualArgs &a, const VVCB20
 {
     const int n = d.nzw * d.nzh;
     const int16_t *lv = a.levels + d.coeff_off;
+    const bool narrow = d.flags & VVCB200_TB_LEVELS8;    // int8 levels, two per slot
     if (!a.sparse) {
-        for (int i = li; i < n; i += lpt)
-            dst[i] = lv[i];
+        if (narrow) {
+            const int8_t *l8 = reinterpret_cast<const int8_t *>(lv);
+            for (int i = li; i < n; i += lpt)
+                dst[i] = l8[i];
+        } else {
+            for (int i = li; i < n; i += lpt)
+                dst[i] = lv[i];
+        }
         return;
     }
     const uint32_t *bitmap = reinterpret_cast<const uint32_t *>(lv);
     const int16_t *nz = lv + 2 * ((n + 31) >> 5);
+    const int8_t *nz8 = reinterpret_cast<const int8_t *>(nz);
     int cur = -1, before = 0;
     uint32_t word = 0;
     for (int i = li; i < n; i += lpt) {
@@ -70,7 +78,8 @@ __device__ __forceinline__ void fetch_levels(const ResidualArgs &a, const VVCB20
             word = __ldg(bitmap + ++cur);
         }
         const uint32_t bit = 1u << (i & 31);
-        dst[i] = (word & bit) ? nz[before + __popc(word & (bit - 1))] : (int16_t)0;
+        const int k = before + __popc(word & (bit - 1));
+        dst[i] = (word & bit) ? (narrow ? (int16_t)nz8[k] : nz[k]) : (int16_t)0;
     }
 }
 

@@ -272,6 +272,7 @@ void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params)
         params->n_w16 += b->blocks[i].w == 16;
         params->n_w8  += b->blocks[i].w == 8;
     }
+    params->dmvr_first = 1;                  /* slow rank 0: the DMVR records lead their width class */
     free(tmp); free(key); free(ktmp);
 }
 

@@ -3,7 +3,7 @@ import hashlib
 
 import numpy as np
 
-from . import lib
+from . import abi, lib
 
 
 def md5(a):
@@ -47,10 +47,14 @@ class EnginePicture:
         self.res_params = rs["params"]
         levels, tbs = rs["levels"], rs["tbs"]
         if sparse_levels and len(tbs):
-            sp_levels, sp_tbs = lib.pack_levels_sparse(levels, tbs)
-            if sparse_levels is True or sp_levels.nbytes < levels.nbytes:     # "auto": whichever form is smaller, as an emitter would
+            # blocks whose levels fit int8 travel as int8 (VVCB200_TB_LEVELS8) in either form
+            d_levels, d_tbs = lib.pack_levels(levels, tbs, sparse=False, narrow=True)
+            sp_levels, sp_tbs = lib.pack_levels(levels, tbs, sparse=True, narrow=True)
+            if sparse_levels is True or sp_levels.nbytes < d_levels.nbytes:   # "auto": whichever form is smaller, as an emitter would
                 levels, tbs = sp_levels, sp_tbs
                 self.res_params = lib.sparse_params(rs["params"])
+            else:
+                levels, tbs = d_levels, d_tbs
         self.levels = ctx.pinned_copy(levels)
         self.tbs = ctx.pinned_copy(tbs)
         edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
@@ -87,8 +91,16 @@ class EnginePicture:
     def picture_bytes(self):
         return int(sum(p.nbytes for p in self.out))
 
+    def refined_bytes(self):
+        """What comes back of the refined vectors: every record's, or — batch in the recommended order — the DMVR records'."""
+        if not len(self.blocks) or not self.want_mv:
+            return 0
+        if self.pic["inter"]["params"].dmvr_first:
+            return 16 * int(((self.pic["inter"]["blocks"]["flags"] & abi.PB_DMVR) != 0).sum())
+        return int(self.refined[0].nbytes)
+
     def d2h_bytes(self):
-        return self.picture_bytes() + (int(self.refined[0].nbytes) if len(self.blocks) and self.want_mv else 0)
+        return self.picture_bytes() + self.refined_bytes()
 
     def upload_refs(self):
         for i, r in enumerate(self.refs):

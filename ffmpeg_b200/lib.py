@@ -83,6 +83,19 @@ def pack_levels_sparse(levels, tbs):
     return out[:n.value].copy(), out_tbs
 
 
+def pack_levels(levels, tbs, sparse=False, narrow=True):
+    """vvcb200_pack_levels (host, no CUDA): dense int16 level buffer + TB records -> (packed buffer, TB records with coeff_off
+    into it and TB_LEVELS8 on the blocks stored as int8).  sparse: pair with sparse_params()."""
+    levels = np.ascontiguousarray(levels, np.int16)
+    out_tbs = np.ascontiguousarray(tbs, abi.TB_DTYPE).copy()
+    cap = levels.size + 4 * len(out_tbs) + 2 * (levels.size // 32) + 64
+    out = np.zeros(cap, np.int16)
+    n = C.c_size_t(0)
+    check(load().vvcb200_pack_levels(_ptr(levels), _ptr(out_tbs), len(out_tbs), int(bool(sparse)), int(bool(narrow)), _ptr(out),
+                                     C.c_size_t(cap), C.byref(n)))
+    return out[:n.value].copy(), out_tbs
+
+
 def sparse_params(params):
     p = abi.ResidualParams.from_buffer_copy(bytes(params))
     p.levels_sparse = 1

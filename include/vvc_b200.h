@@ -71,6 +71,10 @@ enum {
     VVCB200_TB_LMCS_SCALE  = 1 << 8,  /* LMCS chroma residual scaling applies (vvc_intra.c:451); scale in `lmcs_scale`    */
     VVCB200_TB_TO_RESIDUAL = 1 << 9,  /* store the residual in the int16 residual planes instead of adding it to dst: the
                                          TB belongs to an intra / CIIP block whose prediction is not there yet            */
+    VVCB200_TB_LEVELS8     = 1 << 10, /* every level of this TB lies in [-128, 127] and is stored as int8: the dense box, or
+                                         the non-zero list of the sparse form, two levels per int16 slot of the level buffer
+                                         (padded to a whole slot; sparse: to an even number of slots).  Most blocks of most
+                                         streams: halves what they upload (vvcb200_pack_levels)                            */
 };
 
 typedef struct VVCB200TransformBlock {
@@ -151,6 +155,10 @@ VVCB200_API int vvcb200_residual_class(const VVCB200TransformBlock *tb);
  * shrink 3-4x, which is most of what a picture uploads. */
 VVCB200_API int vvcb200_pack_levels_sparse(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int16_t *out,
                                            size_t out_cap, size_t *out_len);
+/* The general form: sparse 0 / 1 as above; narrow != 0: blocks whose levels all fit int8 are stored that way and flagged
+ * VVCB200_TB_LEVELS8 (the others stay int16).  Same worst-case room as above (dense: n_dense + n). */
+VVCB200_API int vvcb200_pack_levels(const int16_t *dense, VVCB200TransformBlock *tbs, int n, int sparse, int narrow,
+                                    int16_t *out, size_t out_cap, size_t *out_len);
 
 VVCB200_API int vvcb200_residual_batch(const VVCB200Planes *dst, const VVCB200Planes *d_residual,
                            const int16_t *d_levels, const VVCB200TransformBlock *d_tbs, int n,
@@ -211,7 +219,11 @@ typedef struct VVCB200InterParams {
                                        width 8, then the width-4 ones (lets a warp own equal-width blocks)      */
     int32_t  num_ref_idx_active[2]; /* entries of ref_slot[list][] in use (RefPicList.nb_refs, vvcdec.h:45-50); 0 = not
                                        stated: Level B then treats all 16 as pictures this one reads                 */
-    int32_t  reserved;
+    int32_t  dmvr_first;            /* the emitter's statement that the records flagged VVCB200_PB_DMVR are the first ones of
+                                       the width-16 class and the first ones of the width-8 class (the recommended order,
+                                       vvcb200_emit_order_blocks): vvcb200_pic_inter then returns refined vectors for those
+                                       records only — the other entries of `refined_mv` are left untouched, they would repeat
+                                       the vectors the host sent.  0: every entry is written                                 */
     int16_t  weight[2][3][16];      /* [list][c_idx][ref_idx]                                  */
     int16_t  offset[2][3][16];
     uint8_t  ref_slot[2][16];       /* index into the `refs` array of (list, ref_idx)          */

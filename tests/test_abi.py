@@ -78,3 +78,34 @@ def test_sparse_level_packer_round_trips():
         assert np.array_equal(bits, dense != 0)
         nz = lv[off + 2 * words:off + 2 * words + int(bits.sum())]
         assert np.array_equal(nz, dense[bits])
+
+
+def test_narrow_level_packer_round_trips():
+    """vvcb200_pack_levels with narrow levels: blocks whose levels fit int8 are stored as int8 (flagged TB_LEVELS8), the
+    others as int16; both the dense and the sparse form decode back to the scan boxes."""
+    import numpy as np
+    from ffmpeg_b200 import abi, synth
+    pic = synth.residual_picture(5, 416, 240)
+    pic["levels"][1::4] = 0
+    for sparse in (False, True):
+        lv, tbs = lib.pack_levels(pic["levels"], pic["tbs"], sparse=sparse, narrow=True)
+        narrow = (tbs["flags"] & abi.TB_LEVELS8) != 0
+        assert narrow.any() and not narrow.all()                 # the synthetic levels reach +-200
+        assert lv.nbytes < 0.8 * (pic["levels"].nbytes if not sparse else lib.pack_levels_sparse(pic["levels"], pic["tbs"])[0].nbytes)
+        if sparse:
+            assert (tbs["coeff_off"] % 2 == 0).all()
+        for t_old, t_new in list(zip(pic["tbs"], tbs))[::23]:
+            n = int(t_old["nzw"]) * int(t_old["nzh"])
+            dense = pic["levels"][t_old["coeff_off"]:t_old["coeff_off"] + n]
+            is8 = bool(t_new["flags"] & abi.TB_LEVELS8)
+            assert is8 == bool(np.all((dense >= -128) & (dense <= 127)))
+            off = int(t_new["coeff_off"])
+            if sparse:
+                words = (n + 31) // 32
+                bits = np.unpackbits(lv[off:off + 2 * words].view(np.uint8), bitorder="little")[:n].astype(bool)
+                assert np.array_equal(bits, dense != 0)
+                want, off = dense[bits], off + 2 * words
+            else:
+                want = dense
+            got = lv[off:off + (len(want) + 1) // 2].view(np.int8)[:len(want)] if is8 else lv[off:off + len(want)]
+            assert np.array_equal(got.astype(np.int16), want)

@@ -66,6 +66,38 @@ def test_picture_from_emitted_descriptors_md5(seed, w, h, ctb, lmcs, ns, lfase):
         ctx.close()
 
 
+def test_refined_vectors_come_back_for_the_dmvr_records():
+    """Level B returns the vectors DMVR settled on (the reference's tab_dmvr_mvf, vvc_inter.c:750-762).  A batch in the
+    recommended order (dmvr_first) gets them for the DMVR records only, the other entries stay as the host left them."""
+    from oracle import refapi
+    from ffmpeg_b200 import abi
+    if not refapi.available():
+        pytest.skip("oracle/_ref not built")
+    w, h = 416, 240
+    pic = synth.full_picture(51, w, h, ctb_log2=7)
+    it = pic["inter"]
+    assert it["params"].dmvr_first == 1
+    dm = (it["blocks"]["flags"] & abi.PB_DMVR) != 0
+    assert dm.sum() > 10
+    planes = [np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]]
+    want = refapi.inter_batch(planes, it["refs"], it["blocks"], it["params"], want_refined_mv=True)
+    ctx = lib.Context(0, w, h, dpb_size=3)
+    try:
+        ep = pipeline.EnginePicture(ctx, pic)
+        ep.upload_refs()
+        for r in ep.refined:
+            r[...] = -77
+        ep.run()
+        ctx.sync()
+        got = ep.refined[ep.count % 4]
+        assert np.array_equal(got[dm], want[dm])
+        assert np.any(want[dm] != it["blocks"]["mv"][dm])
+        assert (got[~dm] == -77).all()
+        assert ep.refined_bytes() == 16 * int(dm.sum())
+    finally:
+        ctx.close()
+
+
 def test_back_to_back_pictures_overlap_safely():
     """Six pictures submitted without a sync in between, alternating between two DPB slots and two host frames: uploads,
     kernels and downloads of neighbouring pictures overlap on the context's three streams and every frame is right."""

@@ -19,10 +19,13 @@ def _params_for(pic):
     return p
 
 
-def _run_gpu(pic, planes_np, to_residual=False, sparse=False):
+def _run_gpu(pic, planes_np, to_residual=False, sparse=False, narrow=False):
     import torch
     pic = dict(pic, params=_params_for(pic))
-    if sparse:
+    if sparse == "narrow" or narrow:
+        lv, tb = lib.pack_levels(pic["levels"], pic["tbs"], sparse=bool(sparse), narrow=True)
+        pic = dict(pic, levels=lv, tbs=tb, params=lib.sparse_params(pic["params"]) if sparse else pic["params"])
+    elif sparse:
         lv, tb = lib.pack_levels_sparse(pic["levels"], pic["tbs"])
         pic = dict(pic, levels=lv, tbs=tb, params=lib.sparse_params(pic["params"]))
     dev = util.to_device_planes(planes_np, torch)
@@ -50,6 +53,8 @@ def test_residual_batch_matches_oracle(seed, w, h, levels):
         assert np.array_equal(got[c], want[c]), "plane %d differs (seed %d)" % (c, seed)
     assert util.plane_md5(got) == util.plane_md5(want)
     assert util.plane_md5(_run_gpu(pic, base, sparse=True)) == util.plane_md5(want), "sparse level format"
+    assert util.plane_md5(_run_gpu(pic, base, narrow=True)) == util.plane_md5(want), "int8 levels, dense boxes"
+    assert util.plane_md5(_run_gpu(pic, base, sparse="narrow")) == util.plane_md5(want), "int8 levels, sparse form"
 
 
 def test_residual_plane_mode_matches_oracle():
