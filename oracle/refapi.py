@@ -342,3 +342,29 @@ def emit_last_ms():
     f = lib().vvcref_emit_last_ns
     f.restype = C.c_int64
     return f() / 1e6
+
+
+# ---- the checkasm-style shim (oracle/shimlib/dsp_shim.c -> oracle/_ref/libvvcshim.so) ---------------------------------
+SHIM_FAMILIES = ("itx.itx", "itx.add_residual", "lmcs.filter", "inter.put", "inter.put_uni", "inter.put_uni_w")
+_shim = None
+
+
+def shim_available():
+    return os.path.exists(os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libvvcshim.so"))
+
+
+def shim():
+    global _shim
+    if _shim is None:
+        _shim = C.CDLL(os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libvvcshim.so"))
+        _shim.vvcshim_report.restype = C.c_char_p
+    return _shim
+
+
+def shim_check(bit_depth, seed=1):
+    """vvcshim_check: the reference's table against vvcb200_dsp_init()'s over the reference's own checkasm shapes.
+    Returns ({family: (members, calls, differing calls)}, device errors, calls the device cannot represent)."""
+    out = (C.c_int * (3 * len(SHIM_FAMILIES)))()
+    r = shim().vvcshim_check(int(bit_depth), int(seed), out)
+    res = {f: (out[3 * i], out[3 * i + 1], out[3 * i + 2]) for i, f in enumerate(SHIM_FAMILIES)}
+    return res, r & 0xffff, r >> 16

@@ -109,3 +109,17 @@ def test_narrow_level_packer_round_trips():
                 want = dense
             got = lv[off:off + (len(want) + 1) // 2].view(np.int8)[:len(want)] if is8 else lv[off:off + len(want)]
             assert np.array_equal(got.astype(np.int16), want)
+
+
+def test_checkasm_shim_loads_and_says_what_it_leaves_to_the_reference():
+    """oracle/_ref/libvvcshim.so: exports vvcb200_dsp_init / vvcshim_check and lists, with reasons, the
+    VVCDSPContext members that have no block-level device view (no compute here)."""
+    import pytest
+    from oracle import refapi
+    if not refapi.shim_available():
+        pytest.skip("oracle/_ref/libvvcshim.so not built")
+    s = refapi.shim()
+    assert hasattr(s, "vvcb200_dsp_init") and hasattr(s, "vvcshim_check")
+    text = s.vvcshim_report().decode()
+    for member in ("inter.avg", "sao.band_filter", "alf.filter", "lf.filter_luma", "intra.", "inter.sad"):
+        assert member in text
