@@ -2,6 +2,7 @@
 // Host-side C++ only; the kernels live in the stage files and are reached through their Level-A entries,
 // so both levels run exactly the same device code.  Everything is enqueued on the context's stream; the
 // caller's host buffers are read by asynchronous copies (pinned memory gives real overlap).
+#include <algorithm>
 #include <new>
 #include <string.h>
 #include <vector>
@@ -12,26 +13,30 @@ using namespace vvcb200;
 namespace {
 
 struct DevBuffer {
-    void *p = nullptr;
+    void *p = nullptr;             // what the kernels read: the owned allocation, or a place in an arena's device mirror
+    void *own = nullptr;
     size_t cap = 0;
     int reserve(size_t bytes)
     {
-        if (bytes <= cap)
+        if (bytes <= cap) {
+            p = own;
             return 0;
-        if (p)
-            cudaFree(p);
-        p = nullptr;
+        }
+        if (own)
+            cudaFree(own);
+        own = p = nullptr;
         cap = 0;
         const size_t want = bytes + bytes / 4 + 4096;
-        VVC_CUDA(cudaMalloc(&p, want));
+        VVC_CUDA(cudaMalloc(&own, want));
         cap = want;
+        p = own;
         return 0;
     }
     void release()
     {
-        if (p)
-            cudaFree(p);
-        p = nullptr;
+        if (own)
+            cudaFree(own);
+        own = p = nullptr;
         cap = 0;
     }
 };
@@ -85,7 +90,20 @@ struct StageSet {
     bool in_use = false, mv_pending = false;
 };
 
+// A pinned host block handed out by vvcb200_ctx_arena_alloc with one device mirror per stage set: a batch array that lies
+// in it is uploaded to the same offset of the current set's mirror, and the uploads of one stage call that lie next to
+// each other travel as ONE copy.  (Measured: with a picture download running, every additional upload of a picture costs
+// about 10 us of link time whatever its size — fifteen uploads per picture made the end-to-end loop 0.72 ms, one 0.52.)
+struct Arena {
+    uint8_t *host = nullptr;
+    size_t bytes = 0;
+    uint8_t *mirror[4] = { nullptr, nullptr, nullptr, nullptr };   // kSets
+};
+struct PendingCopy { int arena; size_t lo, hi; };
+
 struct VVCB200Ctx {
+    std::vector<Arena> arenas;
+    std::vector<PendingCopy> pending;  // arena ranges the current stage call wants on the device
     int device = 0;
     int width = 0, height = 0, bit_depth = 10, hshift = 1, vshift = 1;
     cudaStream_t h2d = nullptr;        // descriptor uploads
@@ -141,8 +159,28 @@ DevPicture *slot_of(VVCB200Ctx *c, int slot)
 
 // Host -> device copy of a descriptor batch on the upload stream.  A buffer that has to grow is only reallocated after
 // the kernels still reading its set have finished (cudaFree would wait for them anyway, but on the whole device).
+// host range inside an arena: remember it for the merged copy, hand out its place in the current set's mirror
+static void *arena_place(VVCB200Ctx *c, const void *host, size_t bytes)
+{
+    const uint8_t *h = (const uint8_t *)host;
+    for (size_t i = 0; i < c->arenas.size(); i++) {
+        const Arena &a = c->arenas[i];
+        if (h >= a.host && h + bytes <= a.host + a.bytes) {
+            const size_t lo = (size_t)(h - a.host);
+            if (bytes)
+                c->pending.push_back({ (int)i, lo, lo + bytes });
+            return a.mirror[c->set] + lo;
+        }
+    }
+    return nullptr;
+}
+
 int upload(VVCB200Ctx *c, DevBuffer &b, const void *host, size_t bytes)
 {
+    if (void *d = arena_place(c, host, bytes)) {
+        b.p = d;
+        return 0;
+    }
     if (bytes > b.cap) {
         VVC_CUDA(cudaStreamSynchronize(lane_stream(c)));
         VVC_CUDA(cudaStreamSynchronize(c->h2d));
@@ -157,6 +195,27 @@ int upload(VVCB200Ctx *c, DevBuffer &b, const void *host, size_t bytes)
 int uploads_visible(VVCB200Ctx *c)
 {
     StageSet &s = c->sets[c->set];
+    if (!c->pending.empty()) {
+        // neighbouring ranges as one copy; a gap of up to 64 KiB goes along (its bytes land in the mirror and mean nothing)
+        std::sort(c->pending.begin(), c->pending.end(), [](const PendingCopy &x, const PendingCopy &y) {
+            return x.arena != y.arena ? x.arena < y.arena : x.lo < y.lo;
+        });
+        size_t i = 0;
+        while (i < c->pending.size()) {
+            PendingCopy m = c->pending[i++];
+            while (i < c->pending.size() && c->pending[i].arena == m.arena && c->pending[i].lo <= m.hi + 65536) {
+                m.hi = std::max(m.hi, c->pending[i].hi);
+                i++;
+            }
+            const Arena &a = c->arenas[m.arena];
+            const cudaError_t e = cudaMemcpyAsync(a.mirror[c->set] + m.lo, a.host + m.lo, m.hi - m.lo, cudaMemcpyHostToDevice, c->h2d);
+            if (e != cudaSuccess) {
+                c->pending.clear();
+                VVC_CUDA(e);
+            }
+        }
+        c->pending.clear();
+    }
     VVC_CUDA(cudaEventRecord(s.uploaded, c->h2d));
     VVC_CUDA(cudaStreamWaitEvent(s.lane->stream, s.uploaded, 0));
     return 0;
@@ -372,6 +431,13 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
         if (l.scratch.base) cudaFree(l.scratch.base);
         if (l.residual.base) cudaFree(l.residual.base);
     }
+    for (Arena &a : c->arenas) {
+        for (uint8_t *m : a.mirror)
+            if (m)
+                cudaFree(m);
+        if (a.host)
+            cudaFreeHost(a.host);
+    }
     for (cudaEvent_t ev : c->downloaded)
         if (ev)
             cudaEventDestroy(ev);
@@ -436,6 +502,32 @@ int vvcb200_ctx_planes(VVCB200Ctx *c, int slot, VVCB200Planes *out)
     }
     *out = p->planes;
     return 0;
+}
+
+void *vvcb200_ctx_arena_alloc(VVCB200Ctx *c, size_t bytes)
+{
+    if (!c || !bytes) {
+        set_error("vvcb200_ctx_arena_alloc: bad argument");
+        return nullptr;
+    }
+    DeviceGuard g(c->device);
+    Arena a;
+    a.bytes = (bytes + 255) & ~(size_t)255;
+    bool ok = cudaHostAlloc((void **)&a.host, a.bytes, cudaHostAllocDefault) == cudaSuccess;
+    for (int i = 0; ok && i < kSets; i++)
+        ok = cudaMalloc((void **)&a.mirror[i], a.bytes) == cudaSuccess;
+    if (!ok) {
+        set_error("vvcb200_ctx_arena_alloc: %zu bytes of pinned host memory + %d device mirrors: %s", a.bytes, kSets,
+                  cudaGetErrorString(cudaGetLastError()));
+        for (uint8_t *m : a.mirror)
+            if (m)
+                cudaFree(m);
+        if (a.host)
+            cudaFreeHost(a.host);
+        return nullptr;
+    }
+    c->arenas.push_back(a);
+    return a.host;
 }
 
 void *vvcb200_host_alloc(size_t bytes)
@@ -511,9 +603,25 @@ int vvcb200_pic_download(VVCB200Ctx *c, int slot, uint16_t *const planes[3], con
     }
     if (c->writer[idx] >= 0)              // whatever wrote the slot last, in whichever lane
         VVC_CUDA(cudaStreamWaitEvent(c->d2h, c->written[idx], 0));
-    for (int i = 0; i < 3; i++)
-        VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
-                                   (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->d2h));
+    // a frame whose three planes lie back to back in host memory exactly as they do on the device leaves as one copy
+    bool one = true;
+    for (int i = 0; i < 3; i++) {
+        const size_t row = (size_t)p->planes.width[i] * 2, plane = row * p->planes.height[i];
+        one = one && (size_t)p->planes.stride[i] == row && (size_t)strides[i] == row;
+        if (i < 2)
+            one = one && (uint8_t *)p->planes.d_plane[i + 1] == (uint8_t *)p->planes.d_plane[i] + plane &&
+                  (uint8_t *)planes[i + 1] == (uint8_t *)planes[i] + plane;
+    }
+    if (one) {
+        size_t total = 0;
+        for (int i = 0; i < 3; i++)
+            total += (size_t)p->planes.width[i] * 2 * p->planes.height[i];
+        VVC_CUDA(cudaMemcpyAsync(planes[0], p->planes.d_plane[0], total, cudaMemcpyDeviceToHost, c->d2h));
+    } else {
+        for (int i = 0; i < 3; i++)
+            VVC_CUDA(cudaMemcpy2DAsync(planes[i], strides[i], p->planes.d_plane[i], p->planes.stride[i],
+                                       (size_t)p->planes.width[i] * 2, p->planes.height[i], cudaMemcpyDeviceToHost, c->d2h));
+    }
     VVC_CUDA(cudaEventRecord(c->downloaded[idx], c->d2h));
     c->download_pending[idx] = 1;
     return 0;
@@ -902,8 +1010,12 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
                 set_error("vvcb200_pic_deblock: missing edge table");
                 return VVCB200_ERR_ARG;
             }
-            VVC_CUDA(cudaMemcpyAsync(d, t->d_edge[dir][k], units, cudaMemcpyHostToDevice, c->h2d));
-            dt.d_edge[dir][k] = d;
+            if (void *m = arena_place(c, t->d_edge[dir][k], units)) {
+                dt.d_edge[dir][k] = (const uint8_t *)m;
+            } else {
+                VVC_CUDA(cudaMemcpyAsync(d, t->d_edge[dir][k], units, cudaMemcpyHostToDevice, c->h2d));
+                dt.d_edge[dir][k] = d;
+            }
             d += units;
         }
     for (int k = 0; k < 3; k++) {
@@ -911,12 +1023,20 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
             set_error("vvcb200_pic_deblock: missing qp table");
             return VVCB200_ERR_ARG;
         }
-        VVC_CUDA(cudaMemcpyAsync(d, t->d_qp[k], units, cudaMemcpyHostToDevice, c->h2d));
-        dt.d_qp[k] = (const int8_t *)d;
+        if (void *m = arena_place(c, t->d_qp[k], units)) {
+            dt.d_qp[k] = (const int8_t *)m;
+        } else {
+            VVC_CUDA(cudaMemcpyAsync(d, t->d_qp[k], units, cudaMemcpyHostToDevice, c->h2d));
+            dt.d_qp[k] = (const int8_t *)d;
+        }
         d += units;
     }
-    VVC_CUDA(cudaMemcpyAsync(d, t->d_ctb_offsets, n_ctb * 6, cudaMemcpyHostToDevice, c->h2d));
-    dt.d_ctb_offsets = (const int8_t *)d;
+    if (void *m = arena_place(c, t->d_ctb_offsets, n_ctb * 6)) {
+        dt.d_ctb_offsets = (const int8_t *)m;
+    } else {
+        VVC_CUDA(cudaMemcpyAsync(d, t->d_ctb_offsets, n_ctb * 6, cudaMemcpyHostToDevice, c->h2d));
+        dt.d_ctb_offsets = (const int8_t *)d;
+    }
     if (int r = uploads_visible(c))
         return r;
     if (c->in_scratch)                    // a second deblocking call for this picture: start from its DPB buffer again

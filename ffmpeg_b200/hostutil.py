@@ -34,14 +34,24 @@ def from_device_planes(tensors):
 class EnginePicture:
     """Pinned host copies of one picture's batches + the Level-B call sequence (HOST buffers in, HOST planes out)."""
 
-    def __init__(self, ctx, pic, max_slots=4, want_mv=True, sparse_levels="auto"):
+    def __init__(self, ctx, pic, max_slots=4, want_mv=True, sparse_levels="auto", arena=True):
         it, rs, db, lf = pic["inter"], pic["residual"], pic["deblock"], pic["lf"]
         self.ctx, self.pic = ctx, pic
         self.n_refs = len(it["refs"])
         self.refs = [[ctx.pinned_copy(np.ascontiguousarray(p)) for p in r] for r in it["refs"]]
-        self.blocks = ctx.pinned_copy(it["blocks"])
+        # the picture's batches in ONE pinned block the context mirrors on the device, laid out in call order: the arrays of
+        # a stage call then travel as one copy (vvcb200_ctx_arena_alloc); arena=False: one pinned allocation per array
+        self.arena = None
+        if arena:
+            ar = self.arena = ctx.arena(self._arena_bytes(pic))
+            put = ar.copy
+        else:
+            put = ctx.pinned_copy
+        self.blocks = put(it["blocks"])
         prof = it.get("prof")
-        self.prof = ctx.pinned_copy(prof) if prof is not None and len(prof) else None
+        self.prof = put(prof) if prof is not None and len(prof) else None
+        luts = None if pic["lmcs"] is None else pic["lmcs"]
+        lut_fwd = put(luts[0]) if luts is not None else None
         # levels travel as dense scan boxes or in the sparse form (bitmap + non-zero values), whichever is smaller for the
         # picture (the synthetic pictures fill their scan boxes to 95 %, real residuals to a third or less)
         self.res_params = rs["params"]
@@ -55,22 +65,22 @@ class EnginePicture:
                 self.res_params = lib.sparse_params(rs["params"])
             else:
                 levels, tbs = d_levels, d_tbs
-        self.levels = ctx.pinned_copy(levels)
-        self.tbs = ctx.pinned_copy(tbs)
-        edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
-        self.edge = ctx.pinned_copy(edge)
-        self.qp = ctx.pinned_copy(db["qp"])
-        self.ctb_offsets = ctx.pinned_copy(db["ctb_offsets"])
-        self.sao = ctx.pinned_copy(lf["sao"])
-        self.alf = ctx.pinned_copy(lf["alf"])
-        self.alf_params = ctx.pinned_copy(lf["alf_params"])
+        self.levels = put(levels)
+        self.tbs = put(tbs)
         ia = pic.get("intra")
         self.intra = None
         if ia is not None and len(ia["blocks"]):
             ctb = pic["ctb_log2"]
-            self.intra = (ctx.pinned_copy(ia["blocks"]), ctx.pinned_copy(ia["ctu_first"]),
+            self.intra = (put(ia["blocks"]), put(ia["ctu_first"]),
                           (pic["width"] + (1 << ctb) - 1) >> ctb, (pic["height"] + (1 << ctb) - 1) >> ctb, ia["params"])
-        self.luts = None if pic["lmcs"] is None else [ctx.pinned_copy(l) for l in pic["lmcs"]]
+        self.luts = None if luts is None else [lut_fwd, put(luts[1])]
+        edge = lib.pack_deblock_edges(db["bs"], db["len_p"], db["len_q"], db["tb_w_c"], db["tb_h_c"], pic["ctb_log2"])
+        self.edge = put(edge)
+        self.qp = put(db["qp"])
+        self.ctb_offsets = put(db["ctb_offsets"])
+        self.sao = put(lf["sao"])
+        self.alf = put(lf["alf"])
+        self.alf_params = put(lf["alf_params"])
         # pictures are reconstructed into the slots after the references (ref_slot[][] already maps to 0..n_refs-1),
         # rotating over up to four slots / host frames when the context has them, as consecutive pictures of a decoder
         # do: the download of one picture then overlaps the reconstruction of the next ones (two compute lanes)
@@ -78,9 +88,24 @@ class EnginePicture:
         self.refined = [ctx.pinned((max(len(it["blocks"]), 1), 2, 2), np.int32) for _ in range(4)]
         self.want_mv = want_mv
         self.n_slots = max(1, min(max_slots, ctx.dpb_size - self.n_refs))
-        self.outs = [ctx.pinned_planes() for _ in range(self.n_slots)]
+        self.outs = [ctx.pinned_frame() for _ in range(self.n_slots)]
         self.count = 0
         self.out = self.outs[0]
+
+    @staticmethod
+    def _arena_bytes(pic):
+        """Room for every batch array of the picture (the level buffer at its dense size: the packed forms are smaller)."""
+        total = 0
+        for a in (pic["inter"]["blocks"], pic["inter"].get("prof"), pic["residual"]["levels"], pic["residual"]["tbs"],
+                  pic["deblock"]["qp"], pic["deblock"]["ctb_offsets"], pic["lf"]["sao"], pic["lf"]["alf"], pic["lf"]["alf_params"]):
+            total += 0 if a is None else a.nbytes + 256
+        total += 6 * pic["deblock"]["qp"][0].nbytes + 256                       # the packed edge tables
+        total += pic["residual"]["levels"].nbytes // 16 + 8 * len(pic["residual"]["tbs"]) + 1024   # sparse form's worst case
+        if pic.get("intra") is not None:
+            total += pic["intra"]["blocks"].nbytes + pic["intra"]["ctu_first"].nbytes + 512
+        if pic["lmcs"] is not None:
+            total += sum(l.nbytes + 256 for l in pic["lmcs"])
+        return total + 4096
 
     def h2d_bytes(self):
         intra = 0 if self.intra is None else self.intra[0].nbytes + self.intra[1].nbytes

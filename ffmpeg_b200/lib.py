@@ -181,6 +181,27 @@ def intra_picture_static(pic, residual, blocks, n, params, stream=None):
 
 
 # ---- Level B: picture engine ---------------------------------------------------------------------------
+class Arena:
+    """Bump allocator over a block from Context.arena()."""
+
+    def __init__(self, base, nbytes):
+        self.base, self.nbytes, self.used = base, nbytes, 0
+
+    def take(self, shape, dtype):
+        n = int(np.prod(shape)) * np.dtype(dtype).itemsize
+        off = (self.used + 255) & ~255
+        if off + n > self.nbytes:
+            raise VVCB200Error("arena of %d bytes is full" % self.nbytes)
+        self.used = off + n
+        buf = (C.c_uint8 * max(n, 1)).from_address(self.base + off)
+        return np.frombuffer(buf, dtype=np.uint8, count=n).view(dtype).reshape(shape)
+
+    def copy(self, a):
+        out = self.take(a.shape, a.dtype)
+        out[...] = a
+        return out
+
+
 class Context:
     """VVCB200Ctx wrapper: one per GPU per stream of pictures.  Host buffers are numpy arrays; use
     pinned() to allocate page-locked ones (needed for asynchronous copies)."""
@@ -219,6 +240,23 @@ class Context:
         self._pinned.append(p)
         buf = (C.c_uint8 * max(n, 1)).from_address(p)
         return np.frombuffer(buf, dtype=np.uint8, count=n).view(dtype).reshape(shape)
+
+    def arena(self, nbytes):
+        """vvcb200_ctx_arena_alloc: a pinned block mirrored on the device (freed with the context); returns an Arena whose
+        take() / copy() carve 256-byte aligned numpy arrays out of it in call order."""
+        l = load()
+        l.vvcb200_ctx_arena_alloc.restype = C.c_void_p
+        p = l.vvcb200_ctx_arena_alloc(self._h, C.c_size_t(int(nbytes)))
+        if not p:
+            raise VVCB200Error(l.vvcb200_last_error().decode())
+        return Arena(p, int(nbytes))
+
+    def pinned_frame(self):
+        """The three planes of a 4:2:0 frame back to back in ONE pinned allocation (a download is then one copy)."""
+        w, h = self.width, self.height
+        flat = self.pinned((w * h * 3 // 2,), np.uint16)
+        y, cb = flat[:w * h].reshape(h, w), flat[w * h:w * h * 5 // 4].reshape(h // 2, w // 2)
+        return [y, cb, flat[w * h * 5 // 4:].reshape(h // 2, w // 2)]
 
     def pinned_copy(self, a):
         out = self.pinned(a.shape, a.dtype)

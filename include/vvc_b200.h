@@ -586,6 +586,15 @@ VVCB200_API void *vvcb200_ctx_stream(VVCB200Ctx *ctx);
 VVCB200_API int  vvcb200_ctx_planes(VVCB200Ctx *ctx, int slot, VVCB200Planes *out);
 
 /* Pinned host memory for descriptor batches and frames. */
+/* A pinned host block (256-byte aligned, freed with the context) that the context mirrors on the device, once per
+ * descriptor set.  Batch arrays the caller carves out of it are uploaded to the same offset of the mirror, and the arrays of
+ * one stage call that lie next to each other (gaps up to 64 KiB) travel as ONE copy: lay a picture's arrays out in call
+ * order, stage by stage.  It pays: with a picture download in flight every additional upload costs ~10 us of link time
+ * whatever its size, and a 4K picture has fifteen.  Arrays elsewhere in host memory keep working, one copy each.  The rule
+ * for host batches holds (valid and unchanged until the copy has happened: vvcb200_ctx_sync()): one region per picture
+ * in flight.
+ * Allocates (host + four device blocks of `bytes`): call it at set-up time, not between pictures. */
+VVCB200_API void *vvcb200_ctx_arena_alloc(VVCB200Ctx *ctx, size_t bytes);
 VVCB200_API void *vvcb200_host_alloc(size_t bytes);
 VVCB200_API void  vvcb200_host_free(void *p);
 

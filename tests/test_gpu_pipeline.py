@@ -66,6 +66,26 @@ def test_picture_from_emitted_descriptors_md5(seed, w, h, ctb, lmcs, ns, lfase):
         ctx.close()
 
 
+def test_batches_in_an_arena_and_in_separate_allocations_give_the_same_picture():
+    """vvcb200_ctx_arena_alloc: batch arrays carved out of the mirrored pinned block travel as one copy per stage call;
+    arrays in allocations of their own (one copy each, the engine's own device buffers) must reconstruct the same picture,
+    and the two kinds may alternate on one context."""
+    w, h = 416, 240
+    pic = synth.full_picture(61, w, h, ctb_log2=6, lmcs=True, intra_fraction=0.3)
+    want = util.plane_md5(pipeline.oracle_picture(pic))
+    ctx = lib.Context(0, w, h, dpb_size=4)
+    try:
+        eps = [pipeline.EnginePicture(ctx, pic, arena=True), pipeline.EnginePicture(ctx, pic, arena=False)]
+        eps[0].upload_refs()
+        for i in range(6):
+            ep = eps[i % 2]
+            ep.run()
+            ctx.sync()
+            assert util.plane_md5(ep.out) == want, "picture %d (%s)" % (i, "arena" if i % 2 == 0 else "separate allocations")
+    finally:
+        ctx.close()
+
+
 def test_refined_vectors_come_back_for_the_dmvr_records():
     """Level B returns the vectors DMVR settled on (the reference's tab_dmvr_mvf, vvc_inter.c:750-762).  A batch in the
     recommended order (dmvr_first) gets them for the DMVR records only, the other entries stay as the host left them."""
