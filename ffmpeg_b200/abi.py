@@ -221,8 +221,8 @@ assert IB_DTYPE.itemsize == 28
 class IntraParams(C.Structure):
     _fields_ = [("bit_depth", C.c_int32), ("ctb_log2_size", C.c_int32), ("chroma_vertical_collocated", C.c_int32),
                 ("lmcs_chroma_scale", C.c_int32), ("lmcs_pivot", C.c_uint16 * 17), ("lmcs_chroma_scale_coeff", C.c_uint16 * 16),
-                ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("pad", C.c_uint8 * 4),
-                ("n_luma", C.c_int32), ("n_add_only", C.c_int32), ("d_phase_counts", C.c_void_p)]
+                ("lmcs_min_bin_idx", C.c_uint8), ("lmcs_max_bin_idx", C.c_uint8), ("prepared", C.c_uint8), ("pad", C.c_uint8 * 3),
+                ("n_luma", C.c_int32), ("n_add_only", C.c_int32), ("d_phase_counts", C.c_void_p), ("luma_done_event", C.c_void_p)]
 
 
 class Window(C.Structure):

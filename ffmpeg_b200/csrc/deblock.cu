@@ -650,7 +650,14 @@ extern "C" int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVCB
                                             const VVCB200DeblockTables *t, const VVCB200DeblockParams *p,
                                             const uint16_t *d_inv_lut, void *stream)
 {
-    if (!dst || !src || !t || !p || t->stride4 <= 0 || !t->d_ctb_offsets) {
+    return vvcb200_deblock_lmcs_planes(dst, src, t, p, d_inv_lut, 3, stream);
+}
+
+extern "C" int vvcb200_deblock_lmcs_planes(const VVCB200Planes *dst, const VVCB200Planes *src,
+                                           const VVCB200DeblockTables *t, const VVCB200DeblockParams *p,
+                                           const uint16_t *d_inv_lut, int planes, void *stream)
+{
+    if (!dst || !src || !t || !p || t->stride4 <= 0 || !t->d_ctb_offsets || planes < 1 || planes > 3) {
         set_error("vvcb200_deblock_lmcs_picture: bad argument");
         return VVCB200_ERR_ARG;
     }
@@ -687,22 +694,26 @@ extern "C" int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVCB
     }
     // luma and the two chroma planes are independent grids: side by side
     const cudaStream_t main_stream = (cudaStream_t)stream;
-    ForkStreams *f = fork_streams(main_stream);
+    ForkStreams *f = planes == 3 ? fork_streams(main_stream) : nullptr;
     cudaStream_t side = main_stream;
     if (f) {
         VVC_CUDA(cudaEventRecord(f->fork, main_stream));
         side = f->side[0];
         VVC_CUDA(cudaStreamWaitEvent(side, f->fork, 0));
     }
-    dim3 gl((src->width[0] + kDT - 1) / kDT, (src->height[0] + kDT - 1) / kDT, 1);
-    if (d_inv_lut)
-        deblock_tile_kernel<false, true><<<gl, kDThreads, 0, main_stream>>>(a);
-    else
-        deblock_tile_kernel<false, false><<<gl, kDThreads, 0, main_stream>>>(a);
-    VVC_LAUNCH_CHECK();
-    dim3 gc((src->width[1] + kDT - 1) / kDT, (src->height[1] + kDT - 1) / kDT, 2);
-    deblock_tile_kernel<true, false><<<gc, kDThreads, 0, side>>>(a);
-    VVC_LAUNCH_CHECK();
+    if (planes & 1) {
+        dim3 gl((src->width[0] + kDT - 1) / kDT, (src->height[0] + kDT - 1) / kDT, 1);
+        if (d_inv_lut)
+            deblock_tile_kernel<false, true><<<gl, kDThreads, 0, main_stream>>>(a);
+        else
+            deblock_tile_kernel<false, false><<<gl, kDThreads, 0, main_stream>>>(a);
+        VVC_LAUNCH_CHECK();
+    }
+    if (planes & 2) {
+        dim3 gc((src->width[1] + kDT - 1) / kDT, (src->height[1] + kDT - 1) / kDT, 2);
+        deblock_tile_kernel<true, false><<<gc, kDThreads, 0, side>>>(a);
+        VVC_LAUNCH_CHECK();
+    }
     if (f) {
         VVC_CUDA(cudaEventRecord(f->join[0], side));
         VVC_CUDA(cudaStreamWaitEvent(main_stream, f->join[0], 0));

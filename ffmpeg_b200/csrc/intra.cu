@@ -1743,9 +1743,12 @@ extern "C" int vvcb200_intra_schedule(const VVCB200IntraBlock *in, const uint32_
     return 0;
 }
 
-extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual, const VVCB200Planes *d_shadow,
-                                     const VVCB200IntraBlock *d_blocks, int n, const VVCB200IntraParams *params,
-                                     void *d_scratch, void *stream)
+// what: bit 0 = the pre-pass (scratch cleared, sentinels, in-place predictions moved to the shadow picture), bit 1 = the
+// wavefronts.  The pre-pass needs the inter prediction only, not the residual stage: a caller that issues it on a stream of
+// its own (vvcb200_intra_prepare) lets it run beside the residual kernels.
+static int intra_impl(const VVCB200Planes *pic, const VVCB200Planes *d_residual, const VVCB200Planes *d_shadow,
+                      const VVCB200IntraBlock *d_blocks, int n, const VVCB200IntraParams *params, void *d_scratch, void *stream,
+                      int what)
 {
     if (!pic || !params || n < 0 || (n && (!d_blocks || !d_scratch))) {
         set_error("vvcb200_intra_picture: bad arguments");
@@ -1821,14 +1824,20 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     a.vpdu_scale = nullptr;
     a.vpdu_pitch = l.vpdu_pitch;
     cudaStream_t s = (cudaStream_t)stream;
-    // ticket counters and in-place flag; the marks too unless a shadow picture makes them unnecessary
-    VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.marks_total, s));
-    if (phased && params->lmcs_chroma_scale) {
+    if (phased && params->lmcs_chroma_scale)
         a.vpdu_scale = (unsigned *)((uint8_t *)d_scratch + l.vpdu_off);
-        VVC_CUDA(cudaMemsetAsync(a.vpdu_scale, 0, l.total - l.vpdu_off, s));
+    if (what & 1) {
+        // ticket counters and in-place flag; the marks too unless a shadow picture makes them unnecessary
+        VVC_CUDA(cudaMemsetAsync(d_scratch, 0, d_shadow ? 256 : l.marks_total, s));
+        if (a.vpdu_scale)
+            VVC_CUDA(cudaMemsetAsync(a.vpdu_scale, 0, l.total - l.vpdu_off, s));
+        intra_mark_kernel<<<(n + 128 / kMarkLanes - 1) / (128 / kMarkLanes), 128, 0, s>>>(a);
+        VVC_LAUNCH_CHECK();
     }
-    intra_mark_kernel<<<(n + 128 / kMarkLanes - 1) / (128 / kMarkLanes), 128, 0, s>>>(a);
-    VVC_LAUNCH_CHECK();
+    if (!(what & 2))
+        return 0;
+    // luma is final once the luma wavefront (or the only wavefront) has run: the event a caller may have asked for
+    cudaEvent_t luma_done = (cudaEvent_t)params->luma_done_event;
     // Pictures with scattered intra units are bound by the number of records in flight and take every warp the SM holds;
     // pictures that are mostly intra are bound by their dependency chains, where more pollers only lengthen a step
     // (4K all-intra: 4.4 ms with 12 warps per SM, 4.8 ms with 16; random access: 2 % the other way).
@@ -1874,12 +1883,19 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         return 0;
     };
     const bool scale = params->lmcs_chroma_scale != 0;
-    if (!phased)
-        return wavefront(0, n, 0, scale, 0);
+    if (!phased) {
+        if (int r = wavefront(0, n, 0, scale, 0))
+            return r;
+        if (luma_done)
+            VVC_CUDA(cudaEventRecord(luma_done, s));
+        return 0;
+    }
     if (d_counts) {
         // the ranges live on the device: every launch is sized for all n records and takes its own share
         if (int r = wavefront(0, n, 0, false, kPhaseLuma))
             return r;
+        if (luma_done)
+            VVC_CUDA(cudaEventRecord(luma_done, s));
         IntraArgs w = a;
         w.n = n;
         if (a.vpdu_scale) {
@@ -1894,6 +1910,8 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
     }
     if (int r = wavefront(0, n_luma, 0, false, 0))                        // luma records never carry the chroma scale
         return r;
+    if (luma_done)
+        VVC_CUDA(cudaEventRecord(luma_done, s));
     if (a.vpdu_scale && n > n_luma) {                                     // every chroma record's VPDU factor, once
         IntraArgs w = a;
         w.blocks = all + n_luma;
@@ -1909,6 +1927,22 @@ extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Plan
         VVC_LAUNCH_CHECK();
     }
     return wavefront(n_luma + n_add, n - n_luma - n_add, 2, scale, 0);
+}
+
+extern "C" int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual, const VVCB200Planes *d_shadow,
+                                     const VVCB200IntraBlock *d_blocks, int n, const VVCB200IntraParams *params,
+                                     void *d_scratch, void *stream)
+{
+    if (params && !n && params->luma_done_event)                          // nothing to do, but the caller waits for the event
+        VVC_CUDA(cudaEventRecord((cudaEvent_t)params->luma_done_event, (cudaStream_t)stream));
+    return intra_impl(pic, d_residual, d_shadow, d_blocks, n, params, d_scratch, stream, params && params->prepared ? 2 : 3);
+}
+
+extern "C" int vvcb200_intra_prepare(const VVCB200Planes *pic, const VVCB200Planes *d_residual, const VVCB200Planes *d_shadow,
+                                     const VVCB200IntraBlock *d_blocks, int n, const VVCB200IntraParams *params,
+                                     void *d_scratch, void *stream)
+{
+    return intra_impl(pic, d_residual, d_shadow, d_blocks, n, params, d_scratch, stream, 1);
 }
 
 extern "C" size_t vvcb200_intra_schedule_scratch_bytes(int n, int ctus_w, int ctus_h)

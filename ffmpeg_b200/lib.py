@@ -174,6 +174,13 @@ def intra_picture(pic, residual, blocks, n, params, scratch, stream=None, shadow
                                        _ptr(blocks), int(n), C.byref(params), _ptr(scratch), _stream(stream)))
 
 
+def intra_prepare(pic, residual, blocks, n, params, scratch, stream=None, shadow=None):
+    """vvcb200_intra_prepare: the pre-pass of intra_picture alone (then call intra_picture with params.prepared = 1)."""
+    check(load().vvcb200_intra_prepare(C.byref(pic), C.byref(residual) if residual is not None else None,
+                                       C.byref(shadow) if shadow is not None else None,
+                                       _ptr(blocks), int(n), C.byref(params), _ptr(scratch), _stream(stream)))
+
+
 def intra_picture_static(pic, residual, blocks, n, params, stream=None):
     """vvcb200_intra_picture_static: as intra_picture, marks in the library's built-in scratch (<= 1920x1088)."""
     check(load().vvcb200_intra_picture_static(C.byref(pic), C.byref(residual) if residual is not None else None,
@@ -396,6 +403,12 @@ def deblock_lmcs_picture(dst, src, tables, params, inv_lut=None, stream=None):
     """vvcb200_deblock_lmcs_picture: both deblocking passes (and the inverse LMCS mapping of luma) in one out-of-place pass."""
     check(load().vvcb200_deblock_lmcs_picture(C.byref(dst), C.byref(src), C.byref(tables), C.byref(params), _ptr(inv_lut),
                                               _stream(stream)))
+
+
+def deblock_lmcs_planes(dst, src, tables, params, inv_lut=None, planes=3, stream=None):
+    """vvcb200_deblock_lmcs_planes: the tile pass for luma (1), chroma (2) or all planes (3)."""
+    check(load().vvcb200_deblock_lmcs_planes(C.byref(dst), C.byref(src), C.byref(tables), C.byref(params), _ptr(inv_lut),
+                                             int(planes), _stream(stream)))
 
 
 def sao_picture(dst, src, ctbs, ctb_log2, bit_depth=10, stream=None):

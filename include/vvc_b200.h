@@ -345,6 +345,14 @@ VVCB200_API int vvcb200_deblock_lmcs_picture(const VVCB200Planes *dst, const VVC
                                              const VVCB200DeblockTables *tables /* host struct */,
                                              const VVCB200DeblockParams *params /* host */,
                                              const uint16_t *d_inv_lut /* 1 << bit_depth entries, or NULL */, void *stream);
+/* The same pass for luma alone (planes = 1), the two chroma planes alone (2) or all three (3): luma depends on luma only
+ * (its QP, its LADF levels, its edges), so the luma half may start as soon as luma is final (VVCB200IntraParams.
+ * luma_done_event) while the chroma phases of the intra stage still run. */
+VVCB200_API int vvcb200_deblock_lmcs_planes(const VVCB200Planes *dst, const VVCB200Planes *src,
+                                            const VVCB200DeblockTables *tables /* host struct */,
+                                            const VVCB200DeblockParams *params /* host */,
+                                            const uint16_t *d_inv_lut /* 1 << bit_depth entries, or NULL */, int planes,
+                                            void *stream);
 
 /* ------------------------------------------------------------------------------------------------
  * SAO and ALF (stages SAO / ALF, ff_vvc_sao_filter vvc_filter.c:154-298, ff_vvc_alf_filter 1254-1319;
@@ -475,7 +483,9 @@ typedef struct VVCB200IntraParams {
     uint16_t lmcs_pivot[17];
     uint16_t lmcs_chroma_scale_coeff[16];
     uint8_t  lmcs_min_bin_idx, lmcs_max_bin_idx;
-    uint8_t  pad[4];
+    uint8_t  prepared;                    /* vvcb200_intra_prepare has been issued for this picture (and is ordered before
+                                             this call): vvcb200_intra_picture then starts with the wavefronts             */
+    uint8_t  pad[3];
     /* Phases (vvcb200_intra_schedule with `phase_counts`): records [0, n_luma) are the luma records, the next n_add_only
      * the chroma VVCB200_IB_ADD_ONLY records, the rest the other chroma records.  Chroma never feeds luma, and an add-only
      * record depends on luma alone, so the three groups run as luma wavefront -> plain batch -> chroma wavefront: the
@@ -485,7 +495,11 @@ typedef struct VVCB200IntraParams {
     /* Alternatively the counts in DEVICE memory, as vvcb200_intra_schedule_device leaves them (three int32: luma, add-only,
      * other chroma); non-NULL: n_luma / n_add_only are ignored and every launch reads its range there. */
     const int32_t *d_phase_counts;
-} VVCB200IntraParams;           /* 104 bytes */
+    /* cudaEvent_t or NULL: recorded on the call's stream as soon as every luma sample of the picture is final (after the
+     * luma wavefront; after the only wavefront when the records are not phased).  What works on luma alone — the luma
+     * half of the deblocking pass — need not wait for the chroma phases. */
+    void *luma_done_event;
+} VVCB200IntraParams;           /* 112 bytes */
 
 /*
  * Reconstruction of the intra blocks of one picture, in place on `pic` (which already holds the inter prediction +
@@ -544,6 +558,13 @@ VVCB200_API int vvcb200_intra_schedule_device(const VVCB200IntraBlock *d_in, con
                                               int ctus_h, VVCB200IntraBlock *d_out, int32_t *d_phase_counts, void *d_scratch,
                                               void *stream);
 VVCB200_API int vvcb200_intra_picture(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
+                                      const VVCB200Planes *d_shadow, const VVCB200IntraBlock *d_blocks, int n,
+                                      const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);
+/* The first part of vvcb200_intra_picture alone (same arguments): scratch cleared, sentinels written, the predictions of
+ * blocks rewritten in place moved to the shadow picture.  It needs the inter prediction but not the residual stage, so a
+ * caller may issue it on a second stream beside vvcb200_residual_batch and then call vvcb200_intra_picture with
+ * params->prepared = 1 (ordered after both). */
+VVCB200_API int vvcb200_intra_prepare(const VVCB200Planes *pic, const VVCB200Planes *d_residual,
                                       const VVCB200Planes *d_shadow, const VVCB200IntraBlock *d_blocks, int n,
                                       const VVCB200IntraParams *params /* host */, void *d_scratch, void *stream);
 

@@ -116,3 +116,23 @@ def test_device_derived_edges_match_the_reference_and_filter_the_same_picture(se
         refapi.deblock_picture(ref_pic, t)
         for fused in (False, True):
             assert util.plane_md5(gpu_deblock(base, t, got, fused)) == util.plane_md5(ref_pic)
+
+
+def test_luma_and_chroma_halves_of_the_tile_pass_equal_the_whole():
+    """vvcb200_deblock_lmcs_planes: luma alone (which may start when luma is final) + chroma alone = the picture call."""
+    import torch
+    seed, w, h, ctb = 47, 832, 480, 7
+    t = synth.deblock_picture(seed, w, h, ctb_log2=ctb)
+    base = synth.smooth_planes(seed, t["dims"])
+    edge = lib.pack_deblock_edges(t["bs"], t["len_p"], t["len_q"], t["tb_w_c"], t["tb_h_c"], ctb)
+    whole = gpu_deblock(base, t, edge, fused=True)
+    src = util.to_device_planes(base, torch)
+    dst = [torch.zeros_like(p) for p in src]
+    d_edge, d_qp, d_off = torch.from_numpy(edge).cuda(), torch.from_numpy(t["qp"]).cuda(), torch.from_numpy(t["ctb_offsets"]).cuda()
+    tabs = lib.deblock_tables(d_edge, d_qp, d_off, t["stride4"])
+    second = torch.cuda.Stream()
+    second.wait_stream(torch.cuda.current_stream())
+    lib.deblock_lmcs_planes(lib.device_planes(dst), lib.device_planes(src), tabs, t["params"], planes=1, stream=second.cuda_stream)
+    lib.deblock_lmcs_planes(lib.device_planes(dst), lib.device_planes(src), tabs, t["params"], planes=2)
+    torch.cuda.synchronize()
+    assert util.plane_md5(util.from_device_planes(dst)) == util.plane_md5(whole)

@@ -242,3 +242,62 @@ def test_uncoded_isp_partitions_add_nothing_whatever_the_residual_planes_hold(se
         got = run_gpu(pic, shadow=shadow, phased=phased, stale_residual=True)[0]
         for c in range(3):
             assert np.array_equal(got[c], want[c]), "plane %d differs (shadow %s)" % (c, shadow)
+
+
+@pytest.mark.parametrize("shadow,phased", [(True, True), (False, True), (True, False)])
+def test_pre_pass_beside_the_residual_stage_and_the_luma_done_event(shadow, phased):
+    """vvcb200_intra_prepare on a second stream before / beside vvcb200_residual_batch, then vvcb200_intra_picture with
+    params.prepared: same picture as the one call.  luma_done_event fires when luma is final: a copy of the luma plane taken
+    on a stream that waits for that event alone, while the chroma phases still run, is the oracle's luma."""
+    import torch
+    seed, w, h, ctb = 73, 416, 240, 6
+    pic = synth.full_picture(seed, w, h, ctb_log2=ctb, lmcs=True, intra_fraction=0.4)
+    want = oracle_to_intra(pic)
+    it, rs, ia = pic["inter"], pic["residual"], pic["intra"]
+    dev = util.to_device_planes([np.zeros((hh, ww), np.uint16) for (ww, hh) in pic["dims"]], torch)
+    dpl = lib.device_planes(dev)
+    refs = [util.to_device_planes(r, torch) for r in it["refs"]]
+    blocks = torch.from_numpy(it["blocks"].view(np.uint8).reshape(-1)).cuda()
+    prof = torch.from_numpy(it["prof"].view(np.uint8).reshape(-1)).cuda() if len(it["prof"]) else None
+    fwd = torch.from_numpy(pic["lmcs"][0]).cuda()
+    res = [torch.full_like(t, 0x2b67) for t in dev]
+    rpl = lib.device_planes(res)
+    tbs = torch.from_numpy(rs["tbs"].view(np.uint8).reshape(-1)).cuda()
+    levels = torch.from_numpy(rs["levels"]).cuda()
+    cw, ch = (w + (1 << ctb) - 1) >> ctb, (h + (1 << ctb) - 1) >> ctb
+    if phased:
+        recs, counts = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h, phases=True)
+        iparams = lib.phased_params(ia["params"], counts)
+    else:
+        recs = lib.intra_schedule(ia["blocks"], ia["ctu_first"], cw, ch, ctb, w, h)
+        iparams = abi.IntraParams.from_buffer_copy(bytes(ia["params"]))
+    d_recs = torch.from_numpy(recs.view(np.uint8).reshape(-1)).cuda()
+    scratch = torch.zeros(lib.intra_scratch_bytes(w, h), dtype=torch.uint8, device="cuda")
+    side = [torch.full_like(t, 0x1234) for t in dev] if shadow else None
+    spl = lib.device_planes(side) if shadow else None
+    main, second = torch.cuda.current_stream(), torch.cuda.Stream()
+    luma_copy = torch.zeros_like(dev[0])
+    for _ in range(3):
+        for t in dev:
+            t.zero_()
+        lib.inter_batch(dpl, [lib.device_planes(r) for r in refs], blocks, len(it["blocks"]), it["params"], lmcs_fwd_lut=fwd, prof=prof)
+        second.wait_stream(main)                                   # the pre-pass needs the inter prediction ...
+        lib.intra_prepare(dpl, rpl, d_recs, len(recs), iparams, scratch, shadow=spl, stream=second.cuda_stream)
+        lib.residual_batch(dpl, levels, tbs, len(rs["tbs"]), rs["params"], residual=rpl)     # ... not the residual stage
+        main.wait_stream(second)
+        ev = torch.cuda.Event()
+        p2 = abi.IntraParams.from_buffer_copy(bytes(iparams))
+        p2.prepared = 1
+        p2.luma_done_event = ev.cuda_event if hasattr(ev, "cuda_event") else None
+        if p2.luma_done_event is None:
+            ev.record()                                            # (forces creation on older torch)
+            p2.luma_done_event = ev.cuda_event
+        lib.intra_picture(dpl, rpl, d_recs, len(recs), p2, scratch, shadow=spl)
+        second.wait_event(ev)
+        with torch.cuda.stream(second):
+            luma_copy.copy_(dev[0])
+        torch.cuda.synchronize()
+        got = util.from_device_planes(dev)
+        for c in range(3):
+            assert np.array_equal(got[c], want[c]), "plane %d differs" % c
+        assert np.array_equal(luma_copy.cpu().numpy().view(np.uint16), want[0])
