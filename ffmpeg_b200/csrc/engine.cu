@@ -77,6 +77,12 @@ struct Lane {
     DevPicture residual;           // int16 residual of intra / CIIP blocks, between stage RESIDUAL and stage INTRA (lazy)
     DevBuffer intra_marks;
     cudaEvent_t tail = nullptr;    // "everything this lane has queued so far", recorded when the other lane must get behind it
+    // Two things inside a picture need not wait for the stage before them and go to a helper stream: the intra pre-pass
+    // (needs the inter prediction, runs beside the residual kernels) and luma deblocking (needs final luma, runs beside the
+    // chroma phases of the intra stage).  Both are joined back into the lane's stream before anything reads their output.
+    cudaStream_t helper = nullptr;
+    cudaEvent_t inter_done = nullptr, luma_done = nullptr, helper_done = nullptr;
+    bool have_inter = false, luma_pending = false;   // of the lane's current picture
 };
 constexpr int kLanes = 2, kSets = 4;   // two descriptor sets per lane: the next picture of a lane uploads while this one runs
 struct StageSet {
@@ -339,6 +345,10 @@ int vvcb200_ctx_create(VVCB200Ctx **out, int device, int width, int height, int 
     for (int i = 0; i < kLanes && e == cudaSuccess; i++) {
         e = cudaStreamCreateWithFlags(&c->lanes[i].stream, cudaStreamNonBlocking);
         if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->lanes[i].tail, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&c->lanes[i].helper, cudaStreamNonBlocking);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->lanes[i].inter_done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->lanes[i].luma_done, cudaEventDisableTiming);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&c->lanes[i].helper_done, cudaEventDisableTiming);
     }
     for (int i = 0; i < kSets && e == cudaSuccess; i++) {
         c->sets[i].lane = &c->lanes[lane_of(i)];
@@ -427,6 +437,9 @@ void vvcb200_ctx_destroy(VVCB200Ctx *c)
     for (Lane &l : c->lanes) {
         if (l.stream) fork_streams_release(l.stream);
         if (l.tail) cudaEventDestroy(l.tail);
+        if (l.helper) { cudaStreamSynchronize(l.helper); cudaStreamDestroy(l.helper); }
+        for (cudaEvent_t ev : { l.inter_done, l.luma_done, l.helper_done })
+            if (ev) cudaEventDestroy(ev);
         l.intra_marks.release();
         if (l.scratch.base) cudaFree(l.scratch.base);
         if (l.residual.base) cudaFree(l.residual.base);
@@ -558,6 +571,7 @@ int vvcb200_pic_begin(VVCB200Ctx *c, int slot)
     c->cur = slot;
     c->set = (c->set + 1) % kSets;
     StageSet &s = c->sets[c->set];
+    s.lane->have_inter = s.lane->luma_pending = false;
     if (s.in_use)                         // uploads of this picture must not overtake the kernels of the picture before last
         VVC_CUDA(cudaStreamWaitEvent(c->h2d, s.consumed, 0));
     return order_before_write(c, slot);
@@ -790,6 +804,8 @@ int vvcb200_pic_inter(VVCB200Ctx *c, const VVCB200PredBlock *blocks, int n, cons
     if (int r = vvcb200_inter_batch(&c->dpb[c->cur].planes, refs, n_refs, (const VVCB200PredBlock *)S.blocks.p, n, params,
                                     d_lut, nullptr, d_mv, d_prof, S.lane->stream))
         return r;
+    VVC_CUDA(cudaEventRecord(S.lane->inter_done, S.lane->stream));
+    S.lane->have_inter = true;
     if (int r = set_consumed(c))
         return r;
     if (refined_mv) {   // DMVR feedback for the host's MV derivation of later pictures (vvc_inter.c:750-762), on the
@@ -946,19 +962,40 @@ int vvcb200_pic_intra(VVCB200Ctx *c, const VVCB200IntraBlock *blocks, const uint
         return r;
     if (int r = uploads_visible(c))
         return r;
+    // The record order and the pre-pass need the records and the inter prediction, not the residual stage: on a picture
+    // that had an INTER call they go to the lane's helper stream, behind that call only, and run beside the residual kernels
+    // (everything older on the lane — the previous picture's use of the marks and of the scratch picture — lies before it).
+    Lane &L = *S.lane;
+    const bool beside = L.have_inter;
+    cudaStream_t ps = beside ? L.helper : L.stream;
+    if (beside) {
+        VVC_CUDA(cudaStreamWaitEvent(L.helper, S.uploaded, 0));
+        VVC_CUDA(cudaStreamWaitEvent(L.helper, L.inter_done, 0));
+    }
     if (int r = vvcb200_intra_schedule_device((const VVCB200IntraBlock *)S.iblocks_in.p, (const uint32_t *)S.ctu_first.p, n, ctus_w,
                                               ctus_h, (VVCB200IntraBlock *)S.iblocks.p, (int32_t *)S.phase_counts.p,
-                                              S.sched_scratch.p, S.lane->stream))
+                                              S.sched_scratch.p, ps))
         return r;
     VVCB200IntraParams phased = *params;
     phased.n_luma = phased.n_add_only = 0;
     phased.d_phase_counts = (const int32_t *)S.phase_counts.p;
+    phased.prepared = 0;
+    phased.luma_done_event = L.luma_done;             // luma deblocking starts there (vvcb200_pic_deblock)
     if (int r = ensure_residual(c, S.lane))           // (a picture without stored residuals still hands the planes over)
         return r;
     // the loop filters' scratch picture is idle until SAO: it keeps the prediction of the blocks rewritten in place
-    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, &S.lane->residual.planes, &S.lane->scratch.planes,
-                                      (const VVCB200IntraBlock *)S.iblocks.p, n, &phased, S.lane->intra_marks.p, S.lane->stream))
+    if (beside) {
+        if (int r = vvcb200_intra_prepare(&c->dpb[c->cur].planes, &L.residual.planes, &L.scratch.planes,
+                                          (const VVCB200IntraBlock *)S.iblocks.p, n, &phased, L.intra_marks.p, ps))
+            return r;
+        VVC_CUDA(cudaEventRecord(L.helper_done, L.helper));
+        VVC_CUDA(cudaStreamWaitEvent(L.stream, L.helper_done, 0));
+        phased.prepared = 1;
+    }
+    if (int r = vvcb200_intra_picture(&c->dpb[c->cur].planes, &L.residual.planes, &L.scratch.planes,
+                                      (const VVCB200IntraBlock *)S.iblocks.p, n, &phased, L.intra_marks.p, L.stream))
         return r;
+    L.luma_pending = true;
     return set_consumed(c);
 }
 
@@ -1043,7 +1080,20 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
         if (int r = settle_picture(c))
             return r;
     const uint16_t *lut = c->lmcs_pending ? (const uint16_t *)S.lut_inv.p : nullptr;
-    if (int r = vvcb200_deblock_lmcs_picture(&S.lane->scratch.planes, &c->dpb[c->cur].planes, &dt, params, lut, S.lane->stream))
+    Lane &L = *S.lane;
+    if (L.luma_pending) {
+        // the intra stage left an event where luma became final: the luma half starts there, on the helper stream, beside
+        // the stage's chroma phases; the chroma half follows the stage on the lane
+        L.luma_pending = false;
+        VVC_CUDA(cudaStreamWaitEvent(L.helper, S.uploaded, 0));
+        VVC_CUDA(cudaStreamWaitEvent(L.helper, L.luma_done, 0));
+        if (int r = vvcb200_deblock_lmcs_planes(&L.scratch.planes, &c->dpb[c->cur].planes, &dt, params, lut, 1, L.helper))
+            return r;
+        if (int r = vvcb200_deblock_lmcs_planes(&L.scratch.planes, &c->dpb[c->cur].planes, &dt, params, lut, 2, L.stream))
+            return r;
+        VVC_CUDA(cudaEventRecord(L.helper_done, L.helper));
+        VVC_CUDA(cudaStreamWaitEvent(L.stream, L.helper_done, 0));
+    } else if (int r = vvcb200_deblock_lmcs_picture(&L.scratch.planes, &c->dpb[c->cur].planes, &dt, params, lut, L.stream))
         return r;
     c->lmcs_pending = false;
     c->in_scratch = true;

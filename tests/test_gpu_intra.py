@@ -288,10 +288,9 @@ def test_pre_pass_beside_the_residual_stage_and_the_luma_done_event(shadow, phas
         ev = torch.cuda.Event()
         p2 = abi.IntraParams.from_buffer_copy(bytes(iparams))
         p2.prepared = 1
-        p2.luma_done_event = ev.cuda_event if hasattr(ev, "cuda_event") else None
-        if p2.luma_done_event is None:
-            ev.record()                                            # (forces creation on older torch)
-            p2.luma_done_event = ev.cuda_event
+        ev.record()                                                # (torch creates the CUDA event on its first record)
+        p2.luma_done_event = ev.cuda_event
+        assert p2.luma_done_event
         lib.intra_picture(dpl, rpl, d_recs, len(recs), p2, scratch, shadow=spl)
         second.wait_event(ev)
         with torch.cuda.stream(second):
