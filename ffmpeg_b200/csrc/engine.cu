@@ -1081,9 +1081,11 @@ int vvcb200_pic_deblock(VVCB200Ctx *c, const VVCB200DeblockTables *t, const VVCB
             return r;
     const uint16_t *lut = c->lmcs_pending ? (const uint16_t *)S.lut_inv.p : nullptr;
     Lane &L = *S.lane;
-    if (L.luma_pending) {
+    if (L.luma_pending && L.have_inter) {
         // the intra stage left an event where luma became final: the luma half starts there, on the helper stream, beside
-        // the stage's chroma phases; the chroma half follows the stage on the lane
+        // the stage's chroma phases; the chroma half follows the stage on the lane.  (Pictures with inter units only: on an
+        // all-intra picture the chroma wavefront is a dependency chain, and a grid that takes SMs from its pollers costs
+        // more than it hides — 11.1 instead of 10.0 ms at 8K.)
         L.luma_pending = false;
         VVC_CUDA(cudaStreamWaitEvent(L.helper, S.uploaded, 0));
         VVC_CUDA(cudaStreamWaitEvent(L.helper, L.luma_done, 0));
