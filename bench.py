@@ -546,7 +546,7 @@ def main():
 
     def step(i, ev=None, lane=None):
         """One picture.  lane: the stream it is queued on (None: torch's current stream, with stage events)."""
-        split = len(irecs) > 0 and (split_mode == 2 or (split_mode == 1 and lane is None))
+        split = len(irecs) > 0 and n_blocks > 0 and (split_mode == 2 or (split_mode == 1 and lane is None))   # (as Level B: pictures with inter units)
         s = sets[i % rot]
         q = lane.cuda_stream if lane is not None else None
         main = lane if lane is not None else torch.cuda.current_stream()
