@@ -17,6 +17,10 @@ static void *grow(VVCB200EmitBatch *b, void *p, int *cap, int need, size_t elem)
 {
     if (need <= *cap)
         return p;
+    if (b->fixed) {                          /* the arrays are the caller's (an arena region): they do not move */
+        b->error = VVCB200_ERR_TOO_BIG;
+        return p;
+    }
     int want = *cap ? *cap * 2 : 1024;
     while (want < need)
         want *= 2;
@@ -38,6 +42,10 @@ void vvcb200_emit_reset(VVCB200EmitBatch *b)
 
 void vvcb200_emit_free(VVCB200EmitBatch *b)
 {
+    if (b->fixed) {
+        memset(b, 0, sizeof(*b));
+        return;
+    }
     free(b->blocks);
     free(b->prof);
     free(b->tbs);
@@ -301,6 +309,10 @@ VVCB200IntraBlock *vvcb200_emit_new_iblock(VVCB200EmitBatch *b)
 int16_t *vvcb200_emit_levels(VVCB200EmitBatch *b, int n, uint32_t *off)
 {
     if (b->n_levels + (size_t)n > b->cap_levels) {
+        if (b->fixed) {
+            b->error = VVCB200_ERR_TOO_BIG;
+            return NULL;
+        }
         size_t want = b->cap_levels ? b->cap_levels * 2 : 1 << 16;
         while (want < b->n_levels + (size_t)n)
             want *= 2;

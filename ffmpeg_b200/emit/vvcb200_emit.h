@@ -41,6 +41,9 @@ typedef struct VVCB200EmitBatch {
     uint32_t *ctu_first;               /* ctb_count + 1 entries once every CTU has been emitted (raster order) */
     int n_ctus, cap_ctus;
     int error;                         /* sticky: out of memory, or a unit the engine does not take */
+    int fixed;                         /* the arrays and their cap_* are the caller's — regions of a vvcb200_ctx_arena_alloc
+                                          block, so that a stage's arrays upload as one copy; a full array sets error to
+                                          VVCB200_ERR_TOO_BIG instead of growing, vvcb200_emit_free() frees nothing */
 } VVCB200EmitBatch;
 
 void vvcb200_emit_reset(VVCB200EmitBatch *b);     /* keep the arrays, forget their content */

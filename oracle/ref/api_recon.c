@@ -503,12 +503,29 @@ VVCREF_EXPORT int vvcref_emit_recon_picture(int width, int height, const VVCRefC
     VVCRefPlanes pl = { { NULL, NULL, NULL }, { 0, 0, 0 }, { width, width / 2, width / 2 }, { height, height / 2, height / 2 } };
     int ret;
 
+    if (with_refs & 2) {
+        /* the caller's arrays as the batch (VVCB200EmitBatch.fixed): what a decoder does with regions of a context arena */
+        batch.fixed = 1;
+        batch.tbs = tbs; batch.cap_tbs = cap_tbs;
+        batch.levels = levels; batch.cap_levels = cap_levels;
+        batch.iblocks = iblocks; batch.cap_iblocks = cap_iblocks;
+        batch.ctu_first = ctu_first; batch.cap_ctus = cap_ctus;
+    }
     g_emit_recon = &batch;
     /* CIIP units want a reference picture list to exist; the emitter never follows it */
-    ret = vvcref_recon_picture(&pl, cus, n_cus, tus, in_tbs, in_levels, params, ip, 1, with_refs ? &pl : NULL, 0, inter, NULL);
+    ret = vvcref_recon_picture(&pl, cus, n_cus, tus, in_tbs, in_levels, params, ip, 1, (with_refs & 1) ? &pl : NULL, 0, inter, NULL);
     g_emit_recon = NULL;
     if (!ret && batch.error)
-        ret = -1;
+        ret = batch.error == VVCB200_ERR_TOO_BIG ? -2 : -1;
+    if (batch.fixed) {
+        if (!ret) {
+            *n_tbs = batch.n_tbs;
+            *n_levels = (int)batch.n_levels;
+            *n_iblocks = batch.n_iblocks;
+            *n_ctus = batch.n_ctus;
+        }
+        return ret;
+    }
     if (!ret && (batch.n_tbs > cap_tbs || batch.n_levels > (size_t)cap_levels || batch.n_iblocks > cap_iblocks ||
                  batch.n_ctus + 1 > cap_ctus))
         ret = -2;

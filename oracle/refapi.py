@@ -253,7 +253,7 @@ def emit_inter_cus(width, height, cus, sb_mv, params, order=False):
     return blocks[:nb.value].copy(), prof[:npf.value].copy(), p
 
 
-def emit_recon_picture(width, height, ref, intra_params, inter=None):
+def emit_recon_picture(width, height, ref, intra_params, inter=None, fixed=False, shrink=0):
     """synth's CU / TU arrays -> the reference's CTU / CodingUnit / TransformUnit / TransformBlock lists and
     per-min-CB tables (as recon_picture builds them) -> the product's RECON emitter (ffmpeg_b200/emit/vvcb200_emit_recon.h)
     -> (tbs, levels, intra blocks, ctu_first).  `inter`: the picture's inter dict when it has CIIP units."""
@@ -262,14 +262,16 @@ def emit_recon_picture(width, height, ref, intra_params, inter=None):
     in_lv = np.ascontiguousarray(ref["levels"], np.int16)
     n_ctus = ((width + (1 << intra_params.ctb_log2_size) - 1) >> intra_params.ctb_log2_size) * \
              ((height + (1 << intra_params.ctb_log2_size) - 1) >> intra_params.ctb_log2_size)
-    tbs = np.zeros(len(in_tbs) + 1, abi.TB_DTYPE)
+    # fixed: the emitter writes straight into these arrays (VVCB200EmitBatch.fixed) instead of growing its own; shrink: make
+    # the TB array that much too small
+    tbs = np.zeros(len(in_tbs) + 1 - shrink, abi.TB_DTYPE)
     lv = np.zeros(len(in_lv) + 1, np.int16)
     ibs = np.zeros(4 * len(cus) + 16, abi.IB_DTYPE)
     first = np.zeros(n_ctus + 2, np.uint32)
     nt, nl, ni, nc = C.c_int(0), C.c_int(0), C.c_int(0), C.c_int(0)
     p = lambda a: C.c_void_p(a.ctypes.data)
     r = lib().vvcref_emit_recon_picture(int(width), int(height), p(cus), len(cus), p(tus), p(in_tbs), p(in_lv),
-                                        C.byref(ref["params"]), C.byref(intra_params), int(inter is not None),
+                                        C.byref(ref["params"]), C.byref(intra_params), int(inter is not None) | (2 if fixed else 0),
                                         C.byref(inter["params"]) if inter is not None else None,
                                         p(tbs), len(tbs), C.byref(nt), p(lv), len(lv), C.byref(nl),
                                         p(ibs), len(ibs), C.byref(ni), p(first), len(first), C.byref(nc))

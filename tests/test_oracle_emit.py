@@ -123,3 +123,15 @@ def test_refined_vectors_go_back_into_the_dmvr_table():
     dm = (pic["blocks"]["flags"] & abi.PB_DMVR) != 0
     assert dm.sum() > 20 and np.any(mv[dm] != pic["blocks"]["mv"][dm])       # DMVR moved something
     assert bad == 0
+
+
+def test_recon_emitter_into_caller_arrays():
+    """VVCB200EmitBatch.fixed: the arrays are regions the caller owns (a context arena): same records, nothing allocated;
+    an array that is too small is an error (VVCB200_ERR_TOO_BIG), not a write past its end."""
+    w, h = 416, 240
+    pic = synth.recon_picture(11, w, h, tools=("mrl", "mip", "cclm", "isp", "mts", "lfnst", "joint"), intra_fraction=0.7)
+    tbs, lv, ibs, first = refapi.emit_recon_picture(w, h, pic["ref"], pic["intra"]["params"], fixed=True)
+    assert tbs.tobytes() == pic["ref"]["tbs"].tobytes() and np.array_equal(lv, pic["ref"]["levels"])
+    assert ibs.tobytes() == pic["intra"]["blocks"].tobytes() and np.array_equal(first, pic["intra"]["ctu_first"])
+    with pytest.raises(RuntimeError, match="-2"):
+        refapi.emit_recon_picture(w, h, pic["ref"], pic["intra"]["params"], fixed=True, shrink=5)
