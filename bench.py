@@ -38,6 +38,27 @@ L2_BYTES = 126 * 1024 * 1024
 STAGES = ["inter", "residual", "intra", "deblock", "sao_alf"]
 
 
+def bind_near_gpu(local_rank):
+    """One process per GPU: run (and, by first touch, allocate pinned host memory) on the cores of the GPU's NUMA node —
+    uploads and downloads that cross the socket interconnect share it with every other rank's.  Returns the cores or None."""
+    if env_int("VVCB200_BENCH_NO_BIND", 0):
+        return None
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+        words = (os.cpu_count() + 63) // 64
+        mask = pynvml.nvmlDeviceGetCpuAffinity(h, words)
+        cpus = [64 * w + b for w in range(words) for b in range(64) if (mask[w] >> b) & 1]
+        allowed = sorted(set(cpus) & os.sched_getaffinity(0))
+        if allowed and len(allowed) < len(os.sched_getaffinity(0)):
+            os.sched_setaffinity(0, allowed)
+            return allowed
+    except Exception:
+        pass
+    return None
+
+
 def env_int(name, default):
     try:
         return int(os.environ.get(name, default))
@@ -459,8 +480,10 @@ def main():
     pipeline = util
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl ours needs a CUDA device: the engine has no CPU fallback")
+    bound = bind_near_gpu(local)
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries the one JSON line and nothing else
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -494,6 +517,8 @@ def main():
     rot = max(2, int(np.ceil(2.2 * L2_BYTES / per_set)))
     n_lanes = env_int("VVCB200_BENCH_LANES", 2)
     rot = -(-rot // n_lanes) * n_lanes               # a multiple of the lanes: a working set always meets the same lane (stream)
+    detail["host_cores"] = ("rank bound to the %d cores of its GPU's NUMA node (pinned memory is then local to the GPU)" % len(bound)
+                            if bound else "not bound (one NUMA node, or no NVML)")
     detail["l2"] = "rotating %d complete working sets (%.0f MB, each with its own reference pictures) > 126 MB L2" % (
         rot, rot * per_set / 1e6)
     detail["lanes"] = ("consecutive pictures alternate between two CUDA streams (independent pictures, as the B pictures of "
@@ -725,7 +750,7 @@ def main():
                          "gpu_md5": dev_md5, "e2e_md5": e2e_ok,
                          "checker": "per-plane MD5 of the reference C's picture (the cpu_baseline leg) against the device-resident "
                                     "arm's and the end-to-end arm's"}
-    print(json.dumps(out))
+    print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
     return 0
