@@ -59,6 +59,29 @@ def bind_near_gpu(local_rank):
     return None
 
 
+_REAL_STDOUT = None
+
+
+def stdout_for_the_json_line_only():
+    """Libraries print to file descriptor 1 on their own (NCCL its version line): from here on fd 1 is stderr, and
+    emit_line() writes the one JSON line to what stdout was."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, line)
+
+
 def env_int(name, default):
     try:
         return int(os.environ.get(name, default))
@@ -409,7 +432,7 @@ def bench_tx(args, rank, world, local):
                                "sample": "%d whole batches, TBs dealt round-robin to %d threads" % (n_cpu, threads)}
         out["parity"] = {"md5_match": got == ref, "ref_md5": ref, "gpu_md5": got}
     if rank == 0:
-        print(json.dumps(out))
+        emit_line(out)
     return 0
 
 
@@ -470,7 +493,7 @@ def main():
                                 "sample": "each step = one whole picture through the full stage chain"},
                "e2e": {"value": v, "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                "gpu_launches": 0}
-        print(json.dumps(out))
+        emit_line(out)
         return 0
 
     import torch
@@ -483,7 +506,7 @@ def main():
     bound = bind_near_gpu(local)
     torch.cuda.set_device(local)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")      # stdout carries the one JSON line and nothing else
+        stdout_for_the_json_line_only()
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
     def barrier():
@@ -750,7 +773,7 @@ def main():
                          "gpu_md5": dev_md5, "e2e_md5": e2e_ok,
                          "checker": "per-plane MD5 of the reference C's picture (the cpu_baseline leg) against the device-resident "
                                     "arm's and the end-to-end arm's"}
-    print(json.dumps(out), flush=True)
+    emit_line(out)
     if world > 1:
         dist.destroy_process_group()
     return 0
