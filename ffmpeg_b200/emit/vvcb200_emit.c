@@ -256,6 +256,48 @@ void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params)
     }
     for (int i = 0; i < n; i++)
         key[i] = block_key(&b->blocks[i]);
+    /* A picture has a few dozen distinct keys (width class x tool set x prediction direction): count per key and scatter —
+     * stable, two passes over the records.  (The general merge sort below takes over if there are more than kMaxKeys.) */
+    {
+        enum { kMaxKeys = 1024 };
+        long long dk[kMaxKeys];
+        int count[kMaxKeys + 1], nd = 0, ok = 1;
+        for (int i = 0; i < n && ok; i++) {
+            int lo = 0, hi = nd;
+            while (lo < hi) {
+                const int mid = (lo + hi) >> 1;
+                if (dk[mid] < key[i]) lo = mid + 1; else hi = mid;
+            }
+            if (lo == nd || dk[lo] != key[i]) {
+                if (nd == kMaxKeys) {
+                    ok = 0;
+                    break;
+                }
+                memmove(&dk[lo + 1], &dk[lo], (size_t)(nd - lo) * sizeof(dk[0]));
+                dk[lo] = key[i];
+                nd++;
+            }
+        }
+        if (ok) {
+            int *bucket = (int *)ktmp;                       /* (ktmp is as large as the keys: room for n ints) */
+            memset(count, 0, sizeof(int) * (size_t)(nd + 1));
+            for (int i = 0; i < n; i++) {
+                int lo = 0, hi = nd;
+                while (lo < hi) {
+                    const int mid = (lo + hi) >> 1;
+                    if (dk[mid] < key[i]) lo = mid + 1; else hi = mid;
+                }
+                bucket[i] = lo;
+                count[lo + 1]++;
+            }
+            for (int k = 0; k < nd; k++)
+                count[k + 1] += count[k];
+            for (int i = 0; i < n; i++)
+                tmp[count[bucket[i]]++] = b->blocks[i];
+            memcpy(b->blocks, tmp, (size_t)n * sizeof(*tmp));
+            goto sorted;
+        }
+    }
     /* bottom-up merge sort: stable, O(n log n), no recursion */
     VVCB200PredBlock *src = b->blocks, *dst = tmp;
     long long *ks = key, *kd = ktmp;
@@ -275,6 +317,7 @@ void vvcb200_emit_order_blocks(VVCB200EmitBatch *b, VVCB200InterParams *params)
     }
     if (src != b->blocks)
         memcpy(b->blocks, src, (size_t)n * sizeof(*src));
+sorted:
     params->n_w16 = params->n_w8 = 0;
     for (int i = 0; i < n; i++) {
         params->n_w16 += b->blocks[i].w == 16;
