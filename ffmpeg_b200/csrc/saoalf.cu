@@ -140,9 +140,11 @@ __device__ __forceinline__ uint4 sao_chunk(const SaoAlfArgs &a, const PlaneWin &
     const int cw = min(1 << l2, W - cx0), ch = min(1 << l2, H - cy0);
     bool slow = x + 8 > W;
     if (type == VVCB200_SAO_EDGE) {
-        const bool side = x == cx0 || x + 8 >= cx0 + cw || y == cy0 || y == cy0 + ch - 1;
-        const bool border = cx0 == 0 || cy0 == 0 || cx0 + cw == W || cy0 + ch == H;
-        slow = slow || (side && (border || pp->no_filter));
+        // only the chunks on a CTB side that is a picture border or carries a no-filter flag (its own or a corner's)
+        const int nf = pp->no_filter;
+        const bool left = cx0 == 0 || (nf & (1 | 16 | 128)), right = cx0 + cw == W || (nf & (2 | 32 | 64));
+        const bool top = cy0 == 0 || (nf & (4 | 16 | 32)), bottom = cy0 + ch == H || (nf & (8 | 64 | 128));
+        slow = slow || (x == cx0 && left) || (x + 8 >= cx0 + cw && right) || (y == cy0 && top) || (y == cy0 + ch - 1 && bottom);
     }
     const uint32_t cw4[4] = { vc.x, vc.y, vc.z, vc.w };
     uint32_t out[4];
