@@ -64,6 +64,8 @@ def main():
         "all": np.ones(len(b), bool),
         "regular": (f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY)) == 0,
         "regular_plain": (f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY | abi.PB_DMVR | abi.PB_BDOF)) == 0,
+        "plain_uni": ((f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY | abi.PB_DMVR | abi.PB_BDOF)) == 0) & (b["pred_flag"] != 3),
+        "plain_bi": ((f & (abi.PB_AFFINE | abi.PB_GPM | abi.PB_CHROMA_ONLY | abi.PB_LUMA_ONLY | abi.PB_DMVR | abi.PB_BDOF)) == 0) & (b["pred_flag"] == 3),
         "dmvr": (f & abi.PB_DMVR) != 0,
         "bdof_only": ((f & abi.PB_BDOF) != 0) & ((f & abi.PB_DMVR) == 0),
         "affine_luma": (f & abi.PB_LUMA_ONLY) != 0,
