@@ -27,7 +27,7 @@ def load():
         _lib = C.CDLL(SO)
         _lib.vvcb200_last_error.restype = C.c_char_p
         _lib.vvcb200_launch_count.restype = C.c_uint64
-        if _lib.vvcb200_abi_version() != 1:
+        if _lib.vvcb200_abi_version() != 2:
             raise VVCB200Error("ABI version mismatch")
     return _lib
 

@@ -30,7 +30,7 @@
 extern "C" {
 #endif
 
-#define VVCB200_ABI_VERSION 1
+#define VVCB200_ABI_VERSION 2   /* 2: VVCB200IntraParams grew (prepared, luma_done_event), VVCB200InterParams.dmvr_first, VVCB200_TB_LEVELS8 */
 #if defined(__GNUC__)
 #define VVCB200_API __attribute__((visibility("default")))
 #else

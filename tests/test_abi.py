@@ -28,7 +28,7 @@ def test_library_exports_every_declared_symbol():
 
 def test_abi_version_and_error_string():
     l = lib.load()
-    assert l.vvcb200_abi_version() == 1
+    assert l.vvcb200_abi_version() == 2
     assert isinstance(l.vvcb200_last_error(), bytes)
 
 
