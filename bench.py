@@ -691,7 +691,7 @@ def main():
                       validate=1)                                         # the library's default batch checks
     ep = pipeline.EnginePicture(ctx, pic)
     ep.upload_refs()                       # reference pictures are earlier outputs of the same decoder: resident
-    e2e_steps = max(3, min(args.steps, 100))
+    e2e_steps = max(60, min(args.steps, 100))         # (a pipeline of four pictures: fewer than that measures its fill and drain)
 
     def e2e_run(n, **kw):
         for _ in range(8):                   # twice round the context's four descriptor sets and four picture slots
